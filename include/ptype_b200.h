@@ -1,0 +1,311 @@
+/*
+ * ptype_b200.h — C ABI of the B200 batched-RPC-dispatch path for edegens/ptype.
+ *
+ * This is the whole drop-in boundary: plain C, plain pointers and sizes, `int`
+ * status returns (0 = OK, never an exception), no torch / C++ types.  A Go host
+ * binds it through cgo; this repo's tests and bench bind it
+ * through Python ctypes.  Citations are file:line in the reference tree
+ * (edegens/ptype) and name the code each item replaces or mirrors.
+ *
+ * One batch = N independent calls.  For each call the device does what one
+ *   cluster.(*Client).Call               (cluster/rpc.go:59-67)
+ * does through net/rpc today:
+ *   1. find the service's node list in the registry snapshot
+ *        etcdRegistry.Services / nodes   (cluster/registry.go:93-117,152-166)
+ *   2. apply the node-selection rule
+ *        selectNodes + hashConnectionIndex (cluster/rpc.go:252-270)
+ *        roundRobinSelect                  (cluster/rpc.go:176-183)
+ *   3. resolve "Receiver.Method" the way the net/rpc server does
+ *        (Go 1.13 stdlib net/rpc; call sites example/calculator/server/server.go:16-20)
+ *   4. run the method body
+ *        Calculator.Multiply             (example/calculator/calculator.go:9-12)
+ *        Calculator.Add                  (not in the reference)
+ *        Prime.Check                     (example/optimus/prime.go:15-25)
+ *   5. pack a fixed-size reply record.
+ */
+#ifndef PTYPE_B200_H
+#define PTYPE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PTYPE_B200_ABI_VERSION 1
+
+/* ------------------------------------------------------------------ records */
+
+/* One call attempt.  48 bytes, 16-byte aligned: three 128-bit loads.
+ * Replaces the (serviceMethod, args) pair of Client.Call (cluster/rpc.go:59)
+ * plus the balancer's sequence number (cluster/rpc.go:181). */
+typedef struct ptype_req {
+    uint64_t svc_key; /* ptype_b200_service_key(cluster service name): the name a
+                         Client was created for (cluster/cluster.go:101-103)       */
+    uint64_t seq;     /* value atomic.AddUint64(&c.seq,1) returned for this attempt
+                         (cluster/rpc.go:181); a batch of N on one Client carries
+                         base+1 .. base+N                                           */
+    uint32_t method;  /* FNV-1a-32 of the whole "Receiver.Method" string           */
+    uint32_t recv;    /* FNV-1a-32 of the text before the last '.', or
+                         PTYPE_RECV_ILL_FORMED when the string has no '.'          */
+    int64_t a0, a1, a2; /* calculator.Args{A,B} (example/calculator/calculator.go:3-5)
+                           or prime.Args{Min,Max,Target} (example/optimus/prime.go:7-11) */
+} ptype_req;
+
+/* One reply.  16 bytes: one 128-bit store; reply j belongs to request j. */
+typedef struct ptype_reply {
+    int64_t value;   /* *reply; 0 when status != OK (the caller's reply is left
+                        untouched on error, cluster/rpc_test.go:160-186)          */
+    uint32_t node;   /* routing decision: global node id in the snapshot (rank of the
+                        node's key in the sorted `services` range), or PTYPE_NO_NODE */
+    uint32_t status; /* enum ptype_status                                          */
+} ptype_reply;
+
+#define PTYPE_NO_NODE 0xFFFFFFFFu
+#define PTYPE_RECV_ILL_FORMED 0xFFFFFFFFu
+
+/* Per-call status.  What the Go caller would have seen from Client.Call. */
+enum ptype_status {
+    PTYPE_ST_OK = 0,
+    PTYPE_ST_NO_SERVICE = 1,        /* service absent from the snapshot: its watch delivers an
+                                       empty list, Call returns ErrNoClientAvailable
+                                       (cluster/rpc.go:16,62-64,178-180)                        */
+    PTYPE_ST_NO_CLIENT = 2,         /* service present with an empty list (same Go error)       */
+    PTYPE_ST_ILL_FORMED = 3,        /* "rpc: service/method request ill-formed: X" [net/rpc]    */
+    PTYPE_ST_CANT_FIND_SERVICE = 4, /* "rpc: can't find service X" [net/rpc]                    */
+    PTYPE_ST_CANT_FIND_METHOD = 5,  /* "rpc: can't find method X" [net/rpc]                     */
+    PTYPE_ST_BAD_INDEX = 6,         /* seq >= 2^63 and int(seq)%k != 0: clients[negative] panics
+                                       in Go (cluster/rpc.go:182)                               */
+    PTYPE_ST_RANGE_LIMIT = 7,       /* Prime.Check range wider than the context's iteration
+                                       limit; not executed (no counterpart: the reference
+                                       would loop, sleeping 250 ms per step, prime.go:16-17)   */
+    PTYPE_ST__COUNT = 8
+};
+
+/* Built-in method bodies (opcodes in the image's method table). */
+enum ptype_opcode {
+    PTYPE_OP_NONE = 0,
+    PTYPE_OP_MULTIPLY = 1, /* example/calculator/calculator.go:9-12 */
+    PTYPE_OP_ADD = 2,      /* SURVEY.md D1 */
+    PTYPE_OP_CHECK = 3     /* example/optimus/prime.go:15-25 (sleep dropped) */
+};
+
+/* ------------------------------------------------------- registry image blob */
+/* Little-endian, position independent, self-describing; the same bytes go to
+ * every GPU (H2D or ncclBroadcast).  It is the device form of what
+ * Registry.Services() returns (cluster/registry.go:93-117) plus the inputs of
+ * the selection rule (localAddr, ConnConfig.MaxConnections; cluster/rpc.go:19-38,128). */
+
+#define PTYPE_IMAGE_MAGIC 0x49595450u /* "PTYI" */
+#define PTYPE_IMAGE_VERSION 1u
+#define PTYPE_SLOT_EMPTY 0xFFFFFFFFu
+#define PTYPE_MAX_RECEIVERS 8
+#define PTYPE_MAX_METHODS 32
+#define PTYPE_LOCAL_ADDR_MAX 64
+
+typedef struct ptype_image_header { /* 192 bytes */
+    uint32_t magic, version;
+    uint64_t epoch;          /* snapshot generation, chosen by the publisher          */
+    uint64_t total_bytes;    /* whole blob                                             */
+    uint64_t body_checksum;  /* FNV-1a-64 of blob[192 .. total_bytes)                  */
+    uint64_t key_salt;       /* xor-ed into the FNV-1a-64 offset basis (0 = plain FNV) */
+    uint32_t n_services;     /* occupied slots                                         */
+    uint32_t n_slots;        /* open-addressing table size (any value >= 1)            */
+    uint32_t n_nodes;        /* global node array length                               */
+    uint32_t max_connections;/* ConnConfig.MaxConnections; 0 = mesh (rpc.go:20-22)     */
+    uint32_t n_conn_hash;    /* == max_connections                                     */
+    uint32_t n_methods;      /* <= PTYPE_MAX_METHODS                                   */
+    uint32_t n_receivers;    /* <= PTYPE_MAX_RECEIVERS                                 */
+    uint32_t off_slots;      /* ptype_slot[n_slots], 16-byte aligned                   */
+    uint32_t off_conn_hash;  /* uint32[n_conn_hash]: FNV-1a-32(localAddr+itoa(i))      */
+    uint32_t off_methods;    /* ptype_method[n_methods]                                */
+    uint32_t off_nodes;      /* ptype_node[n_nodes]      (host-side lookups only)      */
+    uint32_t off_services;   /* ptype_service[n_services](host-side lookups only)      */
+    uint32_t off_strings;    /* string pool, NUL-terminated entries                    */
+    uint32_t strings_bytes;
+    uint32_t device_bytes;   /* prefix of the blob the kernels read (slots, hashes, methods) */
+    uint32_t reserved[7];
+    char local_addr[PTYPE_LOCAL_ADDR_MAX]; /* the Client host's address string (cluster.go:69,82) */
+} ptype_image_header;
+
+/* One open-addressing slot, 16 bytes (one LDS.128 / LDG.128). */
+typedef struct ptype_slot {
+    uint64_t key;       /* ptype_b200_service_key(name, key_salt)                      */
+    uint32_t node_base; /* global id of the service's first node; PTYPE_SLOT_EMPTY = free */
+    uint32_t n_and_recv;/* bits 0..23: number of registered nodes n (sorted list length)
+                           bits 24..31: bitmask of receivers its nodes registered      */
+} ptype_slot;
+
+typedef struct ptype_method { /* 16 bytes */
+    uint32_t method_hash; /* FNV-1a-32("Receiver.Method") */
+    uint32_t recv_hash;   /* FNV-1a-32("Receiver")        */
+    uint32_t opcode;      /* enum ptype_opcode; PTYPE_OP_NONE = receiver-only entry */
+    uint32_t recv_bit;    /* bit index in ptype_slot.n_and_recv >> 24               */
+} ptype_method;
+
+typedef struct ptype_node { /* host-side: cluster.Node (cluster/registry.go:23-26) */
+    uint32_t address_off; /* into the string pool */
+    uint32_t name_off;    /* node name (last key element) */
+    uint32_t service;     /* index into ptype_service[] */
+    int32_t port;
+} ptype_node;
+
+typedef struct ptype_service { /* host-side, sorted by key bytes like the etcd range */
+    uint64_t key;
+    uint32_t name_off;
+    uint32_t node_base;
+    uint32_t n_nodes;
+    uint32_t recv_mask;
+} ptype_service;
+
+/* ------------------------------------------------------------------- errors */
+enum ptype_err {
+    PTYPE_OK = 0,
+    PTYPE_E_INVAL = 1,     /* bad argument                                   */
+    PTYPE_E_NOMEM = 2,
+    PTYPE_E_CUDA = 3,      /* a CUDA call failed; text via ptype_b200_last_error */
+    PTYPE_E_NO_IMAGE = 4,  /* dispatch before any publish_image              */
+    PTYPE_E_BAD_IMAGE = 5, /* magic / version / checksum / bounds            */
+    PTYPE_E_COLLISION = 6, /* builder could not find a collision-free salt   */
+    PTYPE_E_NCCL = 7,
+    PTYPE_E_LIMIT = 8,     /* size beyond a documented maximum               */
+    PTYPE_E_NOT_FOUND = 9,
+    PTYPE_E_BUSY = 10
+};
+const char* ptype_b200_strerror(int err);
+/* Text of the last CUDA/NCCL failure on the calling thread ("" if none). */
+const char* ptype_b200_last_error(void);
+int ptype_b200_abi_version(void);
+
+/* --------------------------------------------------------- hashing (host) */
+/* hash/fnv New32a / New64a [Go stdlib]; the only explicit hash in the reference
+ * is fnv.New32a at cluster/rpc.go:267. */
+uint32_t ptype_b200_fnv1a32(const void* data, size_t len);
+uint64_t ptype_b200_fnv1a64(const void* data, size_t len);
+/* Key of a cluster service name (the string passed to Cluster.NewClient,
+ * cluster/cluster.go:101).  salt comes from the image header (0 unless two
+ * registered names collide). */
+uint64_t ptype_b200_service_key(const char* service_name, uint64_t salt);
+/* Split "Receiver.Method" at the last '.' like net/rpc's server does and hash
+ * both parts.  No '.' → *recv = PTYPE_RECV_ILL_FORMED. */
+void ptype_b200_method_key(const char* service_method, uint32_t* method, uint32_t* recv);
+/* hashConnectionIndex (cluster/rpc.go:266-270). */
+uint32_t ptype_b200_conn_hash(const char* local_addr, int conn_number);
+
+/* --------------------------------------------------- image builder (host) */
+/* Collects what Registry.Register wrote (cluster/registry.go:51-86) and emits
+ * the blob.  Needs no GPU. */
+typedef struct ptype_builder ptype_builder;
+/* local_addr: the Client host's address (cluster/cluster.go:69,82; tests use "").
+ * max_connections: ConnConfig.MaxConnections (3 by default, 0 = mesh; <0 rejected). */
+int ptype_b200_builder_new(const char* local_addr, int max_connections, ptype_builder** out);
+/* One registered node = one etcd key services/<service>/<node_name>/ with value
+ * {"address":address,"port":port}.  Re-registering a key overwrites it. */
+int ptype_b200_builder_register(ptype_builder*, const char* service, const char* node_name,
+                                const char* address, int port);
+/* A service whose watch delivered an empty list (cluster/rpc_test.go:85-90). */
+int ptype_b200_builder_declare(ptype_builder*, const char* service);
+/* The nodes of `service` ran rpc.Register(new(<receiver>)) (server.go:16-17).
+ * Known receivers: "Calculator" {Multiply, Add}, "Prime" {Check}. */
+int ptype_b200_builder_expose(ptype_builder*, const char* service, const char* receiver);
+/* Override the open-addressing table size (must exceed the number of services).
+ * Default: half full, or sized to fill the kernel's shared-memory budget. */
+int ptype_b200_builder_set_slots(ptype_builder*, uint32_t n_slots);
+/* Emit the blob; caller frees with ptype_b200_image_free. */
+int ptype_b200_builder_finish(ptype_builder*, uint64_t epoch, void** image, size_t* bytes);
+void ptype_b200_builder_free(ptype_builder*);
+void ptype_b200_image_free(void* image);
+int ptype_b200_image_validate(const void* image, size_t bytes);
+/* Host-side view of a snapshot: what getSelectedNodes() (cluster/rpc.go:293-297)
+ * would hold for a Client of `service`.  selected[] receives up to cap global
+ * node ids; *k the list length. */
+int ptype_b200_image_selected(const void* image, const char* service, uint32_t* selected,
+                              size_t cap, uint32_t* k);
+/* cluster.Node of a global node id. */
+int ptype_b200_image_node(const void* image, uint32_t node_id, char* address, size_t address_cap,
+                          int* port, char* service, size_t service_cap, char* node_name,
+                          size_t node_name_cap);
+
+/* ------------------------------------------------------------------ context */
+typedef struct ptype_ctx ptype_ctx;
+/* Creates one stream set and a double-buffered image slot per listed CUDA
+ * device.  Entry points may be called from any OS thread (cgo): device state is
+ * held in the context, never in thread-locals. */
+int ptype_b200_open(const int* devices, int ndev, ptype_ctx** out);
+void ptype_b200_close(ptype_ctx*);
+int ptype_b200_device_count(int* out);
+
+/* Pinned host staging the caller may fill (Go slices must not be retained
+ * across an async call; this memory can). */
+void* ptype_b200_alloc_pinned(size_t bytes);
+void ptype_b200_free_pinned(void*);
+/* Device buffers for callers that keep batches resident in HBM. */
+int ptype_b200_device_alloc(ptype_ctx*, int dev, size_t bytes, void** out);
+int ptype_b200_device_free(ptype_ctx*, int dev, void* p);
+int ptype_b200_memcpy_h2d(ptype_ctx*, int dev, void* dst, const void* src, size_t bytes);
+int ptype_b200_memcpy_d2h(ptype_ctx*, int dev, void* dst, const void* src, size_t bytes);
+/* The cudaStream_t dispatches of device `dev` are ordered on (for event timing). */
+int ptype_b200_stream(ptype_ctx*, int dev, void** cuda_stream);
+
+/* Install a new snapshot on every device of the context: copy into the inactive
+ * image buffer, then flip at a batch boundary.  Mirrors the pointer swap of
+ * handleNewNodes (cluster/rpc.go:233-236).  An image with zero services is
+ * installed as given; "ignore empty updates" (rpc.go:204-206) is host policy. */
+int ptype_b200_publish_image(ptype_ctx*, const void* image, size_t bytes);
+int ptype_b200_epoch(ptype_ctx*, int dev, uint64_t* epoch);
+/* Copy of the blob last installed (on non-root ranks: the bytes NCCL delivered).
+ * *bytes in: capacity of out, out: size of the blob; PTYPE_E_LIMIT if too small. */
+int ptype_b200_current_image(ptype_ctx*, void* out, size_t* bytes);
+
+/* Multi-process (one process per GPU): NCCL is used only here.  Rank `root`
+ * passes the blob, the others pass NULL/0; every rank ends with the same
+ * snapshot installed.  The 128-byte id is created on one rank and carried to
+ * the others by the host (in ptype: a KVStore.Put, cluster/store.go:56). */
+int ptype_b200_nccl_unique_id(void* id128);
+int ptype_b200_comm_init(ptype_ctx*, const void* id128, int rank, int nranks);
+int ptype_b200_broadcast_image(ptype_ctx*, const void* image, size_t bytes, int root);
+
+/* ----------------------------------------------------------------- dispatch */
+#define PTYPE_F_DEVICE_PTRS 1u /* reqs/replies are device pointers on `dev`      */
+#define PTYPE_F_ASYNC 2u       /* return after enqueue; pair with ptype_b200_sync */
+#define PTYPE_F_GLOBAL_TABLE 4u/* debug/measurement: probe the table in L2, not shared memory */
+
+/* Optional per-batch outputs (all device-written; host copies made on sync). */
+typedef struct ptype_batch_stats {
+    uint64_t calls;
+    uint64_t by_status[PTYPE_ST__COUNT];
+    uint64_t failed_count; /* entries written to the failed-call list */
+} ptype_batch_stats;
+
+/* N calls through the snapshot currently installed on `dev`.
+ * Host pointers: pageable or pinned; copies are pipelined in chunks.
+ * Device pointers (PTYPE_F_DEVICE_PTRS): no copies, one kernel launch.
+ * Limit: Prime.Check ranges longer than the context's check limit get
+ * PTYPE_ST_RANGE_LIMIT (ptype_b200_set_check_limit; default 1<<16). */
+int ptype_b200_dispatch(ptype_ctx*, int dev, const ptype_req* reqs, size_t n, ptype_reply* replies,
+                        uint32_t flags);
+/* Same, and also compacts the indices of calls with status != OK into
+ * failed_idx[0..failed_cap) (order unspecified) and fills *stats — the set a
+ * withRetry loop (cluster/rpc.go:107-116) would re-issue.  failed_idx/stats
+ * follow the same host/device convention as reqs. */
+int ptype_b200_dispatch_ex(ptype_ctx*, int dev, const ptype_req* reqs, size_t n,
+                           ptype_reply* replies, uint32_t* failed_idx, size_t failed_cap,
+                           ptype_batch_stats* stats, uint32_t flags);
+int ptype_b200_sync(ptype_ctx*, int dev);
+int ptype_b200_set_check_limit(ptype_ctx*, uint64_t max_iterations);
+
+/* Order-independent 64-bit checksum of n reply records (sum over j of
+ * mix64(record j, j) mod 2^64) — compares whole streams across GPUs and against
+ * the oracle without moving the replies.  replies: device pointer when
+ * PTYPE_F_DEVICE_PTRS, else host. */
+int ptype_b200_reply_checksum(ptype_ctx*, int dev, const ptype_reply* replies, size_t n,
+                              uint64_t index_base, uint64_t* checksum, uint32_t flags);
+
+/* Kernel launches issued by this context so far (bench bookkeeping). */
+int ptype_b200_launch_count(ptype_ctx*, uint64_t* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTYPE_B200_H */

@@ -1,0 +1,199 @@
+"""Device contexts: install snapshots, dispatch batches (host or device buffers).
+
+Mirrors the call path of cluster.(*Client).Call (cluster/rpc.go:59-67) for whole
+batches.  Everything goes through the C ABI; nothing here computes a reply.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _abi
+from ._abi import lib, check, REQ_DTYPE, REPLY_DTYPE, F_DEVICE_PTRS, F_ASYNC, F_GLOBAL_TABLE
+from .snapshot import Image
+
+
+class PinnedArray:
+    """A numpy view over page-locked host memory from ptype_b200_alloc_pinned."""
+
+    def __init__(self, count: int, dtype: np.dtype):
+        self.nbytes = int(count) * np.dtype(dtype).itemsize
+        self.ptr = lib.ptype_b200_alloc_pinned(max(self.nbytes, 1))
+        if not self.ptr:
+            raise MemoryError("ptype_b200_alloc_pinned failed")
+        buf = (C.c_char * max(self.nbytes, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=dtype, count=count)
+
+    def free(self) -> None:
+        if self.ptr:
+            self.array = None
+            lib.ptype_b200_free_pinned(self.ptr)
+            self.ptr = None
+
+
+class DeviceBuffer:
+    def __init__(self, ctx: "Context", dev: int, nbytes: int):
+        self.ctx, self.dev, self.nbytes = ctx, dev, nbytes
+        p = C.c_void_p()
+        check(lib.ptype_b200_device_alloc(ctx._h, dev, nbytes, C.byref(p)), "device_alloc")
+        self.ptr = p.value
+
+    def upload(self, arr: np.ndarray) -> "DeviceBuffer":
+        arr = np.ascontiguousarray(arr)
+        assert arr.nbytes <= self.nbytes
+        check(lib.ptype_b200_memcpy_h2d(self.ctx._h, self.dev, self.ptr, arr.ctypes.data, arr.nbytes),
+              "memcpy_h2d")
+        return self
+
+    def download(self, dtype: np.dtype, count: int) -> np.ndarray:
+        out = np.empty(count, dtype=dtype)
+        assert out.nbytes <= self.nbytes
+        check(lib.ptype_b200_memcpy_d2h(self.ctx._h, self.dev, out.ctypes.data, self.ptr, out.nbytes),
+              "memcpy_d2h")
+        return out
+
+    def free(self) -> None:
+        if self.ptr:
+            lib.ptype_b200_device_free(self.ctx._h, self.dev, self.ptr)
+            self.ptr = None
+
+
+def _ptr(x) -> int:
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data
+    if isinstance(x, DeviceBuffer):
+        return x.ptr
+    return int(x)
+
+
+class Context:
+    def __init__(self, devices: Sequence[int] = (0,)):
+        arr = (C.c_int * len(devices))(*devices)
+        self._h = C.c_void_p()
+        check(lib.ptype_b200_open(arr, len(devices), C.byref(self._h)), "open")
+        self.devices = list(devices)
+        self.image: Optional[Image] = None
+
+    def close(self) -> None:
+        if self._h:
+            lib.ptype_b200_close(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # ---- snapshots -------------------------------------------------------
+    def publish(self, image: Image) -> None:
+        check(lib.ptype_b200_publish_image(self._h, image._buf, len(image)), "publish_image")
+        self.image = image
+
+    def epoch(self, dev: int = 0) -> int:
+        e = C.c_uint64()
+        check(lib.ptype_b200_epoch(self._h, dev, C.byref(e)), "epoch")
+        return e.value
+
+    def current_image(self) -> Image:
+        n = C.c_size_t(0)
+        rc = lib.ptype_b200_current_image(self._h, None, C.byref(n))
+        if rc not in (_abi.E_OK, _abi.E_LIMIT):
+            check(rc, "current_image")
+        buf = C.create_string_buffer(n.value)
+        check(lib.ptype_b200_current_image(self._h, buf, C.byref(n)), "current_image")
+        return Image(buf.raw[: n.value])
+
+    def set_check_limit(self, iterations: int) -> None:
+        check(lib.ptype_b200_set_check_limit(self._h, iterations), "set_check_limit")
+
+    # ---- multi-process snapshot broadcast --------------------------------
+    @staticmethod
+    def nccl_unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        check(lib.ptype_b200_nccl_unique_id(buf), "nccl_unique_id")
+        return buf.raw
+
+    def comm_init(self, unique_id: bytes, rank: int, nranks: int) -> None:
+        buf = C.create_string_buffer(unique_id, 128)
+        check(lib.ptype_b200_comm_init(self._h, buf, rank, nranks), "comm_init")
+
+    def broadcast_image(self, image: Optional[Image], root: int = 0) -> Image:
+        if image is not None:
+            check(lib.ptype_b200_broadcast_image(self._h, image._buf, len(image), root),
+                  "broadcast_image")
+        else:
+            check(lib.ptype_b200_broadcast_image(self._h, None, 0, root), "broadcast_image")
+        self.image = self.current_image()
+        return self.image
+
+    # ---- dispatch ---------------------------------------------------------
+    def dispatch(self, reqs: np.ndarray, replies: Optional[np.ndarray] = None, *, dev: int = 0,
+                 flags: int = 0) -> np.ndarray:
+        """Host buffers in, host buffers out (copies are inside the call)."""
+        reqs = np.ascontiguousarray(reqs, dtype=REQ_DTYPE)
+        if replies is None:
+            replies = np.empty(len(reqs), dtype=REPLY_DTYPE)
+        check(lib.ptype_b200_dispatch(self._h, dev, reqs.ctypes.data, len(reqs),
+                                      replies.ctypes.data, flags), "dispatch")
+        return replies
+
+    def dispatch_ex(self, reqs: np.ndarray, failed_cap: int, *, dev: int = 0,
+                    flags: int = 0) -> Tuple[np.ndarray, np.ndarray, _abi.BatchStats]:
+        reqs = np.ascontiguousarray(reqs, dtype=REQ_DTYPE)
+        replies = np.empty(len(reqs), dtype=REPLY_DTYPE)
+        failed = np.zeros(max(failed_cap, 1), dtype=np.uint32)
+        stats = _abi.BatchStats()
+        check(lib.ptype_b200_dispatch_ex(self._h, dev, reqs.ctypes.data, len(reqs),
+                                         replies.ctypes.data, failed.ctypes.data, failed_cap,
+                                         C.addressof(stats), flags), "dispatch_ex")
+        return replies, failed[: min(failed_cap, stats.failed_count)], stats
+
+    def dispatch_device(self, reqs, n: int, replies, *, dev: int = 0, flags: int = 0,
+                        failed=None, failed_cap: int = 0, stats=None, sync: bool = True) -> None:
+        """Batch already resident in HBM: one kernel launch on the context stream."""
+        f = flags | F_DEVICE_PTRS | (0 if sync else F_ASYNC)
+        if stats is None:
+            check(lib.ptype_b200_dispatch(self._h, dev, _ptr(reqs), n, _ptr(replies), f), "dispatch")
+        else:
+            check(lib.ptype_b200_dispatch_ex(self._h, dev, _ptr(reqs), n, _ptr(replies),
+                                             _ptr(failed) if failed is not None else None,
+                                             failed_cap, _ptr(stats), f), "dispatch_ex")
+
+    def sync(self, dev: int = 0) -> None:
+        check(lib.ptype_b200_sync(self._h, dev), "sync")
+
+    def stream(self, dev: int = 0) -> int:
+        s = C.c_void_p()
+        check(lib.ptype_b200_stream(self._h, dev, C.byref(s)), "stream")
+        return s.value or 0
+
+    def reply_checksum(self, replies, n: Optional[int] = None, *, index_base: int = 0, dev: int = 0,
+                       device: bool = False) -> int:
+        out = C.c_uint64()
+        if not device:
+            replies = np.ascontiguousarray(replies, dtype=REPLY_DTYPE)
+            n = len(replies)
+        check(lib.ptype_b200_reply_checksum(self._h, dev, _ptr(replies), n, index_base, C.byref(out),
+                                            F_DEVICE_PTRS if device else 0), "reply_checksum")
+        return out.value
+
+    def launch_count(self) -> int:
+        v = C.c_uint64()
+        check(lib.ptype_b200_launch_count(self._h, C.byref(v)), "launch_count")
+        return v.value
+
+    def device_buffer(self, nbytes: int, dev: int = 0) -> DeviceBuffer:
+        return DeviceBuffer(self, dev, nbytes)
+
+
+def device_count() -> int:
+    n = C.c_int()
+    check(lib.ptype_b200_device_count(C.byref(n)), "device_count")
+    return n.value
+
+
+__all__ = ["Context", "DeviceBuffer", "PinnedArray", "device_count", "F_DEVICE_PTRS", "F_ASYNC",
+           "F_GLOBAL_TABLE"]

@@ -1,0 +1,635 @@
+// context.cu — the C ABI over the kernels: contexts, snapshot installation,
+// host- and device-pointer dispatch, NCCL broadcast of registry images.
+//
+// No CPU fallback exists: every dispatch entry point launches the sm_100a
+// kernels or returns an error.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/ptype_b200.h"
+#include "device_image.h"
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int cuda_fail(cudaError_t e, const char* what) {
+    char buf[512];
+    std::snprintf(buf, sizeof buf, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+    g_last_error = buf;
+    return PTYPE_E_CUDA;
+}
+
+#define CU(call)                                         \
+    do {                                                 \
+        cudaError_t e_ = (call);                         \
+        if (e_ != cudaSuccess) return cuda_fail(e_, #call); \
+    } while (0)
+
+constexpr int kPipe = 4;                     // host-pointer pipeline depth
+constexpr size_t kChunkCalls = 128 * 1024;   // calls per pipelined chunk (6 MiB in, 2 MiB out)
+
+// ---- NCCL, resolved at run time so the library has no link-time NCCL dependency
+// (inside a torch process this picks up the libnccl torch already loaded).
+struct UniqueId128 {
+    char internal[128];
+};
+struct NcclApi {
+    void* handle = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, UniqueId128, int) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+constexpr int kNcclUint8 = 1;  // ncclUint8 in nccl.h's ncclDataType_t
+
+NcclApi* nccl_api() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* nm : names) {
+            api.handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+            if (api.handle) break;
+        }
+        if (!api.handle) return;
+        api.GetUniqueId = reinterpret_cast<int (*)(void*)>(dlsym(api.handle, "ncclGetUniqueId"));
+        api.CommInitRank = reinterpret_cast<int (*)(void**, int, UniqueId128, int)>(
+            dlsym(api.handle, "ncclCommInitRank"));
+        api.Broadcast =
+            reinterpret_cast<int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t)>(
+                dlsym(api.handle, "ncclBroadcast"));
+        api.CommDestroy = reinterpret_cast<int (*)(void*)>(dlsym(api.handle, "ncclCommDestroy"));
+        api.GetErrorString =
+            reinterpret_cast<const char* (*)(int)>(dlsym(api.handle, "ncclGetErrorString"));
+    });
+    if (!api.handle || !api.GetUniqueId || !api.CommInitRank || !api.Broadcast) return nullptr;
+    return &api;
+}
+
+int nccl_fail(int r, const char* what) {
+    NcclApi* a = nccl_api();
+    char buf[512];
+    std::snprintf(buf, sizeof buf, "%s: %s", what,
+                  (a && a->GetErrorString) ? a->GetErrorString(r) : "nccl error");
+    g_last_error = buf;
+    return PTYPE_E_NCCL;
+}
+
+struct Stage {
+    ptype_req* d_reqs = nullptr;
+    ptype_reply* d_replies = nullptr;
+    cudaEvent_t done = nullptr;
+    bool busy = false;
+};
+
+struct DeviceState {
+    int device = -1;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;       // device-pointer dispatches, checksums
+    cudaStream_t copy_stream = nullptr;  // image uploads / broadcast
+    cudaStream_t pipe[kPipe] = {};
+    Stage stage[kPipe];
+    void* image_buf[2] = {nullptr, nullptr};
+    size_t image_cap[2] = {0, 0};
+    ptype::DeviceImage view[2];
+    ptype::LaunchPlan plan[2][2][2];  // [buffer][global_table][extras]
+    uint64_t epoch[2] = {0, 0};
+    int active = -1;
+    unsigned long long* d_stats = nullptr;
+    uint32_t* d_failed = nullptr;
+    size_t failed_cap = 0;
+    unsigned long long* d_cksum_partials = nullptr;  // scratch of the checksum kernel
+    unsigned long long* d_cksum_out = nullptr;
+    unsigned long long* d_size = nullptr;  // broadcast header scratch
+    std::mutex mu;
+};
+
+}  // namespace
+
+struct ptype_ctx {
+    std::vector<DeviceState*> devs;
+    std::atomic<uint64_t> check_limit{1ull << 16};
+    std::atomic<uint64_t> launches{0};
+    void* nccl_comm = nullptr;
+    int rank = 0, nranks = 1;
+    std::mutex image_mu;
+    std::vector<unsigned char> host_image;  // last installed blob (host-side lookups)
+};
+
+namespace {
+
+DeviceState* dev_of(ptype_ctx* ctx, int dev) {
+    if (!ctx || dev < 0 || dev >= static_cast<int>(ctx->devs.size())) return nullptr;
+    return ctx->devs[dev];
+}
+
+int sync_all_streams(DeviceState* d) {
+    CU(cudaStreamSynchronize(d->stream));
+    for (int i = 0; i < kPipe; ++i) {
+        CU(cudaStreamSynchronize(d->pipe[i]));
+        d->stage[i].busy = false;
+    }
+    return PTYPE_OK;
+}
+
+// Make the inactive image buffer at least `bytes` big.  Nothing in flight reads it:
+// every dispatch launched so far captured the active buffer, and callers sync first.
+int reserve_inactive(DeviceState* d, int buf, size_t bytes) {
+    if (d->image_cap[buf] >= bytes) return PTYPE_OK;
+    if (d->image_buf[buf]) CU(cudaFree(d->image_buf[buf]));
+    d->image_buf[buf] = nullptr;
+    d->image_cap[buf] = 0;
+    size_t cap = (bytes + 4095) / 4096 * 4096;
+    CU(cudaMalloc(&d->image_buf[buf], cap));
+    d->image_cap[buf] = cap;
+    return PTYPE_OK;
+}
+
+// Point a DeviceImage at buffer `buf` (which holds at least header.device_bytes of
+// the blob), refresh launch plans, and flip.  Mirrors the swap under lock of
+// handleNewNodes (cluster/rpc.go:233-236).
+int adopt_image(ptype_ctx* ctx, DeviceState* d, int buf, const ptype_image_header& h) {
+    const unsigned char* base = static_cast<const unsigned char*>(d->image_buf[buf]);
+    ptype::DeviceImage& v = d->view[buf];
+    v.slots = reinterpret_cast<const ptype_slot*>(base + h.off_slots);
+    v.conn_hash = reinterpret_cast<const uint32_t*>(base + h.off_conn_hash);
+    v.methods = reinterpret_cast<const ptype_method*>(base + h.off_methods);
+    v.n_slots = h.n_slots;
+    v.max_conn = h.max_connections;
+    v.n_methods = h.n_methods;
+    v.pad = 0;
+    v.check_limit = ctx->check_limit.load();
+    for (int g = 0; g < 2; ++g)
+        for (int x = 0; x < 2; ++x)
+            CU(ptype::plan_dispatch(v, g ? PTYPE_F_GLOBAL_TABLE : 0u, x != 0, &d->plan[buf][g][x]));
+    d->epoch[buf] = h.epoch;
+    d->active = buf;
+    return PTYPE_OK;
+}
+
+bool is_device_pointer(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+int ensure_extras(DeviceState* d, size_t failed_cap) {
+    if (!d->d_stats) CU(cudaMalloc(&d->d_stats, ptype::kStatWords * sizeof(unsigned long long)));
+    if (failed_cap > d->failed_cap) {
+        if (d->d_failed) CU(cudaFree(d->d_failed));
+        d->d_failed = nullptr;
+        d->failed_cap = 0;
+        CU(cudaMalloc(&d->d_failed, failed_cap * sizeof(uint32_t)));
+        d->failed_cap = failed_cap;
+    }
+    return PTYPE_OK;
+}
+
+int ensure_stage(DeviceState* d, int s) {
+    Stage& st = d->stage[s];
+    if (!st.d_reqs) CU(cudaMalloc(&st.d_reqs, kChunkCalls * sizeof(ptype_req)));
+    if (!st.d_replies) CU(cudaMalloc(&st.d_replies, kChunkCalls * sizeof(ptype_reply)));
+    if (!st.done) CU(cudaEventCreateWithFlags(&st.done, cudaEventDisableTiming));
+    return PTYPE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* ptype_b200_strerror(int err) {
+    switch (err) {
+        case PTYPE_OK: return "ok";
+        case PTYPE_E_INVAL: return "invalid argument";
+        case PTYPE_E_NOMEM: return "out of memory";
+        case PTYPE_E_CUDA: return "CUDA call failed (see ptype_b200_last_error)";
+        case PTYPE_E_NO_IMAGE: return "no registry image installed";
+        case PTYPE_E_BAD_IMAGE: return "malformed registry image";
+        case PTYPE_E_COLLISION: return "service-key collision could not be resolved";
+        case PTYPE_E_NCCL: return "NCCL call failed (see ptype_b200_last_error)";
+        case PTYPE_E_LIMIT: return "size beyond a documented maximum";
+        case PTYPE_E_NOT_FOUND: return "not found";
+        case PTYPE_E_BUSY: return "busy";
+        default: return "unknown error";
+    }
+}
+
+const char* ptype_b200_last_error(void) { return g_last_error.c_str(); }
+int ptype_b200_abi_version(void) { return PTYPE_B200_ABI_VERSION; }
+
+int ptype_b200_device_count(int* out) {
+    if (!out) return PTYPE_E_INVAL;
+    CU(cudaGetDeviceCount(out));
+    return PTYPE_OK;
+}
+
+void ptype_b200_close(ptype_ctx* ctx) {
+    if (!ctx) return;
+    if (ctx->nccl_comm) {
+        NcclApi* a = nccl_api();
+        if (a && a->CommDestroy) a->CommDestroy(ctx->nccl_comm);
+    }
+    for (DeviceState* d : ctx->devs) {
+        if (!d) continue;
+        cudaSetDevice(d->device);
+        cudaDeviceSynchronize();
+        for (int i = 0; i < kPipe; ++i) {
+            if (d->stage[i].d_reqs) cudaFree(d->stage[i].d_reqs);
+            if (d->stage[i].d_replies) cudaFree(d->stage[i].d_replies);
+            if (d->stage[i].done) cudaEventDestroy(d->stage[i].done);
+            if (d->pipe[i]) cudaStreamDestroy(d->pipe[i]);
+        }
+        for (int b = 0; b < 2; ++b)
+            if (d->image_buf[b]) cudaFree(d->image_buf[b]);
+        if (d->d_stats) cudaFree(d->d_stats);
+        if (d->d_failed) cudaFree(d->d_failed);
+        if (d->d_cksum_partials) cudaFree(d->d_cksum_partials);
+        if (d->d_cksum_out) cudaFree(d->d_cksum_out);
+        if (d->d_size) cudaFree(d->d_size);
+        if (d->stream) cudaStreamDestroy(d->stream);
+        if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
+        delete d;
+    }
+    delete ctx;
+}
+
+int ptype_b200_open(const int* devices, int ndev, ptype_ctx** out) {
+    if (!out || ndev < 1 || !devices) return PTYPE_E_INVAL;
+    int count = 0;
+    CU(cudaGetDeviceCount(&count));
+    ptype_ctx* ctx = new (std::nothrow) ptype_ctx();
+    if (!ctx) return PTYPE_E_NOMEM;
+    for (int i = 0; i < ndev; ++i) {
+        if (devices[i] < 0 || devices[i] >= count) {
+            ptype_b200_close(ctx);
+            return PTYPE_E_INVAL;
+        }
+        DeviceState* d = new (std::nothrow) DeviceState();
+        if (!d) {
+            ptype_b200_close(ctx);
+            return PTYPE_E_NOMEM;
+        }
+        ctx->devs.push_back(d);
+        d->device = devices[i];
+        cudaError_t e = cudaSetDevice(d->device);
+        if (e == cudaSuccess)
+            e = cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, d->device);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking);
+        for (int s = 0; s < kPipe && e == cudaSuccess; ++s)
+            e = cudaStreamCreateWithFlags(&d->pipe[s], cudaStreamNonBlocking);
+        if (e != cudaSuccess) {
+            ptype_b200_close(ctx);
+            return cuda_fail(e, "ptype_b200_open");
+        }
+    }
+    *out = ctx;
+    return PTYPE_OK;
+}
+
+void* ptype_b200_alloc_pinned(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+void ptype_b200_free_pinned(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+int ptype_b200_device_alloc(ptype_ctx* ctx, int dev, size_t bytes, void** out) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || !out) return PTYPE_E_INVAL;
+    CU(cudaSetDevice(d->device));
+    CU(cudaMalloc(out, bytes ? bytes : 1));
+    return PTYPE_OK;
+}
+int ptype_b200_device_free(ptype_ctx* ctx, int dev, void* p) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d) return PTYPE_E_INVAL;
+    CU(cudaSetDevice(d->device));
+    CU(cudaFree(p));
+    return PTYPE_OK;
+}
+int ptype_b200_memcpy_h2d(ptype_ctx* ctx, int dev, void* dst, const void* src, size_t bytes) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d) return PTYPE_E_INVAL;
+    CU(cudaSetDevice(d->device));
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    return PTYPE_OK;
+}
+int ptype_b200_memcpy_d2h(ptype_ctx* ctx, int dev, void* dst, const void* src, size_t bytes) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d) return PTYPE_E_INVAL;
+    CU(cudaSetDevice(d->device));
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    return PTYPE_OK;
+}
+int ptype_b200_stream(ptype_ctx* ctx, int dev, void** cuda_stream) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || !cuda_stream) return PTYPE_E_INVAL;
+    *cuda_stream = d->stream;
+    return PTYPE_OK;
+}
+
+int ptype_b200_set_check_limit(ptype_ctx* ctx, uint64_t max_iterations) {
+    if (!ctx) return PTYPE_E_INVAL;
+    ctx->check_limit.store(max_iterations);
+    for (DeviceState* d : ctx->devs) {
+        std::lock_guard<std::mutex> lk(d->mu);
+        d->view[0].check_limit = max_iterations;
+        d->view[1].check_limit = max_iterations;
+    }
+    return PTYPE_OK;
+}
+
+int ptype_b200_publish_image(ptype_ctx* ctx, const void* image, size_t bytes) {
+    if (!ctx) return PTYPE_E_INVAL;
+    int rc = ptype_b200_image_validate(image, bytes);
+    if (rc != PTYPE_OK) return rc;
+    const ptype_image_header& h = *static_cast<const ptype_image_header*>(image);
+    for (DeviceState* d : ctx->devs) {
+        std::lock_guard<std::mutex> lk(d->mu);
+        CU(cudaSetDevice(d->device));
+        const int buf = d->active == 0 ? 1 : 0;
+        // work launched against an older flip may still read this buffer
+        rc = sync_all_streams(d);
+        if (rc != PTYPE_OK) return rc;
+        rc = reserve_inactive(d, buf, h.device_bytes);
+        if (rc != PTYPE_OK) return rc;
+        CU(cudaMemcpyAsync(d->image_buf[buf], image, h.device_bytes, cudaMemcpyHostToDevice,
+                           d->copy_stream));
+        CU(cudaStreamSynchronize(d->copy_stream));
+        rc = adopt_image(ctx, d, buf, h);
+        if (rc != PTYPE_OK) return rc;
+    }
+    std::lock_guard<std::mutex> lk(ctx->image_mu);
+    ctx->host_image.assign(static_cast<const unsigned char*>(image),
+                           static_cast<const unsigned char*>(image) + bytes);
+    return PTYPE_OK;
+}
+
+int ptype_b200_epoch(ptype_ctx* ctx, int dev, uint64_t* epoch) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || !epoch) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> lk(d->mu);
+    if (d->active < 0) return PTYPE_E_NO_IMAGE;
+    *epoch = d->epoch[d->active];
+    return PTYPE_OK;
+}
+
+// Copy of the blob last installed in this context (on non-root ranks: the bytes
+// that arrived over NCCL).  *bytes in: capacity, out: size needed.
+int ptype_b200_current_image(ptype_ctx* ctx, void* out, size_t* bytes) {
+    if (!ctx || !bytes) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> lk(ctx->image_mu);
+    if (ctx->host_image.empty()) return PTYPE_E_NO_IMAGE;
+    const size_t need = ctx->host_image.size();
+    if (out && *bytes >= need) std::memcpy(out, ctx->host_image.data(), need);
+    const bool fits = out && *bytes >= need;
+    *bytes = need;
+    return fits ? PTYPE_OK : PTYPE_E_LIMIT;
+}
+
+int ptype_b200_nccl_unique_id(void* id128) {
+    NcclApi* a = nccl_api();
+    if (!a) {
+        g_last_error = "libnccl.so.2 not loadable";
+        return PTYPE_E_NCCL;
+    }
+    int r = a->GetUniqueId(id128);
+    return r == 0 ? PTYPE_OK : nccl_fail(r, "ncclGetUniqueId");
+}
+
+int ptype_b200_comm_init(ptype_ctx* ctx, const void* id128, int rank, int nranks) {
+    if (!ctx || !id128 || ctx->devs.size() != 1 || rank < 0 || rank >= nranks) return PTYPE_E_INVAL;
+    NcclApi* a = nccl_api();
+    if (!a) {
+        g_last_error = "libnccl.so.2 not loadable";
+        return PTYPE_E_NCCL;
+    }
+    CU(cudaSetDevice(ctx->devs[0]->device));
+    UniqueId128 id;
+    std::memcpy(&id, id128, sizeof id);
+    void* comm = nullptr;
+    int r = a->CommInitRank(&comm, nranks, id, rank);
+    if (r != 0) return nccl_fail(r, "ncclCommInitRank");
+    ctx->nccl_comm = comm;
+    ctx->rank = rank;
+    ctx->nranks = nranks;
+    return PTYPE_OK;
+}
+
+// Registry-snapshot broadcast: the only traffic that crosses NVLink on this path.
+int ptype_b200_broadcast_image(ptype_ctx* ctx, const void* image, size_t bytes, int root) {
+    if (!ctx || !ctx->nccl_comm || ctx->devs.size() != 1) return PTYPE_E_INVAL;
+    NcclApi* a = nccl_api();
+    DeviceState* d = ctx->devs[0];
+    const bool is_root = ctx->rank == root;
+    if (is_root) {
+        int rc = ptype_b200_image_validate(image, bytes);
+        if (rc != PTYPE_OK) return rc;
+    }
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(d->device));
+    int rc = sync_all_streams(d);
+    if (rc != PTYPE_OK) return rc;
+    if (!d->d_size) CU(cudaMalloc(&d->d_size, 16));
+    unsigned long long total = is_root ? bytes : 0;
+    if (is_root)
+        CU(cudaMemcpyAsync(d->d_size, &total, sizeof total, cudaMemcpyHostToDevice, d->copy_stream));
+    int r = a->Broadcast(d->d_size, d->d_size, sizeof total, kNcclUint8, root, ctx->nccl_comm,
+                         d->copy_stream);
+    if (r != 0) return nccl_fail(r, "ncclBroadcast(size)");
+    CU(cudaMemcpyAsync(&total, d->d_size, sizeof total, cudaMemcpyDeviceToHost, d->copy_stream));
+    CU(cudaStreamSynchronize(d->copy_stream));
+    if (total < sizeof(ptype_image_header) || total > (1ull << 32)) return PTYPE_E_BAD_IMAGE;
+    const int buf = d->active == 0 ? 1 : 0;
+    rc = reserve_inactive(d, buf, total);
+    if (rc != PTYPE_OK) return rc;
+    if (is_root)
+        CU(cudaMemcpyAsync(d->image_buf[buf], image, total, cudaMemcpyHostToDevice, d->copy_stream));
+    r = a->Broadcast(d->image_buf[buf], d->image_buf[buf], total, kNcclUint8, root, ctx->nccl_comm,
+                     d->copy_stream);
+    if (r != 0) return nccl_fail(r, "ncclBroadcast(image)");
+    std::vector<unsigned char> host(total);
+    if (is_root) {
+        std::memcpy(host.data(), image, total);
+    } else {
+        CU(cudaMemcpyAsync(host.data(), d->image_buf[buf], total, cudaMemcpyDeviceToHost,
+                           d->copy_stream));
+    }
+    CU(cudaStreamSynchronize(d->copy_stream));
+    rc = ptype_b200_image_validate(host.data(), host.size());
+    if (rc != PTYPE_OK) return rc;
+    rc = adopt_image(ctx, d, buf, *reinterpret_cast<const ptype_image_header*>(host.data()));
+    if (rc != PTYPE_OK) return rc;
+    std::lock_guard<std::mutex> lk2(ctx->image_mu);
+    ctx->host_image.swap(host);
+    return PTYPE_OK;
+}
+
+int ptype_b200_sync(ptype_ctx* ctx, int dev) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(d->device));
+    return sync_all_streams(d);
+}
+
+int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_t n,
+                           ptype_reply* replies, uint32_t* failed_idx, size_t failed_cap,
+                           ptype_batch_stats* stats, uint32_t flags) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || (n && (!reqs || !replies))) return PTYPE_E_INVAL;
+    if (n > 0xFFFFFFFFull || failed_cap > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
+    if (failed_idx && !stats) return PTYPE_E_INVAL;  // the list's length lives in stats
+    std::lock_guard<std::mutex> lk(d->mu);
+    if (d->active < 0) return PTYPE_E_NO_IMAGE;
+    CU(cudaSetDevice(d->device));
+    const int buf = d->active;
+    const ptype::DeviceImage img = d->view[buf];
+    const bool extras = stats != nullptr;
+    const ptype::LaunchPlan& plan = d->plan[buf][(flags & PTYPE_F_GLOBAL_TABLE) ? 1 : 0][extras ? 1 : 0];
+
+    if (flags & PTYPE_F_DEVICE_PTRS) {
+        // Batch resident in HBM: one kernel launch, nothing else.
+        unsigned long long* d_stats = nullptr;
+        if (extras) {
+            d_stats = reinterpret_cast<unsigned long long*>(stats);
+            CU(cudaMemsetAsync(d_stats, 0, sizeof(ptype_batch_stats), d->stream));
+        }
+        if (n) {
+            CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, n, d->sm_count), reqs, n,
+                                      replies, failed_idx, static_cast<uint32_t>(failed_cap), 0u,
+                                      d_stats, d->stream));
+            ctx->launches.fetch_add(1);
+        }
+        if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+        return PTYPE_OK;
+    }
+
+    // Host buffers: chunked H2D -> kernel -> D2H pipeline over kPipe streams.
+    int rc;
+    if (extras) {
+        rc = ensure_extras(d, failed_idx ? failed_cap : 0);
+        if (rc != PTYPE_OK) return rc;
+        CU(cudaMemsetAsync(d->d_stats, 0, ptype::kStatWords * sizeof(unsigned long long), d->pipe[0]));
+        CU(cudaStreamSynchronize(d->pipe[0]));
+    }
+    size_t done = 0;
+    int s = 0;
+    while (done < n) {
+        const size_t cnt = n - done < kChunkCalls ? n - done : kChunkCalls;
+        rc = ensure_stage(d, s);
+        if (rc != PTYPE_OK) return rc;
+        Stage& st = d->stage[s];
+        if (st.busy) {
+            CU(cudaEventSynchronize(st.done));
+            st.busy = false;
+        }
+        CU(cudaMemcpyAsync(st.d_reqs, reqs + done, cnt * sizeof(ptype_req), cudaMemcpyHostToDevice,
+                           d->pipe[s]));
+        CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, cnt, d->sm_count), st.d_reqs, cnt,
+                                  st.d_replies, failed_idx ? d->d_failed : nullptr,
+                                  static_cast<uint32_t>(failed_cap), static_cast<uint32_t>(done),
+                                  extras ? d->d_stats : nullptr, d->pipe[s]));
+        ctx->launches.fetch_add(1);
+        CU(cudaMemcpyAsync(replies + done, st.d_replies, cnt * sizeof(ptype_reply),
+                           cudaMemcpyDeviceToHost, d->pipe[s]));
+        CU(cudaEventRecord(st.done, d->pipe[s]));
+        st.busy = true;
+        done += cnt;
+        s = (s + 1) % kPipe;
+    }
+    if (extras || !(flags & PTYPE_F_ASYNC)) {
+        for (int i = 0; i < kPipe; ++i) {
+            if (d->stage[i].busy) {
+                CU(cudaEventSynchronize(d->stage[i].done));
+                d->stage[i].busy = false;
+            }
+        }
+    }
+    if (extras) {
+        unsigned long long words[ptype::kStatWords];
+        CU(cudaMemcpyAsync(words, d->d_stats, sizeof words, cudaMemcpyDeviceToHost, d->pipe[0]));
+        CU(cudaStreamSynchronize(d->pipe[0]));
+        stats->calls = words[ptype::kStatCalls];
+        for (int i = 0; i < PTYPE_ST__COUNT; ++i) stats->by_status[i] = words[ptype::kStatByStatus + i];
+        stats->failed_count = words[ptype::kStatFailed];
+        if (failed_idx && failed_cap) {
+            size_t take = stats->failed_count < failed_cap ? stats->failed_count : failed_cap;
+            if (take) {
+                CU(cudaMemcpyAsync(failed_idx, d->d_failed, take * sizeof(uint32_t),
+                                   cudaMemcpyDeviceToHost, d->pipe[0]));
+                CU(cudaStreamSynchronize(d->pipe[0]));
+            }
+        }
+    }
+    return PTYPE_OK;
+}
+
+int ptype_b200_dispatch(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_t n,
+                        ptype_reply* replies, uint32_t flags) {
+    return ptype_b200_dispatch_ex(ctx, dev, reqs, n, replies, nullptr, 0, nullptr, flags);
+}
+
+int ptype_b200_reply_checksum(ptype_ctx* ctx, int dev, const ptype_reply* replies, size_t n,
+                              uint64_t index_base, uint64_t* checksum, uint32_t flags) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || !checksum || (n && !replies)) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(d->device));
+    if (!d->d_cksum_partials)
+        CU(cudaMalloc(&d->d_cksum_partials, ptype::kChecksumBlocks * sizeof(unsigned long long)));
+    if (!d->d_cksum_out) CU(cudaMalloc(&d->d_cksum_out, sizeof(unsigned long long)));
+    const ptype_reply* d_replies = replies;
+    void* tmp = nullptr;
+    if (!(flags & PTYPE_F_DEVICE_PTRS) && n) {
+        CU(cudaMalloc(&tmp, n * sizeof(ptype_reply)));
+        cudaError_t e = cudaMemcpyAsync(tmp, replies, n * sizeof(ptype_reply), cudaMemcpyHostToDevice,
+                                        d->stream);
+        if (e != cudaSuccess) {
+            cudaFree(tmp);
+            return cuda_fail(e, "cudaMemcpyAsync(replies)");
+        }
+        d_replies = static_cast<const ptype_reply*>(tmp);
+    }
+    cudaError_t e = ptype::launch_reply_checksum(d_replies, n, index_base, d->d_cksum_partials,
+                                                 d->d_cksum_out, d->stream);
+    ctx->launches.fetch_add(2);
+    unsigned long long out = 0;
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(&out, d->d_cksum_out, sizeof out, cudaMemcpyDeviceToHost, d->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(d->stream);
+    if (tmp) cudaFree(tmp);
+    if (e != cudaSuccess) return cuda_fail(e, "reply_checksum");
+    *checksum = out;
+    return PTYPE_OK;
+}
+
+int ptype_b200_launch_count(ptype_ctx* ctx, uint64_t* launches) {
+    if (!ctx || !launches) return PTYPE_E_INVAL;
+    *launches = ctx->launches.load();
+    return PTYPE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,47 @@
+// device_image.h — what a dispatch kernel is handed by value: pointers into the
+// device copy of the registry image plus the per-context limits.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ptype_b200.h"
+
+namespace ptype {
+
+struct DeviceImage {
+    const ptype_slot* slots;     // n_slots entries, 16-byte aligned
+    const uint32_t* conn_hash;   // max_conn entries: FNV-1a-32(localAddr+itoa(i))
+    const ptype_method* methods; // n_methods entries
+    uint32_t n_slots;
+    uint32_t max_conn;           // ConnConfig.MaxConnections, 0 = mesh
+    uint32_t n_methods;
+    uint32_t pad;
+    uint64_t check_limit;        // Prime.Check trip-count limit
+};
+
+// Layout of the device-side ptype_batch_stats accumulator (uint64 words).
+enum : int { kStatCalls = 0, kStatByStatus = 1, kStatFailed = 1 + PTYPE_ST__COUNT, kStatWords = 2 + PTYPE_ST__COUNT };
+
+struct LaunchPlan {
+    int threads = 0;        // per CTA
+    int ctas_per_sm = 0;    // resident CTAs per SM (occupancy query)
+    size_t dyn_smem = 0;    // bytes of staged slot table (0 = probe in L2)
+    bool smem_table = false;
+};
+
+// Number of partial sums the checksum kernel writes to its scratch buffer.
+constexpr int kChecksumBlocks = 148 * 8;
+constexpr int kChecksumThreads = 256;
+
+// Must run with the target device current (sets the kernel's shared-memory attribute).
+cudaError_t plan_dispatch(const DeviceImage& img, uint32_t flags, bool extras, LaunchPlan* plan);
+int grid_for(const LaunchPlan& plan, size_t n, int sm_count);
+cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int blocks,
+                            const ptype_req* reqs, size_t n, ptype_reply* replies, uint32_t* failed_idx,
+                            uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
+                            cudaStream_t stream);
+cudaError_t launch_reply_checksum(const ptype_reply* replies, size_t n, uint64_t index_base,
+                                  unsigned long long* partials, unsigned long long* out,
+                                  cudaStream_t stream);
+
+}  // namespace ptype

@@ -1,0 +1,499 @@
+// dispatch.cu — the fused batched-dispatch kernel for sm_100a and its launcher.
+//
+// One thread handles one call end to end; one warp handles 32 consecutive calls:
+//   load     three coalesced 128-bit loads per lane cover the warp's 32 x 48 B
+//            request records, then a 12-shuffle transpose hands every lane its
+//            own record (no shared memory, no strided global access)
+//   lookup   exact-key probe of the open-addressing registry table staged in
+//            shared memory by one bulk-async (TMA) copy per CTA
+//            — replaces the result of Registry.Services()/nodes()
+//              (cluster/registry.go:93-117,152-166)
+//   route    selectNodes + hashConnectionIndex + roundRobinSelect in closed form
+//            (cluster/rpc.go:176-183,252-270): with n registered nodes and
+//            m = MaxConnections,  k = (m == 0 || n <= m) ? n : m,
+//            r = int(seq) % k,  node = base + (k == n ? r : connHash[r] % n)
+//   resolve  "Receiver.Method" the way the net/rpc server does [Go stdlib]
+//   execute  Multiply / Add / Check (example/calculator/calculator.go:9-12,
+//            example/optimus/prime.go:15-25)
+//   pack     one 128-bit store per lane: 32 x 16 B contiguous reply records
+//
+// HBM-bound integer work: 64 algorithmic bytes per call, no tensor cores.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ptype_b200.h"
+#include "device_image.h"
+#include "table_hash.h"
+
+namespace ptype {
+namespace {
+
+constexpr int kMaxThreads = 1024;
+constexpr int kSmemConn = 256;  // connection hashes kept in shared memory
+constexpr uint32_t kFull = 0xFFFFFFFFu;
+
+// ------------------------------------------------------------- PTX helpers
+
+__device__ __forceinline__ uint4 ld_stream(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ void st_stream(uint4* p, const uint4& v) {
+    asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
+                 "r"(v.w)
+                 : "memory");
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+// Bulk asynchronous copy global -> shared (the TMA engine, 1-D form; SASS UBLKCP).
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes,
+                                         uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+            "r"(smem_u32(dst_smem)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// ------------------------------------------------------------ arithmetic
+
+// int(seq) % k for 0 <= int(seq); 32-bit divide when the sequence number is small.
+__device__ __forceinline__ uint32_t mod_u64_u32(uint64_t a, uint32_t k) {
+    if ((a >> 32) == 0) return static_cast<uint32_t>(a) % k;
+    return static_cast<uint32_t>(a % k);
+}
+
+__device__ __forceinline__ uint64_t abs_u64(int64_t v) {
+    return v < 0 ? 0ull - static_cast<uint64_t>(v) : static_cast<uint64_t>(v);
+}
+
+// Prime.Check (example/optimus/prime.go:15-25), without the sleep:
+//   for i := Min; i < min(Max, Target); i++ { if i != 0 && Target%i == 0 { return i } }
+//   return Target
+// Go's truncated % is zero exactly when |i| divides |Target| (and MinInt64 % -1 is 0,
+// no trap), so the test runs on magnitudes; a 32-bit divide serves the common case.
+__device__ __forceinline__ int64_t prime_check(int64_t lo, int64_t hi, int64_t target,
+                                               uint64_t limit, uint32_t* status) {
+    const int64_t bound = hi < target ? hi : target;
+    if (lo >= bound) return target;
+    const uint64_t width = static_cast<uint64_t>(bound) - static_cast<uint64_t>(lo);
+    if (width > limit) {
+        *status = PTYPE_ST_RANGE_LIMIT;
+        return 0;
+    }
+    const uint64_t tmag = abs_u64(target);
+    const bool t32 = (tmag >> 32) == 0;
+    const uint32_t t_lo = static_cast<uint32_t>(tmag);
+    for (int64_t i = lo; i < bound; ++i) {
+        if (i == 0) continue;
+        const uint64_t imag = abs_u64(i);
+        bool divides;
+        if (t32) {
+            // |i| > |target| > 0 cannot divide; |target| == 0 is divisible by anything
+            divides = (imag >> 32) == 0 ? (t_lo % static_cast<uint32_t>(imag)) == 0 : t_lo == 0;
+        } else {
+            divides = (tmag % imag) == 0;
+        }
+        if (divides) return i;
+    }
+    return target;
+}
+
+struct Tables {
+    const ptype_slot* slots;     // shared or global
+    const uint32_t* conn;        // shared or global
+    const ptype_method* methods; // shared
+};
+
+// One call: lookup -> route -> resolve -> execute.  q0 = {svc_key, seq},
+// q1 = {method, recv, a0}, q2 = {a1, a2}.
+template <bool kSmemTable>
+__device__ __forceinline__ uint4 dispatch_one(const DeviceImage& img, const Tables& tb, uint4 q0,
+                                              uint4 q1, uint4 q2) {
+    const uint64_t key = static_cast<uint64_t>(q0.x) | (static_cast<uint64_t>(q0.y) << 32);
+    const uint64_t seq = static_cast<uint64_t>(q0.z) | (static_cast<uint64_t>(q0.w) << 32);
+
+    // ---- lookup: linear probing, exact 64-bit key compare
+    uint32_t at = home_slot(key, img.n_slots);
+    uint32_t node_base = PTYPE_SLOT_EMPTY, n_and_recv = 0;
+    for (uint32_t probe = 0; probe < img.n_slots; ++probe) {
+        uint4 s;
+        if (kSmemTable) {
+            s = *reinterpret_cast<const uint4*>(tb.slots + at);
+        } else {
+            s = __ldg(reinterpret_cast<const uint4*>(tb.slots + at));
+        }
+        if (s.z == PTYPE_SLOT_EMPTY) break;
+        if (s.x == q0.x && s.y == q0.y) {
+            node_base = s.z;
+            n_and_recv = s.w;
+            break;
+        }
+        at = at + 1 == img.n_slots ? 0 : at + 1;
+    }
+
+    uint32_t status = PTYPE_ST_OK;
+    uint32_t node = PTYPE_NO_NODE;
+    int64_t value = 0;
+    const uint32_t n = n_and_recv & 0xFFFFFFu;
+    if (node_base == PTYPE_SLOT_EMPTY) {
+        status = PTYPE_ST_NO_SERVICE;  // watch delivered no nodes -> ErrNoClientAvailable
+    } else if (n == 0) {
+        status = PTYPE_ST_NO_CLIENT;  // rpc.go:178-180
+    } else {
+        // ---- route
+        const uint32_t m = img.max_conn;
+        const bool identity = m == 0 || n <= m;  // rpc.go:253-255
+        const uint32_t k = identity ? n : m;
+        uint32_t r;
+        if (static_cast<int64_t>(seq) >= 0) {
+            r = mod_u64_u32(seq, k);
+        } else {
+            // int(index) is negative: Go's % keeps the sign, so anything but 0 indexes
+            // clients[] out of range and panics (rpc.go:182)
+            r = 0;
+            if (static_cast<int64_t>(seq) % static_cast<int64_t>(k) != 0) status = PTYPE_ST_BAD_INDEX;
+        }
+        if (status == PTYPE_ST_OK) {
+            const uint32_t local = identity ? r : tb.conn[r] % n;  // rpc.go:258-261,266-270
+            node = node_base + local;
+            // ---- resolve [net/rpc server.readRequestHeader]
+            const uint32_t recv_mask = n_and_recv >> 24;
+            uint32_t opcode = PTYPE_OP_NONE;
+            bool recv_known = false;
+            if (q1.y == PTYPE_RECV_ILL_FORMED) {
+                status = PTYPE_ST_ILL_FORMED;
+            } else {
+                for (uint32_t e = 0; e < img.n_methods; ++e) {
+                    const uint4 md = *reinterpret_cast<const uint4*>(tb.methods + e);
+                    if (md.y == q1.y && ((recv_mask >> md.w) & 1u)) {
+                        recv_known = true;
+                        if (md.x == q1.x) {
+                            opcode = md.z;
+                            break;
+                        }
+                    }
+                }
+                if (opcode == PTYPE_OP_NONE)
+                    status = recv_known ? PTYPE_ST_CANT_FIND_METHOD : PTYPE_ST_CANT_FIND_SERVICE;
+            }
+            // ---- execute
+            if (status == PTYPE_ST_OK) {
+                const uint64_t a0 = static_cast<uint64_t>(q1.z) | (static_cast<uint64_t>(q1.w) << 32);
+                const uint64_t a1 = static_cast<uint64_t>(q2.x) | (static_cast<uint64_t>(q2.y) << 32);
+                if (opcode == PTYPE_OP_MULTIPLY) {
+                    value = static_cast<int64_t>(a0 * a1);  // Go int wraps (calculator.go:10)
+                } else if (opcode == PTYPE_OP_ADD) {
+                    value = static_cast<int64_t>(a0 + a1);
+                } else {
+                    const uint64_t a2 =
+                        static_cast<uint64_t>(q2.z) | (static_cast<uint64_t>(q2.w) << 32);
+                    value = prime_check(static_cast<int64_t>(a0), static_cast<int64_t>(a1),
+                                        static_cast<int64_t>(a2), img.check_limit, &status);
+                }
+            }
+        }
+    }
+    uint4 out;
+    out.x = static_cast<uint32_t>(static_cast<uint64_t>(value));
+    out.y = static_cast<uint32_t>(static_cast<uint64_t>(value) >> 32);
+    out.z = node;
+    out.w = status;
+    return out;
+}
+
+// ------------------------------------------------------------------ kernel
+//
+// Persistent grid: every CTA stages the table once, then its warps walk the
+// batch in 32-call tiles, kUnroll tiles in flight per warp.
+template <bool kSmemTable, bool kExtras, int kUnroll>
+__global__ void __launch_bounds__(kMaxThreads, 1)
+    dispatch_kernel(const DeviceImage img, const uint4* __restrict__ reqs, const size_t n,
+                    uint4* __restrict__ replies, uint32_t* __restrict__ failed_idx,
+                    const uint32_t failed_cap, const uint32_t idx_base,
+                    unsigned long long* __restrict__ stats) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ __align__(16) ptype_method s_methods[PTYPE_MAX_METHODS];
+    __shared__ uint32_t s_conn[kSmemConn];
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ unsigned int s_status[PTYPE_ST__COUNT];
+
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+
+    // ---- stage the registry tables
+    if (kSmemTable) {
+        if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+    }
+    for (uint32_t i = threadIdx.x; i < img.n_methods; i += blockDim.x) s_methods[i] = img.methods[i];
+    const bool conn_in_smem = img.max_conn <= kSmemConn;
+    if (conn_in_smem)
+        for (uint32_t i = threadIdx.x; i < img.max_conn; i += blockDim.x) s_conn[i] = img.conn_hash[i];
+    if (kExtras && threadIdx.x < PTYPE_ST__COUNT) s_status[threadIdx.x] = 0;
+    __syncthreads();
+    if (kSmemTable && threadIdx.x == 0) {
+        const uint32_t bytes = img.n_slots * static_cast<uint32_t>(sizeof(ptype_slot));
+        mbar_expect_tx(&s_bar, bytes);
+        constexpr uint32_t kChunk = 32768;
+        for (uint32_t off = 0; off < bytes; off += kChunk) {
+            const uint32_t len = bytes - off < kChunk ? bytes - off : kChunk;
+            bulk_g2s(dyn_smem + off, reinterpret_cast<const unsigned char*>(img.slots) + off, len,
+                     &s_bar);
+        }
+    }
+
+    Tables tb;
+    tb.slots = kSmemTable ? reinterpret_cast<const ptype_slot*>(dyn_smem) : img.slots;
+    tb.conn = conn_in_smem ? s_conn : img.conn_hash;
+    tb.methods = s_methods;
+
+    // ---- transpose plan.  Lane L loads 16-byte chunks L, 32+L, 64+L of the warp's 96;
+    // record r owns chunks 3r..3r+2.  In round c, lane s feeds the lane whose record
+    // needs chunk index == s (mod 32): r = 11*(s-c) mod 32 (11 = 3^-1 mod 32), out of its
+    // register (3r+c)/32.
+    uint32_t send_reg[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const uint32_t r = ((lane - c) * 11u) & 31u;
+        send_reg[c] = (3u * r + c) >> 5;
+    }
+
+    const size_t n_tiles = (n + 31) >> 5;
+    const size_t n_chunks = n * 3;
+    const size_t total_warps = static_cast<size_t>(gridDim.x) * warps_per_cta;
+    const size_t warp_global = static_cast<size_t>(blockIdx.x) * warps_per_cta + warp;
+
+    unsigned int ok_calls = 0;  // lane 0 only (kExtras)
+    bool table_ready = !kSmemTable;
+
+    for (size_t t0 = warp_global; t0 < n_tiles; t0 += total_warps * kUnroll) {
+        uint4 ld[kUnroll][3];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const size_t t = t0 + static_cast<size_t>(u) * total_warps;
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const size_t c = t * 96 + j * 32 + lane;
+                ld[u][j] = c < n_chunks ? ld_stream(reqs + c) : make_uint4(0, 0, 0, 0);
+            }
+        }
+        if (!table_ready) {  // first tile's loads are already in flight
+            mbar_wait(&s_bar, 0);
+            table_ready = true;
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const size_t t = t0 + static_cast<size_t>(u) * total_warps;
+            if (t >= n_tiles) break;  // warp-uniform
+            uint4 q[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const uint32_t sr = send_reg[c];
+                const uint4 snd = sr == 0 ? ld[u][0] : (sr == 1 ? ld[u][1] : ld[u][2]);
+                const uint32_t src = (3u * lane + c) & 31u;
+                q[c].x = __shfl_sync(kFull, snd.x, src);
+                q[c].y = __shfl_sync(kFull, snd.y, src);
+                q[c].z = __shfl_sync(kFull, snd.z, src);
+                q[c].w = __shfl_sync(kFull, snd.w, src);
+            }
+            const size_t idx = (t << 5) + lane;
+            const bool live = idx < n;
+            uint4 out = make_uint4(0, 0, 0, 0);
+            if (live) {
+                out = dispatch_one<kSmemTable>(img, tb, q[0], q[1], q[2]);
+                st_stream(replies + idx, out);
+            }
+            if (kExtras) {
+                // compaction of failed calls: one atomic per warp, ballot-ranked slots
+                const bool failed = live && out.w != PTYPE_ST_OK;
+                const uint32_t live_mask = __ballot_sync(kFull, live);
+                const uint32_t fail_mask = __ballot_sync(kFull, failed);
+                if (lane == 0) ok_calls += __popc(live_mask & ~fail_mask);
+                if (fail_mask) {
+                    unsigned long long base = 0;
+                    const int leader = __ffs(fail_mask) - 1;
+                    if (static_cast<int>(lane) == leader)
+                        base = atomicAdd(stats + kStatFailed,
+                                         static_cast<unsigned long long>(__popc(fail_mask)));
+                    base = __shfl_sync(kFull, base, leader);
+                    if (failed) {
+                        atomicAdd(&s_status[out.w], 1u);
+                        const unsigned long long slot = base + __popc(fail_mask & ((1u << lane) - 1u));
+                        if (failed_idx != nullptr && slot < failed_cap)
+                            failed_idx[slot] = idx_base + static_cast<uint32_t>(idx);
+                    }
+                }
+            }
+        }
+    }
+    if (!table_ready) mbar_wait(&s_bar, 0);  // never leave a bulk copy in flight behind us
+
+    if (kExtras) {
+        if (lane == 0 && ok_calls) atomicAdd(&s_status[PTYPE_ST_OK], ok_calls);
+        __syncthreads();
+        if (threadIdx.x < PTYPE_ST__COUNT && s_status[threadIdx.x]) {
+            atomicAdd(stats + kStatByStatus + threadIdx.x,
+                      static_cast<unsigned long long>(s_status[threadIdx.x]));
+            atomicAdd(stats + kStatCalls, static_cast<unsigned long long>(s_status[threadIdx.x]));
+        }
+    }
+}
+
+// ---------------------------------------------------------- reply checksum
+
+__global__ void __launch_bounds__(kChecksumThreads)
+    checksum_partials_kernel(const uint4* __restrict__ replies, const size_t n,
+                             const uint64_t index_base, unsigned long long* __restrict__ partials) {
+    unsigned long long acc = 0;
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint4 r = ld_stream(replies + i);
+        const uint64_t value = static_cast<uint64_t>(r.x) | (static_cast<uint64_t>(r.y) << 32);
+        acc += checksum_term(value, r.z, r.w, index_base + i);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
+    __shared__ unsigned long long s_part[kChecksumThreads / 32];
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long b = 0;
+        for (int w = 0; w < kChecksumThreads / 32; ++w) b += s_part[w];
+        partials[blockIdx.x] = b;
+    }
+}
+
+__global__ void __launch_bounds__(kChecksumThreads)
+    checksum_final_kernel(const unsigned long long* __restrict__ partials, const int n_partials,
+                          unsigned long long* __restrict__ out) {
+    unsigned long long acc = 0;
+    for (int i = threadIdx.x; i < n_partials; i += blockDim.x) acc += partials[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
+    __shared__ unsigned long long s_part[kChecksumThreads / 32];
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long b = 0;
+        for (int w = 0; w < kChecksumThreads / 32; ++w) b += s_part[w];
+        *out = b;
+    }
+}
+
+constexpr int kUnrollDefault = 2;
+
+template <bool kSmemTable, bool kExtras>
+cudaError_t launch_variant(const DeviceImage& img, const LaunchPlan& plan, int blocks,
+                           const ptype_req* reqs, size_t n, ptype_reply* replies, uint32_t* failed_idx,
+                           uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
+                           cudaStream_t stream) {
+    auto kernel = dispatch_kernel<kSmemTable, kExtras, kUnrollDefault>;
+    kernel<<<blocks, plan.threads, plan.dyn_smem, stream>>>(
+        img, reinterpret_cast<const uint4*>(reqs), n, reinterpret_cast<uint4*>(replies), failed_idx,
+        failed_cap, idx_base, stats);
+    return cudaGetLastError();
+}
+
+template <bool kSmemTable, bool kExtras>
+cudaError_t occupancy_variant(int threads, size_t dyn_smem, int* ctas_per_sm) {
+    auto kernel = dispatch_kernel<kSmemTable, kExtras, kUnrollDefault>;
+    if (dyn_smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(dyn_smem));
+        if (e != cudaSuccess) return e;
+    }
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, kernel, threads, dyn_smem);
+}
+
+}  // namespace
+
+// Block shape and residency.  A staged table bigger than ~100 KiB leaves room for one
+// CTA per SM, which then runs 1024 threads; small tables run several 256-thread CTAs
+// per SM.  Either way the persistent grid is ctas_per_sm x SM count (148 on B200).
+cudaError_t plan_dispatch(const DeviceImage& img, uint32_t flags, bool extras, LaunchPlan* plan) {
+    const size_t table_bytes = static_cast<size_t>(img.n_slots) * sizeof(ptype_slot);
+    constexpr size_t kSmemBudget = 200 * 1024;
+    plan->smem_table = !(flags & PTYPE_F_GLOBAL_TABLE) && table_bytes <= kSmemBudget;
+    plan->dyn_smem = plan->smem_table ? table_bytes : 0;
+    plan->threads = plan->dyn_smem > 100 * 1024 ? 1024 : 256;
+    int ctas = 0;
+    cudaError_t e;
+    if (plan->smem_table)
+        e = extras ? occupancy_variant<true, true>(plan->threads, plan->dyn_smem, &ctas)
+                   : occupancy_variant<true, false>(plan->threads, plan->dyn_smem, &ctas);
+    else
+        e = extras ? occupancy_variant<false, true>(plan->threads, plan->dyn_smem, &ctas)
+                   : occupancy_variant<false, false>(plan->threads, plan->dyn_smem, &ctas);
+    if (e != cudaSuccess) return e;
+    if (ctas < 1) return cudaErrorLaunchOutOfResources;
+    plan->ctas_per_sm = ctas;
+    return cudaSuccess;
+}
+
+int grid_for(const LaunchPlan& plan, size_t n, int sm_count) {
+    const size_t tiles = (n + 31) / 32;
+    const size_t warps_per_cta = static_cast<size_t>(plan.threads) / 32;
+    size_t want = (tiles + warps_per_cta - 1) / warps_per_cta;
+    const size_t resident = static_cast<size_t>(sm_count) * plan.ctas_per_sm;
+    if (want > resident) want = resident;
+    return want < 1 ? 1 : static_cast<int>(want);
+}
+
+cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int blocks,
+                            const ptype_req* reqs, size_t n, ptype_reply* replies, uint32_t* failed_idx,
+                            uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
+                           cudaStream_t stream) {
+    const bool extras = stats != nullptr;
+    if (plan.smem_table) {
+        return extras ? launch_variant<true, true>(img, plan, blocks, reqs, n, replies, failed_idx, failed_cap, idx_base, stats, stream)
+                      : launch_variant<true, false>(img, plan, blocks, reqs, n, replies, failed_idx, failed_cap, idx_base, stats, stream);
+    }
+    return extras ? launch_variant<false, true>(img, plan, blocks, reqs, n, replies, failed_idx, failed_cap, idx_base, stats, stream)
+                  : launch_variant<false, false>(img, plan, blocks, reqs, n, replies, failed_idx, failed_cap, idx_base, stats, stream);
+}
+
+cudaError_t launch_reply_checksum(const ptype_reply* replies, size_t n, uint64_t index_base,
+                                  unsigned long long* partials, unsigned long long* out,
+                                  cudaStream_t stream) {
+    checksum_partials_kernel<<<kChecksumBlocks, kChecksumThreads, 0, stream>>>(
+        reinterpret_cast<const uint4*>(replies), n, index_base, partials);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    checksum_final_kernel<<<1, kChecksumThreads, 0, stream>>>(partials, kChecksumBlocks, out);
+    return cudaGetLastError();
+}
+
+}  // namespace ptype

@@ -1,0 +1,62 @@
+// table_hash.h — hash functions shared by the host image builder and the kernels.
+// Everything here must give the same bits on host and device.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define PTYPE_HD __host__ __device__ __forceinline__
+#else
+#define PTYPE_HD inline
+#endif
+
+namespace ptype {
+
+// hash/fnv New32a [Go stdlib]; the reference's one explicit hash (cluster/rpc.go:267).
+PTYPE_HD uint32_t fnv1a32(const void* data, size_t len) {
+    const unsigned char* s = static_cast<const unsigned char*>(data);
+    uint32_t h = 0x811c9dc5u;
+    for (size_t i = 0; i < len; ++i) {
+        h ^= s[i];
+        h *= 0x01000193u;
+    }
+    return h;
+}
+
+// hash/fnv New64a with the offset basis xor-ed by `salt` (0 = plain New64a).
+PTYPE_HD uint64_t fnv1a64(const void* data, size_t len, uint64_t salt) {
+    const unsigned char* s = static_cast<const unsigned char*>(data);
+    uint64_t h = 0xcbf29ce484222325ull ^ salt;
+    for (size_t i = 0; i < len; ++i) {
+        h ^= s[i];
+        h *= 0x100000001b3ull;
+    }
+    return h;
+}
+
+// murmur3 finaliser: spreads the FNV key before it picks a slot / mixes a checksum.
+PTYPE_HD uint64_t fmix64(uint64_t x) {
+    x ^= x >> 33;
+    x *= 0xff51afd7ed558ccdull;
+    x ^= x >> 33;
+    x *= 0xc4ceb9fe1a85ec53ull;
+    x ^= x >> 33;
+    return x;
+}
+
+// Home slot of a key in a table of n_slots (any n_slots >= 1): multiply-shift range
+// reduction of the top 32 mixed bits, so the table need not be a power of two and
+// can be sized to fill shared memory.
+PTYPE_HD uint32_t home_slot(uint64_t key, uint32_t n_slots) {
+    uint32_t h = static_cast<uint32_t>(fmix64(key) >> 32);
+    return static_cast<uint32_t>((static_cast<uint64_t>(h) * n_slots) >> 32);
+}
+
+// One term of the order-independent reply checksum (see ptype_b200_reply_checksum).
+PTYPE_HD uint64_t checksum_term(uint64_t value, uint32_t node, uint32_t status, uint64_t idx) {
+    uint64_t w1 = static_cast<uint64_t>(node) | (static_cast<uint64_t>(status) << 32);
+    return fmix64(value + 0x9E3779B97F4A7C15ull * (idx + 1)) ^
+           fmix64(w1 ^ (idx * 0xC2B2AE3D27D4EB4Full + 0x165667B19E3779F9ull));
+}
+
+}  // namespace ptype

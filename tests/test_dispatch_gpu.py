@@ -1,0 +1,323 @@
+"""Parity of the CUDA dispatch path with the CPU oracle, through the C ABI.
+
+Bit-exact bar: every reply record (value, node, status) must equal the oracle's on
+the same seeded inputs.  Sizes the oracle finishes in seconds are compared in full;
+BASELINE.json's full sizes are also checked through size-independent properties
+(idempotence, shard-sum of checksums, status accounting)."""
+import threading
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import ptype_b200 as p
+from ptype_b200 import workloads as w
+from ptype_b200.sharding import shard_indices
+
+pytestmark = pytest.mark.gpu
+GOLD = Path(__file__).parent / "golden"
+LIMIT = 1 << 16  # the context's default Prime.Check iteration limit
+
+
+def assert_same(got: np.ndarray, want: np.ndarray, reqs=None):
+    if got.tobytes() == want.tobytes():
+        return
+    bad = np.flatnonzero((got["value"] != want["value"]) | (got["node"] != want["node"]) |
+                         (got["status"] != want["status"]))
+    j = int(bad[0])
+    raise AssertionError(f"{len(bad)} of {len(got)} replies differ; first at {j}: got {got[j]} want {want[j]}"
+                         + (f" req {reqs[j]}" if reqs is not None else ""))
+
+
+def device_roundtrip(ctx, reqs, flags=0):
+    """Upload, dispatch with device pointers (one launch), download."""
+    n = len(reqs)
+    d_req = ctx.device_buffer(max(n, 1) * 48).upload(reqs)
+    d_rep = ctx.device_buffer(max(n, 1) * 16)
+    try:
+        ctx.dispatch_device(d_req, n, d_rep, flags=flags)
+        return d_rep.download(p.REPLY_DTYPE, n)
+    finally:
+        d_req.free()
+        d_rep.free()
+
+
+SPECS = {
+    "calc3": lambda: w.calculator_registry(),
+    "calcmesh": lambda: w.calculator_registry(mesh=True),
+    "optimus": lambda: w.optimus_registry(),
+}
+
+
+@pytest.mark.parametrize("name", list(SPECS))
+def test_golden_fixtures(ctx, name):
+    """CUDA replies equal the committed fixture replies (tests/golden/make_fixtures.py)."""
+    fx = np.load(GOLD / "dispatch_fixtures.npz")
+    ctx.set_check_limit(LIMIT)
+    ctx.publish(SPECS[name]().image())
+    req = fx[f"{name}_req"].view(p.REQ_DTYPE).reshape(-1)
+    want = fx[f"{name}_rep"].view(p.REPLY_DTYPE).reshape(-1)
+    assert_same(ctx.dispatch(req), want, req)
+    assert_same(device_roundtrip(ctx, req), want, req)
+    assert_same(device_roundtrip(ctx, req, flags=p.F_GLOBAL_TABLE), want, req)
+
+
+@pytest.mark.parametrize("name", list(SPECS))
+@pytest.mark.parametrize("limit", [LIMIT, 1 << 20, 0])
+def test_edge_cases_every_status(ctx, oracle, name, limit):
+    spec = SPECS[name]()
+    spec.declare = ["declared_but_empty"]
+    services = sorted({s for s, *_ in spec.nodes}) + ["declared_but_empty"]
+    ctx.set_check_limit(limit)
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    req = w.edge_case_calls(services)
+    want = snap.dispatch(req, check_limit=limit)
+    seen = set(np.unique(want["status"]).tolist())
+    assert {0, 1, 2, 3, 4, 5, 6} <= seen
+    assert_same(ctx.dispatch(req), want, req)
+    assert_same(device_roundtrip(ctx, req), want, req)
+    ctx.set_check_limit(LIMIT)
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 31, 32, 33, 63, 64, 65, 95, 96, 97, 1000, 4097,
+                               128 * 1024 - 1, 128 * 1024, 128 * 1024 + 1, 3 * 128 * 1024 + 77])
+def test_ragged_sizes(ctx, oracle, n):
+    """Empty, sub-warp, warp-boundary and pipeline-chunk-boundary batch sizes."""
+    spec = w.calculator_registry()
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    req = w.calculator_calls(n, seed=0x5EED0002 + n)
+    want = snap.dispatch(req)
+    assert_same(ctx.dispatch(req), want, req)
+    assert_same(device_roundtrip(ctx, req), want, req)
+
+
+@pytest.mark.parametrize("mesh", [False, True])
+def test_c2_calculator_1m(ctx, oracle, mesh):
+    """BASELINE config 2 at full size: 2^20 mixed Add/Multiply calls, 1 service x 16 nodes."""
+    spec = w.calculator_registry(mesh=mesh)
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    req = w.calculator_calls(1 << 20)
+    want = snap.dispatch(req, threads=8)
+    got = device_roundtrip(ctx, req)
+    assert_same(got, want, req)
+    sel = np.array(snap.selected("calculator"))
+    assert np.array_equal(np.unique(got["node"]), np.unique(sel))
+    assert np.array_equal(got["node"], sel[(req["seq"] % np.uint64(len(sel))).astype(np.int64)])
+    assert_same(ctx.dispatch(req), want, req)           # host-buffer pipeline, 8 chunks
+    assert_same(device_roundtrip(ctx, req), got)         # idempotent
+
+
+@pytest.fixture(scope="module")
+def stress(oracle):
+    spec = w.stress_registry(10_000, 64)
+    kv, snap = oracle.snapshot_from_spec(spec)
+    return spec, spec.image(), snap, kv
+
+
+@pytest.mark.parametrize("zipf", [False, True])
+def test_c3_registry_stress(ctx, stress, oracle, zipf):
+    """BASELINE config 3: 10k services x 64 nodes (12 800-slot table staged in shared
+    memory), 2^22 routed calls compared in full; 1 % name an unregistered service."""
+    spec, img, snap, _ = stress
+    assert img.header.n_slots == 12_800
+    ctx.publish(img)
+    n = 1 << 22
+    req = w.stress_calls(n, 10_000, zipf=zipf)
+    want = snap.dispatch(req, threads=8)
+    got = device_roundtrip(ctx, req)
+    assert_same(got, want, req)
+    assert_same(device_roundtrip(ctx, req, flags=p.F_GLOBAL_TABLE), want, req)
+    miss = got["status"] == p.ST_NO_SERVICE
+    assert 0.005 < miss.mean() < 0.02 and np.all(got["node"][miss] == p.NO_NODE)
+    ok = got["status"] == p.ST_OK
+    assert ok.sum() + miss.sum() == n
+    # every routed node belongs to the service the call named
+    assert np.all((got["node"][ok] // 64) < 10_000)
+
+
+def test_c3_full_size_properties(ctx, stress, oracle):
+    """2^24 calls (config 3's size): full compare against the 8-thread oracle, plus
+    checksum-of-shards == checksum-of-whole computed on the device."""
+    spec, img, snap, _ = stress
+    ctx.publish(img)
+    n = 1 << 24
+    req = w.stress_calls(n, 10_000)
+    d_req = ctx.device_buffer(n * 48).upload(req)
+    d_rep = ctx.device_buffer(n * 16)
+    ctx.dispatch_device(d_req, n, d_rep)
+    whole = ctx.reply_checksum(d_rep, n, device=True)
+    got = d_rep.download(p.REPLY_DTYPE, n)
+    want = snap.dispatch(req, threads=8)
+    assert_same(got, want)
+    assert whole == oracle.reply_checksum(want)
+    # shard the stream 4 ways by request-id hash; the order-independent checksum adds up
+    total = 0
+    for rank in range(4):
+        idx = shard_indices(n, 4, rank)
+        part = ctx.dispatch(req[idx])
+        assert_same(part, want[idx])
+        # shard terms are indexed by their position in the whole stream
+        total = (total + sum_terms(oracle, part, idx)) & ((1 << 64) - 1)
+    assert total == whole
+    d_req.free()
+    d_rep.free()
+
+
+def sum_terms(oracle, part, idx):
+    """Checksum of shard replies under their global stream positions (numpy restatement of
+    the definition in include/ptype_b200.h; checked against the oracle on a prefix)."""
+    from ptype_b200.sharding import mix64
+    with np.errstate(over="ignore"):
+        pos = idx.astype(np.uint64)
+        w0 = part["value"].view(np.uint64)
+        w1 = part["node"].astype(np.uint64) | (part["status"].astype(np.uint64) << np.uint64(32))
+        t = mix64(w0 + np.uint64(0x9E3779B97F4A7C15) * (pos + np.uint64(1))) ^ \
+            mix64(w1 ^ (pos * np.uint64(0xC2B2AE3D27D4EB4F) + np.uint64(0x165667B19E3779F9)))
+        total = int(t.sum(dtype=np.uint64))
+    assert int(t[:1].sum(dtype=np.uint64)) == oracle.reply_checksum(part[:1], int(idx[0]))
+    return total
+
+
+def test_c3_mesh_variant(ctx, oracle):
+    spec = w.stress_registry(2_000, 64, mesh=True)
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    req = w.stress_calls(1 << 20, 2_000)
+    assert_same(device_roundtrip(ctx, req), snap.dispatch(req, threads=8), req)
+
+
+def test_c4_optimus_replay(ctx, oracle):
+    """BASELINE config 4: the coordinator's splitWork stream (>= 2^20 Prime.Check calls)."""
+    spec = w.optimus_registry()
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    req = w.optimus_calls(1 << 20)
+    want = snap.dispatch(req, threads=8)
+    got = device_roundtrip(ctx, req)
+    assert_same(got, want, req)
+    # watchReplies (coordinator.go:91-99): a target is composite iff some chunk reply != target
+    composite = got["value"] != req["a2"]
+    assert composite.any() and (~composite).any()
+    assert np.all(req["a2"][composite] % got["value"][composite] == 0)
+
+
+def test_stats_and_failed_list(ctx, oracle):
+    spec = w.calculator_registry()
+    spec.declare = ["declared_but_empty"]
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    req = np.concatenate([w.edge_case_calls(["calculator", "declared_but_empty"]),
+                          w.calculator_calls(300_000)])
+    want = snap.dispatch(req, check_limit=LIMIT)
+    n_fail = int((want["status"] != 0).sum())
+    rep, failed, stats = ctx.dispatch_ex(req, failed_cap=n_fail + 10)
+    assert_same(rep, want, req)
+    assert stats.calls == len(req) and stats.failed_count == n_fail
+    assert list(stats.by_status) == np.bincount(want["status"], minlength=8).tolist()
+    assert np.array_equal(np.sort(failed), np.flatnonzero(want["status"] != 0))
+    # a list shorter than the failures: count still exact, entries valid and distinct
+    rep, failed, stats = ctx.dispatch_ex(req, failed_cap=7)
+    assert stats.failed_count == n_fail and len(failed) == 7 and len(set(failed.tolist())) == 7
+    assert np.all(want["status"][failed] != 0)
+    # device-pointer flavour
+    n = len(req)
+    d_req, d_rep = ctx.device_buffer(n * 48).upload(req), ctx.device_buffer(n * 16)
+    d_failed, d_stats = ctx.device_buffer((n_fail + 10) * 4), ctx.device_buffer(80)
+    ctx.dispatch_device(d_req, n, d_rep, failed=d_failed, failed_cap=n_fail + 10, stats=d_stats)
+    words = d_stats.download(np.uint64, 10)
+    assert words[0] == n and words[9] == n_fail
+    assert np.array_equal(np.sort(d_failed.download(np.uint32, n_fail)), np.flatnonzero(want["status"] != 0))
+    assert_same(d_rep.download(p.REPLY_DTYPE, n), want)
+    for b in (d_req, d_rep, d_failed, d_stats):
+        b.free()
+
+
+@pytest.mark.parametrize("n", [0, 1, 33, 100_000, (1 << 20) + 3])
+def test_reply_checksum(ctx, oracle, n):
+    rng = np.random.default_rng(n)
+    rep = np.zeros(n, dtype=p.REPLY_DTYPE)
+    rep["value"] = rng.integers(-(1 << 63), (1 << 63) - 1, n, dtype=np.int64)
+    rep["node"] = rng.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32)
+    rep["status"] = rng.integers(0, 8, n, dtype=np.uint32)
+    for base in (0, 12345, (1 << 63) + 5):
+        assert ctx.reply_checksum(rep, index_base=base) == oracle.reply_checksum(rep, base)
+    if n > 1:
+        swapped = rep.copy()
+        swapped[[0, n - 1]] = swapped[[n - 1, 0]]
+        if swapped[0] != rep[0]:
+            assert ctx.reply_checksum(swapped) != ctx.reply_checksum(rep)  # position matters
+
+
+def test_snapshot_flip_between_batches(ctx, oracle):
+    """publish -> epoch flip mirrors handleNewNodes' swap (cluster/rpc.go:226-236): batches
+    before the flip see the old node list, batches after see the new one."""
+    req = w.calculator_calls(50_000)
+    spec_a = w.calculator_registry(16)
+    spec_b = w.calculator_registry(5)           # nodes 06..16 deregistered
+    for epoch, spec in ((11, spec_a), (12, spec_b), (13, spec_a), (14, spec_b)):
+        ctx.publish(spec.image(epoch=epoch))
+        assert ctx.epoch() == epoch
+        kv, snap = oracle.snapshot_from_spec(spec)
+        assert ctx.image.selected("calculator") == snap.selected("calculator")
+        assert_same(ctx.dispatch(req), snap.dispatch(req), req)
+    # an image with no services at all: every call gets NO_SERVICE
+    ctx.publish(w.RegistrySpec([], [], [], "", 3).image(epoch=15))
+    rep = ctx.dispatch(req[:1000])
+    assert np.all(rep["status"] == p.ST_NO_SERVICE) and np.all(rep["node"] == p.NO_NODE)
+    assert np.all(rep["value"] == 0)
+
+
+def test_max_connections_larger_than_shared_cache(ctx, oracle):
+    """MaxConnections above the 256 hashes kept in shared memory: hashes read from global."""
+    nodes = [("wide", f"n{i:04d}", f"10.1.{i >> 8}.{i & 255}", 7000) for i in range(700)]
+    spec = w.RegistrySpec(nodes, [("wide", "Calculator")], [], "10.9.9.9", 300)
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    req = w.calculator_calls(20_000)
+    req["svc_key"] = p.service_key("wide")
+    assert_same(ctx.dispatch(req), snap.dispatch(req), req)
+
+
+def test_colliding_table_slots(ctx, oracle):
+    """A nearly full table (forced size): long probe chains, wrap-around, misses that walk
+    to an empty slot."""
+    spec = w.stress_registry(500, 2)
+    img = spec.image(n_slots=501)
+    ctx.publish(img)
+    kv, snap = oracle.snapshot_from_spec(spec)
+    req = w.stress_calls(100_000, 500, miss_rate=0.2)
+    assert_same(device_roundtrip(ctx, req), snap.dispatch(req), req)
+    assert_same(device_roundtrip(ctx, req, flags=p.F_GLOBAL_TABLE), snap.dispatch(req), req)
+
+
+def test_calls_from_many_threads(ctx, oracle):
+    """cgo calls arrive on arbitrary OS threads: no thread-local CUDA state in the library."""
+    spec = w.calculator_registry()
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    errors = []
+
+    def worker(seed):
+        try:
+            req = w.calculator_calls(70_000, seed=seed)
+            assert_same(ctx.dispatch(req), snap.dispatch(req), req)
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    ts = [threading.Thread(target=worker, args=(100 + i,)) for i in range(6)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errors, errors
+
+
+def test_dispatch_without_image_fails():
+    c = p.Context([0])
+    try:
+        with pytest.raises(p.PtypeError) as e:
+            c.dispatch(w.calculator_calls(10))
+        assert e.value.code == 4  # PTYPE_E_NO_IMAGE
+    finally:
+        c.close()

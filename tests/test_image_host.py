@@ -1,0 +1,183 @@
+"""Host-side logic: the registry image builder against the oracle's snapshot, the C ABI's
+exported symbols against include/ptype_b200.h, workload generators.  No GPU."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import ptype_b200 as p
+from ptype_b200 import _abi, workloads as w
+from ptype_b200.sharding import shard_of, shard_indices
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def test_header_symbols_exported():
+    """Every function include/ptype_b200.h declares is exported by the library and bound."""
+    text = (ROOT / "include" / "ptype_b200.h").read_text()
+    declared = set(re.findall(r"\b(ptype_b200_\w+)\s*\(", text))
+    bound = {name for name, _, _ in _abi.SIGNATURES}
+    assert declared == bound, (declared - bound, bound - declared)
+    lib = C.CDLL(str(p.LIB_PATH))
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert _abi.lib.ptype_b200_abi_version() == 1
+
+
+def test_record_layouts():
+    assert p.REQ_DTYPE.itemsize == 48 and p.REPLY_DTYPE.itemsize == 16
+    assert [p.REQ_DTYPE.fields[f][1] for f in ("svc_key", "seq", "method", "recv", "a0", "a1", "a2")] == \
+        [0, 8, 16, 20, 24, 32, 40]
+    assert [p.REPLY_DTYPE.fields[f][1] for f in ("value", "node", "status")] == [0, 8, 12]
+
+
+def test_hash_helpers_match_oracle(oracle):
+    for s in ["", "0", "calculator", "prime_worker", "svc_00042", "Calculator.Multiply", "x" * 300]:
+        b = s.encode()
+        assert _abi.lib.ptype_b200_fnv1a32(b, len(b)) == oracle.lib().po_fnv1a32(b, len(b))
+        for salt in (0, 1, 0xDEADBEEF):
+            assert p.service_key(s, salt) == oracle.lib().po_fnv1a64_salted(b, len(b), salt)
+    for sm in ["Calculator.Multiply", "Prime.Check", "nodot", "", ".", "a.b.c", "Calculator."]:
+        m, r = C.c_uint32(), C.c_uint32()
+        oracle.lib().po_method_key(sm.encode(), C.byref(m), C.byref(r))
+        assert p.method_key(sm) == (m.value, r.value)
+    assert p.method_key("nodot")[1] == p.RECV_ILL_FORMED
+    for addr in ["", "10.0.0.5", "127.0.0.1"]:
+        for i in (0, 1, 2, 10, 123):
+            for n in (1, 4, 16, 64):
+                assert p.conn_hash(addr, i) % n == oracle.lib().po_hash_connection_index(addr.encode(), i, n)
+
+
+SPECS = {
+    "calc3": lambda: w.calculator_registry(),
+    "calcmesh": lambda: w.calculator_registry(mesh=True),
+    "optimus": lambda: w.optimus_registry(),
+    "stress_small": lambda: w.stress_registry(200, 7),
+    "stress_mesh_small": lambda: w.stress_registry(50, 9, mesh=True),
+}
+
+
+@pytest.mark.parametrize("name", list(SPECS))
+def test_image_selection_matches_oracle(oracle, name):
+    """getSelectedNodes() per service, and the global node numbering, agree with the oracle."""
+    spec = SPECS[name]()
+    spec.declare = ["declared_but_empty"]
+    img = spec.image(epoch=7)
+    kv, snap = oracle.snapshot_from_spec(spec)
+    assert img.epoch == 7 and img.header.n_nodes == len(spec.nodes)
+    services = sorted({s for s, *_ in spec.nodes})
+    for svc in services[:64] + services[-8:]:
+        assert img.selected(svc) == snap.selected(svc), svc
+    assert img.selected("declared_but_empty") == [] == snap.selected("declared_but_empty")
+    assert img.selected("never_heard_of_it") is None and snap.selected("never_heard_of_it") is None
+    for nid in list(range(min(40, len(spec.nodes)))) + [len(spec.nodes) - 1]:
+        a, port, svc, _ = img.node(nid)
+        assert (a, port, svc) == snap.node(nid)
+
+
+def test_node_order_is_etcd_key_order(oracle):
+    """node10 sorts before node2, and 'foo-x' before 'foo' (because '-' < '/')."""
+    nodes = [("foo", "node2", "h2", 2), ("foo", "node10", "h10", 10), ("foo", "node1", "h1", 1),
+             ("foo-x", "a", "hx", 5), ("foo_y", "a", "hy", 6), ("bar", "z", "hb", 7)]
+    spec = w.RegistrySpec(nodes, [], [], "", 0)
+    img = spec.image()
+    kv, snap = oracle.snapshot_from_spec(spec)
+    got = [img.node(i)[:3] for i in range(len(nodes))]
+    assert got == [snap.node(i) for i in range(len(nodes))]
+    assert [g[0] for g in got] == ["hb", "hx", "h1", "h10", "h2", "hy"]
+    assert img.selected("foo") == [2, 3, 4]
+
+
+def test_reregister_overwrites_and_validation():
+    b = p.ImageBuilder("", 3)
+    b.register("s", "n", "old", 1).register("s", "n", "new", 2)
+    img = b.finish(3)
+    assert img.node(0)[:2] == ("new", 2) and img.header.n_nodes == 1
+    for bad in ("", "a/b", ".", ".."):
+        with pytest.raises(p.PtypeError):
+            p.ImageBuilder().register(bad, "n", "h", 1)
+    with pytest.raises(p.PtypeError):
+        p.ImageBuilder("", -1)          # Go would panic in make([]Node, 0, -1) (rpc.go:257)
+    with pytest.raises(p.PtypeError):
+        p.ImageBuilder().expose("s", "NoSuchReceiver")
+    blob = bytearray(img.blob)
+    blob[200] ^= 1
+    with pytest.raises(p.PtypeError):
+        p.Image(bytes(blob))
+    with pytest.raises(p.PtypeError):
+        p.Image(img.blob[:-16])
+
+
+def test_table_sizing():
+    small = w.calculator_registry().image()
+    assert small.header.n_slots == 8
+    spec = w.stress_registry(300, 1)
+    assert spec.image().header.n_slots == 600
+    assert spec.image(n_slots=301).header.n_slots == 301
+    with pytest.raises(p.PtypeError):
+        spec.image(n_slots=300)
+
+
+def test_stress_image_fits_shared_memory_budget():
+    """C3's 10 000 services get a 12 800-slot (200 KiB) table: the size the kernel stages."""
+    spec = w.stress_registry(10_000, 1)
+    img = spec.image()
+    assert img.header.n_slots == 12_800 and img.header.n_services == 10_000
+    assert img.header.n_slots * 16 <= 200 * 1024
+
+
+def test_split_work_generator(oracle):
+    for t in (-5, 0, 1, 9, 10, 11, 91, 100, 1000, 12345):
+        buf = (C.c_int64 * (3 * 2000))()
+        n = oracle.lib().po_split_work(t, buf, 2000)
+        got = w.split_work(t)
+        assert n == len(got)
+        assert np.array_equal(np.array(buf[: 3 * n], dtype=np.int64).reshape(n, 3), got)
+
+
+def test_optimus_stream_is_split_work():
+    r = w.optimus_calls(5000, t_lo=50, t_hi=500)
+    assert len(r) >= 5000
+    # re-derive the stream target by target
+    i = 0
+    while i < len(r):
+        t = int(r["a2"][i])
+        chunks = w.split_work(t)
+        seg = r[i: i + len(chunks)]
+        assert np.array_equal(np.stack([seg["a0"], seg["a1"], seg["a2"]], axis=1), chunks)
+        i += len(chunks)
+    assert np.array_equal(r["seq"], np.arange(1, len(r) + 1, dtype=np.uint64))
+
+
+def test_stress_stream_per_service_seq():
+    r = w.stress_calls(20_000, 50, miss_rate=0.05)
+    keys = {p.service_key(f"svc_{s:05d}"): s for s in range(50)}
+    assert r["seq"].min() == 1
+    hit = np.isin(r["svc_key"], np.array(list(keys), dtype=np.uint64))
+    assert 0.93 < hit.mean() < 0.97
+
+
+def test_sharding_partitions_stream():
+    n, g = 100_000, 8
+    owner = shard_of(np.arange(n, dtype=np.uint64), g)
+    assert owner.min() == 0 and owner.max() == g - 1
+    counts = np.bincount(owner, minlength=g)
+    assert counts.sum() == n and counts.min() > n / g * 0.95
+    parts = [shard_indices(n, g, r) for r in range(g)]
+    allidx = np.sort(np.concatenate(parts))
+    assert np.array_equal(allidx, np.arange(n))
+
+
+def test_sharded_dispatch_equals_unsharded(oracle):
+    """Sharding changes no reply: seq travels in the record (rpc.go:181)."""
+    spec = w.calculator_registry()
+    kv, snap = oracle.snapshot_from_spec(spec)
+    r = w.calculator_calls(10_000)
+    whole = snap.dispatch(r)
+    out = np.empty_like(whole)
+    for rank in range(4):
+        idx = shard_indices(len(r), 4, rank)
+        out[idx] = snap.dispatch(r[idx])
+    assert out.tobytes() == whole.tobytes()
