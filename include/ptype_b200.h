@@ -302,6 +302,39 @@ int ptype_b200_set_check_limit(ptype_ctx*, uint64_t max_iterations);
 int ptype_b200_reply_checksum(ptype_ctx*, int dev, const ptype_reply* replies, size_t n,
                               uint64_t index_base, uint64_t* checksum, uint32_t flags);
 
+/* The same checksum for hosts that cannot allocate device memory while they run.
+ * (No counterpart in the reference: the checksum itself is an addition of this
+ * library, and so is this variant.)
+ *
+ * Who needs it: a host whose dispatch loop must never hit cudaMalloc/cudaFree,
+ * because those calls hold up every stream of the GPU while they run, and a host
+ * that has already given all device memory to its own pool or runs under a fixed
+ * quota, where a late cudaMalloc can simply fail.  ptype_b200_reply_checksum
+ * allocates its partial-sum buffer on first use; this entry point never calls
+ * cudaMalloc, cudaFree or any allocating routine.  It needs no ptype_ctx.
+ *
+ * The partial sums go to a 128 KiB array compiled into the library, present on
+ * every GPU that loads it until the process exits.  That fixes the maximum:
+ * n <= 67 108 864 replies (16384 partial sums x 4096 replies each, 1 GiB of reply
+ * records).  A larger n is refused with PTYPE_E_LIMIT and a message in
+ * ptype_b200_last_error(); split the range (checksums of sub-ranges add up when
+ * each is given its own index_base) or use ptype_b200_reply_checksum.
+ *
+ * device      CUDA ordinal the pointers belong to (made current for the call, then
+ *             the caller's device is restored).
+ * d_replies   device pointer, n records;  d_checksum  device pointer, one uint64.
+ * cuda_stream a cudaStream_t (NULL = default stream); the two kernels are enqueued
+ *             there and the call returns without waiting.
+ *
+ * The first call on each GPU also looks up where that GPU keeps the array; make
+ * that first call before starting any stream capture.  All calls on a GPU share the
+ * one array: two calls whose kernels can overlap (different streams, or several
+ * threads) race on it and both results are garbage — keep calls on one stream or
+ * order them yourself.  Nothing in the array has to be cleared between calls: each
+ * call overwrites every entry it later reads. */
+int ptype_b200_reply_checksum_noalloc(int device, const ptype_reply* d_replies, size_t n,
+                                      uint64_t index_base, uint64_t* d_checksum, void* cuda_stream);
+
 /* Kernel launches issued by this context so far (bench bookkeeping). */
 int ptype_b200_launch_count(ptype_ctx*, uint64_t* launches);
 

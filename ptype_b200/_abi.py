@@ -101,6 +101,8 @@ SIGNATURES = [
     ("ptype_b200_set_check_limit", C.c_int, [_vp, C.c_uint64]),
     ("ptype_b200_reply_checksum", C.c_int,
      [_vp, C.c_int, _vp, C.c_size_t, C.c_uint64, _u64p, C.c_uint32]),
+    ("ptype_b200_reply_checksum_noalloc", C.c_int,
+     [C.c_int, _vp, C.c_size_t, C.c_uint64, _vp, _vp]),
     ("ptype_b200_launch_count", C.c_int, [_vp, _u64p]),
 ]
 

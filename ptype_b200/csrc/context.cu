@@ -117,6 +117,10 @@ struct DeviceState {
 
 }  // namespace
 
+namespace ptype {
+void set_last_error(const char* text) { g_last_error = text ? text : ""; }
+}  // namespace ptype
+
 struct ptype_ctx {
     std::vector<DeviceState*> devs;
     std::atomic<uint64_t> check_limit{1ull << 16};

@@ -44,4 +44,7 @@ cudaError_t launch_reply_checksum(const ptype_reply* replies, size_t n, uint64_t
                                   unsigned long long* partials, unsigned long long* out,
                                   cudaStream_t stream);
 
+// Records the text ptype_b200_last_error() returns on the calling thread.
+void set_last_error(const char* text);
+
 }  // namespace ptype

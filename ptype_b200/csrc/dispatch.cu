@@ -21,6 +21,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdio>
+#include <mutex>
+
 #include "../../include/ptype_b200.h"
 #include "device_image.h"
 #include "table_hash.h"
@@ -497,3 +500,93 @@ cudaError_t launch_reply_checksum(const ptype_reply* replies, size_t n, uint64_t
 }
 
 }  // namespace ptype
+
+// ------------------------------------------------ checksum without allocation
+//
+// Some hosts of this library must not trigger a device allocation while they
+// dispatch: cudaMalloc and cudaFree stall every stream of the device until they
+// return, and a process that has handed all of its HBM to its own pool (or runs
+// under a fixed memory quota) may simply be refused.  ptype_b200_reply_checksum
+// lazily cudaMallocs a partial-sum buffer per context; the entry point below is
+// for those hosts.  Its partial sums live in the fixed array here instead, which
+// every GPU that loads this library carries (128 KiB) until the process exits.
+namespace ptype {
+namespace {
+
+constexpr int kNoAllocTile = kChecksumThreads * 16;  // replies folded into one partial sum
+constexpr int kNoAllocMaxPartials = 16384;           // 16384 x 8 B = 128 KiB of scratch
+constexpr size_t kNoAllocMaxReplies = static_cast<size_t>(kNoAllocMaxPartials) * kNoAllocTile;
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) unsigned long long g_noalloc_partials[kNoAllocMaxPartials];
+
+// Device addresses of the array above, one per GPU.  In host code the symbol name is
+// only a handle for the runtime, so the address each GPU gave the array has to be
+// asked for, once, while that GPU is the current device.
+unsigned long long* g_noalloc_addr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mu;
+
+cudaError_t noalloc_scratch(int device, unsigned long long** out) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (g_noalloc_addr[device] == nullptr) {
+        unsigned long long* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_partials);
+        if (e != cudaSuccess) return e;
+        g_noalloc_addr[device] = ptr;
+    }
+    *out = g_noalloc_addr[device];
+    return cudaSuccess;
+}
+
+}  // namespace
+}  // namespace ptype
+
+extern "C" int ptype_b200_reply_checksum_noalloc(int device, const ptype_reply* d_replies, size_t n,
+                                                 uint64_t index_base, uint64_t* d_checksum,
+                                                 void* cuda_stream) {
+    using namespace ptype;
+    char msg[256];
+    if (device < 0 || device >= kNoAllocMaxDevices || d_checksum == nullptr ||
+        (n != 0 && d_replies == nullptr)) {
+        set_last_error("ptype_b200_reply_checksum_noalloc: bad device ordinal or null pointer");
+        return PTYPE_E_INVAL;
+    }
+    if (n > kNoAllocMaxReplies) {
+        std::snprintf(msg, sizeof msg,
+                      "ptype_b200_reply_checksum_noalloc: n=%zu is beyond the %zu replies the built-in "
+                      "%d KiB scratch array covers; split the range or use ptype_b200_reply_checksum",
+                      n, kNoAllocMaxReplies,
+                      static_cast<int>(kNoAllocMaxPartials * sizeof(unsigned long long) / 1024));
+        set_last_error(msg);
+        return PTYPE_E_LIMIT;
+    }
+    int previous = -1;
+    cudaError_t e = cudaGetDevice(&previous);
+    if (e == cudaSuccess && previous != device) e = cudaSetDevice(device);
+    unsigned long long* partials = nullptr;
+    if (e == cudaSuccess) e = noalloc_scratch(device, &partials);  // first call on this GPU: set-up
+    if (e == cudaSuccess) {
+        cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+        const int tiles = static_cast<int>((n + kNoAllocTile - 1) / kNoAllocTile);
+        // Every partial the second pass reads is written by the first pass of this same
+        // call, so nothing left behind by an earlier call needs clearing.
+        if (tiles > 0) {
+            checksum_partials_kernel<<<tiles, kChecksumThreads, 0, stream>>>(
+                reinterpret_cast<const uint4*>(d_replies), n, index_base, partials);
+            e = cudaGetLastError();
+        }
+        if (e == cudaSuccess) {
+            checksum_final_kernel<<<1, kChecksumThreads, 0, stream>>>(
+                partials, tiles, reinterpret_cast<unsigned long long*>(d_checksum));
+            e = cudaGetLastError();
+        }
+    }
+    if (previous >= 0 && previous != device) cudaSetDevice(previous);
+    if (e != cudaSuccess) {
+        std::snprintf(msg, sizeof msg, "ptype_b200_reply_checksum_noalloc: %s (%s)",
+                      cudaGetErrorString(e), cudaGetErrorName(e));
+        set_last_error(msg);
+        return PTYPE_E_CUDA;
+    }
+    return PTYPE_OK;
+}
