@@ -34,6 +34,9 @@ sys.path.insert(0, str(ROOT))
 
 BYTES_PER_CALL = 64  # 48 B request + 16 B reply
 BATCH = 1 << 20
+# calls per step (per GPU) and resident batches rotated, per workload: C3 is quoted on 16M calls
+BATCH_OF = {"c2": 1 << 20, "c2mesh": 1 << 20, "c3": 1 << 24, "c4": 1 << 20}
+BUFFERS_OF = {"c2": 8, "c2mesh": 8, "c3": 2, "c4": 8}
 
 
 def measured_peak():
@@ -62,7 +65,7 @@ def make_workload(name: str, n: int, seed: int, salt: int = 0):
 WORKLOAD_TEXT = {
     "c2": "calculator batch of 2^20 mixed Add/Multiply calls, 1 service x 16 nodes, MaxConnections 3",
     "c2mesh": "calculator batch of 2^20 mixed Add/Multiply calls, 1 service x 16 nodes, mesh",
-    "c3": "registry lookup stress: 10k services x 64 nodes, batches of 2^20 routed calls (1% unregistered)",
+    "c3": "registry lookup stress: 10k services x 64 nodes, batches of 2^24 routed calls (1% unregistered)",
     "c4": "example/optimus splitWork stream replayed as batches of 2^20 Prime.Check calls",
 }
 
@@ -146,7 +149,7 @@ def run_reference(args, rank: int):
     threads, same config/metric.  Go itself cannot run here (no toolchain on this image)."""
     if rank != 0:
         return
-    spec, reqs = make_workload(args.workload, BATCH, 0x5EED0002)
+    spec, reqs = make_workload(args.workload, args.batch or BATCH_OF[args.workload], 0x5EED0002)
     from oracle import binding as ob
     kv, snap = ob.snapshot_from_spec(spec)
     threads = os.cpu_count() or 1
@@ -167,7 +170,7 @@ def run_reference(args, rank: int):
                    "note": "Go reference path not run - no Go toolchain on this image; C port of "
                            "cluster/rpc.go + registry.go + example method bodies, in-process"},
         "cpu_baseline": {"value": value, "unit": "calls/s", "cores": threads, "kind": "port",
-                         "sample": f"{args.steps} passes over one 2^20-call batch"},
+                         "sample": f"{args.steps} passes over one {len(reqs)}-call batch"},
         "e2e": {"value": value, "unit": "calls/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -181,7 +184,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=list(WORKLOAD_TEXT))
-    ap.add_argument("--buffers", type=int, default=8, help="distinct resident batches rotated (L2 honesty)")
+    ap.add_argument("--buffers", type=int, default=0, help="distinct resident batches rotated (0 = per workload)")
+    ap.add_argument("--batch", type=int, default=0, help="calls per step per GPU (0 = per workload)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = auto (about 1 s)")
     ap.add_argument("--cpu-seconds", type=float, default=8.0)
     ap.add_argument("--flags", type=int, default=0, help="extra dispatch flags (4 = probe table in L2)")
@@ -224,10 +228,11 @@ def main():
         ctx.publish(image)
 
     # ---- per-rank shard of the step's global stream, `buffers` distinct steps resident in HBM
-    nbuf = max(args.buffers, 1)
+    nbuf = args.buffers or BUFFERS_OF[args.workload]
+    batch = args.batch or BATCH_OF[args.workload]
     d_reqs, d_reps, counts, host_batches = [], [], [], []
     for b in range(nbuf):
-        _, stream = make_workload(args.workload, BATCH * world, 0x5EED0002 + b, image.salt)
+        _, stream = make_workload(args.workload, batch * world, 0x5EED0002 + b, image.salt)
         mine = stream[shard_indices(len(stream), world, rank)] if multi else stream
         host_batches.append(mine)
         counts.append(len(mine))
@@ -319,7 +324,7 @@ def main():
             rate, passes, el, _ = cpu_port_rate(spec, hb, threads, args.cpu_seconds)
             rate1, passes1, el1, _ = cpu_port_rate(spec, hb, 1, min(2.0, args.cpu_seconds))
             cpu_baseline = {"value": rate, "unit": "calls/s", "cores": threads, "kind": "port",
-                            "sample": f"{passes} passes over one 2^20-call batch of the same workload "
+                            "sample": f"{passes} passes over one {len(hb)}-call batch of the same workload "
                                       f"in {el:.1f} s, {threads} threads",
                             "single_thread_value": rate1,
                             "note": "Go reference path not run - no Go toolchain on this image"}

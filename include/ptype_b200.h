@@ -98,7 +98,9 @@ enum ptype_opcode {
  * the selection rule (localAddr, ConnConfig.MaxConnections; cluster/rpc.go:19-38,128). */
 
 #define PTYPE_IMAGE_MAGIC 0x49595450u /* "PTYI" */
-#define PTYPE_IMAGE_VERSION 1u
+#define PTYPE_IMAGE_VERSION 2u
+#define PTYPE_SLOT_WAYS 3        /* candidate slots per key (3-way cuckoo hashing) */
+#define PTYPE_MTABLE_SLOTS 64   /* perfect-hash method table size                  */
 #define PTYPE_SLOT_EMPTY 0xFFFFFFFFu
 #define PTYPE_MAX_RECEIVERS 8
 #define PTYPE_MAX_METHODS 32
@@ -111,7 +113,7 @@ typedef struct ptype_image_header { /* 192 bytes */
     uint64_t body_checksum;  /* FNV-1a-64 of blob[192 .. total_bytes)                  */
     uint64_t key_salt;       /* xor-ed into the FNV-1a-64 offset basis (0 = plain FNV) */
     uint32_t n_services;     /* occupied slots                                         */
-    uint32_t n_slots;        /* open-addressing table size (any value >= 1)            */
+    uint32_t n_slots;        /* cuckoo table size (any value >= 1, no power of two)    */
     uint32_t n_nodes;        /* global node array length                               */
     uint32_t max_connections;/* ConnConfig.MaxConnections; 0 = mesh (rpc.go:20-22)     */
     uint32_t n_conn_hash;    /* == max_connections                                     */
@@ -125,11 +127,16 @@ typedef struct ptype_image_header { /* 192 bytes */
     uint32_t off_strings;    /* string pool, NUL-terminated entries                    */
     uint32_t strings_bytes;
     uint32_t device_bytes;   /* prefix of the blob the kernels read (slots, hashes, methods) */
-    uint32_t reserved[7];
+    uint32_t table_seed;     /* xor-ed into the folded key before the three slot hashes */
+    uint32_t method_mul;     /* odd multiplier: mtable index = (method_hash * mul) >> 26 */
+    uint32_t off_mtable;     /* ptype_method[PTYPE_MTABLE_SLOTS], collision-free, opcode 0 = empty */
+    uint32_t reserved[4];
     char local_addr[PTYPE_LOCAL_ADDR_MAX]; /* the Client host's address string (cluster.go:69,82) */
 } ptype_image_header;
 
-/* One open-addressing slot, 16 bytes (one LDS.128 / LDG.128). */
+/* One table slot, 16 bytes (one LDS.128 / LDG.128).  A key lives in exactly one of its
+ * PTYPE_SLOT_WAYS candidate slots (ptype::slot_of in csrc/table_hash.h), so a lookup is
+ * at most three probes, hit or miss. */
 typedef struct ptype_slot {
     uint64_t key;       /* ptype_b200_service_key(name, key_salt)                      */
     uint32_t node_base; /* global id of the service's first node; PTYPE_SLOT_EMPTY = free */
@@ -269,7 +276,9 @@ int ptype_b200_broadcast_image(ptype_ctx*, const void* image, size_t bytes, int 
 /* ----------------------------------------------------------------- dispatch */
 #define PTYPE_F_DEVICE_PTRS 1u /* reqs/replies are device pointers on `dev`      */
 #define PTYPE_F_ASYNC 2u       /* return after enqueue; pair with ptype_b200_sync */
-#define PTYPE_F_GLOBAL_TABLE 4u/* debug/measurement: probe the table in L2, not shared memory */
+#define PTYPE_F_GLOBAL_TABLE 4u/* measurement switch: probe the table in L2, not shared memory  */
+#define PTYPE_F_LDG_LOADS 8u   /* measurement switch: fetch requests with LDG + shuffle transpose
+                                  instead of bulk-async staging                                */
 
 /* Optional per-batch outputs (all device-written; host copies made on sync). */
 typedef struct ptype_batch_stats {

@@ -28,7 +28,7 @@ ST_COUNT = 8
 NO_NODE = 0xFFFFFFFF
 RECV_ILL_FORMED = 0xFFFFFFFF
 
-F_DEVICE_PTRS, F_ASYNC, F_GLOBAL_TABLE = 1, 2, 4
+F_DEVICE_PTRS, F_ASYNC, F_GLOBAL_TABLE, F_LDG_LOADS = 1, 2, 4, 8
 
 E_OK, E_INVAL, E_NOMEM, E_CUDA, E_NO_IMAGE, E_BAD_IMAGE = 0, 1, 2, 3, 4, 5
 E_COLLISION, E_NCCL, E_LIMIT, E_NOT_FOUND, E_BUSY = 6, 7, 8, 9, 10
@@ -48,7 +48,8 @@ class ImageHeader(C.Structure):
         ("n_receivers", C.c_uint32), ("off_slots", C.c_uint32), ("off_conn_hash", C.c_uint32),
         ("off_methods", C.c_uint32), ("off_nodes", C.c_uint32), ("off_services", C.c_uint32),
         ("off_strings", C.c_uint32), ("strings_bytes", C.c_uint32), ("device_bytes", C.c_uint32),
-        ("reserved", C.c_uint32 * 7), ("local_addr", C.c_char * 64),
+        ("table_seed", C.c_uint32), ("method_mul", C.c_uint32), ("off_mtable", C.c_uint32),
+        ("reserved", C.c_uint32 * 4), ("local_addr", C.c_char * 64),
     ]
 
 

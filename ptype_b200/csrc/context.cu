@@ -86,6 +86,14 @@ int nccl_fail(int r, const char* what) {
     return PTYPE_E_NCCL;
 }
 
+// Launch-plan variants selectable through the dispatch flags (measurement switches).
+constexpr int kPlanKinds = 4;
+constexpr uint32_t kPlanFlags[kPlanKinds] = {0u, PTYPE_F_GLOBAL_TABLE, PTYPE_F_LDG_LOADS,
+                                             PTYPE_F_GLOBAL_TABLE | PTYPE_F_LDG_LOADS};
+inline int plan_kind(uint32_t flags) {
+    return ((flags & PTYPE_F_GLOBAL_TABLE) ? 1 : 0) | ((flags & PTYPE_F_LDG_LOADS) ? 2 : 0);
+}
+
 struct Stage {
     ptype_req* d_reqs = nullptr;
     ptype_reply* d_replies = nullptr;
@@ -103,7 +111,7 @@ struct DeviceState {
     void* image_buf[2] = {nullptr, nullptr};
     size_t image_cap[2] = {0, 0};
     ptype::DeviceImage view[2];
-    ptype::LaunchPlan plan[2][2][2];  // [buffer][global_table][extras]
+    ptype::LaunchPlan plan[2][kPlanKinds][2];  // [buffer][variant][extras]
     uint64_t epoch[2] = {0, 0};
     int active = -1;
     unsigned long long* d_stats = nullptr;
@@ -169,26 +177,21 @@ int adopt_image(ptype_ctx* ctx, DeviceState* d, int buf, const ptype_image_heade
     v.slots = reinterpret_cast<const ptype_slot*>(base + h.off_slots);
     v.conn_hash = reinterpret_cast<const uint32_t*>(base + h.off_conn_hash);
     v.methods = reinterpret_cast<const ptype_method*>(base + h.off_methods);
+    v.mtable = reinterpret_cast<const ptype_method*>(base + h.off_mtable);
+    v.table_seed = h.table_seed;
+    v.method_mul = h.method_mul;
     v.n_slots = h.n_slots;
     v.max_conn = h.max_connections;
     v.n_methods = h.n_methods;
     v.pad = 0;
+    v.m_magic = h.max_connections ? ~0ull / h.max_connections + 1ull : 0ull;
     v.check_limit = ctx->check_limit.load();
-    for (int g = 0; g < 2; ++g)
+    for (int g = 0; g < kPlanKinds; ++g)
         for (int x = 0; x < 2; ++x)
-            CU(ptype::plan_dispatch(v, g ? PTYPE_F_GLOBAL_TABLE : 0u, x != 0, &d->plan[buf][g][x]));
+            CU(ptype::plan_dispatch(v, kPlanFlags[g], x != 0, &d->plan[buf][g][x]));
     d->epoch[buf] = h.epoch;
     d->active = buf;
     return PTYPE_OK;
-}
-
-bool is_device_pointer(const void* p) {
-    cudaPointerAttributes a;
-    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
-        cudaGetLastError();
-        return false;
-    }
-    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
 int ensure_extras(DeviceState* d, size_t failed_cap) {
@@ -512,7 +515,7 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
     const int buf = d->active;
     const ptype::DeviceImage img = d->view[buf];
     const bool extras = stats != nullptr;
-    const ptype::LaunchPlan& plan = d->plan[buf][(flags & PTYPE_F_GLOBAL_TABLE) ? 1 : 0][extras ? 1 : 0];
+    const ptype::LaunchPlan& plan = d->plan[buf][plan_kind(flags)][extras ? 1 : 0];
 
     if (flags & PTYPE_F_DEVICE_PTRS) {
         // Batch resident in HBM: one kernel launch, nothing else.

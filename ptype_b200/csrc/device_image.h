@@ -11,11 +11,15 @@ namespace ptype {
 struct DeviceImage {
     const ptype_slot* slots;     // n_slots entries, 16-byte aligned
     const uint32_t* conn_hash;   // max_conn entries: FNV-1a-32(localAddr+itoa(i))
-    const ptype_method* methods; // n_methods entries
+    const ptype_method* methods; // n_methods entries (error paths)
+    const ptype_method* mtable;  // PTYPE_MTABLE_SLOTS entries, perfect hash
     uint32_t n_slots;
     uint32_t max_conn;           // ConnConfig.MaxConnections, 0 = mesh
     uint32_t n_methods;
+    uint32_t table_seed;         // cuckoo hash seed
+    uint32_t method_mul;         // perfect-hash multiplier
     uint32_t pad;
+    uint64_t m_magic;            // 2^64 / max_conn + 1: multiply-shift modulo by max_conn
     uint64_t check_limit;        // Prime.Check trip-count limit
 };
 
@@ -25,8 +29,10 @@ enum : int { kStatCalls = 0, kStatByStatus = 1, kStatFailed = 1 + PTYPE_ST__COUN
 struct LaunchPlan {
     int threads = 0;        // per CTA
     int ctas_per_sm = 0;    // resident CTAs per SM (occupancy query)
-    size_t dyn_smem = 0;    // bytes of staged slot table (0 = probe in L2)
+    size_t dyn_smem = 0;    // dynamic shared memory per CTA: staged table + request stages
+    size_t table_smem = 0;  // bytes of it holding the slot table (0 = probe in L2)
     bool smem_table = false;
+    bool bulk = false;      // requests staged by bulk-async copies (else LDG + shuffle)
 };
 
 // Number of partial sums the checksum kernel writes to its scratch buffer.

@@ -22,6 +22,7 @@
 #include <stdint.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/ptype_b200.h"
@@ -80,6 +81,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
 }
 
+// Orders this thread's earlier generic-proxy shared-memory accesses before later
+// async-proxy (bulk copy) accesses to the same locations.
+__device__ __forceinline__ void fence_proxy_async() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
 // Bulk asynchronous copy global -> shared (the TMA engine, 1-D form; SASS UBLKCP).
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes,
                                          uint64_t* bar) {
@@ -91,12 +98,6 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
 }
 
 // ------------------------------------------------------------ arithmetic
-
-// int(seq) % k for 0 <= int(seq); 32-bit divide when the sequence number is small.
-__device__ __forceinline__ uint32_t mod_u64_u32(uint64_t a, uint32_t k) {
-    if ((a >> 32) == 0) return static_cast<uint32_t>(a) % k;
-    return static_cast<uint32_t>(a % k);
-}
 
 __device__ __forceinline__ uint64_t abs_u64(int64_t v) {
     return v < 0 ? 0ull - static_cast<uint64_t>(v) : static_cast<uint64_t>(v);
@@ -134,113 +135,332 @@ __device__ __forceinline__ int64_t prime_check(int64_t lo, int64_t hi, int64_t t
     return target;
 }
 
-struct Tables {
-    const ptype_slot* slots;     // shared or global
-    const uint32_t* conn;        // shared or global
-    const ptype_method* methods; // shared
+// Shared-memory state every dispatch CTA keeps next to its staged slot table.
+struct CtaShared {
+    ptype_method mtable[PTYPE_MTABLE_SLOTS];  // perfect-hash method table
+    ptype_method methods[PTYPE_MAX_METHODS];  // linear list, error paths only
+    uint32_t conn[kSmemConn];
+    unsigned int status[PTYPE_ST__COUNT];
+    uint64_t table_bar;
 };
+
+// The last service this lane looked up.  A batch issued by one Client names one
+// service (cluster/cluster.go:101-103), so after the first tile the probe is skipped.
+struct LookupCache {
+    uint32_t key_lo = 0, key_hi = 0;
+    uint32_t node_base = PTYPE_SLOT_EMPTY, n_and_recv = 0;
+    bool valid = false;
+};
+
+// Unsigned remainder by a run-time divisor.  Kept out of line so that the common
+// power-of-two case costs one AND and a not-taken branch instead of the ~25 predicated
+// instructions of the inlined divide.
+__device__ __noinline__ uint32_t umod_slow(uint32_t a, uint32_t d) { return a % d; }
+__device__ __forceinline__ uint32_t umod(uint32_t a, uint32_t d) {
+    if ((d & (d - 1u)) == 0u) return a & (d - 1u);
+    return umod_slow(a, d);
+}
+
+// Round-robin index for sequence numbers that do not fit 32 bits, including the range
+// where Go's int(index) is negative (cluster/rpc.go:182).
+__device__ __noinline__ uint32_t route_wide(uint64_t seq, uint32_t k, uint32_t* status) {
+    if (static_cast<int64_t>(seq) >= 0) return static_cast<uint32_t>(seq % k);
+    // Go's % keeps the dividend's sign: any non-zero remainder indexes clients[] below 0
+    if (static_cast<int64_t>(seq) % static_cast<int64_t>(k) != 0) *status = PTYPE_ST_BAD_INDEX;
+    return 0;
+}
+
+// Everything but the fast resolve: which net/rpc error a request gets, or the opcode of
+// a method the perfect-hash entry did not confirm (cannot happen for registered methods).
+__device__ __noinline__ uint32_t resolve_slow(const CtaShared& sh, uint32_t n_methods,
+                                              uint32_t method, uint32_t recv, uint32_t recv_mask,
+                                              uint32_t* status) {
+    if (recv == PTYPE_RECV_ILL_FORMED) {
+        *status = PTYPE_ST_ILL_FORMED;
+        return PTYPE_OP_NONE;
+    }
+    bool recv_known = false;
+    for (uint32_t e = 0; e < n_methods; ++e) {
+        const ptype_method md = sh.methods[e];
+        if (md.recv_hash == recv && ((recv_mask >> md.recv_bit) & 1u)) {
+            recv_known = true;
+            if (md.method_hash == method) return md.opcode;
+        }
+    }
+    *status = recv_known ? PTYPE_ST_CANT_FIND_METHOD : PTYPE_ST_CANT_FIND_SERVICE;
+    return PTYPE_OP_NONE;
+}
+
+// Exact-key lookup: the key sits in one of three candidate slots or nowhere.
+template <bool kSmemTable>
+__device__ __forceinline__ void lookup(const DeviceImage& img, const ptype_slot* slots, uint32_t key_lo,
+                                       uint32_t key_hi, uint32_t& node_base, uint32_t& n_and_recv) {
+    node_base = PTYPE_SLOT_EMPTY;
+    n_and_recv = 0;
+    if (kSmemTable) {
+        // shared memory: issue all three probes at once, no divergence
+        uint4 s[PTYPE_SLOT_WAYS];
+#pragma unroll
+        for (int w = 0; w < PTYPE_SLOT_WAYS; ++w)
+            s[w] = *reinterpret_cast<const uint4*>(slots + slot_of(key_lo, key_hi, img.table_seed, w, img.n_slots));
+#pragma unroll
+        for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
+            if (s[w].x == key_lo && s[w].y == key_hi && s[w].z != PTYPE_SLOT_EMPTY) {
+                node_base = s[w].z;
+                n_and_recv = s[w].w;
+            }
+        }
+    } else {
+        // L2: stop at the first hit so that most calls cost one sector
+#pragma unroll
+        for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
+            const uint4 s = __ldg(reinterpret_cast<const uint4*>(
+                slots + slot_of(key_lo, key_hi, img.table_seed, w, img.n_slots)));
+            if (s.x == key_lo && s.y == key_hi && s.z != PTYPE_SLOT_EMPTY) {
+                node_base = s.z;
+                n_and_recv = s.w;
+                break;
+            }
+        }
+    }
+}
 
 // One call: lookup -> route -> resolve -> execute.  q0 = {svc_key, seq},
 // q1 = {method, recv, a0}, q2 = {a1, a2}.
 template <bool kSmemTable>
-__device__ __forceinline__ uint4 dispatch_one(const DeviceImage& img, const Tables& tb, uint4 q0,
+__device__ __forceinline__ uint4 dispatch_one(const DeviceImage& img, const CtaShared& sh,
+                                              const ptype_slot* slots, LookupCache& cache, uint4 q0,
                                               uint4 q1, uint4 q2) {
-    const uint64_t key = static_cast<uint64_t>(q0.x) | (static_cast<uint64_t>(q0.y) << 32);
-    const uint64_t seq = static_cast<uint64_t>(q0.z) | (static_cast<uint64_t>(q0.w) << 32);
-
-    // ---- lookup: linear probing, exact 64-bit key compare
-    uint32_t at = home_slot(key, img.n_slots);
-    uint32_t node_base = PTYPE_SLOT_EMPTY, n_and_recv = 0;
-    for (uint32_t probe = 0; probe < img.n_slots; ++probe) {
-        uint4 s;
-        if (kSmemTable) {
-            s = *reinterpret_cast<const uint4*>(tb.slots + at);
-        } else {
-            s = __ldg(reinterpret_cast<const uint4*>(tb.slots + at));
-        }
-        if (s.z == PTYPE_SLOT_EMPTY) break;
-        if (s.x == q0.x && s.y == q0.y) {
-            node_base = s.z;
-            n_and_recv = s.w;
-            break;
-        }
-        at = at + 1 == img.n_slots ? 0 : at + 1;
+    if (!(cache.valid && cache.key_lo == q0.x && cache.key_hi == q0.y)) {
+        lookup<kSmemTable>(img, slots, q0.x, q0.y, cache.node_base, cache.n_and_recv);
+        cache.key_lo = q0.x;
+        cache.key_hi = q0.y;
+        cache.valid = true;
     }
+    const uint32_t node_base = cache.node_base, n_and_recv = cache.n_and_recv;
+    const uint32_t n = n_and_recv & 0xFFFFFFu;
 
     uint32_t status = PTYPE_ST_OK;
     uint32_t node = PTYPE_NO_NODE;
-    int64_t value = 0;
-    const uint32_t n = n_and_recv & 0xFFFFFFu;
+    uint64_t value = 0;
     if (node_base == PTYPE_SLOT_EMPTY) {
         status = PTYPE_ST_NO_SERVICE;  // watch delivered no nodes -> ErrNoClientAvailable
     } else if (n == 0) {
         status = PTYPE_ST_NO_CLIENT;  // rpc.go:178-180
     } else {
-        // ---- route
+        // ---- route (rpc.go:176-183,252-270)
         const uint32_t m = img.max_conn;
         const bool identity = m == 0 || n <= m;  // rpc.go:253-255
-        const uint32_t k = identity ? n : m;
         uint32_t r;
-        if (static_cast<int64_t>(seq) >= 0) {
-            r = mod_u64_u32(seq, k);
+        if (q0.w == 0) {  // seq < 2^32
+            // k == m is one constant per image: multiply-shift with the host's magic number
+            // (Lemire fastmod); k == n differs per service and takes the divide.
+            r = identity ? umod(q0.z, n) : static_cast<uint32_t>(__umul64hi(img.m_magic * q0.z, m));
         } else {
-            // int(index) is negative: Go's % keeps the sign, so anything but 0 indexes
-            // clients[] out of range and panics (rpc.go:182)
-            r = 0;
-            if (static_cast<int64_t>(seq) % static_cast<int64_t>(k) != 0) status = PTYPE_ST_BAD_INDEX;
+            r = route_wide(static_cast<uint64_t>(q0.z) | (static_cast<uint64_t>(q0.w) << 32),
+                           identity ? n : m, &status);
         }
         if (status == PTYPE_ST_OK) {
-            const uint32_t local = identity ? r : tb.conn[r] % n;  // rpc.go:258-261,266-270
-            node = node_base + local;
-            // ---- resolve [net/rpc server.readRequestHeader]
-            const uint32_t recv_mask = n_and_recv >> 24;
-            uint32_t opcode = PTYPE_OP_NONE;
-            bool recv_known = false;
-            if (q1.y == PTYPE_RECV_ILL_FORMED) {
-                status = PTYPE_ST_ILL_FORMED;
-            } else {
-                for (uint32_t e = 0; e < img.n_methods; ++e) {
-                    const uint4 md = *reinterpret_cast<const uint4*>(tb.methods + e);
-                    if (md.y == q1.y && ((recv_mask >> md.w) & 1u)) {
-                        recv_known = true;
-                        if (md.x == q1.x) {
-                            opcode = md.z;
-                            break;
-                        }
-                    }
-                }
-                if (opcode == PTYPE_OP_NONE)
-                    status = recv_known ? PTYPE_ST_CANT_FIND_METHOD : PTYPE_ST_CANT_FIND_SERVICE;
+            uint32_t local = r;
+            if (!identity) {
+                const uint32_t h = img.max_conn <= kSmemConn ? sh.conn[r] : __ldg(img.conn_hash + r);
+                local = umod(h, n);  // rpc.go:258-261,266-270
             }
+            node = node_base + local;
+            // ---- resolve [net/rpc server.readRequestHeader]: one perfect-hash probe
+            const uint32_t recv_mask = n_and_recv >> 24;
+            const uint4 md = *reinterpret_cast<const uint4*>(&sh.mtable[mtable_index(q1.x, img.method_mul)]);
+            uint32_t opcode = md.z;
+            if (!(md.x == q1.x && md.y == q1.y && opcode != PTYPE_OP_NONE && ((recv_mask >> md.w) & 1u)))
+                opcode = resolve_slow(sh, img.n_methods, q1.x, q1.y, recv_mask, &status);
             // ---- execute
             if (status == PTYPE_ST_OK) {
                 const uint64_t a0 = static_cast<uint64_t>(q1.z) | (static_cast<uint64_t>(q1.w) << 32);
                 const uint64_t a1 = static_cast<uint64_t>(q2.x) | (static_cast<uint64_t>(q2.y) << 32);
-                if (opcode == PTYPE_OP_MULTIPLY) {
-                    value = static_cast<int64_t>(a0 * a1);  // Go int wraps (calculator.go:10)
-                } else if (opcode == PTYPE_OP_ADD) {
-                    value = static_cast<int64_t>(a0 + a1);
-                } else {
+                if (opcode == PTYPE_OP_CHECK) {
                     const uint64_t a2 =
                         static_cast<uint64_t>(q2.z) | (static_cast<uint64_t>(q2.w) << 32);
-                    value = prime_check(static_cast<int64_t>(a0), static_cast<int64_t>(a1),
-                                        static_cast<int64_t>(a2), img.check_limit, &status);
+                    value = static_cast<uint64_t>(prime_check(static_cast<int64_t>(a0),
+                                                              static_cast<int64_t>(a1),
+                                                              static_cast<int64_t>(a2), img.check_limit,
+                                                              &status));
+                } else {
+                    // Go int wraps (calculator.go:10); both results computed, one selected:
+                    // a mixed Add/Multiply warp does not diverge
+                    const uint64_t prod = a0 * a1, sum = a0 + a1;
+                    value = opcode == PTYPE_OP_MULTIPLY ? prod : sum;
                 }
             }
         }
     }
     uint4 out;
-    out.x = static_cast<uint32_t>(static_cast<uint64_t>(value));
-    out.y = static_cast<uint32_t>(static_cast<uint64_t>(value) >> 32);
+    out.x = static_cast<uint32_t>(value);
+    out.y = static_cast<uint32_t>(value >> 32);
     out.z = node;
     out.w = status;
     return out;
 }
 
-// ------------------------------------------------------------------ kernel
+// Stage method tables / connection hashes with plain loads and start the bulk copy of the
+// slot table.  Ends with the table copy in flight (wait on sh.table_bar, parity 0).
+template <bool kSmemTable>
+__device__ __forceinline__ const ptype_slot* stage_tables(const DeviceImage& img, CtaShared& sh,
+                                                          unsigned char* table_smem) {
+    if (kSmemTable && threadIdx.x == 0) mbar_init(&sh.table_bar, 1);
+    for (uint32_t i = threadIdx.x; i < PTYPE_MTABLE_SLOTS; i += blockDim.x) sh.mtable[i] = img.mtable[i];
+    for (uint32_t i = threadIdx.x; i < img.n_methods; i += blockDim.x) sh.methods[i] = img.methods[i];
+    if (img.max_conn <= kSmemConn)
+        for (uint32_t i = threadIdx.x; i < img.max_conn; i += blockDim.x) sh.conn[i] = img.conn_hash[i];
+    if (threadIdx.x < PTYPE_ST__COUNT) sh.status[threadIdx.x] = 0;
+    __syncthreads();
+    if (kSmemTable && threadIdx.x == 0) {
+        const uint32_t bytes = img.n_slots * static_cast<uint32_t>(sizeof(ptype_slot));
+        mbar_expect_tx(&sh.table_bar, bytes);
+        constexpr uint32_t kChunk = 32768;
+        for (uint32_t off = 0; off < bytes; off += kChunk) {
+            const uint32_t len = bytes - off < kChunk ? bytes - off : kChunk;
+            bulk_g2s(table_smem + off, reinterpret_cast<const unsigned char*>(img.slots) + off, len,
+                     &sh.table_bar);
+        }
+    }
+    return kSmemTable ? reinterpret_cast<const ptype_slot*>(table_smem) : img.slots;
+}
+
+// dispatch_ex outputs for one tile: ballot/popc compaction of the failed calls (one
+// global atomic per warp) and per-status counters.
+__device__ __forceinline__ void tile_extras(CtaShared& sh, uint32_t lane, bool live, uint32_t status,
+                                            size_t idx, uint32_t idx_base, uint32_t* failed_idx,
+                                            uint32_t failed_cap, unsigned long long* stats,
+                                            unsigned int& ok_calls) {
+    const bool failed = live && status != PTYPE_ST_OK;
+    const uint32_t live_mask = __ballot_sync(kFull, live);
+    const uint32_t fail_mask = __ballot_sync(kFull, failed);
+    if (lane == 0) ok_calls += __popc(live_mask & ~fail_mask);
+    if (fail_mask) {
+        unsigned long long base = 0;
+        const int leader = __ffs(fail_mask) - 1;
+        if (static_cast<int>(lane) == leader)
+            base = atomicAdd(stats + kStatFailed, static_cast<unsigned long long>(__popc(fail_mask)));
+        base = __shfl_sync(kFull, base, leader);
+        if (failed) {
+            atomicAdd(&sh.status[status], 1u);
+            const unsigned long long slot = base + __popc(fail_mask & ((1u << lane) - 1u));
+            if (failed_idx != nullptr && slot < failed_cap)
+                failed_idx[slot] = idx_base + static_cast<uint32_t>(idx);
+        }
+    }
+}
+
+__device__ __forceinline__ void flush_extras(CtaShared& sh, uint32_t lane, unsigned int ok_calls,
+                                             unsigned long long* stats) {
+    if (lane == 0 && ok_calls) atomicAdd(&sh.status[PTYPE_ST_OK], ok_calls);
+    __syncthreads();
+    if (threadIdx.x < PTYPE_ST__COUNT && sh.status[threadIdx.x]) {
+        atomicAdd(stats + kStatByStatus + threadIdx.x,
+                  static_cast<unsigned long long>(sh.status[threadIdx.x]));
+        atomicAdd(stats + kStatCalls, static_cast<unsigned long long>(sh.status[threadIdx.x]));
+    }
+}
+
+// Programmatic dependent launch: let the next dispatch on the stream start filling SMs
+// while this one drains (batches are independent), and do not finish before the
+// previous one has, so stream order still means completion order.
+__device__ __forceinline__ void griddep_launch_dependents() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// ------------------------------------------------------- kernel, bulk-staged
 //
-// Persistent grid: every CTA stages the table once, then its warps walk the
-// batch in 32-call tiles, kUnroll tiles in flight per warp.
+// Requests reach shared memory through the bulk-async copy engine: each warp owns a
+// ring of kStages 1536-byte stages (32 records); lane 0 arms the stage's mbarrier and
+// issues one cp.async.bulk per tile, every lane then reads its own 48-byte record with
+// three conflict-free LDS.128 (lanes 0-7 of a quarter-warp land on 8 distinct 16-byte
+// bank groups because 48/16 = 3 is odd).  No load instruction per call is spent on
+// global memory and nothing is transposed through registers.
+constexpr int kTileBytes = 32 * 48;
+constexpr int kBulkThreads = 256;
+
+template <bool kSmemTable, bool kExtras, int kStages>
+__global__ void __launch_bounds__(kBulkThreads, 6)
+    dispatch_bulk_kernel(const DeviceImage img, const uint4* __restrict__ reqs, const size_t n,
+                         uint4* __restrict__ replies, uint32_t* __restrict__ failed_idx,
+                         const uint32_t failed_cap, const uint32_t idx_base,
+                         unsigned long long* __restrict__ stats, const uint32_t table_smem_bytes) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ __align__(16) CtaShared sh;
+    __shared__ __align__(8) uint64_t s_full[(kBulkThreads / 32) * kStages];
+
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+    unsigned char* const my_stage = dyn_smem + table_smem_bytes + warp * (kStages * kTileBytes);
+    uint64_t* const my_bar = s_full + warp * kStages;
+
+    const size_t n_tiles = (n + 31) >> 5;
+    const size_t total_warps = static_cast<size_t>(gridDim.x) * warps_per_cta;
+    const size_t warp_global = static_cast<size_t>(blockIdx.x) * warps_per_cta + warp;
+    const uint32_t my_tiles =
+        warp_global < n_tiles
+            ? static_cast<uint32_t>((n_tiles - warp_global + total_warps - 1) / total_warps)
+            : 0u;
+
+    auto issue = [&](uint32_t i, uint32_t s) {  // lane 0 only
+        const size_t first = (warp_global + static_cast<size_t>(i) * total_warps) << 5;
+        const size_t left = n - first;
+        const uint32_t bytes = static_cast<uint32_t>(left < 32 ? left : 32) * 48u;
+        mbar_expect_tx(&my_bar[s], bytes);
+        bulk_g2s(my_stage + s * kTileBytes, reqs + first * 3, bytes, &my_bar[s]);
+    };
+
+    // ---- request ring first (its latency is the longest), then the tables
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) mbar_init(&my_bar[s], 1);
+#pragma unroll
+        for (int s = 0; s < kStages; ++s)
+            if (static_cast<uint32_t>(s) < my_tiles) issue(s, s);
+    }
+    const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);  // has a __syncthreads
+    griddep_launch_dependents();
+
+    LookupCache cache;
+    unsigned int ok_calls = 0;
+    if (kSmemTable && my_tiles) mbar_wait(&sh.table_bar, 0);
+
+    size_t idx = (warp_global << 5) + lane;          // this lane's call in tile i
+    const size_t idx_step = total_warps << 5;
+    for (uint32_t i = 0; i < my_tiles; ++i, idx += idx_step) {
+        const uint32_t s = i % kStages;
+        mbar_wait(&my_bar[s], (i / kStages) & 1u);
+        const uint4* rec = reinterpret_cast<const uint4*>(my_stage + s * kTileBytes + lane * 48u);
+        const uint4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
+        // The refill below is written by the async proxy; these reads went through the
+        // generic proxy.  Without the proxy fence the two are unordered even across
+        // __syncwarp, and a refill can land under a lane that has not read yet (seen on
+        // B200 as records from tile i+2 answering tile i).
+        fence_proxy_async();
+        __syncwarp();  // every lane has its record: the stage may be refilled
+        if (lane == 0 && i + kStages < my_tiles) issue(i + kStages, s);
+        const bool live = idx < n;
+        uint4 out = make_uint4(0, 0, 0, 0);
+        if (live) {
+            out = dispatch_one<kSmemTable>(img, sh, slots, cache, q0, q1, q2);
+            st_stream(replies + idx, out);
+        }
+        if (kExtras)
+            tile_extras(sh, lane, live, out.w, idx, idx_base, failed_idx, failed_cap, stats, ok_calls);
+    }
+    if (kSmemTable && !my_tiles) mbar_wait(&sh.table_bar, 0);  // leave no bulk copy in flight
+    if (kExtras) flush_extras(sh, lane, ok_calls, stats);
+    griddep_wait();
+}
+
+// ------------------------------------------------------ kernel, LDG-staged
+//
+// Used when the slot table needs (nearly) all of shared memory, so no room is left for
+// request stages: each lane issues three coalesced 128-bit loads covering the warp's
+// contiguous 1536 bytes, then a 12-shuffle transpose hands every lane its own record.
 template <bool kSmemTable, bool kExtras, int kUnroll>
 __global__ void __launch_bounds__(kMaxThreads, 1)
     dispatch_kernel(const DeviceImage img, const uint4* __restrict__ reqs, const size_t n,
@@ -248,40 +468,14 @@ __global__ void __launch_bounds__(kMaxThreads, 1)
                     const uint32_t failed_cap, const uint32_t idx_base,
                     unsigned long long* __restrict__ stats) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
-    __shared__ __align__(16) ptype_method s_methods[PTYPE_MAX_METHODS];
-    __shared__ uint32_t s_conn[kSmemConn];
-    __shared__ __align__(8) uint64_t s_bar;
-    __shared__ unsigned int s_status[PTYPE_ST__COUNT];
+    __shared__ __align__(16) CtaShared sh;
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t warps_per_cta = blockDim.x >> 5;
 
-    // ---- stage the registry tables
-    if (kSmemTable) {
-        if (threadIdx.x == 0) mbar_init(&s_bar, 1);
-    }
-    for (uint32_t i = threadIdx.x; i < img.n_methods; i += blockDim.x) s_methods[i] = img.methods[i];
-    const bool conn_in_smem = img.max_conn <= kSmemConn;
-    if (conn_in_smem)
-        for (uint32_t i = threadIdx.x; i < img.max_conn; i += blockDim.x) s_conn[i] = img.conn_hash[i];
-    if (kExtras && threadIdx.x < PTYPE_ST__COUNT) s_status[threadIdx.x] = 0;
-    __syncthreads();
-    if (kSmemTable && threadIdx.x == 0) {
-        const uint32_t bytes = img.n_slots * static_cast<uint32_t>(sizeof(ptype_slot));
-        mbar_expect_tx(&s_bar, bytes);
-        constexpr uint32_t kChunk = 32768;
-        for (uint32_t off = 0; off < bytes; off += kChunk) {
-            const uint32_t len = bytes - off < kChunk ? bytes - off : kChunk;
-            bulk_g2s(dyn_smem + off, reinterpret_cast<const unsigned char*>(img.slots) + off, len,
-                     &s_bar);
-        }
-    }
-
-    Tables tb;
-    tb.slots = kSmemTable ? reinterpret_cast<const ptype_slot*>(dyn_smem) : img.slots;
-    tb.conn = conn_in_smem ? s_conn : img.conn_hash;
-    tb.methods = s_methods;
+    const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
+    griddep_launch_dependents();
 
     // ---- transpose plan.  Lane L loads 16-byte chunks L, 32+L, 64+L of the warp's 96;
     // record r owns chunks 3r..3r+2.  In round c, lane s feeds the lane whose record
@@ -299,6 +493,7 @@ __global__ void __launch_bounds__(kMaxThreads, 1)
     const size_t total_warps = static_cast<size_t>(gridDim.x) * warps_per_cta;
     const size_t warp_global = static_cast<size_t>(blockIdx.x) * warps_per_cta + warp;
 
+    LookupCache cache;
     unsigned int ok_calls = 0;  // lane 0 only (kExtras)
     bool table_ready = !kSmemTable;
 
@@ -314,7 +509,7 @@ __global__ void __launch_bounds__(kMaxThreads, 1)
             }
         }
         if (!table_ready) {  // first tile's loads are already in flight
-            mbar_wait(&s_bar, 0);
+            mbar_wait(&sh.table_bar, 0);
             table_ready = true;
         }
 #pragma unroll
@@ -336,43 +531,16 @@ __global__ void __launch_bounds__(kMaxThreads, 1)
             const bool live = idx < n;
             uint4 out = make_uint4(0, 0, 0, 0);
             if (live) {
-                out = dispatch_one<kSmemTable>(img, tb, q[0], q[1], q[2]);
+                out = dispatch_one<kSmemTable>(img, sh, slots, cache, q[0], q[1], q[2]);
                 st_stream(replies + idx, out);
             }
-            if (kExtras) {
-                // compaction of failed calls: one atomic per warp, ballot-ranked slots
-                const bool failed = live && out.w != PTYPE_ST_OK;
-                const uint32_t live_mask = __ballot_sync(kFull, live);
-                const uint32_t fail_mask = __ballot_sync(kFull, failed);
-                if (lane == 0) ok_calls += __popc(live_mask & ~fail_mask);
-                if (fail_mask) {
-                    unsigned long long base = 0;
-                    const int leader = __ffs(fail_mask) - 1;
-                    if (static_cast<int>(lane) == leader)
-                        base = atomicAdd(stats + kStatFailed,
-                                         static_cast<unsigned long long>(__popc(fail_mask)));
-                    base = __shfl_sync(kFull, base, leader);
-                    if (failed) {
-                        atomicAdd(&s_status[out.w], 1u);
-                        const unsigned long long slot = base + __popc(fail_mask & ((1u << lane) - 1u));
-                        if (failed_idx != nullptr && slot < failed_cap)
-                            failed_idx[slot] = idx_base + static_cast<uint32_t>(idx);
-                    }
-                }
-            }
+            if (kExtras)
+                tile_extras(sh, lane, live, out.w, idx, idx_base, failed_idx, failed_cap, stats, ok_calls);
         }
     }
-    if (!table_ready) mbar_wait(&s_bar, 0);  // never leave a bulk copy in flight behind us
-
-    if (kExtras) {
-        if (lane == 0 && ok_calls) atomicAdd(&s_status[PTYPE_ST_OK], ok_calls);
-        __syncthreads();
-        if (threadIdx.x < PTYPE_ST__COUNT && s_status[threadIdx.x]) {
-            atomicAdd(stats + kStatByStatus + threadIdx.x,
-                      static_cast<unsigned long long>(s_status[threadIdx.x]));
-            atomicAdd(stats + kStatCalls, static_cast<unsigned long long>(s_status[threadIdx.x]));
-        }
-    }
+    if (!table_ready) mbar_wait(&sh.table_bar, 0);  // never leave a bulk copy in flight behind us
+    if (kExtras) flush_extras(sh, lane, ok_calls, stats);
+    griddep_wait();
 }
 
 // ---------------------------------------------------------- reply checksum
@@ -417,22 +585,52 @@ __global__ void __launch_bounds__(kChecksumThreads)
 }
 
 constexpr int kUnrollDefault = 2;
+constexpr int kStagesDefault = 2;
+constexpr size_t kBulkStageBytes = (kBulkThreads / 32) * kStagesDefault * kTileBytes;  // per CTA
+
+bool pdl_enabled() {
+    static const bool on = [] {
+        const char* v = std::getenv("PTYPE_B200_PDL");
+        return !(v && v[0] == '0');
+    }();
+    return on;
+}
+
+// One launch, optionally with programmatic stream serialization so that consecutive
+// dispatches on a stream overlap their ramp-up and drain.
+template <typename Kernel, typename... Args>
+cudaError_t launch_kernel(Kernel kernel, int blocks, int threads, size_t smem, cudaStream_t stream,
+                          Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned>(blocks));
+    cfg.blockDim = dim3(static_cast<unsigned>(threads));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
 
 template <bool kSmemTable, bool kExtras>
 cudaError_t launch_variant(const DeviceImage& img, const LaunchPlan& plan, int blocks,
                            const ptype_req* reqs, size_t n, ptype_reply* replies, uint32_t* failed_idx,
                            uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
                            cudaStream_t stream) {
-    auto kernel = dispatch_kernel<kSmemTable, kExtras, kUnrollDefault>;
-    kernel<<<blocks, plan.threads, plan.dyn_smem, stream>>>(
-        img, reinterpret_cast<const uint4*>(reqs), n, reinterpret_cast<uint4*>(replies), failed_idx,
-        failed_cap, idx_base, stats);
-    return cudaGetLastError();
+    const uint4* q = reinterpret_cast<const uint4*>(reqs);
+    uint4* r = reinterpret_cast<uint4*>(replies);
+    if (plan.bulk)
+        return launch_kernel(dispatch_bulk_kernel<kSmemTable, kExtras, kStagesDefault>, blocks,
+                             plan.threads, plan.dyn_smem, stream, img, q, n, r, failed_idx, failed_cap,
+                             idx_base, stats, static_cast<uint32_t>(plan.table_smem));
+    return launch_kernel(dispatch_kernel<kSmemTable, kExtras, kUnrollDefault>, blocks, plan.threads,
+                         plan.dyn_smem, stream, img, q, n, r, failed_idx, failed_cap, idx_base, stats);
 }
 
-template <bool kSmemTable, bool kExtras>
-cudaError_t occupancy_variant(int threads, size_t dyn_smem, int* ctas_per_sm) {
-    auto kernel = dispatch_kernel<kSmemTable, kExtras, kUnrollDefault>;
+template <typename Kernel>
+cudaError_t occupancy_of(Kernel kernel, int threads, size_t dyn_smem, int* ctas_per_sm) {
     if (dyn_smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              static_cast<int>(dyn_smem));
@@ -441,25 +639,45 @@ cudaError_t occupancy_variant(int threads, size_t dyn_smem, int* ctas_per_sm) {
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, kernel, threads, dyn_smem);
 }
 
+template <bool kSmemTable, bool kExtras>
+cudaError_t occupancy_variant(const LaunchPlan& plan, int* ctas_per_sm) {
+    if (plan.bulk)
+        return occupancy_of(dispatch_bulk_kernel<kSmemTable, kExtras, kStagesDefault>, plan.threads,
+                            plan.dyn_smem, ctas_per_sm);
+    return occupancy_of(dispatch_kernel<kSmemTable, kExtras, kUnrollDefault>, plan.threads,
+                        plan.dyn_smem, ctas_per_sm);
+}
+
 }  // namespace
 
-// Block shape and residency.  A staged table bigger than ~100 KiB leaves room for one
-// CTA per SM, which then runs 1024 threads; small tables run several 256-thread CTAs
-// per SM.  Either way the persistent grid is ctas_per_sm x SM count (148 on B200).
+// Which kernel, block shape and residency.
+//   slot table <= 16 KiB : bulk-staged requests, table in shared memory, 256-thread CTAs
+//   <= 200 KiB           : table fills shared memory, requests by LDG + shuffle transpose
+//                          (1024-thread CTA, one per SM, once the table passes 100 KiB)
+//   larger, or PTYPE_F_GLOBAL_TABLE : bulk-staged requests, table probed in L2
+// The persistent grid is ctas_per_sm x SM count (148 on B200) in every case.
 cudaError_t plan_dispatch(const DeviceImage& img, uint32_t flags, bool extras, LaunchPlan* plan) {
     const size_t table_bytes = static_cast<size_t>(img.n_slots) * sizeof(ptype_slot);
     constexpr size_t kSmemBudget = 200 * 1024;
-    plan->smem_table = !(flags & PTYPE_F_GLOBAL_TABLE) && table_bytes <= kSmemBudget;
-    plan->dyn_smem = plan->smem_table ? table_bytes : 0;
-    plan->threads = plan->dyn_smem > 100 * 1024 ? 1024 : 256;
+    constexpr size_t kSmallTable = 16 * 1024;
+    const bool force_global = (flags & PTYPE_F_GLOBAL_TABLE) != 0;
+    const bool force_ldg = (flags & PTYPE_F_LDG_LOADS) != 0;
+    plan->smem_table = !force_global && table_bytes <= kSmemBudget;
+    plan->bulk = !force_ldg && (!plan->smem_table || table_bytes <= kSmallTable);
+    plan->table_smem = plan->smem_table ? (table_bytes + 127) / 128 * 128 : 0;
+    if (plan->bulk) {
+        plan->threads = kBulkThreads;
+        plan->dyn_smem = plan->table_smem + kBulkStageBytes;
+    } else {
+        plan->threads = plan->table_smem > 100 * 1024 ? 1024 : 256;
+        plan->dyn_smem = plan->table_smem;
+    }
     int ctas = 0;
     cudaError_t e;
     if (plan->smem_table)
-        e = extras ? occupancy_variant<true, true>(plan->threads, plan->dyn_smem, &ctas)
-                   : occupancy_variant<true, false>(plan->threads, plan->dyn_smem, &ctas);
+        e = extras ? occupancy_variant<true, true>(*plan, &ctas) : occupancy_variant<true, false>(*plan, &ctas);
     else
-        e = extras ? occupancy_variant<false, true>(plan->threads, plan->dyn_smem, &ctas)
-                   : occupancy_variant<false, false>(plan->threads, plan->dyn_smem, &ctas);
+        e = extras ? occupancy_variant<false, true>(*plan, &ctas) : occupancy_variant<false, false>(*plan, &ctas);
     if (e != cudaSuccess) return e;
     if (ctas < 1) return cudaErrorLaunchOutOfResources;
     plan->ctas_per_sm = ctas;
@@ -478,14 +696,18 @@ int grid_for(const LaunchPlan& plan, size_t n, int sm_count) {
 cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int blocks,
                             const ptype_req* reqs, size_t n, ptype_reply* replies, uint32_t* failed_idx,
                             uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
-                           cudaStream_t stream) {
+                            cudaStream_t stream) {
     const bool extras = stats != nullptr;
     if (plan.smem_table) {
-        return extras ? launch_variant<true, true>(img, plan, blocks, reqs, n, replies, failed_idx, failed_cap, idx_base, stats, stream)
-                      : launch_variant<true, false>(img, plan, blocks, reqs, n, replies, failed_idx, failed_cap, idx_base, stats, stream);
+        return extras ? launch_variant<true, true>(img, plan, blocks, reqs, n, replies, failed_idx,
+                                                   failed_cap, idx_base, stats, stream)
+                      : launch_variant<true, false>(img, plan, blocks, reqs, n, replies, failed_idx,
+                                                    failed_cap, idx_base, stats, stream);
     }
-    return extras ? launch_variant<false, true>(img, plan, blocks, reqs, n, replies, failed_idx, failed_cap, idx_base, stats, stream)
-                  : launch_variant<false, false>(img, plan, blocks, reqs, n, replies, failed_idx, failed_cap, idx_base, stats, stream);
+    return extras ? launch_variant<false, true>(img, plan, blocks, reqs, n, replies, failed_idx,
+                                                failed_cap, idx_base, stats, stream)
+                  : launch_variant<false, false>(img, plan, blocks, reqs, n, replies, failed_idx,
+                                                 failed_cap, idx_base, stats, stream);
 }
 
 cudaError_t launch_reply_checksum(const ptype_reply* replies, size_t n, uint64_t index_base,

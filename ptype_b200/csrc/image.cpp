@@ -13,6 +13,7 @@
 #include <map>
 #include <new>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/ptype_b200.h"
@@ -173,10 +174,14 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     }
 
     // Table size: half full when that fits the shared-memory budget, otherwise
-    // fill the budget (up to 80 % load), otherwise a half-full table probed in L2.
+    // fill the budget (up to 80 % load: 3-way cuckoo places that reliably), otherwise
+    // a half-full table probed in L2.
     uint32_t n_slots;
     if (b->forced_slots) {
-        if (b->forced_slots <= n_services) return PTYPE_E_INVAL;  // needs one free slot
+        // 3-way cuckoo hashing stops placing reliably a little above 90 % load
+        if (static_cast<uint64_t>(b->forced_slots) * 9 < static_cast<uint64_t>(n_services) * 10 ||
+            b->forced_slots <= n_services)
+            return PTYPE_E_INVAL;
         n_slots = b->forced_slots;
     } else {
         size_t want = std::max<size_t>(8, align_up(2 * n_services, 8));
@@ -205,6 +210,8 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     off = align_up(off + static_cast<size_t>(n_conn) * sizeof(uint32_t), 16);
     const size_t off_methods = off;
     off += n_methods * sizeof(ptype_method);
+    const size_t off_mtable = off;
+    off += PTYPE_MTABLE_SLOTS * sizeof(ptype_method);
     const size_t device_bytes = off;
     const size_t off_services = off;
     off += n_services * sizeof(ptype_service);
@@ -240,18 +247,51 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     unsigned char* blob = static_cast<unsigned char*>(std::calloc(1, total));
     if (!blob) return PTYPE_E_NOMEM;
 
+    // 3-way cuckoo placement: every key ends up in one of its three candidate slots, so a
+    // device lookup is three independent probes at most.  Random-walk insertion; a walk that
+    // does not settle restarts the whole table under the next seed.
     ptype_slot* slots = reinterpret_cast<ptype_slot*>(blob + off_slots);
-    for (uint32_t i = 0; i < n_slots; ++i) {
-        slots[i].key = 0;
-        slots[i].node_base = PTYPE_SLOT_EMPTY;
-        slots[i].n_and_recv = 0;
-    }
-    for (size_t i = 0; i < n_services; ++i) {
-        uint32_t at = ptype::home_slot(services[i].key, n_slots);
-        while (slots[at].node_base != PTYPE_SLOT_EMPTY) at = at + 1 == n_slots ? 0 : at + 1;
-        slots[at].key = services[i].key;
-        slots[at].node_base = services[i].node_base;
-        slots[at].n_and_recv = services[i].n_nodes | (services[i].recv_mask << 24);
+    uint32_t table_seed = 0;
+    for (;; ++table_seed) {
+        if (table_seed == 32) {
+            std::free(blob);
+            return PTYPE_E_COLLISION;
+        }
+        for (uint32_t i = 0; i < n_slots; ++i) {
+            slots[i].key = 0;
+            slots[i].node_base = PTYPE_SLOT_EMPTY;
+            slots[i].n_and_recv = 0;
+        }
+        uint64_t rng = 0x9E3779B97F4A7C15ull ^ table_seed;
+        bool ok = true;
+        for (size_t i = 0; i < n_services && ok; ++i) {
+            ptype_slot cur;
+            cur.key = services[i].key;
+            cur.node_base = services[i].node_base;
+            cur.n_and_recv = services[i].n_nodes | (services[i].recv_mask << 24);
+            ok = false;
+            for (int kick = 0; kick < 2000; ++kick) {
+                const uint32_t lo = static_cast<uint32_t>(cur.key), hi = static_cast<uint32_t>(cur.key >> 32);
+                uint32_t cand[PTYPE_SLOT_WAYS];
+                bool placed = false;
+                for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
+                    cand[w] = ptype::slot_of(lo, hi, table_seed, w, n_slots);
+                    if (slots[cand[w]].node_base == PTYPE_SLOT_EMPTY) {
+                        slots[cand[w]] = cur;
+                        placed = true;
+                        break;
+                    }
+                }
+                if (placed) {
+                    ok = true;
+                    break;
+                }
+                rng = rng * 6364136223846793005ull + 1442695040888963407ull;
+                const uint32_t victim = cand[(rng >> 33) % PTYPE_SLOT_WAYS];
+                std::swap(cur, slots[victim]);
+            }
+        }
+        if (ok) break;
     }
     uint32_t* conn = reinterpret_cast<uint32_t*>(blob + off_conn);
     for (uint32_t i = 0; i < n_conn; ++i)
@@ -264,6 +304,24 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
         methods[i].recv_hash = ptype::fnv1a32(m.recv, std::strlen(m.recv));
         methods[i].opcode = m.opcode;
         methods[i].recv_bit = m.recv_bit;
+    }
+    // Perfect-hash method table: pick an odd multiplier under which the registered method
+    // hashes fall into distinct entries, so the device resolves a method with one load.
+    ptype_method* mtable = reinterpret_cast<ptype_method*>(blob + off_mtable);
+    uint32_t method_mul = 1;
+    for (;; method_mul += 2) {
+        if (method_mul > (1u << 20)) {
+            std::free(blob);
+            return PTYPE_E_COLLISION;
+        }
+        std::memset(mtable, 0, PTYPE_MTABLE_SLOTS * sizeof(ptype_method));
+        bool ok = true;
+        for (uint32_t i = 0; i < n_methods && ok; ++i) {
+            ptype_method& e = mtable[ptype::mtable_index(methods[i].method_hash, method_mul)];
+            ok = e.opcode == PTYPE_OP_NONE;
+            e = methods[i];
+        }
+        if (ok) break;
     }
     // Host-side service records sorted by key for binary search.
     std::vector<uint32_t> perm(n_services);
@@ -302,6 +360,9 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     h->off_strings = static_cast<uint32_t>(off_strings);
     h->strings_bytes = static_cast<uint32_t>(pool.size());
     h->device_bytes = static_cast<uint32_t>(device_bytes);
+    h->table_seed = table_seed;
+    h->method_mul = method_mul;
+    h->off_mtable = static_cast<uint32_t>(off_mtable);
     std::snprintf(h->local_addr, sizeof h->local_addr, "%s", b->local_addr.c_str());
     h->body_checksum = ptype::fnv1a64(blob + sizeof(ptype_image_header),
                                       total - sizeof(ptype_image_header), 0);
@@ -323,10 +384,12 @@ int ptype_b200_image_validate(const void* image, size_t bytes) {
     if (!inside(h->off_slots, uint64_t(h->n_slots) * sizeof(ptype_slot)) ||
         !inside(h->off_conn_hash, uint64_t(h->n_conn_hash) * 4) ||
         !inside(h->off_methods, uint64_t(h->n_methods) * sizeof(ptype_method)) ||
+        !inside(h->off_mtable, uint64_t(PTYPE_MTABLE_SLOTS) * sizeof(ptype_method)) ||
+        (h->off_mtable & 15u) || !(h->method_mul & 1u) ||
         !inside(h->off_services, uint64_t(h->n_services) * sizeof(ptype_service)) ||
         !inside(h->off_nodes, uint64_t(h->n_nodes) * sizeof(ptype_node)) ||
         !inside(h->off_strings, h->strings_bytes) || h->device_bytes > bytes ||
-        h->device_bytes < h->off_methods + h->n_methods * sizeof(ptype_method))
+        h->device_bytes < h->off_mtable + PTYPE_MTABLE_SLOTS * sizeof(ptype_method))
         return PTYPE_E_BAD_IMAGE;
     if (h->local_addr[PTYPE_LOCAL_ADDR_MAX - 1] != 0) return PTYPE_E_BAD_IMAGE;
     const unsigned char* p = static_cast<const unsigned char*>(image);

@@ -44,13 +44,19 @@ PTYPE_HD uint64_t fmix64(uint64_t x) {
     return x;
 }
 
-// Home slot of a key in a table of n_slots (any n_slots >= 1): multiply-shift range
-// reduction of the top 32 mixed bits, so the table need not be a power of two and
-// can be sized to fill shared memory.
-PTYPE_HD uint32_t home_slot(uint64_t key, uint32_t n_slots) {
-    uint32_t h = static_cast<uint32_t>(fmix64(key) >> 32);
+// Candidate slot `way` (0..2) of a key in a table of n_slots (any n_slots >= 1).  The key
+// is already an FNV-1a-64 hash: xor-fold it to 32 bits, mix in the table seed, scramble
+// with one odd multiply per way, then reduce by multiply-shift, so the table need not be
+// a power of two and can be sized to fill shared memory.  Three integer instructions per
+// way on the device.
+PTYPE_HD uint32_t slot_of(uint32_t key_lo, uint32_t key_hi, uint32_t seed, int way, uint32_t n_slots) {
+    const uint32_t mul = way == 0 ? 0x9E3779B1u : (way == 1 ? 0x85EBCA77u : 0xC2B2AE3Du);
+    const uint32_t h = ((key_lo ^ key_hi) ^ seed) * mul;
     return static_cast<uint32_t>((static_cast<uint64_t>(h) * n_slots) >> 32);
 }
+
+// Index into the 64-entry perfect-hash method table.
+PTYPE_HD uint32_t mtable_index(uint32_t method_hash, uint32_t mul) { return (method_hash * mul) >> 26; }
 
 // One term of the order-independent reply checksum (see ptype_b200_reply_checksum).
 PTYPE_HD uint64_t checksum_term(uint64_t value, uint32_t node, uint32_t status, uint64_t idx) {

@@ -42,6 +42,10 @@ def device_roundtrip(ctx, reqs, flags=0):
         d_rep.free()
 
 
+# kernel variants selectable by flag: table in shared memory or L2, requests staged by
+# bulk-async copies or by LDG + shuffle transpose
+VARIANTS = [0, p.F_GLOBAL_TABLE, p.F_LDG_LOADS, p.F_GLOBAL_TABLE | p.F_LDG_LOADS]
+
 SPECS = {
     "calc3": lambda: w.calculator_registry(),
     "calcmesh": lambda: w.calculator_registry(mesh=True),
@@ -59,7 +63,9 @@ def test_golden_fixtures(ctx, name):
     want = fx[f"{name}_rep"].view(p.REPLY_DTYPE).reshape(-1)
     assert_same(ctx.dispatch(req), want, req)
     assert_same(device_roundtrip(ctx, req), want, req)
-    assert_same(device_roundtrip(ctx, req, flags=p.F_GLOBAL_TABLE), want, req)
+    for flags in VARIANTS:
+        assert_same(device_roundtrip(ctx, req, flags=flags), want, req)
+        assert_same(ctx.dispatch(req, flags=flags), want, req)
 
 
 @pytest.mark.parametrize("name", list(SPECS))
@@ -76,7 +82,8 @@ def test_edge_cases_every_status(ctx, oracle, name, limit):
     seen = set(np.unique(want["status"]).tolist())
     assert {0, 1, 2, 3, 4, 5, 6} <= seen
     assert_same(ctx.dispatch(req), want, req)
-    assert_same(device_roundtrip(ctx, req), want, req)
+    for flags in VARIANTS:
+        assert_same(device_roundtrip(ctx, req, flags=flags), want, req)
     ctx.set_check_limit(LIMIT)
 
 
@@ -90,7 +97,8 @@ def test_ragged_sizes(ctx, oracle, n):
     req = w.calculator_calls(n, seed=0x5EED0002 + n)
     want = snap.dispatch(req)
     assert_same(ctx.dispatch(req), want, req)
-    assert_same(device_roundtrip(ctx, req), want, req)
+    for flags in VARIANTS:
+        assert_same(device_roundtrip(ctx, req, flags=flags), want, req)
 
 
 @pytest.mark.parametrize("mesh", [False, True])
@@ -129,7 +137,8 @@ def test_c3_registry_stress(ctx, stress, oracle, zipf):
     want = snap.dispatch(req, threads=8)
     got = device_roundtrip(ctx, req)
     assert_same(got, want, req)
-    assert_same(device_roundtrip(ctx, req, flags=p.F_GLOBAL_TABLE), want, req)
+    for flags in VARIANTS[1:] * 3:   # repeated: the staged-request ring once raced here
+        assert_same(device_roundtrip(ctx, req, flags=flags), want, req)
     miss = got["status"] == p.ST_NO_SERVICE
     assert 0.005 < miss.mean() < 0.02 and np.all(got["node"][miss] == p.NO_NODE)
     ok = got["status"] == p.ST_OK
@@ -282,15 +291,15 @@ def test_max_connections_larger_than_shared_cache(ctx, oracle):
 
 
 def test_colliding_table_slots(ctx, oracle):
-    """A nearly full table (forced size): long probe chains, wrap-around, misses that walk
-    to an empty slot."""
+    """A table forced to ~89 % load: keys displaced to their second and third candidate
+    slots, and misses that probe all three."""
     spec = w.stress_registry(500, 2)
-    img = spec.image(n_slots=501)
+    img = spec.image(n_slots=560)
     ctx.publish(img)
     kv, snap = oracle.snapshot_from_spec(spec)
     req = w.stress_calls(100_000, 500, miss_rate=0.2)
-    assert_same(device_roundtrip(ctx, req), snap.dispatch(req), req)
-    assert_same(device_roundtrip(ctx, req, flags=p.F_GLOBAL_TABLE), snap.dispatch(req), req)
+    for flags in VARIANTS:
+        assert_same(device_roundtrip(ctx, req, flags=flags), snap.dispatch(req), req)
 
 
 def test_calls_from_many_threads(ctx, oracle):

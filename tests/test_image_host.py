@@ -115,9 +115,9 @@ def test_table_sizing():
     assert small.header.n_slots == 8
     spec = w.stress_registry(300, 1)
     assert spec.image().header.n_slots == 600
-    assert spec.image(n_slots=301).header.n_slots == 301
+    assert spec.image(n_slots=340).header.n_slots == 340
     with pytest.raises(p.PtypeError):
-        spec.image(n_slots=300)
+        spec.image(n_slots=320)         # above the ~90 % load 3-way cuckoo hashing can place
 
 
 def test_stress_image_fits_shared_memory_budget():
@@ -126,6 +126,44 @@ def test_stress_image_fits_shared_memory_budget():
     img = spec.image()
     assert img.header.n_slots == 12_800 and img.header.n_services == 10_000
     assert img.header.n_slots * 16 <= 200 * 1024
+
+
+def slot_candidates(key: np.ndarray, seed: int, n_slots: int) -> np.ndarray:
+    """numpy restatement of ptype::slot_of (csrc/table_hash.h) for all three ways."""
+    with np.errstate(over="ignore"):
+        fold = ((key & np.uint64(0xFFFFFFFF)) ^ (key >> np.uint64(32))).astype(np.uint32) ^ np.uint32(seed)
+        out = []
+        for mul in (0x9E3779B1, 0x85EBCA77, 0xC2B2AE3D):
+            h = fold * np.uint32(mul)
+            out.append(((h.astype(np.uint64) * np.uint64(n_slots)) >> np.uint64(32)).astype(np.int64))
+    return np.stack(out, axis=1)
+
+
+@pytest.mark.parametrize("n_services,n_slots", [(10_000, 0), (500, 560), (3, 0), (1, 0)])
+def test_every_key_sits_in_one_of_its_three_slots(n_services, n_slots):
+    """3-way cuckoo placement: a device lookup is at most three probes, hit or miss."""
+    img = w.stress_registry(n_services, 1).image(n_slots=n_slots)
+    h = img.header
+    slots = np.frombuffer(img.blob, dtype=[("key", "<u8"), ("base", "<u4"), ("nr", "<u4")],
+                          count=h.n_slots, offset=h.off_slots)
+    occ = np.flatnonzero(slots["base"] != 0xFFFFFFFF)
+    assert len(occ) == n_services
+    cand = slot_candidates(slots["key"][occ], h.table_seed, h.n_slots)
+    assert np.all((cand == occ[:, None]).any(axis=1))
+    keys = np.array([p.service_key(f"svc_{s:05d}", h.key_salt) for s in range(n_services)], dtype=np.uint64)
+    assert set(keys.tolist()) == set(slots["key"][occ].tolist())
+
+
+def test_method_table_is_a_perfect_hash():
+    img = w.calculator_registry().image()
+    h = img.header
+    mt = np.frombuffer(img.blob, dtype=[("m", "<u4"), ("r", "<u4"), ("op", "<u4"), ("bit", "<u4")],
+                       count=64, offset=h.off_mtable)
+    assert h.method_mul % 2 == 1 and (mt["op"] != 0).sum() == h.n_methods == 3
+    for name, op in (("Calculator.Multiply", 1), ("Calculator.Add", 2), ("Prime.Check", 3)):
+        m, r = p.method_key(name)
+        e = mt[((m * h.method_mul) & 0xFFFFFFFF) >> 26]
+        assert (e["m"], e["r"], e["op"]) == (m, r, op)
 
 
 def test_split_work_generator(oracle):
