@@ -277,8 +277,8 @@ int ptype_b200_broadcast_image(ptype_ctx*, const void* image, size_t bytes, int 
 #define PTYPE_F_DEVICE_PTRS 1u /* reqs/replies are device pointers on `dev`      */
 #define PTYPE_F_ASYNC 2u       /* return after enqueue; pair with ptype_b200_sync */
 #define PTYPE_F_GLOBAL_TABLE 4u/* measurement switch: probe the table in L2, not shared memory  */
-#define PTYPE_F_LDG_LOADS 8u   /* measurement switch: fetch requests with LDG + shuffle transpose
-                                  instead of bulk-async staging                                */
+#define PTYPE_F_LDG_LOADS 8u   /* measurement switch: fetch requests with LDG + shuffle transpose */
+#define PTYPE_F_BULK_LOADS 16u /* measurement switch: stage requests with bulk-async copies      */
 
 /* Optional per-batch outputs (all device-written; host copies made on sync). */
 typedef struct ptype_batch_stats {

@@ -87,11 +87,16 @@ int nccl_fail(int r, const char* what) {
 }
 
 // Launch-plan variants selectable through the dispatch flags (measurement switches).
-constexpr int kPlanKinds = 4;
-constexpr uint32_t kPlanFlags[kPlanKinds] = {0u, PTYPE_F_GLOBAL_TABLE, PTYPE_F_LDG_LOADS,
-                                             PTYPE_F_GLOBAL_TABLE | PTYPE_F_LDG_LOADS};
+constexpr int kPlanKinds = 6;
+constexpr uint32_t kPlanFlags[kPlanKinds] = {0u,
+                                             PTYPE_F_GLOBAL_TABLE,
+                                             PTYPE_F_LDG_LOADS,
+                                             PTYPE_F_GLOBAL_TABLE | PTYPE_F_LDG_LOADS,
+                                             PTYPE_F_BULK_LOADS,
+                                             PTYPE_F_GLOBAL_TABLE | PTYPE_F_BULK_LOADS};
 inline int plan_kind(uint32_t flags) {
-    return ((flags & PTYPE_F_GLOBAL_TABLE) ? 1 : 0) | ((flags & PTYPE_F_LDG_LOADS) ? 2 : 0);
+    const int load = (flags & PTYPE_F_LDG_LOADS) ? 1 : ((flags & PTYPE_F_BULK_LOADS) ? 2 : 0);
+    return load * 2 + ((flags & PTYPE_F_GLOBAL_TABLE) ? 1 : 0);
 }
 
 struct Stage {

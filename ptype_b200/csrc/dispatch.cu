@@ -109,13 +109,30 @@ __device__ __forceinline__ uint64_t abs_u64(int64_t v) {
 // Go's truncated % is zero exactly when |i| divides |Target| (and MinInt64 % -1 is 0,
 // no trap), so the test runs on magnitudes; a 32-bit divide serves the common case.
 __device__ __forceinline__ int64_t prime_check(int64_t lo, int64_t hi, int64_t target,
-                                               uint64_t limit, uint32_t* status) {
+                                               uint64_t limit, uint32_t& status) {
     const int64_t bound = hi < target ? hi : target;
     if (lo >= bound) return target;
     const uint64_t width = static_cast<uint64_t>(bound) - static_cast<uint64_t>(lo);
     if (width > limit) {
-        *status = PTYPE_ST_RANGE_LIMIT;
+        status = PTYPE_ST_RANGE_LIMIT;
         return 0;
+    }
+    if (target > 0 && target < (1ll << 22) && lo >= 1) {
+        // The coordinator's streams (coordinator.go:67-73): small positive targets and
+        // divisors.  t/i through the approximate reciprocal is off by less than 1 when
+        // t < 2^22 (relative error < 2^-22), so the truncated quotient is the true one
+        // or a neighbour and the remainder test below is exact.
+        const int t = static_cast<int>(target);
+        const float tf = static_cast<float>(t);
+        int i = static_cast<int>(lo);
+        const int end = static_cast<int>(bound);
+        float fi = static_cast<float>(i);
+        for (; i < end; ++i, fi += 1.0f) {
+            const int q = __float2int_rz(__fdividef(tf, fi));
+            const int r = t - q * i;
+            if (r == 0 || r == i || r == -i) return i;
+        }
+        return target;
     }
     const uint64_t tmag = abs_u64(target);
     const bool t32 = (tmag >> 32) == 0;
@@ -163,32 +180,33 @@ __device__ __forceinline__ uint32_t umod(uint32_t a, uint32_t d) {
 
 // Round-robin index for sequence numbers that do not fit 32 bits, including the range
 // where Go's int(index) is negative (cluster/rpc.go:182).
-__device__ __noinline__ uint32_t route_wide(uint64_t seq, uint32_t k, uint32_t* status) {
-    if (static_cast<int64_t>(seq) >= 0) return static_cast<uint32_t>(seq % k);
+// Out-of-line helpers return (status << 32) | result so that status never needs a stack slot.
+__device__ __forceinline__ uint64_t pack_result(uint32_t status, uint32_t result) {
+    return (static_cast<uint64_t>(status) << 32) | result;
+}
+
+__device__ __noinline__ uint64_t route_wide(uint64_t seq, uint32_t k) {
+    if (static_cast<int64_t>(seq) >= 0) return pack_result(PTYPE_ST_OK, static_cast<uint32_t>(seq % k));
     // Go's % keeps the dividend's sign: any non-zero remainder indexes clients[] below 0
-    if (static_cast<int64_t>(seq) % static_cast<int64_t>(k) != 0) *status = PTYPE_ST_BAD_INDEX;
-    return 0;
+    const bool bad = static_cast<int64_t>(seq) % static_cast<int64_t>(k) != 0;
+    return pack_result(bad ? PTYPE_ST_BAD_INDEX : PTYPE_ST_OK, 0);
 }
 
 // Everything but the fast resolve: which net/rpc error a request gets, or the opcode of
 // a method the perfect-hash entry did not confirm (cannot happen for registered methods).
-__device__ __noinline__ uint32_t resolve_slow(const CtaShared& sh, uint32_t n_methods,
-                                              uint32_t method, uint32_t recv, uint32_t recv_mask,
-                                              uint32_t* status) {
-    if (recv == PTYPE_RECV_ILL_FORMED) {
-        *status = PTYPE_ST_ILL_FORMED;
-        return PTYPE_OP_NONE;
-    }
+__device__ __noinline__ uint64_t resolve_slow(const CtaShared& sh, uint32_t n_methods,
+                                              uint32_t method, uint32_t recv, uint32_t recv_mask) {
+    if (recv == PTYPE_RECV_ILL_FORMED) return pack_result(PTYPE_ST_ILL_FORMED, PTYPE_OP_NONE);
     bool recv_known = false;
     for (uint32_t e = 0; e < n_methods; ++e) {
         const ptype_method md = sh.methods[e];
         if (md.recv_hash == recv && ((recv_mask >> md.recv_bit) & 1u)) {
             recv_known = true;
-            if (md.method_hash == method) return md.opcode;
+            if (md.method_hash == method) return pack_result(PTYPE_ST_OK, md.opcode);
         }
     }
-    *status = recv_known ? PTYPE_ST_CANT_FIND_METHOD : PTYPE_ST_CANT_FIND_SERVICE;
-    return PTYPE_OP_NONE;
+    return pack_result(recv_known ? PTYPE_ST_CANT_FIND_METHOD : PTYPE_ST_CANT_FIND_SERVICE,
+                       PTYPE_OP_NONE);
 }
 
 // Exact-key lookup: the key sits in one of three candidate slots or nowhere.
@@ -257,8 +275,10 @@ __device__ __forceinline__ uint4 dispatch_one(const DeviceImage& img, const CtaS
             // (Lemire fastmod); k == n differs per service and takes the divide.
             r = identity ? umod(q0.z, n) : static_cast<uint32_t>(__umul64hi(img.m_magic * q0.z, m));
         } else {
-            r = route_wide(static_cast<uint64_t>(q0.z) | (static_cast<uint64_t>(q0.w) << 32),
-                           identity ? n : m, &status);
+            const uint64_t rw = route_wide(
+                static_cast<uint64_t>(q0.z) | (static_cast<uint64_t>(q0.w) << 32), identity ? n : m);
+            r = static_cast<uint32_t>(rw);
+            status = static_cast<uint32_t>(rw >> 32);
         }
         if (status == PTYPE_ST_OK) {
             uint32_t local = r;
@@ -271,8 +291,11 @@ __device__ __forceinline__ uint4 dispatch_one(const DeviceImage& img, const CtaS
             const uint32_t recv_mask = n_and_recv >> 24;
             const uint4 md = *reinterpret_cast<const uint4*>(&sh.mtable[mtable_index(q1.x, img.method_mul)]);
             uint32_t opcode = md.z;
-            if (!(md.x == q1.x && md.y == q1.y && opcode != PTYPE_OP_NONE && ((recv_mask >> md.w) & 1u)))
-                opcode = resolve_slow(sh, img.n_methods, q1.x, q1.y, recv_mask, &status);
+            if (!(md.x == q1.x && md.y == q1.y && opcode != PTYPE_OP_NONE && ((recv_mask >> md.w) & 1u))) {
+                const uint64_t rs = resolve_slow(sh, img.n_methods, q1.x, q1.y, recv_mask);
+                opcode = static_cast<uint32_t>(rs);
+                status = static_cast<uint32_t>(rs >> 32);
+            }
             // ---- execute
             if (status == PTYPE_ST_OK) {
                 const uint64_t a0 = static_cast<uint64_t>(q1.z) | (static_cast<uint64_t>(q1.w) << 32);
@@ -283,7 +306,7 @@ __device__ __forceinline__ uint4 dispatch_one(const DeviceImage& img, const CtaS
                     value = static_cast<uint64_t>(prime_check(static_cast<int64_t>(a0),
                                                               static_cast<int64_t>(a1),
                                                               static_cast<int64_t>(a2), img.check_limit,
-                                                              &status));
+                                                              status));
                 } else {
                     // Go int wraps (calculator.go:10); both results computed, one selected:
                     // a mixed Add/Multiply warp does not diverge
@@ -382,7 +405,7 @@ constexpr int kTileBytes = 32 * 48;
 constexpr int kBulkThreads = 256;
 
 template <bool kSmemTable, bool kExtras, int kStages>
-__global__ void __launch_bounds__(kBulkThreads, 6)
+__global__ void __launch_bounds__(kBulkThreads, 5)
     dispatch_bulk_kernel(const DeviceImage img, const uint4* __restrict__ reqs, const size_t n,
                          uint4* __restrict__ replies, uint32_t* __restrict__ failed_idx,
                          const uint32_t failed_cap, const uint32_t idx_base,
@@ -650,11 +673,13 @@ cudaError_t occupancy_variant(const LaunchPlan& plan, int* ctas_per_sm) {
 
 }  // namespace
 
-// Which kernel, block shape and residency.
-//   slot table <= 16 KiB : bulk-staged requests, table in shared memory, 256-thread CTAs
-//   <= 200 KiB           : table fills shared memory, requests by LDG + shuffle transpose
-//                          (1024-thread CTA, one per SM, once the table passes 100 KiB)
-//   larger, or PTYPE_F_GLOBAL_TABLE : bulk-staged requests, table probed in L2
+// Which kernel, block shape and residency (measured on B200, profiles/README.md):
+//   slot table <= 200 KiB : table staged in shared memory, requests by LDG + shuffle
+//                           transpose (1024-thread CTA, one per SM, once the table passes
+//                           100 KiB; 256-thread CTAs otherwise)
+//   larger                : table probed in L2, requests staged by bulk-async copies
+// PTYPE_F_GLOBAL_TABLE / PTYPE_F_LDG_LOADS / PTYPE_F_BULK_LOADS force the other variants
+// (bulk staging with a shared-memory table needs the table to fit 16 KiB).
 // The persistent grid is ctas_per_sm x SM count (148 on B200) in every case.
 cudaError_t plan_dispatch(const DeviceImage& img, uint32_t flags, bool extras, LaunchPlan* plan) {
     const size_t table_bytes = static_cast<size_t>(img.n_slots) * sizeof(ptype_slot);
@@ -662,8 +687,10 @@ cudaError_t plan_dispatch(const DeviceImage& img, uint32_t flags, bool extras, L
     constexpr size_t kSmallTable = 16 * 1024;
     const bool force_global = (flags & PTYPE_F_GLOBAL_TABLE) != 0;
     const bool force_ldg = (flags & PTYPE_F_LDG_LOADS) != 0;
-    plan->smem_table = !force_global && table_bytes <= kSmemBudget;
-    plan->bulk = !force_ldg && (!plan->smem_table || table_bytes <= kSmallTable);
+    const bool force_bulk = (flags & PTYPE_F_BULK_LOADS) != 0 && !force_ldg;
+    plan->smem_table = !force_global && table_bytes <= kSmemBudget &&
+                       !(force_bulk && table_bytes > kSmallTable);
+    plan->bulk = force_bulk || (!force_ldg && !plan->smem_table);
     plan->table_smem = plan->smem_table ? (table_bytes + 127) / 128 * 128 : 0;
     if (plan->bulk) {
         plan->threads = kBulkThreads;

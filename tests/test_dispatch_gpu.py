@@ -44,7 +44,8 @@ def device_roundtrip(ctx, reqs, flags=0):
 
 # kernel variants selectable by flag: table in shared memory or L2, requests staged by
 # bulk-async copies or by LDG + shuffle transpose
-VARIANTS = [0, p.F_GLOBAL_TABLE, p.F_LDG_LOADS, p.F_GLOBAL_TABLE | p.F_LDG_LOADS]
+VARIANTS = [0, p.F_GLOBAL_TABLE, p.F_LDG_LOADS, p.F_GLOBAL_TABLE | p.F_LDG_LOADS, p.F_BULK_LOADS,
+            p.F_GLOBAL_TABLE | p.F_BULK_LOADS]
 
 SPECS = {
     "calc3": lambda: w.calculator_registry(),
