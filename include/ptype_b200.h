@@ -301,6 +301,18 @@ int ptype_b200_dispatch(ptype_ctx*, int dev, const ptype_req* reqs, size_t n, pt
 int ptype_b200_dispatch_ex(ptype_ctx*, int dev, const ptype_req* reqs, size_t n,
                            ptype_reply* replies, uint32_t* failed_idx, size_t failed_cap,
                            ptype_batch_stats* stats, uint32_t flags);
+/* Several device-resident batches in one call: the launches are enqueued back to back
+ * on the context's stream (consecutive kernels overlap their ramp-up and drain through
+ * programmatic dependent launch) and the call returns without waiting unless
+ * PTYPE_F_ASYNC is absent.  This is what a host pipelining the batches of many Clients
+ * (one Client per service, cluster/cluster.go:101-103) submits per scheduling round. */
+typedef struct ptype_batch {
+    const ptype_req* reqs; /* device pointer */
+    ptype_reply* replies;  /* device pointer */
+    size_t n;
+} ptype_batch;
+int ptype_b200_dispatch_batches(ptype_ctx*, int dev, const ptype_batch* batches, size_t count,
+                                uint32_t flags);
 int ptype_b200_sync(ptype_ctx*, int dev);
 int ptype_b200_set_check_limit(ptype_ctx*, uint64_t max_iterations);
 

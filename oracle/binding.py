@@ -85,12 +85,36 @@ def lib() -> C.CDLL:
             "po_method_key": (None, [C.c_char_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
             "po_gob_uint": (C.c_int, [C.c_uint64, C.c_char_p]),
             "po_gob_int": (C.c_int, [C.c_int64, C.c_char_p]),
+            "po_loopback_run": (C.c_int, [vp, C.c_size_t, vp, C.c_int, C.c_uint32, C.c_uint64,
+                                          C.POINTER(LoopbackStats)]),
+            "po_gob_reply_int_message": (C.c_int, [C.c_int64, C.c_char_p]),
+            "po_gob_args_body": (C.c_int, [C.POINTER(C.c_int64), C.c_int, C.c_char_p]),
+            "po_gob_request_typedef": (C.c_int, [C.c_char_p]),
         }
         for name, (res, args) in sigs.items():
             fn = getattr(L, name)
             fn.restype, fn.argtypes = res, args
         _lib = L
     return _lib
+
+
+class LoopbackStats(C.Structure):
+    _fields_ = [("seconds", C.c_double), ("calls", C.c_uint64), ("bytes_client_to_server", C.c_uint64),
+                ("bytes_server_to_client", C.c_uint64)]
+
+
+def loopback_run(reqs: np.ndarray, k: int = 1, receivers: int = 1, check_limit: int = 1 << 16):
+    """BASELINE config 1: len(reqs) sequential synchronous Client.Call()s over loopback TCP with
+    the net/rpc handshake and gob framing restated in C (oracle/loopback.c).  Returns
+    (replies, stats); replies[j].node is the index of the connection the call went out on."""
+    reqs = np.ascontiguousarray(reqs, dtype=REQ_DTYPE)
+    rep = np.zeros(len(reqs), dtype=REPLY_DTYPE)
+    st = LoopbackStats()
+    rc = lib().po_loopback_run(reqs.ctypes.data, len(reqs), rep.ctypes.data, k, receivers, check_limit,
+                               C.byref(st))
+    if rc != 0:
+        raise RuntimeError(f"po_loopback_run failed: {rc}")
+    return rep, st
 
 
 class KV:

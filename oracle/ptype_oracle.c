@@ -701,7 +701,10 @@ typedef struct {
     uint32_t receivers; /* PO_RECV_* bits */
 } po_client;
 
+#define PO_MAX_METHODS 8
 struct po_snapshot {
+    uint32_t method_hash[PO_MAX_METHODS]; /* FNV-1a-32("Recv.Method"), hashed once per snapshot */
+    uint32_t recv_hash[PO_MAX_METHODS];   /* FNV-1a-32("Recv") */
     po_client* clients; /* sorted by key for bsearch */
     size_t n_clients;
     po_node* nodes; /* global node array, in `services` range order */
@@ -709,6 +712,8 @@ struct po_snapshot {
     size_t n_nodes;
     uint64_t salt;
 };
+
+static void po_snapshot_hash_methods(po_snapshot* s);
 
 static int po_client_cmp(const void* a, const void* b) {
     uint64_t ka = ((const po_client*)a)->key, kb = ((const po_client*)b)->key;
@@ -795,6 +800,7 @@ po_snapshot* po_snapshot_build(const po_kv* kv, const char* local_addr, int64_t 
             }
     }
     free(names);
+    po_snapshot_hash_methods(s);
     return s;
 }
 
@@ -876,6 +882,17 @@ static const po_method_def PO_METHODS[] = {
 };
 #define PO_N_METHODS (sizeof PO_METHODS / sizeof PO_METHODS[0])
 
+/* What rpc.Register builds once per server: the method table, here as name hashes. */
+static void po_snapshot_hash_methods(po_snapshot* s) {
+    for (size_t m = 0; m < PO_N_METHODS; m++) {
+        const po_method_def* d = &PO_METHODS[m];
+        char full[128];
+        int l = snprintf(full, sizeof full, "%s.%s", d->recv, d->method);
+        s->method_hash[m] = po_fnv1a32(full, (size_t)l);
+        s->recv_hash[m] = po_fnv1a32(d->recv, strlen(d->recv));
+    }
+}
+
 void po_method_key(const char* service_method, uint32_t* method, uint32_t* recv) {
     *method = po_fnv1a32(service_method, strlen(service_method));
     const char* dot = strrchr(service_method, '.'); /* strings.LastIndex(sm, ".") [net/rpc] */
@@ -903,7 +920,6 @@ static void po_execute(int opcode, const int64_t a[3], uint64_t check_limit, pty
 static void po_call_client(const po_snapshot* s, const po_client* c, uint64_t seq, uint32_t method,
                            uint32_t recv, const int64_t a[3], uint64_t check_limit,
                            ptype_reply* r) {
-    (void)s;
     r->value = 0;
     r->node = PTYPE_NO_NODE;
     if (!c) {
@@ -928,11 +944,9 @@ static void po_call_client(const po_snapshot* s, const po_client* c, uint64_t se
     for (size_t m = 0; m < PO_N_METHODS; m++) {
         const po_method_def* d = &PO_METHODS[m];
         if (!(c->receivers & d->recv_bit)) continue;
-        if (po_fnv1a32(d->recv, strlen(d->recv)) != recv) continue;
+        if (s->recv_hash[m] != recv) continue;
         recv_known = 1;
-        char full[128];
-        int l = snprintf(full, sizeof full, "%s.%s", d->recv, d->method);
-        if (po_fnv1a32(full, (size_t)l) != method) continue;
+        if (s->method_hash[m] != method) continue;
         r->status = PTYPE_ST_OK;
         po_execute(d->opcode, a, check_limit, r);
         return;

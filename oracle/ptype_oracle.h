@@ -125,6 +125,21 @@ void po_method_key(const char* service_method, uint32_t* method, uint32_t* recv)
 int po_gob_uint(uint64_t v, uint8_t* out);
 int po_gob_int(int64_t v, uint8_t* out);
 
+/* ---- config 1: the reference's real path over loopback TCP (oracle/loopback.c) ---- */
+typedef struct po_loopback_stats {
+    double seconds;
+    uint64_t calls;
+    uint64_t bytes_client_to_server;
+    uint64_t bytes_server_to_client;
+} po_loopback_stats;
+/* n sequential synchronous Client.Call()s of one Client holding k connections; every node
+ * registered `receivers` (bit0 Calculator, bit1 Prime).  replies[j].node = connection index. */
+int po_loopback_run(const ptype_req* reqs, size_t n, ptype_reply* replies, int k, uint32_t receivers,
+                    uint64_t check_limit, po_loopback_stats* stats);
+int po_gob_reply_int_message(int64_t v, uint8_t* out);
+int po_gob_args_body(const int64_t* a, int nargs, uint8_t* out);
+int po_gob_request_typedef(uint8_t* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -39,6 +39,10 @@ class BatchStats(C.Structure):
                 ("failed_count", C.c_uint64)]
 
 
+class Batch(C.Structure):
+    _fields_ = [("reqs", C.c_void_p), ("replies", C.c_void_p), ("n", C.c_size_t)]
+
+
 class ImageHeader(C.Structure):
     _fields_ = [
         ("magic", C.c_uint32), ("version", C.c_uint32), ("epoch", C.c_uint64),
@@ -98,6 +102,7 @@ SIGNATURES = [
     ("ptype_b200_dispatch", C.c_int, [_vp, C.c_int, _vp, C.c_size_t, _vp, C.c_uint32]),
     ("ptype_b200_dispatch_ex", C.c_int,
      [_vp, C.c_int, _vp, C.c_size_t, _vp, _vp, C.c_size_t, _vp, C.c_uint32]),
+    ("ptype_b200_dispatch_batches", C.c_int, [_vp, C.c_int, _vp, C.c_size_t, C.c_uint32]),
     ("ptype_b200_sync", C.c_int, [_vp, C.c_int]),
     ("ptype_b200_set_check_limit", C.c_int, [_vp, C.c_uint64]),
     ("ptype_b200_reply_checksum", C.c_int,

@@ -162,6 +162,20 @@ class Context:
                                              _ptr(failed) if failed is not None else None,
                                              failed_cap, _ptr(stats), f), "dispatch_ex")
 
+    def make_batches(self, items) -> "C.Array":
+        """items: iterable of (device reqs, device replies, n) -> a ptype_batch array."""
+        items = list(items)
+        arr = (_abi.Batch * len(items))()
+        for i, (q, r, n) in enumerate(items):
+            arr[i].reqs, arr[i].replies, arr[i].n = _ptr(q), _ptr(r), n
+        return arr
+
+    def dispatch_batches(self, batches, *, dev: int = 0, flags: int = 0, sync: bool = True) -> None:
+        """Enqueue several device-resident batches with one C call (see make_batches)."""
+        f = flags | F_DEVICE_PTRS | (0 if sync else F_ASYNC)
+        check(lib.ptype_b200_dispatch_batches(self._h, dev, batches, len(batches), f),
+              "dispatch_batches")
+
     def sync(self, dev: int = 0) -> None:
         check(lib.ptype_b200_sync(self._h, dev), "sync")
 

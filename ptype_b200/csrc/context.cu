@@ -599,6 +599,29 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
     return PTYPE_OK;
 }
 
+int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batches, size_t count,
+                                uint32_t flags) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || (count && !batches)) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> lk(d->mu);
+    if (d->active < 0) return PTYPE_E_NO_IMAGE;
+    CU(cudaSetDevice(d->device));
+    const int buf = d->active;
+    const ptype::DeviceImage img = d->view[buf];
+    const ptype::LaunchPlan& plan = d->plan[buf][plan_kind(flags)][0];
+    for (size_t b = 0; b < count; ++b) {
+        const ptype_batch& bt = batches[b];
+        if (bt.n == 0) continue;
+        if (!bt.reqs || !bt.replies) return PTYPE_E_INVAL;
+        if (bt.n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
+        CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, bt.n, d->sm_count), bt.reqs, bt.n,
+                                  bt.replies, nullptr, 0u, 0u, nullptr, d->stream));
+        ctx->launches.fetch_add(1);
+    }
+    if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+    return PTYPE_OK;
+}
+
 int ptype_b200_dispatch(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_t n,
                         ptype_reply* replies, uint32_t flags) {
     return ptype_b200_dispatch_ex(ctx, dev, reqs, n, replies, nullptr, 0, nullptr, flags);

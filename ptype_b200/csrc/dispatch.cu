@@ -484,8 +484,8 @@ __global__ void __launch_bounds__(kBulkThreads, 5)
 // Used when the slot table needs (nearly) all of shared memory, so no room is left for
 // request stages: each lane issues three coalesced 128-bit loads covering the warp's
 // contiguous 1536 bytes, then a 12-shuffle transpose hands every lane its own record.
-template <bool kSmemTable, bool kExtras, int kUnroll>
-__global__ void __launch_bounds__(kMaxThreads, 1)
+template <bool kSmemTable, bool kExtras, int kUnroll, int kThreads, int kMinCtas>
+__global__ void __launch_bounds__(kThreads, kMinCtas)
     dispatch_kernel(const DeviceImage img, const uint4* __restrict__ reqs, const size_t n,
                     uint4* __restrict__ replies, uint32_t* __restrict__ failed_idx,
                     const uint32_t failed_cap, const uint32_t idx_base,
@@ -607,7 +607,17 @@ __global__ void __launch_bounds__(kChecksumThreads)
     }
 }
 
-constexpr int kUnrollDefault = 2;
+// LDG kernel shapes: one 1024-thread CTA per SM when the staged table is large (2 tiles in
+// flight per warp, 64 registers), several 256-thread CTAs otherwise.
+#ifndef PTYPE_SMALL_UNROLL
+#define PTYPE_SMALL_UNROLL 2
+#endif
+#ifndef PTYPE_SMALL_MINCTAS
+#define PTYPE_SMALL_MINCTAS 4
+#endif
+constexpr int kSmallThreads = 256;
+constexpr int kSmallUnroll = PTYPE_SMALL_UNROLL;
+constexpr int kSmallMinCtas = PTYPE_SMALL_MINCTAS;
 constexpr int kStagesDefault = 2;
 constexpr size_t kBulkStageBytes = (kBulkThreads / 32) * kStagesDefault * kTileBytes;  // per CTA
 
@@ -648,8 +658,13 @@ cudaError_t launch_variant(const DeviceImage& img, const LaunchPlan& plan, int b
         return launch_kernel(dispatch_bulk_kernel<kSmemTable, kExtras, kStagesDefault>, blocks,
                              plan.threads, plan.dyn_smem, stream, img, q, n, r, failed_idx, failed_cap,
                              idx_base, stats, static_cast<uint32_t>(plan.table_smem));
-    return launch_kernel(dispatch_kernel<kSmemTable, kExtras, kUnrollDefault>, blocks, plan.threads,
-                         plan.dyn_smem, stream, img, q, n, r, failed_idx, failed_cap, idx_base, stats);
+    if (plan.threads == kMaxThreads)
+        return launch_kernel(dispatch_kernel<kSmemTable, kExtras, 2, kMaxThreads, 1>, blocks,
+                             plan.threads, plan.dyn_smem, stream, img, q, n, r, failed_idx, failed_cap,
+                             idx_base, stats);
+    return launch_kernel(dispatch_kernel<kSmemTable, kExtras, kSmallUnroll, kSmallThreads, kSmallMinCtas>,
+                         blocks, plan.threads, plan.dyn_smem, stream, img, q, n, r, failed_idx,
+                         failed_cap, idx_base, stats);
 }
 
 template <typename Kernel>
@@ -667,8 +682,11 @@ cudaError_t occupancy_variant(const LaunchPlan& plan, int* ctas_per_sm) {
     if (plan.bulk)
         return occupancy_of(dispatch_bulk_kernel<kSmemTable, kExtras, kStagesDefault>, plan.threads,
                             plan.dyn_smem, ctas_per_sm);
-    return occupancy_of(dispatch_kernel<kSmemTable, kExtras, kUnrollDefault>, plan.threads,
-                        plan.dyn_smem, ctas_per_sm);
+    if (plan.threads == kMaxThreads)
+        return occupancy_of(dispatch_kernel<kSmemTable, kExtras, 2, kMaxThreads, 1>, plan.threads,
+                            plan.dyn_smem, ctas_per_sm);
+    return occupancy_of(dispatch_kernel<kSmemTable, kExtras, kSmallUnroll, kSmallThreads, kSmallMinCtas>,
+                        plan.threads, plan.dyn_smem, ctas_per_sm);
 }
 
 }  // namespace
@@ -696,7 +714,7 @@ cudaError_t plan_dispatch(const DeviceImage& img, uint32_t flags, bool extras, L
         plan->threads = kBulkThreads;
         plan->dyn_smem = plan->table_smem + kBulkStageBytes;
     } else {
-        plan->threads = plan->table_smem > 100 * 1024 ? 1024 : 256;
+        plan->threads = plan->table_smem > 100 * 1024 ? kMaxThreads : kSmallThreads;
         plan->dyn_smem = plan->table_smem;
     }
     int ctas = 0;

@@ -323,6 +323,26 @@ def test_calls_from_many_threads(ctx, oracle):
     assert not errors, errors
 
 
+def test_dispatch_batches_equals_one_by_one(ctx, oracle):
+    """Many device-resident batches enqueued by one C call (kernels overlap through
+    programmatic dependent launch) give the replies of separate dispatches."""
+    spec = w.calculator_registry()
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    sizes = [1 << 18, 5, 0, 77_777, 1 << 20, 33, 1 << 16] * 3
+    reqs = [w.calculator_calls(n, seed=900 + i, seq_base=i * 1000) for i, n in enumerate(sizes)]
+    d_reqs = [ctx.device_buffer(max(n, 1) * 48).upload(r) for n, r in zip(sizes, reqs)]
+    d_reps = [ctx.device_buffer(max(n, 1) * 16) for n in sizes]
+    batches = ctx.make_batches(zip(d_reqs, d_reps, sizes))
+    for flags in (0, p.F_BULK_LOADS):
+        ctx.dispatch_batches(batches, flags=flags, sync=False)
+        ctx.sync()
+        for n, r, d in zip(sizes, reqs, d_reps):
+            assert_same(d.download(p.REPLY_DTYPE, n), snap.dispatch(r), r)
+    for b in d_reqs + d_reps:
+        b.free()
+
+
 def test_dispatch_without_image_fails():
     c = p.Context([0])
     try:

@@ -172,3 +172,47 @@ def test_golden_fixtures_match_oracle(oracle):
         kv, snap = oracle.snapshot_from_spec(spec)
         rep = snap.dispatch(fx[f"{name}_req"].view(oracle.REQ_DTYPE).reshape(-1), check_limit=1 << 16)
         assert rep.tobytes() == fx[f"{name}_rep"].tobytes(), name
+
+
+# ---- BASELINE config 1: the reference's real path, restated over loopback TCP ---------
+
+def test_loopback_wire_bytes(oracle):
+    """gob messages of the calculator example: reply 56 is 03 04 00 70,
+    Args{7,8} body is 01 0e 01 10 00, and rpc.Request's type definition names its two fields."""
+    buf = C.create_string_buffer(128)
+    n = oracle.lib().po_gob_reply_int_message(56, buf)
+    assert buf.raw[:n].hex() == "03040070"
+    a = (C.c_int64 * 3)(7, 8, 0)
+    n = oracle.lib().po_gob_args_body(a, 2, buf)
+    assert buf.raw[:n].hex() == "010e011000"
+    a = (C.c_int64 * 3)(0, 8, 0)          # zero-valued fields are omitted: delta 2 reaches B
+    n = oracle.lib().po_gob_args_body(a, 2, buf)
+    assert buf.raw[:n].hex() == "021000"
+    n = oracle.lib().po_gob_request_typedef(buf)
+    raw = buf.raw[:n]
+    assert raw[1:3] == b"\xff\x81" and b"Request" in raw and b"ServiceMethod" in raw and b"Seq" in raw
+
+
+def test_loopback_calls_match_in_process_oracle(oracle):
+    """Config 1 in miniature: sequential synchronous calls through TCP 127.0.0.1, the
+    CONNECT /_goRPC_ handshake and gob framing give the replies of the in-process oracle, and
+    the connection used is roundRobinSelect's (first call -> index 1 of 3, rpc_test.go:118-158)."""
+    import ptype_b200.workloads as w
+    spec = w.calculator_registry()
+    kv, snap = oracle.snapshot_from_spec(spec)
+    reqs = w.calculator_calls(3000)
+    rep, st = oracle.loopback_run(reqs, k=3, receivers=1)
+    want = snap.dispatch(reqs)
+    assert np.array_equal(rep["value"], want["value"]) and np.array_equal(rep["status"], want["status"])
+    sel = np.array(snap.selected("calculator"))
+    assert np.array_equal(sel[rep["node"]], want["node"]) and rep["node"][0] == 1
+    assert st.calls == 3000 and 30 < st.bytes_client_to_server / st.calls < 120
+    # a node that registered only Prime answers "can't find service" to Calculator calls
+    rep, _ = oracle.loopback_run(reqs[:50], k=1, receivers=2)
+    assert np.all(rep["status"] == 4) and np.all(rep["value"] == 0)
+    # optimus chunks over the wire
+    chk = w.optimus_calls(500, t_lo=50, t_hi=400)
+    rep, _ = oracle.loopback_run(chk, k=2, receivers=2)
+    kv2, snap2 = oracle.snapshot_from_spec(w.optimus_registry())
+    want = snap2.dispatch(chk)
+    assert np.array_equal(rep["value"], want["value"]) and np.array_equal(rep["node"], want["node"])
