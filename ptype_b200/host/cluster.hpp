@@ -1,0 +1,632 @@
+// cluster.hpp — C++ mirror of the part of edegens/ptype's `package cluster` that sits on
+// the batched-dispatch path, written against the C ABI only (include/ptype_b200.h).
+//
+// The reference is Go; this image has no Go toolchain, so the host side above the C ABI is
+// mirrored here in C++ with the reference's names, argument meaning and error behaviour:
+//
+//   cluster::Node, cluster::Registry          cluster/registry.go:17-26
+//   cluster::MemRegistry                      stands in for etcdRegistry (registry.go:28-170):
+//                                             same keys, JSON values, range order, watch rule
+//   cluster::ConnConfig, DefaultConnConfig    cluster/rpc.go:19-38
+//   cluster::ErrNoClientAvailable             cluster/rpc.go:15-17
+//   cluster::Dispatcher                       new: owns the ptype_ctx and the whole-registry
+//                                             snapshot image (what Services() returns)
+//   cluster::Client{Call,CallBatch,Close,ConnectionErrs,getSelectedNodes}
+//                                             cluster/rpc.go:40-124,126-297
+//
+// What differs, on purpose: connections are not dialled (connectToNodes, rpc.go:272-285, has
+// no device analogue), and withRetry retries at most cfg.Retries times (the reference loops
+// forever when Retries > 0 and a call keeps failing, rpc.go:107-116).
+#pragma once
+
+#include <algorithm>
+#include <atomic>
+#include <cctype>
+#include <chrono>
+#include <condition_variable>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <functional>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <optional>
+#include <string>
+#include <thread>
+#include <utility>
+#include <vector>
+
+#include "../../include/ptype_b200.h"
+
+namespace cluster {
+
+// ----------------------------------------------------------------------------- errors
+// Go's `error`: empty message = nil.
+struct Error {
+    std::string msg;
+    Error() = default;
+    explicit Error(std::string m) : msg(std::move(m)) {}
+    explicit operator bool() const { return !msg.empty(); }  // true = there IS an error
+    const std::string& Error_() const { return msg; }
+    bool Is(const Error& other) const { return msg == other.msg; }
+};
+inline const Error& ErrNoClientAvailable() {  // cluster/rpc.go:15-17
+    static const Error e("no client nodes available");
+    return e;
+}
+
+// ------------------------------------------------------------------------------- Node
+struct Node {  // cluster/registry.go:23-26
+    std::string Address;
+    int Port = 0;
+    bool operator==(const Node& o) const { return Address == o.Address && Port == o.Port; }
+    bool operator!=(const Node& o) const { return !(*this == o); }
+};
+
+namespace detail {
+
+// json.Marshal(Node) (registry.go:52-53): {"address":"...","port":N}
+inline std::string MarshalNode(const Node& n) {
+    std::string out = "{\"address\":\"";
+    for (unsigned char c : n.Address) {
+        char buf[8];
+        if (c == '"' || c == '\\') {
+            out.push_back('\\');
+            out.push_back(static_cast<char>(c));
+        } else if (c == '\n') {
+            out += "\\n";
+        } else if (c == '\r') {
+            out += "\\r";
+        } else if (c == '\t') {
+            out += "\\t";
+        } else if (c < 0x20 || c == '<' || c == '>' || c == '&') {
+            std::snprintf(buf, sizeof buf, "\\u%04x", c);
+            out += buf;
+        } else {
+            out.push_back(static_cast<char>(c));
+        }
+    }
+    out += "\",\"port\":" + std::to_string(n.Port) + "}";
+    return out;
+}
+
+// json.Unmarshal into an existing Node: absent fields keep their value (registry.go:99,102).
+// Accepts the JSON the reference writes and its tests insert by hand; false = error.
+inline bool UnmarshalNode(const std::string& js, Node* n) {
+    size_t i = 0;
+    auto ws = [&] { while (i < js.size() && (js[i] == ' ' || js[i] == '\t' || js[i] == '\n' || js[i] == '\r')) ++i; };
+    auto str = [&](std::string* out) {
+        if (i >= js.size() || js[i] != '"') return false;
+        ++i;
+        out->clear();
+        while (i < js.size() && js[i] != '"') {
+            char c = js[i++];
+            if (c == '\\') {
+                if (i >= js.size()) return false;
+                char e = js[i++];
+                switch (e) {
+                    case 'n': out->push_back('\n'); break;
+                    case 'r': out->push_back('\r'); break;
+                    case 't': out->push_back('\t'); break;
+                    case 'b': out->push_back('\b'); break;
+                    case 'f': out->push_back('\f'); break;
+                    case 'u': {
+                        if (i + 4 > js.size()) return false;
+                        unsigned cp = static_cast<unsigned>(std::stoul(js.substr(i, 4), nullptr, 16));
+                        i += 4;
+                        if (cp < 0x80) {
+                            out->push_back(static_cast<char>(cp));
+                        } else if (cp < 0x800) {
+                            out->push_back(static_cast<char>(0xC0 | (cp >> 6)));
+                            out->push_back(static_cast<char>(0x80 | (cp & 0x3F)));
+                        } else {
+                            out->push_back(static_cast<char>(0xE0 | (cp >> 12)));
+                            out->push_back(static_cast<char>(0x80 | ((cp >> 6) & 0x3F)));
+                            out->push_back(static_cast<char>(0x80 | (cp & 0x3F)));
+                        }
+                        break;
+                    }
+                    default: out->push_back(e);
+                }
+            } else {
+                out->push_back(c);
+            }
+        }
+        if (i >= js.size()) return false;
+        ++i;
+        return true;
+    };
+    ws();
+    if (i >= js.size() || js[i] != '{') return false;
+    ++i;
+    ws();
+    if (i < js.size() && js[i] == '}') return true;
+    for (;;) {
+        std::string key;
+        ws();
+        if (!str(&key)) return false;
+        for (char& c : key) c = static_cast<char>(std::tolower(static_cast<unsigned char>(c)));
+        ws();
+        if (i >= js.size() || js[i] != ':') return false;
+        ++i;
+        ws();
+        if (key == "address") {
+            std::string v;
+            if (!str(&v)) return false;
+            n->Address = v;
+        } else if (key == "port") {
+            size_t j = i;
+            if (j < js.size() && js[j] == '-') ++j;
+            size_t d0 = j;
+            while (j < js.size() && js[j] >= '0' && js[j] <= '9') ++j;
+            if (j == d0 || (j < js.size() && (js[j] == '.' || js[j] == 'e' || js[j] == 'E'))) return false;
+            n->Port = std::stoi(js.substr(i, j - i));
+            i = j;
+        } else {  // unknown field: skip a scalar or string
+            if (i < js.size() && js[i] == '"') {
+                std::string skip;
+                if (!str(&skip)) return false;
+            } else {
+                while (i < js.size() && js[i] != ',' && js[i] != '}') ++i;
+            }
+        }
+        ws();
+        if (i < js.size() && js[i] == ',') {
+            ++i;
+            continue;
+        }
+        if (i < js.size() && js[i] == '}') return true;
+        return false;
+    }
+}
+
+// etcdKey (registry.go:168-170) for names without '/', '.' or '..' elements.
+inline std::string EtcdKey(std::initializer_list<std::string> elems) {
+    std::string k;
+    for (const std::string& e : elems) {
+        if (e.empty()) continue;
+        if (!k.empty()) k.push_back('/');
+        k += e;
+    }
+    return k + "/";
+}
+
+}  // namespace detail
+
+// ---------------------------------------------------------------------------- channels
+// `chan []Node` of WatchService: blocking receive with timeout, close by the sender.
+class NodeChan {
+   public:
+    void Send(std::vector<Node> v) {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (closed_) return;
+        q_.push_back(std::move(v));
+        cv_.notify_all();
+    }
+    void Close() {
+        std::lock_guard<std::mutex> lk(mu_);
+        closed_ = true;
+        cv_.notify_all();
+    }
+    // nullopt on timeout; ok=false once closed and drained (Go: v, ok := <-ch)
+    std::optional<std::vector<Node>> Recv(std::chrono::milliseconds timeout, bool* ok) {
+        std::unique_lock<std::mutex> lk(mu_);
+        *ok = true;
+        if (!cv_.wait_for(lk, timeout, [&] { return !q_.empty() || closed_; })) return std::nullopt;
+        if (q_.empty()) {
+            *ok = false;
+            return std::nullopt;
+        }
+        std::vector<Node> v = std::move(q_.front());
+        q_.pop_front();
+        return v;
+    }
+
+   private:
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::deque<std::vector<Node>> q_;
+    bool closed_ = false;
+};
+
+// ---------------------------------------------------------------------------- Registry
+class Registry {  // cluster/registry.go:17-21
+   public:
+    virtual ~Registry() = default;
+    virtual Error Register(const std::string& serviceName, const std::string& nodeName,
+                           const std::string& host, int port) = 0;
+    virtual Error Services(std::map<std::string, std::vector<Node>>* out) = 0;
+    // Sends the current list first, then the full list after every change under the
+    // service's prefix (registry.go:119-150); Cancel closes the channel.
+    virtual std::shared_ptr<NodeChan> WatchService(const std::string& serviceName) = 0;
+    virtual void CancelWatch(const std::shared_ptr<NodeChan>& ch) = 0;
+};
+
+// In-memory stand-in for etcdRegistry: an ordered KV with the reference's key layout.
+class MemRegistry : public Registry {
+   public:
+    Error Register(const std::string& serviceName, const std::string& nodeName, const std::string& host,
+                   int port) override {  // registry.go:51-86 (lease/keep-alive: no stored effect)
+        Put(detail::EtcdKey({"services", serviceName, nodeName}), detail::MarshalNode(Node{host, port}));
+        return Error();
+    }
+    void Put(const std::string& key, const std::string& value) {
+        std::vector<std::pair<std::shared_ptr<NodeChan>, std::vector<Node>>> notify;
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            kv_[key] = value;
+            CollectLocked(key, &notify);
+        }
+        for (auto& n : notify) n.first->Send(std::move(n.second));
+    }
+    int Delete(const std::string& key) {
+        std::vector<std::pair<std::shared_ptr<NodeChan>, std::vector<Node>>> notify;
+        int deleted;
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            deleted = static_cast<int>(kv_.erase(key));
+            if (deleted) CollectLocked(key, &notify);
+        }
+        for (auto& n : notify) n.first->Send(std::move(n.second));
+        return deleted;
+    }
+    // registry.go:93-117: ONE range over the prefix "services", ONE reused Node variable.
+    Error Services(std::map<std::string, std::vector<Node>>* out) override {
+        std::lock_guard<std::mutex> lk(mu_);
+        out->clear();
+        Node node;
+        for (auto it = kv_.lower_bound("services"); it != kv_.end() && it->first.compare(0, 8, "services") == 0; ++it) {
+            if (!detail::UnmarshalNode(it->second, &node)) return Error("failed to unmarshal services nodes");
+            size_t s1 = it->first.find('/');
+            if (s1 == std::string::npos) continue;
+            size_t s2 = it->first.find('/', s1 + 1);
+            (*out)[it->first.substr(s1 + 1, s2 == std::string::npos ? std::string::npos : s2 - s1 - 1)].push_back(node);
+        }
+        return Error();
+    }
+    // registry.go:152-166
+    Error nodes(const std::string& serviceName, std::vector<Node>* out) {
+        std::lock_guard<std::mutex> lk(mu_);
+        return NodesLocked(serviceName, out);
+    }
+    std::shared_ptr<NodeChan> WatchService(const std::string& serviceName) override {
+        auto ch = std::make_shared<NodeChan>();
+        std::vector<Node> now;
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            NodesLocked(serviceName, &now);
+            watchers_.push_back({serviceName, ch});
+        }
+        ch->Send(std::move(now));
+        return ch;
+    }
+    void CancelWatch(const std::shared_ptr<NodeChan>& ch) override {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            for (auto it = watchers_.begin(); it != watchers_.end();)
+                it = it->second == ch ? watchers_.erase(it) : it + 1;
+        }
+        ch->Close();
+    }
+
+   private:
+    Error NodesLocked(const std::string& serviceName, std::vector<Node>* out) {
+        const std::string prefix = detail::EtcdKey({"services", serviceName});  // trailing '/' matters
+        out->clear();
+        for (auto it = kv_.lower_bound(prefix); it != kv_.end() && it->first.compare(0, prefix.size(), prefix) == 0; ++it) {
+            Node n;
+            if (!detail::UnmarshalNode(it->second, &n)) return Error("failed to unmarshal services nodes");
+            out->push_back(n);
+        }
+        return Error();
+    }
+    void CollectLocked(const std::string& key, std::vector<std::pair<std::shared_ptr<NodeChan>, std::vector<Node>>>* notify) {
+        for (auto& w : watchers_) {
+            const std::string prefix = detail::EtcdKey({"services", w.first});
+            if (key.compare(0, prefix.size(), prefix) != 0) continue;
+            std::vector<Node> now;
+            NodesLocked(w.first, &now);
+            notify->push_back({w.second, std::move(now)});
+        }
+    }
+    std::mutex mu_;
+    std::map<std::string, std::string> kv_;  // byte-ordered like the etcd range
+    std::vector<std::pair<std::string, std::shared_ptr<NodeChan>>> watchers_;
+};
+
+// -------------------------------------------------------------------------- ConnConfig
+struct ConnConfig {  // cluster/rpc.go:19-31
+    int MaxConnections = 3;
+    std::chrono::milliseconds InitialNodeTimeout{5000};
+    std::chrono::milliseconds DebounceTime{3000};
+    int Retries = 2;
+};
+inline const ConnConfig& DefaultConnConfig() {  // cluster/rpc.go:33-38
+    static const ConnConfig c;
+    return c;
+}
+
+// -------------------------------------------------------------------------- Dispatcher
+// Owns the device context and the registry snapshot shared by every Client of this host:
+// per service, the last node list its Client accepted.  Rebuilding and publishing the
+// image is the device form of handleNewNodes' swap (rpc.go:226-244).
+class Dispatcher {
+   public:
+    Dispatcher(std::string localAddr, int maxConnections, int device = 0)
+        : localAddr_(std::move(localAddr)), maxConnections_(maxConnections) {
+        int rc = ptype_b200_open(&device, 1, &ctx_);
+        if (rc != PTYPE_OK) err_ = Error(std::string("ptype_b200_open: ") + ptype_b200_strerror(rc) + ": " + ptype_b200_last_error());
+    }
+    ~Dispatcher() {
+        if (ctx_) ptype_b200_close(ctx_);
+        if (image_) ptype_b200_image_free(image_);
+    }
+    Dispatcher(const Dispatcher&) = delete;
+    Dispatcher& operator=(const Dispatcher&) = delete;
+    const Error& Err() const { return err_; }
+    ptype_ctx* ctx() { return ctx_; }
+    int MaxConnections() const { return maxConnections_; }
+
+    // rpc.Register(new(T)) on the nodes of a service (server.go:16-17).
+    void Expose(const std::string& service, const std::string& receiver) {
+        std::lock_guard<std::mutex> lk(mu_);
+        exposed_[service].push_back(receiver);
+    }
+    // Install `nodes` as the service's list and publish a new epoch.
+    Error SetNodes(const std::string& service, const std::vector<Node>& nodes) {
+        std::lock_guard<std::mutex> lk(mu_);
+        lists_[service] = nodes;
+        return PublishLocked();
+    }
+    uint64_t ServiceKey(const std::string& service) {
+        std::lock_guard<std::mutex> lk(mu_);
+        return ptype_b200_service_key(service.c_str(), salt_);
+    }
+    // getSelectedNodes() (rpc.go:293-297)
+    std::vector<Node> SelectedNodes(const std::string& service) {
+        std::lock_guard<std::mutex> lk(mu_);
+        std::vector<Node> out;
+        if (!image_) return out;
+        uint32_t k = 0;
+        std::vector<uint32_t> ids(4096);
+        if (ptype_b200_image_selected(image_, service.c_str(), ids.data(), ids.size(), &k) != PTYPE_OK) return out;
+        if (k > ids.size()) {
+            ids.resize(k);
+            ptype_b200_image_selected(image_, service.c_str(), ids.data(), ids.size(), &k);
+        }
+        for (uint32_t i = 0; i < k; ++i) out.push_back(NodeOfLocked(ids[i]));
+        return out;
+    }
+    Node NodeOf(uint32_t id) {
+        std::lock_guard<std::mutex> lk(mu_);
+        return NodeOfLocked(id);
+    }
+    uint64_t Epoch() {
+        std::lock_guard<std::mutex> lk(mu_);
+        return epoch_;
+    }
+
+   private:
+    Node NodeOfLocked(uint32_t id) {
+        char addr[256];
+        int port = 0;
+        Node n;
+        if (image_ && ptype_b200_image_node(image_, id, addr, sizeof addr, &port, nullptr, 0, nullptr, 0) == PTYPE_OK) {
+            n.Address = addr;
+            n.Port = port;
+        }
+        return n;
+    }
+    Error PublishLocked() {
+        ptype_builder* b = nullptr;
+        int rc = ptype_b200_builder_new(localAddr_.c_str(), maxConnections_, &b);
+        if (rc != PTYPE_OK) return Error(std::string("builder_new: ") + ptype_b200_strerror(rc));
+        for (const auto& kv : lists_) {
+            ptype_b200_builder_declare(b, kv.first.c_str());
+            char name[32];
+            for (size_t i = 0; i < kv.second.size(); ++i) {
+                std::snprintf(name, sizeof name, "%08zu", i);  // keeps the watch's order under byte sort
+                rc = ptype_b200_builder_register(b, kv.first.c_str(), name, kv.second[i].Address.c_str(), kv.second[i].Port);
+                if (rc != PTYPE_OK) break;
+            }
+            auto ex = exposed_.find(kv.first);
+            if (ex != exposed_.end())
+                for (const std::string& r : ex->second) ptype_b200_builder_expose(b, kv.first.c_str(), r.c_str());
+        }
+        void* blob = nullptr;
+        size_t bytes = 0;
+        if (rc == PTYPE_OK) rc = ptype_b200_builder_finish(b, epoch_ + 1, &blob, &bytes);
+        ptype_b200_builder_free(b);
+        if (rc != PTYPE_OK) return Error(std::string("image build: ") + ptype_b200_strerror(rc));
+        rc = ptype_b200_publish_image(ctx_, blob, bytes);
+        if (rc != PTYPE_OK) {
+            ptype_b200_image_free(blob);
+            return Error(std::string("publish_image: ") + ptype_b200_strerror(rc) + ": " + ptype_b200_last_error());
+        }
+        if (image_) ptype_b200_image_free(image_);
+        image_ = blob;
+        ++epoch_;
+        salt_ = static_cast<const ptype_image_header*>(blob)->key_salt;
+        return Error();
+    }
+    std::string localAddr_;
+    int maxConnections_;
+    ptype_ctx* ctx_ = nullptr;
+    Error err_;
+    std::mutex mu_;
+    std::map<std::string, std::vector<Node>> lists_;
+    std::map<std::string, std::vector<std::string>> exposed_;
+    void* image_ = nullptr;
+    uint64_t epoch_ = 0, salt_ = 0;
+};
+
+// ------------------------------------------------------------------------------ Client
+struct BatchReply {  // mirrors ptype_reply
+    int64_t Value = 0;
+    uint32_t NodeId = PTYPE_NO_NODE;
+    uint32_t Status = 0;
+};
+
+// What Client.Call would have returned for a per-call status.
+inline Error StatusError(uint32_t status, const std::string& serviceMethod) {
+    switch (status) {
+        case PTYPE_ST_OK: return Error();
+        case PTYPE_ST_NO_SERVICE:
+        case PTYPE_ST_NO_CLIENT: return ErrNoClientAvailable();                                     // rpc.go:62-64
+        case PTYPE_ST_ILL_FORMED: return Error("rpc: service/method request ill-formed: " + serviceMethod);  // [net/rpc]
+        case PTYPE_ST_CANT_FIND_SERVICE: return Error("rpc: can't find service " + serviceMethod);
+        case PTYPE_ST_CANT_FIND_METHOD: return Error("rpc: can't find method " + serviceMethod);
+        case PTYPE_ST_BAD_INDEX: return Error("runtime error: index out of range");
+        case PTYPE_ST_RANGE_LIMIT: return Error("ptype_b200: Prime.Check range beyond the dispatch limit");
+        default: return Error("ptype_b200: unknown status");
+    }
+}
+
+class Client {  // cluster/rpc.go:40-43,126-139
+   public:
+    // newClient + newConnectionBalancer (rpc.go:45-57,141-170): waits InitialNodeTimeout for the
+    // first list ("no initial nodes provided for <svc>"), applies it, then watches with debounce.
+    static Error New(Dispatcher* gpu, const std::string& serviceName, Registry* r, const ConnConfig* cfg,
+                     std::unique_ptr<Client>* out) {
+        std::unique_ptr<Client> c(new Client(gpu, serviceName, r, cfg ? *cfg : DefaultConnConfig()));
+        if (c->cfg_.MaxConnections != gpu->MaxConnections())
+            return Error("ptype_b200: ConnConfig.MaxConnections must equal the Dispatcher's (one selection rule per image)");
+        c->nodesChan_ = r->WatchService(serviceName);
+        bool ok = true;
+        auto initial = c->nodesChan_->Recv(c->cfg_.InitialNodeTimeout, &ok);
+        if (!initial) {
+            r->CancelWatch(c->nodesChan_);
+            return Error("no initial nodes provided for " + serviceName);  // rpc.go:159
+        }
+        if (Error e = c->handleNewNodes(*initial)) {
+            r->CancelWatch(c->nodesChan_);
+            return e;
+        }
+        c->watcher_ = std::thread([p = c.get()] { p->watchForNewNodes(); });
+        *out = std::move(c);
+        return Error();
+    }
+    ~Client() { Close(); }
+
+    // rpc.go:59-67.  args = calculator.Args{A,B} or prime.Args{Min,Max,Target}.
+    Error Call(const std::string& serviceMethod, const int64_t (&args)[3], int64_t* reply) {
+        BatchReply rep;
+        Error e = CallBatch(serviceMethod, &args, 1, &rep);
+        if (e) return e;
+        if (Error se = StatusError(rep.Status, serviceMethod)) return se;  // reply untouched on error
+        *reply = rep.Value;
+        return Error();
+    }
+
+    // N calls routed exactly as N sequential Call()s: the sequence range is reserved with ONE
+    // atomic add (rpc.go:181 batched).  Per-call outcomes are in replies[j].Status; calls that
+    // failed are re-issued with fresh sequence numbers up to cfg.Retries more times (withRetry,
+    // rpc.go:107-116, bounded — see the header comment).
+    Error CallBatch(const std::string& serviceMethod, const int64_t (*args)[3], size_t n, BatchReply* replies) {
+        if (n == 0) return Error();
+        uint32_t method = 0, recv = 0;
+        ptype_b200_method_key(serviceMethod.c_str(), &method, &recv);
+        const uint64_t key = gpu_->ServiceKey(service_);
+        std::vector<ptype_req> reqs(n);
+        std::vector<ptype_reply> out(n);
+        std::vector<uint32_t> todo(n);
+        for (size_t j = 0; j < n; ++j) todo[j] = static_cast<uint32_t>(j);
+        for (int attempt = 0;; ++attempt) {
+            const uint64_t m = todo.size();
+            const uint64_t base = seq_.fetch_add(m) ;  // value before the add; first call sees base+1
+            for (uint64_t t = 0; t < m; ++t) {
+                const size_t j = todo[t];
+                reqs[t] = ptype_req{key, base + 1 + t, method, recv, args[j][0], args[j][1], args[j][2]};
+            }
+            std::vector<uint32_t> failed(m);
+            ptype_batch_stats stats;
+            int rc = ptype_b200_dispatch_ex(gpu_->ctx(), 0, reqs.data(), m, out.data(), failed.data(), m, &stats, 0);
+            if (rc != PTYPE_OK)
+                return Error(std::string("ptype_b200_dispatch: ") + ptype_b200_strerror(rc) + ": " + ptype_b200_last_error());
+            for (uint64_t t = 0; t < m; ++t) {
+                const size_t j = todo[t];
+                replies[j].Value = out[t].value;
+                replies[j].NodeId = out[t].node;
+                replies[j].Status = out[t].status;
+            }
+            if (stats.failed_count == 0 || attempt >= cfg_.Retries) return Error();
+            std::vector<uint32_t> next;
+            next.reserve(stats.failed_count);
+            for (uint64_t f = 0; f < stats.failed_count; ++f) next.push_back(todo[failed[f]]);
+            std::sort(next.begin(), next.end());
+            todo.swap(next);
+        }
+    }
+
+    std::vector<Node> getSelectedNodes() { return gpu_->SelectedNodes(service_); }  // rpc.go:293-297
+    // Background update failures (rpc.go:122-124,213-218): at most one pending, like chan error, 1.
+    std::optional<Error> ConnectionErrs() {
+        std::lock_guard<std::mutex> lk(errMu_);
+        std::optional<Error> e = pendingErr_;
+        pendingErr_.reset();
+        return e;
+    }
+    // Number of updates applied so far (the tests' <-c.connsUpdated).
+    uint64_t ConnsUpdated() const { return connsUpdated_.load(); }
+    bool WaitConnsUpdated(uint64_t target, std::chrono::milliseconds timeout) {
+        auto end = std::chrono::steady_clock::now() + timeout;
+        while (connsUpdated_.load() < target) {
+            if (std::chrono::steady_clock::now() > end) return false;
+            std::this_thread::sleep_for(std::chrono::milliseconds(5));
+        }
+        return true;
+    }
+    Error Close() {  // rpc.go:118-120,185-195
+        if (closed_.exchange(true)) return Error();
+        if (nodesChan_) registry_->CancelWatch(nodesChan_);
+        if (watcher_.joinable()) watcher_.join();
+        return Error();
+    }
+
+   private:
+    Client(Dispatcher* gpu, std::string service, Registry* r, ConnConfig cfg)
+        : gpu_(gpu), service_(std::move(service)), registry_(r), cfg_(cfg) {}
+
+    // rpc.go:226-244: selectNodes happens inside the image; the swap is the publish.
+    Error handleNewNodes(const std::vector<Node>& nodes) {
+        if (Error e = gpu_->SetNodes(service_, nodes)) return e;
+        connsUpdated_.fetch_add(1);
+        return Error();
+    }
+    // rpc.go:197-224: keep only the latest non-empty list, apply it after DebounceTime of quiet.
+    void watchForNewNodes() {
+        std::optional<std::vector<Node>> newNodes;
+        for (;;) {
+            bool ok = true;
+            auto got = nodesChan_->Recv(cfg_.DebounceTime, &ok);
+            if (!ok) return;  // ctx.Done()
+            if (got) {
+                if (got->empty()) continue;  // rpc.go:204-206
+                newNodes = std::move(got);
+                continue;
+            }
+            if (!newNodes) continue;  // debounce timer fired with nothing pending
+            if (Error e = handleNewNodes(*newNodes)) {
+                std::lock_guard<std::mutex> lk(errMu_);
+                if (!pendingErr_) pendingErr_ = e;
+            }
+            newNodes.reset();
+        }
+    }
+
+    Dispatcher* gpu_;
+    std::string service_;
+    Registry* registry_;
+    ConnConfig cfg_;
+    std::atomic<uint64_t> seq_{0};  // connectionBalancer.seq (rpc.go:129)
+    std::shared_ptr<NodeChan> nodesChan_;
+    std::thread watcher_;
+    std::atomic<bool> closed_{false};
+    std::atomic<uint64_t> connsUpdated_{0};
+    std::mutex errMu_;
+    std::optional<Error> pendingErr_;
+};
+
+}  // namespace cluster

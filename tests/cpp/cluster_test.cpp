@@ -1,0 +1,314 @@
+// cluster_test.cpp — the reference's own tests for the dispatch path, re-stated against the
+// C++ mirror (ptype_b200/host/cluster.hpp).  Each test names the Go test it follows.
+//   ./cluster_test cpu   registry tests (no GPU)
+//   ./cluster_test gpu   + client / balancer tests through the C ABI on cuda:0
+#include <cstdio>
+#include <cstdlib>
+#include <set>
+
+#include "../../ptype_b200/host/cluster.hpp"
+
+using namespace cluster;
+using namespace std::chrono_literals;
+
+static int g_fail = 0, g_run = 0;
+#define REQUIRE(cond)                                                    \
+    do {                                                                 \
+        if (!(cond)) {                                                   \
+            std::printf("  FAIL %s:%d: %s\n", __FILE__, __LINE__, #cond); \
+            ++g_fail;                                                    \
+            return;                                                      \
+        }                                                                \
+    } while (0)
+#define RUN(fn)                       \
+    do {                              \
+        std::printf("%s\n", #fn);     \
+        ++g_run;                      \
+        fn();                         \
+    } while (0)
+
+// mockRegistry (cluster/rpc_test.go:16-40): WatchService hands out a channel the test feeds.
+struct MockRegistry : Registry {
+    std::shared_ptr<NodeChan> nodeChan = std::make_shared<NodeChan>();
+    bool sendInitial = false;
+    std::vector<Node> initial;
+    explicit MockRegistry(std::vector<Node> init) : sendInitial(true), initial(std::move(init)) {}
+    MockRegistry() = default;
+    Error Register(const std::string&, const std::string&, const std::string&, int) override { return Error(); }
+    Error Services(std::map<std::string, std::vector<Node>>* out) override {
+        out->clear();
+        return Error();
+    }
+    std::shared_ptr<NodeChan> WatchService(const std::string&) override {
+        if (sendInitial) nodeChan->Send(initial);
+        return nodeChan;
+    }
+    void CancelWatch(const std::shared_ptr<NodeChan>& ch) override { ch->Close(); }
+};
+
+static ConnConfig testConnConfig() {  // rpc_test.go:79-83 (note Retries == 0 there)
+    ConnConfig c;
+    c.MaxConnections = DefaultConnConfig().MaxConnections;
+    c.InitialNodeTimeout = 300ms;
+    c.DebounceTime = 150ms;
+    c.Retries = 0;
+    return c;
+}
+
+// ------------------------------------------------------------------ registry (CPU)
+
+// TestEtcdRegistry_Register (registry_test.go:41-87)
+static void TestRegistry_Register() {
+    MemRegistry sr;
+    REQUIRE(!sr.Register("foo", "node1", "host", 8000));
+    REQUIRE(!sr.Register("foo", "node2", "host2", 8000));
+    REQUIRE(!sr.Register("bar", "node3", "host3", 3000));
+    std::vector<Node> n;
+    REQUIRE(!sr.nodes("foo", &n));
+    REQUIRE((n == std::vector<Node>{{"host", 8000}, {"host2", 8000}}));
+    REQUIRE(!sr.nodes("bar", &n));
+    REQUIRE((n == std::vector<Node>{{"host3", 3000}}));
+    REQUIRE(detail::MarshalNode(Node{"host", 8000}) == "{\"address\":\"host\",\"port\":8000}");
+}
+
+// TestEtcdRegistry_Services (registry_test.go:90-122)
+static void TestRegistry_Services() {
+    MemRegistry sr;
+    sr.Put("services/foo/node1/", "{\"address\":\"host\", \"port\":8000}");
+    sr.Put("services/foo/node2/", "{\"address\":\"host2\", \"port\":8000}");
+    sr.Put("services/bar/node3/", "{\"address\":\"host3\", \"port\":3000}");
+    std::map<std::string, std::vector<Node>> got;
+    REQUIRE(!sr.Services(&got));
+    REQUIRE(got.size() == 2);
+    REQUIRE((got["foo"] == std::vector<Node>{{"host", 8000}, {"host2", 8000}}));
+    REQUIRE((got["bar"] == std::vector<Node>{{"host3", 3000}}));
+}
+
+// TestEtcdRegistry_WatchService (registry_test.go:149-192)
+static void TestRegistry_WatchService() {
+    MemRegistry sr;
+    sr.Put("services/foo/node1/", "{\"address\":\"host\", \"port\":8000}");
+    auto ch = sr.WatchService("foo");
+    bool ok;
+    auto v = ch->Recv(1s, &ok);
+    REQUIRE(v && (*v == std::vector<Node>{{"host", 8000}}));
+    sr.Put("services/foo/node3/", "{\"address\":\"host3\", \"port\":3000}");
+    v = ch->Recv(1s, &ok);
+    REQUIRE(v && (*v == std::vector<Node>{{"host", 8000}, {"host3", 3000}}));
+    REQUIRE(sr.Delete("services/foo/node1/") == 1);
+    v = ch->Recv(1s, &ok);
+    REQUIRE(v && (*v == std::vector<Node>{{"host3", 3000}}));
+    // ..._stops_with_context_cancel (registry_test.go:194-207)
+    sr.CancelWatch(ch);
+    v = ch->Recv(1s, &ok);
+    REQUIRE(!v && !ok);
+}
+
+// TestEtcdRegistry_nodes (registry_test.go:209-236)
+static void TestRegistry_nodes_prefix_case() {
+    MemRegistry sr;
+    sr.Put("services/foo/node1/", "{\"address\":\"host\", \"port\":8000}");
+    sr.Put("services/foo/node2/", "{\"address\":\"host2\", \"port\":8000}");
+    sr.Put("services/foo_broken_prefix_case/node3/", "{\"address\":\"host3\", \"port\":3000}");
+    std::vector<Node> n;
+    REQUIRE(!sr.nodes("foo", &n));
+    REQUIRE((n == std::vector<Node>{{"host", 8000}, {"host2", 8000}}));
+}
+
+// ------------------------------------------------------------- client / balancer (GPU)
+
+static std::vector<Node> fakeNodes(int n, int base = 40000) {
+    std::vector<Node> v;
+    for (int i = 0; i < n; ++i) v.push_back(Node{"127.0.0.1", base + i});
+    return v;
+}
+
+// TestClient_default_conn_config (rpc_test.go:85-90): an empty initial list is accepted,
+// and a later Call yields ErrNoClientAvailable (rpc.go:62-64,178-180)
+static void TestClient_default_conn_config() {
+    Dispatcher gpu("", DefaultConnConfig().MaxConnections);
+    REQUIRE(!gpu.Err());
+    MockRegistry mock{std::vector<Node>{}};
+    std::unique_ptr<Client> c;
+    ConnConfig fast = DefaultConnConfig();
+    fast.Retries = 0;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &fast, &c));
+    int64_t reply = 123;
+    const int64_t args[3] = {7, 8, 0};
+    Error e = c->Call("Calculator.Multiply", args, &reply);
+    REQUIRE(e.Is(ErrNoClientAvailable()));
+    REQUIRE(reply == 123);
+}
+
+// TestClient_Call (rpc_test.go:92-116) with the calculator example's method (client.go:38-44)
+static void TestClient_Call() {
+    Dispatcher gpu("", 3);
+    gpu.Expose("foo", "Calculator");
+    MockRegistry mock{fakeNodes(1)};
+    ConnConfig cfg = testConnConfig();
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c));
+    int64_t reply = 0;
+    const int64_t args[3] = {7, 8, 0};
+    REQUIRE(!c->Call("Calculator.Multiply", args, &reply));
+    REQUIRE(reply == 56);
+    Error e = c->Call("Calculator.Divide", args, &reply);
+    REQUIRE(e.msg == "rpc: can't find method Calculator.Divide" && reply == 56);
+    e = c->Call("Prime.Check", args, &reply);
+    REQUIRE(e.msg == "rpc: can't find service Prime.Check");
+    e = c->Call("nodot", args, &reply);
+    REQUIRE(e.msg == "rpc: service/method request ill-formed: nodot");
+}
+
+// TestClient_Call_with_retry_multi_node (rpc_test.go:118-158): with 2 nodes the FIRST attempt
+// goes to index 1 (AddUint64 returns the new value)
+static void TestClient_first_call_goes_to_index_1() {
+    Dispatcher gpu("", 3);
+    gpu.Expose("foo", "Calculator");
+    MockRegistry mock{fakeNodes(2)};
+    ConnConfig cfg = testConnConfig();
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c));
+    BatchReply rep[4];
+    const int64_t args[4][3] = {{1, 1, 0}, {2, 2, 0}, {3, 3, 0}, {4, 4, 0}};
+    REQUIRE(!c->CallBatch("Calculator.Add", args, 4, rep));
+    auto sel = c->getSelectedNodes();
+    REQUIRE(sel.size() == 2);
+    REQUIRE(gpu.NodeOf(rep[0].NodeId) == sel[1]);
+    REQUIRE(gpu.NodeOf(rep[1].NodeId) == sel[0]);
+    REQUIRE(gpu.NodeOf(rep[2].NodeId) == sel[1]);
+    REQUIRE(rep[3].Value == 8);
+}
+
+// TestNewConnectionBalancer_with_no_available_server (rpc_test.go:307-314)
+static void TestNewClient_with_no_available_server() {
+    Dispatcher gpu("", 3);
+    MockRegistry mock;  // never sends
+    ConnConfig cfg = testConnConfig();
+    std::unique_ptr<Client> c;
+    Error e = Client::New(&gpu, "foo", &mock, &cfg, &c);
+    REQUIRE(e.msg == "no initial nodes provided for foo");
+    REQUIRE(!c);
+}
+
+// TestConnectionBalancer_watchForNewNodes (rpc_test.go:323-388)
+static void TestBalancer_watchForNewNodes() {
+    Dispatcher gpu("", 3);
+    auto n = fakeNodes(4);
+    Node node = n[0], node2 = n[1], node3 = n[2], node4 = n[3];
+    MockRegistry mock{std::vector<Node>{node}};
+    ConnConfig cfg = testConnConfig();
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c));
+    REQUIRE((c->getSelectedNodes() == std::vector<Node>{node}));
+    // more than max connections of nodes get sent -> [node4, node, node2]
+    mock.nodeChan->Send({node, node2, node3, node4});
+    REQUIRE(c->WaitConnsUpdated(2, 3s));
+    REQUIRE((c->getSelectedNodes() == std::vector<Node>{node4, node, node2}));
+    // connected node is removed -> identity
+    mock.nodeChan->Send({node, node3, node4});
+    REQUIRE(c->WaitConnsUpdated(3, 3s));
+    REQUIRE((c->getSelectedNodes() == std::vector<Node>{node, node3, node4}));
+    // debounce: only the last of a burst is applied, once; empty lists are ignored
+    mock.nodeChan->Send({node});
+    mock.nodeChan->Send({node2});
+    mock.nodeChan->Send({});
+    mock.nodeChan->Send({node3});
+    mock.nodeChan->Send({node, node2, node3});
+    REQUIRE(c->WaitConnsUpdated(4, 3s));
+    REQUIRE((c->getSelectedNodes() == std::vector<Node>{node, node2, node3}));
+    std::this_thread::sleep_for(400ms);
+    REQUIRE(c->ConnsUpdated() == 4);
+    REQUIRE(!c->ConnectionErrs());
+}
+
+// TestConnectionBalancer_roundRobinSelect (rpc_test.go:390-425): n consecutive selections are
+// n distinct clients, and the sequence wraps
+static void TestBalancer_roundRobinSelect() {
+    Dispatcher gpu("", 0);  // mesh: all 100 nodes selected
+    gpu.Expose("foo", "Calculator");
+    MockRegistry mock{fakeNodes(100)};
+    ConnConfig cfg = testConnConfig();
+    cfg.MaxConnections = 0;
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c));
+    std::vector<BatchReply> rep(200);
+    std::vector<std::array<int64_t, 3>> args(200, std::array<int64_t, 3>{1, 2, 0});
+    REQUIRE(!c->CallBatch("Calculator.Add", reinterpret_cast<const int64_t(*)[3]>(args.data()), 200, rep.data()));
+    std::set<uint32_t> first, second;
+    for (int i = 0; i < 100; ++i) first.insert(rep[i].NodeId);
+    for (int i = 100; i < 200; ++i) second.insert(rep[i].NodeId);
+    REQUIRE(first.size() == 100 && second.size() == 100);
+    for (int i = 0; i < 100; ++i) REQUIRE(rep[i].NodeId == rep[i + 100].NodeId);
+    for (auto& r : rep) REQUIRE(r.Status == 0 && r.Value == 3);
+}
+
+// TestConnectionBalancer_mesh_network (rpc_test.go:427-476)
+static void TestBalancer_mesh_network() {
+    Dispatcher gpu("", 0);
+    auto n = fakeNodes(4);
+    MockRegistry mock{std::vector<Node>{n[0], n[1]}};
+    ConnConfig cfg = testConnConfig();
+    cfg.MaxConnections = 0;
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c));
+    REQUIRE((c->getSelectedNodes() == std::vector<Node>{n[0], n[1]}));
+    mock.nodeChan->Send({n[0], n[1], n[2]});
+    REQUIRE(c->WaitConnsUpdated(2, 3s));
+    REQUIRE((c->getSelectedNodes() == std::vector<Node>{n[0], n[1], n[2]}));
+    mock.nodeChan->Send({n[0], n[1], n[2], n[3]});
+    REQUIRE(c->WaitConnsUpdated(3, 3s));
+    REQUIRE((c->getSelectedNodes() == n));
+}
+
+// Registry -> Client end to end with the in-memory registry: the calculator example
+// (server.go:16-38 registers, client.go:33-44 calls), then a node leaves and calls re-route.
+static void TestExample_calculator_with_registry() {
+    MemRegistry reg;
+    for (int i = 1; i <= 16; ++i) {
+        char name[32], addr[32];
+        std::snprintf(name, sizeof name, "calculator_node_%02d", i);
+        std::snprintf(addr, sizeof addr, "10.0.0.%d", i);
+        REQUIRE(!reg.Register("calculator", name, addr, 31234));
+    }
+    Dispatcher gpu("10.0.0.5", 3);
+    gpu.Expose("calculator", "Calculator");
+    ConnConfig cfg = testConnConfig();
+    cfg.Retries = 2;
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "calculator", &reg, &cfg, &c));
+    // derived known answer: localAddr 10.0.0.5, 16 nodes, max 3 -> [3,0,9]
+    auto sel = c->getSelectedNodes();
+    REQUIRE((sel == std::vector<Node>{{"10.0.0.4", 31234}, {"10.0.0.1", 31234}, {"10.0.0.10", 31234}}));
+    int64_t reply = 0;
+    const int64_t args[3] = {7, 8, 0};
+    REQUIRE(!c->Call("Calculator.Multiply", args, &reply));
+    REQUIRE(reply == 56);
+    const int64_t wrap[3] = {INT64_C(3037000500), INT64_C(3037000500), 0};
+    REQUIRE(!c->Call("Calculator.Multiply", wrap, &reply));
+    REQUIRE(reply == INT64_C(-9223372036709301616));
+    REQUIRE(reg.Delete("services/calculator/calculator_node_04/") == 1);
+    REQUIRE(c->WaitConnsUpdated(2, 3s));
+    sel = c->getSelectedNodes();
+    REQUIRE(sel.size() == 3 && sel[0] != Node({"10.0.0.4", 31234}));
+}
+
+int main(int argc, char** argv) {
+    const bool gpu = argc > 1 && std::string(argv[1]) == "gpu";
+    RUN(TestRegistry_Register);
+    RUN(TestRegistry_Services);
+    RUN(TestRegistry_WatchService);
+    RUN(TestRegistry_nodes_prefix_case);
+    if (gpu) {
+        RUN(TestClient_default_conn_config);
+        RUN(TestClient_Call);
+        RUN(TestClient_first_call_goes_to_index_1);
+        RUN(TestNewClient_with_no_available_server);
+        RUN(TestBalancer_watchForNewNodes);
+        RUN(TestBalancer_roundRobinSelect);
+        RUN(TestBalancer_mesh_network);
+        RUN(TestExample_calculator_with_registry);
+    }
+    std::printf("%d tests, %d failed\n", g_run, g_fail);
+    return g_fail ? 1 : 0;
+}
