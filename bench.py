@@ -144,6 +144,33 @@ def cpu_port_rate(spec, reqs, threads: int, min_seconds: float, check_limit: int
     return passes * len(reqs) / el, passes, el, rep
 
 
+def loopback_rate(reqs, callers: int, calls_per_caller: int, k: int, receivers: int):
+    """BASELINE config 1: the reference's REAL path restated in C (oracle/loopback.c) - sequential
+    synchronous Client.Call()s over TCP 127.0.0.1 with the net/rpc handshake and gob framing,
+    `callers` independent Clients (threads), each holding k connections to its own servers."""
+    from oracle import binding as ob
+    import threading as th
+    ob.lib()
+    results = [None] * callers
+
+    def one(i):
+        part = np.ascontiguousarray(reqs[i * calls_per_caller:(i + 1) * calls_per_caller])
+        results[i] = ob.loopback_run(part, k=k, receivers=receivers)[1]
+
+    t0 = time.perf_counter()
+    ts = [th.Thread(target=one, args=(i,)) for i in range(callers)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    el = time.perf_counter() - t0
+    calls = sum(r.calls for r in results)
+    return {"value": calls / el, "unit": "calls/s", "callers": callers, "connections_per_caller": k,
+            "calls": int(calls), "seconds": el,
+            "bytes_per_call_out": results[0].bytes_client_to_server / max(results[0].calls, 1),
+            "bytes_per_call_in": results[0].bytes_server_to_client / max(results[0].calls, 1),
+            "what": "C restatement of Client.Call -> net/rpc -> TCP loopback -> method (gob framing, one call in "
+                    "flight per Client); the Go runtime itself is not restated"}
+
+
 def run_reference(args, rank: int):
     """Reference arm: the reference's own path restated on the CPU (oracle port), all host
     threads, same config/metric.  Go itself cannot run here (no toolchain on this image)."""
@@ -161,6 +188,10 @@ def run_reference(args, rank: int):
         snap.dispatch_into(reqs, rep, 1 << 16, threads)
     el = time.perf_counter() - t0
     value = args.steps * len(reqs) / el
+    k = len(snap.selected("prime_worker" if args.workload == "c4" else "calculator") or [0]) \
+        if args.workload != "c3" else 3
+    lb1 = loopback_rate(reqs, 1, min(len(reqs), 30_000), k, 2 if args.workload == "c4" else 1)
+    lbn = loopback_rate(reqs, threads, min(len(reqs) // threads, 20_000), k, 2 if args.workload == "c4" else 1)
     line = {
         "impl": "reference", "metric": "rpc_calls_per_sec_batched_dispatch", "value": value,
         "unit": "calls/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -170,7 +201,10 @@ def run_reference(args, rank: int):
                    "note": "Go reference path not run - no Go toolchain on this image; C port of "
                            "cluster/rpc.go + registry.go + example method bodies, in-process"},
         "cpu_baseline": {"value": value, "unit": "calls/s", "cores": threads, "kind": "port",
-                         "sample": f"{args.steps} passes over one {len(reqs)}-call batch"},
+                         "sample": f"{args.steps} passes over one {len(reqs)}-call batch",
+                         "what": "in-process C port of the path's algorithm, no transport: the fastest CPU "
+                                 "form, used for `value`"},
+        "loopback_1_caller": lb1, "loopback_all_threads": lbn,
         "e2e": {"value": value, "unit": "calls/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -310,9 +344,47 @@ def main():
         e2e_calls = float(len(hb) * e2e_steps)
     e2e_value = e2e_calls / e2e_s
 
+    # ---- e2e of ONE Client's batch in compact form (ptype_b200_call_batch): what
+    # (*Client).CallBatch submits - arguments plus a method byte per call instead of 48-byte
+    # records.  Only for the single-service workloads.
+    e2e_compact = None
+    if args.workload != "c3" and not multi:
+        import ptype_b200.workloads as wl
+        key, base, methods, sel, cargs = wl.as_client_batch(hb)
+        pin_args = p.PinnedArray(cargs.size, np.int64)
+        pin_args.array[:] = cargs.reshape(-1)
+        pa = pin_args.array.reshape(cargs.shape)
+        pin_sel = None
+        if sel is not None:
+            pin_sel = p.PinnedArray(len(sel), np.uint8)
+            pin_sel.array[:] = sel
+        ps = pin_sel.array if pin_sel is not None else None
+        for _ in range(3):
+            ctx.call_batch(key, base, methods, pa, ps, pin_rep.array, flags=args.flags & 4)
+        compact_ok = pin_rep.array.tobytes()
+        barrier()
+        c0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            ctx.call_batch(key, base, methods, pa, ps, pin_rep.array, flags=args.flags & 4)
+        barrier()
+        c1 = time.perf_counter()
+        cs = c1 - c0
+        if multi:
+            t = torch.tensor([cs], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            cs = float(t.item())
+        e2e_compact = {"value": e2e_calls / cs, "unit": "calls/s",
+                       "h2d_bytes_per_step": int(cargs.nbytes + (len(sel) if sel is not None else 0)),
+                       "d2h_bytes_per_step": int(len(hb) * 16), "steps": e2e_steps,
+                       "api": "ptype_b200_call_batch(one Client's batch: args + method byte per call, "
+                              "pinned host buffers)"}
+
     sampler.stop()
     sampler.join(timeout=1.0)
     clocks = sampler.summary([(w0, w1), (e0, e1)])
+    e2e_records = {"value": e2e_value, "unit": "calls/s", "h2d_bytes_per_step": int(len(hb) * 48),
+                   "d2h_bytes_per_step": int(len(hb) * 16), "steps": e2e_steps,
+                   "api": "ptype_b200_dispatch(host pinned 48-byte records -> host pinned replies)"}
 
     # ---- parity spot check of what was just timed, and the CPU baseline (rank 0, N=1 only)
     cpu_baseline = None
@@ -323,11 +395,16 @@ def main():
         got = d_reps[0].download(p.REPLY_DTYPE, counts[0])
         if got.tobytes() != want.tobytes() or pin_rep.array.tobytes() != want.tobytes():
             raise SystemExit("bench.py: CUDA replies differ from the oracle - number withheld")
+        if e2e_compact is not None and compact_ok != want.tobytes():
+            raise SystemExit("bench.py: call_batch replies differ from the oracle - number withheld")
         if not multi:
             threads = os.cpu_count() or 1
             rate, passes, el, _ = cpu_port_rate(spec, hb, threads, args.cpu_seconds)
             rate1, passes1, el1, _ = cpu_port_rate(spec, hb, 1, min(2.0, args.cpu_seconds))
+            lb = loopback_rate(hb, 1, min(len(hb), 20_000), 3 if args.workload != "c4" else 2,
+                               2 if args.workload == "c4" else 1) if args.workload != "c3" else None
             cpu_baseline = {"value": rate, "unit": "calls/s", "cores": threads, "kind": "port",
+                            "loopback_config1": lb,
                             "sample": f"{passes} passes over one {len(hb)}-call batch of the same workload "
                                       f"in {el:.1f} s, {threads} threads",
                             "single_thread_value": rate1,
@@ -361,9 +438,8 @@ def main():
                          "frac": achieved / peak, "traffic": traffic, "peak_kind": peak_kind,
                          "kernel": "dispatch_kernel", "algorithmic_bytes_per_call": BYTES_PER_CALL,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
-            "e2e": {"value": e2e_value, "unit": "calls/s", "h2d_bytes_per_step": int(len(hb) * 48),
-                    "d2h_bytes_per_step": int(len(hb) * 16), "steps": e2e_steps,
-                    "api": "ptype_b200_dispatch(host pinned reqs -> host pinned replies)"},
+            "e2e": e2e_compact if e2e_compact is not None else e2e_records,
+            "e2e_records": e2e_records,
             "gpu_launches": int(launches),
             "clocks": clocks,
         }

@@ -313,6 +313,24 @@ typedef struct ptype_batch {
 } ptype_batch;
 int ptype_b200_dispatch_batches(ptype_ctx*, int dev, const ptype_batch* batches, size_t count,
                                 uint32_t flags);
+/* One Client's batch in its compact form — what (*Client).CallBatch would submit.  All n
+ * calls name the service `svc_key` and own the consecutive sequence numbers
+ * seq_base+1 .. seq_base+n (ONE atomic.AddUint64(&c.seq, n), cluster/rpc.go:181), so only the
+ * arguments travel per call: args holds args_per_call (2: calculator.Args{A,B}; 3:
+ * prime.Args{Min,Max,Target}) int64 per call.  method_sel is NULL when every call uses
+ * methods[0], else one byte per call indexing methods[] (values >= n_methods read as 0).
+ * Replies are the same 16-byte records as ptype_b200_dispatch and identical to what
+ * dispatching the equivalent 48-byte ptype_req records gives.  Host pointers are copied in
+ * pipelined chunks (16-25 B/call over PCIe instead of 48); PTYPE_F_DEVICE_PTRS = one launch. */
+#define PTYPE_BATCH_METHODS 4
+typedef struct ptype_method_ref {
+    uint32_t method; /* as ptype_req.method */
+    uint32_t recv;   /* as ptype_req.recv   */
+} ptype_method_ref;
+int ptype_b200_call_batch(ptype_ctx*, int dev, uint64_t svc_key, uint64_t seq_base,
+                          const ptype_method_ref* methods, int n_methods, const uint8_t* method_sel,
+                          const int64_t* args, int args_per_call, size_t n, ptype_reply* replies,
+                          uint32_t flags);
 int ptype_b200_sync(ptype_ctx*, int dev);
 int ptype_b200_set_check_limit(ptype_ctx*, uint64_t max_iterations);
 

@@ -39,6 +39,10 @@ class BatchStats(C.Structure):
                 ("failed_count", C.c_uint64)]
 
 
+class MethodRef(C.Structure):
+    _fields_ = [("method", C.c_uint32), ("recv", C.c_uint32)]
+
+
 class Batch(C.Structure):
     _fields_ = [("reqs", C.c_void_p), ("replies", C.c_void_p), ("n", C.c_size_t)]
 
@@ -103,6 +107,8 @@ SIGNATURES = [
     ("ptype_b200_dispatch_ex", C.c_int,
      [_vp, C.c_int, _vp, C.c_size_t, _vp, _vp, C.c_size_t, _vp, C.c_uint32]),
     ("ptype_b200_dispatch_batches", C.c_int, [_vp, C.c_int, _vp, C.c_size_t, C.c_uint32]),
+    ("ptype_b200_call_batch", C.c_int,
+     [_vp, C.c_int, C.c_uint64, C.c_uint64, _vp, C.c_int, _vp, _vp, C.c_int, C.c_size_t, _vp, C.c_uint32]),
     ("ptype_b200_sync", C.c_int, [_vp, C.c_int]),
     ("ptype_b200_set_check_limit", C.c_int, [_vp, C.c_uint64]),
     ("ptype_b200_reply_checksum", C.c_int,

@@ -162,6 +162,26 @@ class Context:
                                              _ptr(failed) if failed is not None else None,
                                              failed_cap, _ptr(stats), f), "dispatch_ex")
 
+    def call_batch(self, service_key: int, seq_base: int, methods, args, method_sel=None, replies=None,
+                   *, dev: int = 0, flags: int = 0, n: Optional[int] = None, args_per_call: int = 2):
+        """One Client's batch in compact form (ptype_b200_call_batch).  methods: list of
+        (method, recv) hash pairs; args: int64 array [n, 2|3] (host) or a device buffer with
+        n/args_per_call given; method_sel: uint8 [n] or None."""
+        refs = (_abi.MethodRef * len(methods))(*[_abi.MethodRef(m, r) for m, r in methods])
+        if isinstance(args, np.ndarray):
+            args = np.ascontiguousarray(args, dtype=np.int64)
+            n, args_per_call = args.shape
+            if method_sel is not None:
+                method_sel = np.ascontiguousarray(method_sel, dtype=np.uint8)
+            if replies is None:
+                replies = np.empty(n, dtype=REPLY_DTYPE)
+        else:
+            flags |= F_DEVICE_PTRS
+        check(lib.ptype_b200_call_batch(self._h, dev, service_key, seq_base, refs, len(methods),
+                                        _ptr(method_sel) if method_sel is not None else None,
+                                        _ptr(args), args_per_call, n, _ptr(replies), flags), "call_batch")
+        return replies
+
     def make_batches(self, items) -> "C.Array":
         """items: iterable of (device reqs, device replies, n) -> a ptype_batch array."""
         items = list(items)

@@ -36,7 +36,20 @@ int cuda_fail(cudaError_t e, const char* what) {
     } while (0)
 
 constexpr int kPipe = 4;                     // host-pointer pipeline depth
-constexpr size_t kChunkCalls = 128 * 1024;   // calls per pipelined chunk (6 MiB in, 2 MiB out)
+constexpr size_t kMaxChunkCalls = 1024 * 1024;  // staging capacity per pipeline slot
+// Calls per pipelined chunk of the host-buffer paths.  PTYPE_B200_CHUNK overrides it
+// (measurement switch; multiples of 32, at most kMaxChunkCalls).
+size_t chunk_calls() {
+    static const size_t v = [] {
+        size_t c = 128 * 1024;
+        if (const char* e = std::getenv("PTYPE_B200_CHUNK")) {
+            const long long x = std::atoll(e);
+            if (x >= 32 && static_cast<size_t>(x) <= kMaxChunkCalls) c = static_cast<size_t>(x) / 32 * 32;
+        }
+        return c;
+    }();
+    return v;
+}
 
 // ---- NCCL, resolved at run time so the library has no link-time NCCL dependency
 // (inside a torch process this picks up the libnccl torch already loaded).
@@ -199,6 +212,27 @@ int adopt_image(ptype_ctx* ctx, DeviceState* d, int buf, const ptype_image_heade
     return PTYPE_OK;
 }
 
+// Device alias of a page-locked host pointer (UVA maps every cudaHostAlloc / registered
+// range), or nullptr for pageable memory.  Lets a kernel stream requests and replies over
+// PCIe itself instead of going through chunked copy-engine transfers.
+void* pinned_alias(const void* host) {
+    if (!host) return nullptr;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, host) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
+}
+
+bool zero_copy_enabled() {
+    static const bool on = [] {
+        const char* v = std::getenv("PTYPE_B200_ZERO_COPY");
+        return !(v && v[0] == '0');
+    }();
+    return on;
+}
+
 int ensure_extras(DeviceState* d, size_t failed_cap) {
     if (!d->d_stats) CU(cudaMalloc(&d->d_stats, ptype::kStatWords * sizeof(unsigned long long)));
     if (failed_cap > d->failed_cap) {
@@ -213,8 +247,8 @@ int ensure_extras(DeviceState* d, size_t failed_cap) {
 
 int ensure_stage(DeviceState* d, int s) {
     Stage& st = d->stage[s];
-    if (!st.d_reqs) CU(cudaMalloc(&st.d_reqs, kChunkCalls * sizeof(ptype_req)));
-    if (!st.d_replies) CU(cudaMalloc(&st.d_replies, kChunkCalls * sizeof(ptype_reply)));
+    if (!st.d_reqs) CU(cudaMalloc(&st.d_reqs, chunk_calls() * sizeof(ptype_req)));
+    if (!st.d_replies) CU(cudaMalloc(&st.d_replies, chunk_calls() * sizeof(ptype_reply)));
     if (!st.done) CU(cudaEventCreateWithFlags(&st.done, cudaEventDisableTiming));
     return PTYPE_OK;
 }
@@ -539,6 +573,19 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
         return PTYPE_OK;
     }
 
+    // Page-locked host buffers: the kernel reads the records and writes the replies across
+    // PCIe itself (both directions overlap, no staging, one launch).
+    if (zero_copy_enabled() && !extras && n) {
+        const ptype_req* q = static_cast<const ptype_req*>(pinned_alias(reqs));
+        ptype_reply* r = static_cast<ptype_reply*>(pinned_alias(replies));
+        if (q && r) {
+            CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, n, d->sm_count), q, n, r, nullptr,
+                                      0u, 0u, nullptr, d->stream));
+            ctx->launches.fetch_add(1);
+            if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+            return PTYPE_OK;
+        }
+    }
     // Host buffers: chunked H2D -> kernel -> D2H pipeline over kPipe streams.
     int rc;
     if (extras) {
@@ -550,7 +597,7 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
     size_t done = 0;
     int s = 0;
     while (done < n) {
-        const size_t cnt = n - done < kChunkCalls ? n - done : kChunkCalls;
+        const size_t cnt = n - done < chunk_calls() ? n - done : chunk_calls();
         rc = ensure_stage(d, s);
         if (rc != PTYPE_OK) return rc;
         Stage& st = d->stage[s];
@@ -619,6 +666,93 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
         ctx->launches.fetch_add(1);
     }
     if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+    return PTYPE_OK;
+}
+
+int ptype_b200_call_batch(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base,
+                          const ptype_method_ref* methods, int n_methods, const uint8_t* method_sel,
+                          const int64_t* args, int args_per_call, size_t n, ptype_reply* replies,
+                          uint32_t flags) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || !methods || n_methods < 1 || n_methods > PTYPE_BATCH_METHODS ||
+        (args_per_call != 2 && args_per_call != 3) || (n && (!args || !replies)))
+        return PTYPE_E_INVAL;
+    if (n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
+    std::lock_guard<std::mutex> lk(d->mu);
+    if (d->active < 0) return PTYPE_E_NO_IMAGE;
+    CU(cudaSetDevice(d->device));
+    const int buf = d->active;
+    const ptype::DeviceImage img = d->view[buf];
+    // the batch kernel loads with LDG: use that plan's block shape and table placement
+    const ptype::LaunchPlan& plan =
+        d->plan[buf][plan_kind((flags & PTYPE_F_GLOBAL_TABLE) | PTYPE_F_LDG_LOADS)][0];
+    uint32_t m[PTYPE_BATCH_METHODS], r[PTYPE_BATCH_METHODS];
+    for (int i = 0; i < n_methods; ++i) {
+        m[i] = methods[i].method;
+        r[i] = methods[i].recv;
+    }
+    const size_t arg_bytes = static_cast<size_t>(args_per_call) * sizeof(int64_t);
+    if (flags & PTYPE_F_DEVICE_PTRS) {
+        if (n) {
+            CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, n, d->sm_count), svc_key, seq_base,
+                                        m, r, n_methods, args, args_per_call, method_sel, n, replies,
+                                        d->stream));
+            ctx->launches.fetch_add(1);
+        }
+        if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+        return PTYPE_OK;
+    }
+    if (zero_copy_enabled() && n) {
+        const int64_t* za = static_cast<const int64_t*>(pinned_alias(args));
+        ptype_reply* zr = static_cast<ptype_reply*>(pinned_alias(replies));
+        const uint8_t* zs = method_sel ? static_cast<const uint8_t*>(pinned_alias(method_sel)) : nullptr;
+        if (za && zr && (!method_sel || zs)) {
+            CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, n, d->sm_count), svc_key, seq_base,
+                                        m, r, n_methods, za, args_per_call, zs, n, zr, d->stream));
+            ctx->launches.fetch_add(1);
+            if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+            return PTYPE_OK;
+        }
+    }
+    // Host buffers: the staging slot of each pipeline stream holds a chunk's arguments
+    // (<= 24 B/call) and, behind them, its method selectors (1 B/call).
+    size_t done = 0;
+    int s = 0;
+    while (done < n) {
+        const size_t cnt = n - done < chunk_calls() ? n - done : chunk_calls();
+        int rc = ensure_stage(d, s);
+        if (rc != PTYPE_OK) return rc;
+        Stage& st = d->stage[s];
+        if (st.busy) {
+            CU(cudaEventSynchronize(st.done));
+            st.busy = false;
+        }
+        unsigned char* base = reinterpret_cast<unsigned char*>(st.d_reqs);
+        int64_t* d_args = reinterpret_cast<int64_t*>(base);
+        uint8_t* d_sel = method_sel ? base + chunk_calls() * 24 : nullptr;
+        CU(cudaMemcpyAsync(d_args, reinterpret_cast<const unsigned char*>(args) + done * arg_bytes,
+                           cnt * arg_bytes, cudaMemcpyHostToDevice, d->pipe[s]));
+        if (method_sel)
+            CU(cudaMemcpyAsync(d_sel, method_sel + done, cnt, cudaMemcpyHostToDevice, d->pipe[s]));
+        CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, cnt, d->sm_count), svc_key,
+                                    seq_base + done, m, r, n_methods, d_args, args_per_call, d_sel, cnt,
+                                    st.d_replies, d->pipe[s]));
+        ctx->launches.fetch_add(1);
+        CU(cudaMemcpyAsync(replies + done, st.d_replies, cnt * sizeof(ptype_reply), cudaMemcpyDeviceToHost,
+                           d->pipe[s]));
+        CU(cudaEventRecord(st.done, d->pipe[s]));
+        st.busy = true;
+        done += cnt;
+        s = (s + 1) % kPipe;
+    }
+    if (!(flags & PTYPE_F_ASYNC)) {
+        for (int i = 0; i < kPipe; ++i) {
+            if (d->stage[i].busy) {
+                CU(cudaEventSynchronize(d->stage[i].done));
+                d->stage[i].busy = false;
+            }
+        }
+    }
     return PTYPE_OK;
 }
 

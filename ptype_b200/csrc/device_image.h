@@ -46,6 +46,11 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
                             const ptype_req* reqs, size_t n, ptype_reply* replies, uint32_t* failed_idx,
                             uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
                             cudaStream_t stream);
+cudaError_t launch_call_batch(const DeviceImage& img, const LaunchPlan& plan, int blocks,
+                              uint64_t svc_key, uint64_t seq_base, const uint32_t* methods,
+                              const uint32_t* recvs, int n_methods, const int64_t* args,
+                              int args_per_call, const uint8_t* method_sel, size_t n,
+                              ptype_reply* replies, cudaStream_t stream);
 cudaError_t launch_reply_checksum(const ptype_reply* replies, size_t n, uint64_t index_base,
                                   unsigned long long* partials, unsigned long long* out,
                                   cudaStream_t stream);

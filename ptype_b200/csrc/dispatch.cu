@@ -566,6 +566,89 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     griddep_wait();
 }
 
+// ------------------------------------------------ kernel, one Client's batch
+//
+// What (*Client).CallBatch submits: every call names the same service and the batch owns
+// the consecutive sequence numbers seq_base+1 .. seq_base+n (one atomic add, rpc.go:181),
+// so only the arguments (16 or 24 bytes) and, for mixed batches, a one-byte method
+// selector travel per call.  Same lookup/route/resolve/execute as the general kernel.
+struct ClientBatch {
+    uint64_t svc_key;
+    uint64_t seq_base;
+    uint32_t method[PTYPE_BATCH_METHODS];
+    uint32_t recv[PTYPE_BATCH_METHODS];
+};
+
+template <bool kSmemTable, int kArgs, bool kHasSel, int kUnroll, int kThreads, int kMinCtas>
+__global__ void __launch_bounds__(kThreads, kMinCtas)
+    call_batch_kernel(const DeviceImage img, const ClientBatch batch, const int64_t* __restrict__ args,
+                      const uint8_t* __restrict__ method_sel, const size_t n, uint4* __restrict__ replies) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ __align__(16) CtaShared sh;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+    const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
+    griddep_launch_dependents();
+
+    const size_t n_tiles = (n + 31) >> 5;
+    const size_t total_warps = static_cast<size_t>(gridDim.x) * warps_per_cta;
+    const size_t warp_global = static_cast<size_t>(blockIdx.x) * warps_per_cta + (threadIdx.x >> 5);
+    LookupCache cache;
+    bool table_ready = !kSmemTable;
+    const uint32_t key_lo = static_cast<uint32_t>(batch.svc_key), key_hi = static_cast<uint32_t>(batch.svc_key >> 32);
+
+    for (size_t t0 = warp_global; t0 < n_tiles; t0 += total_warps * kUnroll) {
+        uint4 a01[kUnroll];
+        uint2 a2[kUnroll];
+        uint32_t sel[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const size_t idx = ((t0 + static_cast<size_t>(u) * total_warps) << 5) + lane;
+            a01[u] = make_uint4(0, 0, 0, 0);
+            a2[u] = make_uint2(0, 0);
+            sel[u] = 0;
+            if (idx < n) {
+                if (kArgs == 2) {
+                    a01[u] = ld_stream(reinterpret_cast<const uint4*>(args) + idx);
+                } else {
+                    const uint2* p = reinterpret_cast<const uint2*>(args) + idx * 3;
+                    const uint2 x = __ldg(p), y = __ldg(p + 1);
+                    a01[u] = make_uint4(x.x, x.y, y.x, y.y);
+                    a2[u] = __ldg(p + 2);
+                }
+                if (kHasSel) sel[u] = __ldg(method_sel + idx);
+            }
+        }
+        if (!table_ready) {
+            mbar_wait(&sh.table_bar, 0);
+            table_ready = true;
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const size_t idx = ((t0 + static_cast<size_t>(u) * total_warps) << 5) + lane;
+            if (idx >= n) continue;
+            const uint64_t seq = batch.seq_base + 1 + idx;
+            const uint32_t which = kHasSel ? (sel[u] < PTYPE_BATCH_METHODS ? sel[u] : 0u) : 0u;
+            uint32_t m = batch.method[0], rv = batch.recv[0];
+            if (kHasSel) {
+#pragma unroll
+                for (int k = 1; k < PTYPE_BATCH_METHODS; ++k) {
+                    if (which == static_cast<uint32_t>(k)) {
+                        m = batch.method[k];
+                        rv = batch.recv[k];
+                    }
+                }
+            }
+            const uint4 q0 = make_uint4(key_lo, key_hi, static_cast<uint32_t>(seq), static_cast<uint32_t>(seq >> 32));
+            const uint4 q1 = make_uint4(m, rv, a01[u].x, a01[u].y);
+            const uint4 q2 = make_uint4(a01[u].z, a01[u].w, a2[u].x, a2[u].y);
+            st_stream(replies + idx, dispatch_one<kSmemTable>(img, sh, slots, cache, q0, q1, q2));
+        }
+    }
+    if (!table_ready) mbar_wait(&sh.table_bar, 0);
+    griddep_wait();
+}
+
 // ---------------------------------------------------------- reply checksum
 
 __global__ void __launch_bounds__(kChecksumThreads)
@@ -753,6 +836,53 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
                                                 failed_cap, idx_base, stats, stream)
                   : launch_variant<false, false>(img, plan, blocks, reqs, n, replies, failed_idx,
                                                  failed_cap, idx_base, stats, stream);
+}
+
+namespace {
+template <bool kSmemTable, int kArgs, bool kHasSel>
+cudaError_t launch_call_batch_variant(const DeviceImage& img, const LaunchPlan& plan, int blocks,
+                                      const ClientBatch& batch, const int64_t* args,
+                                      const uint8_t* method_sel, size_t n, ptype_reply* replies,
+                                      cudaStream_t stream) {
+    uint4* r = reinterpret_cast<uint4*>(replies);
+    if (plan.threads == kMaxThreads) {
+        auto kernel = call_batch_kernel<kSmemTable, kArgs, kHasSel, 4, kMaxThreads, 1>;
+        if (plan.dyn_smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 static_cast<int>(plan.dyn_smem));
+            if (e != cudaSuccess) return e;
+        }
+        return launch_kernel(kernel, blocks, plan.threads, plan.dyn_smem, stream, img, batch, args,
+                             method_sel, n, r);
+    }
+    return launch_kernel(call_batch_kernel<kSmemTable, kArgs, kHasSel, 4, kSmallThreads, kSmallMinCtas>,
+                         blocks, plan.threads, plan.dyn_smem, stream, img, batch, args, method_sel, n, r);
+}
+}  // namespace
+
+// One Client's batch (see call_batch_kernel).  Uses the LDG-shaped plan of the image.
+cudaError_t launch_call_batch(const DeviceImage& img, const LaunchPlan& plan, int blocks,
+                              uint64_t svc_key, uint64_t seq_base, const uint32_t* methods,
+                              const uint32_t* recvs, int n_methods, const int64_t* args,
+                              int args_per_call, const uint8_t* method_sel, size_t n,
+                              ptype_reply* replies, cudaStream_t stream) {
+    ClientBatch batch = {};
+    batch.svc_key = svc_key;
+    batch.seq_base = seq_base;
+    for (int i = 0; i < PTYPE_BATCH_METHODS; ++i) {
+        batch.method[i] = methods[i < n_methods ? i : 0];
+        batch.recv[i] = recvs[i < n_methods ? i : 0];
+    }
+    const bool sel = method_sel != nullptr;
+#define PTYPE_CB(SM, AR, SEL) \
+    launch_call_batch_variant<SM, AR, SEL>(img, plan, blocks, batch, args, method_sel, n, replies, stream)
+    if (plan.smem_table) {
+        if (args_per_call == 2) return sel ? PTYPE_CB(true, 2, true) : PTYPE_CB(true, 2, false);
+        return sel ? PTYPE_CB(true, 3, true) : PTYPE_CB(true, 3, false);
+    }
+    if (args_per_call == 2) return sel ? PTYPE_CB(false, 2, true) : PTYPE_CB(false, 2, false);
+    return sel ? PTYPE_CB(false, 3, true) : PTYPE_CB(false, 3, false);
+#undef PTYPE_CB
 }
 
 cudaError_t launch_reply_checksum(const ptype_reply* replies, size_t n, uint64_t index_base,

@@ -224,3 +224,23 @@ def edge_case_calls(spec_services: List[str], *, salt: int = 0, seed: int = 0x5E
     tgt = splitmix64(seed, n, 8).view(np.int64) >> (splitmix64(seed, n, 9) % np.uint64(64)).astype(np.int64)
     rnd["a2"] = tgt
     return np.concatenate([fixed, rnd])
+
+
+def as_client_batch(reqs: np.ndarray):
+    """Compact form of a stream issued by ONE Client (same service, consecutive seq): what
+    (*Client).CallBatch submits.  Returns (svc_key, seq_base, methods, method_sel, args) for
+    Context.call_batch; method_sel is None when every call uses one method."""
+    assert len(reqs) > 0
+    key = int(reqs["svc_key"][0])
+    assert np.all(reqs["svc_key"] == reqs["svc_key"][0]), "one Client names one service"
+    seq0 = int(reqs["seq"][0])
+    assert np.array_equal(reqs["seq"], np.arange(seq0, seq0 + len(reqs), dtype=np.uint64))
+    pairs = np.stack([reqs["method"], reqs["recv"]], axis=1)
+    uniq, inv = np.unique(pairs, axis=0, return_inverse=True)
+    assert len(uniq) <= 4, "at most PTYPE_BATCH_METHODS methods per batch"
+    methods = [(int(m), int(r)) for m, r in uniq]
+    sel = None if len(uniq) == 1 else inv.reshape(-1).astype(np.uint8)
+    three = bool(np.any(reqs["a2"] != 0))
+    cols = [reqs["a0"], reqs["a1"]] + ([reqs["a2"]] if three else [])
+    args = np.ascontiguousarray(np.stack(cols, axis=1), dtype=np.int64)
+    return key, (seq0 - 1) & 0xFFFFFFFFFFFFFFFF, methods, sel, args

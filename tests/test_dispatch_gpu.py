@@ -343,6 +343,88 @@ def test_dispatch_batches_equals_one_by_one(ctx, oracle):
         b.free()
 
 
+@pytest.mark.parametrize("n", [1, 33, 4097, 128 * 1024 + 1, 1 << 20])
+@pytest.mark.parametrize("seq_base", [0, (1 << 32) - 7, (1 << 63) - 5])
+def test_call_batch_compact_form(ctx, oracle, n, seq_base):
+    """ptype_b200_call_batch (one Client's batch: args + a method byte per call) gives the
+    replies of dispatching the equivalent 48-byte records, for host and device buffers."""
+    spec = w.calculator_registry()
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    reqs = w.calculator_calls(n, seed=31 + n, seq_base=seq_base)
+    want = snap.dispatch(reqs)
+    key, base, methods, sel, args = w.as_client_batch(reqs)
+    assert base == seq_base and args.shape == (n, 2) and (sel is not None or n == 1)
+    assert_same(ctx.call_batch(key, base, methods, args, sel), want, reqs)
+    d_args = ctx.device_buffer(args.nbytes).upload(args)
+    d_sel = ctx.device_buffer(max(n, 1)).upload(sel) if sel is not None else None
+    d_rep = ctx.device_buffer(n * 16)
+    ctx.call_batch(key, base, methods, d_args, d_sel, d_rep, n=n, args_per_call=2)
+    assert_same(d_rep.download(p.REPLY_DTYPE, n), want, reqs)
+    for b in (d_args, d_sel, d_rep):
+        if b is not None:
+            b.free()
+
+
+def test_call_batch_prime_and_errors(ctx, oracle):
+    spec = w.optimus_registry()
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    reqs = w.optimus_calls(300_000)
+    key, base, methods, sel, args = w.as_client_batch(reqs)
+    assert sel is None and args.shape[1] == 3
+    assert_same(ctx.call_batch(key, base, methods, args), snap.dispatch(reqs, threads=8), reqs)
+    # a method the nodes never registered, an ill-formed name, and a service nobody registered
+    for sm, status in (("Prime.Sieve", p.ST_CANT_FIND_METHOD), ("Calculator.Add", p.ST_CANT_FIND_SERVICE),
+                       ("nodot", p.ST_ILL_FORMED)):
+        rep = ctx.call_batch(key, 0, [p.method_key(sm)], args[:1000])
+        assert np.all(rep["status"] == status) and np.all(rep["value"] == 0)
+        assert np.all(rep["node"] == np.array(snap.selected("prime_worker"))[np.arange(1, 1001) % 2])
+    rep = ctx.call_batch(p.service_key("nobody"), 0, methods, args[:1000])
+    assert np.all(rep["status"] == p.ST_NO_SERVICE) and np.all(rep["node"] == p.NO_NODE)
+
+
+def test_call_batch_against_the_big_table(ctx, stress, oracle):
+    """The compact form with the 12 800-slot table staged in shared memory (1024-thread CTAs)."""
+    spec, img, snap, _ = stress
+    ctx.publish(img)
+    n = 500_000
+    reqs = w.calculator_calls(n, seed=5)
+    reqs["svc_key"] = p.service_key("svc_01234")
+    key, base, methods, sel, args = w.as_client_batch(reqs)
+    assert_same(ctx.call_batch(key, base, methods, args, sel), snap.dispatch(reqs, threads=8), reqs)
+    assert_same(ctx.call_batch(key, base, methods, args, sel, flags=p.F_GLOBAL_TABLE),
+                snap.dispatch(reqs, threads=8), reqs)
+
+
+def test_pinned_buffers_take_the_zero_copy_path(ctx, oracle):
+    """Page-locked host buffers (ptype_b200_alloc_pinned) are read and written by the kernel
+    across PCIe directly; results equal the staged-copy path's and the oracle's."""
+    spec = w.calculator_registry()
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    n = 300_001
+    reqs = np.concatenate([w.calculator_calls(n - 5000), w.edge_case_calls(["calculator"])])[:n]
+    want = snap.dispatch(reqs, check_limit=LIMIT)
+    pq, pr = p.PinnedArray(n, p.REQ_DTYPE), p.PinnedArray(n, p.REPLY_DTYPE)
+    pq.array[:] = reqs
+    launches = ctx.launch_count()
+    ctx.dispatch(pq.array, pr.array)
+    assert ctx.launch_count() == launches + 1          # one launch, no chunk pipeline
+    assert_same(pr.array.copy(), want, reqs)
+    assert_same(ctx.dispatch(reqs), want, reqs)         # pageable: staged copies, 3 chunks
+    cal = w.calculator_calls(n, seed=9)
+    key, base, methods, sel, args = w.as_client_batch(cal)
+    pa, ps = p.PinnedArray(args.size, np.int64), p.PinnedArray(n, np.uint8)
+    pa.array[:] = args.reshape(-1)
+    ps.array[:] = sel
+    pr.array[:] = np.zeros(1, dtype=p.REPLY_DTYPE)
+    ctx.call_batch(key, base, methods, pa.array.reshape(args.shape), ps.array, pr.array)
+    assert_same(pr.array.copy(), snap.dispatch(cal), cal)
+    for b in (pq, pr, pa, ps):
+        b.free()
+
+
 def test_dispatch_without_image_fails():
     c = p.Context([0])
     try:
