@@ -130,7 +130,8 @@ typedef struct ptype_image_header { /* 192 bytes */
     uint32_t table_seed;     /* xor-ed into the folded key before the three slot hashes */
     uint32_t method_mul;     /* odd multiplier: mtable index = (method_hash * mul) >> 26 */
     uint32_t off_mtable;     /* ptype_method[PTYPE_MTABLE_SLOTS], collision-free, opcode 0 = empty */
-    uint32_t reserved[4];
+    uint32_t host_sections;  /* 1: services/nodes/strings present; 0: device-only image       */
+    uint32_t reserved[3];
     char local_addr[PTYPE_LOCAL_ADDR_MAX]; /* the Client host's address string (cluster.go:69,82) */
 } ptype_image_header;
 
@@ -211,6 +212,12 @@ int ptype_b200_builder_new(const char* local_addr, int max_connections, ptype_bu
  * {"address":address,"port":port}.  Re-registering a key overwrites it. */
 int ptype_b200_builder_register(ptype_builder*, const char* service, const char* node_name,
                                 const char* address, int port);
+/* The key of one node went away (lease expiry, cluster/registry.go:58-83, or a delete as in
+ * cluster/registry_test.go:179-191).  PTYPE_E_NOT_FOUND if it was not registered. */
+int ptype_b200_builder_unregister(ptype_builder*, const char* service, const char* node_name);
+/* Emit only what the kernels read (slots, connection hashes, method tables): small blobs for
+ * frequent live updates.  ptype_b200_image_selected / _node answer PTYPE_E_NOT_FOUND on them. */
+int ptype_b200_builder_set_device_only(ptype_builder*, int on);
 /* A service whose watch delivered an empty list (cluster/rpc_test.go:85-90). */
 int ptype_b200_builder_declare(ptype_builder*, const char* service);
 /* The nodes of `service` ran rpc.Register(new(<receiver>)) (server.go:16-17).

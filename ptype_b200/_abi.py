@@ -57,7 +57,7 @@ class ImageHeader(C.Structure):
         ("off_methods", C.c_uint32), ("off_nodes", C.c_uint32), ("off_services", C.c_uint32),
         ("off_strings", C.c_uint32), ("strings_bytes", C.c_uint32), ("device_bytes", C.c_uint32),
         ("table_seed", C.c_uint32), ("method_mul", C.c_uint32), ("off_mtable", C.c_uint32),
-        ("reserved", C.c_uint32 * 4), ("local_addr", C.c_char * 64),
+        ("host_sections", C.c_uint32), ("reserved", C.c_uint32 * 3), ("local_addr", C.c_char * 64),
     ]
 
 
@@ -76,6 +76,8 @@ SIGNATURES = [
     ("ptype_b200_conn_hash", C.c_uint32, [C.c_char_p, C.c_int]),
     ("ptype_b200_builder_new", C.c_int, [C.c_char_p, C.c_int, C.POINTER(_vp)]),
     ("ptype_b200_builder_register", C.c_int, [_vp, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]),
+    ("ptype_b200_builder_unregister", C.c_int, [_vp, C.c_char_p, C.c_char_p]),
+    ("ptype_b200_builder_set_device_only", C.c_int, [_vp, C.c_int]),
     ("ptype_b200_builder_declare", C.c_int, [_vp, C.c_char_p]),
     ("ptype_b200_builder_expose", C.c_int, [_vp, C.c_char_p, C.c_char_p]),
     ("ptype_b200_builder_set_slots", C.c_int, [_vp, C.c_uint32]),

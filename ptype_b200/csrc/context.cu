@@ -138,6 +138,10 @@ struct DeviceState {
     unsigned long long* d_cksum_partials = nullptr;  // scratch of the checksum kernel
     unsigned long long* d_cksum_out = nullptr;
     unsigned long long* d_size = nullptr;  // broadcast header scratch
+    cudaEvent_t drained[1 + kPipe] = {};   // "everything enqueued so far" markers, one per dispatch stream
+    cudaEvent_t image_ready = nullptr;     // the inactive buffer holds the new image
+    void* h_stage[2] = {nullptr, nullptr}; // page-locked copies of the published blobs' device part
+    size_t h_stage_cap[2] = {0, 0};
     std::mutex mu;
 };
 
@@ -173,10 +177,34 @@ int sync_all_streams(DeviceState* d) {
     return PTYPE_OK;
 }
 
+// Snapshot updates do not stop the dispatch streams.  Before the inactive buffer is
+// overwritten the copy stream waits (on the device) for everything enqueued so far, since
+// launches made two flips ago may still read it; after the upload every dispatch stream
+// waits (on the device) for the copy before its next launch.  The host never blocks.
+int copy_stream_waits_for_dispatches(DeviceState* d) {
+    for (int i = 0; i <= kPipe; ++i) {
+        cudaStream_t s = i == 0 ? d->stream : d->pipe[i - 1];
+        if (!d->drained[i]) CU(cudaEventCreateWithFlags(&d->drained[i], cudaEventDisableTiming));
+        CU(cudaEventRecord(d->drained[i], s));
+        CU(cudaStreamWaitEvent(d->copy_stream, d->drained[i], 0));
+    }
+    return PTYPE_OK;
+}
+
+int dispatches_wait_for_copy_stream(DeviceState* d) {
+    if (!d->image_ready) CU(cudaEventCreateWithFlags(&d->image_ready, cudaEventDisableTiming));
+    CU(cudaEventRecord(d->image_ready, d->copy_stream));
+    CU(cudaStreamWaitEvent(d->stream, d->image_ready, 0));
+    for (int i = 0; i < kPipe; ++i) CU(cudaStreamWaitEvent(d->pipe[i], d->image_ready, 0));
+    return PTYPE_OK;
+}
+
 // Make the inactive image buffer at least `bytes` big.  Nothing in flight reads it:
 // every dispatch launched so far captured the active buffer, and callers sync first.
 int reserve_inactive(DeviceState* d, int buf, size_t bytes) {
     if (d->image_cap[buf] >= bytes) return PTYPE_OK;
+    int rc0 = sync_all_streams(d);  // growing frees the old buffer: nothing may still read it
+    if (rc0 != PTYPE_OK) return rc0;
     if (d->image_buf[buf]) CU(cudaFree(d->image_buf[buf]));
     d->image_buf[buf] = nullptr;
     d->image_cap[buf] = 0;
@@ -306,6 +334,11 @@ void ptype_b200_close(ptype_ctx* ctx) {
         if (d->d_cksum_partials) cudaFree(d->d_cksum_partials);
         if (d->d_cksum_out) cudaFree(d->d_cksum_out);
         if (d->d_size) cudaFree(d->d_size);
+        for (int i = 0; i <= kPipe; ++i)
+            if (d->drained[i]) cudaEventDestroy(d->drained[i]);
+        if (d->image_ready) cudaEventDestroy(d->image_ready);
+        for (int b = 0; b < 2; ++b)
+            if (d->h_stage[b]) cudaFreeHost(d->h_stage[b]);
         if (d->stream) cudaStreamDestroy(d->stream);
         if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
         delete d;
@@ -416,15 +449,29 @@ int ptype_b200_publish_image(ptype_ctx* ctx, const void* image, size_t bytes) {
         std::lock_guard<std::mutex> lk(d->mu);
         CU(cudaSetDevice(d->device));
         const int buf = d->active == 0 ? 1 : 0;
-        // work launched against an older flip may still read this buffer
-        rc = sync_all_streams(d);
-        if (rc != PTYPE_OK) return rc;
         rc = reserve_inactive(d, buf, h.device_bytes);
         if (rc != PTYPE_OK) return rc;
-        CU(cudaMemcpyAsync(d->image_buf[buf], image, h.device_bytes, cudaMemcpyHostToDevice,
+        // Stage the blob in page-locked memory so the upload is a true asynchronous DMA.  The
+        // staging slot was last used two publishes ago; its copy has long been ordered before
+        // the previous publish's, which the copy stream has to have finished first.
+        if (d->h_stage_cap[buf] < h.device_bytes) {
+            CU(cudaStreamSynchronize(d->copy_stream));
+            if (d->h_stage[buf]) CU(cudaFreeHost(d->h_stage[buf]));
+            d->h_stage[buf] = nullptr;
+            d->h_stage_cap[buf] = 0;
+            CU(cudaHostAlloc(&d->h_stage[buf], (h.device_bytes + 4095) / 4096 * 4096, cudaHostAllocDefault));
+            d->h_stage_cap[buf] = (h.device_bytes + 4095) / 4096 * 4096;
+        } else {
+            CU(cudaStreamSynchronize(d->copy_stream));
+        }
+        std::memcpy(d->h_stage[buf], image, h.device_bytes);
+        rc = copy_stream_waits_for_dispatches(d);
+        if (rc != PTYPE_OK) return rc;
+        CU(cudaMemcpyAsync(d->image_buf[buf], d->h_stage[buf], h.device_bytes, cudaMemcpyHostToDevice,
                            d->copy_stream));
-        CU(cudaStreamSynchronize(d->copy_stream));
-        rc = adopt_image(ctx, d, buf, h);
+        rc = dispatches_wait_for_copy_stream(d);
+        if (rc != PTYPE_OK) return rc;
+        rc = adopt_image(ctx, d, buf, h);  // the flip: later dispatches use the new image
         if (rc != PTYPE_OK) return rc;
     }
     std::lock_guard<std::mutex> lk(ctx->image_mu);
@@ -496,7 +543,7 @@ int ptype_b200_broadcast_image(ptype_ctx* ctx, const void* image, size_t bytes, 
     }
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(d->device));
-    int rc = sync_all_streams(d);
+    int rc = copy_stream_waits_for_dispatches(d);
     if (rc != PTYPE_OK) return rc;
     if (!d->d_size) CU(cudaMalloc(&d->d_size, 16));
     unsigned long long total = is_root ? bytes : 0;
@@ -525,6 +572,8 @@ int ptype_b200_broadcast_image(ptype_ctx* ctx, const void* image, size_t bytes, 
     }
     CU(cudaStreamSynchronize(d->copy_stream));
     rc = ptype_b200_image_validate(host.data(), host.size());
+    if (rc != PTYPE_OK) return rc;
+    rc = dispatches_wait_for_copy_stream(d);
     if (rc != PTYPE_OK) return rc;
     rc = adopt_image(ctx, d, buf, *reinterpret_cast<const ptype_image_header*>(host.data()));
     if (rc != PTYPE_OK) return rc;

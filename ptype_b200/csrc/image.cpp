@@ -68,6 +68,7 @@ struct ptype_builder {
     std::string local_addr;
     int max_connections = 0;
     uint32_t forced_slots = 0;
+    bool device_only = false;
     std::map<std::string, ServiceRec> services;
 };
 
@@ -118,6 +119,21 @@ int ptype_b200_builder_register(ptype_builder* b, const char* service, const cha
     NodeRec& n = b->services[service].nodes[node_name];  // Put on an existing key overwrites
     n.address = address;
     n.port = port;
+    return PTYPE_OK;
+}
+
+// Deleting the key services/<service>/<node_name>/ (lease expiry, registry.go:58-83, or an
+// explicit delete as in registry_test.go:179-191).  The service stays known with the nodes left.
+int ptype_b200_builder_unregister(ptype_builder* b, const char* service, const char* node_name) {
+    if (!b || !valid_name(service) || !valid_name(node_name)) return PTYPE_E_INVAL;
+    auto it = b->services.find(service);
+    if (it == b->services.end() || it->second.nodes.erase(node_name) == 0) return PTYPE_E_NOT_FOUND;
+    return PTYPE_OK;
+}
+
+int ptype_b200_builder_set_device_only(ptype_builder* b, int on) {
+    if (!b) return PTYPE_E_INVAL;
+    b->device_only = on != 0;
     return PTYPE_OK;
 }
 
@@ -213,10 +229,11 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     const size_t off_mtable = off;
     off += PTYPE_MTABLE_SLOTS * sizeof(ptype_method);
     const size_t device_bytes = off;
+    const bool host_sections = !b->device_only;
     const size_t off_services = off;
-    off += n_services * sizeof(ptype_service);
+    if (host_sections) off += n_services * sizeof(ptype_service);
     const size_t off_nodes = off;
-    off += n_nodes * sizeof(ptype_node);
+    if (host_sections) off += n_nodes * sizeof(ptype_node);
     const size_t off_strings = off;
 
     std::vector<ptype_service> services(n_services);
@@ -227,12 +244,16 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
         const ServiceRec& rec = b->services[name];
         ptype_service& s = services[i];
         s.key = keys[i];
-        s.name_off = intern(name);
+        s.name_off = host_sections ? intern(name) : 0;
         s.node_base = next_node;
         s.n_nodes = static_cast<uint32_t>(rec.nodes.size());
         s.recv_mask = rec.recv_mask;
         // std::map iterates node names in byte order = key order within the service
         // ("node10" before "node2", like the etcd range).
+        if (!host_sections) {
+            next_node += s.n_nodes;
+            continue;
+        }
         for (const auto& nk : rec.nodes) {
             ptype_node& nd = nodes[next_node++];
             nd.address_off = intern(nk.second.address);
@@ -330,12 +351,14 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
               [&](uint32_t a, uint32_t c) { return services[a].key < services[c].key; });
     std::vector<uint32_t> inv(n_services);
     for (size_t i = 0; i < n_services; ++i) inv[perm[i]] = static_cast<uint32_t>(i);
-    ptype_service* out_services = reinterpret_cast<ptype_service*>(blob + off_services);
-    for (size_t i = 0; i < n_services; ++i) out_services[i] = services[perm[i]];
-    ptype_node* out_nodes = reinterpret_cast<ptype_node*>(blob + off_nodes);
-    for (size_t i = 0; i < n_nodes; ++i) {
-        out_nodes[i] = nodes[i];
-        out_nodes[i].service = inv[nodes[i].service];
+    if (host_sections) {
+        ptype_service* out_services = reinterpret_cast<ptype_service*>(blob + off_services);
+        for (size_t i = 0; i < n_services; ++i) out_services[i] = services[perm[i]];
+        ptype_node* out_nodes = reinterpret_cast<ptype_node*>(blob + off_nodes);
+        for (size_t i = 0; i < n_nodes; ++i) {
+            out_nodes[i] = nodes[i];
+            out_nodes[i].service = inv[nodes[i].service];
+        }
     }
     std::memcpy(blob + off_strings, pool.data(), pool.size());
 
@@ -352,6 +375,7 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     h->n_conn_hash = n_conn;
     h->n_methods = n_methods;
     h->n_receivers = 2;
+    h->host_sections = host_sections ? 1u : 0u;
     h->off_slots = static_cast<uint32_t>(off_slots);
     h->off_conn_hash = static_cast<uint32_t>(off_conn);
     h->off_methods = static_cast<uint32_t>(off_methods);
@@ -386,8 +410,8 @@ int ptype_b200_image_validate(const void* image, size_t bytes) {
         !inside(h->off_methods, uint64_t(h->n_methods) * sizeof(ptype_method)) ||
         !inside(h->off_mtable, uint64_t(PTYPE_MTABLE_SLOTS) * sizeof(ptype_method)) ||
         (h->off_mtable & 15u) || !(h->method_mul & 1u) ||
-        !inside(h->off_services, uint64_t(h->n_services) * sizeof(ptype_service)) ||
-        !inside(h->off_nodes, uint64_t(h->n_nodes) * sizeof(ptype_node)) ||
+        (h->host_sections && (!inside(h->off_services, uint64_t(h->n_services) * sizeof(ptype_service)) ||
+                              !inside(h->off_nodes, uint64_t(h->n_nodes) * sizeof(ptype_node)))) ||
         !inside(h->off_strings, h->strings_bytes) || h->device_bytes > bytes ||
         h->device_bytes < h->off_mtable + PTYPE_MTABLE_SLOTS * sizeof(ptype_method))
         return PTYPE_E_BAD_IMAGE;
@@ -400,6 +424,7 @@ int ptype_b200_image_validate(const void* image, size_t bytes) {
 
 static const ptype_service* find_service(const void* image, const char* service) {
     const ptype_image_header* h = static_cast<const ptype_image_header*>(image);
+    if (!h->host_sections) return nullptr;
     const unsigned char* p = static_cast<const unsigned char*>(image);
     const ptype_service* sv = reinterpret_cast<const ptype_service*>(p + h->off_services);
     const char* pool = reinterpret_cast<const char*>(p + h->off_strings);
@@ -435,7 +460,7 @@ int ptype_b200_image_node(const void* image, uint32_t node_id, char* address, si
                           size_t node_name_cap) {
     if (!image) return PTYPE_E_INVAL;
     const ptype_image_header* h = static_cast<const ptype_image_header*>(image);
-    if (node_id >= h->n_nodes) return PTYPE_E_NOT_FOUND;
+    if (node_id >= h->n_nodes || !h->host_sections) return PTYPE_E_NOT_FOUND;
     const unsigned char* p = static_cast<const unsigned char*>(image);
     const ptype_node* nd = reinterpret_cast<const ptype_node*>(p + h->off_nodes) + node_id;
     const ptype_service* sv = reinterpret_cast<const ptype_service*>(p + h->off_services);

@@ -90,6 +90,15 @@ class ImageBuilder:
                                               address.encode(), port), "builder_register")
         return self
 
+    def unregister(self, service: str, node_name: str) -> "ImageBuilder":
+        check(lib.ptype_b200_builder_unregister(self._b, service.encode(), node_name.encode()),
+              "builder_unregister")
+        return self
+
+    def set_device_only(self, on: bool = True) -> "ImageBuilder":
+        check(lib.ptype_b200_builder_set_device_only(self._b, 1 if on else 0), "builder_set_device_only")
+        return self
+
     def declare(self, service: str) -> "ImageBuilder":
         check(lib.ptype_b200_builder_declare(self._b, service.encode()), "builder_declare")
         return self

@@ -280,6 +280,55 @@ def test_snapshot_flip_between_batches(ctx, oracle):
     assert np.all(rep["value"] == 0)
 
 
+def test_live_updates_without_stopping_the_stream(ctx, oracle):
+    """BASELINE config 5 in miniature: snapshots are published while batches are in flight
+    (no host synchronisation in between); every batch is answered from the snapshot that was
+    current when it was submitted - the epoch flips at batch boundaries (rpc.go:233-236)."""
+    base = w.stress_registry(400, 6)
+    b = p.ImageBuilder(base.local_addr, base.max_connections)
+    for svc, node, addr, port in base.nodes:
+        b.register(svc, node, addr, port)
+    for svc, recv in base.expose:
+        b.expose(svc, recv)
+    b.set_device_only(True)
+    nodes = list(base.nodes)
+    n, per_epoch = 200_000, 4
+    images, d_reqs, d_reps, wants = [], [], [], []
+    rng = np.random.default_rng(5)
+    for epoch in range(1, 7):
+        if epoch > 1:     # one node of a random service leaves, or comes back
+            s = int(rng.integers(0, 400))
+            name = (f"svc_{s:05d}", f"node_{int(rng.integers(0, 6)):02d}")
+            hit = [x for x in nodes if (x[0], x[1]) == name]
+            if hit:
+                nodes.remove(hit[0])
+                b.unregister(*name)
+            else:
+                nodes.append((name[0], name[1], "10.9.9.9", 9999))
+                b.register(name[0], name[1], "10.9.9.9", 9999)
+        images.append(b.finish(epoch))
+        spec = w.RegistrySpec(sorted(nodes), base.expose, [], base.local_addr, base.max_connections)
+        kv, snap = oracle.snapshot_from_spec(spec)
+        for k in range(per_epoch):
+            req = w.stress_calls(n, 400, seed=1000 * epoch + k)
+            d_reqs.append(ctx.device_buffer(n * 48).upload(req))
+            d_reps.append(ctx.device_buffer(n * 16))
+            wants.append(snap.dispatch(req, threads=8))
+    assert len({img.blob[192:img.header.device_bytes] for img in images}) == len(images)
+    # everything is resident: now publish and submit back to back, no synchronisation
+    for e, img in enumerate(images):
+        ctx.publish(img)
+        lo = e * per_epoch
+        ctx.dispatch_batches(ctx.make_batches(zip(d_reqs[lo:lo + per_epoch], d_reps[lo:lo + per_epoch],
+                                                  [n] * per_epoch)), sync=False)
+    assert ctx.epoch() == len(images)
+    ctx.sync()
+    for d, want in zip(d_reps, wants):
+        assert_same(d.download(p.REPLY_DTYPE, n), want)
+    for d in d_reqs + d_reps:
+        d.free()
+
+
 def test_max_connections_larger_than_shared_cache(ctx, oracle):
     """MaxConnections above the 256 hashes kept in shared memory: hashes read from global."""
     nodes = [("wide", f"n{i:04d}", f"10.1.{i >> 8}.{i & 255}", 7000) for i in range(700)]

@@ -166,6 +166,30 @@ def test_method_table_is_a_perfect_hash():
         assert (e["m"], e["r"], e["op"]) == (m, r, op)
 
 
+def test_unregister_and_device_only_images(oracle):
+    """A node's key goes away (lease expiry / delete, registry_test.go:179-191): the rebuilt image
+    selects from the nodes left, like the oracle after the same delete.  Device-only images carry
+    just what the kernels read."""
+    spec = w.calculator_registry()
+    b = p.ImageBuilder(spec.local_addr, spec.max_connections)
+    for svc, node, addr, port in spec.nodes:
+        b.register(svc, node, addr, port)
+    b.expose("calculator", "Calculator")
+    kv, snap = oracle.snapshot_from_spec(spec)
+    assert b.finish(1).selected("calculator") == snap.selected("calculator")
+    b.unregister("calculator", "calculator_node_04")
+    assert kv.delete("services/calculator/calculator_node_04/") == 1
+    snap2 = oracle.Snapshot(kv, spec.local_addr, spec.max_connections, [], 0, spec.expose)
+    img2 = b.finish(2)
+    assert img2.header.n_nodes == 15 and img2.selected("calculator") == snap2.selected("calculator")
+    with pytest.raises(p.PtypeError):
+        b.unregister("calculator", "calculator_node_04")
+    small = b.set_device_only(True).finish(3)
+    assert small.header.host_sections == 0 and small.header.n_nodes == 15
+    assert len(small) < len(img2) and small.selected("calculator") is None
+    assert small.blob[192:small.header.device_bytes] == img2.blob[192:img2.header.device_bytes]
+
+
 def test_split_work_generator(oracle):
     for t in (-5, 0, 1, 9, 10, 11, 91, 100, 1000, 12345):
         buf = (C.c_int64 * (3 * 2000))()
