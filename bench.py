@@ -35,8 +35,8 @@ sys.path.insert(0, str(ROOT))
 BYTES_PER_CALL = 64  # 48 B request + 16 B reply
 BATCH = 1 << 20
 # calls per step (per GPU) and resident batches rotated, per workload: C3 is quoted on 16M calls
-BATCH_OF = {"c2": 1 << 20, "c2mesh": 1 << 20, "c3": 1 << 24, "c4": 1 << 20}
-BUFFERS_OF = {"c2": 8, "c2mesh": 8, "c3": 2, "c4": 8}
+BATCH_OF = {"c2": 1 << 20, "c2mesh": 1 << 20, "c3": 1 << 24, "c4": 1 << 20, "c5": 1 << 20}
+BUFFERS_OF = {"c2": 8, "c2mesh": 8, "c3": 2, "c4": 8, "c5": 8}
 
 
 def measured_peak():
@@ -55,7 +55,7 @@ def make_workload(name: str, n: int, seed: int, salt: int = 0):
         return w.calculator_registry(), w.calculator_calls(n, seed=seed, salt=salt)
     if name == "c2mesh":
         return w.calculator_registry(mesh=True), w.calculator_calls(n, seed=seed, salt=salt)
-    if name == "c3":
+    if name in ("c3", "c5"):
         return w.stress_registry(10_000, 64), w.stress_calls(n, 10_000, seed=seed, salt=salt)
     if name == "c4":
         return w.optimus_registry(), w.optimus_calls(n, seed=seed, salt=salt)[:n]
@@ -67,6 +67,8 @@ WORKLOAD_TEXT = {
     "c2mesh": "calculator batch of 2^20 mixed Add/Multiply calls, 1 service x 16 nodes, mesh",
     "c3": "registry lookup stress: 10k services x 64 nodes, batches of 2^24 routed calls (1% unregistered)",
     "c4": "example/optimus splitWork stream replayed as batches of 2^20 Prime.Check calls",
+    "c5": "sharded stream over the 10k x 64 registry, 2^20 routed calls per GPU per step, live registry "
+          "snapshot updates (one node leaves or joins) broadcast to every GPU between batches",
 }
 
 
@@ -223,6 +225,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = auto (about 1 s)")
     ap.add_argument("--cpu-seconds", type=float, default=8.0)
     ap.add_argument("--flags", type=int, default=0, help="extra dispatch flags (4 = probe table in L2)")
+    ap.add_argument("--update-every", type=int, default=64, help="c5: steps between snapshot updates")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -252,14 +255,48 @@ def main():
     ctx = p.Context([local_rank])
     # ---- registry snapshot: built on rank 0, replicated to every GPU over NCCL
     spec, _ = make_workload(args.workload, 32, 1)
+    live = args.workload == "c5"
+    builder = None
+    if live and rank == 0:   # a builder kept alive: each update changes one key and re-emits
+        builder = p.ImageBuilder(spec.local_addr, spec.max_connections)
+        for svc, node, addr, port in spec.nodes:
+            builder.register(svc, node, addr, port)
+        for svc, recv in spec.expose:
+            builder.expose(svc, recv)
+        builder.set_device_only(True)
+    first_image = (builder.finish(1) if live else spec.image(epoch=1)) if rank == 0 or not multi else None
     if multi:
         ids = [p.Context.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         ctx.comm_init(ids[0], rank, world)
-        image = ctx.broadcast_image(spec.image(epoch=1) if rank == 0 else None, root=0)
+        image = ctx.broadcast_image(first_image, root=0)
     else:
-        image = spec.image(epoch=1)
+        image = first_image
         ctx.publish(image)
+    live_nodes = {(x[0], x[1]): x for x in spec.nodes} if live else {}
+    live_rng = np.random.default_rng(0x5EED0005)
+    update_ms = []
+
+    def live_update(epoch: int):
+        """One registry change on rank 0 (a random node leaves, or a departed one returns), a new
+        device-only image, and its installation on every GPU: ncclBroadcast, or publish on 1 GPU."""
+        t0 = time.perf_counter()
+        img = None
+        if rank == 0:
+            svc = f"svc_{int(live_rng.integers(0, 10_000)):05d}"
+            node = f"node_{int(live_rng.integers(0, 64)):02d}"
+            if (svc, node) in live_nodes:
+                del live_nodes[(svc, node)]
+                builder.unregister(svc, node)
+            else:
+                live_nodes[(svc, node)] = (svc, node, "10.99.0.1", 9000)
+                builder.register(svc, node, "10.99.0.1", 9000)
+            img = builder.finish(epoch)
+        if multi:
+            ctx.broadcast_image(img, root=0)
+        else:
+            ctx.publish(img)
+        update_ms.append((time.perf_counter() - t0) * 1e3)
 
     # ---- per-rank shard of the step's global stream, `buffers` distinct steps resident in HBM
     nbuf = args.buffers or BUFFERS_OF[args.workload]
@@ -297,7 +334,16 @@ def main():
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     w0 = time.perf_counter()
     ev0.record(ext)
-    ctx.dispatch_batches(timed, flags=args.flags, sync=False)
+    if live:
+        every = max(args.update_every, 1)
+        for lo in range(0, args.steps, every):
+            seg = ctx.make_batches((d_reqs[i % nbuf], d_reps[i % nbuf], counts[i % nbuf])
+                                   for i in range(lo, min(lo + every, args.steps)))
+            ctx.dispatch_batches(seg, flags=args.flags, sync=False)
+            if lo + every < args.steps:
+                live_update(2 + lo // every)
+    else:
+        ctx.dispatch_batches(timed, flags=args.flags, sync=False)
     ev1.record(ext)
     barrier()
     w1 = time.perf_counter()
@@ -348,7 +394,7 @@ def main():
     # (*Client).CallBatch submits - arguments plus a method byte per call instead of 48-byte
     # records.  Only for the single-service workloads.
     e2e_compact = None
-    if args.workload != "c3" and not multi:
+    if args.workload not in ("c3", "c5") and not multi:
         import ptype_b200.workloads as wl
         key, base, methods, sel, cargs = wl.as_client_batch(hb)
         pin_args = p.PinnedArray(cargs.size, np.int64)
@@ -390,6 +436,11 @@ def main():
     cpu_baseline = None
     if rank == 0:
         from oracle import binding as ob
+        if live:   # the registry as it stands after the last update
+            import ptype_b200.workloads as wl
+            spec = wl.RegistrySpec(sorted(live_nodes.values()), spec.expose, [], spec.local_addr,
+                                   spec.max_connections)
+            ctx.dispatch_device(d_reqs[0], counts[0], d_reps[0], flags=args.flags)
         kv, snap = ob.snapshot_from_spec(spec, image.salt)
         want = snap.dispatch(hb, check_limit=1 << 16, threads=os.cpu_count() or 1)
         got = d_reps[0].download(p.REPLY_DTYPE, counts[0])
@@ -402,7 +453,7 @@ def main():
             rate, passes, el, _ = cpu_port_rate(spec, hb, threads, args.cpu_seconds)
             rate1, passes1, el1, _ = cpu_port_rate(spec, hb, 1, min(2.0, args.cpu_seconds))
             lb = loopback_rate(hb, 1, min(len(hb), 20_000), 3 if args.workload != "c4" else 2,
-                               2 if args.workload == "c4" else 1) if args.workload != "c3" else None
+                               2 if args.workload == "c4" else 1) if args.workload not in ("c3", "c5") else None
             cpu_baseline = {"value": rate, "unit": "calls/s", "cores": threads, "kind": "port",
                             "loopback_config1": lb,
                             "sample": f"{passes} passes over one {len(hb)}-call batch of the same workload "
@@ -443,6 +494,10 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
         }
+        if live:
+            line["config"]["live_updates"] = {"count": len(update_ms), "every_steps": args.update_every,
+                                              "host_ms_avg": float(np.mean(update_ms)) if update_ms else None,
+                                              "transport": "ncclBroadcast" if multi else "publish (1 GPU)"}
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
         print(json.dumps(line), flush=True)
