@@ -344,6 +344,7 @@ def main():
                 live_update(2 + lo // every)
     else:
         ctx.dispatch_batches(timed, flags=args.flags, sync=False)
+    host_enqueue_s = time.perf_counter() - w0
     ev1.record(ext)
     barrier()
     w1 = time.perf_counter()
@@ -492,6 +493,7 @@ def main():
             "e2e": e2e_compact if e2e_compact is not None else e2e_records,
             "e2e_records": e2e_records,
             "gpu_launches": int(launches),
+            "host_enqueue_us_per_step": host_enqueue_s / args.steps * 1e6,
             "clocks": clocks,
         }
         if live:

@@ -286,6 +286,8 @@ int ptype_b200_broadcast_image(ptype_ctx*, const void* image, size_t bytes, int 
 #define PTYPE_F_GLOBAL_TABLE 4u/* measurement switch: probe the table in L2, not shared memory  */
 #define PTYPE_F_LDG_LOADS 8u   /* measurement switch: fetch requests with LDG + shuffle transpose */
 #define PTYPE_F_BULK_LOADS 16u /* measurement switch: stage requests with bulk-async copies      */
+#define PTYPE_F_ONE_LAUNCH_PER_BATCH 32u /* dispatch_batches: one kernel launch per batch instead of
+                                            one launch per group of up to 96 batches               */
 
 /* Optional per-batch outputs (all device-written; host copies made on sync). */
 typedef struct ptype_batch_stats {
@@ -308,10 +310,11 @@ int ptype_b200_dispatch(ptype_ctx*, int dev, const ptype_req* reqs, size_t n, pt
 int ptype_b200_dispatch_ex(ptype_ctx*, int dev, const ptype_req* reqs, size_t n,
                            ptype_reply* replies, uint32_t* failed_idx, size_t failed_cap,
                            ptype_batch_stats* stats, uint32_t flags);
-/* Several device-resident batches in one call: the launches are enqueued back to back
- * on the context's stream (consecutive kernels overlap their ramp-up and drain through
- * programmatic dependent launch) and the call returns without waiting unless
- * PTYPE_F_ASYNC is absent.  This is what a host pipelining the batches of many Clients
+/* Several device-resident batches in one call.  Groups of up to 96 batches run as ONE
+ * kernel launch whose persistent grid walks all their tiles as a single stream (no gap or
+ * ramp between batches); with PTYPE_F_ONE_LAUNCH_PER_BATCH, or when the registry table is
+ * probed in L2, every batch is its own launch and consecutive kernels overlap through
+ * programmatic dependent launch.  Returns without waiting when PTYPE_F_ASYNC is set.  This is what a host pipelining the batches of many Clients
  * (one Client per service, cluster/cluster.go:101-103) submits per scheduling round. */
 typedef struct ptype_batch {
     const ptype_req* reqs; /* device pointer */

@@ -28,7 +28,7 @@ ST_COUNT = 8
 NO_NODE = 0xFFFFFFFF
 RECV_ILL_FORMED = 0xFFFFFFFF
 
-F_DEVICE_PTRS, F_ASYNC, F_GLOBAL_TABLE, F_LDG_LOADS, F_BULK_LOADS = 1, 2, 4, 8, 16
+F_DEVICE_PTRS, F_ASYNC, F_GLOBAL_TABLE, F_LDG_LOADS, F_BULK_LOADS, F_ONE_LAUNCH_PER_BATCH = 1, 2, 4, 8, 16, 32
 
 E_OK, E_INVAL, E_NOMEM, E_CUDA, E_NO_IMAGE, E_BAD_IMAGE = 0, 1, 2, 3, 4, 5
 E_COLLISION, E_NCCL, E_LIMIT, E_NOT_FOUND, E_BUSY = 6, 7, 8, 9, 10

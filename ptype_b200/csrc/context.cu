@@ -706,13 +706,37 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
     const ptype::DeviceImage img = d->view[buf];
     const ptype::LaunchPlan& plan = d->plan[buf][plan_kind(flags)][0];
     for (size_t b = 0; b < count; ++b) {
-        const ptype_batch& bt = batches[b];
-        if (bt.n == 0) continue;
-        if (!bt.reqs || !bt.replies) return PTYPE_E_INVAL;
-        if (bt.n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
-        CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, bt.n, d->sm_count), bt.reqs, bt.n,
-                                  bt.replies, nullptr, 0u, 0u, nullptr, d->stream));
-        ctx->launches.fetch_add(1);
+        if (batches[b].n && (!batches[b].reqs || !batches[b].replies)) return PTYPE_E_INVAL;
+        if (batches[b].n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
+    }
+    if (!plan.bulk && !(flags & PTYPE_F_ONE_LAUNCH_PER_BATCH)) {
+        // One launch per group of batches: the persistent grid walks their tiles as one
+        // stream.  Groups are cut so that a launch stays below 2^32 tiles.
+        const size_t group = static_cast<size_t>(ptype::max_batches_per_launch());
+        size_t b = 0;
+        while (b < count) {
+            size_t e = b;
+            uint64_t tiles = 0;
+            while (e < count && e - b < group && tiles + (batches[e].n + 31) / 32 < 0xFFFFFFFFull) {
+                tiles += (batches[e].n + 31) / 32;
+                ++e;
+            }
+            if (e == b) return PTYPE_E_LIMIT;
+            if (tiles) {
+                CU(ptype::launch_dispatch_multi(img, plan, d->sm_count, batches + b, static_cast<int>(e - b),
+                                                d->stream));
+                ctx->launches.fetch_add(1);
+            }
+            b = e;
+        }
+    } else {
+        for (size_t b = 0; b < count; ++b) {
+            const ptype_batch& bt = batches[b];
+            if (bt.n == 0) continue;
+            CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, bt.n, d->sm_count), bt.reqs, bt.n,
+                                      bt.replies, nullptr, 0u, 0u, nullptr, d->stream));
+            ctx->launches.fetch_add(1);
+        }
     }
     if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
     return PTYPE_OK;

@@ -46,6 +46,9 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
                             const ptype_req* reqs, size_t n, ptype_reply* replies, uint32_t* failed_idx,
                             uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
                             cudaStream_t stream);
+int max_batches_per_launch();
+cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
+                                  const ptype_batch* batches, int count, cudaStream_t stream);
 cudaError_t launch_call_batch(const DeviceImage& img, const LaunchPlan& plan, int blocks,
                               uint64_t svc_key, uint64_t seq_base, const uint32_t* methods,
                               const uint32_t* recvs, int n_methods, const int64_t* args,

@@ -566,6 +566,97 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     griddep_wait();
 }
 
+// ------------------------------------------- kernel, many batches per launch
+//
+// ptype_b200_dispatch_batches: the tiles of up to kMaxBatchesPerLaunch batches form one
+// tile stream that the persistent grid walks without ever draining - no launch gap, no
+// ramp between batches, and one launch per ~hundred batches on the host side.
+constexpr int kMaxBatchesPerLaunch = 96;
+struct BatchList {
+    const uint4* reqs[kMaxBatchesPerLaunch];
+    uint4* replies[kMaxBatchesPerLaunch];
+    uint32_t n[kMaxBatchesPerLaunch];
+    uint32_t tile_end[kMaxBatchesPerLaunch];  // running total of 32-call tiles (< 2^32 per launch)
+    int count;
+};
+
+template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas>
+__global__ void __launch_bounds__(kThreads, kMinCtas)
+    dispatch_multi_kernel(const DeviceImage img, const __grid_constant__ BatchList list) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ __align__(16) CtaShared sh;
+
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+    const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
+    griddep_launch_dependents();
+
+    uint32_t send_reg[3];  // transpose plan, see dispatch_kernel
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const uint32_t r = ((lane - c) * 11u) & 31u;
+        send_reg[c] = (3u * r + c) >> 5;
+    }
+    const uint32_t total_tiles = list.tile_end[list.count - 1];
+    const uint32_t total_warps = gridDim.x * warps_per_cta;
+    const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
+
+    LookupCache cache;
+    bool table_ready = !kSmemTable;
+    int cursor[kUnroll];  // batch holding each in-flight tile; tiles only move forward
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) cursor[u] = 0;
+
+    for (uint32_t g0 = warp_global; g0 < total_tiles; g0 += total_warps * kUnroll) {
+        uint4 ld[kUnroll][3];
+        uint32_t tile[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const uint32_t g = g0 + u * total_warps;
+            tile[u] = 0;
+            ld[u][0] = ld[u][1] = ld[u][2] = make_uint4(0, 0, 0, 0);
+            if (g < total_tiles) {
+                int b = cursor[u];
+                while (g >= list.tile_end[b]) ++b;
+                cursor[u] = b;
+                tile[u] = g - (b ? list.tile_end[b - 1] : 0u);
+                const size_t n_chunks = static_cast<size_t>(list.n[b]) * 3;
+                const uint4* reqs = list.reqs[b];
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    const size_t c = static_cast<size_t>(tile[u]) * 96 + j * 32 + lane;
+                    if (c < n_chunks) ld[u][j] = ld_stream(reqs + c);
+                }
+            }
+        }
+        if (!table_ready) {
+            mbar_wait(&sh.table_bar, 0);
+            table_ready = true;
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            if (g0 + u * total_warps >= total_tiles) break;  // warp-uniform
+            uint4 q[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const uint32_t sr = send_reg[c];
+                const uint4 snd = sr == 0 ? ld[u][0] : (sr == 1 ? ld[u][1] : ld[u][2]);
+                const uint32_t src = (3u * lane + c) & 31u;
+                q[c].x = __shfl_sync(kFull, snd.x, src);
+                q[c].y = __shfl_sync(kFull, snd.y, src);
+                q[c].z = __shfl_sync(kFull, snd.z, src);
+                q[c].w = __shfl_sync(kFull, snd.w, src);
+            }
+            const int b = cursor[u];
+            const size_t idx = (static_cast<size_t>(tile[u]) << 5) + lane;
+            if (idx < list.n[b])
+                st_stream(list.replies[b] + idx, dispatch_one<kSmemTable>(img, sh, slots, cache, q[0], q[1], q[2]));
+        }
+    }
+    if (!table_ready) mbar_wait(&sh.table_bar, 0);
+    griddep_wait();
+}
+
 // ------------------------------------------------ kernel, one Client's batch
 //
 // What (*Client).CallBatch submits: every call names the same service and the batch owns
@@ -836,6 +927,50 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
                                                 failed_cap, idx_base, stats, stream)
                   : launch_variant<false, false>(img, plan, blocks, reqs, n, replies, failed_idx,
                                                  failed_cap, idx_base, stats, stream);
+}
+
+// Up to kMaxBatchesPerLaunch device-resident batches in ONE launch (LDG-shaped plans only).
+int max_batches_per_launch() { return kMaxBatchesPerLaunch; }
+
+cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
+                                  const ptype_batch* batches, int count, cudaStream_t stream) {
+    BatchList list = {};
+    uint64_t tiles = 0;
+    int m = 0;
+    for (int b = 0; b < count; ++b) {
+        if (batches[b].n == 0) continue;
+        list.reqs[m] = reinterpret_cast<const uint4*>(batches[b].reqs);
+        list.replies[m] = reinterpret_cast<uint4*>(batches[b].replies);
+        list.n[m] = static_cast<uint32_t>(batches[b].n);
+        tiles += (batches[b].n + 31) / 32;
+        list.tile_end[m] = static_cast<uint32_t>(tiles);
+        ++m;
+    }
+    if (m == 0) return cudaSuccess;
+    if (tiles >= 0xFFFFFFFFull) return cudaErrorInvalidValue;
+    list.count = m;
+    const size_t warps_per_cta = static_cast<size_t>(plan.threads) / 32;
+    size_t want = (tiles + warps_per_cta - 1) / warps_per_cta;
+    const size_t resident = static_cast<size_t>(sm_count) * plan.ctas_per_sm;
+    const int blocks = static_cast<int>(want < resident ? (want ? want : 1) : resident);
+    if (plan.threads == kMaxThreads) {
+        if (plan.smem_table) {
+            auto k = dispatch_multi_kernel<true, 2, kMaxThreads, 1>;
+            if (plan.dyn_smem > 48 * 1024) {
+                cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                     static_cast<int>(plan.dyn_smem));
+                if (e != cudaSuccess) return e;
+            }
+            return launch_kernel(k, blocks, plan.threads, plan.dyn_smem, stream, img, list);
+        }
+        return launch_kernel(dispatch_multi_kernel<false, 2, kMaxThreads, 1>, blocks, plan.threads,
+                             plan.dyn_smem, stream, img, list);
+    }
+    if (plan.smem_table)
+        return launch_kernel(dispatch_multi_kernel<true, kSmallUnroll, kSmallThreads, kSmallMinCtas>, blocks,
+                             plan.threads, plan.dyn_smem, stream, img, list);
+    return launch_kernel(dispatch_multi_kernel<false, kSmallUnroll, kSmallThreads, kSmallMinCtas>, blocks,
+                         plan.threads, plan.dyn_smem, stream, img, list);
 }
 
 namespace {

@@ -383,7 +383,9 @@ def test_dispatch_batches_equals_one_by_one(ctx, oracle):
     d_reqs = [ctx.device_buffer(max(n, 1) * 48).upload(r) for n, r in zip(sizes, reqs)]
     d_reps = [ctx.device_buffer(max(n, 1) * 16) for n in sizes]
     batches = ctx.make_batches(zip(d_reqs, d_reps, sizes))
-    for flags in (0, p.F_BULK_LOADS):
+    for flags in (0, p.F_ONE_LAUNCH_PER_BATCH, p.F_BULK_LOADS, p.F_GLOBAL_TABLE):
+        for d in d_reps:                       # poison, so stale replies cannot pass
+            d.upload(np.full(4, 0xAB, dtype=np.uint8))
         ctx.dispatch_batches(batches, flags=flags, sync=False)
         ctx.sync()
         for n, r, d in zip(sizes, reqs, d_reps):
