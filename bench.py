@@ -488,7 +488,8 @@ def main():
                        "table": "shared memory" if not (args.flags & 4) else "global/L2"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_kind": peak_kind,
-                         "kernel": "dispatch_kernel", "algorithmic_bytes_per_call": BYTES_PER_CALL,
+                         "kernel": "dispatch_kernel (one launch per batch)" if (args.flags & 32) else
+                                   "dispatch_multi_kernel (one persistent launch per 96 batches)", "algorithmic_bytes_per_call": BYTES_PER_CALL,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
             "e2e": e2e_compact if e2e_compact is not None else e2e_records,
             "e2e_records": e2e_records,

@@ -384,6 +384,27 @@ int ptype_b200_reply_checksum(ptype_ctx*, int dev, const ptype_reply* replies, s
 int ptype_b200_reply_checksum_noalloc(int device, const ptype_reply* d_replies, size_t n,
                                       uint64_t index_base, uint64_t* d_checksum, void* cuda_stream);
 
+/* ---------------------------------------------- formats either side of the path */
+/* All pointers below are DEVICE pointers on `dev`; the calls wait for completion.
+ *
+ * resolve_names: "Receiver.Method" strings -> hashes, split at the last '.' like net/rpc's
+ * server (readRequestHeader [Go 1.13 net/rpc]).  names holds n NUL-padded strings of `stride`
+ * bytes each (stride a multiple of 16; a string that fills its slot needs no NUL).  out[j]
+ * (may be NULL) receives the pair; patch (may be NULL) gets reqs[j].method/.recv written. */
+int ptype_b200_resolve_names(ptype_ctx*, int dev, const char* names, uint32_t stride, size_t n,
+                             ptype_method_ref* out, ptype_req* patch);
+/* gob_encode_replies: the reply VALUES as encoding/gob messages, `LL 04 00 <int>` each, in
+ * call order, nothing for replies whose status is not OK (their body is net/rpc's empty
+ * invalidRequest).  offsets[0..n] receive the byte position of every message (offsets[n] =
+ * total); out receives the bytes that fit in out_cap; *total_bytes the size needed. */
+int ptype_b200_gob_encode_replies(ptype_ctx*, int dev, const ptype_reply* replies, size_t n,
+                                  uint64_t* offsets, uint8_t* out, size_t out_cap, uint64_t* total_bytes);
+/* gob_decode_args: n gob struct bodies of calculator.Args / prime.Args (field delta, gob int)*
+ * 00, zero fields omitted; body j spans bytes[offsets[j] .. offsets[j+1]).  args receives
+ * args_per_call int64 per call, status[j] (may be NULL) 0 = ok, 1 = malformed. */
+int ptype_b200_gob_decode_args(ptype_ctx*, int dev, const uint8_t* bytes, const uint64_t* offsets, size_t n,
+                               int64_t* args, int args_per_call, uint8_t* status);
+
 /* Kernel launches issued by this context so far (bench bookkeeping). */
 int ptype_b200_launch_count(ptype_ctx*, uint64_t* launches);
 

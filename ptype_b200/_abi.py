@@ -117,6 +117,9 @@ SIGNATURES = [
      [_vp, C.c_int, _vp, C.c_size_t, C.c_uint64, _u64p, C.c_uint32]),
     ("ptype_b200_reply_checksum_noalloc", C.c_int,
      [C.c_int, _vp, C.c_size_t, C.c_uint64, _vp, _vp]),
+    ("ptype_b200_resolve_names", C.c_int, [_vp, C.c_int, _vp, C.c_uint32, C.c_size_t, _vp, _vp]),
+    ("ptype_b200_gob_encode_replies", C.c_int, [_vp, C.c_int, _vp, C.c_size_t, _vp, _vp, C.c_size_t, _u64p]),
+    ("ptype_b200_gob_decode_args", C.c_int, [_vp, C.c_int, _vp, _vp, C.c_size_t, _vp, C.c_int, _vp]),
     ("ptype_b200_launch_count", C.c_int, [_vp, _u64p]),
 ]
 

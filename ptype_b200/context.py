@@ -196,6 +196,53 @@ class Context:
         check(lib.ptype_b200_dispatch_batches(self._h, dev, batches, len(batches), f),
               "dispatch_batches")
 
+    # ---- formats either side of the path (device buffers) ----------------------
+    def resolve_names(self, names: Sequence[str], stride: int = 32, *, dev: int = 0) -> np.ndarray:
+        """"Receiver.Method" strings -> [(method, recv)] hashes computed on the device."""
+        n = len(names)
+        host = np.zeros((n, stride), dtype=np.uint8)
+        for j, s in enumerate(names):
+            b = s.encode()[:stride]
+            host[j, : len(b)] = np.frombuffer(b, dtype=np.uint8)
+        d_names = self.device_buffer(max(host.nbytes, 16), dev).upload(host)
+        d_out = self.device_buffer(max(n, 1) * 8, dev)
+        check(lib.ptype_b200_resolve_names(self._h, dev, d_names.ptr, stride, n, d_out.ptr, None),
+              "resolve_names")
+        out = d_out.download(np.dtype([("method", "<u4"), ("recv", "<u4")]), n)
+        d_names.free()
+        d_out.free()
+        return out
+
+    def gob_encode_replies(self, d_replies, n: int, *, dev: int = 0):
+        """Reply values as gob messages: returns (offsets[n+1], bytes)."""
+        d_off = self.device_buffer((n + 1) * 8, dev)
+        total = C.c_uint64()
+        check(lib.ptype_b200_gob_encode_replies(self._h, dev, _ptr(d_replies), n, d_off.ptr, None, 0,
+                                                C.byref(total)), "gob_encode_replies")
+        d_out = self.device_buffer(max(total.value, 1), dev)
+        check(lib.ptype_b200_gob_encode_replies(self._h, dev, _ptr(d_replies), n, d_off.ptr, d_out.ptr,
+                                                total.value, C.byref(total)), "gob_encode_replies")
+        off = d_off.download(np.uint64, n + 1)
+        data = d_out.download(np.uint8, total.value)
+        d_off.free()
+        d_out.free()
+        return off, data
+
+    def gob_decode_args(self, data: np.ndarray, offsets: np.ndarray, args_per_call: int, *, dev: int = 0):
+        """gob Args bodies -> (args[n, args_per_call], status[n])."""
+        n = len(offsets) - 1
+        d_bytes = self.device_buffer(max(len(data), 1), dev).upload(np.ascontiguousarray(data, dtype=np.uint8))
+        d_off = self.device_buffer((n + 1) * 8, dev).upload(np.ascontiguousarray(offsets, dtype=np.uint64))
+        d_args = self.device_buffer(max(n, 1) * 8 * args_per_call, dev)
+        d_st = self.device_buffer(max(n, 1), dev)
+        check(lib.ptype_b200_gob_decode_args(self._h, dev, d_bytes.ptr, d_off.ptr, n, d_args.ptr,
+                                             args_per_call, d_st.ptr), "gob_decode_args")
+        args = d_args.download(np.int64, n * args_per_call).reshape(n, args_per_call)
+        st = d_st.download(np.uint8, n)
+        for b in (d_bytes, d_off, d_args, d_st):
+            b.free()
+        return args, st
+
     def sync(self, dev: int = 0) -> None:
         check(lib.ptype_b200_sync(self._h, dev), "sync")
 

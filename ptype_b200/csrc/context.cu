@@ -138,6 +138,8 @@ struct DeviceState {
     unsigned long long* d_cksum_partials = nullptr;  // scratch of the checksum kernel
     unsigned long long* d_cksum_out = nullptr;
     unsigned long long* d_size = nullptr;  // broadcast header scratch
+    void* d_codec = nullptr;               // scratch of the gob encoder (lengths, block sums)
+    size_t codec_cap = 0;
     cudaEvent_t drained[1 + kPipe] = {};   // "everything enqueued so far" markers, one per dispatch stream
     cudaEvent_t image_ready = nullptr;     // the inactive buffer holds the new image
     void* h_stage[2] = {nullptr, nullptr}; // page-locked copies of the published blobs' device part
@@ -334,6 +336,7 @@ void ptype_b200_close(ptype_ctx* ctx) {
         if (d->d_cksum_partials) cudaFree(d->d_cksum_partials);
         if (d->d_cksum_out) cudaFree(d->d_cksum_out);
         if (d->d_size) cudaFree(d->d_size);
+        if (d->d_codec) cudaFree(d->d_codec);
         for (int i = 0; i <= kPipe; ++i)
             if (d->drained[i]) cudaEventDestroy(d->drained[i]);
         if (d->image_ready) cudaEventDestroy(d->image_ready);
@@ -865,6 +868,59 @@ int ptype_b200_reply_checksum(ptype_ctx* ctx, int dev, const ptype_reply* replie
     if (tmp) cudaFree(tmp);
     if (e != cudaSuccess) return cuda_fail(e, "reply_checksum");
     *checksum = out;
+    return PTYPE_OK;
+}
+
+int ptype_b200_resolve_names(ptype_ctx* ctx, int dev, const char* names, uint32_t stride, size_t n,
+                             ptype_method_ref* out, ptype_req* patch) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || (n && !names) || stride == 0 || (stride & 15u) || (!out && !patch)) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(d->device));
+    CU(ptype::launch_resolve_names(reinterpret_cast<const unsigned char*>(names), stride, n, out, patch,
+                                   d->stream));
+    ctx->launches.fetch_add(1);
+    CU(cudaStreamSynchronize(d->stream));
+    return PTYPE_OK;
+}
+
+int ptype_b200_gob_encode_replies(ptype_ctx* ctx, int dev, const ptype_reply* replies, size_t n,
+                                  uint64_t* offsets, uint8_t* out, size_t out_cap, uint64_t* total_bytes) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || !offsets || !total_bytes || (n && !replies) || (out_cap && !out)) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(d->device));
+    const size_t need = ptype::gob_scratch_bytes(n) + 64;
+    if (need > d->codec_cap) {
+        CU(cudaStreamSynchronize(d->stream));
+        if (d->d_codec) CU(cudaFree(d->d_codec));
+        d->d_codec = nullptr;
+        d->codec_cap = 0;
+        CU(cudaMalloc(&d->d_codec, need));
+        d->codec_cap = need;
+    }
+    if (!d->d_cksum_out) CU(cudaMalloc(&d->d_cksum_out, sizeof(unsigned long long)));
+    CU(ptype::launch_gob_encode_replies(replies, n, reinterpret_cast<unsigned long long*>(offsets), out,
+                                        out_cap, d->d_codec, d->d_cksum_out, d->stream));
+    ctx->launches.fetch_add(3);
+    unsigned long long total = 0;
+    if (n) CU(cudaMemcpyAsync(&total, d->d_cksum_out, sizeof total, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    *total_bytes = total;
+    return PTYPE_OK;
+}
+
+int ptype_b200_gob_decode_args(ptype_ctx* ctx, int dev, const uint8_t* bytes, const uint64_t* offsets, size_t n,
+                               int64_t* args, int args_per_call, uint8_t* status) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || (n && (!bytes || !offsets || !args)) || (args_per_call != 2 && args_per_call != 3))
+        return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(d->device));
+    CU(ptype::launch_gob_decode_args(bytes, reinterpret_cast<const unsigned long long*>(offsets), n, args,
+                                     args_per_call, status, d->stream));
+    ctx->launches.fetch_add(1);
+    CU(cudaStreamSynchronize(d->stream));
     return PTYPE_OK;
 }
 

@@ -58,6 +58,15 @@ cudaError_t launch_reply_checksum(const ptype_reply* replies, size_t n, uint64_t
                                   unsigned long long* partials, unsigned long long* out,
                                   cudaStream_t stream);
 
+cudaError_t launch_resolve_names(const unsigned char* names, uint32_t stride, size_t n, ptype_method_ref* out,
+                                 ptype_req* patch, cudaStream_t stream);
+size_t gob_scratch_bytes(size_t n);
+cudaError_t launch_gob_encode_replies(const ptype_reply* replies, size_t n, unsigned long long* offsets,
+                                      uint8_t* out, unsigned long long out_cap, void* scratch,
+                                      unsigned long long* total, cudaStream_t stream);
+cudaError_t launch_gob_decode_args(const uint8_t* bytes, const unsigned long long* offsets, size_t n,
+                                   int64_t* args, int args_per_call, uint8_t* status, cudaStream_t stream);
+
 // Records the text ptype_b200_last_error() returns on the calling thread.
 void set_last_error(const char* text);
 

@@ -981,7 +981,7 @@ cudaError_t launch_call_batch_variant(const DeviceImage& img, const LaunchPlan& 
                                       cudaStream_t stream) {
     uint4* r = reinterpret_cast<uint4*>(replies);
     if (plan.threads == kMaxThreads) {
-        auto kernel = call_batch_kernel<kSmemTable, kArgs, kHasSel, 4, kMaxThreads, 1>;
+        auto kernel = call_batch_kernel<kSmemTable, kArgs, kHasSel, 2, kMaxThreads, 1>;
         if (plan.dyn_smem > 48 * 1024) {
             cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                  static_cast<int>(plan.dyn_smem));
@@ -990,7 +990,7 @@ cudaError_t launch_call_batch_variant(const DeviceImage& img, const LaunchPlan& 
         return launch_kernel(kernel, blocks, plan.threads, plan.dyn_smem, stream, img, batch, args,
                              method_sel, n, r);
     }
-    return launch_kernel(call_batch_kernel<kSmemTable, kArgs, kHasSel, 4, kSmallThreads, kSmallMinCtas>,
+    return launch_kernel(call_batch_kernel<kSmemTable, kArgs, kHasSel, 2, kSmallThreads, kSmallMinCtas>,
                          blocks, plan.threads, plan.dyn_smem, stream, img, batch, args, method_sel, n, r);
 }
 }  // namespace
