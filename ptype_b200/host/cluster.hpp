@@ -336,6 +336,101 @@ class MemRegistry : public Registry {
     std::vector<std::pair<std::string, std::shared_ptr<NodeChan>>> watchers_;
 };
 
+// ----------------------------------------------------------------------------- KVStore
+// cluster/store.go:14-74 over an in-memory ordered map (etcd is not in this image).  Only the
+// options the reference's tests use are mirrored: prefix, limit (sort by key ascending is the
+// map's order).  New use: the place a registry image is published so that
+// every host of a deployment loads the same snapshot epoch.
+inline const Error& ErrNoKey() {  // store.go:14-16
+    static const Error e("Key could not be found");
+    return e;
+}
+struct GetOptions {
+    bool Prefix = false;  // WithPrefix()
+    size_t Limit = 0;     // WithLimit(n), 0 = none
+};
+class KVStore {
+   public:
+    // filepath.Join("store", key): joins with '/', drops a trailing '/'
+    static std::string StoreKey(const std::string& key) {
+        std::string k = "store/" + key;
+        while (k.size() > 1 && k.back() == '/') k.pop_back();
+        return k;
+    }
+    Error Get(const std::string& key, std::vector<std::string>* out, GetOptions opt = {}) {  // store.go:38-54
+        std::lock_guard<std::mutex> lk(mu_);
+        out->clear();
+        const std::string k = StoreKey(key);
+        if (opt.Prefix) {
+            for (auto it = kv_.lower_bound(k); it != kv_.end() && it->first.compare(0, k.size(), k) == 0; ++it) {
+                out->push_back(it->second);
+                if (opt.Limit && out->size() == opt.Limit) break;
+            }
+        } else {
+            auto it = kv_.find(k);
+            if (it != kv_.end()) out->push_back(it->second);
+        }
+        return out->empty() ? ErrNoKey() : Error();
+    }
+    Error Put(const std::string& key, const std::string& value) {  // store.go:56-62
+        std::lock_guard<std::mutex> lk(mu_);
+        kv_[StoreKey(key)] = value;
+        return Error();
+    }
+    Error Delete(const std::string& key) {  // store.go:64-74
+        std::lock_guard<std::mutex> lk(mu_);
+        return kv_.erase(StoreKey(key)) ? Error() : ErrNoKey();
+    }
+    void PutRaw(const std::string& full_key, const std::string& value) {  // the tests' tmpKV.Put
+        std::lock_guard<std::mutex> lk(mu_);
+        kv_[full_key] = value;
+    }
+    // Publish / load a registry image blob under store/registry_image/<epoch, zero padded>.
+    Error PublishImage(uint64_t epoch, const void* blob, size_t bytes) {
+        char name[64];
+        std::snprintf(name, sizeof name, "registry_image/%020llu", static_cast<unsigned long long>(epoch));
+        return Put(name, std::string(static_cast<const char*>(blob), bytes));
+    }
+    Error LatestImage(std::string* blob) {
+        std::vector<std::string> all;
+        GetOptions o;
+        o.Prefix = true;
+        if (Error e = Get("registry_image/", &all, o)) return e;
+        *blob = all.back();  // keys sort by epoch
+        return Error();
+    }
+
+   private:
+    std::mutex mu_;
+    std::map<std::string, std::string> kv_;
+};
+
+// ----------------------------------------------------------------------------- optimus
+// example/optimus/coordinator/coordinator.go:67-99: the call stream one target generates and
+// the rule that picks the answer.
+namespace optimus {
+struct Args {  // example/optimus/prime.go:7-11
+    int64_t Min, Max, Target;
+};
+inline std::vector<Args> SplitWork(int64_t target) {  // coordinator.go:67-73
+    std::vector<Args> out;
+    int64_t min = 2;
+    const int64_t limit = static_cast<int64_t>(static_cast<uint64_t>(target) + 10u);
+    for (int64_t i = 10; i < limit; i += 10) {
+        out.push_back(Args{min, i, target});
+        min = i;
+    }
+    return out;
+}
+// watchReplies (coordinator.go:91-99) on replies in arrival order: the first one that is not
+// the target, else the target.
+inline int64_t WatchReplies(int64_t target, const std::vector<int64_t>& replies) {
+    for (int64_t r : replies)
+        if (r != target) return r;
+    return target;
+}
+}  // namespace optimus
+
 // -------------------------------------------------------------------------- ConnConfig
 struct ConnConfig {  // cluster/rpc.go:19-31
     int MaxConnections = 3;
@@ -525,6 +620,10 @@ class Client {  // cluster/rpc.go:40-43,126-139
     // failed are re-issued with fresh sequence numbers up to cfg.Retries more times (withRetry,
     // rpc.go:107-116, bounded — see the header comment).
     Error CallBatch(const std::string& serviceMethod, const int64_t (*args)[3], size_t n, BatchReply* replies) {
+        return CallBatchAttempts(serviceMethod, args, n, replies, cfg_.Retries);
+    }
+    Error CallBatchAttempts(const std::string& serviceMethod, const int64_t (*args)[3], size_t n,
+                            BatchReply* replies, int retries) {
         if (n == 0) return Error();
         uint32_t method = 0, recv = 0;
         ptype_b200_method_key(serviceMethod.c_str(), &method, &recv);
@@ -551,13 +650,59 @@ class Client {  // cluster/rpc.go:40-43,126-139
                 replies[j].NodeId = out[t].node;
                 replies[j].Status = out[t].status;
             }
-            if (stats.failed_count == 0 || attempt >= cfg_.Retries) return Error();
+            if (stats.failed_count == 0 || attempt >= retries) return Error();
             std::vector<uint32_t> next;
             next.reserve(stats.failed_count);
             for (uint64_t f = 0; f < stats.failed_count; ++f) next.push_back(todo[failed[f]]);
             std::sort(next.begin(), next.end());
             todo.swap(next);
         }
+    }
+
+    // rpc.go:69-105.  The asynchronous twin: the call runs on its own thread and the returned
+    // object is signalled when done.  Like the reference it makes ONE attempt (rpc.go:91 tests
+    // the outer call's Error, which is still nil, so the retry loop never repeats - SURVEY.md
+    // D6); on failure the delivered call carries the error and *reply is left untouched
+    // (rpc_test.go:262-292).
+    struct AsyncCall {
+        std::string ServiceMethod;
+        Error Err;
+        bool Done() {
+            std::lock_guard<std::mutex> lk(mu);
+            return done;
+        }
+        void Wait() {
+            std::unique_lock<std::mutex> lk(mu);
+            cv.wait(lk, [&] { return done; });
+        }
+        ~AsyncCall() {
+            if (worker.joinable()) worker.join();
+        }
+
+       private:
+        friend class Client;
+        std::mutex mu;
+        std::condition_variable cv;
+        bool done = false;
+        std::thread worker;
+    };
+    std::shared_ptr<AsyncCall> Go(const std::string& serviceMethod, const int64_t (&args)[3], int64_t* reply) {
+        auto call = std::make_shared<AsyncCall>();
+        call->ServiceMethod = serviceMethod;
+        const int64_t a0 = args[0], a1 = args[1], a2 = args[2];
+        AsyncCall* raw = call.get();
+        call->worker = std::thread([this, raw, serviceMethod, a0, a1, a2, reply] {
+            const int64_t a[1][3] = {{a0, a1, a2}};
+            BatchReply rep;
+            Error e = CallBatchAttempts(serviceMethod, a, 1, &rep, /*retries=*/0);
+            if (!e) e = StatusError(rep.Status, serviceMethod);
+            if (!e) *reply = rep.Value;
+            std::lock_guard<std::mutex> lk(raw->mu);
+            raw->Err = e;
+            raw->done = true;
+            raw->cv.notify_all();
+        });
+        return call;
     }
 
     std::vector<Node> getSelectedNodes() { return gpu_->SelectedNodes(service_); }  // rpc.go:293-297

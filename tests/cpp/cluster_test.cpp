@@ -115,6 +115,46 @@ static void TestRegistry_nodes_prefix_case() {
     REQUIRE((n == std::vector<Node>{{"host", 8000}, {"host2", 8000}}));
 }
 
+// TestKVGet / GetErrorsOnNoKey / GetWithPrefix / GetWithMultipleOptions / Put / Delete /
+// DeleteNoKey (cluster/store_test.go:17-169)
+static void TestKVStore() {
+    KVStore kvs;
+    std::vector<std::string> vals;
+    kvs.PutRaw("store/raccoon1/", "uwu1");
+    kvs.PutRaw("store/raccoon2/", "uwu2");
+    GetOptions prefix;
+    prefix.Prefix = true;
+    REQUIRE(!kvs.Get("raccoon1", &vals, prefix));
+    REQUIRE((vals == std::vector<std::string>{"uwu1"}));
+    REQUIRE(kvs.Get("raccoon", &vals).Is(ErrNoKey()) && vals.empty());
+    REQUIRE(!kvs.Get("raccoon", &vals, prefix));
+    REQUIRE((vals == std::vector<std::string>{"uwu1", "uwu2"}));
+    REQUIRE(!kvs.Put("hello1", "world1") && !kvs.Put("hello2", "world2") && !kvs.Put("hello3", "world3"));
+    GetOptions two = prefix;
+    two.Limit = 2;
+    REQUIRE(!kvs.Get("hello", &vals, two));
+    REQUIRE((vals == std::vector<std::string>{"world1", "world2"}));
+    REQUIRE(!kvs.Put("hello", "world"));
+    REQUIRE(!kvs.Get("hello", &vals) && vals == std::vector<std::string>{"world"});
+    REQUIRE(!kvs.Delete("hello"));
+    REQUIRE(kvs.Get("hello", &vals).Is(ErrNoKey()));
+    REQUIRE(kvs.Delete("hello").Is(ErrNoKey()));
+    // new use: registry images by epoch; the latest epoch wins
+    REQUIRE(kvs.LatestImage(&vals.emplace_back()).Is(ErrNoKey()));
+    REQUIRE(!kvs.PublishImage(9, "nine", 4) && !kvs.PublishImage(10, "ten!", 4) && !kvs.PublishImage(2, "two.", 4));
+    std::string blob;
+    REQUIRE(!kvs.LatestImage(&blob) && blob == "ten!");
+}
+
+// example/optimus/coordinator/coordinator.go:67-99
+static void TestOptimus_splitWork_watchReplies() {
+    auto w = optimus::SplitWork(91);
+    REQUIRE(w.size() == 10 && w[0].Min == 2 && w[0].Max == 10 && w[1].Min == 10 && w[9].Max == 100);
+    REQUIRE(optimus::SplitWork(0).empty() && optimus::SplitWork(-7).empty() && optimus::SplitWork(10).size() == 1);
+    REQUIRE(optimus::WatchReplies(91, {91, 91, 7, 13}) == 7);
+    REQUIRE(optimus::WatchReplies(97, {97, 97, 97}) == 97);
+}
+
 // ------------------------------------------------------------- client / balancer (GPU)
 
 static std::vector<Node> fakeNodes(int n, int base = 40000) {
@@ -178,6 +218,58 @@ static void TestClient_first_call_goes_to_index_1() {
     REQUIRE(gpu.NodeOf(rep[1].NodeId) == sel[0]);
     REQUIRE(gpu.NodeOf(rep[2].NodeId) == sel[1]);
     REQUIRE(rep[3].Value == 8);
+}
+
+// TestClient_Go / TestClient_Go_with_retry_error (rpc_test.go:188-215,262-292): async call,
+// completion signalled; on failure the call carries the error and the reply stays 0
+static void TestClient_Go() {
+    Dispatcher gpu("", 3);
+    gpu.Expose("foo", "Calculator");
+    MockRegistry mock{fakeNodes(1)};
+    ConnConfig cfg = testConnConfig();
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c));
+    int64_t reply = 0, untouched = 0;
+    const int64_t args[3] = {7, 8, 0};
+    auto call = c->Go("Calculator.Multiply", args, &reply);
+    auto bad = c->Go("Calculator.Nope", args, &untouched);
+    call->Wait();
+    bad->Wait();
+    REQUIRE(call->Done() && !call->Err && reply == 56);
+    REQUIRE(bad->Err.msg == "rpc: can't find method Calculator.Nope" && untouched == 0);
+}
+
+// The optimus example end to end: one target's splitWork stream through a Prime client, the
+// answer picked by watchReplies (coordinator.go:46-99; the 250 ms sleep of prime.go:17 dropped)
+static void TestExample_optimus() {
+    MemRegistry reg;
+    REQUIRE(!reg.Register("prime_worker", "prime_worker_1", "127.0.0.1", 8000));
+    REQUIRE(!reg.Register("prime_worker", "prime_worker_2", "127.0.0.1", 8002));
+    Dispatcher gpu("127.0.0.1", 3);
+    gpu.Expose("prime_worker", "Prime");
+    ConnConfig cfg = testConnConfig();
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "prime_worker", &reg, &cfg, &c));
+    for (int64_t target : {91, 97, 100, 121, 7919, 7917}) {
+        auto work = optimus::SplitWork(target);
+        std::vector<std::array<int64_t, 3>> args;
+        for (auto& a : work) args.push_back({a.Min, a.Max, a.Target});
+        std::vector<BatchReply> rep(args.size());
+        REQUIRE(!c->CallBatch("Prime.Check", reinterpret_cast<const int64_t(*)[3]>(args.data()), args.size(), rep.data()));
+        std::vector<int64_t> values;
+        for (auto& r : rep) {
+            REQUIRE(r.Status == 0);
+            values.push_back(r.Value);
+        }
+        const int64_t answer = optimus::WatchReplies(target, values);
+        int64_t smallest = target;
+        for (int64_t d = 2; d < target; ++d)
+            if (target % d == 0) {
+                smallest = d;
+                break;
+            }
+        REQUIRE(answer == smallest);   // in order of submission the first non-target reply is the smallest divisor
+    }
 }
 
 // TestNewConnectionBalancer_with_no_available_server (rpc_test.go:307-314)
@@ -299,7 +391,11 @@ int main(int argc, char** argv) {
     RUN(TestRegistry_Services);
     RUN(TestRegistry_WatchService);
     RUN(TestRegistry_nodes_prefix_case);
+    RUN(TestKVStore);
+    RUN(TestOptimus_splitWork_watchReplies);
     if (gpu) {
+        RUN(TestClient_Go);
+        RUN(TestExample_optimus);
         RUN(TestClient_default_conn_config);
         RUN(TestClient_Call);
         RUN(TestClient_first_call_goes_to_index_1);

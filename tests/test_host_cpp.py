@@ -17,7 +17,7 @@ def test_registry_mirror_cpu():
     exe = _build()
     out = subprocess.run([str(exe), "cpu"], capture_output=True, text=True, timeout=120)
     assert out.returncode == 0, out.stdout + out.stderr
-    assert "4 tests, 0 failed" in out.stdout
+    assert "6 tests, 0 failed" in out.stdout
 
 
 @pytest.mark.gpu
@@ -25,4 +25,4 @@ def test_client_and_balancer_mirror_gpu():
     exe = _build()
     out = subprocess.run([str(exe), "gpu"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
-    assert "12 tests, 0 failed" in out.stdout
+    assert "16 tests, 0 failed" in out.stdout
