@@ -467,11 +467,17 @@ def main():
         launch_s = (ms_max * 1e-3) / args.steps
         per_launch_calls = calls_all / world / args.steps
         achieved = per_launch_calls * BYTES_PER_CALL / launch_s / 1e9
-        traffic = None
+        traffic, traffic_note = None, None
         tp = ROOT / "profiles" / "dispatch_traffic.json"
         if tp.exists():
             try:
-                traffic = json.loads(tp.read_text()).get(args.workload)
+                t = json.loads(tp.read_text()).get(args.workload + ("_one_launch_per_batch" if args.flags & 32 else ""))
+                if isinstance(t, dict):   # measured on a launch of `batches_per_launch` batches
+                    traffic = t["per_launch_bytes"]
+                    traffic_note = (f"ncu: one launch = {t['batches_per_launch']} batches, "
+                                    f"{t['algorithmic_bytes_per_launch']} algorithmic bytes")
+                else:
+                    traffic = t
             except Exception:
                 traffic = None
         line = {
@@ -487,7 +493,8 @@ def main():
                                    if multi else "single GPU",
                        "table": "shared memory" if not (args.flags & 4) else "global/L2"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_kind": peak_kind,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
+                         "peak_kind": peak_kind,
                          "kernel": "dispatch_kernel (one launch per batch)" if (args.flags & 32) else
                                    "dispatch_multi_kernel (one persistent launch per 96 batches)", "algorithmic_bytes_per_call": BYTES_PER_CALL,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
