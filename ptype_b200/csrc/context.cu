@@ -219,7 +219,7 @@ int reserve_inactive(DeviceState* d, int buf, size_t bytes) {
 // Point a DeviceImage at buffer `buf` (which holds at least header.device_bytes of
 // the blob), refresh launch plans, and flip.  Mirrors the swap under lock of
 // handleNewNodes (cluster/rpc.go:233-236).
-int adopt_image(ptype_ctx* ctx, DeviceState* d, int buf, const ptype_image_header& h) {
+int adopt_image(ptype_ctx* ctx, DeviceState* d, int buf, const ptype_image_header& h, const void* host_blob) {
     const unsigned char* base = static_cast<const unsigned char*>(d->image_buf[buf]);
     ptype::DeviceImage& v = d->view[buf];
     v.slots = reinterpret_cast<const ptype_slot*>(base + h.off_slots);
@@ -231,7 +231,12 @@ int adopt_image(ptype_ctx* ctx, DeviceState* d, int buf, const ptype_image_heade
     v.n_slots = h.n_slots;
     v.max_conn = h.max_connections;
     v.n_methods = h.n_methods;
-    v.pad = 0;
+    // which receivers do the registered services expose? (slot masks, host copy of the blob)
+    uint32_t recv_union = 0;
+    const ptype_slot* hs = reinterpret_cast<const ptype_slot*>(static_cast<const unsigned char*>(host_blob) + h.off_slots);
+    for (uint32_t i = 0; i < h.n_slots; ++i)
+        if (hs[i].node_base != PTYPE_SLOT_EMPTY) recv_union |= hs[i].n_and_recv >> 24;
+    v.check_only = recv_union == 2u ? 1u : 0u;  // bit 1 = Prime, bit 0 = Calculator (image.cpp)
     v.m_magic = h.max_connections ? ~0ull / h.max_connections + 1ull : 0ull;
     v.check_limit = ctx->check_limit.load();
     for (int g = 0; g < kPlanKinds; ++g)
@@ -474,7 +479,7 @@ int ptype_b200_publish_image(ptype_ctx* ctx, const void* image, size_t bytes) {
                            d->copy_stream));
         rc = dispatches_wait_for_copy_stream(d);
         if (rc != PTYPE_OK) return rc;
-        rc = adopt_image(ctx, d, buf, h);  // the flip: later dispatches use the new image
+        rc = adopt_image(ctx, d, buf, h, image);  // the flip: later dispatches use the new image
         if (rc != PTYPE_OK) return rc;
     }
     std::lock_guard<std::mutex> lk(ctx->image_mu);
@@ -578,7 +583,7 @@ int ptype_b200_broadcast_image(ptype_ctx* ctx, const void* image, size_t bytes, 
     if (rc != PTYPE_OK) return rc;
     rc = dispatches_wait_for_copy_stream(d);
     if (rc != PTYPE_OK) return rc;
-    rc = adopt_image(ctx, d, buf, *reinterpret_cast<const ptype_image_header*>(host.data()));
+    rc = adopt_image(ctx, d, buf, *reinterpret_cast<const ptype_image_header*>(host.data()), host.data());
     if (rc != PTYPE_OK) return rc;
     std::lock_guard<std::mutex> lk2(ctx->image_mu);
     ctx->host_image.swap(host);
@@ -712,7 +717,7 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
         if (batches[b].n && (!batches[b].reqs || !batches[b].replies)) return PTYPE_E_INVAL;
         if (batches[b].n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
     }
-    if (!plan.bulk && !(flags & PTYPE_F_ONE_LAUNCH_PER_BATCH)) {
+    if (!(flags & PTYPE_F_ONE_LAUNCH_PER_BATCH)) {
         // One launch per group of batches: the persistent grid walks their tiles as one
         // stream.  Groups are cut so that a launch stays below 2^32 tiles.
         const size_t group = static_cast<size_t>(ptype::max_batches_per_launch());

@@ -18,7 +18,7 @@ struct DeviceImage {
     uint32_t n_methods;
     uint32_t table_seed;         // cuckoo hash seed
     uint32_t method_mul;         // perfect-hash multiplier
-    uint32_t pad;
+    uint32_t check_only;         // 1: the only receiver any service exposes is Prime (ALU-heavy calls)
     uint64_t m_magic;            // 2^64 / max_conn + 1: multiply-shift modulo by max_conn
     uint64_t check_limit;        // Prime.Check trip-count limit
 };
