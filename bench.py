@@ -5,7 +5,8 @@ A step = one pass of the fused dispatch kernel over one batch of the named workl
 Default workload (N=1 and up): BASELINE config 2 — 2^20 mixed Add/Multiply calls,
 1 service x 16 registered nodes, MaxConnections 3.  For N>1 the stream is sharded by
 request-id hash (mix64(id) % N), a full registry replica per GPU installed by one
-ncclBroadcast; the data path has no collective ("scaling": "weak").
+ncclBroadcast (inside the library); the data path has no collective ("scaling": "weak").
+Barriers and the max-over-ranks reduction of the device times use a gloo group.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
                     [--workload c2|c2mesh|c3|c4]
@@ -247,7 +248,16 @@ def main():
     multi = world > 1
     if multi:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # Host-side plumbing (barriers, the max over ranks of the device times, the NCCL id) goes
+        # over gloo.  The path's one collective, the registry-image broadcast, is NCCL inside the
+        # library.  A torch NCCL process group is deliberately NOT created: with it (peer access
+        # enabled by torch's NCCL init) the same HBM-bound kernel ran 12.1 us per step instead of
+        # 9.5 us on every rank (measured at N=2; NCCL_P2P_DISABLE=1 restored 9.7 us).
+        # PTYPE_BENCH_TORCH_NCCL=1 reproduces that.
+        if os.environ.get("PTYPE_BENCH_TORCH_NCCL") == "1":
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        else:
+            dist.init_process_group("gloo")
 
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -265,6 +275,7 @@ def main():
             builder.expose(svc, recv)
         builder.set_device_only(True)
     first_image = (builder.finish(1) if live else spec.image(epoch=1)) if rank == 0 or not multi else None
+    torch_nccl = os.environ.get("PTYPE_BENCH_TORCH_NCCL") == "1"
     if multi:
         ids = [p.Context.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
@@ -352,10 +363,11 @@ def main():
     ms = ev0.elapsed_time(ev1)
     calls_mine = sum(counts[i % nbuf] for i in range(args.steps))
     if multi:
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        rdev = "cuda" if torch_nccl else "cpu"
+        t = torch.tensor([ms], device=rdev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_max = float(t.item())
-        c = torch.tensor([calls_mine], device="cuda", dtype=torch.float64)
+        c = torch.tensor([calls_mine], device=rdev, dtype=torch.float64)
         dist.all_reduce(c, op=dist.ReduceOp.SUM)
         calls_all = float(c.item())
     else:
@@ -381,10 +393,10 @@ def main():
     e1 = time.perf_counter()
     e2e_s = e1 - e0
     if multi:
-        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        t = torch.tensor([e2e_s], device=rdev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-        c = torch.tensor([float(len(hb) * e2e_steps)], device="cuda", dtype=torch.float64)
+        c = torch.tensor([float(len(hb) * e2e_steps)], device=rdev, dtype=torch.float64)
         dist.all_reduce(c, op=dist.ReduceOp.SUM)
         e2e_calls = float(c.item())
     else:
