@@ -346,7 +346,7 @@ int ptype_b200_set_check_limit(ptype_ctx*, uint64_t max_iterations);
 
 /* Order-independent 64-bit checksum of n reply records (sum over j of
  * mix64(record j, j) mod 2^64) — compares whole streams across GPUs and against
- * the oracle without moving the replies.  replies: device pointer when
+ * a CPU reference without moving the replies.  replies: device pointer when
  * PTYPE_F_DEVICE_PTRS, else host. */
 int ptype_b200_reply_checksum(ptype_ctx*, int dev, const ptype_reply* replies, size_t n,
                               uint64_t index_base, uint64_t* checksum, uint32_t flags);
