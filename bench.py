@@ -432,6 +432,24 @@ def main():
             t = torch.tensor([cs], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             cs = float(t.item())
+        # ... and with the replies CallBatch's caller reads: 8-byte values + the failed list
+        pin_val = p.PinnedArray(len(hb), np.int64)
+        for _ in range(3):
+            _, vfailed, vcount = ctx.call_batch_values(key, base, methods, pa, ps, pin_val.array,
+                                                       failed_cap=1024, flags=args.flags & 4)
+        values_ok = pin_val.array.copy()
+        barrier()
+        v0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            ctx.call_batch_values(key, base, methods, pa, ps, pin_val.array, failed_cap=1024,
+                                  flags=args.flags & 4)
+        barrier()
+        vs = time.perf_counter() - v0
+        e2e_values = {"value": e2e_calls / vs, "unit": "calls/s",
+                      "h2d_bytes_per_step": int(cargs.nbytes + (len(sel) if sel is not None else 0)),
+                      "d2h_bytes_per_step": int(len(hb) * 8), "steps": e2e_steps, "failed_calls": int(vcount),
+                      "api": "ptype_b200_call_batch_values(args + method byte in, 8-byte values + failed list "
+                             "out, pinned host buffers)"}
         e2e_compact = {"value": e2e_calls / cs, "unit": "calls/s",
                        "h2d_bytes_per_step": int(cargs.nbytes + (len(sel) if sel is not None else 0)),
                        "d2h_bytes_per_step": int(len(hb) * 16), "steps": e2e_steps,
@@ -461,6 +479,9 @@ def main():
             raise SystemExit("bench.py: CUDA replies differ from the oracle - number withheld")
         if e2e_compact is not None and compact_ok != want.tobytes():
             raise SystemExit("bench.py: call_batch replies differ from the oracle - number withheld")
+        if e2e_compact is not None and (not np.array_equal(values_ok, want["value"]) or
+                                        vcount != int((want["status"] != 0).sum())):
+            raise SystemExit("bench.py: call_batch_values differs from the oracle - number withheld")
         if not multi:
             threads = os.cpu_count() or 1
             rate, passes, el, _ = cpu_port_rate(spec, hb, threads, args.cpu_seconds)
@@ -510,7 +531,8 @@ def main():
                          "kernel": "dispatch_kernel (one launch per batch)" if (args.flags & 32) else
                                    "dispatch_multi_kernel (one persistent launch per 96 batches)", "algorithmic_bytes_per_call": BYTES_PER_CALL,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
-            "e2e": e2e_compact if e2e_compact is not None else e2e_records,
+            "e2e": e2e_values if e2e_compact is not None else e2e_records,
+            "e2e_reply_records": e2e_compact,
             "e2e_records": e2e_records,
             "gpu_launches": int(launches),
             "host_enqueue_us_per_step": host_enqueue_s / args.steps * 1e6,

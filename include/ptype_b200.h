@@ -341,6 +341,21 @@ int ptype_b200_call_batch(ptype_ctx*, int dev, uint64_t svc_key, uint64_t seq_ba
                           const ptype_method_ref* methods, int n_methods, const uint8_t* method_sel,
                           const int64_t* args, int args_per_call, size_t n, ptype_reply* replies,
                           uint32_t flags);
+/* The same batch with the replies CallBatch's caller actually reads: values[j] (8 bytes per
+ * call, 0 for a failed call) and, for the calls whose status is not OK, one (index, status)
+ * entry in failed[0..failed_cap) (order unspecified; *failed_count is the exact number even if
+ * it exceeds failed_cap).  Routing decisions are not returned.  Host pointers (pinned: the
+ * kernel streams across PCIe itself; pageable: staged copies) or, with PTYPE_F_DEVICE_PTRS,
+ * device pointers for args/method_sel/values; failed and failed_count are always host. */
+typedef struct ptype_failed {
+    uint32_t index;
+    uint32_t status; /* enum ptype_status */
+} ptype_failed;
+int ptype_b200_call_batch_values(ptype_ctx*, int dev, uint64_t svc_key, uint64_t seq_base,
+                                 const ptype_method_ref* methods, int n_methods, const uint8_t* method_sel,
+                                 const int64_t* args, int args_per_call, size_t n, int64_t* values,
+                                 ptype_failed* failed, size_t failed_cap, uint64_t* failed_count,
+                                 uint32_t flags);
 int ptype_b200_sync(ptype_ctx*, int dev);
 int ptype_b200_set_check_limit(ptype_ctx*, uint64_t max_iterations);
 

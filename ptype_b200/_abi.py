@@ -111,6 +111,9 @@ SIGNATURES = [
     ("ptype_b200_dispatch_batches", C.c_int, [_vp, C.c_int, _vp, C.c_size_t, C.c_uint32]),
     ("ptype_b200_call_batch", C.c_int,
      [_vp, C.c_int, C.c_uint64, C.c_uint64, _vp, C.c_int, _vp, _vp, C.c_int, C.c_size_t, _vp, C.c_uint32]),
+    ("ptype_b200_call_batch_values", C.c_int,
+     [_vp, C.c_int, C.c_uint64, C.c_uint64, _vp, C.c_int, _vp, _vp, C.c_int, C.c_size_t, _vp, _vp,
+      C.c_size_t, _u64p, C.c_uint32]),
     ("ptype_b200_sync", C.c_int, [_vp, C.c_int]),
     ("ptype_b200_set_check_limit", C.c_int, [_vp, C.c_uint64]),
     ("ptype_b200_reply_checksum", C.c_int,

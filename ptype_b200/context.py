@@ -182,6 +182,29 @@ class Context:
                                         _ptr(args), args_per_call, n, _ptr(replies), flags), "call_batch")
         return replies
 
+    def call_batch_values(self, service_key: int, seq_base: int, methods, args, method_sel=None,
+                          values=None, failed_cap: int = 1024, *, dev: int = 0, flags: int = 0,
+                          n: Optional[int] = None, args_per_call: int = 2):
+        """ptype_b200_call_batch_values: returns (values, failed[(index, status)], failed_count)."""
+        refs = (_abi.MethodRef * len(methods))(*[_abi.MethodRef(m, r) for m, r in methods])
+        if isinstance(args, np.ndarray):
+            args = np.ascontiguousarray(args, dtype=np.int64)
+            n, args_per_call = args.shape
+            if method_sel is not None:
+                method_sel = np.ascontiguousarray(method_sel, dtype=np.uint8)
+            if values is None:
+                values = np.empty(n, dtype=np.int64)
+        else:
+            flags |= F_DEVICE_PTRS
+        failed = np.zeros(max(failed_cap, 1), dtype=[("index", "<u4"), ("status", "<u4")])
+        count = C.c_uint64()
+        check(lib.ptype_b200_call_batch_values(self._h, dev, service_key, seq_base, refs, len(methods),
+                                               _ptr(method_sel) if method_sel is not None else None,
+                                               _ptr(args), args_per_call, n, _ptr(values),
+                                               failed.ctypes.data, failed_cap, C.byref(count), flags),
+              "call_batch_values")
+        return values, failed[: min(failed_cap, count.value)], count.value
+
     def make_batches(self, items) -> "C.Array":
         """items: iterable of (device reqs, device replies, n) -> a ptype_batch array."""
         items = list(items)

@@ -138,6 +138,8 @@ struct DeviceState {
     unsigned long long* d_cksum_partials = nullptr;  // scratch of the checksum kernel
     unsigned long long* d_cksum_out = nullptr;
     unsigned long long* d_size = nullptr;  // broadcast header scratch
+    ptype_failed* d_failed2 = nullptr;     // (index, status) list of call_batch_values
+    size_t failed2_cap = 0;
     void* d_codec = nullptr;               // scratch of the gob encoder (lengths, block sums)
     size_t codec_cap = 0;
     cudaEvent_t drained[1 + kPipe] = {};   // "everything enqueued so far" markers, one per dispatch stream
@@ -342,6 +344,7 @@ void ptype_b200_close(ptype_ctx* ctx) {
         if (d->d_cksum_out) cudaFree(d->d_cksum_out);
         if (d->d_size) cudaFree(d->d_size);
         if (d->d_codec) cudaFree(d->d_codec);
+        if (d->d_failed2) cudaFree(d->d_failed2);
         for (int i = 0; i <= kPipe; ++i)
             if (d->drained[i]) cudaEventDestroy(d->drained[i]);
         if (d->image_ready) cudaEventDestroy(d->image_ready);
@@ -750,15 +753,22 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
     return PTYPE_OK;
 }
 
-int ptype_b200_call_batch(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base,
-                          const ptype_method_ref* methods, int n_methods, const uint8_t* method_sel,
-                          const int64_t* args, int args_per_call, size_t n, ptype_reply* replies,
-                          uint32_t flags) {
+namespace {
+
+// Shared body of ptype_b200_call_batch (16-byte reply records) and
+// ptype_b200_call_batch_values (8-byte values + failed list).
+int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base,
+                    const ptype_method_ref* methods, int n_methods, const uint8_t* method_sel,
+                    const int64_t* args, int args_per_call, size_t n, ptype_reply* replies,
+                    int64_t* values, ptype_failed* failed, size_t failed_cap, uint64_t* failed_count,
+                    uint32_t flags) {
     DeviceState* d = dev_of(ctx, dev);
+    const bool values_mode = values != nullptr;
     if (!d || !methods || n_methods < 1 || n_methods > PTYPE_BATCH_METHODS ||
-        (args_per_call != 2 && args_per_call != 3) || (n && (!args || !replies)))
+        (args_per_call != 2 && args_per_call != 3) || (n && (!args || (!replies && !values))) ||
+        (failed_cap && !failed))
         return PTYPE_E_INVAL;
-    if (n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
+    if (n > 0xFFFFFFFFull || failed_cap > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
     std::lock_guard<std::mutex> lk(d->mu);
     if (d->active < 0) return PTYPE_E_NO_IMAGE;
     CU(cudaSetDevice(d->device));
@@ -772,31 +782,62 @@ int ptype_b200_call_batch(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t se
         m[i] = methods[i].method;
         r[i] = methods[i].recv;
     }
+    ptype::CallBatchOut out;
+    if (values_mode) {
+        // the failed list and its counter live in device memory; copied out at the end
+        if (!d->d_stats) CU(cudaMalloc(&d->d_stats, ptype::kStatWords * sizeof(unsigned long long)));
+        if (failed_cap > d->failed2_cap) {
+            CU(cudaStreamSynchronize(d->stream));
+            if (d->d_failed2) CU(cudaFree(d->d_failed2));
+            d->d_failed2 = nullptr;
+            d->failed2_cap = 0;
+            CU(cudaMalloc(&d->d_failed2, failed_cap * sizeof(ptype_failed)));
+            d->failed2_cap = failed_cap;
+        }
+        CU(cudaMemsetAsync(d->d_stats, 0, sizeof(unsigned long long), d->stream));
+        CU(cudaStreamSynchronize(d->stream));
+        out.failed = d->d_failed2;
+        out.failed_cap = static_cast<uint32_t>(failed_cap);
+        out.failed_count = d->d_stats;
+    }
+    auto finish_values = [&]() -> int {
+        if (!values_mode) return PTYPE_OK;
+        unsigned long long count = 0;
+        CU(cudaMemcpy(&count, d->d_stats, sizeof count, cudaMemcpyDeviceToHost));
+        if (failed_count) *failed_count = count;
+        const size_t take = count < failed_cap ? static_cast<size_t>(count) : failed_cap;
+        if (take) CU(cudaMemcpy(failed, d->d_failed2, take * sizeof(ptype_failed), cudaMemcpyDeviceToHost));
+        return PTYPE_OK;
+    };
     const size_t arg_bytes = static_cast<size_t>(args_per_call) * sizeof(int64_t);
     if (flags & PTYPE_F_DEVICE_PTRS) {
         if (n) {
+            out.values = values;
             CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, n, d->sm_count), svc_key, seq_base,
-                                        m, r, n_methods, args, args_per_call, method_sel, n, replies,
+                                        m, r, n_methods, args, args_per_call, method_sel, n, replies, out,
                                         d->stream));
             ctx->launches.fetch_add(1);
         }
-        if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
-        return PTYPE_OK;
+        if (values_mode || !(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+        return finish_values();
     }
     if (zero_copy_enabled() && n) {
         const int64_t* za = static_cast<const int64_t*>(pinned_alias(args));
-        ptype_reply* zr = static_cast<ptype_reply*>(pinned_alias(replies));
+        ptype_reply* zr = replies ? static_cast<ptype_reply*>(pinned_alias(replies)) : nullptr;
+        int64_t* zv = values ? static_cast<int64_t*>(pinned_alias(values)) : nullptr;
         const uint8_t* zs = method_sel ? static_cast<const uint8_t*>(pinned_alias(method_sel)) : nullptr;
-        if (za && zr && (!method_sel || zs)) {
+        if (za && (values_mode ? zv != nullptr : zr != nullptr) && (!method_sel || zs)) {
+            out.values = zv;
             CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, n, d->sm_count), svc_key, seq_base,
-                                        m, r, n_methods, za, args_per_call, zs, n, zr, d->stream));
+                                        m, r, n_methods, za, args_per_call, zs, n, zr, out, d->stream));
             ctx->launches.fetch_add(1);
-            if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
-            return PTYPE_OK;
+            if (values_mode || !(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+            return finish_values();
         }
     }
-    // Host buffers: the staging slot of each pipeline stream holds a chunk's arguments
-    // (<= 24 B/call) and, behind them, its method selectors (1 B/call).
+    // Pageable host buffers: the staging slot of each pipeline stream holds a chunk's arguments
+    // (<= 24 B/call) and, behind them, its method selectors (1 B/call); the reply slot holds
+    // the chunk's records or values.
     size_t done = 0;
     int s = 0;
     while (done < n) {
@@ -815,18 +856,24 @@ int ptype_b200_call_batch(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t se
                            cnt * arg_bytes, cudaMemcpyHostToDevice, d->pipe[s]));
         if (method_sel)
             CU(cudaMemcpyAsync(d_sel, method_sel + done, cnt, cudaMemcpyHostToDevice, d->pipe[s]));
+        out.values = values_mode ? reinterpret_cast<int64_t*>(st.d_replies) : nullptr;
+        out.index_base = static_cast<uint32_t>(done);
         CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, cnt, d->sm_count), svc_key,
                                     seq_base + done, m, r, n_methods, d_args, args_per_call, d_sel, cnt,
-                                    st.d_replies, d->pipe[s]));
+                                    st.d_replies, out, d->pipe[s]));
         ctx->launches.fetch_add(1);
-        CU(cudaMemcpyAsync(replies + done, st.d_replies, cnt * sizeof(ptype_reply), cudaMemcpyDeviceToHost,
-                           d->pipe[s]));
+        if (values_mode)
+            CU(cudaMemcpyAsync(values + done, st.d_replies, cnt * sizeof(int64_t), cudaMemcpyDeviceToHost,
+                               d->pipe[s]));
+        else
+            CU(cudaMemcpyAsync(replies + done, st.d_replies, cnt * sizeof(ptype_reply),
+                               cudaMemcpyDeviceToHost, d->pipe[s]));
         CU(cudaEventRecord(st.done, d->pipe[s]));
         st.busy = true;
         done += cnt;
         s = (s + 1) % kPipe;
     }
-    if (!(flags & PTYPE_F_ASYNC)) {
+    if (values_mode || !(flags & PTYPE_F_ASYNC)) {
         for (int i = 0; i < kPipe; ++i) {
             if (d->stage[i].busy) {
                 CU(cudaEventSynchronize(d->stage[i].done));
@@ -834,7 +881,30 @@ int ptype_b200_call_batch(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t se
             }
         }
     }
-    return PTYPE_OK;
+    return finish_values();
+}
+
+}  // namespace
+
+int ptype_b200_call_batch(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base,
+                          const ptype_method_ref* methods, int n_methods, const uint8_t* method_sel,
+                          const int64_t* args, int args_per_call, size_t n, ptype_reply* replies,
+                          uint32_t flags) {
+    if (n && !replies) return PTYPE_E_INVAL;
+    return call_batch_impl(ctx, dev, svc_key, seq_base, methods, n_methods, method_sel, args, args_per_call, n,
+                           replies, nullptr, nullptr, 0, nullptr, flags);
+}
+
+int ptype_b200_call_batch_values(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base,
+                                 const ptype_method_ref* methods, int n_methods, const uint8_t* method_sel,
+                                 const int64_t* args, int args_per_call, size_t n, int64_t* values,
+                                 ptype_failed* failed, size_t failed_cap, uint64_t* failed_count,
+                                 uint32_t flags) {
+    if (!values) return PTYPE_E_INVAL;
+    if (failed_count) *failed_count = 0;
+    if (n == 0) return PTYPE_OK;
+    return call_batch_impl(ctx, dev, svc_key, seq_base, methods, n_methods, method_sel, args, args_per_call, n,
+                           nullptr, values, failed, failed_cap, failed_count, flags);
 }
 
 int ptype_b200_dispatch(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_t n,

@@ -49,11 +49,20 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
 int max_batches_per_launch();
 cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
                                   const ptype_batch* batches, int count, cudaStream_t stream);
+// Values-only output of a client batch: values != nullptr switches the kernel from 16-byte
+// reply records to 8-byte values plus an (index, status) list of the failed calls.
+struct CallBatchOut {
+    int64_t* values = nullptr;
+    ptype_failed* failed = nullptr;
+    uint32_t failed_cap = 0;
+    uint32_t index_base = 0;
+    unsigned long long* failed_count = nullptr;
+};
 cudaError_t launch_call_batch(const DeviceImage& img, const LaunchPlan& plan, int blocks,
                               uint64_t svc_key, uint64_t seq_base, const uint32_t* methods,
                               const uint32_t* recvs, int n_methods, const int64_t* args,
                               int args_per_call, const uint8_t* method_sel, size_t n,
-                              ptype_reply* replies, cudaStream_t stream);
+                              ptype_reply* replies, const CallBatchOut& out, cudaStream_t stream);
 cudaError_t launch_reply_checksum(const ptype_reply* replies, size_t n, uint64_t index_base,
                                   unsigned long long* partials, unsigned long long* out,
                                   cudaStream_t stream);

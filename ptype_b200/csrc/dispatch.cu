@@ -753,6 +753,8 @@ __global__ void __launch_bounds__(kBulkThreads, 5)
 struct ClientBatch {
     uint64_t svc_key;
     uint64_t seq_base;
+    uint32_t index_base;  // added to the indices written to the failed list (chunked host path)
+    uint32_t pad;
     uint32_t method[PTYPE_BATCH_METHODS];
     uint32_t recv[PTYPE_BATCH_METHODS];
 };
@@ -760,7 +762,9 @@ struct ClientBatch {
 template <bool kSmemTable, int kArgs, bool kHasSel, int kUnroll, int kThreads, int kMinCtas>
 __global__ void __launch_bounds__(kThreads, kMinCtas)
     call_batch_kernel(const DeviceImage img, const ClientBatch batch, const int64_t* __restrict__ args,
-                      const uint8_t* __restrict__ method_sel, const size_t n, uint4* __restrict__ replies) {
+                      const uint8_t* __restrict__ method_sel, const size_t n, uint4* __restrict__ replies,
+                      unsigned long long* __restrict__ values, uint2* __restrict__ failed,
+                      const uint32_t failed_cap, unsigned long long* __restrict__ failed_count) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ __align__(16) CtaShared sh;
     const uint32_t lane = threadIdx.x & 31u;
@@ -820,7 +824,18 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
             const uint4 q0 = make_uint4(key_lo, key_hi, static_cast<uint32_t>(seq), static_cast<uint32_t>(seq >> 32));
             const uint4 q1 = make_uint4(m, rv, a01[u].x, a01[u].y);
             const uint4 q2 = make_uint4(a01[u].z, a01[u].w, a2[u].x, a2[u].y);
-            st_stream(replies + idx, dispatch_one<kSmemTable>(img, sh, slots, cache, q0, q1, q2));
+            const uint4 out = dispatch_one<kSmemTable>(img, sh, slots, cache, q0, q1, q2);
+            if (values == nullptr) {
+                st_stream(replies + idx, out);
+            } else {
+                // values-only replies (what CallBatch's caller reads): 8 bytes per call, plus an
+                // (index, status) entry for the rare call that failed
+                values[idx] = static_cast<unsigned long long>(out.x) | (static_cast<unsigned long long>(out.y) << 32);
+                if (out.w != PTYPE_ST_OK) {
+                    const unsigned long long slot = atomicAdd(failed_count, 1ull);
+                    if (slot < failed_cap) failed[slot] = make_uint2(static_cast<uint32_t>(idx) + batch.index_base, out.w);
+                }
+            }
         }
     }
     if (!table_ready) mbar_wait(&sh.table_bar, 0);
@@ -1078,8 +1093,10 @@ template <bool kSmemTable, int kArgs, bool kHasSel>
 cudaError_t launch_call_batch_variant(const DeviceImage& img, const LaunchPlan& plan, int blocks,
                                       const ClientBatch& batch, const int64_t* args,
                                       const uint8_t* method_sel, size_t n, ptype_reply* replies,
-                                      cudaStream_t stream) {
+                                      const CallBatchOut& o, cudaStream_t stream) {
     uint4* r = reinterpret_cast<uint4*>(replies);
+    unsigned long long* values = reinterpret_cast<unsigned long long*>(o.values);
+    uint2* failed = reinterpret_cast<uint2*>(o.failed);
     if (plan.threads == kMaxThreads) {
         auto kernel = call_batch_kernel<kSmemTable, kArgs, kHasSel, 2, kMaxThreads, 1>;
         if (plan.dyn_smem > 48 * 1024) {
@@ -1088,10 +1105,11 @@ cudaError_t launch_call_batch_variant(const DeviceImage& img, const LaunchPlan& 
             if (e != cudaSuccess) return e;
         }
         return launch_kernel(kernel, blocks, plan.threads, plan.dyn_smem, stream, img, batch, args,
-                             method_sel, n, r);
+                             method_sel, n, r, values, failed, o.failed_cap, o.failed_count);
     }
     return launch_kernel(call_batch_kernel<kSmemTable, kArgs, kHasSel, 2, kSmallThreads, kSmallMinCtas>,
-                         blocks, plan.threads, plan.dyn_smem, stream, img, batch, args, method_sel, n, r);
+                         blocks, plan.threads, plan.dyn_smem, stream, img, batch, args, method_sel, n, r,
+                         values, failed, o.failed_cap, o.failed_count);
 }
 }  // namespace
 
@@ -1100,17 +1118,18 @@ cudaError_t launch_call_batch(const DeviceImage& img, const LaunchPlan& plan, in
                               uint64_t svc_key, uint64_t seq_base, const uint32_t* methods,
                               const uint32_t* recvs, int n_methods, const int64_t* args,
                               int args_per_call, const uint8_t* method_sel, size_t n,
-                              ptype_reply* replies, cudaStream_t stream) {
+                              ptype_reply* replies, const CallBatchOut& out, cudaStream_t stream) {
     ClientBatch batch = {};
     batch.svc_key = svc_key;
     batch.seq_base = seq_base;
+    batch.index_base = out.index_base;
     for (int i = 0; i < PTYPE_BATCH_METHODS; ++i) {
         batch.method[i] = methods[i < n_methods ? i : 0];
         batch.recv[i] = recvs[i < n_methods ? i : 0];
     }
     const bool sel = method_sel != nullptr;
 #define PTYPE_CB(SM, AR, SEL) \
-    launch_call_batch_variant<SM, AR, SEL>(img, plan, blocks, batch, args, method_sel, n, replies, stream)
+    launch_call_batch_variant<SM, AR, SEL>(img, plan, blocks, batch, args, method_sel, n, replies, out, stream)
     if (plan.smem_table) {
         if (args_per_call == 2) return sel ? PTYPE_CB(true, 2, true) : PTYPE_CB(true, 2, false);
         return sel ? PTYPE_CB(true, 3, true) : PTYPE_CB(true, 3, false);

@@ -435,6 +435,54 @@ def test_call_batch_prime_and_errors(ctx, oracle):
     assert np.all(rep["status"] == p.ST_NO_SERVICE) and np.all(rep["node"] == p.NO_NODE)
 
 
+@pytest.mark.parametrize("kind", ["pageable", "pinned", "device"])
+def test_call_batch_values_only(ctx, oracle, kind):
+    """ptype_b200_call_batch_values: 8-byte values plus an (index, status) list of the failed
+    calls - what CallBatch's caller reads - equal the full reply records' value/status."""
+    spec = w.calculator_registry()
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    n = 300_017
+    reqs = w.calculator_calls(n, seed=77)
+    bad = np.arange(0, n, 9973)
+    reqs["method"][bad] = 0xDEAD0000 | (bad & 0xFFFF).astype(np.uint32) % 2   # two unknown methods
+    want = snap.dispatch(reqs)
+    assert (want["status"] != 0).sum() == len(bad)
+    key, base, methods, sel, args = w.as_client_batch(reqs)
+    assert len(methods) == 4
+    if kind == "pageable":
+        values, failed, count = ctx.call_batch_values(key, base, methods, args, sel, failed_cap=64)
+    elif kind == "pinned":
+        pa, ps, pv = p.PinnedArray(args.size, np.int64), p.PinnedArray(n, np.uint8), p.PinnedArray(n, np.int64)
+        pa.array[:] = args.reshape(-1)
+        ps.array[:] = sel
+        launches = ctx.launch_count()
+        _, failed, count = ctx.call_batch_values(key, base, methods, pa.array.reshape(args.shape), ps.array,
+                                                 pv.array, failed_cap=64)
+        assert ctx.launch_count() == launches + 1
+        values = pv.array.copy()
+        for b in (pa, ps, pv):
+            b.free()
+    else:
+        d_args = ctx.device_buffer(args.nbytes).upload(args)
+        d_sel = ctx.device_buffer(n).upload(sel)
+        d_val = ctx.device_buffer(n * 8)
+        _, failed, count = ctx.call_batch_values(key, base, methods, d_args, d_sel, d_val, failed_cap=64,
+                                                 n=n, args_per_call=2)
+        values = d_val.download(np.int64, n)
+        for b in (d_args, d_sel, d_val):
+            b.free()
+    assert np.array_equal(values, want["value"])
+    assert count == len(bad) and len(failed) == len(bad)
+    order = np.argsort(failed["index"])
+    assert np.array_equal(failed["index"][order], bad.astype(np.uint32))
+    assert np.array_equal(failed["status"][order], want["status"][bad])
+    # a list shorter than the failures: exact count, valid distinct entries
+    _, few, count = ctx.call_batch_values(key, base, methods, args, sel, failed_cap=5)
+    assert count == len(bad) and len(few) == 5 and len(set(few["index"].tolist())) == 5
+    assert np.all(np.isin(few["index"], bad))
+
+
 def test_call_batch_against_the_big_table(ctx, stress, oracle):
     """The compact form with the 12 800-slot table staged in shared memory (1024-thread CTAs)."""
     spec, img, snap, _ = stress
