@@ -227,6 +227,9 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=8.0)
     ap.add_argument("--flags", type=int, default=0, help="extra dispatch flags (4 = probe table in L2)")
     ap.add_argument("--update-every", type=int, default=64, help="c5: steps between snapshot updates")
+    ap.add_argument("--update-mode", default="image", choices=["image", "delta"],
+                    help="c5: 'image' rebuilds the snapshot on rank 0 and broadcasts it (NCCL); 'delta' has "
+                         "every rank apply the same watch event to its table on the device")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -293,14 +296,22 @@ def main():
         device-only image, and its installation on every GPU: ncclBroadcast, or publish on 1 GPU."""
         t0 = time.perf_counter()
         img = None
+        # every rank draws the same event (same seed), like every host seeing the same etcd watch
+        svc = f"svc_{int(live_rng.integers(0, 10_000)):05d}"
+        node = f"node_{int(live_rng.integers(0, 64)):02d}"
+        leaving = (svc, node) in live_nodes
+        if leaving:
+            del live_nodes[(svc, node)]
+        else:
+            live_nodes[(svc, node)] = (svc, node, "10.99.0.1", 9000)
+        if args.update_mode == "delta":
+            ctx.update_service(svc, -1 if leaving else +1)
+            update_ms.append((time.perf_counter() - t0) * 1e3)
+            return
         if rank == 0:
-            svc = f"svc_{int(live_rng.integers(0, 10_000)):05d}"
-            node = f"node_{int(live_rng.integers(0, 64)):02d}"
-            if (svc, node) in live_nodes:
-                del live_nodes[(svc, node)]
+            if leaving:
                 builder.unregister(svc, node)
             else:
-                live_nodes[(svc, node)] = (svc, node, "10.99.0.1", 9000)
                 builder.register(svc, node, "10.99.0.1", 9000)
             img = builder.finish(epoch)
         if multi:
@@ -541,7 +552,9 @@ def main():
         if live:
             line["config"]["live_updates"] = {"count": len(update_ms), "every_steps": args.update_every,
                                               "host_ms_avg": float(np.mean(update_ms)) if update_ms else None,
-                                              "transport": "ncclBroadcast" if multi else "publish (1 GPU)"}
+                                              "transport": "on-device patch of the table (update_service)"
+                                              if args.update_mode == "delta" else
+                                              ("rebuilt image, ncclBroadcast" if multi else "rebuilt image, publish")}
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
         print(json.dumps(line), flush=True)

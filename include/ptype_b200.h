@@ -267,6 +267,18 @@ int ptype_b200_stream(ptype_ctx*, int dev, void** cuda_stream);
  * handleNewNodes (cluster/rpc.go:233-236).  An image with zero services is
  * installed as given; "ignore empty updates" (rpc.go:204-206) is host policy. */
 int ptype_b200_publish_image(ptype_ctx*, const void* image, size_t bytes);
+/* One node joined (+1) or left (-1) `service` (any delta is accepted): patch the installed
+ * snapshot ON THE DEVICE instead of rebuilding and uploading an image.  The service's node count
+ * changes by delta and every service that sorts after it moves its node ids by delta - what
+ * rebuilding from the changed registry would give (cluster/registry.go:152-166 re-lists the
+ * service on every watch event; this is that event applied in place).  The active table is
+ * copied to the inactive buffer and patched there, then the epoch advances by one at a batch
+ * boundary, without stopping the dispatch streams.  In a multi-process deployment every
+ * process applies the same events (each has its own watch, as in the reference).
+ * PTYPE_E_NOT_FOUND: the snapshot has no such service (a new service needs a new image);
+ * PTYPE_E_LIMIT: the count would leave [0, 2^24).  Host-side lookups on the context's copy of
+ * the image (ptype_b200_current_image) see the patched table but lose the node names. */
+int ptype_b200_update_service(ptype_ctx*, const char* service, int delta);
 int ptype_b200_epoch(ptype_ctx*, int dev, uint64_t* epoch);
 /* Copy of the blob last installed (on non-root ranks: the bytes NCCL delivered).
  * *bytes in: capacity of out, out: size of the blob; PTYPE_E_LIMIT if too small. */

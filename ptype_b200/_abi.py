@@ -100,6 +100,7 @@ SIGNATURES = [
     ("ptype_b200_memcpy_d2h", C.c_int, [_vp, C.c_int, _vp, _vp, C.c_size_t]),
     ("ptype_b200_stream", C.c_int, [_vp, C.c_int, C.POINTER(_vp)]),
     ("ptype_b200_publish_image", C.c_int, [_vp, _vp, C.c_size_t]),
+    ("ptype_b200_update_service", C.c_int, [_vp, C.c_char_p, C.c_int]),
     ("ptype_b200_epoch", C.c_int, [_vp, C.c_int, _u64p]),
     ("ptype_b200_current_image", C.c_int, [_vp, _vp, C.POINTER(C.c_size_t)]),
     ("ptype_b200_nccl_unique_id", C.c_int, [_vp]),

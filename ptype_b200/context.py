@@ -92,6 +92,10 @@ class Context:
         check(lib.ptype_b200_publish_image(self._h, image._buf, len(image)), "publish_image")
         self.image = image
 
+    def update_service(self, service: str, delta: int) -> None:
+        """A node joined (+1) or left (-1) `service`: patch the installed snapshot on the device."""
+        check(lib.ptype_b200_update_service(self._h, service.encode(), delta), "update_service")
+
     def epoch(self, dev: int = 0) -> int:
         e = C.c_uint64()
         check(lib.ptype_b200_epoch(self._h, dev, C.byref(e)), "epoch")

@@ -17,6 +17,7 @@
 
 #include "../../include/ptype_b200.h"
 #include "device_image.h"
+#include "table_hash.h"
 
 namespace {
 
@@ -163,6 +164,7 @@ struct ptype_ctx {
     int rank = 0, nranks = 1;
     std::mutex image_mu;
     std::vector<unsigned char> host_image;  // last installed blob (host-side lookups)
+    bool host_checksum_stale = false;       // update_service patched it since the checksum was taken
 };
 
 namespace {
@@ -488,6 +490,73 @@ int ptype_b200_publish_image(ptype_ctx* ctx, const void* image, size_t bytes) {
     std::lock_guard<std::mutex> lk(ctx->image_mu);
     ctx->host_image.assign(static_cast<const unsigned char*>(image),
                            static_cast<const unsigned char*>(image) + bytes);
+    ctx->host_checksum_stale = false;
+    return PTYPE_OK;
+}
+
+int ptype_b200_update_service(ptype_ctx* ctx, const char* service, int delta) {
+    if (!ctx || !service) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> ilk(ctx->image_mu);
+    if (ctx->host_image.empty()) return PTYPE_E_NO_IMAGE;
+    ptype_image_header* hh = reinterpret_cast<ptype_image_header*>(ctx->host_image.data());
+    const uint64_t key = ptype_b200_service_key(service, hh->key_salt);
+    // Patch the host copy first: it tells whether the service exists and keeps host-side readers
+    // of the device part in step.  Same rule as the kernel (update.cu).
+    ptype_slot* hs = reinterpret_cast<ptype_slot*>(ctx->host_image.data() + hh->off_slots);
+    uint32_t at = PTYPE_SLOT_EMPTY;
+    for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
+        const uint32_t c = ptype::slot_of(static_cast<uint32_t>(key), static_cast<uint32_t>(key >> 32),
+                                          hh->table_seed, w, hh->n_slots);
+        if (hs[c].node_base != PTYPE_SLOT_EMPTY && hs[c].key == key) at = c;
+    }
+    if (at == PTYPE_SLOT_EMPTY) return PTYPE_E_NOT_FOUND;
+    const uint32_t n_old = hs[at].n_and_recv & 0xFFFFFFu;
+    const long long n_new = static_cast<long long>(n_old) + delta;
+    if (n_new < 0 || n_new > 0xFFFFFF) return PTYPE_E_LIMIT;
+    for (DeviceState* d : ctx->devs) {
+        std::lock_guard<std::mutex> lk(d->mu);
+        if (d->active < 0) return PTYPE_E_NO_IMAGE;
+        CU(cudaSetDevice(d->device));
+        const int src = d->active, buf = src == 0 ? 1 : 0;
+        int rc = reserve_inactive(d, buf, hh->device_bytes);
+        if (rc != PTYPE_OK) return rc;
+        if (!d->d_size) CU(cudaMalloc(&d->d_size, 16));
+        rc = copy_stream_waits_for_dispatches(d);
+        if (rc != PTYPE_OK) return rc;
+        CU(cudaMemcpyAsync(d->image_buf[buf], d->image_buf[src], hh->device_bytes, cudaMemcpyDeviceToDevice,
+                           d->copy_stream));
+        CU(ptype::launch_patch_service(
+            reinterpret_cast<ptype_slot*>(static_cast<unsigned char*>(d->image_buf[buf]) + hh->off_slots),
+            hh->n_slots, hh->table_seed, key, delta, reinterpret_cast<uint32_t*>(d->d_size), d->copy_stream));
+        ctx->launches.fetch_add(1);
+        rc = dispatches_wait_for_copy_stream(d);
+        if (rc != PTYPE_OK) return rc;
+        // same tables, same plans: only the pointers and the epoch move
+        const unsigned char* base = static_cast<const unsigned char*>(d->image_buf[buf]);
+        ptype::DeviceImage v = d->view[src];
+        v.slots = reinterpret_cast<const ptype_slot*>(base + hh->off_slots);
+        v.conn_hash = reinterpret_cast<const uint32_t*>(base + hh->off_conn_hash);
+        v.methods = reinterpret_cast<const ptype_method*>(base + hh->off_methods);
+        v.mtable = reinterpret_cast<const ptype_method*>(base + hh->off_mtable);
+        d->view[buf] = v;
+        for (int g = 0; g < kPlanKinds; ++g)
+            for (int x = 0; x < 2; ++x) d->plan[buf][g][x] = d->plan[src][g][x];
+        d->epoch[buf] = d->epoch[src] + 1;
+        d->active = buf;
+    }
+    const uint32_t pivot = hs[at].node_base + n_old;
+    for (uint32_t i = 0; i < hh->n_slots; ++i) {
+        if (hs[i].node_base == PTYPE_SLOT_EMPTY) continue;
+        if (i == at)
+            hs[i].n_and_recv = (hs[i].n_and_recv & 0xFF000000u) | static_cast<uint32_t>(n_new);
+        else if (hs[i].node_base >= pivot)
+            hs[i].node_base = static_cast<uint32_t>(static_cast<long long>(hs[i].node_base) + delta);
+    }
+    // the blob no longer matches its node/string sections: keep only what the kernels read
+    hh->epoch += 1;
+    hh->n_nodes = static_cast<uint32_t>(static_cast<long long>(hh->n_nodes) + delta);
+    hh->host_sections = 0;
+    ctx->host_checksum_stale = true;  // recomputed when somebody asks for the blob
     return PTYPE_OK;
 }
 
@@ -506,6 +575,12 @@ int ptype_b200_current_image(ptype_ctx* ctx, void* out, size_t* bytes) {
     if (!ctx || !bytes) return PTYPE_E_INVAL;
     std::lock_guard<std::mutex> lk(ctx->image_mu);
     if (ctx->host_image.empty()) return PTYPE_E_NO_IMAGE;
+    if (ctx->host_checksum_stale) {
+        ptype_image_header* hh = reinterpret_cast<ptype_image_header*>(ctx->host_image.data());
+        hh->body_checksum = ptype::fnv1a64(ctx->host_image.data() + sizeof(ptype_image_header),
+                                           ctx->host_image.size() - sizeof(ptype_image_header), 0);
+        ctx->host_checksum_stale = false;
+    }
     const size_t need = ctx->host_image.size();
     if (out && *bytes >= need) std::memcpy(out, ctx->host_image.data(), need);
     const bool fits = out && *bytes >= need;
@@ -552,6 +627,7 @@ int ptype_b200_broadcast_image(ptype_ctx* ctx, const void* image, size_t bytes, 
         int rc = ptype_b200_image_validate(image, bytes);
         if (rc != PTYPE_OK) return rc;
     }
+    std::lock_guard<std::mutex> lk2(ctx->image_mu);  // lock order: image_mu, then a device's mu
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(d->device));
     int rc = copy_stream_waits_for_dispatches(d);
@@ -588,8 +664,8 @@ int ptype_b200_broadcast_image(ptype_ctx* ctx, const void* image, size_t bytes, 
     if (rc != PTYPE_OK) return rc;
     rc = adopt_image(ctx, d, buf, *reinterpret_cast<const ptype_image_header*>(host.data()), host.data());
     if (rc != PTYPE_OK) return rc;
-    std::lock_guard<std::mutex> lk2(ctx->image_mu);
     ctx->host_image.swap(host);
+    ctx->host_checksum_stale = false;
     return PTYPE_OK;
 }
 

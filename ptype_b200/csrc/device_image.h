@@ -76,6 +76,9 @@ cudaError_t launch_gob_encode_replies(const ptype_reply* replies, size_t n, unsi
 cudaError_t launch_gob_decode_args(const uint8_t* bytes, const unsigned long long* offsets, size_t n,
                                    int64_t* args, int args_per_call, uint8_t* status, cudaStream_t stream);
 
+cudaError_t launch_patch_service(ptype_slot* slots, uint32_t n_slots, uint32_t seed, uint64_t key, int delta,
+                                 uint32_t* result, cudaStream_t stream);
+
 // Records the text ptype_b200_last_error() returns on the calling thread.
 void set_last_error(const char* text);
 

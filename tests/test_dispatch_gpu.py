@@ -329,6 +329,57 @@ def test_live_updates_without_stopping_the_stream(ctx, oracle):
         d.free()
 
 
+def test_update_service_patches_the_table_on_the_device(ctx, oracle):
+    """ptype_b200_update_service: one node joins or leaves; the table is patched on the device
+    (node count of the service, node ids of every service after it) and batches submitted after
+    the update - with none of them synchronised - are answered as from a freshly built image."""
+    base = w.stress_registry(300, 5)
+    base.declare = ["svc_00100x_empty"]
+    ctx.publish(base.image(epoch=1))
+    nodes = {(s, nd): (s, nd, a, pt) for s, nd, a, pt in base.nodes}
+    rng = np.random.default_rng(11)
+    n, rounds = 100_000, 12
+    d_reqs, d_reps, wants = [], [], []
+    plan = []
+    for k in range(rounds):
+        svc = f"svc_{int(rng.integers(0, 300)):05d}" if k != 3 else "svc_00100x_empty"
+        present = sorted(nd for (s, nd) in nodes if s == svc)
+        if present and (rng.integers(0, 2) == 0 or len(present) >= 5):
+            del nodes[(svc, present[int(rng.integers(0, len(present)))])]
+            plan.append((svc, -1))
+        else:
+            name = f"node_{int(rng.integers(5, 99)):02d}"
+            nodes[(svc, name)] = (svc, name, "10.7.7.7", 7777)
+            plan.append((svc, +1))
+        spec = w.RegistrySpec(sorted(nodes.values()), base.expose + [("svc_00100x_empty", "Calculator")],
+                              ["svc_00100x_empty"], base.local_addr, base.max_connections)
+        kv, snap = oracle.snapshot_from_spec(spec)
+        req = w.stress_calls(n, 300, seed=50 + k)
+        req["svc_key"][::97] = p.service_key("svc_00100x_empty")
+        d_reqs.append(ctx.device_buffer(n * 48).upload(req))
+        d_reps.append(ctx.device_buffer(n * 16))
+        wants.append(snap.dispatch(req, threads=8))
+    # the image does not expose Calculator on the empty service: rebuild the first image with it
+    first = w.RegistrySpec(base.nodes, base.expose + [("svc_00100x_empty", "Calculator")],
+                           ["svc_00100x_empty"], base.local_addr, base.max_connections)
+    ctx.publish(first.image(epoch=1))
+    for k, (svc, delta) in enumerate(plan):
+        ctx.update_service(svc, delta)
+        assert ctx.epoch() == 2 + k
+        ctx.dispatch_batches(ctx.make_batches([(d_reqs[k], d_reps[k], n)]), sync=False)
+    ctx.sync()
+    for k in range(rounds):
+        assert_same(d_reps[k].download(p.REPLY_DTYPE, n), wants[k])
+    img = ctx.current_image()            # patched host copy: valid, device-only
+    assert img.epoch == 1 + rounds and img.header.host_sections == 0 and img.header.n_nodes == len(nodes)
+    with pytest.raises(p.PtypeError):
+        ctx.update_service("never_registered", +1)
+    with pytest.raises(p.PtypeError):
+        ctx.update_service("svc_00000", -1000)
+    for d in d_reqs + d_reps:
+        d.free()
+
+
 def test_max_connections_larger_than_shared_cache(ctx, oracle):
     """MaxConnections above the 256 hashes kept in shared memory: hashes read from global."""
     nodes = [("wide", f"n{i:04d}", f"10.1.{i >> 8}.{i & 255}", 7000) for i in range(700)]
