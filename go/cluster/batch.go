@@ -192,6 +192,21 @@ func (d *Dispatcher) publishLocked() error {
 	return nil
 }
 
+// UpdateService applies one watch event in place: a node joined (+1) or left (-1) `service`.
+// The table is patched on the GPU (ptype_b200_update_service); nothing is rebuilt or uploaded.
+// The Dispatcher's own node lists must be kept in step by the caller (SetNodes does both).
+func (d *Dispatcher) UpdateService(service string, delta int) error {
+	d.mu.Lock()
+	defer d.mu.Unlock()
+	cs := C.CString(service)
+	defer C.free(unsafe.Pointer(cs))
+	if err := abiError("ptype_b200_update_service", C.ptype_b200_update_service(d.ctx, cs, C.int(delta))); err != nil {
+		return err
+	}
+	d.epoch++
+	return nil
+}
+
 // SelectedNodes is getSelectedNodes() (rpc.go:293-297) read back from the snapshot.
 func (d *Dispatcher) SelectedNodes(service string) []Node {
 	d.mu.Lock()

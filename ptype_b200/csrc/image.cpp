@@ -248,13 +248,19 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
         s.node_base = next_node;
         s.n_nodes = static_cast<uint32_t>(rec.nodes.size());
         s.recv_mask = rec.recv_mask;
-        // std::map iterates node names in byte order = key order within the service
-        // ("node10" before "node2", like the etcd range).
         if (!host_sections) {
             next_node += s.n_nodes;
             continue;
         }
-        for (const auto& nk : rec.nodes) {
+        // Order inside the service = byte order of the keys services/<svc>/<node>/, i.e. of the
+        // node names WITH their trailing '/': "node10" before "node2", and "a-b" before "a"
+        // because '-' sorts below '/'.
+        std::vector<std::pair<std::string, const std::pair<const std::string, NodeRec>*>> by_key;
+        by_key.reserve(rec.nodes.size());
+        for (const auto& nk : rec.nodes) by_key.emplace_back(nk.first + "/", &nk);
+        std::sort(by_key.begin(), by_key.end(), [](const auto& a, const auto& c) { return a.first < c.first; });
+        for (const auto& e : by_key) {
+            const auto& nk = *e.second;
             ptype_node& nd = nodes[next_node++];
             nd.address_off = intern(nk.second.address);
             nd.name_off = intern(nk.first);

@@ -243,3 +243,38 @@ def test_sharded_dispatch_equals_unsharded(oracle):
         idx = shard_indices(len(r), 4, rank)
         out[idx] = snap.dispatch(r[idx])
     assert out.tobytes() == whole.tobytes()
+
+
+def test_random_registries_match_oracle(oracle):
+    """Randomised registries with awkward names (characters that sort around '/', long and short
+    names, re-registration, empty services): the image's per-service selection and global node
+    numbering equal the oracle's for several (localAddr, MaxConnections) pairs."""
+    rng = np.random.default_rng(2024)
+    alphabet = list("abcXYZ019-._~+ !#$%&'()*,:;<=>?@[]^`{|}")
+    for trial in range(25):
+        n_services = int(rng.integers(1, 30))
+        names = set()
+        while len(names) < n_services:
+            k = int(rng.integers(1, 12))
+            s = "".join(rng.choice(alphabet, k))
+            if s not in (".", ".."):
+                names.add(s)
+        nodes = {}
+        for svc in names:
+            for _ in range(int(rng.integers(0, 12))):
+                nd = "".join(rng.choice(alphabet, int(rng.integers(1, 8))))
+                if nd in (".", ".."):
+                    continue
+                nodes[(svc, nd)] = (svc, nd, f"h{int(rng.integers(0, 1000))}", int(rng.integers(1, 65536)))
+        declared = [s for s in names if not any(k[0] == s for k in nodes)]
+        local_addr = str(rng.choice(["", "10.0.0.5", "127.0.0.1", "192.168.1.77"]))
+        max_conn = int(rng.choice([0, 1, 2, 3, 5, 300]))
+        spec = w.RegistrySpec(list(nodes.values()), [], declared, local_addr, max_conn)
+        img = spec.image()
+        kv, snap = oracle.snapshot_from_spec(spec)
+        assert img.header.n_nodes == len(nodes) == len(kv.range_prefix("services/"))
+        for svc in names:
+            assert img.selected(svc) == snap.selected(svc), (trial, svc)
+        for nid in range(len(nodes)):
+            a, port, svc, _ = img.node(nid)
+            assert (a, port, svc) == snap.node(nid), (trial, nid)
