@@ -131,6 +131,36 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(seen), "samples": len(use), "samples_in_timed_region": len(inside)}
 
 
+_ORIGINAL_AFFINITY: set = set()
+
+
+def restore_affinity() -> None:
+    """Give the CPU baseline every host core back."""
+    if _ORIGINAL_AFFINITY:
+        try:
+            os.sched_setaffinity(0, _ORIGINAL_AFFINITY)
+        except Exception:
+            pass
+
+
+def bind_to_gpu_numa_node(index: int) -> None:
+    """Run this rank on the CPUs next to its GPU (NVML's affinity mask) so that pinned buffers are
+    first-touched on the local NUMA node; host<->device traffic of 8 ranks otherwise crosses sockets."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {w * 64 + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        if cpus & allowed:
+            _ORIGINAL_AFFINITY.update(allowed)
+            os.sched_setaffinity(0, cpus & allowed)
+    except Exception:
+        pass
+
+
 def cpu_port_rate(spec, reqs, threads: int, min_seconds: float, check_limit: int = 1 << 16):
     """calls/s of the CPU oracle (C port of the reference path) over repeated passes."""
     from oracle import binding as ob
@@ -248,6 +278,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the dispatch path has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    bind_to_gpu_numa_node(local_rank)
     multi = world > 1
     if multi:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -494,6 +525,7 @@ def main():
                                         vcount != int((want["status"] != 0).sum())):
             raise SystemExit("bench.py: call_batch_values differs from the oracle - number withheld")
         if not multi:
+            restore_affinity()
             threads = os.cpu_count() or 1
             rate, passes, el, _ = cpu_port_rate(spec, hb, threads, args.cpu_seconds)
             rate1, passes1, el1, _ = cpu_port_rate(spec, hb, 1, min(2.0, args.cpu_seconds))
