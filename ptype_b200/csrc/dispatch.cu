@@ -1,21 +1,29 @@
-// dispatch.cu — the fused batched-dispatch kernel for sm_100a and its launcher.
+// dispatch.cu — the fused batched-dispatch kernels for sm_100a and their launchers.
 //
 // One thread handles one call end to end; one warp handles 32 consecutive calls:
-//   load     three coalesced 128-bit loads per lane cover the warp's 32 x 48 B
-//            request records, then a 12-shuffle transpose hands every lane its
-//            own record (no shared memory, no strided global access)
-//   lookup   exact-key probe of the open-addressing registry table staged in
-//            shared memory by one bulk-async (TMA) copy per CTA
+//   load     LDG kernels: three coalesced 128-bit loads per lane cover the warp's 32 x 48 B
+//            request records, then a 12-shuffle transpose hands every lane its own record.
+//            Bulk kernels: one bulk-async (TMA) copy per tile into a per-warp shared-memory
+//            ring, then three conflict-free LDS.128 per lane.
+//   lookup   exact-key lookup in the 3-way cuckoo registry table, staged in shared memory by
+//            bulk-async copies once per CTA (or probed in L2 when it does not fit); a per-lane
+//            cache of the last service skips it for single-service batches
 //            — replaces the result of Registry.Services()/nodes()
 //              (cluster/registry.go:93-117,152-166)
 //   route    selectNodes + hashConnectionIndex + roundRobinSelect in closed form
 //            (cluster/rpc.go:176-183,252-270): with n registered nodes and
 //            m = MaxConnections,  k = (m == 0 || n <= m) ? n : m,
 //            r = int(seq) % k,  node = base + (k == n ? r : connHash[r] % n)
-//   resolve  "Receiver.Method" the way the net/rpc server does [Go stdlib]
+//   resolve  "Receiver.Method" the way the net/rpc server does [Go stdlib]: one perfect-hash probe
 //   execute  Multiply / Add / Check (example/calculator/calculator.go:9-12,
 //            example/optimus/prime.go:15-25)
 //   pack     one 128-bit store per lane: 32 x 16 B contiguous reply records
+//
+// Kernels: dispatch_kernel (one batch, LDG), dispatch_multi_kernel (up to 96 batches per
+// launch, LDG - what ptype_b200_dispatch_batches runs), dispatch_bulk_kernel /
+// dispatch_bulk_multi_kernel (TMA-staged requests), call_batch_kernel (one Client's batch in
+// compact form), checksum kernels.  All persistent; all carry programmatic-dependent-launch
+// hooks so consecutive launches overlap ramp-up and drain.
 //
 // HBM-bound integer work: 64 algorithmic bytes per call, no tensor cores.
 #include <cuda_runtime.h>
