@@ -70,3 +70,30 @@ def test_two_gpu_broadcast_and_sharded_dispatch(tmp_path):
     import torch.multiprocessing as mp
     mp.spawn(_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok").read_text() == "ok"
+
+
+def test_one_process_two_devices(oracle=None):
+    """A single host process driving two GPUs through one context (how a Go host with several
+    GPUs would use the ABI): one publish installs the snapshot on both, dispatches carry the
+    device index, and both devices answer like the oracle."""
+    import ptype_b200 as p
+    from ptype_b200 import workloads as w
+    from oracle import binding as ob
+    if p.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    spec = w.stress_registry(500, 4)
+    kv, snap = ob.snapshot_from_spec(spec)
+    with p.Context([0, 1]) as ctx:
+        ctx.publish(spec.image(epoch=3))
+        assert ctx.epoch(0) == 3 and ctx.epoch(1) == 3
+        for dev in (0, 1):
+            reqs = w.stress_calls(200_000, 500, seed=40 + dev)
+            want = snap.dispatch(reqs, threads=4)
+            assert ctx.dispatch(reqs, dev=dev).tobytes() == want.tobytes()
+            d_req = ctx.device_buffer(len(reqs) * 48, dev).upload(reqs)
+            d_rep = ctx.device_buffer(len(reqs) * 16, dev)
+            ctx.dispatch_batches(ctx.make_batches([(d_req, d_rep, len(reqs))]), dev=dev)
+            assert d_rep.download(p.REPLY_DTYPE, len(reqs)).tobytes() == want.tobytes()
+            assert ctx.reply_checksum(d_rep, len(reqs), dev=dev, device=True) == ob.reply_checksum(want)
+        ctx.update_service("svc_00007", -1)
+        assert ctx.epoch(0) == 4 and ctx.epoch(1) == 4
