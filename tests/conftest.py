@@ -11,6 +11,12 @@ if str(ROOT) not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run with -m gpu on a B200)")
+    # The package refuses to import without its CUDA library (no CPU fallback).  nvcc
+    # cross-compiles it without a GPU, so build it here if a fresh checkout has not yet.
+    lib = ROOT / "ptype_b200" / "libptype_b200.so"
+    if not lib.exists():
+        import subprocess
+        subprocess.run(["make", "-C", str(ROOT / "ptype_b200" / "csrc")], check=True)
 
 
 @pytest.fixture(scope="session")
