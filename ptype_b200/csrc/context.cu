@@ -169,6 +169,10 @@ struct ptype_ctx {
 
 namespace {
 
+// 128-bit loads and stores need 16-byte aligned record arrays (cudaMalloc, cudaHostAlloc and
+// ptype_b200_alloc_pinned all give at least that); 8 for int64 arrays.
+bool misaligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) != 0; }
+
 DeviceState* dev_of(ptype_ctx* ctx, int dev) {
     if (!ctx || dev < 0 || dev >= static_cast<int>(ctx->devs.size())) return nullptr;
     return ctx->devs[dev];
@@ -682,6 +686,8 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
                            ptype_batch_stats* stats, uint32_t flags) {
     DeviceState* d = dev_of(ctx, dev);
     if (!d || (n && (!reqs || !replies))) return PTYPE_E_INVAL;
+    if (misaligned(reqs, 16) || misaligned(replies, 16) || misaligned(failed_idx, 4) || misaligned(stats, 8))
+        return PTYPE_E_INVAL;
     if (n > 0xFFFFFFFFull || failed_cap > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
     if (failed_idx && !stats) return PTYPE_E_INVAL;  // the list's length lives in stats
     std::lock_guard<std::mutex> lk(d->mu);
@@ -794,6 +800,7 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
     const ptype::LaunchPlan& plan = d->plan[buf][plan_kind(flags)][0];
     for (size_t b = 0; b < count; ++b) {
         if (batches[b].n && (!batches[b].reqs || !batches[b].replies)) return PTYPE_E_INVAL;
+        if (misaligned(batches[b].reqs, 16) || misaligned(batches[b].replies, 16)) return PTYPE_E_INVAL;
         if (batches[b].n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
     }
     if (!(flags & PTYPE_F_ONE_LAUNCH_PER_BATCH)) {
@@ -843,6 +850,8 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
     if (!d || !methods || n_methods < 1 || n_methods > PTYPE_BATCH_METHODS ||
         (args_per_call != 2 && args_per_call != 3) || (n && (!args || (!replies && !values))) ||
         (failed_cap && !failed))
+        return PTYPE_E_INVAL;
+    if (misaligned(args, args_per_call == 2 ? 16 : 8) || misaligned(replies, 16) || misaligned(values, 8))
         return PTYPE_E_INVAL;
     if (n > 0xFFFFFFFFull || failed_cap > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
     std::lock_guard<std::mutex> lk(d->mu);

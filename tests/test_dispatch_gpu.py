@@ -575,6 +575,21 @@ def test_pinned_buffers_take_the_zero_copy_path(ctx, oracle):
         b.free()
 
 
+def test_misaligned_buffers_are_rejected(ctx):
+    """Record arrays must be 16-byte aligned (128-bit loads/stores): a misaligned pointer is an
+    argument error, not a device fault."""
+    from ptype_b200._abi import lib, E_INVAL, F_DEVICE_PTRS, Batch
+    ctx.publish(w.calculator_registry().image())
+    d = ctx.device_buffer(4096)
+    assert lib.ptype_b200_dispatch(ctx._h, 0, d.ptr + 8, 10, d.ptr + 1024, F_DEVICE_PTRS) == E_INVAL
+    assert lib.ptype_b200_dispatch(ctx._h, 0, d.ptr, 10, d.ptr + 1032, F_DEVICE_PTRS) == E_INVAL
+    one = (Batch * 1)()
+    one[0].reqs, one[0].replies, one[0].n = d.ptr + 4, d.ptr + 1024, 10
+    assert lib.ptype_b200_dispatch_batches(ctx._h, 0, one, 1, F_DEVICE_PTRS) == E_INVAL
+    d.free()
+    ctx.dispatch(w.calculator_calls(10))        # the context is still usable
+
+
 def test_dispatch_without_image_fails():
     c = p.Context([0])
     try:
