@@ -20,6 +20,7 @@
 #pragma once
 
 #include <algorithm>
+#include <array>
 #include <atomic>
 #include <cctype>
 #include <chrono>
@@ -772,6 +773,95 @@ class Client {  // cluster/rpc.go:40-43,126-139
     std::atomic<uint64_t> connsUpdated_{0};
     std::mutex errMu_;
     std::optional<Error> pendingErr_;
+};
+
+// -------------------------------------------------------------------------- coalescing
+// The dispatch loop a host puts in front of the GPU path: many goroutine-style callers invoke
+// Call() concurrently, as they do with cluster.(*Client).Call (rpc.go:59 is goroutine-safe); a
+// background thread gathers what arrived within `max_wait` (or `max_batch` calls, whichever comes
+// first), submits one CallBatch per method name and hands every caller its own reply or error.
+// Sequence numbers are still taken from the Client's single counter, so the calls of a batch
+// are routed like consecutive Call()s made in the order they were gathered.
+class CallCoalescer {
+   public:
+    explicit CallCoalescer(Client* client, size_t max_batch = 65536,
+                           std::chrono::microseconds max_wait = std::chrono::microseconds(200))
+        : client_(client), max_batch_(max_batch), max_wait_(max_wait), worker_([this] { Run(); }) {}
+    ~CallCoalescer() {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        worker_.join();
+    }
+    // Blocks until the call has been dispatched; same results and errors as Client::Call.
+    Error Call(const std::string& serviceMethod, const int64_t (&args)[3], int64_t* reply) {
+        Pending p;
+        p.args[0] = args[0];
+        p.args[1] = args[1];
+        p.args[2] = args[2];
+        {
+            std::unique_lock<std::mutex> lk(mu_);
+            queue_[serviceMethod].push_back(&p);
+            ++queued_;
+            cv_.notify_all();
+            done_cv_.wait(lk, [&] { return p.done; });
+        }
+        if (p.err) return p.err;
+        if (Error se = StatusError(p.rep.Status, serviceMethod)) return se;
+        *reply = p.rep.Value;
+        return Error();
+    }
+    uint64_t Batches() const { return batches_.load(); }
+
+   private:
+    struct Pending {
+        int64_t args[3];
+        BatchReply rep;
+        Error err;
+        bool done = false;
+    };
+    void Run() {
+        for (;;) {
+            std::map<std::string, std::vector<Pending*>> take;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return stop_ || queued_ > 0; });
+                if (stop_ && queued_ == 0) return;
+                // let the window fill: until max_batch calls are waiting or max_wait has passed
+                cv_.wait_for(lk, max_wait_, [&] { return stop_ || queued_ >= max_batch_; });
+                take.swap(queue_);
+                queued_ = 0;
+            }
+            for (auto& group : take) {
+                std::vector<Pending*>& ps = group.second;
+                std::vector<std::array<int64_t, 3>> args(ps.size());
+                for (size_t i = 0; i < ps.size(); ++i) args[i] = {ps[i]->args[0], ps[i]->args[1], ps[i]->args[2]};
+                std::vector<BatchReply> reps(ps.size());
+                Error e = client_->CallBatch(group.first, reinterpret_cast<const int64_t(*)[3]>(args.data()),
+                                             ps.size(), reps.data());
+                batches_.fetch_add(1);
+                std::lock_guard<std::mutex> lk(mu_);
+                for (size_t i = 0; i < ps.size(); ++i) {
+                    ps[i]->rep = reps[i];
+                    ps[i]->err = e;
+                    ps[i]->done = true;
+                }
+            }
+            done_cv_.notify_all();
+        }
+    }
+    Client* client_;
+    size_t max_batch_;
+    std::chrono::microseconds max_wait_;
+    std::mutex mu_;
+    std::condition_variable cv_, done_cv_;
+    std::map<std::string, std::vector<Pending*>> queue_;
+    size_t queued_ = 0;
+    bool stop_ = false;
+    std::atomic<uint64_t> batches_{0};
+    std::thread worker_;
 };
 
 }  // namespace cluster

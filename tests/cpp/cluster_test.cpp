@@ -272,6 +272,49 @@ static void TestExample_optimus() {
     }
 }
 
+// Client.Call is goroutine-safe (rpc.go:59,181,287-291): many concurrent callers, each gets
+// its own reply; here they are gathered into batches by the CallCoalescer.  The sequence
+// numbers handed out are exactly 1..N (one counter), so the 3 selected nodes are used evenly.
+static void TestCoalescer_concurrent_callers() {
+    Dispatcher gpu("10.0.0.5", 3);
+    gpu.Expose("calculator", "Calculator");
+    MemRegistry reg;
+    for (int i = 1; i <= 16; ++i) {
+        char name[32], addr[32];
+        std::snprintf(name, sizeof name, "calculator_node_%02d", i);
+        std::snprintf(addr, sizeof addr, "10.0.0.%d", i);
+        REQUIRE(!reg.Register("calculator", name, addr, 31234));
+    }
+    ConnConfig cfg = testConnConfig();
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "calculator", &reg, &cfg, &c));
+    CallCoalescer co(c.get(), 4096, std::chrono::microseconds(300));
+    constexpr int kThreads = 16, kCalls = 1500;
+    std::atomic<int> wrong{0}, errors{0};
+    std::vector<std::thread> ts;
+    for (int t = 0; t < kThreads; ++t)
+        ts.emplace_back([&, t] {
+            for (int i = 0; i < kCalls; ++i) {
+                const int64_t a = t * 100000 + i, b = i - 700;
+                const int64_t args[3] = {a, b, 0};
+                int64_t reply = -1;
+                const bool mul = (i + t) % 2 == 0;
+                Error e = co.Call(mul ? "Calculator.Multiply" : "Calculator.Add", args, &reply);
+                if (e) ++errors;
+                if (reply != (mul ? a * b : a + b)) ++wrong;
+                if (i % 500 == 0) {
+                    int64_t untouched = 7;
+                    if (co.Call("Calculator.Nope", args, &untouched).msg != "rpc: can't find method Calculator.Nope" ||
+                        untouched != 7)
+                        ++wrong;
+                }
+            }
+        });
+    for (auto& th : ts) th.join();
+    REQUIRE(errors == 0 && wrong == 0);
+    REQUIRE(co.Batches() < static_cast<uint64_t>(kThreads) * kCalls / 2);   // calls really were coalesced
+}
+
 // TestNewConnectionBalancer_with_no_available_server (rpc_test.go:307-314)
 static void TestNewClient_with_no_available_server() {
     Dispatcher gpu("", 3);
@@ -395,6 +438,7 @@ int main(int argc, char** argv) {
     RUN(TestOptimus_splitWork_watchReplies);
     if (gpu) {
         RUN(TestClient_Go);
+        RUN(TestCoalescer_concurrent_callers);
         RUN(TestExample_optimus);
         RUN(TestClient_default_conn_config);
         RUN(TestClient_Call);
