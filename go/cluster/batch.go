@@ -405,3 +405,81 @@ func (c *BatchClient) CallBatch(serviceMethod string, args [][3]int64, replies [
 		todo = next
 	}
 }
+
+// Coalescer is the dispatch loop in front of the GPU path: goroutines call Call concurrently,
+// as they do with (*Client).Call today; one goroutine gathers what arrived within MaxWait (or
+// MaxBatch calls), submits one CallBatch per method name and hands every caller its reply.
+type Coalescer struct {
+	c        *BatchClient
+	MaxBatch int
+	MaxWait  time.Duration
+	in       chan *pendingCall
+	done     chan struct{}
+}
+
+type pendingCall struct {
+	method string
+	args   [3]int64
+	rep    BatchReply
+	err    error
+	ready  chan struct{}
+}
+
+func NewCoalescer(c *BatchClient) *Coalescer {
+	co := &Coalescer{c: c, MaxBatch: 65536, MaxWait: 200 * time.Microsecond,
+		in: make(chan *pendingCall, 1<<16), done: make(chan struct{})}
+	go co.run()
+	return co
+}
+
+func (co *Coalescer) Close() { close(co.in); <-co.done }
+
+// Call blocks until the call has been dispatched; results and errors are those of BatchClient.Call.
+func (co *Coalescer) Call(serviceMethod string, args [3]int64, reply *int64) error {
+	p := &pendingCall{method: serviceMethod, args: args, ready: make(chan struct{})}
+	co.in <- p
+	<-p.ready
+	if p.err != nil {
+		return p.err
+	}
+	if err := StatusError(p.rep.Status, serviceMethod); err != nil {
+		return err
+	}
+	*reply = p.rep.Value
+	return nil
+}
+
+func (co *Coalescer) run() {
+	defer close(co.done)
+	for first := range co.in {
+		groups := map[string][]*pendingCall{first.method: {first}}
+		n := 1
+		timer := time.NewTimer(co.MaxWait)
+	gather:
+		for n < co.MaxBatch {
+			select {
+			case p, ok := <-co.in:
+				if !ok {
+					break gather
+				}
+				groups[p.method] = append(groups[p.method], p)
+				n++
+			case <-timer.C:
+				break gather
+			}
+		}
+		timer.Stop()
+		for method, ps := range groups {
+			args := make([][3]int64, len(ps))
+			for i, p := range ps {
+				args[i] = p.args
+			}
+			reps := make([]BatchReply, len(ps))
+			err := co.c.CallBatch(method, args, reps)
+			for i, p := range ps {
+				p.rep, p.err = reps[i], err
+				close(p.ready)
+			}
+		}
+	}
+}
