@@ -98,7 +98,7 @@ enum ptype_opcode {
  * the selection rule (localAddr, ConnConfig.MaxConnections; cluster/rpc.go:19-38,128). */
 
 #define PTYPE_IMAGE_MAGIC 0x49595450u /* "PTYI" */
-#define PTYPE_IMAGE_VERSION 2u
+#define PTYPE_IMAGE_VERSION 3u
 #define PTYPE_SLOT_WAYS 3        /* candidate slots per key (3-way cuckoo hashing) */
 #define PTYPE_MTABLE_SLOTS 64   /* perfect-hash method table size                  */
 #define PTYPE_SLOT_EMPTY 0xFFFFFFFFu
@@ -110,7 +110,7 @@ typedef struct ptype_image_header { /* 192 bytes */
     uint32_t magic, version;
     uint64_t epoch;          /* snapshot generation, chosen by the publisher          */
     uint64_t total_bytes;    /* whole blob                                             */
-    uint64_t body_checksum;  /* FNV-1a-64 of blob[192 .. total_bytes)                  */
+    uint64_t body_checksum;  /* 4-lane word-wise FNV of blob[192 .. total_bytes)        */
     uint64_t key_salt;       /* xor-ed into the FNV-1a-64 offset basis (0 = plain FNV) */
     uint32_t n_services;     /* occupied slots                                         */
     uint32_t n_slots;        /* cuckoo table size (any value >= 1, no power of two)    */

@@ -581,8 +581,8 @@ int ptype_b200_current_image(ptype_ctx* ctx, void* out, size_t* bytes) {
     if (ctx->host_image.empty()) return PTYPE_E_NO_IMAGE;
     if (ctx->host_checksum_stale) {
         ptype_image_header* hh = reinterpret_cast<ptype_image_header*>(ctx->host_image.data());
-        hh->body_checksum = ptype::fnv1a64(ctx->host_image.data() + sizeof(ptype_image_header),
-                                           ctx->host_image.size() - sizeof(ptype_image_header), 0);
+        hh->body_checksum = ptype::image_body_hash(ctx->host_image.data() + sizeof(ptype_image_header),
+                                                   ctx->host_image.size() - sizeof(ptype_image_header));
         ctx->host_checksum_stale = false;
     }
     const size_t need = ctx->host_image.size();

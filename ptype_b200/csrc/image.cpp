@@ -32,6 +32,7 @@ struct NodeRec {
 struct ServiceRec {
     std::map<std::string, NodeRec> nodes;  // by node name
     uint32_t recv_mask = 0;
+    uint32_t order_index = 0;  // position in Placement::order while the placement is valid
 };
 
 struct KnownMethod {
@@ -64,13 +65,143 @@ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 }  // namespace
 
+// What finish() derives from the SET of service names alone: key order, salt, table size and
+// the cuckoo placement.  A node joining or leaving an existing service (the common live update,
+// registry.go:119-150) changes none of it, so it is kept between finish() calls and dropped
+// whenever a service name is added or the table size is forced.
+struct Placement {
+    bool valid = false;
+    std::vector<const std::pair<const std::string, ServiceRec>*> order;  // etcd key order
+    std::vector<uint64_t> keys;
+    uint64_t salt = 0;
+    uint32_t n_slots = 0;
+    uint32_t table_seed = 0;
+    std::vector<uint32_t> slot_index;  // per service (in `order`), its slot in the table
+    std::vector<uint32_t> by_key;      // `order` indices sorted by key (host-side binary search)
+    // Dense copies of each service's node count and receiver mask, kept current by the
+    // mutators, so finish() walks two flat arrays instead of 10 000 scattered map nodes.
+    std::vector<uint32_t> n_nodes, recv_mask;
+    uint64_t total_nodes = 0;
+
+    void note(const ServiceRec& rec) {
+        if (!valid) return;
+        total_nodes += rec.nodes.size();
+        total_nodes -= n_nodes[rec.order_index];
+        n_nodes[rec.order_index] = static_cast<uint32_t>(rec.nodes.size());
+        recv_mask[rec.order_index] = rec.recv_mask;
+    }
+};
+
 struct ptype_builder {
     std::string local_addr;
     int max_connections = 0;
     uint32_t forced_slots = 0;
     bool device_only = false;
-    std::map<std::string, ServiceRec> services;
+    std::map<std::string, ServiceRec> services;  // node-stable: Placement points into it
+    Placement placement;
 };
+
+// Key order, salt, table size and cuckoo placement for the builder's current set of service names.
+static int compute_placement(ptype_builder* b) {
+    Placement& pl = b->placement;
+    pl.valid = false;
+    const size_t n_services = b->services.size();
+
+    // Key order of the etcd range: compare the full keys bytewise.  '/' (0x2f) sorts
+    // after '-' and '.', so "foo-x" precedes "foo" here although the names alone
+    // would sort the other way.
+    std::vector<std::pair<std::string, const std::pair<const std::string, ServiceRec>*>> order;
+    order.reserve(n_services);
+    for (const auto& kv : b->services) order.emplace_back("services/" + kv.first + "/", &kv);
+    std::sort(order.begin(), order.end(),
+              [](const auto& a, const auto& c) { return a.first < c.first; });
+    pl.order.resize(n_services);
+    pl.n_nodes.resize(n_services);
+    pl.recv_mask.resize(n_services);
+    pl.total_nodes = 0;
+    for (size_t i = 0; i < n_services; ++i) {
+        pl.order[i] = order[i].second;
+        ServiceRec& rec = b->services.find(order[i].second->first)->second;
+        rec.order_index = static_cast<uint32_t>(i);
+        pl.n_nodes[i] = static_cast<uint32_t>(rec.nodes.size());
+        pl.recv_mask[i] = rec.recv_mask;
+        pl.total_nodes += rec.nodes.size();
+    }
+
+    // Pick a salt under which all registered names have distinct 64-bit keys (H7).
+    pl.keys.assign(n_services, 0);
+    for (pl.salt = 0;; ++pl.salt) {
+        if (pl.salt == 64) return PTYPE_E_COLLISION;
+        for (size_t i = 0; i < n_services; ++i)
+            pl.keys[i] = ptype::fnv1a64(pl.order[i]->first.data(), pl.order[i]->first.size(), pl.salt);
+        std::vector<uint64_t> sorted(pl.keys);
+        std::sort(sorted.begin(), sorted.end());
+        if (std::adjacent_find(sorted.begin(), sorted.end()) == sorted.end()) break;
+    }
+
+    // Table size: half full when that fits the shared-memory budget, otherwise
+    // fill the budget (up to 80 % load: 3-way cuckoo places that reliably), otherwise
+    // a half-full table probed in L2.
+    if (b->forced_slots) {
+        // 3-way cuckoo hashing stops placing reliably a little above 90 % load
+        if (static_cast<uint64_t>(b->forced_slots) * 9 < static_cast<uint64_t>(n_services) * 10 ||
+            b->forced_slots <= n_services)
+            return PTYPE_E_INVAL;
+        pl.n_slots = b->forced_slots;
+    } else {
+        size_t want = std::max<size_t>(8, align_up(2 * n_services, 8));
+        if (want > kSmemSlotBudget && n_services * 5 <= static_cast<size_t>(kSmemSlotBudget) * 4)
+            want = kSmemSlotBudget;
+        pl.n_slots = static_cast<uint32_t>(want);
+    }
+
+    // Random-walk insertion; a walk that does not settle restarts the whole table under the
+    // next seed.  `table` holds service indices while placing.
+    constexpr uint32_t kFree = 0xFFFFFFFFu;
+    std::vector<uint32_t> table;
+    for (pl.table_seed = 0;; ++pl.table_seed) {
+        if (pl.table_seed == 32) return PTYPE_E_COLLISION;
+        table.assign(pl.n_slots, kFree);
+        uint64_t rng = 0x9E3779B97F4A7C15ull ^ pl.table_seed;
+        bool ok = true;
+        for (size_t i = 0; i < n_services && ok; ++i) {
+            uint32_t cur = static_cast<uint32_t>(i);
+            ok = false;
+            for (int kick = 0; kick < 2000; ++kick) {
+                const uint64_t key = pl.keys[cur];
+                const uint32_t lo = static_cast<uint32_t>(key), hi = static_cast<uint32_t>(key >> 32);
+                uint32_t cand[PTYPE_SLOT_WAYS];
+                bool placed = false;
+                for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
+                    cand[w] = ptype::slot_of(lo, hi, pl.table_seed, w, pl.n_slots);
+                    if (table[cand[w]] == kFree) {
+                        table[cand[w]] = cur;
+                        placed = true;
+                        break;
+                    }
+                }
+                if (placed) {
+                    ok = true;
+                    break;
+                }
+                rng = rng * 6364136223846793005ull + 1442695040888963407ull;
+                const uint32_t victim = cand[(rng >> 33) % PTYPE_SLOT_WAYS];
+                std::swap(cur, table[victim]);
+            }
+        }
+        if (ok) break;
+    }
+    pl.slot_index.assign(n_services, 0);
+    for (uint32_t s = 0; s < pl.n_slots; ++s)
+        if (table[s] != kFree) pl.slot_index[table[s]] = s;
+
+    pl.by_key.resize(n_services);
+    for (size_t i = 0; i < n_services; ++i) pl.by_key[i] = static_cast<uint32_t>(i);
+    std::sort(pl.by_key.begin(), pl.by_key.end(),
+              [&](uint32_t a, uint32_t c) { return pl.keys[a] < pl.keys[c]; });
+    pl.valid = true;
+    return PTYPE_OK;
+}
 
 extern "C" {
 
@@ -110,15 +241,22 @@ int ptype_b200_builder_new(const char* local_addr, int max_connections, ptype_bu
 int ptype_b200_builder_set_slots(ptype_builder* b, uint32_t n_slots) {
     if (!b) return PTYPE_E_INVAL;
     b->forced_slots = n_slots;
+    b->placement.valid = false;
     return PTYPE_OK;
 }
 
 int ptype_b200_builder_register(ptype_builder* b, const char* service, const char* node_name,
                                 const char* address, int port) {
     if (!b || !valid_name(service) || !valid_name(node_name) || !address) return PTYPE_E_INVAL;
-    NodeRec& n = b->services[service].nodes[node_name];  // Put on an existing key overwrites
+    auto it = b->services.find(service);
+    if (it == b->services.end()) {
+        it = b->services.emplace(service, ServiceRec()).first;
+        b->placement.valid = false;
+    }
+    NodeRec& n = it->second.nodes[node_name];  // Put on an existing key overwrites
     n.address = address;
     n.port = port;
+    b->placement.note(it->second);
     return PTYPE_OK;
 }
 
@@ -128,6 +266,7 @@ int ptype_b200_builder_unregister(ptype_builder* b, const char* service, const c
     if (!b || !valid_name(service) || !valid_name(node_name)) return PTYPE_E_INVAL;
     auto it = b->services.find(service);
     if (it == b->services.end() || it->second.nodes.erase(node_name) == 0) return PTYPE_E_NOT_FOUND;
+    b->placement.note(it->second);
     return PTYPE_OK;
 }
 
@@ -139,7 +278,10 @@ int ptype_b200_builder_set_device_only(ptype_builder* b, int on) {
 
 int ptype_b200_builder_declare(ptype_builder* b, const char* service) {
     if (!b || !valid_name(service)) return PTYPE_E_INVAL;
-    b->services[service];
+    if (b->services.find(service) == b->services.end()) {
+        b->services[service];
+        b->placement.valid = false;
+    }
     return PTYPE_OK;
 }
 
@@ -147,7 +289,10 @@ int ptype_b200_builder_expose(ptype_builder* b, const char* service, const char*
     if (!b || !valid_name(service) || !receiver) return PTYPE_E_INVAL;
     for (const KnownMethod& m : kKnownMethods) {
         if (!std::strcmp(m.recv, receiver)) {
-            b->services[service].recv_mask |= 1u << m.recv_bit;
+            if (b->services.find(service) == b->services.end()) b->placement.valid = false;
+            ServiceRec& rec = b->services[service];
+            rec.recv_mask |= 1u << m.recv_bit;
+            b->placement.note(rec);
             return PTYPE_OK;
         }
     }
@@ -160,51 +305,18 @@ void ptype_b200_image_free(void* image) { std::free(image); }
 int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, size_t* bytes) {
     if (!b || !image || !bytes) return PTYPE_E_INVAL;
     const size_t n_services = b->services.size();
-
-    // Key order of the etcd range: compare the full keys bytewise.  '/' (0x2f) sorts
-    // after '-' and '.', so "foo-x" precedes "foo" here although the names alone
-    // would sort the other way.
-    std::vector<std::pair<std::string, const std::string*>> order;
-    order.reserve(n_services);
-    for (const auto& kv : b->services) order.emplace_back("services/" + kv.first + "/", &kv.first);
-    std::sort(order.begin(), order.end(),
-              [](const auto& a, const auto& c) { return a.first < c.first; });
-
-    size_t n_nodes = 0;
-    for (const auto& kv : b->services) {
-        if (kv.second.nodes.size() > 0xFFFFFFu) return PTYPE_E_LIMIT;
-        n_nodes += kv.second.nodes.size();
+    if (n_services >= 0x7FFFFFFFu) return PTYPE_E_LIMIT;
+    if (!b->placement.valid) {
+        const int rc = compute_placement(b);
+        if (rc != PTYPE_OK) return rc;
     }
-    if (n_nodes >= PTYPE_NO_NODE || n_services >= 0x7FFFFFFFu) return PTYPE_E_LIMIT;
-
-    // Pick a salt under which all registered names have distinct 64-bit keys (H7).
-    uint64_t salt = 0;
-    std::vector<uint64_t> keys(n_services);
-    for (;; ++salt) {
-        if (salt == 64) return PTYPE_E_COLLISION;
-        for (size_t i = 0; i < n_services; ++i)
-            keys[i] = ptype::fnv1a64(order[i].second->data(), order[i].second->size(), salt);
-        std::vector<uint64_t> sorted(keys);
-        std::sort(sorted.begin(), sorted.end());
-        if (std::adjacent_find(sorted.begin(), sorted.end()) == sorted.end()) break;
-    }
-
-    // Table size: half full when that fits the shared-memory budget, otherwise
-    // fill the budget (up to 80 % load: 3-way cuckoo places that reliably), otherwise
-    // a half-full table probed in L2.
-    uint32_t n_slots;
-    if (b->forced_slots) {
-        // 3-way cuckoo hashing stops placing reliably a little above 90 % load
-        if (static_cast<uint64_t>(b->forced_slots) * 9 < static_cast<uint64_t>(n_services) * 10 ||
-            b->forced_slots <= n_services)
-            return PTYPE_E_INVAL;
-        n_slots = b->forced_slots;
-    } else {
-        size_t want = std::max<size_t>(8, align_up(2 * n_services, 8));
-        if (want > kSmemSlotBudget && n_services * 5 <= static_cast<size_t>(kSmemSlotBudget) * 4)
-            want = kSmemSlotBudget;
-        n_slots = static_cast<uint32_t>(want);
-    }
+    const Placement& pl = b->placement;
+    const size_t n_nodes = pl.total_nodes;
+    if (n_nodes >= PTYPE_NO_NODE) return PTYPE_E_LIMIT;
+    for (size_t i = 0; i < n_services; ++i)
+        if (pl.n_nodes[i] > 0xFFFFFFu) return PTYPE_E_LIMIT;
+    const uint64_t salt = pl.salt;
+    const uint32_t n_slots = pl.n_slots, table_seed = pl.table_seed;
 
     const uint32_t n_conn = static_cast<uint32_t>(b->max_connections);
     const uint32_t n_methods = sizeof(kKnownMethods) / sizeof(kKnownMethods[0]);
@@ -237,21 +349,22 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     const size_t off_strings = off;
 
     std::vector<ptype_service> services(n_services);
-    std::vector<ptype_node> nodes(n_nodes);
+    std::vector<ptype_node> nodes(host_sections ? n_nodes : 0);
     uint32_t next_node = 0;
     for (size_t i = 0; i < n_services; ++i) {
-        const std::string& name = *order[i].second;
-        const ServiceRec& rec = b->services[name];
         ptype_service& s = services[i];
-        s.key = keys[i];
-        s.name_off = host_sections ? intern(name) : 0;
+        s.key = pl.keys[i];
+        s.name_off = 0;
         s.node_base = next_node;
-        s.n_nodes = static_cast<uint32_t>(rec.nodes.size());
-        s.recv_mask = rec.recv_mask;
+        s.n_nodes = pl.n_nodes[i];
+        s.recv_mask = pl.recv_mask[i];
         if (!host_sections) {
             next_node += s.n_nodes;
             continue;
         }
+        const std::string& name = pl.order[i]->first;
+        const ServiceRec& rec = pl.order[i]->second;
+        s.name_off = intern(name);
         // Order inside the service = byte order of the keys services/<svc>/<node>/, i.e. of the
         // node names WITH their trailing '/': "node10" before "node2", and "a-b" before "a"
         // because '-' sorts below '/'.
@@ -274,51 +387,15 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     unsigned char* blob = static_cast<unsigned char*>(std::calloc(1, total));
     if (!blob) return PTYPE_E_NOMEM;
 
-    // 3-way cuckoo placement: every key ends up in one of its three candidate slots, so a
-    // device lookup is three independent probes at most.  Random-walk insertion; a walk that
-    // does not settle restarts the whole table under the next seed.
+    // Every key sits in one of its three candidate slots (compute_placement), so a device
+    // lookup is three independent probes at most.
     ptype_slot* slots = reinterpret_cast<ptype_slot*>(blob + off_slots);
-    uint32_t table_seed = 0;
-    for (;; ++table_seed) {
-        if (table_seed == 32) {
-            std::free(blob);
-            return PTYPE_E_COLLISION;
-        }
-        for (uint32_t i = 0; i < n_slots; ++i) {
-            slots[i].key = 0;
-            slots[i].node_base = PTYPE_SLOT_EMPTY;
-            slots[i].n_and_recv = 0;
-        }
-        uint64_t rng = 0x9E3779B97F4A7C15ull ^ table_seed;
-        bool ok = true;
-        for (size_t i = 0; i < n_services && ok; ++i) {
-            ptype_slot cur;
-            cur.key = services[i].key;
-            cur.node_base = services[i].node_base;
-            cur.n_and_recv = services[i].n_nodes | (services[i].recv_mask << 24);
-            ok = false;
-            for (int kick = 0; kick < 2000; ++kick) {
-                const uint32_t lo = static_cast<uint32_t>(cur.key), hi = static_cast<uint32_t>(cur.key >> 32);
-                uint32_t cand[PTYPE_SLOT_WAYS];
-                bool placed = false;
-                for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
-                    cand[w] = ptype::slot_of(lo, hi, table_seed, w, n_slots);
-                    if (slots[cand[w]].node_base == PTYPE_SLOT_EMPTY) {
-                        slots[cand[w]] = cur;
-                        placed = true;
-                        break;
-                    }
-                }
-                if (placed) {
-                    ok = true;
-                    break;
-                }
-                rng = rng * 6364136223846793005ull + 1442695040888963407ull;
-                const uint32_t victim = cand[(rng >> 33) % PTYPE_SLOT_WAYS];
-                std::swap(cur, slots[victim]);
-            }
-        }
-        if (ok) break;
+    for (uint32_t i = 0; i < n_slots; ++i) slots[i].node_base = PTYPE_SLOT_EMPTY;
+    for (size_t i = 0; i < n_services; ++i) {
+        ptype_slot& e = slots[pl.slot_index[i]];
+        e.key = services[i].key;
+        e.node_base = services[i].node_base;
+        e.n_and_recv = services[i].n_nodes | (services[i].recv_mask << 24);
     }
     uint32_t* conn = reinterpret_cast<uint32_t*>(blob + off_conn);
     for (uint32_t i = 0; i < n_conn; ++i)
@@ -351,13 +428,10 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
         if (ok) break;
     }
     // Host-side service records sorted by key for binary search.
-    std::vector<uint32_t> perm(n_services);
-    for (size_t i = 0; i < n_services; ++i) perm[i] = static_cast<uint32_t>(i);
-    std::sort(perm.begin(), perm.end(),
-              [&](uint32_t a, uint32_t c) { return services[a].key < services[c].key; });
-    std::vector<uint32_t> inv(n_services);
-    for (size_t i = 0; i < n_services; ++i) inv[perm[i]] = static_cast<uint32_t>(i);
     if (host_sections) {
+        const std::vector<uint32_t>& perm = pl.by_key;
+        std::vector<uint32_t> inv(n_services);
+        for (size_t i = 0; i < n_services; ++i) inv[perm[i]] = static_cast<uint32_t>(i);
         ptype_service* out_services = reinterpret_cast<ptype_service*>(blob + off_services);
         for (size_t i = 0; i < n_services; ++i) out_services[i] = services[perm[i]];
         ptype_node* out_nodes = reinterpret_cast<ptype_node*>(blob + off_nodes);
@@ -394,8 +468,8 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     h->method_mul = method_mul;
     h->off_mtable = static_cast<uint32_t>(off_mtable);
     std::snprintf(h->local_addr, sizeof h->local_addr, "%s", b->local_addr.c_str());
-    h->body_checksum = ptype::fnv1a64(blob + sizeof(ptype_image_header),
-                                      total - sizeof(ptype_image_header), 0);
+    h->body_checksum = ptype::image_body_hash(blob + sizeof(ptype_image_header),
+                                              total - sizeof(ptype_image_header));
     *image = blob;
     *bytes = total;
     return PTYPE_OK;
@@ -405,7 +479,7 @@ int ptype_b200_image_validate(const void* image, size_t bytes) {
     if (!image || bytes < sizeof(ptype_image_header)) return PTYPE_E_BAD_IMAGE;
     const ptype_image_header* h = static_cast<const ptype_image_header*>(image);
     if (h->magic != PTYPE_IMAGE_MAGIC || h->version != PTYPE_IMAGE_VERSION) return PTYPE_E_BAD_IMAGE;
-    if (h->total_bytes != bytes || h->n_slots == 0 || h->n_services >= h->n_slots)
+    if (h->total_bytes != bytes || (bytes & 7u) || h->n_slots == 0 || h->n_services >= h->n_slots)
         return PTYPE_E_BAD_IMAGE;
     if (h->n_methods > PTYPE_MAX_METHODS || h->n_conn_hash != h->max_connections)
         return PTYPE_E_BAD_IMAGE;
@@ -423,7 +497,7 @@ int ptype_b200_image_validate(const void* image, size_t bytes) {
         return PTYPE_E_BAD_IMAGE;
     if (h->local_addr[PTYPE_LOCAL_ADDR_MAX - 1] != 0) return PTYPE_E_BAD_IMAGE;
     const unsigned char* p = static_cast<const unsigned char*>(image);
-    if (ptype::fnv1a64(p + sizeof(*h), bytes - sizeof(*h), 0) != h->body_checksum)
+    if (ptype::image_body_hash(p + sizeof(*h), bytes - sizeof(*h)) != h->body_checksum)
         return PTYPE_E_BAD_IMAGE;
     return PTYPE_OK;
 }

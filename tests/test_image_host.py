@@ -278,3 +278,53 @@ def test_random_registries_match_oracle(oracle):
         for nid in range(len(nodes)):
             a, port, svc, _ = img.node(nid)
             assert (a, port, svc) == snap.node(nid), (trial, nid)
+
+
+@pytest.mark.parametrize("device_only", [False, True])
+def test_builder_kept_alive_emits_the_same_bytes_as_a_fresh_one(device_only):
+    """A builder that lives across live updates keeps its key order and table placement while the
+    set of service names stands still (only nodes join and leave); every image it emits must be
+    byte-identical to one built from scratch from the same registrations."""
+    rng = np.random.default_rng(0xB111D)
+    state = {}       # (service, node) -> (address, port)
+    exposed = set()  # (service, receiver)
+    declared = set()
+    live = p.ImageBuilder("10.0.0.5", 3).set_device_only(device_only)
+
+    def fresh(epoch):
+        b = p.ImageBuilder("10.0.0.5", 3).set_device_only(device_only)
+        for (svc, node), (addr, port) in state.items():
+            b.register(svc, node, addr, port)
+        for svc in declared:
+            b.declare(svc)
+        for svc, recv in exposed:
+            b.expose(svc, recv)
+        return b.finish(epoch)
+
+    for step in range(120):
+        kind = rng.integers(0, 10)
+        svc = f"svc_{int(rng.integers(0, 40 if step > 30 else 12)):03d}"
+        node = f"node_{int(rng.integers(0, 6)):02d}"
+        if kind < 5:
+            addr, port = f"10.1.{step}.{int(rng.integers(1, 250))}", int(rng.integers(1000, 60000))
+            live.register(svc, node, addr, port)
+            state[(svc, node)] = (addr, port)
+            declared.add(svc)
+        elif kind < 8:
+            if (svc, node) in state:
+                live.unregister(svc, node)
+                del state[(svc, node)]
+            elif svc not in declared:
+                with pytest.raises(p.PtypeError):
+                    live.unregister(svc, node)
+        elif kind == 8:
+            live.declare(svc)
+            declared.add(svc)
+        else:
+            recv = "Calculator" if rng.integers(0, 2) else "Prime"
+            live.expose(svc, recv)
+            exposed.add((svc, recv))
+            declared.add(svc)
+        if step % 3 == 0:
+            assert live.finish(step + 1).blob == fresh(step + 1).blob, step
+    assert live.finish(999).blob == fresh(999).blob
