@@ -141,6 +141,10 @@ struct DeviceState {
     unsigned long long* d_size = nullptr;  // broadcast header scratch
     ptype_failed* d_failed2 = nullptr;     // (index, status) list of call_batch_values
     size_t failed2_cap = 0;
+    unsigned long long* d_tally = nullptr;  // {failed calls, finished CTAs} of a single-launch values batch;
+                                            // the kernel leaves both at zero
+    unsigned long long* h_tally = nullptr;  // page-locked word the kernel's last CTA writes the count to
+    unsigned long long* h_tally_dev = nullptr;
     void* d_codec = nullptr;               // scratch of the gob encoder (lengths, block sums)
     size_t codec_cap = 0;
     cudaEvent_t drained[1 + kPipe] = {};   // "everything enqueued so far" markers, one per dispatch stream
@@ -258,6 +262,20 @@ int adopt_image(ptype_ctx* ctx, DeviceState* d, int buf, const ptype_image_heade
 // Device alias of a page-locked host pointer (UVA maps every cudaHostAlloc / registered
 // range), or nullptr for pageable memory.  Lets a kernel stream requests and replies over
 // PCIe itself instead of going through chunked copy-engine transfers.
+// Grid of a kernel that streams its batch over PCIe: the link, not the SMs, sets the pace, and
+// one CTA per SM keeps it fullest (measured: 402 us per 2^20-call batch against 417 us with the
+// plan's four, tools/e2e_probe.py).  PTYPE_B200_ZC_CTAS overrides (0 = the plan's grid).
+int zero_copy_grid(const ptype::LaunchPlan& plan, size_t n, int sm_count) {
+    static const int ctas = [] {
+        const char* e = std::getenv("PTYPE_B200_ZC_CTAS");
+        return e ? std::atoi(e) : 1;
+    }();
+    const int full = ptype::grid_for(plan, n, sm_count);
+    if (ctas <= 0 || ctas >= plan.ctas_per_sm) return full;
+    const int want = sm_count * ctas;
+    return want < full ? want : full;
+}
+
 void* pinned_alias(const void* host) {
     if (!host) return nullptr;
     cudaPointerAttributes a;
@@ -351,6 +369,8 @@ void ptype_b200_close(ptype_ctx* ctx) {
         if (d->d_size) cudaFree(d->d_size);
         if (d->d_codec) cudaFree(d->d_codec);
         if (d->d_failed2) cudaFree(d->d_failed2);
+        if (d->d_tally) cudaFree(d->d_tally);
+        if (d->h_tally) cudaFreeHost(d->h_tally);
         for (int i = 0; i <= kPipe; ++i)
             if (d->drained[i]) cudaEventDestroy(d->drained[i]);
         if (d->image_ready) cudaEventDestroy(d->image_ready);
@@ -721,7 +741,7 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
         const ptype_req* q = static_cast<const ptype_req*>(pinned_alias(reqs));
         ptype_reply* r = static_cast<ptype_reply*>(pinned_alias(replies));
         if (q && r) {
-            CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, n, d->sm_count), q, n, r, nullptr,
+            CU(ptype::launch_dispatch(img, plan, zero_copy_grid(plan, n, d->sm_count), q, n, r, nullptr,
                                       0u, 0u, nullptr, d->stream));
             ctx->launches.fetch_add(1);
             if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
@@ -868,9 +888,25 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
         r[i] = methods[i].recv;
     }
     ptype::CallBatchOut out;
+    // Where the batch goes out as ONE launch (device pointers, or page-locked host buffers the
+    // kernel streams itself) the kernel reports the failure count through h_tally; the chunked
+    // pipeline below launches several kernels at once and keeps the memset / copy-back protocol.
+    bool single_launch = (flags & PTYPE_F_DEVICE_PTRS) != 0;
+    const int64_t* za = nullptr;
+    ptype_reply* zr = nullptr;
+    int64_t* zv = nullptr;
+    const uint8_t* zs = nullptr;
+    bool zero_copy = false;
+    if (!single_launch && zero_copy_enabled() && n) {
+        za = static_cast<const int64_t*>(pinned_alias(args));
+        zr = replies ? static_cast<ptype_reply*>(pinned_alias(replies)) : nullptr;
+        zv = values ? static_cast<int64_t*>(pinned_alias(values)) : nullptr;
+        zs = method_sel ? static_cast<const uint8_t*>(pinned_alias(method_sel)) : nullptr;
+        zero_copy = za && (values_mode ? zv != nullptr : zr != nullptr) && (!method_sel || zs);
+        single_launch = zero_copy;
+    }
     if (values_mode) {
         // the failed list and its counter live in device memory; copied out at the end
-        if (!d->d_stats) CU(cudaMalloc(&d->d_stats, ptype::kStatWords * sizeof(unsigned long long)));
         if (failed_cap > d->failed2_cap) {
             CU(cudaStreamSynchronize(d->stream));
             if (d->d_failed2) CU(cudaFree(d->d_failed2));
@@ -879,16 +915,36 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
             CU(cudaMalloc(&d->d_failed2, failed_cap * sizeof(ptype_failed)));
             d->failed2_cap = failed_cap;
         }
-        CU(cudaMemsetAsync(d->d_stats, 0, sizeof(unsigned long long), d->stream));
-        CU(cudaStreamSynchronize(d->stream));
         out.failed = d->d_failed2;
         out.failed_cap = static_cast<uint32_t>(failed_cap);
-        out.failed_count = d->d_stats;
+        if (single_launch) {
+            if (!d->d_tally) {
+                CU(cudaMalloc(&d->d_tally, 2 * sizeof(unsigned long long)));
+                CU(cudaMemset(d->d_tally, 0, 2 * sizeof(unsigned long long)));
+            }
+            if (!d->h_tally) {
+                CU(cudaHostAlloc(reinterpret_cast<void**>(&d->h_tally), sizeof(unsigned long long),
+                                 cudaHostAllocMapped | cudaHostAllocPortable));
+                CU(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d->h_tally_dev), d->h_tally, 0));
+            }
+            *d->h_tally = 0;
+            out.failed_count = d->d_tally;
+            out.done_ctas = d->d_tally + 1;
+            out.host_count = d->h_tally_dev;
+        } else {
+            if (!d->d_stats) CU(cudaMalloc(&d->d_stats, ptype::kStatWords * sizeof(unsigned long long)));
+            CU(cudaMemsetAsync(d->d_stats, 0, sizeof(unsigned long long), d->stream));
+            CU(cudaStreamSynchronize(d->stream));
+            out.failed_count = d->d_stats;
+        }
     }
     auto finish_values = [&]() -> int {
         if (!values_mode) return PTYPE_OK;
         unsigned long long count = 0;
-        CU(cudaMemcpy(&count, d->d_stats, sizeof count, cudaMemcpyDeviceToHost));
+        if (single_launch)
+            count = n ? *static_cast<volatile unsigned long long*>(d->h_tally) : 0;
+        else
+            CU(cudaMemcpy(&count, d->d_stats, sizeof count, cudaMemcpyDeviceToHost));
         if (failed_count) *failed_count = count;
         const size_t take = count < failed_cap ? static_cast<size_t>(count) : failed_cap;
         if (take) CU(cudaMemcpy(failed, d->d_failed2, take * sizeof(ptype_failed), cudaMemcpyDeviceToHost));
@@ -906,19 +962,13 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
         if (values_mode || !(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
         return finish_values();
     }
-    if (zero_copy_enabled() && n) {
-        const int64_t* za = static_cast<const int64_t*>(pinned_alias(args));
-        ptype_reply* zr = replies ? static_cast<ptype_reply*>(pinned_alias(replies)) : nullptr;
-        int64_t* zv = values ? static_cast<int64_t*>(pinned_alias(values)) : nullptr;
-        const uint8_t* zs = method_sel ? static_cast<const uint8_t*>(pinned_alias(method_sel)) : nullptr;
-        if (za && (values_mode ? zv != nullptr : zr != nullptr) && (!method_sel || zs)) {
-            out.values = zv;
-            CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, n, d->sm_count), svc_key, seq_base,
-                                        m, r, n_methods, za, args_per_call, zs, n, zr, out, d->stream));
-            ctx->launches.fetch_add(1);
-            if (values_mode || !(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
-            return finish_values();
-        }
+    if (zero_copy) {
+        out.values = zv;
+        CU(ptype::launch_call_batch(img, plan, zero_copy_grid(plan, n, d->sm_count), svc_key, seq_base,
+                                    m, r, n_methods, za, args_per_call, zs, n, zr, out, d->stream));
+        ctx->launches.fetch_add(1);
+        if (values_mode || !(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+        return finish_values();
     }
     // Pageable host buffers: the staging slot of each pipeline stream holds a chunk's arguments
     // (<= 24 B/call) and, behind them, its method selectors (1 B/call); the reply slot holds

@@ -57,6 +57,11 @@ struct CallBatchOut {
     uint32_t failed_cap = 0;
     uint32_t index_base = 0;
     unsigned long long* failed_count = nullptr;
+    // Single-launch batches only: the last CTA to finish copies the failure count to
+    // *host_count (mapped page-locked memory) and zeroes failed_count and done_ctas again, so
+    // the caller needs no memset before the launch and no copy after it.
+    unsigned long long* done_ctas = nullptr;
+    unsigned long long* host_count = nullptr;
 };
 cudaError_t launch_call_batch(const DeviceImage& img, const LaunchPlan& plan, int blocks,
                               uint64_t svc_key, uint64_t seq_base, const uint32_t* methods,

@@ -772,7 +772,8 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     call_batch_kernel(const DeviceImage img, const ClientBatch batch, const int64_t* __restrict__ args,
                       const uint8_t* __restrict__ method_sel, const size_t n, uint4* __restrict__ replies,
                       unsigned long long* __restrict__ values, uint2* __restrict__ failed,
-                      const uint32_t failed_cap, unsigned long long* __restrict__ failed_count) {
+                      const uint32_t failed_cap, unsigned long long* __restrict__ failed_count,
+                      unsigned long long* __restrict__ done_ctas, unsigned long long* __restrict__ host_count) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ __align__(16) CtaShared sh;
     const uint32_t lane = threadIdx.x & 31u;
@@ -787,67 +788,108 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     bool table_ready = !kSmemTable;
     const uint32_t key_lo = static_cast<uint32_t>(batch.svc_key), key_hi = static_cast<uint32_t>(batch.svc_key >> 32);
 
-    for (size_t t0 = warp_global; t0 < n_tiles; t0 += total_warps * kUnroll) {
-        uint4 a01[kUnroll];
-        uint2 a2[kUnroll];
-        uint32_t sel[kUnroll];
+    // A warp takes groups of kGroupTiles consecutive tiles (128 calls), kUnroll tiles at a time.
+    // The group's method bytes are one 128-byte line: each lane loads four of them with one
+    // 32-bit load and the byte of call (tile u, lane l) is fetched from lane u*8 + l/4 by
+    // shuffle - one memory request per 128 calls instead of one 32-byte request per tile,
+    // which matters when the batch is streamed from host memory over PCIe.
+    constexpr int kGroupTiles = 4;
+    static_assert(kGroupTiles % kUnroll == 0, "a group is a whole number of unrolled rounds");
+    const size_t n_groups = (n_tiles + kGroupTiles - 1) / kGroupTiles;
+    const bool sel_words = kHasSel && (reinterpret_cast<uintptr_t>(method_sel) & 3u) == 0;
+    for (size_t g = warp_global; g < n_groups; g += total_warps) {
+        const size_t group_base = g * (kGroupTiles * 32);
+        uint32_t sel_word = 0;
+        if (kHasSel) {
+            const size_t j = group_base + lane * 4;
+            if (sel_words && j + 4 <= n) {
+                sel_word = __ldg(reinterpret_cast<const uint32_t*>(method_sel + j));
+            } else {
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-            const size_t idx = ((t0 + static_cast<size_t>(u) * total_warps) << 5) + lane;
-            a01[u] = make_uint4(0, 0, 0, 0);
-            a2[u] = make_uint2(0, 0);
-            sel[u] = 0;
-            if (idx < n) {
-                if (kArgs == 2) {
-                    a01[u] = ld_stream(reinterpret_cast<const uint4*>(args) + idx);
-                } else {
-                    const uint2* p = reinterpret_cast<const uint2*>(args) + idx * 3;
-                    const uint2 x = __ldg(p), y = __ldg(p + 1);
-                    a01[u] = make_uint4(x.x, x.y, y.x, y.y);
-                    a2[u] = __ldg(p + 2);
-                }
-                if (kHasSel) sel[u] = __ldg(method_sel + idx);
+                for (int k = 0; k < 4; ++k)
+                    if (j + k < n) sel_word |= static_cast<uint32_t>(__ldg(method_sel + j + k)) << (8 * k);
             }
         }
-        if (!table_ready) {
-            mbar_wait(&sh.table_bar, 0);
-            table_ready = true;
-        }
+#pragma unroll 1
+        for (int round = 0; round < kGroupTiles; round += kUnroll) {
+            if (group_base + static_cast<size_t>(round) * 32 >= n) break;
+            uint4 a01[kUnroll];
+            uint2 a2[kUnroll];
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-            const size_t idx = ((t0 + static_cast<size_t>(u) * total_warps) << 5) + lane;
-            if (idx >= n) continue;
-            const uint64_t seq = batch.seq_base + 1 + idx;
-            const uint32_t which = kHasSel ? (sel[u] < PTYPE_BATCH_METHODS ? sel[u] : 0u) : 0u;
-            uint32_t m = batch.method[0], rv = batch.recv[0];
-            if (kHasSel) {
-#pragma unroll
-                for (int k = 1; k < PTYPE_BATCH_METHODS; ++k) {
-                    if (which == static_cast<uint32_t>(k)) {
-                        m = batch.method[k];
-                        rv = batch.recv[k];
+            for (int u = 0; u < kUnroll; ++u) {
+                const size_t idx = group_base + static_cast<size_t>(round + u) * 32 + lane;
+                a01[u] = make_uint4(0, 0, 0, 0);
+                a2[u] = make_uint2(0, 0);
+                if (idx < n) {
+                    if (kArgs == 2) {
+                        a01[u] = ld_stream(reinterpret_cast<const uint4*>(args) + idx);
+                    } else {
+                        const uint2* p = reinterpret_cast<const uint2*>(args) + idx * 3;
+                        const uint2 x = __ldg(p), y = __ldg(p + 1);
+                        a01[u] = make_uint4(x.x, x.y, y.x, y.y);
+                        a2[u] = __ldg(p + 2);
                     }
                 }
             }
-            const uint4 q0 = make_uint4(key_lo, key_hi, static_cast<uint32_t>(seq), static_cast<uint32_t>(seq >> 32));
-            const uint4 q1 = make_uint4(m, rv, a01[u].x, a01[u].y);
-            const uint4 q2 = make_uint4(a01[u].z, a01[u].w, a2[u].x, a2[u].y);
-            const uint4 out = dispatch_one<kSmemTable>(img, sh, slots, cache, q0, q1, q2);
-            if (values == nullptr) {
-                st_stream(replies + idx, out);
-            } else {
-                // values-only replies (what CallBatch's caller reads): 8 bytes per call, plus an
-                // (index, status) entry for the rare call that failed
-                values[idx] = static_cast<unsigned long long>(out.x) | (static_cast<unsigned long long>(out.y) << 32);
-                if (out.w != PTYPE_ST_OK) {
-                    const unsigned long long slot = atomicAdd(failed_count, 1ull);
-                    if (slot < failed_cap) failed[slot] = make_uint2(static_cast<uint32_t>(idx) + batch.index_base, out.w);
+            if (!table_ready) {
+                mbar_wait(&sh.table_bar, 0);
+                table_ready = true;
+            }
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u) {
+                const size_t idx = group_base + static_cast<size_t>(round + u) * 32 + lane;
+                uint32_t which = 0;
+                if (kHasSel) {
+                    const uint32_t w = __shfl_sync(kFull, sel_word, (round + u) * 8 + (lane >> 2));
+                    which = (w >> ((lane & 3u) * 8)) & 0xFFu;
+                    if (which >= PTYPE_BATCH_METHODS) which = 0;
+                }
+                if (idx >= n) continue;
+                const uint64_t seq = batch.seq_base + 1 + idx;
+                uint32_t m = batch.method[0], rv = batch.recv[0];
+                if (kHasSel) {
+#pragma unroll
+                    for (int k = 1; k < PTYPE_BATCH_METHODS; ++k) {
+                        if (which == static_cast<uint32_t>(k)) {
+                            m = batch.method[k];
+                            rv = batch.recv[k];
+                        }
+                    }
+                }
+                const uint4 q0 = make_uint4(key_lo, key_hi, static_cast<uint32_t>(seq), static_cast<uint32_t>(seq >> 32));
+                const uint4 q1 = make_uint4(m, rv, a01[u].x, a01[u].y);
+                const uint4 q2 = make_uint4(a01[u].z, a01[u].w, a2[u].x, a2[u].y);
+                const uint4 out = dispatch_one<kSmemTable>(img, sh, slots, cache, q0, q1, q2);
+                if (values == nullptr) {
+                    st_stream(replies + idx, out);
+                } else {
+                    // values-only replies (what CallBatch's caller reads): 8 bytes per call, plus an
+                    // (index, status) entry for the rare call that failed
+                    values[idx] = static_cast<unsigned long long>(out.x) | (static_cast<unsigned long long>(out.y) << 32);
+                    if (out.w != PTYPE_ST_OK) {
+                        const unsigned long long slot = atomicAdd(failed_count, 1ull);
+                        if (slot < failed_cap) failed[slot] = make_uint2(static_cast<uint32_t>(idx) + batch.index_base, out.w);
+                    }
                 }
             }
         }
     }
     if (!table_ready) mbar_wait(&sh.table_bar, 0);
     griddep_wait();
+    if (host_count != nullptr) {
+        // The CTA that finishes last hands the failure count to the host and leaves both
+        // counters at zero for the next batch (batches of one context never overlap).
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(done_ctas, 1ull) == gridDim.x - 1) {
+                __threadfence();
+                *host_count = atomicExch(failed_count, 0ull);
+                *done_ctas = 0;
+                __threadfence_system();
+            }
+        }
+    }
 }
 
 // ---------------------------------------------------------- reply checksum
@@ -1113,11 +1155,12 @@ cudaError_t launch_call_batch_variant(const DeviceImage& img, const LaunchPlan& 
             if (e != cudaSuccess) return e;
         }
         return launch_kernel(kernel, blocks, plan.threads, plan.dyn_smem, stream, img, batch, args,
-                             method_sel, n, r, values, failed, o.failed_cap, o.failed_count);
+                             method_sel, n, r, values, failed, o.failed_cap, o.failed_count, o.done_ctas,
+                             o.host_count);
     }
     return launch_kernel(call_batch_kernel<kSmemTable, kArgs, kHasSel, 2, kSmallThreads, kSmallMinCtas>,
                          blocks, plan.threads, plan.dyn_smem, stream, img, batch, args, method_sel, n, r,
-                         values, failed, o.failed_cap, o.failed_count);
+                         values, failed, o.failed_cap, o.failed_count, o.done_ctas, o.host_count);
 }
 }  // namespace
 
