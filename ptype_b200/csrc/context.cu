@@ -123,6 +123,7 @@ struct Stage {
 struct DeviceState {
     int device = -1;
     int sm_count = 0;
+    int dispatch_sms = 0;  // SMs the dispatch grids are sized for (see ptype_b200_comm_init)
     cudaStream_t stream = nullptr;       // device-pointer dispatches, checksums
     cudaStream_t copy_stream = nullptr;  // image uploads / broadcast
     cudaStream_t pipe[kPipe] = {};
@@ -147,7 +148,12 @@ struct DeviceState {
     unsigned long long* h_tally_dev = nullptr;
     void* d_codec = nullptr;               // scratch of the gob encoder (lengths, block sums)
     size_t codec_cap = 0;
-    cudaEvent_t drained[1 + kPipe] = {};   // "everything enqueued so far" markers, one per dispatch stream
+    // retired[b][i]: recorded on dispatch stream i at the moment image buffer b stopped being the
+    // active one - every kernel that reads b was enqueued before it.  Refilling b waits for these
+    // only, not for the batches queued since (they read the other buffer), so an upload or
+    // broadcast overlaps the dispatches in flight.
+    cudaEvent_t retired[2][1 + kPipe] = {};
+    bool retired_set[2] = {false, false};
     cudaEvent_t image_ready = nullptr;     // the inactive buffer holds the new image
     void* h_stage[2] = {nullptr, nullptr}; // page-locked copies of the published blobs' device part
     size_t h_stage_cap[2] = {0, 0};
@@ -195,13 +201,25 @@ int sync_all_streams(DeviceState* d) {
 // overwritten the copy stream waits (on the device) for everything enqueued so far, since
 // launches made two flips ago may still read it; after the upload every dispatch stream
 // waits (on the device) for the copy before its next launch.  The host never blocks.
-int copy_stream_waits_for_dispatches(DeviceState* d) {
-    for (int i = 0; i <= kPipe; ++i) {
-        cudaStream_t s = i == 0 ? d->stream : d->pipe[i - 1];
-        if (!d->drained[i]) CU(cudaEventCreateWithFlags(&d->drained[i], cudaEventDisableTiming));
-        CU(cudaEventRecord(d->drained[i], s));
-        CU(cudaStreamWaitEvent(d->copy_stream, d->drained[i], 0));
+// Before the copy stream overwrites image buffer `buf`: wait for the kernels that may still read it.
+int copy_stream_waits_for_readers(DeviceState* d, int buf) {
+    if (!d->retired_set[buf]) return PTYPE_OK;  // never been active
+    for (int i = 0; i <= kPipe; ++i) CU(cudaStreamWaitEvent(d->copy_stream, d->retired[buf][i], 0));
+    return PTYPE_OK;
+}
+// The flip: dispatches enqueued from here on read buffer `buf`; the buffer they read until now
+// is marked retired on every dispatch stream.
+int make_active(DeviceState* d, int buf) {
+    const int old = d->active;
+    if (old >= 0 && old != buf) {
+        for (int i = 0; i <= kPipe; ++i) {
+            cudaStream_t s = i == 0 ? d->stream : d->pipe[i - 1];
+            if (!d->retired[old][i]) CU(cudaEventCreateWithFlags(&d->retired[old][i], cudaEventDisableTiming));
+            CU(cudaEventRecord(d->retired[old][i], s));
+        }
+        d->retired_set[old] = true;
     }
+    d->active = buf;
     return PTYPE_OK;
 }
 
@@ -255,8 +273,7 @@ int adopt_image(ptype_ctx* ctx, DeviceState* d, int buf, const ptype_image_heade
         for (int x = 0; x < 2; ++x)
             CU(ptype::plan_dispatch(v, kPlanFlags[g], x != 0, &d->plan[buf][g][x]));
     d->epoch[buf] = h.epoch;
-    d->active = buf;
-    return PTYPE_OK;
+    return make_active(d, buf);
 }
 
 // Device alias of a page-locked host pointer (UVA maps every cudaHostAlloc / registered
@@ -372,7 +389,8 @@ void ptype_b200_close(ptype_ctx* ctx) {
         if (d->d_tally) cudaFree(d->d_tally);
         if (d->h_tally) cudaFreeHost(d->h_tally);
         for (int i = 0; i <= kPipe; ++i)
-            if (d->drained[i]) cudaEventDestroy(d->drained[i]);
+            for (int b = 0; b < 2; ++b)
+                if (d->retired[b][i]) cudaEventDestroy(d->retired[b][i]);
         if (d->image_ready) cudaEventDestroy(d->image_ready);
         for (int b = 0; b < 2; ++b)
             if (d->h_stage[b]) cudaFreeHost(d->h_stage[b]);
@@ -405,7 +423,12 @@ int ptype_b200_open(const int* devices, int ndev, ptype_ctx** out) {
         if (e == cudaSuccess)
             e = cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, d->device);
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
-        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking);
+        // uploads and the snapshot broadcast go first wherever they compete with dispatch CTAs
+        int prio_least = 0, prio_greatest = 0;
+        if (e == cudaSuccess) e = cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
+        if (e == cudaSuccess)
+            e = cudaStreamCreateWithPriority(&d->copy_stream, cudaStreamNonBlocking, prio_greatest);
+        d->dispatch_sms = d->sm_count;
         for (int s = 0; s < kPipe && e == cudaSuccess; ++s)
             e = cudaStreamCreateWithFlags(&d->pipe[s], cudaStreamNonBlocking);
         if (e != cudaSuccess) {
@@ -502,7 +525,7 @@ int ptype_b200_publish_image(ptype_ctx* ctx, const void* image, size_t bytes) {
             CU(cudaStreamSynchronize(d->copy_stream));
         }
         std::memcpy(d->h_stage[buf], image, h.device_bytes);
-        rc = copy_stream_waits_for_dispatches(d);
+        rc = copy_stream_waits_for_readers(d, buf);
         if (rc != PTYPE_OK) return rc;
         CU(cudaMemcpyAsync(d->image_buf[buf], d->h_stage[buf], h.device_bytes, cudaMemcpyHostToDevice,
                            d->copy_stream));
@@ -545,7 +568,7 @@ int ptype_b200_update_service(ptype_ctx* ctx, const char* service, int delta) {
         int rc = reserve_inactive(d, buf, hh->device_bytes);
         if (rc != PTYPE_OK) return rc;
         if (!d->d_size) CU(cudaMalloc(&d->d_size, 16));
-        rc = copy_stream_waits_for_dispatches(d);
+        rc = copy_stream_waits_for_readers(d, buf);
         if (rc != PTYPE_OK) return rc;
         CU(cudaMemcpyAsync(d->image_buf[buf], d->image_buf[src], hh->device_bytes, cudaMemcpyDeviceToDevice,
                            d->copy_stream));
@@ -566,7 +589,8 @@ int ptype_b200_update_service(ptype_ctx* ctx, const char* service, int delta) {
         for (int g = 0; g < kPlanKinds; ++g)
             for (int x = 0; x < 2; ++x) d->plan[buf][g][x] = d->plan[src][g][x];
         d->epoch[buf] = d->epoch[src] + 1;
-        d->active = buf;
+        rc = make_active(d, buf);
+        if (rc != PTYPE_OK) return rc;
     }
     const uint32_t pivot = hs[at].node_base + n_old;
     for (uint32_t i = 0; i < hh->n_slots; ++i) {
@@ -638,6 +662,15 @@ int ptype_b200_comm_init(ptype_ctx* ctx, const void* id128, int rank, int nranks
     ctx->nccl_comm = comm;
     ctx->rank = rank;
     ctx->nranks = nranks;
+    // The dispatch kernels are persistent and fill every SM, so a collective's kernel enqueued
+    // beside them would not start until the running launch (up to 96 batches) has drained.  With a
+    // communicator attached the dispatch grids leave PTYPE_B200_COMM_SMS SMs (default 1) free,
+    // which is where ncclBroadcast runs while the batches in flight carry on.
+    const char* e = std::getenv("PTYPE_B200_COMM_SMS");
+    const int spare = e ? std::atoi(e) : 1;
+    DeviceState* d = ctx->devs[0];
+    std::lock_guard<std::mutex> lk(d->mu);
+    d->dispatch_sms = d->sm_count - spare > 0 ? d->sm_count - (spare > 0 ? spare : 0) : 1;
     return PTYPE_OK;
 }
 
@@ -654,8 +687,6 @@ int ptype_b200_broadcast_image(ptype_ctx* ctx, const void* image, size_t bytes, 
     std::lock_guard<std::mutex> lk2(ctx->image_mu);  // lock order: image_mu, then a device's mu
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(d->device));
-    int rc = copy_stream_waits_for_dispatches(d);
-    if (rc != PTYPE_OK) return rc;
     if (!d->d_size) CU(cudaMalloc(&d->d_size, 16));
     unsigned long long total = is_root ? bytes : 0;
     if (is_root)
@@ -667,7 +698,9 @@ int ptype_b200_broadcast_image(ptype_ctx* ctx, const void* image, size_t bytes, 
     CU(cudaStreamSynchronize(d->copy_stream));
     if (total < sizeof(ptype_image_header) || total > (1ull << 32)) return PTYPE_E_BAD_IMAGE;
     const int buf = d->active == 0 ? 1 : 0;
-    rc = reserve_inactive(d, buf, total);
+    int rc = reserve_inactive(d, buf, total);
+    if (rc != PTYPE_OK) return rc;
+    rc = copy_stream_waits_for_readers(d, buf);
     if (rc != PTYPE_OK) return rc;
     if (is_root)
         CU(cudaMemcpyAsync(d->image_buf[buf], image, total, cudaMemcpyHostToDevice, d->copy_stream));
@@ -726,7 +759,7 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
             CU(cudaMemsetAsync(d_stats, 0, sizeof(ptype_batch_stats), d->stream));
         }
         if (n) {
-            CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, n, d->sm_count), reqs, n,
+            CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, n, d->dispatch_sms), reqs, n,
                                       replies, failed_idx, static_cast<uint32_t>(failed_cap), 0u,
                                       d_stats, d->stream));
             ctx->launches.fetch_add(1);
@@ -741,7 +774,7 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
         const ptype_req* q = static_cast<const ptype_req*>(pinned_alias(reqs));
         ptype_reply* r = static_cast<ptype_reply*>(pinned_alias(replies));
         if (q && r) {
-            CU(ptype::launch_dispatch(img, plan, zero_copy_grid(plan, n, d->sm_count), q, n, r, nullptr,
+            CU(ptype::launch_dispatch(img, plan, zero_copy_grid(plan, n, d->dispatch_sms), q, n, r, nullptr,
                                       0u, 0u, nullptr, d->stream));
             ctx->launches.fetch_add(1);
             if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
@@ -769,7 +802,7 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
         }
         CU(cudaMemcpyAsync(st.d_reqs, reqs + done, cnt * sizeof(ptype_req), cudaMemcpyHostToDevice,
                            d->pipe[s]));
-        CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, cnt, d->sm_count), st.d_reqs, cnt,
+        CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, cnt, d->dispatch_sms), st.d_reqs, cnt,
                                   st.d_replies, failed_idx ? d->d_failed : nullptr,
                                   static_cast<uint32_t>(failed_cap), static_cast<uint32_t>(done),
                                   extras ? d->d_stats : nullptr, d->pipe[s]));
@@ -837,7 +870,7 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
             }
             if (e == b) return PTYPE_E_LIMIT;
             if (tiles) {
-                CU(ptype::launch_dispatch_multi(img, plan, d->sm_count, batches + b, static_cast<int>(e - b),
+                CU(ptype::launch_dispatch_multi(img, plan, d->dispatch_sms, batches + b, static_cast<int>(e - b),
                                                 d->stream));
                 ctx->launches.fetch_add(1);
             }
@@ -847,7 +880,7 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
         for (size_t b = 0; b < count; ++b) {
             const ptype_batch& bt = batches[b];
             if (bt.n == 0) continue;
-            CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, bt.n, d->sm_count), bt.reqs, bt.n,
+            CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, bt.n, d->dispatch_sms), bt.reqs, bt.n,
                                       bt.replies, nullptr, 0u, 0u, nullptr, d->stream));
             ctx->launches.fetch_add(1);
         }
@@ -954,7 +987,7 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
     if (flags & PTYPE_F_DEVICE_PTRS) {
         if (n) {
             out.values = values;
-            CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, n, d->sm_count), svc_key, seq_base,
+            CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, n, d->dispatch_sms), svc_key, seq_base,
                                         m, r, n_methods, args, args_per_call, method_sel, n, replies, out,
                                         d->stream));
             ctx->launches.fetch_add(1);
@@ -964,7 +997,7 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
     }
     if (zero_copy) {
         out.values = zv;
-        CU(ptype::launch_call_batch(img, plan, zero_copy_grid(plan, n, d->sm_count), svc_key, seq_base,
+        CU(ptype::launch_call_batch(img, plan, zero_copy_grid(plan, n, d->dispatch_sms), svc_key, seq_base,
                                     m, r, n_methods, za, args_per_call, zs, n, zr, out, d->stream));
         ctx->launches.fetch_add(1);
         if (values_mode || !(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
@@ -993,7 +1026,7 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
             CU(cudaMemcpyAsync(d_sel, method_sel + done, cnt, cudaMemcpyHostToDevice, d->pipe[s]));
         out.values = values_mode ? reinterpret_cast<int64_t*>(st.d_replies) : nullptr;
         out.index_base = static_cast<uint32_t>(done);
-        CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, cnt, d->sm_count), svc_key,
+        CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, cnt, d->dispatch_sms), svc_key,
                                     seq_base + done, m, r, n_methods, d_args, args_per_call, d_sel, cnt,
                                     st.d_replies, out, d->pipe[s]));
         ctx->launches.fetch_add(1);
