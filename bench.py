@@ -382,6 +382,10 @@ def main():
 
     for i in range(max(args.warmup, 3)):
         step(i)
+    if live:   # the update path warms up too (first-use costs of the rebuild and the collective)
+        live_update(2)
+        step(0)
+        update_ms.clear()
     barrier()
     launches0 = ctx.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -394,7 +398,7 @@ def main():
                                    for i in range(lo, min(lo + every, args.steps)))
             ctx.dispatch_batches(seg, flags=args.flags, sync=False)
             if lo + every < args.steps:
-                live_update(2 + lo // every)
+                live_update(3 + lo // every)
     else:
         ctx.dispatch_batches(timed, flags=args.flags, sync=False)
     host_enqueue_s = time.perf_counter() - w0
