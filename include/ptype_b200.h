@@ -432,6 +432,30 @@ int ptype_b200_gob_encode_replies(ptype_ctx*, int dev, const ptype_reply* replie
 int ptype_b200_gob_decode_args(ptype_ctx*, int dev, const uint8_t* bytes, const uint64_t* offsets, size_t n,
                                int64_t* args, int args_per_call, uint8_t* status);
 
+/* ---- the balancer's counters on the device ---------------------------------
+ * Every reference Client owns one counter, `seq` (cluster/rpc.go:129); roundRobinSelect takes its
+ * next value for each call that finds a non-empty client list - the length check at rpc.go:178-180
+ * comes before atomic.AddUint64 at rpc.go:181, so calls to a service without nodes, like calls to
+ * a service no Client exists for, consume nothing.  A context keeps those counters on the device,
+ * one per service of the installed image, all starting at 0 like a fresh Client's.
+ *
+ * assign_seq fills ptype_req.seq of n device-resident records exactly as n sequential
+ * Client.Call()s in batch order would have drawn them: record j gets
+ *   counter[service_j] + 1 + (number of earlier counted records of the same service),
+ * the counters move past the batch, and records that consume nothing get seq 0.  The host then
+ * need not carry seq at all (nor keep per-service counters for a batch that mixes services).
+ * Counters follow their services, matched by key, through publish_image / broadcast_image /
+ * update_service; a service missing from a new image loses its counter, and an image built under
+ * a different key salt (only after a 64-bit key collision among the registered names) starts all
+ * of them at 0 - seq_get/seq_set carry them over by name in that case.
+ * Device pointers only; PTYPE_F_ASYNC is honoured.  PTYPE_E_LIMIT: tables beyond 51 200 slots
+ * (the per-CTA histogram is one 32-bit count per slot in shared memory). */
+int ptype_b200_assign_seq(ptype_ctx*, int dev, ptype_req* d_reqs, size_t n, uint32_t flags);
+/* Read / set one service's counter (the value the next call will exceed by one).
+ * PTYPE_E_NOT_FOUND: the installed image has no such service. */
+int ptype_b200_seq_get(ptype_ctx*, int dev, const char* service, uint64_t* value);
+int ptype_b200_seq_set(ptype_ctx*, int dev, const char* service, uint64_t value);
+
 /* Kernel launches issued by this context so far (bench bookkeeping). */
 int ptype_b200_launch_count(ptype_ctx*, uint64_t* launches);
 

@@ -81,6 +81,9 @@ def lib() -> C.CDLL:
             "po_call": (None, [vp, C.c_char_p, C.c_uint64, C.c_char_p, C.POINTER(C.c_int64), C.c_uint64, vp]),
             "po_dispatch": (None, [vp, vp, C.c_size_t, vp, C.c_uint64]),
             "po_dispatch_mt": (None, [vp, vp, C.c_size_t, vp, C.c_uint64, C.c_int]),
+            "po_assign_seq": (None, [vp, vp, C.c_size_t, vp]),
+            "po_snapshot_n_clients": (C.c_size_t, [vp]),
+            "po_snapshot_client_index": (C.c_long, [vp, C.c_char_p]),
             "po_reply_checksum": (C.c_uint64, [vp, C.c_size_t, C.c_uint64]),
             "po_method_key": (None, [C.c_char_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
             "po_gob_uint": (C.c_int, [C.c_uint64, C.c_char_p]),
@@ -214,6 +217,18 @@ class Snapshot:
         else:
             lib().po_dispatch(self.h, reqs.ctypes.data, len(reqs), rep.ctypes.data, check_limit)
         return rep
+
+    def n_clients(self) -> int:
+        return lib().po_snapshot_n_clients(self.h)
+
+    def client_index(self, service: str) -> int:
+        return lib().po_snapshot_client_index(self.h, service.encode())
+
+    def assign_seq(self, reqs: np.ndarray, counters: np.ndarray) -> None:
+        """Fills reqs['seq'] in place and advances counters (uint64[n_clients()], key order)."""
+        assert reqs.dtype == REQ_DTYPE and reqs.flags.c_contiguous
+        assert counters.dtype == np.uint64 and len(counters) == self.n_clients()
+        lib().po_assign_seq(self.h, reqs.ctypes.data, len(reqs), counters.ctypes.data)
 
     def dispatch_into(self, reqs: np.ndarray, rep: np.ndarray, check_limit: int, threads: int) -> None:
         lib().po_dispatch_mt(self.h, reqs.ctypes.data, len(reqs), rep.ctypes.data, check_limit, threads)

@@ -973,6 +973,26 @@ void po_dispatch(const po_snapshot* s, const ptype_req* reqs, size_t n, ptype_re
     }
 }
 
+/* rpc.go:177-182 per record, in order:
+ *   clients := c.getClients(); if len(clients) == 0 { return nil }
+ *   index := atomic.AddUint64(&c.seq, uint64(1))                                  */
+void po_assign_seq(const po_snapshot* s, ptype_req* reqs, size_t n, uint64_t* counters) {
+    for (size_t j = 0; j < n; j++) {
+        const po_client* c = po_find_key(s, reqs[j].svc_key);
+        if (!c || c->k == 0) {
+            reqs[j].seq = 0;
+            continue;
+        }
+        reqs[j].seq = ++counters[c - s->clients];
+    }
+}
+size_t po_snapshot_n_clients(const po_snapshot* s) { return s->n_clients; }
+long po_snapshot_client_index(const po_snapshot* s, const char* service) {
+    for (size_t j = 0; j < s->n_clients; j++)
+        if (!strcmp(s->clients[j].name, service)) return (long)j;
+    return -1;
+}
+
 typedef struct {
     const po_snapshot* s;
     const ptype_req* reqs;

@@ -118,6 +118,15 @@ void po_dispatch(const po_snapshot*, const ptype_req* reqs, size_t n, ptype_repl
                  uint64_t check_limit);
 void po_dispatch_mt(const po_snapshot*, const ptype_req* reqs, size_t n, ptype_reply* replies,
                     uint64_t check_limit, int threads);
+/* The counters behind the seq field: n sequential Client.Call()s in batch order, each on the
+ * Client of its record's service (one Client, one counter: rpc.go:129).  A call that finds its
+ * Client's list non-empty takes the counter's next value (rpc.go:177-182: the length check comes
+ * first, so an empty list - like a service no Client exists for - consumes nothing; such records
+ * get seq 0).  counters[i] belongs to the i-th Client in key order (po_snapshot_client_index) and
+ * is advanced. */
+void po_assign_seq(const po_snapshot*, ptype_req* reqs, size_t n, uint64_t* counters);
+size_t po_snapshot_n_clients(const po_snapshot*);
+long po_snapshot_client_index(const po_snapshot*, const char* service); /* -1: no such Client */
 uint64_t po_reply_checksum(const ptype_reply* replies, size_t n, uint64_t index_base);
 void po_method_key(const char* service_method, uint32_t* method, uint32_t* recv);
 

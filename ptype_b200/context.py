@@ -96,6 +96,19 @@ class Context:
         """A node joined (+1) or left (-1) `service`: patch the installed snapshot on the device."""
         check(lib.ptype_b200_update_service(self._h, service.encode(), delta), "update_service")
 
+    # ---- the balancer's counters on the device (rpc.go:129,172-183) --------
+    def assign_seq(self, reqs, n: int, *, dev: int = 0, sync: bool = True) -> None:
+        """Fill the seq field of n device-resident records as n sequential Client.Call()s would."""
+        check(lib.ptype_b200_assign_seq(self._h, dev, _ptr(reqs), n, 0 if sync else F_ASYNC), "assign_seq")
+
+    def seq_get(self, service: str, dev: int = 0) -> int:
+        v = C.c_uint64()
+        check(lib.ptype_b200_seq_get(self._h, dev, service.encode(), C.byref(v)), "seq_get")
+        return v.value
+
+    def seq_set(self, service: str, value: int, dev: int = 0) -> None:
+        check(lib.ptype_b200_seq_set(self._h, dev, service.encode(), value), "seq_set")
+
     def epoch(self, dev: int = 0) -> int:
         e = C.c_uint64()
         check(lib.ptype_b200_epoch(self._h, dev, C.byref(e)), "epoch")

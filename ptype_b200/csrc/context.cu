@@ -142,6 +142,14 @@ struct DeviceState {
     unsigned long long* d_size = nullptr;  // broadcast header scratch
     ptype_failed* d_failed2 = nullptr;     // (index, status) list of call_batch_values
     size_t failed2_cap = 0;
+    // Balancer counters (rank.cu): one per table slot and image buffer, carried across flips.
+    unsigned long long* seq_counters[2] = {nullptr, nullptr};
+    size_t seq_cap[2] = {0, 0};             // entries
+    bool seq_in_use = false;                // ptype_b200_assign_seq / seq_set has been called
+    uint32_t* rank_rows = nullptr;          // (chunks x n_slots) histogram matrix of assign_seq
+    size_t rank_rows_cap = 0;               // entries
+    unsigned long long* seq_start = nullptr;
+    size_t seq_start_cap = 0;
     unsigned long long* d_tally = nullptr;  // {failed calls, finished CTAs} of a single-launch values batch;
                                             // the kernel leaves both at zero
     unsigned long long* h_tally = nullptr;  // page-locked word the kernel's last CTA writes the count to
@@ -211,8 +219,29 @@ int copy_stream_waits_for_readers(DeviceState* d, int buf) {
 }
 // The flip: dispatches enqueued from here on read buffer `buf`; the buffer they read until now
 // is marked retired on every dispatch stream.
+// Zeroed counter array of at least n_slots entries for image buffer `buf`.
+int ensure_counters(DeviceState* d, int buf, uint32_t n_slots) {
+    if (d->seq_cap[buf] >= n_slots) return PTYPE_OK;
+    CU(cudaStreamSynchronize(d->stream));
+    if (d->seq_counters[buf]) CU(cudaFree(d->seq_counters[buf]));
+    d->seq_counters[buf] = nullptr;
+    d->seq_cap[buf] = 0;
+    CU(cudaMalloc(&d->seq_counters[buf], static_cast<size_t>(n_slots) * sizeof(unsigned long long)));
+    CU(cudaMemset(d->seq_counters[buf], 0, static_cast<size_t>(n_slots) * sizeof(unsigned long long)));
+    d->seq_cap[buf] = n_slots;
+    return PTYPE_OK;
+}
+
 int make_active(DeviceState* d, int buf) {
     const int old = d->active;
+    if (old >= 0 && old != buf && d->seq_in_use) {
+        // the balancer counters follow their services into the new table, in stream order
+        // after every assign_seq enqueued so far (d->stream already waits for the new image)
+        int rc = ensure_counters(d, buf, d->view[buf].n_slots);
+        if (rc != PTYPE_OK) return rc;
+        CU(ptype::launch_carry_counters(d->view[old], d->seq_counters[old], d->view[buf], d->seq_counters[buf],
+                                        d->stream));
+    }
     if (old >= 0 && old != buf) {
         for (int i = 0; i <= kPipe; ++i) {
             cudaStream_t s = i == 0 ? d->stream : d->pipe[i - 1];
@@ -389,6 +418,10 @@ void ptype_b200_close(ptype_ctx* ctx) {
         if (d->d_codec) cudaFree(d->d_codec);
         if (d->d_failed2) cudaFree(d->d_failed2);
         if (d->d_tally) cudaFree(d->d_tally);
+        for (int b = 0; b < 2; ++b)
+            if (d->seq_counters[b]) cudaFree(d->seq_counters[b]);
+        if (d->rank_rows) cudaFree(d->rank_rows);
+        if (d->seq_start) cudaFree(d->seq_start);
         if (d->h_tally) cudaFreeHost(d->h_tally);
         for (int i = 0; i <= kPipe; ++i)
             for (int b = 0; b < 2; ++b)
@@ -1168,6 +1201,102 @@ int ptype_b200_gob_decode_args(ptype_ctx* ctx, int dev, const uint8_t* bytes, co
                                      args_per_call, status, d->stream));
     ctx->launches.fetch_add(1);
     CU(cudaStreamSynchronize(d->stream));
+    return PTYPE_OK;
+}
+
+namespace {
+// Slot of a service in the host copy of the active image's table, or PTYPE_SLOT_EMPTY.
+uint32_t host_slot_of(const ptype_ctx* ctx, const char* service) {
+    const ptype_image_header* hh = reinterpret_cast<const ptype_image_header*>(ctx->host_image.data());
+    const uint64_t key = ptype_b200_service_key(service, hh->key_salt);
+    const ptype_slot* hs = reinterpret_cast<const ptype_slot*>(ctx->host_image.data() + hh->off_slots);
+    for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
+        const uint32_t c = ptype::slot_of(static_cast<uint32_t>(key), static_cast<uint32_t>(key >> 32),
+                                          hh->table_seed, w, hh->n_slots);
+        if (hs[c].node_base != PTYPE_SLOT_EMPTY && hs[c].key == key) return c;
+    }
+    return PTYPE_SLOT_EMPTY;
+}
+}  // namespace
+
+int ptype_b200_assign_seq(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, uint32_t flags) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || (n && !d_reqs) || misaligned(d_reqs, 16)) return PTYPE_E_INVAL;
+    if (n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
+    std::lock_guard<std::mutex> lk(d->mu);
+    if (d->active < 0) return PTYPE_E_NO_IMAGE;
+    CU(cudaSetDevice(d->device));
+    const ptype::DeviceImage img = d->view[d->active];
+    if (ptype::rank_smem_bytes(img.n_slots) > 200 * 1024) {
+        g_last_error = "ptype_b200_assign_seq: the per-CTA histogram holds at most 51200 table slots";
+        return PTYPE_E_LIMIT;
+    }
+    int rc = ensure_counters(d, d->active, img.n_slots);
+    if (rc != PTYPE_OK) return rc;
+    d->seq_in_use = true;
+    if (n == 0) return PTYPE_OK;
+    int n_chunks = 0;
+    size_t chunk = 0;
+    CU(ptype::rank_plan(img.n_slots, n, d->dispatch_sms, &n_chunks, &chunk));
+    const size_t cells = static_cast<size_t>(n_chunks) * img.n_slots;
+    if (cells > d->rank_rows_cap) {
+        CU(cudaStreamSynchronize(d->stream));
+        if (d->rank_rows) CU(cudaFree(d->rank_rows));
+        d->rank_rows = nullptr;
+        d->rank_rows_cap = 0;
+        CU(cudaMalloc(&d->rank_rows, cells * sizeof(uint32_t)));
+        d->rank_rows_cap = cells;
+    }
+    if (img.n_slots > d->seq_start_cap) {
+        CU(cudaStreamSynchronize(d->stream));
+        if (d->seq_start) CU(cudaFree(d->seq_start));
+        d->seq_start = nullptr;
+        d->seq_start_cap = 0;
+        CU(cudaMalloc(&d->seq_start, static_cast<size_t>(img.n_slots) * sizeof(unsigned long long)));
+        d->seq_start_cap = img.n_slots;
+    }
+    CU(ptype::launch_assign_seq(img, d_reqs, n, n_chunks, chunk, d->rank_rows, d->seq_counters[d->active],
+                                d->seq_start, d->stream));
+    ctx->launches.fetch_add(3);
+    if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+    return PTYPE_OK;
+}
+
+int ptype_b200_seq_get(ptype_ctx* ctx, int dev, const char* service, uint64_t* value) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || !service || !value) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> ilk(ctx->image_mu);
+    if (ctx->host_image.empty()) return PTYPE_E_NO_IMAGE;
+    const uint32_t at = host_slot_of(ctx, service);
+    if (at == PTYPE_SLOT_EMPTY) return PTYPE_E_NOT_FOUND;
+    std::lock_guard<std::mutex> lk(d->mu);
+    if (d->active < 0) return PTYPE_E_NO_IMAGE;
+    *value = 0;
+    if (!d->seq_in_use) return PTYPE_OK;
+    CU(cudaSetDevice(d->device));
+    CU(cudaStreamSynchronize(d->stream));
+    unsigned long long v = 0;
+    CU(cudaMemcpy(&v, d->seq_counters[d->active] + at, sizeof v, cudaMemcpyDeviceToHost));
+    *value = v;
+    return PTYPE_OK;
+}
+
+int ptype_b200_seq_set(ptype_ctx* ctx, int dev, const char* service, uint64_t value) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || !service) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> ilk(ctx->image_mu);
+    if (ctx->host_image.empty()) return PTYPE_E_NO_IMAGE;
+    const uint32_t at = host_slot_of(ctx, service);
+    if (at == PTYPE_SLOT_EMPTY) return PTYPE_E_NOT_FOUND;
+    std::lock_guard<std::mutex> lk(d->mu);
+    if (d->active < 0) return PTYPE_E_NO_IMAGE;
+    CU(cudaSetDevice(d->device));
+    int rc = ensure_counters(d, d->active, d->view[d->active].n_slots);
+    if (rc != PTYPE_OK) return rc;
+    d->seq_in_use = true;
+    CU(cudaStreamSynchronize(d->stream));
+    const unsigned long long v = value;
+    CU(cudaMemcpy(d->seq_counters[d->active] + at, &v, sizeof v, cudaMemcpyHostToDevice));
     return PTYPE_OK;
 }
 

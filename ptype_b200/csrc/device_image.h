@@ -84,6 +84,15 @@ cudaError_t launch_gob_decode_args(const uint8_t* bytes, const unsigned long lon
 cudaError_t launch_patch_service(ptype_slot* slots, uint32_t n_slots, uint32_t seed, uint64_t key, int delta,
                                  uint32_t* result, cudaStream_t stream);
 
+// rank.cu: balancer counters on the device.
+size_t rank_smem_bytes(uint32_t n_slots);
+cudaError_t rank_plan(uint32_t n_slots, size_t n, int sm_count, int* n_chunks, size_t* chunk);
+cudaError_t launch_assign_seq(const DeviceImage& img, ptype_req* reqs, size_t n, int n_chunks, size_t chunk,
+                              uint32_t* rows, unsigned long long* counters, unsigned long long* seq_start,
+                              cudaStream_t stream);
+cudaError_t launch_carry_counters(const DeviceImage& from, const unsigned long long* from_counters,
+                                  const DeviceImage& to, unsigned long long* to_counters, cudaStream_t stream);
+
 // Records the text ptype_b200_last_error() returns on the calling thread.
 void set_last_error(const char* text);
 

@@ -216,3 +216,38 @@ def test_loopback_calls_match_in_process_oracle(oracle):
     kv2, snap2 = oracle.snapshot_from_spec(w.optimus_registry())
     want = snap2.dispatch(chk)
     assert np.array_equal(rep["value"], want["value"]) and np.array_equal(rep["node"], want["node"])
+
+
+def test_assign_seq_is_n_sequential_calls(oracle):
+    """po_assign_seq against the rule written out in numpy: a counter per Client, advanced only by
+    calls that find a non-empty client list (rpc.go:177-182), values taken in batch order; and
+    against the reference's own fixed point - a fresh Client's first call draws 1, so with two
+    nodes it lands on index 1 (rpc_test.go:118-158)."""
+    import ptype_b200.workloads as w
+    from ptype_b200 import service_key
+    spec = w.RegistrySpec([("a", "n1", "h", 1), ("a", "n2", "h", 2), ("b", "n1", "h", 3)], [("a", "Calculator")],
+                          ["empty"], "", 3)
+    kv, snap = oracle.snapshot_from_spec(spec)
+    names = ["a", "b", "empty", "ghost"]
+    rng = np.random.default_rng(7)
+    pick = rng.integers(0, 4, 5000)
+    reqs = np.zeros(len(pick), dtype=oracle.REQ_DTYPE)
+    reqs["svc_key"] = np.array([service_key(s) for s in names], dtype=np.uint64)[pick]
+    reqs["seq"] = 0xDEAD
+    counters = np.zeros(snap.n_clients(), dtype=np.uint64)
+    counters[snap.client_index("b")] = 41
+    snap.assign_seq(reqs[:3000], counters)
+    snap.assign_seq(reqs[3000:], counters)      # counters persist across batches
+    want = np.zeros(len(pick), dtype=np.uint64)
+    for i, start in ((0, 0), (1, 41)):
+        at = np.flatnonzero(pick == i)
+        want[at] = start + 1 + np.arange(len(at), dtype=np.uint64)
+    assert np.array_equal(reqs["seq"], want)
+    assert counters[snap.client_index("a")] == (pick == 0).sum()
+    assert counters[snap.client_index("b")] == 41 + (pick == 1).sum()
+    assert counters[snap.client_index("empty")] == 0 and snap.client_index("ghost") == -1
+    first = np.zeros(1, dtype=oracle.REQ_DTYPE)
+    first["svc_key"] = service_key("a")
+    fresh = np.zeros(snap.n_clients(), dtype=np.uint64)
+    snap.assign_seq(first, fresh)
+    assert first["seq"][0] == 1 and oracle.lib().po_round_robin(int(first["seq"][0]), 2) == 1
