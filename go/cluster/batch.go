@@ -207,6 +207,25 @@ func (d *Dispatcher) UpdateService(service string, delta int) error {
 	return nil
 }
 
+// AssignSeq fills the seq field of n device-resident request records the way n sequential
+// Client.Call()s, each on the Client of its record's service, would have drawn them: every
+// service's counter (connectionBalancer.seq, rpc.go:129) lives on the GPU, advances only for
+// calls that find a non-empty client list (rpc.go:178-181), and follows its service through
+// SetNodes / UpdateService.  dReqs is device memory from ptype_b200_device_alloc.
+func (d *Dispatcher) AssignSeq(dReqs unsafe.Pointer, n int) error {
+	return abiError("ptype_b200_assign_seq",
+		C.ptype_b200_assign_seq(d.ctx, 0, (*C.ptype_req)(dReqs), C.size_t(n), 0))
+}
+
+// Seq reads a service's counter: the last value drawn.
+func (d *Dispatcher) Seq(service string) (uint64, error) {
+	cs := C.CString(service)
+	defer C.free(unsafe.Pointer(cs))
+	var v C.uint64_t
+	err := abiError("ptype_b200_seq_get", C.ptype_b200_seq_get(d.ctx, 0, cs, &v))
+	return uint64(v), err
+}
+
 // SelectedNodes is getSelectedNodes() (rpc.go:293-297) read back from the snapshot.
 func (d *Dispatcher) SelectedNodes(service string) []Node {
 	d.mu.Lock()

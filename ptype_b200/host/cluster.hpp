@@ -504,6 +504,47 @@ class Dispatcher {
         return epoch_;
     }
 
+    // One batch for MANY services: what a process holding one Client per service does when it
+    // issues reqs[0], reqs[1], ... in order, each through the Client of its own service.  Every
+    // Client draws its sequence number from its own counter (rpc.go:129,181) and only when its
+    // client list is not empty (rpc.go:178-180); here those counters live on the device and the
+    // seq field of the records is filled there (ptype_b200_assign_seq), so callers set svc_key,
+    // method, recv and the arguments only.
+    Error CallMixed(std::vector<ptype_req>& reqs, std::vector<ptype_reply>* replies) {
+        replies->assign(reqs.size(), ptype_reply{});
+        if (reqs.empty()) return Error();
+        void *d_req = nullptr, *d_rep = nullptr;
+        auto fail = [&](const char* what, int rc) {
+            if (d_req) ptype_b200_device_free(ctx_, 0, d_req);
+            if (d_rep) ptype_b200_device_free(ctx_, 0, d_rep);
+            return Error(std::string(what) + ": " + ptype_b200_strerror(rc) + ": " + ptype_b200_last_error());
+        };
+        int rc = ptype_b200_device_alloc(ctx_, 0, reqs.size() * sizeof(ptype_req), &d_req);
+        if (rc != PTYPE_OK) return fail("device_alloc", rc);
+        rc = ptype_b200_device_alloc(ctx_, 0, reqs.size() * sizeof(ptype_reply), &d_rep);
+        if (rc != PTYPE_OK) return fail("device_alloc", rc);
+        rc = ptype_b200_memcpy_h2d(ctx_, 0, d_req, reqs.data(), reqs.size() * sizeof(ptype_req));
+        if (rc != PTYPE_OK) return fail("memcpy_h2d", rc);
+        rc = ptype_b200_assign_seq(ctx_, 0, static_cast<ptype_req*>(d_req), reqs.size(), PTYPE_F_ASYNC);
+        if (rc != PTYPE_OK) return fail("assign_seq", rc);
+        rc = ptype_b200_dispatch(ctx_, 0, static_cast<const ptype_req*>(d_req), reqs.size(),
+                                 static_cast<ptype_reply*>(d_rep), PTYPE_F_DEVICE_PTRS);
+        if (rc != PTYPE_OK) return fail("dispatch", rc);
+        rc = ptype_b200_memcpy_d2h(ctx_, 0, replies->data(), d_rep, reqs.size() * sizeof(ptype_reply));
+        if (rc != PTYPE_OK) return fail("memcpy_d2h", rc);
+        rc = ptype_b200_memcpy_d2h(ctx_, 0, reqs.data(), d_req, reqs.size() * sizeof(ptype_req));  // the seq drawn
+        if (rc != PTYPE_OK) return fail("memcpy_d2h", rc);
+        ptype_b200_device_free(ctx_, 0, d_req);
+        ptype_b200_device_free(ctx_, 0, d_rep);
+        return Error();
+    }
+    // The device-side counter of a service's Client (the last value drawn).
+    uint64_t Seq(const std::string& service) {
+        uint64_t v = 0;
+        ptype_b200_seq_get(ctx_, 0, service.c_str(), &v);
+        return v;
+    }
+
    private:
     Node NodeOfLocked(uint32_t id) {
         char addr[256];

@@ -315,6 +315,58 @@ static void TestCoalescer_concurrent_callers() {
     REQUIRE(co.Batches() < static_cast<uint64_t>(kThreads) * kCalls / 2);   // calls really were coalesced
 }
 
+// A batch that mixes services: every service's Client draws from its own counter, in batch
+// order, and a service without nodes draws nothing (rpc.go:129,172-183) - on the device.
+static void TestDispatcher_mixed_batch_draws_seq_on_device() {
+    Dispatcher gpu("", 3);
+    gpu.Expose("foo", "Calculator");
+    gpu.Expose("bar", "Calculator");
+    auto n = fakeNodes(5);
+    REQUIRE(!gpu.SetNodes("foo", {n[0], n[1]}));
+    REQUIRE(!gpu.SetNodes("bar", {n[2], n[3], n[4]}));
+    REQUIRE(!gpu.SetNodes("idle", {}));
+    uint32_t method = 0, recv = 0;
+    ptype_b200_method_key("Calculator.Multiply", &method, &recv);
+    const char* names[3] = {"foo", "bar", "idle"};
+    std::vector<ptype_req> reqs(3000);
+    std::vector<int> which(reqs.size());
+    for (size_t j = 0; j < reqs.size(); ++j) {
+        which[j] = static_cast<int>((j * 7 + j / 5) % 3);
+        reqs[j] = ptype_req{};
+        reqs[j].svc_key = gpu.ServiceKey(names[which[j]]);
+        reqs[j].seq = 999;  // ignored
+        reqs[j].method = method;
+        reqs[j].recv = recv;
+        reqs[j].a0 = static_cast<int64_t>(j);
+        reqs[j].a1 = 3;
+    }
+    std::vector<ptype_reply> rep;
+    REQUIRE(!gpu.CallMixed(reqs, &rep));
+    const std::vector<Node> sel[2] = {gpu.SelectedNodes("foo"), gpu.SelectedNodes("bar")};
+    REQUIRE(sel[0].size() == 2 && sel[1].size() == 3);
+    uint64_t drawn[3] = {0, 0, 0};
+    int bad = 0;
+    for (size_t j = 0; j < reqs.size(); ++j) {
+        const int s = which[j];
+        if (s == 2) {   // no nodes: ErrNoClientAvailable, nothing drawn
+            if (rep[j].status != PTYPE_ST_NO_CLIENT || reqs[j].seq != 0) ++bad;
+            continue;
+        }
+        const uint64_t seq = ++drawn[s];
+        if (reqs[j].seq != seq || rep[j].status != PTYPE_ST_OK || rep[j].value != static_cast<int64_t>(j) * 3 ||
+            !(gpu.NodeOf(rep[j].node) == sel[s][seq % sel[s].size()]))
+            ++bad;
+    }
+    REQUIRE(bad == 0);
+    REQUIRE(gpu.Seq("foo") == drawn[0] && gpu.Seq("bar") == drawn[1] && gpu.Seq("idle") == 0);
+    // a node joins foo: new image, new selection, the counters carry on
+    REQUIRE(!gpu.SetNodes("foo", {n[0], n[1], n[4]}));
+    std::vector<ptype_req> more(10, reqs[0]);
+    for (auto& q : more) q.svc_key = gpu.ServiceKey("foo");
+    REQUIRE(!gpu.CallMixed(more, &rep));
+    REQUIRE(more[0].seq == drawn[0] + 1 && more[9].seq == drawn[0] + 10);
+}
+
 // TestNewConnectionBalancer_with_no_available_server (rpc_test.go:307-314)
 static void TestNewClient_with_no_available_server() {
     Dispatcher gpu("", 3);
@@ -439,6 +491,7 @@ int main(int argc, char** argv) {
     if (gpu) {
         RUN(TestClient_Go);
         RUN(TestCoalescer_concurrent_callers);
+        RUN(TestDispatcher_mixed_batch_draws_seq_on_device);
         RUN(TestExample_optimus);
         RUN(TestClient_default_conn_config);
         RUN(TestClient_Call);
