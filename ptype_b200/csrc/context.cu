@@ -1227,7 +1227,7 @@ int ptype_b200_assign_seq(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, 
     if (d->active < 0) return PTYPE_E_NO_IMAGE;
     CU(cudaSetDevice(d->device));
     const ptype::DeviceImage img = d->view[d->active];
-    if (ptype::rank_smem_bytes(img.n_slots) > 200 * 1024) {
+    if (!ptype::rank_supported(img.n_slots)) {
         g_last_error = "ptype_b200_assign_seq: the per-CTA histogram holds at most 51200 table slots";
         return PTYPE_E_LIMIT;
     }
@@ -1235,10 +1235,9 @@ int ptype_b200_assign_seq(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, 
     if (rc != PTYPE_OK) return rc;
     d->seq_in_use = true;
     if (n == 0) return PTYPE_OK;
-    int n_chunks = 0;
-    size_t chunk = 0;
-    CU(ptype::rank_plan(img.n_slots, n, d->dispatch_sms, &n_chunks, &chunk));
-    const size_t cells = static_cast<size_t>(n_chunks) * img.n_slots;
+    ptype::RankPlan plan;
+    CU(ptype::rank_plan(img.n_slots, n, d->dispatch_sms, &plan));
+    const size_t cells = static_cast<size_t>(plan.n_chunks) * img.n_slots;
     if (cells > d->rank_rows_cap) {
         CU(cudaStreamSynchronize(d->stream));
         if (d->rank_rows) CU(cudaFree(d->rank_rows));
@@ -1255,8 +1254,8 @@ int ptype_b200_assign_seq(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, 
         CU(cudaMalloc(&d->seq_start, static_cast<size_t>(img.n_slots) * sizeof(unsigned long long)));
         d->seq_start_cap = img.n_slots;
     }
-    CU(ptype::launch_assign_seq(img, d_reqs, n, n_chunks, chunk, d->rank_rows, d->seq_counters[d->active],
-                                d->seq_start, d->stream));
+    CU(ptype::launch_assign_seq(img, plan, d_reqs, n, d->rank_rows, d->seq_counters[d->active], d->seq_start,
+                                d->stream));
     ctx->launches.fetch_add(3);
     if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
     return PTYPE_OK;

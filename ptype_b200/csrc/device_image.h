@@ -85,9 +85,16 @@ cudaError_t launch_patch_service(ptype_slot* slots, uint32_t n_slots, uint32_t s
                                  uint32_t* result, cudaStream_t stream);
 
 // rank.cu: balancer counters on the device.
-size_t rank_smem_bytes(uint32_t n_slots);
-cudaError_t rank_plan(uint32_t n_slots, size_t n, int sm_count, int* n_chunks, size_t* chunk);
-cudaError_t launch_assign_seq(const DeviceImage& img, ptype_req* reqs, size_t n, int n_chunks, size_t chunk,
+struct RankPlan {
+    bool staged = false;  // table keys staged in shared memory (else probed in L1/L2)
+    int threads = 0;
+    size_t smem = 0;
+    int n_chunks = 0;     // CTAs = contiguous chunks of the batch = rows of the histogram matrix
+    size_t chunk = 0;     // records per chunk
+};
+bool rank_supported(uint32_t n_slots);
+cudaError_t rank_plan(uint32_t n_slots, size_t n, int sm_count, RankPlan* plan);
+cudaError_t launch_assign_seq(const DeviceImage& img, const RankPlan& plan, ptype_req* reqs, size_t n,
                               uint32_t* rows, unsigned long long* counters, unsigned long long* seq_start,
                               cudaStream_t stream);
 cudaError_t launch_carry_counters(const DeviceImage& from, const unsigned long long* from_counters,

@@ -10,13 +10,20 @@
 //   rank_count_kernel   each CTA owns a contiguous chunk of the batch and histograms it by table
 //                       slot in shared memory; the histogram goes to row `blockIdx.x` of a
 //                       (chunks x n_slots) matrix
-//   rank_scan_kernel    one thread per slot: exclusive scan down its column, counter update
+//   rank_scan_kernel    exclusive scan down every column (eight warps per 32 columns), counter update
 //   rank_assign_kernel  each CTA reloads its row (= calls to each service in earlier chunks) and
-//                       walks its chunk 256 calls at a time in order: __match_any_sync ranks the
-//                       calls of one service inside a warp, the warps of the CTA take turns on
-//                       the running counts, and the seq field of every record is written
+//                       walks its chunk in order, each warp holding 128 consecutive calls per
+//                       trip: __match_any_sync ranks the calls of one service inside a tile of
+//                       32, the warps of the CTA take turns on the running counts (one turn
+//                       settles a warp's four tiles), and the seq field of every record is written
 // Counters are indexed by table slot; carry_counters_kernel moves them to the slots of the next
 // image when the registry flips (services are matched by key).
+//
+// Where they fit (tables up to ~18 500 slots) the table's keys are staged in shared memory beside
+// the histogram, 12 bytes per slot, one 1024-thread CTA per SM: three random 16-byte probes per
+// record against a table in L2 cost more than everything else together (measured on the
+// 12 800-slot registry: 497 + 693 us per 2^24 records for the two passes).  Larger tables, up to
+// 51 200 slots, are probed in L1/L2 by 256-thread CTAs.
 //
 // HBM traffic: two passes over the keys (a 32-byte sector per 48-byte record each) and one 8-byte
 // store per record; the (chunks x n_slots) matrix stays in L2.
@@ -30,9 +37,12 @@
 namespace ptype {
 namespace {
 
-constexpr int kRankThreads = 256;
+constexpr int kStagedThreads = 1024;  // keys in shared memory: one CTA per SM (two for small tables)
+constexpr int kProbeThreads = 256;    // table probed in L1/L2: up to four CTAs per SM
+constexpr int kScanThreads = 256;
 constexpr uint32_t kNoSlot = 0xFFFFFFFFu;
 constexpr uint32_t kFull = 0xFFFFFFFFu;
+constexpr size_t kRankSmemBudget = 220 * 1024;
 
 struct RankTable {
     const ptype_slot* slots;
@@ -40,161 +50,371 @@ struct RankTable {
     uint32_t seed;
 };
 
-// Slot of `key` in the cuckoo table, or kNoSlot.  *n_nodes: the service's registered nodes.
-__device__ __forceinline__ uint32_t find_slot(const RankTable& t, uint64_t key, uint32_t* n_nodes) {
-    const uint32_t lo = static_cast<uint32_t>(key), hi = static_cast<uint32_t>(key >> 32);
-#pragma unroll
-    for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
-        const uint32_t at = slot_of(lo, hi, t.seed, w, t.n_slots);
-        const uint4 s = __ldg(reinterpret_cast<const uint4*>(t.slots) + at);
-        if (s.z != PTYPE_SLOT_EMPTY && s.x == lo && s.y == hi) {
-            *n_nodes = s.w & 0xFFFFFFu;
-            return at;
-        }
+// Shared memory of a rank CTA: [keys: 8 B per slot][counts: 4 B per slot][countable: 1 bit per
+// slot]; the first and last part only when the keys are staged.
+template <bool kStaged>
+struct RankShared {
+    const unsigned long long* keys;
+    uint32_t* counts;
+    const uint32_t* countable;
+};
+
+__host__ __device__ inline size_t rank_shared_bytes(bool staged, uint32_t n_slots) {
+    return staged ? static_cast<size_t>(n_slots) * 12 + static_cast<size_t>((n_slots + 31) / 32) * 4
+                  : static_cast<size_t>(n_slots) * 4;
+}
+
+__device__ __forceinline__ uint4 ld_slot(const ptype_slot* slot) {
+    return __ldg(reinterpret_cast<const uint4*>(slot));
+}
+
+// Carves the CTA's dynamic shared memory and, when staging, copies the table's keys in and
+// marks the slots that count: occupied, and the service has at least one node.
+template <bool kStaged>
+__device__ __forceinline__ RankShared<kStaged> rank_shared(const RankTable& t, unsigned char* smem) {
+    RankShared<kStaged> sh;
+    if (!kStaged) {
+        sh.keys = nullptr;
+        sh.countable = nullptr;
+        sh.counts = reinterpret_cast<uint32_t*>(smem);
+        return sh;
     }
-    *n_nodes = 0;
-    return kNoSlot;
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem);
+    sh.counts = reinterpret_cast<uint32_t*>(smem + static_cast<size_t>(t.n_slots) * 8);
+    uint32_t* countable = sh.counts + t.n_slots;
+    const uint32_t lane = threadIdx.x & 31u;
+    for (uint32_t base = (threadIdx.x >> 5) * 32u; base < t.n_slots; base += blockDim.x) {
+        const uint32_t s = base + lane;
+        bool counts_here = false;
+        if (s < t.n_slots) {
+            const uint4 e = ld_slot(t.slots + s);
+            keys[s] = static_cast<unsigned long long>(e.x) | (static_cast<unsigned long long>(e.y) << 32);
+            counts_here = e.z != PTYPE_SLOT_EMPTY && (e.w & 0xFFFFFFu) != 0;
+        }
+        const uint32_t bits = __ballot_sync(kFull, counts_here);
+        if (lane == 0) countable[base >> 5] = bits;
+    }
+    sh.keys = keys;
+    sh.countable = countable;
+    return sh;
 }
 
 // The slot a call is counted under, or kNoSlot when it consumes no counter value: unknown
-// service (no Client exists) or a Client whose list is empty (rpc.go:178-180).
-__device__ __forceinline__ uint32_t counted_slot(const RankTable& t, const ptype_req* reqs, size_t j) {
-    const uint64_t key = __ldg(reinterpret_cast<const unsigned long long*>(reqs + j));
-    uint32_t n_nodes;
-    const uint32_t at = find_slot(t, key, &n_nodes);
-    return n_nodes ? at : kNoSlot;
+// service (no Client exists) or a Client whose list is empty (rpc.go:178-180).  All three
+// candidates are read unconditionally: independent loads, one latency.
+template <bool kStaged>
+__device__ __forceinline__ uint32_t counted_slot(const RankTable& t, const RankShared<kStaged>& sh,
+                                                 unsigned long long key) {
+    const uint32_t lo = static_cast<uint32_t>(key), hi = static_cast<uint32_t>(key >> 32);
+    uint32_t at[PTYPE_SLOT_WAYS];
+    bool hit[PTYPE_SLOT_WAYS];
+    if (kStaged) {
+        unsigned long long k[PTYPE_SLOT_WAYS];
+        uint32_t bits[PTYPE_SLOT_WAYS];
+#pragma unroll
+        for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
+            at[w] = slot_of(lo, hi, t.seed, w, t.n_slots);
+            k[w] = sh.keys[at[w]];
+            bits[w] = sh.countable[at[w] >> 5];
+        }
+#pragma unroll
+        for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) hit[w] = k[w] == key && ((bits[w] >> (at[w] & 31u)) & 1u);
+    } else {
+        uint4 e[PTYPE_SLOT_WAYS];
+#pragma unroll
+        for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
+            at[w] = slot_of(lo, hi, t.seed, w, t.n_slots);
+            e[w] = ld_slot(t.slots + at[w]);
+        }
+#pragma unroll
+        for (int w = 0; w < PTYPE_SLOT_WAYS; ++w)
+            hit[w] = e[w].z != PTYPE_SLOT_EMPTY && e[w].x == lo && e[w].y == hi && (e[w].w & 0xFFFFFFu) != 0;
+    }
+    uint32_t found = kNoSlot;
+#pragma unroll
+    for (int w = PTYPE_SLOT_WAYS - 1; w >= 0; --w)
+        if (hit[w]) found = at[w];
+    return found;
 }
 
-__global__ void __launch_bounds__(kRankThreads)
+// Records handled per thread and loop trip.  Their keys are loaded one trip ahead and their
+// probes are independent of one another.  A warp's records are CONSECUTIVE: kRankDepth tiles of
+// 32, so that in rank_assign_kernel a warp settles all of them in one turn.
+constexpr int kRankDepth = 4;
+
+// Index of the r-th record of this thread in the trip that starts at `base`.
+__device__ __forceinline__ size_t record_index(size_t base, int r) {
+    return base + (static_cast<size_t>(threadIdx.x >> 5) * kRankDepth + r) * 32 + (threadIdx.x & 31u);
+}
+
+// Keys of this thread's records; addresses past `hi` are clamped.
+__device__ __forceinline__ void load_keys(const ptype_req* reqs, size_t base, size_t hi,
+                                          unsigned long long (&key)[kRankDepth]) {
+#pragma unroll
+    for (int r = 0; r < kRankDepth; ++r) {
+        const size_t j = record_index(base, r);
+        key[r] = __ldg(reinterpret_cast<const unsigned long long*>(reqs + (j < hi ? j : hi - 1)));
+    }
+}
+
+template <bool kStaged>
+__device__ __forceinline__ void counted_slots(const RankTable& t, const RankShared<kStaged>& sh,
+                                              const unsigned long long (&key)[kRankDepth], size_t base, size_t hi,
+                                              uint32_t (&at)[kRankDepth]) {
+#pragma unroll
+    for (int r = 0; r < kRankDepth; ++r) {
+        const size_t j = record_index(base, r);
+        const uint32_t slot = counted_slot<kStaged>(t, sh, key[r]);
+        at[r] = j < hi ? slot : kNoSlot;
+    }
+}
+
+template <bool kStaged, int kThreads>
+__global__ void __launch_bounds__(kThreads)
     rank_count_kernel(const RankTable t, const ptype_req* __restrict__ reqs, const size_t n, const size_t chunk,
                       uint32_t* __restrict__ rows) {
-    extern __shared__ uint32_t hist[];
-    for (uint32_t s = threadIdx.x; s < t.n_slots; s += kRankThreads) hist[s] = 0;
+    extern __shared__ __align__(16) unsigned char rank_smem[];
+    const RankShared<kStaged> sh = rank_shared<kStaged>(t, rank_smem);
+    for (uint32_t s = threadIdx.x; s < t.n_slots; s += kThreads) sh.counts[s] = 0;
     __syncthreads();
     const size_t lo = static_cast<size_t>(blockIdx.x) * chunk;
     const size_t hi = lo + chunk < n ? lo + chunk : n;
-    for (size_t j = lo + threadIdx.x; j < hi; j += kRankThreads) {
-        const uint32_t at = counted_slot(t, reqs, j);
-        if (at != kNoSlot) atomicAdd(&hist[at], 1u);
+    const uint32_t lane = threadIdx.x & 31u;
+    constexpr size_t kTrip = static_cast<size_t>(kThreads) * kRankDepth;
+    unsigned long long key[kRankDepth], next[kRankDepth];
+    if (lo < hi) load_keys(reqs, lo, hi, next);
+    for (size_t base = lo; base < hi; base += kTrip) {
+#pragma unroll
+        for (int r = 0; r < kRankDepth; ++r) key[r] = next[r];
+        if (base + kTrip < hi) load_keys(reqs, base + kTrip, hi, next);
+        uint32_t at[kRankDepth];
+        counted_slots<kStaged>(t, sh, key, base, hi, at);
+#pragma unroll
+        for (int r = 0; r < kRankDepth; ++r) {
+            // A tile that names one service only (a single Client's batch) adds once; otherwise
+            // every counted record adds for itself - __match_any_sync would merge equal slots, but
+            // its latency was ~45 % of this kernel's stall samples on the 10 000-service stream.
+            const uint32_t lead = __shfl_sync(kFull, at[r], 0);
+            if (__all_sync(kFull, at[r] == lead)) {
+                if (lane == 0 && lead != kNoSlot) atomicAdd(&sh.counts[lead], 32u);
+            } else if (at[r] != kNoSlot) {
+                atomicAdd(&sh.counts[at[r]], 1u);
+            }
+        }
     }
     __syncthreads();
     uint32_t* row = rows + static_cast<size_t>(blockIdx.x) * t.n_slots;
-    for (uint32_t s = threadIdx.x; s < t.n_slots; s += kRankThreads) row[s] = hist[s];
+    for (uint32_t s = threadIdx.x; s < t.n_slots; s += kThreads) row[s] = sh.counts[s];
 }
 
 // Column s of the matrix becomes its exclusive prefix sum; seq_start[s] keeps the counter value
-// the batch started from and the counter moves past the batch.
-__global__ void __launch_bounds__(kRankThreads)
+// the batch started from and the counter moves past the batch.  A CTA takes 32 adjacent columns
+// (a row segment is one 128-byte line); its eight warps split the rows into eight runs, sum
+// their runs, exchange the sums, then rewrite their runs - a column's latency chain is a
+// sixteenth of walking it top to bottom, and the loads of eight rows are always in flight.
+constexpr int kScanRows = 8;
+__global__ void __launch_bounds__(kScanThreads)
     rank_scan_kernel(uint32_t* __restrict__ rows, const int n_chunks, const uint32_t n_slots,
                      unsigned long long* __restrict__ counters, unsigned long long* __restrict__ seq_start) {
-    const uint32_t s = blockIdx.x * kRankThreads + threadIdx.x;
-    if (s >= n_slots) return;
-    uint32_t run = 0;
-    for (int c = 0; c < n_chunks; ++c) {
-        uint32_t* cell = rows + static_cast<size_t>(c) * n_slots + s;
-        const uint32_t v = *cell;
-        *cell = run;
+    __shared__ uint32_t warp_sum[kScanThreads / 32][32];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t s = blockIdx.x * 32u + lane;
+    const bool live = s < n_slots;
+    constexpr int kWarps = kScanThreads / 32;
+    const int per = (n_chunks + kWarps - 1) / kWarps;
+    const int c0 = static_cast<int>(warp) * per < n_chunks ? static_cast<int>(warp) * per : n_chunks;
+    const int c1 = c0 + per < n_chunks ? c0 + per : n_chunks;
+    uint32_t* col = rows + (live ? s : 0);
+    uint32_t sum = 0;
+    if (live) {
+        int c = c0;
+        for (; c + kScanRows <= c1; c += kScanRows) {
+            uint32_t v[kScanRows];
+#pragma unroll
+            for (int k = 0; k < kScanRows; ++k) v[k] = col[static_cast<size_t>(c + k) * n_slots];
+#pragma unroll
+            for (int k = 0; k < kScanRows; ++k) sum += v[k];
+        }
+        for (; c < c1; ++c) sum += col[static_cast<size_t>(c) * n_slots];
+    }
+    warp_sum[warp][lane] = sum;
+    __syncthreads();
+    uint32_t run = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+        const uint32_t v = warp_sum[w][lane];
+        if (w < static_cast<int>(warp)) run += v;
+        total += v;
+    }
+    if (!live) return;
+    int c = c0;
+    for (; c + kScanRows <= c1; c += kScanRows) {
+        uint32_t v[kScanRows];
+#pragma unroll
+        for (int k = 0; k < kScanRows; ++k) v[k] = col[static_cast<size_t>(c + k) * n_slots];
+#pragma unroll
+        for (int k = 0; k < kScanRows; ++k) {
+            col[static_cast<size_t>(c + k) * n_slots] = run;
+            run += v[k];
+        }
+    }
+    for (; c < c1; ++c) {
+        const uint32_t v = col[static_cast<size_t>(c) * n_slots];
+        col[static_cast<size_t>(c) * n_slots] = run;
         run += v;
     }
-    const unsigned long long start = counters[s];
-    seq_start[s] = start;
-    counters[s] = start + run;
+    if (warp == 0) {
+        const unsigned long long start = counters[s];
+        seq_start[s] = start;
+        counters[s] = start + total;
+    }
 }
 
-__global__ void __launch_bounds__(kRankThreads)
+template <bool kStaged, int kThreads>
+__global__ void __launch_bounds__(kThreads)
     rank_assign_kernel(const RankTable t, ptype_req* __restrict__ reqs, const size_t n, const size_t chunk,
                        const uint32_t* __restrict__ rows, const unsigned long long* __restrict__ seq_start) {
-    extern __shared__ uint32_t run[];  // counted calls to each service before the CTA's cursor
+    extern __shared__ __align__(16) unsigned char rank_smem[];
+    const RankShared<kStaged> sh = rank_shared<kStaged>(t, rank_smem);
+    uint32_t* run = sh.counts;  // counted calls to each service before the CTA's cursor
     const uint32_t* row = rows + static_cast<size_t>(blockIdx.x) * t.n_slots;
-    for (uint32_t s = threadIdx.x; s < t.n_slots; s += kRankThreads) run[s] = row[s];
+    for (uint32_t s = threadIdx.x; s < t.n_slots; s += kThreads) run[s] = row[s];
     __syncthreads();
     const size_t lo = static_cast<size_t>(blockIdx.x) * chunk;
     const size_t hi = lo + chunk < n ? lo + chunk : n;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    for (size_t base = lo; base < hi; base += kRankThreads) {  // uniform trip count per CTA
-        const size_t j = base + threadIdx.x;
-        const uint32_t at = j < hi ? counted_slot(t, reqs, j) : kNoSlot;
-        // calls of one service inside this warp: lanes in `peers`, in batch order
-        const uint32_t peers = __match_any_sync(kFull, at != kNoSlot ? at : 0x80000000u + lane);
-        const uint32_t before = __popc(peers & ((1u << lane) - 1u));
-        uint32_t first = 0;
-        // the warps hold consecutive calls, so they update the running counts in warp order
-        for (uint32_t w = 0; w < kRankThreads / 32; ++w) {
-            if (w == warp && at != kNoSlot && before == 0) {
-                first = run[at];
-                run[at] = first + __popc(peers);
+    constexpr size_t kTrip = static_cast<size_t>(kThreads) * kRankDepth;
+    unsigned long long key[kRankDepth], next[kRankDepth];
+    if (lo < hi) load_keys(reqs, lo, hi, next);
+    for (size_t base = lo; base < hi; base += kTrip) {  // uniform trip count per CTA
+#pragma unroll
+        for (int r = 0; r < kRankDepth; ++r) key[r] = next[r];
+        if (base + kTrip < hi) load_keys(reqs, base + kTrip, hi, next);
+        uint32_t at[kRankDepth];
+        counted_slots<kStaged>(t, sh, key, base, hi, at);
+        unsigned long long start[kRankDepth];  // fetched now, needed after the warps' turns
+#pragma unroll
+        for (int r = 0; r < kRankDepth; ++r) start[r] = at[r] != kNoSlot ? __ldg(seq_start + at[r]) : 0ull;
+        // calls of one service inside a tile of 32: lanes in `peers`, in batch order
+        uint32_t peers[kRankDepth], before[kRankDepth], first[kRankDepth];
+#pragma unroll
+        for (int r = 0; r < kRankDepth; ++r) {
+            peers[r] = __match_any_sync(kFull, at[r] != kNoSlot ? at[r] : 0x80000000u + lane);
+            before[r] = __popc(peers[r] & ((1u << lane) - 1u));
+            first[r] = 0;
+        }
+        // The warps hold consecutive runs of the batch, so they update the running counts in
+        // warp order; inside its turn a warp settles its tiles in order.  (Passing a ticket from
+        // warp to warp through shared memory instead of CTA-wide barriers was measured too: the
+        // two fences it needs per turn cost what the barrier costs.)
+        for (uint32_t w = 0; w < kThreads / 32; ++w) {
+            if (w == warp) {
+#pragma unroll
+                for (int r = 0; r < kRankDepth; ++r) {
+                    if (at[r] != kNoSlot && before[r] == 0) {
+                        first[r] = run[at[r]];
+                        run[at[r]] = first[r] + __popc(peers[r]);
+                    }
+                    __syncwarp();  // the next tile may name the same service from another lane
+                }
             }
             __syncthreads();
         }
-        first = __shfl_sync(kFull, first, __ffs(peers) - 1);
-        if (j < hi) {
-            const unsigned long long seq = at != kNoSlot ? seq_start[at] + first + before + 1ull : 0ull;
-            reinterpret_cast<unsigned long long*>(reqs + j)[1] = seq;  // ptype_req.seq
+#pragma unroll
+        for (int r = 0; r < kRankDepth; ++r) {
+            const size_t j = record_index(base, r);
+            const uint32_t f = __shfl_sync(kFull, first[r], __ffs(peers[r]) - 1);
+            if (j < hi) {
+                const unsigned long long seq = at[r] != kNoSlot ? start[r] + f + before[r] + 1ull : 0ull;
+                reinterpret_cast<unsigned long long*>(reqs + j)[1] = seq;  // ptype_req.seq
+            }
         }
     }
 }
 
 // Counters follow their services from the table of the outgoing image to the table of the
 // incoming one (placement may differ; a service the new image does not know is dropped).
-__global__ void __launch_bounds__(kRankThreads)
+__global__ void __launch_bounds__(kScanThreads)
     carry_counters_kernel(const RankTable from, const unsigned long long* __restrict__ from_counters,
                           const RankTable to, unsigned long long* __restrict__ to_counters) {
-    const uint32_t s = blockIdx.x * kRankThreads + threadIdx.x;
+    const uint32_t s = blockIdx.x * kScanThreads + threadIdx.x;
     if (s >= from.n_slots) return;
-    const uint4 e = __ldg(reinterpret_cast<const uint4*>(from.slots) + s);
+    const uint4 e = ld_slot(from.slots + s);
     if (e.z == PTYPE_SLOT_EMPTY) return;
-    uint32_t n_nodes;
-    const uint32_t at = find_slot(to, static_cast<uint64_t>(e.x) | (static_cast<uint64_t>(e.y) << 32), &n_nodes);
-    if (at != kNoSlot) to_counters[at] = from_counters[s];
+    const uint32_t lo = e.x, hi = e.y;
+#pragma unroll
+    for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
+        const uint32_t at = slot_of(lo, hi, to.seed, w, to.n_slots);
+        const uint4 d = ld_slot(to.slots + at);
+        if (d.z != PTYPE_SLOT_EMPTY && d.x == lo && d.y == hi) {
+            to_counters[at] = from_counters[s];
+            return;
+        }
+    }
 }
 
 RankTable table_of(const DeviceImage& img) { return RankTable{img.slots, img.n_slots, img.table_seed}; }
 
-}  // namespace
-
-size_t rank_smem_bytes(uint32_t n_slots) { return static_cast<size_t>(n_slots) * sizeof(uint32_t); }
-
-// CTAs (= chunks) a batch of n calls is split over, given how many CTAs fit the device at once.
-cudaError_t rank_plan(uint32_t n_slots, size_t n, int sm_count, int* n_chunks, size_t* chunk) {
-    const size_t smem = rank_smem_bytes(n_slots);
+template <bool kStaged, int kThreads>
+cudaError_t prepare_variant(size_t smem, int* per_sm) {
     if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(rank_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             static_cast<int>(smem));
+        cudaError_t e = cudaFuncSetAttribute(rank_count_kernel<kStaged, kThreads>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(rank_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     static_cast<int>(smem));
+            e = cudaFuncSetAttribute(rank_assign_kernel<kStaged, kThreads>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
         if (e != cudaSuccess) return e;
     }
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(per_sm, rank_assign_kernel<kStaged, kThreads>, kThreads, smem);
+}
+
+}  // namespace
+
+bool rank_supported(uint32_t n_slots) { return rank_shared_bytes(false, n_slots) <= 200 * 1024; }
+
+// How a batch of n calls is split: variant, CTAs (= chunks = matrix rows) and records per chunk.
+cudaError_t rank_plan(uint32_t n_slots, size_t n, int sm_count, RankPlan* plan) {
+    plan->staged = rank_shared_bytes(true, n_slots) <= kRankSmemBudget;
+    plan->threads = plan->staged ? kStagedThreads : kProbeThreads;
+    plan->smem = rank_shared_bytes(plan->staged, n_slots);
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rank_assign_kernel, kRankThreads, smem);
+    cudaError_t e = plan->staged ? prepare_variant<true, kStagedThreads>(plan->smem, &per_sm)
+                                 : prepare_variant<false, kProbeThreads>(plan->smem, &per_sm);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorInvalidConfiguration;
-    if (per_sm > 4) per_sm = 4;
+    const int cap = plan->staged ? 2 : 4;
+    if (per_sm > cap) per_sm = cap;
     size_t ctas = static_cast<size_t>(sm_count) * per_sm;
-    const size_t rounds = (n + kRankThreads - 1) / kRankThreads;
+    const size_t rounds = (n + plan->threads - 1) / plan->threads;
     if (ctas > rounds) ctas = rounds ? rounds : 1;
-    // chunk: a whole number of 256-call rounds, so chunk boundaries are warp-aligned
-    const size_t per = (rounds + ctas - 1) / ctas;
-    *chunk = per * kRankThreads;
-    *n_chunks = static_cast<int>((n + *chunk - 1) / *chunk);
-    if (*n_chunks < 1) *n_chunks = 1;
+    // a chunk is a whole number of CTA-wide rounds, so chunk boundaries are warp-aligned
+    plan->chunk = (rounds + ctas - 1) / ctas * plan->threads;
+    plan->n_chunks = static_cast<int>((n + plan->chunk - 1) / plan->chunk);
+    if (plan->n_chunks < 1) plan->n_chunks = 1;
     return cudaSuccess;
 }
 
 // rows: n_chunks x n_slots uint32 scratch; seq_start: n_slots uint64 scratch.
-cudaError_t launch_assign_seq(const DeviceImage& img, ptype_req* reqs, size_t n, int n_chunks, size_t chunk,
+cudaError_t launch_assign_seq(const DeviceImage& img, const RankPlan& plan, ptype_req* reqs, size_t n,
                               uint32_t* rows, unsigned long long* counters, unsigned long long* seq_start,
                               cudaStream_t stream) {
     const RankTable t = table_of(img);
-    const size_t smem = rank_smem_bytes(img.n_slots);
-    rank_count_kernel<<<n_chunks, kRankThreads, smem, stream>>>(t, reqs, n, chunk, rows);
+    if (plan.staged)
+        rank_count_kernel<true, kStagedThreads><<<plan.n_chunks, kStagedThreads, plan.smem, stream>>>(t, reqs, n, plan.chunk, rows);
+    else
+        rank_count_kernel<false, kProbeThreads><<<plan.n_chunks, kProbeThreads, plan.smem, stream>>>(t, reqs, n, plan.chunk, rows);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    rank_scan_kernel<<<(img.n_slots + kRankThreads - 1) / kRankThreads, kRankThreads, 0, stream>>>(
-        rows, n_chunks, img.n_slots, counters, seq_start);
+    rank_scan_kernel<<<(img.n_slots + 31) / 32, kScanThreads, 0, stream>>>(rows, plan.n_chunks, img.n_slots, counters,
+                                                                          seq_start);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    rank_assign_kernel<<<n_chunks, kRankThreads, smem, stream>>>(t, reqs, n, chunk, rows, seq_start);
+    if (plan.staged)
+        rank_assign_kernel<true, kStagedThreads><<<plan.n_chunks, kStagedThreads, plan.smem, stream>>>(t, reqs, n, plan.chunk, rows,
+                                                                                                   seq_start);
+    else
+        rank_assign_kernel<false, kProbeThreads><<<plan.n_chunks, kProbeThreads, plan.smem, stream>>>(t, reqs, n, plan.chunk, rows,
+                                                                                                  seq_start);
     return cudaGetLastError();
 }
 
@@ -202,7 +422,7 @@ cudaError_t launch_carry_counters(const DeviceImage& from, const unsigned long l
                                   const DeviceImage& to, unsigned long long* to_counters, cudaStream_t stream) {
     cudaError_t e = cudaMemsetAsync(to_counters, 0, static_cast<size_t>(to.n_slots) * sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
-    carry_counters_kernel<<<(from.n_slots + kRankThreads - 1) / kRankThreads, kRankThreads, 0, stream>>>(
+    carry_counters_kernel<<<(from.n_slots + kScanThreads - 1) / kScanThreads, kScanThreads, 0, stream>>>(
         table_of(from), from_counters, table_of(to), to_counters);
     return cudaGetLastError();
 }

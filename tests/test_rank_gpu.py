@@ -201,3 +201,29 @@ def test_tables_beyond_the_histogram_are_refused(oracle):
         with pytest.raises(p.PtypeError):
             ctx.assign_seq(d, 4)
         d.free()
+
+
+@pytest.mark.parametrize("n_slots", [18_000, 19_000, 30_000, 51_200])
+def test_large_tables_either_side_of_the_staging_limit(oracle, n_slots):
+    """Up to ~18 500 slots the keys sit in shared memory beside the histogram; beyond that (to
+    51 200) the table is probed in L2.  Same answers either way."""
+    nodes = [(f"svc{i:04d}", f"n{j}", "h", 1) for i in range(1500) for j in range(1 + i % 2)]
+    spec = w.RegistrySpec(nodes, [], ["idle"], "10.0.0.5", 3)
+    img = p.build_image(spec.nodes, local_addr=spec.local_addr, max_connections=3, declare=spec.declare,
+                        n_slots=n_slots)
+    assert img.header.n_slots == n_slots
+    kv, snap = oracle.snapshot_from_spec(spec, img.salt)
+    rng = np.random.default_rng(n_slots)
+    keys = np.array([p.service_key(f"svc{i:04d}", img.salt) for i in range(1500)] +
+                    [p.service_key("idle", img.salt), p.service_key("nobody", img.salt)], dtype=np.uint64)
+    with p.Context([0]) as ctx:
+        ctx.publish(img)
+        counters = np.zeros(snap.n_clients(), dtype=np.uint64)
+        for n in (100_000, 3):
+            reqs = np.zeros(n, dtype=p.REQ_DTYPE)
+            reqs["svc_key"] = keys[rng.integers(0, len(keys), n)]
+            want = reqs.copy()
+            snap.assign_seq(want, counters)
+            assert device_assign(ctx, reqs).tobytes() == want.tobytes(), (n_slots, n)
+        assert ctx.seq_get("svc0007") == int(counters[snap.client_index("svc0007")]) > 0
+        assert ctx.seq_get("idle") == 0

@@ -9,8 +9,11 @@ from ptype_b200 import workloads as wl  # noqa: E402
 
 
 def main() -> None:
+    only = sys.argv[1] if len(sys.argv) > 1 else None
     for name, spec, make, n in (("c2", wl.calculator_registry(), wl.calculator_calls, 1 << 20),
                                 ("c3", wl.stress_registry(), wl.stress_calls, 1 << 24)):
+        if only and name != only:
+            continue
         image = spec.image(epoch=1)
         with p.Context([0]) as ctx:
             ctx.publish(image)
