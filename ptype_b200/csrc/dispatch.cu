@@ -421,6 +421,37 @@ __device__ __forceinline__ void griddep_launch_dependents() {
 }
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// ---- the LDG kernels' transpose.  Lane L loads 16-byte chunks L, 32+L, 64+L of the warp's 96
+// (three fully coalesced 512-byte requests); record r owns chunks 3r..3r+2.  In round c, lane s
+// feeds the lane whose record needs chunk index == s (mod 32): r = 11*(s-c) mod 32
+// (11 = 3^-1 mod 32), out of its register (3r+c)/32.
+struct TransposePlan {
+    uint32_t send_reg[3];
+};
+__device__ __forceinline__ TransposePlan transpose_plan(uint32_t lane) {
+    TransposePlan p;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const uint32_t r = ((lane - c) * 11u) & 31u;
+        p.send_reg[c] = (3u * r + c) >> 5;
+    }
+    return p;
+}
+// ld[0..2]: what this lane loaded; q[0..2]: the 48-byte record of call (tile, lane).  12 shuffles.
+__device__ __forceinline__ void transpose_tile(const TransposePlan& p, uint32_t lane, const uint4 (&ld)[3],
+                                               uint4 (&q)[3]) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const uint32_t sr = p.send_reg[c];
+        const uint4 snd = sr == 0 ? ld[0] : (sr == 1 ? ld[1] : ld[2]);
+        const uint32_t src = (3u * lane + c) & 31u;
+        q[c].x = __shfl_sync(kFull, snd.x, src);
+        q[c].y = __shfl_sync(kFull, snd.y, src);
+        q[c].z = __shfl_sync(kFull, snd.z, src);
+        q[c].w = __shfl_sync(kFull, snd.w, src);
+    }
+}
+
 // ------------------------------------------------------- kernel, bulk-staged
 //
 // Requests reach shared memory through the bulk-async copy engine: each warp owns a
@@ -528,16 +559,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
 
-    // ---- transpose plan.  Lane L loads 16-byte chunks L, 32+L, 64+L of the warp's 96;
-    // record r owns chunks 3r..3r+2.  In round c, lane s feeds the lane whose record
-    // needs chunk index == s (mod 32): r = 11*(s-c) mod 32 (11 = 3^-1 mod 32), out of its
-    // register (3r+c)/32.
-    uint32_t send_reg[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        const uint32_t r = ((lane - c) * 11u) & 31u;
-        send_reg[c] = (3u * r + c) >> 5;
-    }
+    const TransposePlan plan = transpose_plan(lane);
 
     const size_t n_tiles = (n + 31) >> 5;
     const size_t n_chunks = n * 3;
@@ -568,16 +590,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
             const size_t t = t0 + static_cast<size_t>(u) * total_warps;
             if (t >= n_tiles) break;  // warp-uniform
             uint4 q[3];
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                const uint32_t sr = send_reg[c];
-                const uint4 snd = sr == 0 ? ld[u][0] : (sr == 1 ? ld[u][1] : ld[u][2]);
-                const uint32_t src = (3u * lane + c) & 31u;
-                q[c].x = __shfl_sync(kFull, snd.x, src);
-                q[c].y = __shfl_sync(kFull, snd.y, src);
-                q[c].z = __shfl_sync(kFull, snd.z, src);
-                q[c].w = __shfl_sync(kFull, snd.w, src);
-            }
+            transpose_tile(plan, lane, ld[u], q);
             const size_t idx = (t << 5) + lane;
             const bool live = idx < n;
             uint4 out = make_uint4(0, 0, 0, 0);
@@ -619,12 +632,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
 
-    uint32_t send_reg[3];  // transpose plan, see dispatch_kernel
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        const uint32_t r = ((lane - c) * 11u) & 31u;
-        send_reg[c] = (3u * r + c) >> 5;
-    }
+    const TransposePlan plan = transpose_plan(lane);
     const uint32_t total_tiles = list.tile_end[list.count - 1];
     const uint32_t total_warps = gridDim.x * warps_per_cta;
     const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
@@ -665,16 +673,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         for (int u = 0; u < kUnroll; ++u) {
             if (g0 + u * total_warps >= total_tiles) break;  // warp-uniform
             uint4 q[3];
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                const uint32_t sr = send_reg[c];
-                const uint4 snd = sr == 0 ? ld[u][0] : (sr == 1 ? ld[u][1] : ld[u][2]);
-                const uint32_t src = (3u * lane + c) & 31u;
-                q[c].x = __shfl_sync(kFull, snd.x, src);
-                q[c].y = __shfl_sync(kFull, snd.y, src);
-                q[c].z = __shfl_sync(kFull, snd.z, src);
-                q[c].w = __shfl_sync(kFull, snd.w, src);
-            }
+            transpose_tile(plan, lane, ld[u], q);
             const int b = cursor[u];
             const size_t idx = (static_cast<size_t>(tile[u]) << 5) + lane;
             if (idx < list.n[b])
