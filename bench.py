@@ -448,14 +448,22 @@ def main():
     else:
         e2e_calls = float(len(hb) * e2e_steps)
     e2e_value = e2e_calls / e2e_s
+    records_ok = pin_rep.array.tobytes()
 
     # ---- e2e of ONE Client's batch in compact form (ptype_b200_call_batch): what
     # (*Client).CallBatch submits - arguments plus a method byte per call instead of 48-byte
     # records.  Only for the single-service workloads.
+    # At N > 1 every rank is a host process with its own Client (its own counter, rpc.go:129),
+    # submitting its own batch to its own GPU over its own PCIe link: weak scaling, like `value`.
     e2e_compact = None
-    if args.workload not in ("c3", "c5") and not multi:
+    cb = hb   # the Client batch that is timed
+    if args.workload not in ("c3", "c5"):
         import ptype_b200.workloads as wl
-        key, base, methods, sel, cargs = wl.as_client_batch(hb)
+        if multi:
+            cb = make_workload(args.workload, batch, 0x5EED0100 + rank, image.salt)[1]
+            pin_rep.free()
+            pin_rep = p.PinnedArray(len(cb), p.REPLY_DTYPE)
+        key, base, methods, sel, cargs = wl.as_client_batch(cb)
         pin_args = p.PinnedArray(cargs.size, np.int64)
         pin_args.array[:] = cargs.reshape(-1)
         pa = pin_args.array.reshape(cargs.shape)
@@ -474,12 +482,16 @@ def main():
         barrier()
         c1 = time.perf_counter()
         cs = c1 - c0
+        cb_calls = float(len(cb) * e2e_steps)
         if multi:
-            t = torch.tensor([cs], device="cuda", dtype=torch.float64)
+            t = torch.tensor([cs], device=rdev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             cs = float(t.item())
+            c = torch.tensor([cb_calls], device=rdev, dtype=torch.float64)
+            dist.all_reduce(c, op=dist.ReduceOp.SUM)
+            cb_calls = float(c.item())
         # ... and with the replies CallBatch's caller reads: 8-byte values + the failed list
-        pin_val = p.PinnedArray(len(hb), np.int64)
+        pin_val = p.PinnedArray(len(cb), np.int64)
         for _ in range(3):
             _, vfailed, vcount = ctx.call_batch_values(key, base, methods, pa, ps, pin_val.array,
                                                        failed_cap=1024, flags=args.flags & 4)
@@ -491,14 +503,18 @@ def main():
                                   flags=args.flags & 4)
         barrier()
         vs = time.perf_counter() - v0
-        e2e_values = {"value": e2e_calls / vs, "unit": "calls/s",
+        if multi:
+            t = torch.tensor([vs], device=rdev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            vs = float(t.item())
+        e2e_values = {"value": cb_calls / vs, "unit": "calls/s",
                       "h2d_bytes_per_step": int(cargs.nbytes + (len(sel) if sel is not None else 0)),
-                      "d2h_bytes_per_step": int(len(hb) * 8), "steps": e2e_steps, "failed_calls": int(vcount),
+                      "d2h_bytes_per_step": int(len(cb) * 8), "steps": e2e_steps, "failed_calls": int(vcount),
                       "api": "ptype_b200_call_batch_values(args + method byte in, 8-byte values + failed list "
                              "out, pinned host buffers)"}
-        e2e_compact = {"value": e2e_calls / cs, "unit": "calls/s",
+        e2e_compact = {"value": cb_calls / cs, "unit": "calls/s",
                        "h2d_bytes_per_step": int(cargs.nbytes + (len(sel) if sel is not None else 0)),
-                       "d2h_bytes_per_step": int(len(hb) * 16), "steps": e2e_steps,
+                       "d2h_bytes_per_step": int(len(cb) * 16), "steps": e2e_steps,
                        "api": "ptype_b200_call_batch(one Client's batch: args + method byte per call, "
                               "pinned host buffers)"}
 
@@ -521,12 +537,13 @@ def main():
         kv, snap = ob.snapshot_from_spec(spec, image.salt)
         want = snap.dispatch(hb, check_limit=1 << 16, threads=os.cpu_count() or 1)
         got = d_reps[0].download(p.REPLY_DTYPE, counts[0])
-        if got.tobytes() != want.tobytes() or pin_rep.array.tobytes() != want.tobytes():
+        if got.tobytes() != want.tobytes() or records_ok != want.tobytes():
             raise SystemExit("bench.py: CUDA replies differ from the oracle - number withheld")
-        if e2e_compact is not None and compact_ok != want.tobytes():
+        want_cb = want if cb is hb else snap.dispatch(cb, check_limit=1 << 16, threads=os.cpu_count() or 1)
+        if e2e_compact is not None and compact_ok != want_cb.tobytes():
             raise SystemExit("bench.py: call_batch replies differ from the oracle - number withheld")
-        if e2e_compact is not None and (not np.array_equal(values_ok, want["value"]) or
-                                        vcount != int((want["status"] != 0).sum())):
+        if e2e_compact is not None and (not np.array_equal(values_ok, want_cb["value"]) or
+                                        vcount != int((want_cb["status"] != 0).sum())):
             raise SystemExit("bench.py: call_batch_values differs from the oracle - number withheld")
         if not multi:
             restore_affinity()
