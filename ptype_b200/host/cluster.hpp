@@ -748,6 +748,7 @@ class Client {  // cluster/rpc.go:40-43,126-139
     }
 
     std::vector<Node> getSelectedNodes() { return gpu_->SelectedNodes(service_); }  // rpc.go:293-297
+    uint64_t Seq() const { return seq_.load(); }  // connectionBalancer.seq: the last value drawn
     // Background update failures (rpc.go:122-124,213-218): at most one pending, like chan error, 1.
     std::optional<Error> ConnectionErrs() {
         std::lock_guard<std::mutex> lk(errMu_);

@@ -220,6 +220,57 @@ static void TestClient_first_call_goes_to_index_1() {
     REQUIRE(rep[3].Value == 8);
 }
 
+// TestClient_Call_with_retry_error (rpc_test.go:160-186): one node, the method fails, Retries
+// is 0 in testConnConfig -> one attempt, an error, and the caller's reply is still 0
+static void TestClient_Call_with_retry_error() {
+    Dispatcher gpu("", 3);
+    gpu.Expose("foo", "Prime");
+    MockRegistry mock{fakeNodes(1)};
+    ConnConfig cfg = testConnConfig();
+    REQUIRE(cfg.Retries == 0);
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c));
+    int64_t calls = 0;
+    const int64_t wide[3] = {2, int64_t(1) << 40, int64_t(1) << 41};   // a Check the device refuses to walk
+    Error e = c->Call("Prime.Check", wide, &calls);
+    REQUIRE(e && calls == 0);
+    REQUIRE(c->Seq() == 1);   // the one attempt drew one sequence number
+}
+
+// withRetry (rpc.go:107-116) + roundRobinSelect: every attempt draws the next sequence number,
+// so after a call that failed 1 + Retries times the next call is routed by seq 1 + Retries + 1.
+static void TestClient_retry_draws_a_sequence_number_per_attempt() {
+    Dispatcher gpu("", 3);
+    gpu.Expose("foo", "Calculator");
+    MockRegistry mock{fakeNodes(3)};
+    ConnConfig cfg = testConnConfig();
+    cfg.Retries = 2;
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c));
+    int64_t reply = 0;
+    const int64_t args[3] = {5, 6, 0};
+    REQUIRE(c->Call("Calculator.Nope", args, &reply).msg == "rpc: can't find method Calculator.Nope");
+    REQUIRE(reply == 0 && c->Seq() == 3);
+    BatchReply rep[1];
+    const int64_t one[1][3] = {{5, 6, 0}};
+    REQUIRE(!c->CallBatch("Calculator.Multiply", one, 1, rep));
+    auto sel = c->getSelectedNodes();
+    REQUIRE(sel.size() == 3 && rep[0].Value == 30 && c->Seq() == 4);
+    REQUIRE(gpu.NodeOf(rep[0].NodeId) == sel[4 % 3]);
+}
+
+// TestNewConnectionBalancer_successul_initial_connect (rpc_test.go:293-304)
+static void TestBalancer_successful_initial_connect() {
+    Dispatcher gpu("", 3);
+    auto n = fakeNodes(1);
+    MockRegistry mock{n};
+    ConnConfig cfg = testConnConfig();
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c));
+    REQUIRE((c->getSelectedNodes() == std::vector<Node>{n[0]}));
+    REQUIRE(!c->ConnectionErrs().has_value());
+}
+
 // TestClient_Go / TestClient_Go_with_retry_error (rpc_test.go:188-215,262-292): async call,
 // completion signalled; on failure the call carries the error and the reply stays 0
 static void TestClient_Go() {
@@ -496,6 +547,9 @@ int main(int argc, char** argv) {
         RUN(TestClient_default_conn_config);
         RUN(TestClient_Call);
         RUN(TestClient_first_call_goes_to_index_1);
+        RUN(TestClient_Call_with_retry_error);
+        RUN(TestClient_retry_draws_a_sequence_number_per_attempt);
+        RUN(TestBalancer_successful_initial_connect);
         RUN(TestNewClient_with_no_available_server);
         RUN(TestBalancer_watchForNewNodes);
         RUN(TestBalancer_roundRobinSelect);
