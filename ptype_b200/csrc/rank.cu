@@ -284,12 +284,12 @@ __global__ void __launch_bounds__(kThreads)
     const size_t hi = lo + chunk < n ? lo + chunk : n;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     constexpr size_t kTrip = static_cast<size_t>(kThreads) * kRankDepth;
-    unsigned long long key[kRankDepth], next[kRankDepth];
-    if (lo < hi) load_keys(reqs, lo, hi, next);
     for (size_t base = lo; base < hi; base += kTrip) {  // uniform trip count per CTA
-#pragma unroll
-        for (int r = 0; r < kRankDepth; ++r) key[r] = next[r];
-        if (base + kTrip < hi) load_keys(reqs, base + kTrip, hi, next);
+        // Keys are NOT fetched a trip ahead here: this pass writes into the sector it read the
+        // key from, and the longer that sector waits in L2 the likelier it is gone by then
+        // (ncu: 1.2 GB read for 0.8 GB of records with the prefetch in place).
+        unsigned long long key[kRankDepth];
+        load_keys(reqs, base, hi, key);
         uint32_t at[kRankDepth];
         counted_slots<kStaged>(t, sh, key, base, hi, at);
         unsigned long long start[kRankDepth];  // fetched now, needed after the warps' turns
