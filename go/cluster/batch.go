@@ -217,6 +217,54 @@ func (d *Dispatcher) AssignSeq(dReqs unsafe.Pointer, n int) error {
 		C.ptype_b200_assign_seq(d.ctx, 0, (*C.ptype_req)(dReqs), C.size_t(n), 0))
 }
 
+// MixedCall mirrors ptype_req (48 bytes): one call of a batch that mixes services.  Seq is
+// filled in by CallMixed.
+type MixedCall struct {
+	SvcKey, Seq  uint64
+	Method, Recv uint32
+	A0, A1, A2   int64
+}
+
+// CallMixed issues calls[0], calls[1], ... as the process would through one Client per service,
+// in that order: sequence numbers are drawn on the GPU from each service's own counter
+// (AssignSeq), then the batch is dispatched.  On return calls[j].Seq holds the number drawn
+// (0 for a call that found no client) and replies[j] the outcome.
+func (d *Dispatcher) CallMixed(calls []MixedCall, replies []BatchReply) error {
+	if len(calls) == 0 {
+		return nil
+	}
+	if len(replies) < len(calls) {
+		return errors.New("ptype_b200: replies shorter than calls")
+	}
+	n := C.size_t(len(calls))
+	var dReq, dRep unsafe.Pointer
+	if err := abiError("ptype_b200_device_alloc", C.ptype_b200_device_alloc(d.ctx, 0, n*48, &dReq)); err != nil {
+		return err
+	}
+	defer C.ptype_b200_device_free(d.ctx, 0, dReq)
+	if err := abiError("ptype_b200_device_alloc", C.ptype_b200_device_alloc(d.ctx, 0, n*16, &dRep)); err != nil {
+		return err
+	}
+	defer C.ptype_b200_device_free(d.ctx, 0, dRep)
+	if err := abiError("ptype_b200_memcpy_h2d",
+		C.ptype_b200_memcpy_h2d(d.ctx, 0, dReq, unsafe.Pointer(&calls[0]), n*48)); err != nil {
+		return err
+	}
+	if err := d.AssignSeq(dReq, len(calls)); err != nil {
+		return err
+	}
+	if err := abiError("ptype_b200_dispatch", C.ptype_b200_dispatch(d.ctx, 0, (*C.ptype_req)(dReq), n,
+		(*C.ptype_reply)(dRep), C.PTYPE_F_DEVICE_PTRS)); err != nil {
+		return err
+	}
+	if err := abiError("ptype_b200_memcpy_d2h",
+		C.ptype_b200_memcpy_d2h(d.ctx, 0, unsafe.Pointer(&replies[0]), dRep, n*16)); err != nil {
+		return err
+	}
+	return abiError("ptype_b200_memcpy_d2h",
+		C.ptype_b200_memcpy_d2h(d.ctx, 0, unsafe.Pointer(&calls[0]), dReq, n*48))
+}
+
 // Seq reads a service's counter: the last value drawn.
 func (d *Dispatcher) Seq(service string) (uint64, error) {
 	cs := C.CString(service)
