@@ -420,6 +420,21 @@ def main():
         ms_max, calls_all = ms, float(calls_mine)
     value = calls_all / (ms_max * 1e-3)
 
+    # ---- CUDA events around >= 50 individual launches, median and best.  Outside
+    # the timed region; the events between launches keep consecutive kernels from overlapping, so
+    # this is the duration of one launch on its own, not the pipelined step time above.
+    per_launch = None
+    if not live:
+        pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(64)]
+        for i, (a, b) in enumerate(pairs):
+            a.record(ext)
+            step(i)
+            b.record(ext)
+        barrier()
+        us = sorted(a.elapsed_time(b) * 1e3 for a, b in pairs)
+        per_launch = {"launches": len(us), "median_us": us[len(us) // 2], "best_us": us[0],
+                      "what": "one dispatch launch per batch, CUDA events around each (rank 0's GPU)"}
+
     # ---- e2e: the C-ABI call a host makes, pinned HOST buffers, copies inside the timing
     hb = host_batches[0]
     pin_req = p.PinnedArray(len(hb), p.REQ_DTYPE)
@@ -599,6 +614,7 @@ def main():
             "e2e_reply_records": e2e_compact,
             "e2e_records": e2e_records,
             "gpu_launches": int(launches),
+            "per_launch": per_launch,
             "host_enqueue_us_per_step": host_enqueue_s / args.steps * 1e6,
             "clocks": clocks,
         }
