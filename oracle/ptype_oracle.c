@@ -699,14 +699,18 @@ typedef struct {
     uint32_t* selected; /* global node ids: getSelectedNodes() */
     uint32_t k;
     uint32_t receivers; /* PO_RECV_* bits */
+    uint32_t created;   /* position before the sort by key (build-time bookkeeping) */
 } po_client;
 
 #define PO_MAX_METHODS 8
 struct po_snapshot {
     uint32_t method_hash[PO_MAX_METHODS]; /* FNV-1a-32("Recv.Method"), hashed once per snapshot */
     uint32_t recv_hash[PO_MAX_METHODS];   /* FNV-1a-32("Recv") */
-    po_client* clients; /* sorted by key for bsearch */
+    po_client* clients; /* sorted by key */
     size_t n_clients;
+    uint32_t* index;    /* open-addressing hash over clients[].key: the Go side of this lookup is
+                         * a map from service name to *Client, i.e. a hash table */
+    size_t index_mask;
     po_node* nodes; /* global node array, in `services` range order */
     uint32_t* node_service;
     size_t n_nodes;
@@ -787,19 +791,23 @@ po_snapshot* po_snapshot_build(const po_kv* kv, const char* local_addr, int64_t 
         po_select_nodes(local_addr, c->n_nodes, max_connections, c->selected, (size_t)k);
         for (long i = 0; i < k; i++) c->selected[i] += c->node_base;
     }
-    /* node_service indexes clients by creation order; remember names before sorting */
-    char(*names)[256] = (char(*)[256])calloc(s->n_clients ? s->n_clients : 1, 256);
-    for (size_t j = 0; j < s->n_clients; j++) strcpy(names[j], s->clients[j].name);
+    /* node_service indexes clients by creation order; renumber after the sort by key */
+    for (size_t j = 0; j < s->n_clients; j++) s->clients[j].created = (uint32_t)j;
     qsort(s->clients, s->n_clients, sizeof(po_client), po_client_cmp);
-    for (size_t i = 0; i < s->n_nodes; i++) {
-        const char* nm = names[s->node_service[i]];
-        for (size_t j = 0; j < s->n_clients; j++)
-            if (!strcmp(s->clients[j].name, nm)) {
-                s->node_service[i] = (uint32_t)j;
-                break;
-            }
+    uint32_t* now_at = (uint32_t*)calloc(s->n_clients ? s->n_clients : 1, sizeof(uint32_t));
+    for (size_t j = 0; j < s->n_clients; j++) now_at[s->clients[j].created] = (uint32_t)j;
+    for (size_t i = 0; i < s->n_nodes; i++) s->node_service[i] = now_at[s->node_service[i]];
+    free(now_at);
+    /* hash index, at most half full, linear probing; entries are client positions + 1 */
+    size_t cap = 16;
+    while (cap < 2 * s->n_clients) cap <<= 1;
+    s->index = (uint32_t*)calloc(cap, sizeof(uint32_t));
+    s->index_mask = cap - 1;
+    for (size_t j = 0; j < s->n_clients; j++) {
+        size_t h = (size_t)((s->clients[j].key * 0x9E3779B97F4A7C15ull) >> 20) & s->index_mask;
+        while (s->index[h]) h = (h + 1) & s->index_mask;
+        s->index[h] = (uint32_t)j + 1;
     }
-    free(names);
     po_snapshot_hash_methods(s);
     return s;
 }
@@ -808,6 +816,7 @@ void po_snapshot_free(po_snapshot* s) {
     if (!s) return;
     for (size_t j = 0; j < s->n_clients; j++) free(s->clients[j].selected);
     free(s->clients);
+    free(s->index);
     free(s->nodes);
     free(s->node_service);
     free(s);
@@ -820,15 +829,9 @@ static po_client* po_find_name(const po_snapshot* s, const char* service) {
 }
 
 static const po_client* po_find_key(const po_snapshot* s, uint64_t key) {
-    size_t lo = 0, hi = s->n_clients;
-    while (lo < hi) {
-        size_t mid = (lo + hi) / 2;
-        if (s->clients[mid].key < key)
-            lo = mid + 1;
-        else
-            hi = mid;
-    }
-    if (lo < s->n_clients && s->clients[lo].key == key) return &s->clients[lo];
+    size_t h = (size_t)((key * 0x9E3779B97F4A7C15ull) >> 20) & s->index_mask;
+    for (uint32_t e; (e = s->index[h]) != 0; h = (h + 1) & s->index_mask)
+        if (s->clients[e - 1].key == key) return &s->clients[e - 1];
     return NULL;
 }
 
