@@ -9,20 +9,27 @@ ncclBroadcast (inside the library); the data path has no collective ("scaling": 
 Barriers and the max-over-ranks reduction of the device times use a gloo group.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
-                    [--workload c2|c2mesh|c3|c4]
+                    [--workload c2|c2mesh|c3|c4|c5] [--no-extras]
 
 `value`     calls/s with batches resident in HBM (CUDA events on the library's stream).
 `e2e`       calls/s through the C ABI with pinned HOST buffers, H2D/D2H inside the timing.
 `roofline`  64 algorithmic bytes per call / average launch duration vs measured HBM peak.
+`parity`    every rank's reply buffers, checksummed on the device (order-independent 64-bit
+            checksum), compared with the oracle's replies for the same shard; a mismatch on
+            any rank withholds the number (exit status 1).
+`extras`    short runs of the other single-GPU configs (C3, C4, C5) under the same rules, so
+            that the default line carries them; at N>1 a C5 segment (live snapshot updates).
 `cpu_baseline` the CPU oracle (a C port of the reference's path; Go itself cannot run on
             this image) on the box's host cores, bounded sample.
---impl reference times that same CPU port as the reference arm.
+--impl reference times that same CPU port as the reference arm; that arm imports nothing of
+the product (workloads.py and oracle/ only).
 """
 from __future__ import annotations
 
 import argparse
 import json
 import os
+import subprocess
 import sys
 import threading
 import time
@@ -34,10 +41,10 @@ ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
 BYTES_PER_CALL = 64  # 48 B request + 16 B reply
-BATCH = 1 << 20
 # calls per step (per GPU) and resident batches rotated, per workload: C3 is quoted on 16M calls
 BATCH_OF = {"c2": 1 << 20, "c2mesh": 1 << 20, "c3": 1 << 24, "c4": 1 << 20, "c5": 1 << 20}
 BUFFERS_OF = {"c2": 8, "c2mesh": 8, "c3": 2, "c4": 8, "c5": 8}
+U64 = (1 << 64) - 1
 
 
 def measured_peak():
@@ -51,7 +58,8 @@ def measured_peak():
 
 
 def make_workload(name: str, n: int, seed: int, salt: int = 0):
-    import ptype_b200.workloads as w
+    """(registry spec, call stream) of a BASELINE config.  Pure numpy: no product code."""
+    import workloads as w
     if name == "c2":
         return w.calculator_registry(), w.calculator_calls(n, seed=seed, salt=salt)
     if name == "c2mesh":
@@ -71,6 +79,13 @@ WORKLOAD_TEXT = {
     "c5": "sharded stream over the 10k x 64 registry, 2^20 routed calls per GPU per step, live registry "
           "snapshot updates (one node leaves or joins) broadcast to every GPU between batches",
 }
+
+
+def common_config(workload: str, batch: int, nbuf: int) -> dict:
+    """The `config` object: the same keys and values in both arms for the same arguments."""
+    return {"workload": WORKLOAD_TEXT[workload], "batch_calls_per_gpu": int(batch), "resident_batches": int(nbuf),
+            "l2": f"{nbuf} distinct batches rotated: {nbuf * batch * BYTES_PER_CALL / 1e6:.0f} MB working set "
+                  f"> 126 MB L2"}
 
 
 class ClockSampler(threading.Thread):
@@ -204,25 +219,47 @@ def loopback_rate(reqs, callers: int, calls_per_caller: int, k: int, receivers: 
                     "flight per Client); the Go runtime itself is not restated"}
 
 
+def in_tree_libs():
+    """Shared objects of this repository mapped into the process (evidence of what an arm ran)."""
+    try:
+        maps = Path("/proc/self/maps").read_text()
+    except OSError:
+        return None
+    return sorted({ln.split()[-1][len(str(ROOT)) + 1:] for ln in maps.splitlines()
+                   if ln.rstrip().endswith(".so") and str(ROOT) in ln})
+
+
+GO_NOTE = ("Go reference path not run - no Go toolchain on this image; C port of cluster/rpc.go + registry.go + "
+           "example method bodies, in-process")
+
+
 def run_reference(args, rank: int):
     """Reference arm: the reference's own path restated on the CPU (oracle port), all host
-    threads, same config/metric.  Go itself cannot run here (no toolchain on this image)."""
+    threads, same config/metric.  Go itself cannot run here (no toolchain on this image).
+    Nothing of the product is imported: inputs come from workloads.py, replies from oracle/."""
     if rank != 0:
         return
-    spec, reqs = make_workload(args.workload, args.batch or BATCH_OF[args.workload], 0x5EED0002)
     from oracle import binding as ob
+    batch = args.batch or BATCH_OF[args.workload]
+    nbuf = args.buffers or BUFFERS_OF[args.workload]
+    spec, _ = make_workload(args.workload, 32, 1)
+    batches = [make_workload(args.workload, batch, 0x5EED0002 + b)[1] for b in range(nbuf)]
     kv, snap = ob.snapshot_from_spec(spec)
     threads = os.cpu_count() or 1
-    rep = np.empty(len(reqs), dtype=ob.REPLY_DTYPE)
-    for _ in range(args.warmup):
-        snap.dispatch_into(reqs, rep, 1 << 16, threads)
+    rep = np.empty(max(len(b) for b in batches), dtype=ob.REPLY_DTYPE)
+    for i in range(args.warmup):
+        snap.dispatch_into(batches[i % nbuf], rep[:len(batches[i % nbuf])], 1 << 16, threads)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        snap.dispatch_into(reqs, rep, 1 << 16, threads)
+    calls = 0
+    for i in range(args.steps):
+        q = batches[i % nbuf]
+        snap.dispatch_into(q, rep[:len(q)], 1 << 16, threads)
+        calls += len(q)
     el = time.perf_counter() - t0
-    value = args.steps * len(reqs) / el
+    value = calls / el
+    reqs = batches[0]
     k = len(snap.selected("prime_worker" if args.workload == "c4" else "calculator") or [0]) \
-        if args.workload != "c3" else 3
+        if args.workload not in ("c3", "c5") else 3
     lb1 = loopback_rate(reqs, 1, min(len(reqs), 30_000), k, 2 if args.workload == "c4" else 1)
     lbn = loopback_rate(reqs, threads, min(len(reqs) // threads, 20_000), k, 2 if args.workload == "c4" else 1)
     line = {
@@ -230,18 +267,401 @@ def run_reference(args, rank: int):
         "unit": "calls/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": el / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-        "config": {"workload": WORKLOAD_TEXT[args.workload], "batch_calls": len(reqs),
-                   "note": "Go reference path not run - no Go toolchain on this image; C port of "
-                           "cluster/rpc.go + registry.go + example method bodies, in-process"},
+        "config": common_config(args.workload, batch, nbuf),
+        "note": GO_NOTE,
         "cpu_baseline": {"value": value, "unit": "calls/s", "cores": threads, "kind": "port",
-                         "sample": f"{args.steps} passes over one {len(reqs)}-call batch",
+                         "sample": f"{args.steps} passes, each over one of {nbuf} rotated {batch}-call batches",
                          "what": "in-process C port of the path's algorithm, no transport: the fastest CPU "
                                  "form, used for `value`"},
         "loopback_1_caller": lb1, "loopback_all_threads": lbn,
         "e2e": {"value": value, "unit": "calls/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "in_tree_libs_loaded": in_tree_libs(),
     }
     print(json.dumps(line), flush=True)
+
+
+class Env:
+    """Process-level plumbing of one rank: torch (device memory, events), gloo (barriers, reductions)."""
+
+    def __init__(self, rank, local_rank, world, torch, dist, pkg, torch_nccl):
+        self.rank, self.local_rank, self.world = rank, local_rank, world
+        self.torch, self.dist, self.p = torch, dist, pkg
+        self.multi = world > 1
+        self.rdev = "cuda" if torch_nccl else "cpu"
+
+    def barrier(self, ctx):
+        if self.multi:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+        ctx.sync()
+
+    def reduce(self, x: float, op: str) -> float:
+        if not self.multi:
+            return float(x)
+        t = self.torch.tensor([x], device=self.rdev, dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def gather(self, obj):
+        """Every rank's object, in rank order, on every rank."""
+        if not self.multi:
+            return [obj]
+        out = [None] * self.world
+        self.dist.all_gather_object(out, obj)
+        return out
+
+
+def measure(ctx, env, workload: str, *, steps: int, warmup: int, nbuf: int, batch: int, flags: int = 0,
+            update_every: int = 64, update_mode: str = "image", per_launch: bool = False,
+            parity_epochs: int = 2) -> dict:
+    """Install the workload's registry on every GPU, keep `nbuf` batches resident, warm every kernel
+    that the timed region launches, time `steps` steps with CUDA events, then check every rank's
+    replies against the oracle through the device-side checksum."""
+    import workloads as wl
+    from ptype_b200.sharding import shard_of
+    p, torch, rank, world, multi = env.p, env.torch, env.rank, env.world, env.multi
+    ob = None
+    if rank == 0:
+        from oracle import binding as ob   # the checker: rank 0 only, never on the timed path
+
+    spec, _ = make_workload(workload, 32, 1)
+    live = workload == "c5"
+    builder = None
+    if live and rank == 0:   # a builder kept alive: each update changes one key and re-emits
+        builder = p.ImageBuilder(spec.local_addr, spec.max_connections)
+        for svc, node, addr, port in spec.nodes:
+            builder.register(svc, node, addr, port)
+        for svc, recv in spec.expose:
+            builder.expose(svc, recv)
+        builder.set_device_only(True)
+    epoch = [1]
+    first_image = (builder.finish(1) if live else spec.image(epoch=1)) if rank == 0 or not multi else None
+    if multi:
+        image = ctx.broadcast_image(first_image, root=0)
+    else:
+        image = first_image
+        ctx.publish(image)
+    live_nodes = {(x[0], x[1]): x for x in spec.nodes} if live else {}
+    live_rng = np.random.default_rng(0x5EED0005)
+    update_ms = []
+
+    def live_update():
+        """One registry change on rank 0 (a random node leaves, or a departed one returns), a new
+        device-only image, and its installation on every GPU: ncclBroadcast, or publish on 1 GPU."""
+        t0 = time.perf_counter()
+        epoch[0] += 1
+        img = None
+        # every rank draws the same event (same seed), like every host seeing the same etcd watch
+        svc = f"svc_{int(live_rng.integers(0, 10_000)):05d}"
+        node = f"node_{int(live_rng.integers(0, 64)):02d}"
+        leaving = (svc, node) in live_nodes
+        if leaving:
+            del live_nodes[(svc, node)]
+        else:
+            live_nodes[(svc, node)] = (svc, node, "10.99.0.1", 9000)
+        if update_mode == "delta":
+            ctx.update_service(svc, -1 if leaving else +1)
+            update_ms.append((time.perf_counter() - t0) * 1e3)
+            return
+        if rank == 0:
+            if leaving:
+                builder.unregister(svc, node)
+            else:
+                builder.register(svc, node, "10.99.0.1", 9000)
+            img = builder.finish(epoch[0])
+        if multi:
+            ctx.broadcast_image(img, root=0)
+        else:
+            ctx.publish(img)
+        update_ms.append((time.perf_counter() - t0) * 1e3)
+
+    def oracle_snapshot():
+        now = spec if not live else wl.RegistrySpec(sorted(live_nodes.values()), spec.expose, [],
+                                                    spec.local_addr, spec.max_connections)
+        return ob.snapshot_from_spec(now, image.salt)
+
+    threads = os.cpu_count() or 1
+    # ---- per-rank shard of each step's global stream, `nbuf` distinct steps resident in HBM
+    d_reqs, d_reps, counts, hb = [], [], [], None
+    expected, streams, owners_of, want0 = [], [], [], None
+    snap = oracle_snapshot()[1] if rank == 0 and not live else None
+    for b in range(nbuf):
+        _, stream = make_workload(workload, batch * world, 0x5EED0002 + b, image.salt)
+        owners = shard_of(np.arange(len(stream), dtype=np.uint64), world) if multi else None
+        mine = stream[owners == rank] if multi else stream
+        if b == 0:
+            hb = mine
+        counts.append(len(mine))
+        d_reqs.append(ctx.device_buffer(len(mine) * 48).upload(mine))
+        d_reps.append(ctx.device_buffer(len(mine) * 16))
+        if rank == 0 and not live:
+            want = snap.dispatch(stream, check_limit=1 << 16, threads=threads)
+            expected.append([ob.reply_checksum(want[owners == r] if multi else want) for r in range(world)])
+            if b == 0:
+                want0 = want[owners == 0] if multi else want
+        elif rank == 0:
+            streams.append(stream)
+            owners_of.append(owners)
+    stream_ptr = ctx.stream()
+    ext = torch.cuda.ExternalStream(stream_ptr, device=torch.device("cuda", env.local_rank))
+
+    def step(i: int):
+        b = i % nbuf
+        ctx.dispatch_device(d_reqs[b], counts[b], d_reps[b], flags=flags, sync=False)
+
+    def batches_of(lo: int, hi: int):
+        return ctx.make_batches((d_reqs[i % nbuf], d_reps[i % nbuf], counts[i % nbuf]) for i in range(lo, hi))
+
+    # the K timed steps are submitted by C calls (ptype_b200_dispatch_batches): no Python between launches
+    every = max(update_every, 1)
+
+    def run_steps(k: int):
+        if not live:
+            ctx.dispatch_batches(batches_of(0, k), flags=flags, sync=False)
+            return
+        for lo in range(0, k, every):
+            ctx.dispatch_batches(batches_of(lo, min(lo + every, k)), flags=flags, sync=False)
+            if lo + every < k:
+                live_update()
+
+    # ---- warm-up: W single steps, then one pass of exactly what is timed (same kernel instances,
+    # same launch shapes; for C5 the update path too), so no first-use cost lands between the events
+    for i in range(max(warmup, 3)):
+        step(i)
+    if live:
+        live_update()
+    run_steps(steps if not live else min(steps, 2 * every + 1))
+    env.barrier(ctx)
+    update_ms.clear()
+    # A short pre-roll keeps the GPU busy while the host enqueues the start event and the first
+    # timed launch: the timed region then starts when the pre-roll ends, not after a host launch
+    # latency on an idle GPU.  (The event between the two launches keeps them from overlapping.)
+    ctx.dispatch_batches(batches_of(0, min(8, steps)), flags=flags, sync=False)
+    launches0 = ctx.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    w0 = time.perf_counter()
+    ev0.record(ext)
+    run_steps(steps)
+    host_enqueue_s = time.perf_counter() - w0
+    ev1.record(ext)
+    env.barrier(ctx)
+    w1 = time.perf_counter()
+    launches = ctx.launch_count() - launches0
+    ms = ev0.elapsed_time(ev1)
+    calls_mine = sum(counts[i % nbuf] for i in range(steps))
+    ms_max = env.reduce(ms, "max")
+    calls_all = env.reduce(float(calls_mine), "sum")
+
+    # ---- SURVEY.md 8d: CUDA events around >= 50 individual launches, median and best.  Outside
+    # the timed region; the events between launches keep consecutive kernels from overlapping, so
+    # this is the duration of one launch on its own, not the pipelined step time above.
+    lone = None
+    if per_launch and not live:
+        pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(64)]
+        for i, (a, b) in enumerate(pairs):
+            a.record(ext)
+            step(i)
+            b.record(ext)
+        env.barrier(ctx)
+        us = sorted(a.elapsed_time(b) * 1e3 for a, b in pairs)
+        lone = {"launches": len(us), "median_us": us[len(us) // 2], "best_us": us[0],
+                "what": "one dispatch launch per batch, CUDA events around each (rank 0's GPU)"}
+
+    # ---- parity on EVERY rank: device-side checksum of each reply buffer vs the oracle's replies
+    # for that rank's shard (rank 0 holds the oracle; the sums travel over gloo)
+    checked = min(nbuf, steps)
+    parity = {"ranks": world, "buffers_per_rank": checked, "checksum_ok": True, "mismatches": []}
+
+    def compare(sums_by_rank, want_of):
+        for r in range(world):
+            for b in range(checked):
+                if sums_by_rank[r][b] != want_of(b, r):
+                    parity["checksum_ok"] = False
+                    parity["mismatches"].append({"rank": r, "buffer": b})
+
+    if not live:
+        sums = env.gather([ctx.reply_checksum(d_reps[b], counts[b], device=True) for b in range(checked)])
+        if rank == 0:
+            compare(sums, lambda b, r: expected[b][r])
+            got0 = d_reps[0].download(p.REPLY_DTYPE, counts[0])
+            parity["rank0_buffer0_bytes_equal"] = bool(got0.tobytes() == want0.tobytes())
+            parity["checksum_ok"] = parity["checksum_ok"] and parity["rank0_buffer0_bytes_equal"]
+    else:
+        # the registry keeps changing: replay `parity_epochs` more segments, one pass over the
+        # resident batches each, and compare each against the oracle's view of the registry as it
+        # stands in that epoch (untimed; same kernels, same update path as the timed region)
+        parity["epochs_checked"] = parity_epochs
+        for _ in range(parity_epochs):
+            live_update()
+            ctx.dispatch_batches(batches_of(0, checked), flags=flags, sync=True)
+            sums = env.gather([ctx.reply_checksum(d_reps[b], counts[b], device=True) for b in range(checked)])
+            if rank == 0:
+                snap_now = oracle_snapshot()[1]
+                wants = [snap_now.dispatch(streams[b], check_limit=1 << 16, threads=threads) for b in range(checked)]
+                compare(sums, lambda b, r: ob.reply_checksum(wants[b][owners_of[b] == r] if multi else wants[b]))
+    ok = env.gather(parity["checksum_ok"] if rank == 0 else None)[0]
+    for buf in d_reqs + d_reps:
+        buf.free()
+    launch_s = (ms_max * 1e-3) / steps
+    per_launch_calls = calls_all / world / steps
+    peak, peak_kind = measured_peak()
+    achieved = per_launch_calls * BYTES_PER_CALL / launch_s / 1e9
+    out = {"workload": workload, "value": calls_all / (ms_max * 1e-3), "ms_max": ms_max, "steps": steps,
+           "launches": int(launches), "host_enqueue_s": host_enqueue_s, "calls_all": calls_all,
+           "per_launch_calls": per_launch_calls, "achieved_gbs": achieved, "peak": peak, "peak_kind": peak_kind,
+           "parity": parity, "parity_ok": bool(ok), "window": (w0, w1), "lone": lone, "hb": hb, "image": image,
+           "spec": spec, "nbuf": nbuf, "batch": batch}
+    if live:
+        out["live_updates"] = {"count": len(update_ms), "every_steps": update_every,
+                               "host_ms_avg": float(np.mean(update_ms)) if update_ms else None,
+                               "transport": "on-device patch of the table (update_service)"
+                               if update_mode == "delta" else
+                               ("rebuilt image, ncclBroadcast" if multi else "rebuilt image, publish")}
+    return out
+
+
+def extra_summary(m: dict) -> dict:
+    """A sub-run as it appears under `extras` in the JSON line."""
+    s = {"workload": WORKLOAD_TEXT[m["workload"]], "value": m["value"], "unit": "calls/s", "steps": m["steps"],
+         "ms_per_step": m["ms_max"] / m["steps"], "batch_calls_per_gpu": m["batch"], "resident_batches": m["nbuf"],
+         "roofline_frac": m["achieved_gbs"] / m["peak"], "achieved_gbs": m["achieved_gbs"],
+         "gpu_launches": m["launches"], "parity": m["parity"]}
+    if "live_updates" in m:
+        s["live_updates"] = m["live_updates"]
+    return s
+
+
+def measure_e2e(ctx, env, args, m: dict) -> dict:
+    """End to end through the C-ABI calls a host makes: pinned HOST buffers in, host buffers out,
+    the copies inside the timed region.  Three forms: 48-byte records (ptype_b200_dispatch), one
+    Client's compact batch with 16-byte replies (call_batch) and with 8-byte values + failed list
+    (call_batch_values - what the CallBatch mirrors call).  Every result is compared with the oracle."""
+    import workloads as wl
+    p, rank, multi = env.p, env.rank, env.multi
+    hb, image, spec, workload, batch = m["hb"], m["image"], m["spec"], m["workload"], m["batch"]
+    flags = args.flags
+    pin_req = p.PinnedArray(len(hb), p.REQ_DTYPE)
+    pin_rep = p.PinnedArray(len(hb), p.REPLY_DTYPE)
+    pin_req.array[:] = hb
+    for _ in range(3):
+        ctx.dispatch(pin_req.array, pin_rep.array, flags=flags)
+    t0 = time.perf_counter()
+    ctx.dispatch(pin_req.array, pin_rep.array, flags=flags)
+    one = time.perf_counter() - t0
+    e2e_steps = args.e2e_steps or max(5, min(2000, int(1.0 / max(one, 1e-6))))
+    env.barrier(ctx)
+    e0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ctx.dispatch(pin_req.array, pin_rep.array, flags=flags)
+    env.barrier(ctx)
+    e1 = time.perf_counter()
+    e2e_s = env.reduce(e1 - e0, "max")
+    e2e_calls = env.reduce(float(len(hb) * e2e_steps), "sum")
+    records_bytes = pin_rep.array.tobytes()
+    out = {"window": (e0, e1), "steps": e2e_steps,
+           "records": {"value": e2e_calls / e2e_s, "unit": "calls/s", "h2d_bytes_per_step": int(len(hb) * 48),
+                       "d2h_bytes_per_step": int(len(hb) * 16), "steps": e2e_steps,
+                       "api": "ptype_b200_dispatch(host pinned 48-byte records -> host pinned replies)"},
+           "compact": None, "values": None}
+
+    # ---- ONE Client's batch in compact form: what (*Client).CallBatch submits - arguments plus a
+    # method byte per call instead of 48-byte records.  Only for the single-service workloads.
+    # At N > 1 every rank is a host process with its own Client (its own counter, rpc.go:129),
+    # submitting its own batch to its own GPU over its own PCIe link: weak scaling, like `value`.
+    cb = hb
+    compact_bytes = values_got = vcount = None
+    if workload not in ("c3", "c5"):
+        if multi:
+            cb = make_workload(workload, batch, 0x5EED0100 + rank, image.salt)[1]
+            pin_rep.free()
+            pin_rep = p.PinnedArray(len(cb), p.REPLY_DTYPE)
+        key, base, methods, sel, cargs = wl.as_client_batch(cb)
+        pin_args = p.PinnedArray(cargs.size, np.int64)
+        pin_args.array[:] = cargs.reshape(-1)
+        pa = pin_args.array.reshape(cargs.shape)
+        pin_sel = None
+        if sel is not None:
+            pin_sel = p.PinnedArray(len(sel), np.uint8)
+            pin_sel.array[:] = sel
+        ps = pin_sel.array if pin_sel is not None else None
+        h2d = int(cargs.nbytes + (len(sel) if sel is not None else 0))
+        for _ in range(3):
+            ctx.call_batch(key, base, methods, pa, ps, pin_rep.array, flags=flags & 4)
+        compact_bytes = pin_rep.array.tobytes()
+        env.barrier(ctx)
+        c0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            ctx.call_batch(key, base, methods, pa, ps, pin_rep.array, flags=flags & 4)
+        env.barrier(ctx)
+        cs = env.reduce(time.perf_counter() - c0, "max")
+        cb_calls = env.reduce(float(len(cb) * e2e_steps), "sum")
+        # ... and with the replies CallBatch's caller reads: 8-byte values + the failed list
+        pin_val = p.PinnedArray(len(cb), np.int64)
+        for _ in range(3):
+            _, _, vcount = ctx.call_batch_values(key, base, methods, pa, ps, pin_val.array,
+                                                 failed_cap=1024, flags=flags & 4)
+        values_got = pin_val.array.copy()
+        env.barrier(ctx)
+        v0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            ctx.call_batch_values(key, base, methods, pa, ps, pin_val.array, failed_cap=1024, flags=flags & 4)
+        env.barrier(ctx)
+        vs = env.reduce(time.perf_counter() - v0, "max")
+        out["values"] = {"value": cb_calls / vs, "unit": "calls/s", "h2d_bytes_per_step": h2d,
+                         "d2h_bytes_per_step": int(len(cb) * 8), "steps": e2e_steps, "failed_calls": int(vcount),
+                         "api": "ptype_b200_call_batch_values(args + method byte in, 8-byte values + failed list "
+                                "out, pinned host buffers)"}
+        out["compact"] = {"value": cb_calls / cs, "unit": "calls/s", "h2d_bytes_per_step": h2d,
+                          "d2h_bytes_per_step": int(len(cb) * 16), "steps": e2e_steps,
+                          "api": "ptype_b200_call_batch(one Client's batch: args + method byte per call, "
+                                 "pinned host buffers)"}
+        pin_args.free()
+        pin_val.free()
+        if pin_sel is not None:
+            pin_sel.free()
+    pin_req.free()
+    pin_rep.free()
+
+    # ---- every rank checks what its host-buffer calls returned (each rank's Client has its own batch)
+    from oracle import binding as ob
+    kv, snap = ob.snapshot_from_spec(spec, image.salt)
+    threads = max(1, (os.cpu_count() or 1) // env.world)
+    want = snap.dispatch(hb, check_limit=1 << 16, threads=threads)
+    good = records_bytes == want.tobytes()
+    if compact_bytes is not None:
+        want_cb = want if cb is hb else snap.dispatch(cb, check_limit=1 << 16, threads=threads)
+        good = good and compact_bytes == want_cb.tobytes() and np.array_equal(values_got, want_cb["value"]) \
+            and vcount == int((want_cb["status"] != 0).sum())
+    out["parity_ok"] = all(env.gather(bool(good)))
+    return out
+
+
+def mirror_e2e(env, args, workload: str, batch: int, steps: int):
+    """End to end through the C++ mirror of the reference's Client (ptype_b200/host/cluster.hpp):
+    tools/ptype_b200_bench drives cluster::Client::CallBatch - argument marshalling, sequence
+    reservation, the C-ABI call and reply unpacking inside the timing - one process per GPU."""
+    tool = ROOT / "tools" / "ptype_b200_bench"
+    if workload not in ("c2", "c2mesh") or not tool.exists():
+        return None
+    cmd = [str(tool), "mirror", str(batch), str(steps), str(env.local_rank), "1" if workload == "c2mesh" else "0"]
+    if env.multi:
+        env.dist.barrier()
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        kv = dict(zip(r.stdout.split()[0::2], r.stdout.split()[1::2])) if r.returncode == 0 else {}
+    except Exception:
+        kv = {}
+    secs = float(kv.get("seconds", 0.0))
+    calls = float(kv.get("calls", 0.0))
+    all_ok = all(env.gather(bool(kv) and kv.get("parity") == "ok"))
+    secs_max, calls_all = env.reduce(secs, "max"), env.reduce(calls, "sum")
+    if not all_ok or secs_max <= 0:
+        return {"value": None, "error": "tools/ptype_b200_bench mirror failed or its replies were wrong"}
+    return {"value": calls_all / secs_max, "unit": "calls/s", "steps": steps,
+            "h2d_bytes_per_step": int(float(kv.get("h2d_bytes_per_step", 0))),
+            "d2h_bytes_per_step": int(float(kv.get("d2h_bytes_per_step", 0))),
+            "api": "cluster::Client::CallBatch (C++ mirror of cluster/rpc.go:59-67) -> ptype_b200_call_batch_values"}
 
 
 def main():
@@ -260,6 +680,8 @@ def main():
     ap.add_argument("--update-mode", default="image", choices=["image", "delta"],
                     help="c5: 'image' rebuilds the snapshot on rank 0 and broadcasts it (NCCL); 'delta' has "
                          "every rank apply the same watch event to its table on the device")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the short C3/C4/C5 sub-runs the default (c2) line carries")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -273,13 +695,13 @@ def main():
     import torch
     import torch.distributed as dist
     import ptype_b200 as p
-    from ptype_b200.sharding import shard_indices
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the dispatch path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     bind_to_gpu_numa_node(local_rank)
     multi = world > 1
+    torch_nccl = os.environ.get("PTYPE_BENCH_TORCH_NCCL") == "1"
     if multi:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # Host-side plumbing (barriers, the max over ranks of the device times, the NCCL id) goes
@@ -288,297 +710,75 @@ def main():
         # enabled by torch's NCCL init) the same HBM-bound kernel ran 12.1 us per step instead of
         # 9.5 us on every rank (measured at N=2; NCCL_P2P_DISABLE=1 restored 9.7 us).
         # PTYPE_BENCH_TORCH_NCCL=1 reproduces that.
-        if os.environ.get("PTYPE_BENCH_TORCH_NCCL") == "1":
+        if torch_nccl:
             dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         else:
             dist.init_process_group("gloo")
+    env = Env(rank, local_rank, world, torch, dist, p, torch_nccl)
 
     sampler = ClockSampler(local_rank)
     sampler.start()
 
     ctx = p.Context([local_rank])
-    # ---- registry snapshot: built on rank 0, replicated to every GPU over NCCL
-    spec, _ = make_workload(args.workload, 32, 1)
-    live = args.workload == "c5"
-    builder = None
-    if live and rank == 0:   # a builder kept alive: each update changes one key and re-emits
-        builder = p.ImageBuilder(spec.local_addr, spec.max_connections)
-        for svc, node, addr, port in spec.nodes:
-            builder.register(svc, node, addr, port)
-        for svc, recv in spec.expose:
-            builder.expose(svc, recv)
-        builder.set_device_only(True)
-    first_image = (builder.finish(1) if live else spec.image(epoch=1)) if rank == 0 or not multi else None
-    torch_nccl = os.environ.get("PTYPE_BENCH_TORCH_NCCL") == "1"
     if multi:
         ids = [p.Context.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         ctx.comm_init(ids[0], rank, world)
-        image = ctx.broadcast_image(first_image, root=0)
-    else:
-        image = first_image
-        ctx.publish(image)
-    live_nodes = {(x[0], x[1]): x for x in spec.nodes} if live else {}
-    live_rng = np.random.default_rng(0x5EED0005)
-    update_ms = []
 
-    def live_update(epoch: int):
-        """One registry change on rank 0 (a random node leaves, or a departed one returns), a new
-        device-only image, and its installation on every GPU: ncclBroadcast, or publish on 1 GPU."""
-        t0 = time.perf_counter()
-        img = None
-        # every rank draws the same event (same seed), like every host seeing the same etcd watch
-        svc = f"svc_{int(live_rng.integers(0, 10_000)):05d}"
-        node = f"node_{int(live_rng.integers(0, 64)):02d}"
-        leaving = (svc, node) in live_nodes
-        if leaving:
-            del live_nodes[(svc, node)]
-        else:
-            live_nodes[(svc, node)] = (svc, node, "10.99.0.1", 9000)
-        if args.update_mode == "delta":
-            ctx.update_service(svc, -1 if leaving else +1)
-            update_ms.append((time.perf_counter() - t0) * 1e3)
-            return
-        if rank == 0:
-            if leaving:
-                builder.unregister(svc, node)
-            else:
-                builder.register(svc, node, "10.99.0.1", 9000)
-            img = builder.finish(epoch)
-        if multi:
-            ctx.broadcast_image(img, root=0)
-        else:
-            ctx.publish(img)
-        update_ms.append((time.perf_counter() - t0) * 1e3)
-
-    # ---- per-rank shard of the step's global stream, `buffers` distinct steps resident in HBM
     nbuf = args.buffers or BUFFERS_OF[args.workload]
     batch = args.batch or BATCH_OF[args.workload]
-    d_reqs, d_reps, counts, host_batches = [], [], [], []
-    for b in range(nbuf):
-        _, stream = make_workload(args.workload, batch * world, 0x5EED0002 + b, image.salt)
-        mine = stream[shard_indices(len(stream), world, rank)] if multi else stream
-        host_batches.append(mine)
-        counts.append(len(mine))
-        d_reqs.append(ctx.device_buffer(len(mine) * 48).upload(mine))
-        d_reps.append(ctx.device_buffer(len(mine) * 16))
-    stream_ptr = ctx.stream()
-    ext = torch.cuda.ExternalStream(stream_ptr, device=torch.device("cuda", local_rank))
+    m = measure(ctx, env, args.workload, steps=args.steps, warmup=args.warmup, nbuf=nbuf, batch=batch,
+                flags=args.flags, update_every=args.update_every, update_mode=args.update_mode, per_launch=True)
+    e2e = measure_e2e(ctx, env, args, m)
+    mirror = mirror_e2e(env, args, args.workload, batch, max(5, min(200, e2e["steps"])))
+    windows = [m["window"], e2e["window"]]
 
-    def step(i: int):
-        b = i % nbuf
-        ctx.dispatch_device(d_reqs[b], counts[b], d_reps[b], flags=args.flags, sync=False)
-
-    # the K timed steps are submitted by one C call (ptype_b200_dispatch_batches): K kernel
-    # launches back to back, no Python between them
-    timed = ctx.make_batches((d_reqs[i % nbuf], d_reps[i % nbuf], counts[i % nbuf])
-                             for i in range(args.steps))
-
-    def barrier():
-        if multi:
-            dist.barrier()
-        torch.cuda.synchronize()
-        ctx.sync()
-
-    for i in range(max(args.warmup, 3)):
-        step(i)
-    if live:   # the update path warms up too (first-use costs of the rebuild and the collective)
-        live_update(2)
-        step(0)
-        update_ms.clear()
-    barrier()
-    launches0 = ctx.launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    w0 = time.perf_counter()
-    ev0.record(ext)
-    if live:
-        every = max(args.update_every, 1)
-        for lo in range(0, args.steps, every):
-            seg = ctx.make_batches((d_reqs[i % nbuf], d_reps[i % nbuf], counts[i % nbuf])
-                                   for i in range(lo, min(lo + every, args.steps)))
-            ctx.dispatch_batches(seg, flags=args.flags, sync=False)
-            if lo + every < args.steps:
-                live_update(3 + lo // every)
-    else:
-        ctx.dispatch_batches(timed, flags=args.flags, sync=False)
-    host_enqueue_s = time.perf_counter() - w0
-    ev1.record(ext)
-    barrier()
-    w1 = time.perf_counter()
-    launches = ctx.launch_count() - launches0
-    ms = ev0.elapsed_time(ev1)
-    calls_mine = sum(counts[i % nbuf] for i in range(args.steps))
-    if multi:
-        rdev = "cuda" if torch_nccl else "cpu"
-        t = torch.tensor([ms], device=rdev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_max = float(t.item())
-        c = torch.tensor([calls_mine], device=rdev, dtype=torch.float64)
-        dist.all_reduce(c, op=dist.ReduceOp.SUM)
-        calls_all = float(c.item())
-    else:
-        ms_max, calls_all = ms, float(calls_mine)
-    value = calls_all / (ms_max * 1e-3)
-
-    # ---- SURVEY.md 8d: CUDA events around >= 50 individual launches, median and best.  Outside
-    # the timed region; the events between launches keep consecutive kernels from overlapping, so
-    # this is the duration of one launch on its own, not the pipelined step time above.
-    per_launch = None
-    if not live:
-        pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(64)]
-        for i, (a, b) in enumerate(pairs):
-            a.record(ext)
-            step(i)
-            b.record(ext)
-        barrier()
-        us = sorted(a.elapsed_time(b) * 1e3 for a, b in pairs)
-        per_launch = {"launches": len(us), "median_us": us[len(us) // 2], "best_us": us[0],
-                      "what": "one dispatch launch per batch, CUDA events around each (rank 0's GPU)"}
-
-    # ---- e2e: the C-ABI call a host makes, pinned HOST buffers, copies inside the timing
-    hb = host_batches[0]
-    pin_req = p.PinnedArray(len(hb), p.REQ_DTYPE)
-    pin_rep = p.PinnedArray(len(hb), p.REPLY_DTYPE)
-    pin_req.array[:] = hb
-    for _ in range(3):
-        ctx.dispatch(pin_req.array, pin_rep.array, flags=args.flags)
-    t0 = time.perf_counter()
-    ctx.dispatch(pin_req.array, pin_rep.array, flags=args.flags)
-    one = time.perf_counter() - t0
-    e2e_steps = args.e2e_steps or max(5, min(2000, int(1.0 / max(one, 1e-6))))
-    barrier()
-    e0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        ctx.dispatch(pin_req.array, pin_rep.array, flags=args.flags)
-    barrier()
-    e1 = time.perf_counter()
-    e2e_s = e1 - e0
-    if multi:
-        t = torch.tensor([e2e_s], device=rdev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-        c = torch.tensor([float(len(hb) * e2e_steps)], device=rdev, dtype=torch.float64)
-        dist.all_reduce(c, op=dist.ReduceOp.SUM)
-        e2e_calls = float(c.item())
-    else:
-        e2e_calls = float(len(hb) * e2e_steps)
-    e2e_value = e2e_calls / e2e_s
-    records_ok = pin_rep.array.tobytes()
-
-    # ---- e2e of ONE Client's batch in compact form (ptype_b200_call_batch): what
-    # (*Client).CallBatch submits - arguments plus a method byte per call instead of 48-byte
-    # records.  Only for the single-service workloads.
-    # At N > 1 every rank is a host process with its own Client (its own counter, rpc.go:129),
-    # submitting its own batch to its own GPU over its own PCIe link: weak scaling, like `value`.
-    e2e_compact = None
-    cb = hb   # the Client batch that is timed
-    if args.workload not in ("c3", "c5"):
-        import ptype_b200.workloads as wl
-        if multi:
-            cb = make_workload(args.workload, batch, 0x5EED0100 + rank, image.salt)[1]
-            pin_rep.free()
-            pin_rep = p.PinnedArray(len(cb), p.REPLY_DTYPE)
-        key, base, methods, sel, cargs = wl.as_client_batch(cb)
-        pin_args = p.PinnedArray(cargs.size, np.int64)
-        pin_args.array[:] = cargs.reshape(-1)
-        pa = pin_args.array.reshape(cargs.shape)
-        pin_sel = None
-        if sel is not None:
-            pin_sel = p.PinnedArray(len(sel), np.uint8)
-            pin_sel.array[:] = sel
-        ps = pin_sel.array if pin_sel is not None else None
-        for _ in range(3):
-            ctx.call_batch(key, base, methods, pa, ps, pin_rep.array, flags=args.flags & 4)
-        compact_ok = pin_rep.array.tobytes()
-        barrier()
-        c0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            ctx.call_batch(key, base, methods, pa, ps, pin_rep.array, flags=args.flags & 4)
-        barrier()
-        c1 = time.perf_counter()
-        cs = c1 - c0
-        cb_calls = float(len(cb) * e2e_steps)
-        if multi:
-            t = torch.tensor([cs], device=rdev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            cs = float(t.item())
-            c = torch.tensor([cb_calls], device=rdev, dtype=torch.float64)
-            dist.all_reduce(c, op=dist.ReduceOp.SUM)
-            cb_calls = float(c.item())
-        # ... and with the replies CallBatch's caller reads: 8-byte values + the failed list
-        pin_val = p.PinnedArray(len(cb), np.int64)
-        for _ in range(3):
-            _, vfailed, vcount = ctx.call_batch_values(key, base, methods, pa, ps, pin_val.array,
-                                                       failed_cap=1024, flags=args.flags & 4)
-        values_ok = pin_val.array.copy()
-        barrier()
-        v0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            ctx.call_batch_values(key, base, methods, pa, ps, pin_val.array, failed_cap=1024,
-                                  flags=args.flags & 4)
-        barrier()
-        vs = time.perf_counter() - v0
-        if multi:
-            t = torch.tensor([vs], device=rdev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            vs = float(t.item())
-        e2e_values = {"value": cb_calls / vs, "unit": "calls/s",
-                      "h2d_bytes_per_step": int(cargs.nbytes + (len(sel) if sel is not None else 0)),
-                      "d2h_bytes_per_step": int(len(cb) * 8), "steps": e2e_steps, "failed_calls": int(vcount),
-                      "api": "ptype_b200_call_batch_values(args + method byte in, 8-byte values + failed list "
-                             "out, pinned host buffers)"}
-        e2e_compact = {"value": cb_calls / cs, "unit": "calls/s",
-                       "h2d_bytes_per_step": int(cargs.nbytes + (len(sel) if sel is not None else 0)),
-                       "d2h_bytes_per_step": int(len(cb) * 16), "steps": e2e_steps,
-                       "api": "ptype_b200_call_batch(one Client's batch: args + method byte per call, "
-                              "pinned host buffers)"}
+    # ---- the other configs, short, under the same rules (the default line carries them)
+    extras = {}
+    if args.workload == "c2" and not args.no_extras and not args.flags:
+        plan = [("c5", dict(steps=192, nbuf=4))] if multi else \
+               [("c3", dict(steps=12, nbuf=2)), ("c4", dict(steps=200, nbuf=8)), ("c5", dict(steps=256, nbuf=8))]
+        for name, kw in plan:
+            x = measure(ctx, env, name, warmup=3, batch=BATCH_OF[name], update_every=64, **kw)
+            windows.append(x["window"])
+            extras[name] = x
 
     sampler.stop()
     sampler.join(timeout=1.0)
-    clocks = sampler.summary([(w0, w1), (e0, e1)])
-    e2e_records = {"value": e2e_value, "unit": "calls/s", "h2d_bytes_per_step": int(len(hb) * 48),
-                   "d2h_bytes_per_step": int(len(hb) * 16), "steps": e2e_steps,
-                   "api": "ptype_b200_dispatch(host pinned 48-byte records -> host pinned replies)"}
+    clocks = sampler.summary(windows)
 
-    # ---- parity spot check of what was just timed, and the CPU baseline (rank 0, N=1 only)
+    parity_ok = m["parity_ok"] and e2e["parity_ok"] and all(x["parity_ok"] for x in extras.values())
+    if not parity_ok:
+        if rank == 0:
+            bad = {"primary": m["parity"], "e2e_ok": e2e["parity_ok"],
+                   "extras": {k: x["parity"] for k, x in extras.items()}}
+            print(json.dumps({"error": "CUDA replies differ from the oracle - number withheld", "parity": bad}),
+                  file=sys.stderr, flush=True)
+        ctx.close()
+        if multi:
+            dist.destroy_process_group()
+        raise SystemExit(1)
+
+    # ---- the CPU baseline (rank 0, N=1 only)
     cpu_baseline = None
-    if rank == 0:
-        from oracle import binding as ob
-        if live:   # the registry as it stands after the last update
-            import ptype_b200.workloads as wl
-            spec = wl.RegistrySpec(sorted(live_nodes.values()), spec.expose, [], spec.local_addr,
-                                   spec.max_connections)
-            ctx.dispatch_device(d_reqs[0], counts[0], d_reps[0], flags=args.flags)
-        kv, snap = ob.snapshot_from_spec(spec, image.salt)
-        want = snap.dispatch(hb, check_limit=1 << 16, threads=os.cpu_count() or 1)
-        got = d_reps[0].download(p.REPLY_DTYPE, counts[0])
-        if got.tobytes() != want.tobytes() or records_ok != want.tobytes():
-            raise SystemExit("bench.py: CUDA replies differ from the oracle - number withheld")
-        want_cb = want if cb is hb else snap.dispatch(cb, check_limit=1 << 16, threads=os.cpu_count() or 1)
-        if e2e_compact is not None and compact_ok != want_cb.tobytes():
-            raise SystemExit("bench.py: call_batch replies differ from the oracle - number withheld")
-        if e2e_compact is not None and (not np.array_equal(values_ok, want_cb["value"]) or
-                                        vcount != int((want_cb["status"] != 0).sum())):
-            raise SystemExit("bench.py: call_batch_values differs from the oracle - number withheld")
-        if not multi:
-            restore_affinity()
-            threads = os.cpu_count() or 1
-            rate, passes, el, _ = cpu_port_rate(spec, hb, threads, args.cpu_seconds)
-            rate1, passes1, el1, _ = cpu_port_rate(spec, hb, 1, min(2.0, args.cpu_seconds))
-            lb = loopback_rate(hb, 1, min(len(hb), 20_000), 3 if args.workload != "c4" else 2,
-                               2 if args.workload == "c4" else 1) if args.workload not in ("c3", "c5") else None
-            cpu_baseline = {"value": rate, "unit": "calls/s", "cores": threads, "kind": "port",
-                            "loopback_config1": lb,
-                            "sample": f"{passes} passes over one {len(hb)}-call batch of the same workload "
-                                      f"in {el:.1f} s, {threads} threads",
-                            "single_thread_value": rate1,
-                            "note": "Go reference path not run - no Go toolchain on this image"}
+    if rank == 0 and not multi:
+        restore_affinity()
+        spec, hb = m["spec"], m["hb"]
+        if args.workload == "c5":   # the registry as first installed: the CPU port has no live updates to pay for
+            spec = make_workload("c3", 32, 1)[0]
+        threads = os.cpu_count() or 1
+        rate, passes, el, _ = cpu_port_rate(spec, hb, threads, args.cpu_seconds)
+        rate1, passes1, el1, _ = cpu_port_rate(spec, hb, 1, min(2.0, args.cpu_seconds))
+        lb = loopback_rate(hb, 1, min(len(hb), 20_000), 3 if args.workload != "c4" else 2,
+                           2 if args.workload == "c4" else 1) if args.workload not in ("c3", "c5") else None
+        cpu_baseline = {"value": rate, "unit": "calls/s", "cores": threads, "kind": "port",
+                        "loopback_config1": lb,
+                        "sample": f"{passes} passes over one {len(hb)}-call batch of the same workload "
+                                  f"in {el:.1f} s, {threads} threads",
+                        "single_thread_value": rate1,
+                        "note": "Go reference path not run - no Go toolchain on this image"}
 
     if rank == 0:
-        peak, peak_kind = measured_peak()
-        launch_s = (ms_max * 1e-3) / args.steps
-        per_launch_calls = calls_all / world / args.steps
-        achieved = per_launch_calls * BYTES_PER_CALL / launch_s / 1e9
         traffic, traffic_note = None, None
         tp = ROOT / "profiles" / "dispatch_traffic.json"
         if tp.exists():
@@ -593,45 +793,41 @@ def main():
             except Exception:
                 traffic = None
         line = {
-            "metric": "rpc_calls_per_sec_batched_dispatch", "value": value, "unit": "calls/s",
+            "metric": "rpc_calls_per_sec_batched_dispatch", "value": m["value"], "unit": "calls/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": m["ms_max"] / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-            "config": {"workload": WORKLOAD_TEXT[args.workload], "batch_calls_per_gpu": int(per_launch_calls),
-                       "resident_batches": nbuf,
-                       "l2": f"{nbuf} distinct batches rotated: {nbuf * per_launch_calls * 64 / 1e6:.0f} MB "
-                             f"working set > 126 MB L2",
-                       "sharding": "mix64(request_id) % n_gpus, registry replica per GPU via ncclBroadcast"
-                                   if multi else "single GPU",
-                       "table": "shared memory" if not (args.flags & 4) else "global/L2"},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
-                         "peak_kind": peak_kind,
+            "config": common_config(args.workload, batch, nbuf),
+            "placement": {"sharding": "mix64(request_id) % n_gpus, registry replica per GPU via ncclBroadcast"
+                                      if multi else "single GPU",
+                          "table": "shared memory" if not (args.flags & 4) else "global/L2",
+                          "calls_per_gpu_per_step": m["per_launch_calls"],
+                          "warm": "W single-launch steps, one untimed pass of the timed launch list, an 8-batch "
+                                  "pre-roll in flight when the start event is recorded"},
+            "roofline": {"bound": "hbm", "achieved": m["achieved_gbs"], "peak": m["peak"], "unit": "GB/s",
+                         "frac": m["achieved_gbs"] / m["peak"], "traffic": traffic, "traffic_note": traffic_note,
+                         "peak_kind": m["peak_kind"],
                          "kernel": "dispatch_kernel (one launch per batch)" if (args.flags & 32) else
-                                   "dispatch_multi_kernel (one persistent launch per 96 batches)", "algorithmic_bytes_per_call": BYTES_PER_CALL,
-                         "frac_of_nominal_8TBs": achieved / 8000.0},
-            "e2e": e2e_values if e2e_compact is not None else e2e_records,
-            "e2e_reply_records": e2e_compact,
-            "e2e_records": e2e_records,
-            "gpu_launches": int(launches),
-            "per_launch": per_launch,
-            "host_enqueue_us_per_step": host_enqueue_s / args.steps * 1e6,
+                                   "dispatch_multi_kernel (one persistent launch per 96 batches)",
+                         "algorithmic_bytes_per_call": BYTES_PER_CALL,
+                         "frac_of_nominal_8TBs": m["achieved_gbs"] / 8000.0},
+            "e2e": e2e["values"] if e2e["values"] is not None else e2e["records"],
+            "e2e_mirror": mirror,
+            "e2e_reply_records": e2e["compact"],
+            "e2e_records": e2e["records"],
+            "parity": m["parity"],
+            "gpu_launches": m["launches"],
+            "per_launch": m["lone"],
+            "host_enqueue_us_per_step": m["host_enqueue_s"] / args.steps * 1e6,
+            "extras": {k: extra_summary(x) for k, x in extras.items()},
             "clocks": clocks,
         }
-        if live:
-            line["config"]["live_updates"] = {"count": len(update_ms), "every_steps": args.update_every,
-                                              "host_ms_avg": float(np.mean(update_ms)) if update_ms else None,
-                                              "transport": "on-device patch of the table (update_service)"
-                                              if args.update_mode == "delta" else
-                                              ("rebuilt image, ncclBroadcast" if multi else "rebuilt image, publish")}
+        if "live_updates" in m:
+            line["placement"]["live_updates"] = m["live_updates"]
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
         print(json.dumps(line), flush=True)
 
-    pin_req.free()
-    pin_rep.free()
-    for b in d_reqs + d_reps:
-        b.free()
     ctx.close()
     if multi:
         dist.destroy_process_group()

@@ -98,7 +98,7 @@ enum ptype_opcode {
  * the selection rule (localAddr, ConnConfig.MaxConnections; cluster/rpc.go:19-38,128). */
 
 #define PTYPE_IMAGE_MAGIC 0x49595450u /* "PTYI" */
-#define PTYPE_IMAGE_VERSION 3u
+#define PTYPE_IMAGE_VERSION 4u
 #define PTYPE_SLOT_WAYS 3        /* candidate slots per key (3-way cuckoo hashing) */
 #define PTYPE_MTABLE_SLOTS 64   /* perfect-hash method table size                  */
 #define PTYPE_SLOT_EMPTY 0xFFFFFFFFu
@@ -126,12 +126,15 @@ typedef struct ptype_image_header { /* 192 bytes */
     uint32_t off_services;   /* ptype_service[n_services](host-side lookups only)      */
     uint32_t off_strings;    /* string pool, NUL-terminated entries                    */
     uint32_t strings_bytes;
-    uint32_t device_bytes;   /* prefix of the blob the kernels read (slots, hashes, methods) */
+    uint32_t device_bytes;   /* prefix of the blob the kernels read (slots, hashes, methods, order) */
     uint32_t table_seed;     /* xor-ed into the folded key before the three slot hashes */
     uint32_t method_mul;     /* odd multiplier: mtable index = (method_hash * mul) >> 26 */
     uint32_t off_mtable;     /* ptype_method[PTYPE_MTABLE_SLOTS], collision-free, opcode 0 = empty */
     uint32_t host_sections;  /* 1: services/nodes/strings present; 0: device-only image       */
-    uint32_t reserved[3];
+    uint32_t off_order;      /* uint32[n_slots]: rank of the slot's service in etcd key order
+                                (services/<name>/ compared bytewise), PTYPE_SLOT_EMPTY for a free
+                                slot; read by ptype_b200_update_service only                       */
+    uint32_t reserved[2];
     char local_addr[PTYPE_LOCAL_ADDR_MAX]; /* the Client host's address string (cluster.go:69,82) */
 } ptype_image_header;
 
@@ -259,7 +262,14 @@ int ptype_b200_device_alloc(ptype_ctx*, int dev, size_t bytes, void** out);
 int ptype_b200_device_free(ptype_ctx*, int dev, void* p);
 int ptype_b200_memcpy_h2d(ptype_ctx*, int dev, void* dst, const void* src, size_t bytes);
 int ptype_b200_memcpy_d2h(ptype_ctx*, int dev, void* dst, const void* src, size_t bytes);
-/* The cudaStream_t dispatches of device `dev` are ordered on (for event timing). */
+/* The cudaStream_t dispatches of device `dev` are ordered on (for event timing, or to enqueue a
+ * kernel of your own that fills a batch).  Ordering rule: consecutive dispatch launches of this
+ * library overlap each other's ramp-up and drain (programmatic dependent launch), which is sound
+ * because a dispatch never reads what the previous one wrote.  The library drops that overlap by
+ * itself after anything else IT enqueues on the stream (copies, assign_seq, codec and checksum
+ * kernels, a new image).  Work YOU enqueue there is invisible to it: if that work produces the
+ * requests (or anything else) the next dispatch reads, pass PTYPE_F_AFTER_PRODUCER to that
+ * dispatch so that it starts only after everything before it on the stream has completed. */
 int ptype_b200_stream(ptype_ctx*, int dev, void** cuda_stream);
 
 /* Install a new snapshot on every device of the context: copy into the inactive
@@ -298,6 +308,8 @@ int ptype_b200_broadcast_image(ptype_ctx*, const void* image, size_t bytes, int 
 #define PTYPE_F_GLOBAL_TABLE 4u/* measurement switch: probe the table in L2, not shared memory  */
 #define PTYPE_F_LDG_LOADS 8u   /* measurement switch: fetch requests with LDG + shuffle transpose */
 #define PTYPE_F_BULK_LOADS 16u /* measurement switch: stage requests with bulk-async copies      */
+#define PTYPE_F_AFTER_PRODUCER 64u /* the work enqueued before this call on ptype_b200_stream() wrote
+                                     this batch's inputs: no overlap with it (see ptype_b200_stream) */
 #define PTYPE_F_ONE_LAUNCH_PER_BATCH 32u /* dispatch_batches: one kernel launch per batch instead of
                                             one launch per group of up to 96 batches               */
 

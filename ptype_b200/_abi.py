@@ -29,6 +29,7 @@ NO_NODE = 0xFFFFFFFF
 RECV_ILL_FORMED = 0xFFFFFFFF
 
 F_DEVICE_PTRS, F_ASYNC, F_GLOBAL_TABLE, F_LDG_LOADS, F_BULK_LOADS, F_ONE_LAUNCH_PER_BATCH = 1, 2, 4, 8, 16, 32
+F_AFTER_PRODUCER = 64
 
 E_OK, E_INVAL, E_NOMEM, E_CUDA, E_NO_IMAGE, E_BAD_IMAGE = 0, 1, 2, 3, 4, 5
 E_COLLISION, E_NCCL, E_LIMIT, E_NOT_FOUND, E_BUSY = 6, 7, 8, 9, 10
@@ -57,7 +58,7 @@ class ImageHeader(C.Structure):
         ("off_methods", C.c_uint32), ("off_nodes", C.c_uint32), ("off_services", C.c_uint32),
         ("off_strings", C.c_uint32), ("strings_bytes", C.c_uint32), ("device_bytes", C.c_uint32),
         ("table_seed", C.c_uint32), ("method_mul", C.c_uint32), ("off_mtable", C.c_uint32),
-        ("host_sections", C.c_uint32), ("reserved", C.c_uint32 * 3), ("local_addr", C.c_char * 64),
+        ("host_sections", C.c_uint32), ("off_order", C.c_uint32), ("reserved", C.c_uint32 * 2), ("local_addr", C.c_char * 64),
     ]
 
 

@@ -125,6 +125,14 @@ struct DeviceState {
     int sm_count = 0;
     int dispatch_sms = 0;  // SMs the dispatch grids are sized for (see ptype_b200_comm_init)
     cudaStream_t stream = nullptr;       // device-pointer dispatches, checksums
+    // True while the last thing enqueued on `stream` is a dispatch launch of this library.  Only
+    // then may the next dispatch carry the programmatic-dependent-launch attribute: it can start
+    // (and load its requests and the tables) before its predecessor has finished, which is only
+    // sound when the predecessor wrote none of that - dispatch kernels write replies only.
+    // Anything else the library enqueues there (copies, memsets, assign_seq, codec, checksum and
+    // counter kernels, waits for a new image) clears it; producers the library cannot see are
+    // declared by the caller with PTYPE_F_AFTER_PRODUCER.
+    std::atomic<bool> after_dispatch{false};
     cudaStream_t copy_stream = nullptr;  // image uploads / broadcast
     cudaStream_t pipe[kPipe] = {};
     Stage stage[kPipe];
@@ -193,6 +201,12 @@ namespace {
 // ptype_b200_alloc_pinned all give at least that); 8 for int64 arrays.
 bool misaligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) != 0; }
 
+// May the dispatch launch that is about to go onto d->stream overlap its predecessor?
+bool take_pdl(DeviceState* d, uint32_t flags) {
+    const bool was = d->after_dispatch.exchange(true);
+    return was && !(flags & PTYPE_F_AFTER_PRODUCER);
+}
+
 DeviceState* dev_of(ptype_ctx* ctx, int dev) {
     if (!ctx || dev < 0 || dev >= static_cast<int>(ctx->devs.size())) return nullptr;
     return ctx->devs[dev];
@@ -234,6 +248,7 @@ int ensure_counters(DeviceState* d, int buf, uint32_t n_slots) {
 
 int make_active(DeviceState* d, int buf) {
     const int old = d->active;
+    d->after_dispatch = false;  // the next dispatch reads tables another stream has just written
     if (old >= 0 && old != buf && d->seq_in_use) {
         // the balancer counters follow their services into the new table, in stream order
         // after every assign_seq enqueued so far (d->stream already waits for the new image)
@@ -505,6 +520,7 @@ int ptype_b200_memcpy_h2d(ptype_ctx* ctx, int dev, void* dst, const void* src, s
     DeviceState* d = dev_of(ctx, dev);
     if (!d) return PTYPE_E_INVAL;
     CU(cudaSetDevice(d->device));
+    d->after_dispatch = false;
     CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, d->stream));
     CU(cudaStreamSynchronize(d->stream));
     return PTYPE_OK;
@@ -513,6 +529,7 @@ int ptype_b200_memcpy_d2h(ptype_ctx* ctx, int dev, void* dst, const void* src, s
     DeviceState* d = dev_of(ctx, dev);
     if (!d) return PTYPE_E_INVAL;
     CU(cudaSetDevice(d->device));
+    d->after_dispatch = false;
     CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, d->stream));
     CU(cudaStreamSynchronize(d->stream));
     return PTYPE_OK;
@@ -521,6 +538,7 @@ int ptype_b200_stream(ptype_ctx* ctx, int dev, void** cuda_stream) {
     DeviceState* d = dev_of(ctx, dev);
     if (!d || !cuda_stream) return PTYPE_E_INVAL;
     *cuda_stream = d->stream;
+    d->after_dispatch = false;
     return PTYPE_OK;
 }
 
@@ -609,6 +627,7 @@ int ptype_b200_update_service(ptype_ctx* ctx, const char* service, int delta) {
                            d->copy_stream));
         CU(ptype::launch_patch_service(
             reinterpret_cast<ptype_slot*>(static_cast<unsigned char*>(d->image_buf[buf]) + hh->off_slots),
+            reinterpret_cast<const uint32_t*>(static_cast<unsigned char*>(d->image_buf[buf]) + hh->off_order),
             hh->n_slots, hh->table_seed, key, delta, reinterpret_cast<uint32_t*>(d->d_size), d->copy_stream));
         ctx->launches.fetch_add(1);
         rc = dispatches_wait_for_copy_stream(d);
@@ -627,12 +646,12 @@ int ptype_b200_update_service(ptype_ctx* ctx, const char* service, int delta) {
         rc = make_active(d, buf);
         if (rc != PTYPE_OK) return rc;
     }
-    const uint32_t pivot = hs[at].node_base + n_old;
+    const uint32_t* order = reinterpret_cast<const uint32_t*>(ctx->host_image.data() + hh->off_order);
     for (uint32_t i = 0; i < hh->n_slots; ++i) {
         if (hs[i].node_base == PTYPE_SLOT_EMPTY) continue;
         if (i == at)
             hs[i].n_and_recv = (hs[i].n_and_recv & 0xFF000000u) | static_cast<uint32_t>(n_new);
-        else if (hs[i].node_base >= pivot)
+        else if (order[i] > order[at])
             hs[i].node_base = static_cast<uint32_t>(static_cast<long long>(hs[i].node_base) + delta);
     }
     // the blob no longer matches its node/string sections: keep only what the kernels read
@@ -794,11 +813,12 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
         if (extras) {
             d_stats = reinterpret_cast<unsigned long long*>(stats);
             CU(cudaMemsetAsync(d_stats, 0, sizeof(ptype_batch_stats), d->stream));
+            d->after_dispatch = false;
         }
         if (n) {
             CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, n, d->dispatch_sms), reqs, n,
                                       replies, failed_idx, static_cast<uint32_t>(failed_cap), 0u,
-                                      d_stats, d->stream));
+                                      d_stats, d->stream, take_pdl(d, flags)));
             ctx->launches.fetch_add(1);
         }
         if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
@@ -812,7 +832,7 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
         ptype_reply* r = static_cast<ptype_reply*>(pinned_alias(replies));
         if (q && r) {
             CU(ptype::launch_dispatch(img, plan, zero_copy_grid(plan, n, d->dispatch_sms), q, n, r, nullptr,
-                                      0u, 0u, nullptr, d->stream));
+                                      0u, 0u, nullptr, d->stream, take_pdl(d, flags)));
             ctx->launches.fetch_add(1);
             if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
             return PTYPE_OK;
@@ -842,7 +862,7 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
         CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, cnt, d->dispatch_sms), st.d_reqs, cnt,
                                   st.d_replies, failed_idx ? d->d_failed : nullptr,
                                   static_cast<uint32_t>(failed_cap), static_cast<uint32_t>(done),
-                                  extras ? d->d_stats : nullptr, d->pipe[s]));
+                                  extras ? d->d_stats : nullptr, d->pipe[s], false));
         ctx->launches.fetch_add(1);
         CU(cudaMemcpyAsync(replies + done, st.d_replies, cnt * sizeof(ptype_reply),
                            cudaMemcpyDeviceToHost, d->pipe[s]));
@@ -908,7 +928,7 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
             if (e == b) return PTYPE_E_LIMIT;
             if (tiles) {
                 CU(ptype::launch_dispatch_multi(img, plan, d->dispatch_sms, batches + b, static_cast<int>(e - b),
-                                                d->stream));
+                                                d->stream, take_pdl(d, flags)));
                 ctx->launches.fetch_add(1);
             }
             b = e;
@@ -918,7 +938,7 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
             const ptype_batch& bt = batches[b];
             if (bt.n == 0) continue;
             CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, bt.n, d->dispatch_sms), bt.reqs, bt.n,
-                                      bt.replies, nullptr, 0u, 0u, nullptr, d->stream));
+                                      bt.replies, nullptr, 0u, 0u, nullptr, d->stream, take_pdl(d, flags)));
             ctx->launches.fetch_add(1);
         }
     }
@@ -1005,6 +1025,7 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
             if (!d->d_stats) CU(cudaMalloc(&d->d_stats, ptype::kStatWords * sizeof(unsigned long long)));
             CU(cudaMemsetAsync(d->d_stats, 0, sizeof(unsigned long long), d->stream));
             CU(cudaStreamSynchronize(d->stream));
+            d->after_dispatch = false;
             out.failed_count = d->d_stats;
         }
     }
@@ -1026,7 +1047,7 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
             out.values = values;
             CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, n, d->dispatch_sms), svc_key, seq_base,
                                         m, r, n_methods, args, args_per_call, method_sel, n, replies, out,
-                                        d->stream));
+                                        d->stream, take_pdl(d, flags)));
             ctx->launches.fetch_add(1);
         }
         if (values_mode || !(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
@@ -1035,7 +1056,8 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
     if (zero_copy) {
         out.values = zv;
         CU(ptype::launch_call_batch(img, plan, zero_copy_grid(plan, n, d->dispatch_sms), svc_key, seq_base,
-                                    m, r, n_methods, za, args_per_call, zs, n, zr, out, d->stream));
+                                    m, r, n_methods, za, args_per_call, zs, n, zr, out, d->stream,
+                                    take_pdl(d, flags)));
         ctx->launches.fetch_add(1);
         if (values_mode || !(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
         return finish_values();
@@ -1065,7 +1087,7 @@ int call_batch_impl(ptype_ctx* ctx, int dev, uint64_t svc_key, uint64_t seq_base
         out.index_base = static_cast<uint32_t>(done);
         CU(ptype::launch_call_batch(img, plan, ptype::grid_for(plan, cnt, d->dispatch_sms), svc_key,
                                     seq_base + done, m, r, n_methods, d_args, args_per_call, d_sel, cnt,
-                                    st.d_replies, out, d->pipe[s]));
+                                    st.d_replies, out, d->pipe[s], false));
         ctx->launches.fetch_add(1);
         if (values_mode)
             CU(cudaMemcpyAsync(values + done, st.d_replies, cnt * sizeof(int64_t), cudaMemcpyDeviceToHost,
@@ -1128,6 +1150,7 @@ int ptype_b200_reply_checksum(ptype_ctx* ctx, int dev, const ptype_reply* replie
     if (!d->d_cksum_out) CU(cudaMalloc(&d->d_cksum_out, sizeof(unsigned long long)));
     const ptype_reply* d_replies = replies;
     void* tmp = nullptr;
+    d->after_dispatch = false;
     if (!(flags & PTYPE_F_DEVICE_PTRS) && n) {
         CU(cudaMalloc(&tmp, n * sizeof(ptype_reply)));
         cudaError_t e = cudaMemcpyAsync(tmp, replies, n * sizeof(ptype_reply), cudaMemcpyHostToDevice,
@@ -1157,6 +1180,7 @@ int ptype_b200_resolve_names(ptype_ctx* ctx, int dev, const char* names, uint32_
     if (!d || (n && !names) || stride == 0 || (stride & 15u) || (!out && !patch)) return PTYPE_E_INVAL;
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(d->device));
+    d->after_dispatch = false;
     CU(ptype::launch_resolve_names(reinterpret_cast<const unsigned char*>(names), stride, n, out, patch,
                                    d->stream));
     ctx->launches.fetch_add(1);
@@ -1180,6 +1204,7 @@ int ptype_b200_gob_encode_replies(ptype_ctx* ctx, int dev, const ptype_reply* re
         d->codec_cap = need;
     }
     if (!d->d_cksum_out) CU(cudaMalloc(&d->d_cksum_out, sizeof(unsigned long long)));
+    d->after_dispatch = false;
     CU(ptype::launch_gob_encode_replies(replies, n, reinterpret_cast<unsigned long long*>(offsets), out,
                                         out_cap, d->d_codec, d->d_cksum_out, d->stream));
     ctx->launches.fetch_add(3);
@@ -1197,6 +1222,7 @@ int ptype_b200_gob_decode_args(ptype_ctx* ctx, int dev, const uint8_t* bytes, co
         return PTYPE_E_INVAL;
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(d->device));
+    d->after_dispatch = false;
     CU(ptype::launch_gob_decode_args(bytes, reinterpret_cast<const unsigned long long*>(offsets), n, args,
                                      args_per_call, status, d->stream));
     ctx->launches.fetch_add(1);
@@ -1254,6 +1280,7 @@ int ptype_b200_assign_seq(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, 
         CU(cudaMalloc(&d->seq_start, static_cast<size_t>(img.n_slots) * sizeof(unsigned long long)));
         d->seq_start_cap = img.n_slots;
     }
+    d->after_dispatch = false;
     CU(ptype::launch_assign_seq(img, plan, d_reqs, n, d->rank_rows, d->seq_counters[d->active], d->seq_start,
                                 d->stream));
     ctx->launches.fetch_add(3);

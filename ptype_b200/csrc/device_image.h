@@ -39,16 +39,18 @@ struct LaunchPlan {
 constexpr int kChecksumBlocks = 148 * 8;
 constexpr int kChecksumThreads = 256;
 
-// Must run with the target device current (sets the kernel's shared-memory attribute).
+// Must run with the target device current (occupancy query of the kernel the plan names).
+// `pdl` in the launchers below: the launch may overlap the tail of the previous kernel on the
+// stream (programmatic dependent launch); pass true only when that kernel was a dispatch launch.
 cudaError_t plan_dispatch(const DeviceImage& img, uint32_t flags, bool extras, LaunchPlan* plan);
 int grid_for(const LaunchPlan& plan, size_t n, int sm_count);
 cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int blocks,
                             const ptype_req* reqs, size_t n, ptype_reply* replies, uint32_t* failed_idx,
                             uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
-                            cudaStream_t stream);
+                            cudaStream_t stream, bool pdl);
 int max_batches_per_launch();
 cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
-                                  const ptype_batch* batches, int count, cudaStream_t stream);
+                                  const ptype_batch* batches, int count, cudaStream_t stream, bool pdl);
 // Values-only output of a client batch: values != nullptr switches the kernel from 16-byte
 // reply records to 8-byte values plus an (index, status) list of the failed calls.
 struct CallBatchOut {
@@ -67,7 +69,7 @@ cudaError_t launch_call_batch(const DeviceImage& img, const LaunchPlan& plan, in
                               uint64_t svc_key, uint64_t seq_base, const uint32_t* methods,
                               const uint32_t* recvs, int n_methods, const int64_t* args,
                               int args_per_call, const uint8_t* method_sel, size_t n,
-                              ptype_reply* replies, const CallBatchOut& out, cudaStream_t stream);
+                              ptype_reply* replies, const CallBatchOut& out, cudaStream_t stream, bool pdl);
 cudaError_t launch_reply_checksum(const ptype_reply* replies, size_t n, uint64_t index_base,
                                   unsigned long long* partials, unsigned long long* out,
                                   cudaStream_t stream);
@@ -81,8 +83,8 @@ cudaError_t launch_gob_encode_replies(const ptype_reply* replies, size_t n, unsi
 cudaError_t launch_gob_decode_args(const uint8_t* bytes, const unsigned long long* offsets, size_t n,
                                    int64_t* args, int args_per_call, uint8_t* status, cudaStream_t stream);
 
-cudaError_t launch_patch_service(ptype_slot* slots, uint32_t n_slots, uint32_t seed, uint64_t key, int delta,
-                                 uint32_t* result, cudaStream_t stream);
+cudaError_t launch_patch_service(ptype_slot* slots, const uint32_t* order, uint32_t n_slots, uint32_t seed,
+                                 uint64_t key, int delta, uint32_t* result, cudaStream_t stream);
 
 // rank.cu: balancer counters on the device.
 struct RankPlan {

@@ -954,11 +954,19 @@ bool pdl_enabled() {
     return on;
 }
 
-// One launch, optionally with programmatic stream serialization so that consecutive
-// dispatches on a stream overlap their ramp-up and drain.
+// One launch.  `pdl` adds programmatic stream serialization, so that this kernel may start while
+// its predecessor on the stream drains; the caller passes it only when that predecessor is another
+// dispatch launch of this library (whose output this kernel does not read) - see after_dispatch in
+// context.cu.  A kernel that asks for more than 48 KiB of dynamic shared memory has to opt in, per
+// function and per device; doing it here covers every variant that is ever launched.
 template <typename Kernel, typename... Args>
-cudaError_t launch_kernel(Kernel kernel, int blocks, int threads, size_t smem, cudaStream_t stream,
+cudaError_t launch_kernel(Kernel kernel, int blocks, int threads, size_t smem, cudaStream_t stream, bool pdl,
                           Args... args) {
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(smem));
+        if (e != cudaSuccess) return e;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(static_cast<unsigned>(blocks));
     cfg.blockDim = dim3(static_cast<unsigned>(threads));
@@ -968,7 +976,7 @@ cudaError_t launch_kernel(Kernel kernel, int blocks, int threads, size_t smem, c
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cfg.numAttrs = (pdl && pdl_enabled()) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, args...);
 }
 
@@ -976,19 +984,19 @@ template <bool kSmemTable, bool kExtras>
 cudaError_t launch_variant(const DeviceImage& img, const LaunchPlan& plan, int blocks,
                            const ptype_req* reqs, size_t n, ptype_reply* replies, uint32_t* failed_idx,
                            uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, bool pdl) {
     const uint4* q = reinterpret_cast<const uint4*>(reqs);
     uint4* r = reinterpret_cast<uint4*>(replies);
     if (plan.bulk)
         return launch_kernel(dispatch_bulk_kernel<kSmemTable, kExtras, kStagesDefault>, blocks,
-                             plan.threads, plan.dyn_smem, stream, img, q, n, r, failed_idx, failed_cap,
+                             plan.threads, plan.dyn_smem, stream, pdl, img, q, n, r, failed_idx, failed_cap,
                              idx_base, stats, static_cast<uint32_t>(plan.table_smem));
     if (plan.threads == kMaxThreads)
         return launch_kernel(dispatch_kernel<kSmemTable, kExtras, 2, kMaxThreads, 1>, blocks,
-                             plan.threads, plan.dyn_smem, stream, img, q, n, r, failed_idx, failed_cap,
+                             plan.threads, plan.dyn_smem, stream, pdl, img, q, n, r, failed_idx, failed_cap,
                              idx_base, stats);
     return launch_kernel(dispatch_kernel<kSmemTable, kExtras, kSmallUnroll, kSmallThreads, kSmallMinCtas>,
-                         blocks, plan.threads, plan.dyn_smem, stream, img, q, n, r, failed_idx,
+                         blocks, plan.threads, plan.dyn_smem, stream, pdl, img, q, n, r, failed_idx,
                          failed_cap, idx_base, stats);
 }
 
@@ -1072,25 +1080,25 @@ int grid_for(const LaunchPlan& plan, size_t n, int sm_count) {
 cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int blocks,
                             const ptype_req* reqs, size_t n, ptype_reply* replies, uint32_t* failed_idx,
                             uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
-                            cudaStream_t stream) {
+                            cudaStream_t stream, bool pdl) {
     const bool extras = stats != nullptr;
     if (plan.smem_table) {
         return extras ? launch_variant<true, true>(img, plan, blocks, reqs, n, replies, failed_idx,
-                                                   failed_cap, idx_base, stats, stream)
+                                                   failed_cap, idx_base, stats, stream, pdl)
                       : launch_variant<true, false>(img, plan, blocks, reqs, n, replies, failed_idx,
-                                                    failed_cap, idx_base, stats, stream);
+                                                    failed_cap, idx_base, stats, stream, pdl);
     }
     return extras ? launch_variant<false, true>(img, plan, blocks, reqs, n, replies, failed_idx,
-                                                failed_cap, idx_base, stats, stream)
+                                                failed_cap, idx_base, stats, stream, pdl)
                   : launch_variant<false, false>(img, plan, blocks, reqs, n, replies, failed_idx,
-                                                 failed_cap, idx_base, stats, stream);
+                                                 failed_cap, idx_base, stats, stream, pdl);
 }
 
 // Up to kMaxBatchesPerLaunch device-resident batches in ONE launch.
 int max_batches_per_launch() { return kMaxBatchesPerLaunch; }
 
 cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
-                                  const ptype_batch* batches, int count, cudaStream_t stream) {
+                                  const ptype_batch* batches, int count, cudaStream_t stream, bool pdl) {
     BatchList list = {};
     uint64_t tiles = 0;
     int m = 0;
@@ -1110,31 +1118,26 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     size_t want = (tiles + warps_per_cta - 1) / warps_per_cta;
     const size_t resident = static_cast<size_t>(sm_count) * plan.ctas_per_sm;
     const int blocks = static_cast<int>(want < resident ? (want ? want : 1) : resident);
+    const uint32_t table_smem = static_cast<uint32_t>(plan.table_smem);
     if (plan.bulk) {
         if (plan.smem_table)
             return launch_kernel(dispatch_bulk_multi_kernel<true, kStagesDefault>, blocks, plan.threads,
-                                 plan.dyn_smem, stream, img, list, static_cast<uint32_t>(plan.table_smem));
+                                 plan.dyn_smem, stream, pdl, img, list, table_smem);
         return launch_kernel(dispatch_bulk_multi_kernel<false, kStagesDefault>, blocks, plan.threads,
-                             plan.dyn_smem, stream, img, list, static_cast<uint32_t>(plan.table_smem));
+                             plan.dyn_smem, stream, pdl, img, list, table_smem);
     }
     if (plan.threads == kMaxThreads) {
-        if (plan.smem_table) {
-            auto k = dispatch_multi_kernel<true, 2, kMaxThreads, 1>;
-            if (plan.dyn_smem > 48 * 1024) {
-                cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                     static_cast<int>(plan.dyn_smem));
-                if (e != cudaSuccess) return e;
-            }
-            return launch_kernel(k, blocks, plan.threads, plan.dyn_smem, stream, img, list);
-        }
+        if (plan.smem_table)
+            return launch_kernel(dispatch_multi_kernel<true, 2, kMaxThreads, 1>, blocks, plan.threads,
+                                 plan.dyn_smem, stream, pdl, img, list);
         return launch_kernel(dispatch_multi_kernel<false, 2, kMaxThreads, 1>, blocks, plan.threads,
-                             plan.dyn_smem, stream, img, list);
+                             plan.dyn_smem, stream, pdl, img, list);
     }
     if (plan.smem_table)
         return launch_kernel(dispatch_multi_kernel<true, kSmallUnroll, kSmallThreads, kSmallMinCtas>, blocks,
-                             plan.threads, plan.dyn_smem, stream, img, list);
+                             plan.threads, plan.dyn_smem, stream, pdl, img, list);
     return launch_kernel(dispatch_multi_kernel<false, kSmallUnroll, kSmallThreads, kSmallMinCtas>, blocks,
-                         plan.threads, plan.dyn_smem, stream, img, list);
+                         plan.threads, plan.dyn_smem, stream, pdl, img, list);
 }
 
 namespace {
@@ -1142,23 +1145,16 @@ template <bool kSmemTable, int kArgs, bool kHasSel>
 cudaError_t launch_call_batch_variant(const DeviceImage& img, const LaunchPlan& plan, int blocks,
                                       const ClientBatch& batch, const int64_t* args,
                                       const uint8_t* method_sel, size_t n, ptype_reply* replies,
-                                      const CallBatchOut& o, cudaStream_t stream) {
+                                      const CallBatchOut& o, cudaStream_t stream, bool pdl) {
     uint4* r = reinterpret_cast<uint4*>(replies);
     unsigned long long* values = reinterpret_cast<unsigned long long*>(o.values);
     uint2* failed = reinterpret_cast<uint2*>(o.failed);
-    if (plan.threads == kMaxThreads) {
-        auto kernel = call_batch_kernel<kSmemTable, kArgs, kHasSel, 2, kMaxThreads, 1>;
-        if (plan.dyn_smem > 48 * 1024) {
-            cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 static_cast<int>(plan.dyn_smem));
-            if (e != cudaSuccess) return e;
-        }
-        return launch_kernel(kernel, blocks, plan.threads, plan.dyn_smem, stream, img, batch, args,
-                             method_sel, n, r, values, failed, o.failed_cap, o.failed_count, o.done_ctas,
-                             o.host_count);
-    }
+    if (plan.threads == kMaxThreads)
+        return launch_kernel(call_batch_kernel<kSmemTable, kArgs, kHasSel, 2, kMaxThreads, 1>, blocks,
+                             plan.threads, plan.dyn_smem, stream, pdl, img, batch, args, method_sel, n, r,
+                             values, failed, o.failed_cap, o.failed_count, o.done_ctas, o.host_count);
     return launch_kernel(call_batch_kernel<kSmemTable, kArgs, kHasSel, 2, kSmallThreads, kSmallMinCtas>,
-                         blocks, plan.threads, plan.dyn_smem, stream, img, batch, args, method_sel, n, r,
+                         blocks, plan.threads, plan.dyn_smem, stream, pdl, img, batch, args, method_sel, n, r,
                          values, failed, o.failed_cap, o.failed_count, o.done_ctas, o.host_count);
 }
 }  // namespace
@@ -1168,7 +1164,7 @@ cudaError_t launch_call_batch(const DeviceImage& img, const LaunchPlan& plan, in
                               uint64_t svc_key, uint64_t seq_base, const uint32_t* methods,
                               const uint32_t* recvs, int n_methods, const int64_t* args,
                               int args_per_call, const uint8_t* method_sel, size_t n,
-                              ptype_reply* replies, const CallBatchOut& out, cudaStream_t stream) {
+                              ptype_reply* replies, const CallBatchOut& out, cudaStream_t stream, bool pdl) {
     ClientBatch batch = {};
     batch.svc_key = svc_key;
     batch.seq_base = seq_base;
@@ -1179,7 +1175,7 @@ cudaError_t launch_call_batch(const DeviceImage& img, const LaunchPlan& plan, in
     }
     const bool sel = method_sel != nullptr;
 #define PTYPE_CB(SM, AR, SEL) \
-    launch_call_batch_variant<SM, AR, SEL>(img, plan, blocks, batch, args, method_sel, n, replies, out, stream)
+    launch_call_batch_variant<SM, AR, SEL>(img, plan, blocks, batch, args, method_sel, n, replies, out, stream, pdl)
     if (plan.smem_table) {
         if (args_per_call == 2) return sel ? PTYPE_CB(true, 2, true) : PTYPE_CB(true, 2, false);
         return sel ? PTYPE_CB(true, 3, true) : PTYPE_CB(true, 3, false);

@@ -128,17 +128,6 @@ static int compute_placement(ptype_builder* b) {
         pl.total_nodes += rec.nodes.size();
     }
 
-    // Pick a salt under which all registered names have distinct 64-bit keys (H7).
-    pl.keys.assign(n_services, 0);
-    for (pl.salt = 0;; ++pl.salt) {
-        if (pl.salt == 64) return PTYPE_E_COLLISION;
-        for (size_t i = 0; i < n_services; ++i)
-            pl.keys[i] = ptype::fnv1a64(pl.order[i]->first.data(), pl.order[i]->first.size(), pl.salt);
-        std::vector<uint64_t> sorted(pl.keys);
-        std::sort(sorted.begin(), sorted.end());
-        if (std::adjacent_find(sorted.begin(), sorted.end()) == sorted.end()) break;
-    }
-
     // Table size: half full when that fits the shared-memory budget, otherwise
     // fill the budget (up to 80 % load: 3-way cuckoo places that reliably), otherwise
     // a half-full table probed in L2.
@@ -155,42 +144,59 @@ static int compute_placement(ptype_builder* b) {
         pl.n_slots = static_cast<uint32_t>(want);
     }
 
-    // Random-walk insertion; a walk that does not settle restarts the whole table under the
-    // next seed.  `table` holds service indices while placing.
+    // Pick a salt under which all registered names have distinct 64-bit keys (H7) AND the cuckoo
+    // placement settles.  The three candidate slots of a key depend on its 32-bit fold only, so
+    // four names whose keys fold alike can never be placed under any table seed; a new salt gives
+    // them new keys (and folds), which is why a placement failure moves on to the next salt.
     constexpr uint32_t kFree = 0xFFFFFFFFu;
+    constexpr uint32_t kSeedsPerSalt = 8;
     std::vector<uint32_t> table;
-    for (pl.table_seed = 0;; ++pl.table_seed) {
-        if (pl.table_seed == 32) return PTYPE_E_COLLISION;
-        table.assign(pl.n_slots, kFree);
-        uint64_t rng = 0x9E3779B97F4A7C15ull ^ pl.table_seed;
-        bool ok = true;
-        for (size_t i = 0; i < n_services && ok; ++i) {
-            uint32_t cur = static_cast<uint32_t>(i);
-            ok = false;
-            for (int kick = 0; kick < 2000; ++kick) {
-                const uint64_t key = pl.keys[cur];
-                const uint32_t lo = static_cast<uint32_t>(key), hi = static_cast<uint32_t>(key >> 32);
-                uint32_t cand[PTYPE_SLOT_WAYS];
-                bool placed = false;
-                for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
-                    cand[w] = ptype::slot_of(lo, hi, pl.table_seed, w, pl.n_slots);
-                    if (table[cand[w]] == kFree) {
-                        table[cand[w]] = cur;
-                        placed = true;
+    pl.keys.assign(n_services, 0);
+    bool placed_all = false;
+    for (pl.salt = 0; !placed_all; ++pl.salt) {
+        if (pl.salt == 64) return PTYPE_E_COLLISION;
+        for (size_t i = 0; i < n_services; ++i)
+            pl.keys[i] = ptype::fnv1a64(pl.order[i]->first.data(), pl.order[i]->first.size(), pl.salt);
+        std::vector<uint64_t> sorted(pl.keys);
+        std::sort(sorted.begin(), sorted.end());
+        if (std::adjacent_find(sorted.begin(), sorted.end()) != sorted.end()) continue;
+
+        // Random-walk insertion; a walk that does not settle restarts the whole table under the
+        // next seed.  `table` holds service indices while placing.
+        for (pl.table_seed = 0; pl.table_seed < kSeedsPerSalt && !placed_all; ++pl.table_seed) {
+            table.assign(pl.n_slots, kFree);
+            uint64_t rng = 0x9E3779B97F4A7C15ull ^ pl.table_seed;
+            bool ok = true;
+            for (size_t i = 0; i < n_services && ok; ++i) {
+                uint32_t cur = static_cast<uint32_t>(i);
+                ok = false;
+                for (int kick = 0; kick < 2000; ++kick) {
+                    const uint64_t key = pl.keys[cur];
+                    const uint32_t lo = static_cast<uint32_t>(key), hi = static_cast<uint32_t>(key >> 32);
+                    uint32_t cand[PTYPE_SLOT_WAYS];
+                    bool placed = false;
+                    for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
+                        cand[w] = ptype::slot_of(lo, hi, pl.table_seed, w, pl.n_slots);
+                        if (table[cand[w]] == kFree) {
+                            table[cand[w]] = cur;
+                            placed = true;
+                            break;
+                        }
+                    }
+                    if (placed) {
+                        ok = true;
                         break;
                     }
+                    rng = rng * 6364136223846793005ull + 1442695040888963407ull;
+                    const uint32_t victim = cand[(rng >> 33) % PTYPE_SLOT_WAYS];
+                    std::swap(cur, table[victim]);
                 }
-                if (placed) {
-                    ok = true;
-                    break;
-                }
-                rng = rng * 6364136223846793005ull + 1442695040888963407ull;
-                const uint32_t victim = cand[(rng >> 33) % PTYPE_SLOT_WAYS];
-                std::swap(cur, table[victim]);
             }
+            placed_all = ok;
         }
-        if (ok) break;
+        if (placed_all) break;  // keep pl.salt; pl.table_seed is one past the seed that worked
     }
+    pl.table_seed -= 1;
     pl.slot_index.assign(n_services, 0);
     for (uint32_t s = 0; s < pl.n_slots; ++s)
         if (table[s] != kFree) pl.slot_index[table[s]] = s;
@@ -340,6 +346,8 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     off += n_methods * sizeof(ptype_method);
     const size_t off_mtable = off;
     off += PTYPE_MTABLE_SLOTS * sizeof(ptype_method);
+    const size_t off_order = off;
+    off = align_up(off + static_cast<size_t>(n_slots) * sizeof(uint32_t), 16);
     const size_t device_bytes = off;
     const bool host_sections = !b->device_only;
     const size_t off_services = off;
@@ -397,6 +405,12 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
         e.node_base = services[i].node_base;
         e.n_and_recv = services[i].n_nodes | (services[i].recv_mask << 24);
     }
+    // Key-order rank per slot: global node ids are ranks in the sorted key range, so a node joining
+    // or leaving service r moves the ids of exactly the services whose rank exceeds r - including
+    // node-less ones, which node_base alone cannot order (ptype_b200_update_service).
+    uint32_t* order = reinterpret_cast<uint32_t*>(blob + off_order);
+    for (uint32_t i = 0; i < n_slots; ++i) order[i] = PTYPE_SLOT_EMPTY;
+    for (size_t i = 0; i < n_services; ++i) order[pl.slot_index[i]] = static_cast<uint32_t>(i);
     uint32_t* conn = reinterpret_cast<uint32_t*>(blob + off_conn);
     for (uint32_t i = 0; i < n_conn; ++i)
         conn[i] = ptype_b200_conn_hash(b->local_addr.c_str(), static_cast<int>(i));
@@ -467,6 +481,7 @@ int ptype_b200_builder_finish(ptype_builder* b, uint64_t epoch, void** image, si
     h->table_seed = table_seed;
     h->method_mul = method_mul;
     h->off_mtable = static_cast<uint32_t>(off_mtable);
+    h->off_order = static_cast<uint32_t>(off_order);
     std::snprintf(h->local_addr, sizeof h->local_addr, "%s", b->local_addr.c_str());
     h->body_checksum = ptype::image_body_hash(blob + sizeof(ptype_image_header),
                                               total - sizeof(ptype_image_header));
@@ -490,6 +505,8 @@ int ptype_b200_image_validate(const void* image, size_t bytes) {
         !inside(h->off_methods, uint64_t(h->n_methods) * sizeof(ptype_method)) ||
         !inside(h->off_mtable, uint64_t(PTYPE_MTABLE_SLOTS) * sizeof(ptype_method)) ||
         (h->off_mtable & 15u) || !(h->method_mul & 1u) ||
+        !inside(h->off_order, uint64_t(h->n_slots) * 4) || (h->off_order & 3u) ||
+        h->device_bytes < h->off_order + uint64_t(h->n_slots) * 4 ||
         (h->host_sections && (!inside(h->off_services, uint64_t(h->n_services) * sizeof(ptype_service)) ||
                               !inside(h->off_nodes, uint64_t(h->n_nodes) * sizeof(ptype_node)))) ||
         !inside(h->off_strings, h->strings_bytes) || h->device_bytes > bytes ||

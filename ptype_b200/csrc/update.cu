@@ -17,14 +17,16 @@ namespace ptype {
 namespace {
 
 // One CTA.  Phase 1: find the service's slot among its three cuckoo candidates.  Phase 2: walk
-// the table: the service's own count changes by `delta`, every other service whose nodes come
-// after it in key order moves its base by `delta`.  result[0] = 0 ok, 1 unknown service,
-// 2 count would leave [0, 2^24).
+// the table: the service's own count changes by `delta`, every service that sorts after it in
+// etcd key order (order[]: the rank the image builder recorded per slot) moves its base by
+// `delta`.  Ranks, not bases, decide: node-less services share their base with a neighbour.
+// result[0] = 0 ok, 1 unknown service, 2 count would leave [0, 2^24).
 __global__ void __launch_bounds__(1024)
-    patch_service_kernel(ptype_slot* __restrict__ slots, const uint32_t n_slots, const uint32_t seed,
+    patch_service_kernel(ptype_slot* __restrict__ slots, const uint32_t* __restrict__ order,
+                         const uint32_t n_slots, const uint32_t seed,
                          const uint32_t key_lo, const uint32_t key_hi, const int delta,
                          uint32_t* __restrict__ result) {
-    __shared__ uint32_t s_at, s_base, s_n;
+    __shared__ uint32_t s_at, s_n;
     if (threadIdx.x == 0) s_at = PTYPE_SLOT_EMPTY;
     __syncthreads();
     if (threadIdx.x < PTYPE_SLOT_WAYS) {
@@ -33,7 +35,6 @@ __global__ void __launch_bounds__(1024)
         if (s.node_base != PTYPE_SLOT_EMPTY && static_cast<uint32_t>(s.key) == key_lo &&
             static_cast<uint32_t>(s.key >> 32) == key_hi) {
             s_at = at;  // duplicates among the candidates name the same slot
-            s_base = s.node_base;
             s_n = s.n_and_recv & 0xFFFFFFu;
         }
     }
@@ -47,14 +48,14 @@ __global__ void __launch_bounds__(1024)
         if (threadIdx.x == 0) result[0] = 2;
         return;
     }
-    const uint32_t pivot = s_base + s_n;  // first global id past the service's nodes
+    const uint32_t rank = order[s_at];
     for (uint32_t i = threadIdx.x; i < n_slots; i += blockDim.x) {
         ptype_slot s = slots[i];
         if (s.node_base == PTYPE_SLOT_EMPTY) continue;
         if (i == s_at) {
             s.n_and_recv = (s.n_and_recv & 0xFF000000u) | static_cast<uint32_t>(n_new);
             slots[i] = s;
-        } else if (s.node_base >= pivot) {
+        } else if (order[i] > rank) {
             s.node_base = static_cast<uint32_t>(static_cast<long long>(s.node_base) + delta);
             slots[i] = s;
         }
@@ -64,9 +65,9 @@ __global__ void __launch_bounds__(1024)
 
 }  // namespace
 
-cudaError_t launch_patch_service(ptype_slot* slots, uint32_t n_slots, uint32_t seed, uint64_t key, int delta,
-                                 uint32_t* result, cudaStream_t stream) {
-    patch_service_kernel<<<1, 1024, 0, stream>>>(slots, n_slots, seed, static_cast<uint32_t>(key),
+cudaError_t launch_patch_service(ptype_slot* slots, const uint32_t* order, uint32_t n_slots, uint32_t seed,
+                                 uint64_t key, int delta, uint32_t* result, cudaStream_t stream) {
+    patch_service_kernel<<<1, 1024, 0, stream>>>(slots, order, n_slots, seed, static_cast<uint32_t>(key),
                                                   static_cast<uint32_t>(key >> 32), delta, result);
     return cudaGetLastError();
 }

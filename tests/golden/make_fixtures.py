@@ -15,7 +15,7 @@ ROOT = Path(__file__).resolve().parents[2]
 sys.path.insert(0, str(ROOT))
 
 from oracle import binding as ob          # noqa: E402
-import ptype_b200.workloads as w          # noqa: E402
+import workloads as w          # noqa: E402
 
 out = {}
 cases = {

@@ -20,7 +20,10 @@ def test_reference_arm_json_line():
     assert line["cpu_baseline"]["value"] == line["value"]
     assert line["e2e"] == {"value": line["value"], "unit": "calls/s", "h2d_bytes_per_step": 0,
                            "d2h_bytes_per_step": 0}
-    assert "no Go toolchain" in line["config"]["note"]
+    assert "no Go toolchain" in line["note"]
+    # the CPU arm depends on nothing of the product: only the oracle's library is mapped
+    assert line["in_tree_libs_loaded"] == ["oracle/_build/libptype_oracle.so"]
+    assert set(line["config"]) == {"workload", "batch_calls_per_gpu", "resident_batches", "l2"}
     # config 1: the reference's real path restated over loopback TCP
     assert line["loopback_1_caller"]["value"] > 0 and line["loopback_all_threads"]["value"] > 0
     assert 30 < line["loopback_1_caller"]["bytes_per_call_out"] < 120

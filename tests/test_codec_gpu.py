@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 import ptype_b200 as p
-from ptype_b200 import workloads as w
+import workloads as w
 
 pytestmark = pytest.mark.gpu
 

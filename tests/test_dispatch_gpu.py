@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 import ptype_b200 as p
-from ptype_b200 import workloads as w
+import workloads as w
 from ptype_b200.sharding import shard_indices
 
 pytestmark = pytest.mark.gpu

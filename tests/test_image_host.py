@@ -8,7 +8,8 @@ import numpy as np
 import pytest
 
 import ptype_b200 as p
-from ptype_b200 import _abi, workloads as w
+from ptype_b200 import _abi
+import workloads as w
 from ptype_b200.sharding import shard_of, shard_indices
 
 ROOT = Path(__file__).resolve().parent.parent
@@ -31,6 +32,17 @@ def test_record_layouts():
     assert [p.REQ_DTYPE.fields[f][1] for f in ("svc_key", "seq", "method", "recv", "a0", "a1", "a2")] == \
         [0, 8, 16, 20, 24, 32, 40]
     assert [p.REPLY_DTYPE.fields[f][1] for f in ("value", "node", "status")] == [0, 8, 12]
+
+
+def test_workload_generators_hash_like_the_library():
+    """workloads.py hashes names in pure Python (so the CPU arm of bench.py needs no product code);
+    the keys it writes into request records must be the library's."""
+    assert w.REQ_DTYPE == p.REQ_DTYPE and w.RECV_ILL_FORMED == p.RECV_ILL_FORMED
+    for name in ["", "calculator", "prime_worker", "svc_00042", "ghost_00001", "a/b", "é"]:
+        for salt in (0, 1, 0x1234_5678_9ABC_DEF0):
+            assert w.service_key(name, salt) == p.service_key(name, salt)
+    for sm in ["Calculator.Multiply", "Calculator.Add", "Prime.Check", "nodot", "", ".", "a.b.c", ".x", "x."]:
+        assert w.method_key(sm) == p.method_key(sm), sm
 
 
 def test_hash_helpers_match_oracle(oracle):

@@ -24,7 +24,7 @@ def _worker(rank: int, world: int, port: int, out_dir: str):
     sys.path.insert(0, str(ROOT))
     import torch.distributed as dist
     import ptype_b200 as p
-    from ptype_b200 import workloads as w
+    import workloads as w
     from ptype_b200.sharding import shard_indices
     from oracle import binding as ob
 
@@ -77,7 +77,7 @@ def test_one_process_two_devices(oracle=None):
     GPUs would use the ABI): one publish installs the snapshot on both, dispatches carry the
     device index, and both devices answer like the oracle."""
     import ptype_b200 as p
-    from ptype_b200 import workloads as w
+    import workloads as w
     from oracle import binding as ob
     if p.device_count() < 2:
         pytest.skip("needs 2 GPUs")

@@ -24,7 +24,7 @@ def _worker(rank: int, world: int, port: int, out_dir: str):
     import torch
     import torch.distributed as dist
     import ptype_b200 as p
-    from ptype_b200 import workloads as w
+    import workloads as w
     from ptype_b200.sharding import shard_indices
     from oracle import binding as ob
 

@@ -98,7 +98,7 @@ def test_wrapping_multiply(oracle):
 
 
 def test_check_chunks(oracle):
-    import ptype_b200.workloads as w
+    import workloads as w
     for t, want in DER["check_chunks"].items():
         chunks = w.split_work(int(t))
         buf = (C.c_int64 * (3 * 64))()
@@ -148,7 +148,7 @@ def test_json_unmarshal_rules(oracle):
 
 
 def test_client_call_statuses(oracle):
-    import ptype_b200.workloads as w
+    import workloads as w
     spec = w.calculator_registry()
     spec.declare = ["ghost"]
     kv, snap = oracle.snapshot_from_spec(spec)
@@ -165,7 +165,7 @@ def test_client_call_statuses(oracle):
 
 def test_golden_fixtures_match_oracle(oracle):
     """The committed fixture replies are what the oracle says today."""
-    import ptype_b200.workloads as w
+    import workloads as w
     fx = np.load(GOLD / "dispatch_fixtures.npz")
     for name, spec in (("calc3", w.calculator_registry()), ("calcmesh", w.calculator_registry(mesh=True)),
                        ("optimus", w.optimus_registry())):
@@ -197,7 +197,7 @@ def test_loopback_calls_match_in_process_oracle(oracle):
     """Config 1 in miniature: sequential synchronous calls through TCP 127.0.0.1, the
     CONNECT /_goRPC_ handshake and gob framing give the replies of the in-process oracle, and
     the connection used is roundRobinSelect's (first call -> index 1 of 3, rpc_test.go:118-158)."""
-    import ptype_b200.workloads as w
+    import workloads as w
     spec = w.calculator_registry()
     kv, snap = oracle.snapshot_from_spec(spec)
     reqs = w.calculator_calls(3000)
@@ -223,7 +223,7 @@ def test_assign_seq_is_n_sequential_calls(oracle):
     calls that find a non-empty client list (rpc.go:177-182), values taken in batch order; and
     against the reference's own fixed point - a fresh Client's first call draws 1, so with two
     nodes it lands on index 1 (rpc_test.go:118-158)."""
-    import ptype_b200.workloads as w
+    import workloads as w
     from ptype_b200 import service_key
     spec = w.RegistrySpec([("a", "n1", "h", 1), ("a", "n2", "h", 2), ("b", "n1", "h", 3)], [("a", "Calculator")],
                           ["empty"], "", 3)

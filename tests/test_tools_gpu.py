@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("mesh", [0, 1])
 def test_cpp_driver_checksum_matches_oracle(oracle, mesh):
-    import ptype_b200.workloads as w
+    import workloads as w
     subprocess.run(["make", "-C", str(ROOT / "tools")], check=True, capture_output=True)
     n = 300_000
     out = subprocess.run([str(ROOT / "tools" / "ptype_b200_bench"), str(n), "50", "3", str(mesh)],

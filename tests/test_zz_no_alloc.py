@@ -30,18 +30,19 @@ def random_replies(n: int, seed: int) -> np.ndarray:
     return rep
 
 
-def noalloc_checksum(ctx, d_rep, n, index_base, d_out) -> int:
+def noalloc_checksum(ctx, d_rep, n, index_base, d_out, device=0) -> int:
     """Call the entry point through the C ABI on the context's stream, then read the result."""
-    rc = _abi.lib.ptype_b200_reply_checksum_noalloc(0, d_rep.ptr, n, index_base, d_out.ptr, ctx.stream())
+    rc = _abi.lib.ptype_b200_reply_checksum_noalloc(device, d_rep.ptr, n, index_base, d_out.ptr, ctx.stream())
     assert rc == 0, _abi.lib.ptype_b200_last_error().decode()
     ctx.sync()
     return int(d_out.download(np.uint64, 1)[0])
 
 
-def test_noalloc_matches_allocating_entry_point_twice():
+def test_noalloc_matches_allocating_entry_point_twice(oracle):
     """Two calls in a row — the second smaller than the first, so stale partial sums from
     the first call sit in the shared array — must both equal ptype_b200_reply_checksum
-    exactly (integer result: the tolerance is zero, as in every other test here)."""
+    exactly (integer result: the tolerance is zero, as in every other test here), and
+    both must equal the checksum the CPU oracle computes for the same records."""
     ctx = p.Context([0])
     try:
         d_out = ctx.device_buffer(8)
@@ -49,6 +50,7 @@ def test_noalloc_matches_allocating_entry_point_twice():
             rep = random_replies(n, seed)
             d_rep = ctx.device_buffer(max(n, 1) * 16).upload(rep) if n else ctx.device_buffer(16)
             want = ctx.reply_checksum(d_rep, n, index_base=base, device=True)
+            assert want == oracle.reply_checksum(rep, base)
             assert noalloc_checksum(ctx, d_rep, n, base, d_out) == want
             assert noalloc_checksum(ctx, d_rep, n, base, d_out) == want   # and again, same array
             d_rep.free()
@@ -70,3 +72,36 @@ def test_noalloc_rejects_sizes_beyond_the_scratch_array():
         d.free()
     finally:
         ctx.close()
+
+
+def test_noalloc_on_a_gpu_that_is_not_the_current_one(oracle):
+    """Each GPU has its own copy of the built-in array, looked up on that GPU's first call.
+    Asking for GPU 1 while GPU 0 is the thread's current device (and the other way round) must
+    use the right copy and leave the caller's current device as it was.  Needs two GPUs."""
+    import torch
+    if p.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    rep = random_replies(1_234_567, 9)
+    want = oracle.reply_checksum(rep, 42)
+    ctxs = {dev: p.Context([dev]) for dev in (0, 1)}
+    try:
+        for current, target in ((0, 1), (1, 0), (1, 1), (0, 0)):
+            torch.cuda.set_device(current)
+            ctx = ctxs[target]
+            d_rep = ctx.device_buffer(len(rep) * 16).upload(rep)
+            d_out = ctx.device_buffer(8)
+            torch.cuda.set_device(current)   # the context calls above may have moved it
+            for _ in range(2):
+                assert noalloc_checksum(ctx, d_rep, len(rep), 42, d_out, device=target) == want
+            d_rep.free()
+            d_out.free()
+        torch.cuda.set_device(0)
+        before = torch.cuda.current_device()
+        d = ctxs[1].device_buffer(16)
+        torch.cuda.set_device(0)
+        assert _abi.lib.ptype_b200_reply_checksum_noalloc(1, d.ptr, 0, 0, d.ptr, None) == 0
+        assert torch.cuda.current_device() == before == 0
+        d.free()
+    finally:
+        for c in ctxs.values():
+            c.close()

@@ -12,7 +12,7 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import ptype_b200 as p  # noqa: E402
-from ptype_b200 import workloads as wl  # noqa: E402
+import workloads as wl  # noqa: E402
 
 
 def main() -> None:

@@ -1,7 +1,9 @@
 """Synthetic registries and call streams for the BASELINE.json configs.
 
-Pure data generation (numpy); nothing here computes a reply.  PRNG: splitmix64,
-seed 0x5eed0000 + config number, little-endian records.
+Pure data generation (numpy and pure-Python FNV); nothing here computes a reply and nothing
+here loads libptype_b200.so or the oracle, so both arms of bench.py, the tests and the tools
+build their inputs from the same code without depending on the thing they measure.  PRNG:
+splitmix64, seed 0x5eed0000 + config number, little-endian records.
 """
 from __future__ import annotations
 
@@ -10,8 +12,35 @@ from typing import List, Tuple
 
 import numpy as np
 
-from ._abi import REQ_DTYPE, RECV_ILL_FORMED
-from .snapshot import Image, build_image, method_key, service_key
+# Record layout of include/ptype_b200.h (ptype_req, 48 bytes).
+REQ_DTYPE = np.dtype(
+    [("svc_key", "<u8"), ("seq", "<u8"), ("method", "<u4"), ("recv", "<u4"),
+     ("a0", "<i8"), ("a1", "<i8"), ("a2", "<i8")], align=False)
+RECV_ILL_FORMED = 0xFFFFFFFF
+
+
+def fnv1a32(data: bytes) -> int:
+    """hash/fnv New32a [Go stdlib]; the reference's one explicit hash (cluster/rpc.go:267)."""
+    h = 0x811C9DC5
+    for b in data:
+        h = ((h ^ b) * 0x01000193) & 0xFFFFFFFF
+    return h
+
+
+def service_key(name: str, salt: int = 0) -> int:
+    """FNV-1a-64 of a cluster service name, offset basis xor-ed with the image's key salt
+    (include/ptype_b200.h: ptype_b200_service_key; equality is pinned by tests/test_image_host.py)."""
+    h = 0xCBF29CE484222325 ^ salt
+    for b in name.encode():
+        h = ((h ^ b) * 0x100000001B3) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def method_key(service_method: str) -> Tuple[int, int]:
+    """(method, recv) hashes of "Receiver.Method", split at the last '.' like net/rpc's server."""
+    raw = service_method.encode()
+    dot = raw.rfind(b".")
+    return fnv1a32(raw), (fnv1a32(raw[:dot]) if dot >= 0 else RECV_ILL_FORMED)
 
 _GAMMA = np.uint64(0x9E3779B97F4A7C15)
 
@@ -35,7 +64,9 @@ class RegistrySpec:
     local_addr: str = ""
     max_connections: int = 3
 
-    def image(self, epoch: int = 1, n_slots: int = 0) -> Image:
+    def image(self, epoch: int = 1, n_slots: int = 0):
+        """The registry image of this spec (needs the product library: imported here only)."""
+        from ptype_b200.snapshot import build_image
         return build_image(self.nodes, local_addr=self.local_addr,
                            max_connections=self.max_connections, expose=self.expose,
                            declare=self.declare, epoch=epoch, n_slots=n_slots)
