@@ -416,13 +416,16 @@ def measure(ctx, env, workload: str, *, steps: int, warmup: int, nbuf: int, batc
     # the K timed steps are submitted by C calls (ptype_b200_dispatch_batches): no Python between launches
     every = max(update_every, 1)
 
-    def run_steps(k: int):
+    def plan_steps(k: int):
+        """The ptype_batch arrays of k steps, built ahead so that no Python runs between launches."""
         if not live:
-            ctx.dispatch_batches(batches_of(0, k), flags=flags, sync=False)
-            return
-        for lo in range(0, k, every):
-            ctx.dispatch_batches(batches_of(lo, min(lo + every, k)), flags=flags, sync=False)
-            if lo + every < k:
+            return [batches_of(0, k)]
+        return [batches_of(lo, min(lo + every, k)) for lo in range(0, k, every)]
+
+    def run_steps(segments):
+        for i, seg in enumerate(segments):
+            ctx.dispatch_batches(seg, flags=flags, sync=False)
+            if live and i + 1 < len(segments):
                 live_update()
 
     # ---- warm-up: W single steps, then one pass of exactly what is timed (same kernel instances,
@@ -431,18 +434,21 @@ def measure(ctx, env, workload: str, *, steps: int, warmup: int, nbuf: int, batc
         step(i)
     if live:
         live_update()
-    run_steps(steps if not live else min(steps, 2 * every + 1))
+    run_steps(plan_steps(steps if not live else min(steps, 2 * every + 1)))
+    timed = plan_steps(steps)
+    preroll = batches_of(0, min(32, steps))
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     env.barrier(ctx)
     update_ms.clear()
-    # A short pre-roll keeps the GPU busy while the host enqueues the start event and the first
-    # timed launch: the timed region then starts when the pre-roll ends, not after a host launch
-    # latency on an idle GPU.  (The event between the two launches keeps them from overlapping.)
-    ctx.dispatch_batches(batches_of(0, min(8, steps)), flags=flags, sync=False)
+    # A pre-roll (untimed, at most 32 batches) keeps the GPU busy while the host enqueues the start
+    # event and the first timed launch: the timed region then starts when the pre-roll ends, not
+    # after a host launch latency on an idle GPU.  (The event between the two launches keeps them
+    # from overlapping.)
+    ctx.dispatch_batches(preroll, flags=flags, sync=False)
     launches0 = ctx.launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     w0 = time.perf_counter()
     ev0.record(ext)
-    run_steps(steps)
+    run_steps(timed)
     host_enqueue_s = time.perf_counter() - w0
     ev1.record(ext)
     env.barrier(ctx)
@@ -656,9 +662,14 @@ def mirror_e2e(env, args, workload: str, batch: int, steps: int):
     calls = float(kv.get("calls", 0.0))
     all_ok = all(env.gather(bool(kv) and kv.get("parity") == "ok"))
     secs_max, calls_all = env.reduce(secs, "max"), env.reduce(calls, "sum")
+    arr_secs = env.reduce(float(kv.get("array_seconds", 0.0)), "max")
+    arr_calls = env.reduce(float(kv.get("array_calls", 0.0)), "sum")
     if not all_ok or secs_max <= 0:
         return {"value": None, "error": "tools/ptype_b200_bench mirror failed or its replies were wrong"}
     return {"value": calls_all / secs_max, "unit": "calls/s", "steps": steps,
+            "array_form": {"value": arr_calls / arr_secs if arr_secs > 0 else None, "unit": "calls/s",
+                           "api": "cluster::Client::CallBatch(method, int64[n][3], n, BatchReply*): arguments "
+                                  "copied into the pooled batch, 16-byte reply records unpacked, one host thread"},
             "h2d_bytes_per_step": int(float(kv.get("h2d_bytes_per_step", 0))),
             "d2h_bytes_per_step": int(float(kv.get("d2h_bytes_per_step", 0))),
             "api": "cluster::Client::CallBatch (C++ mirror of cluster/rpc.go:59-67) -> ptype_b200_call_batch_values"}
@@ -802,8 +813,8 @@ def main():
                                       if multi else "single GPU",
                           "table": "shared memory" if not (args.flags & 4) else "global/L2",
                           "calls_per_gpu_per_step": m["per_launch_calls"],
-                          "warm": "W single-launch steps, one untimed pass of the timed launch list, an 8-batch "
-                                  "pre-roll in flight when the start event is recorded"},
+                          "warm": "W single-launch steps, one untimed pass of the timed launch list, a pre-roll of "
+                                  "min(32, K) batches in flight when the start event is recorded"},
             "roofline": {"bound": "hbm", "achieved": m["achieved_gbs"], "peak": m["peak"], "unit": "GB/s",
                          "frac": m["achieved_gbs"] / m["peak"], "traffic": traffic, "traffic_note": traffic_note,
                          "peak_kind": m["peak_kind"],

@@ -192,6 +192,54 @@ func (d *Dispatcher) publishLocked() error {
 	return nil
 }
 
+// Snapshot publication through the KV store (SURVEY.md 8f N3).  One host builds the registry image
+// (SetNodes) and publishes it under store/registry_image/<epoch>; every other host of the
+// deployment installs the newest epoch, so all GPUs answer from the same bytes.  Only the
+// unchanged KVStore.Put / KVStore.Get (store.go:38-62) are used; etcd values are byte strings,
+// so the blob travels as it is.
+const imageKeyPrefix = "registry_image/"
+
+// PublishImage stores the image this Dispatcher last built.
+func (d *Dispatcher) PublishImage(ctx context.Context, store *KVStore) error {
+	d.mu.Lock()
+	defer d.mu.Unlock()
+	if d.image == nil {
+		return errors.New("ptype_b200: no image built yet")
+	}
+	h := (*C.ptype_image_header)(d.image)
+	blob := C.GoBytes(d.image, C.int(h.total_bytes))
+	return store.Put(ctx, fmt.Sprintf("%s%020d", imageKeyPrefix, uint64(h.epoch)), string(blob))
+}
+
+// LoadLatestImage installs the newest published image on this Dispatcher's GPU and returns its
+// epoch.  ErrNoKey when nothing has been published.  A Dispatcher that follows a publisher this
+// way does not call SetNodes itself.
+func (d *Dispatcher) LoadLatestImage(ctx context.Context, store *KVStore) (uint64, error) {
+	vals, err := store.Get(ctx, imageKeyPrefix, WithPrefix(), WithSort(SortByKey, SortDescend), WithLimit(1))
+	if err != nil {
+		return 0, err
+	}
+	blob := C.CBytes([]byte(vals[0])) // malloc'ed copy: ptype_b200_image_free is free()
+	size := C.size_t(len(vals[0]))
+	if err := abiError("ptype_b200_image_validate", C.ptype_b200_image_validate(blob, size)); err != nil {
+		C.free(blob)
+		return 0, err
+	}
+	d.mu.Lock()
+	defer d.mu.Unlock()
+	if err := abiError("ptype_b200_publish_image", C.ptype_b200_publish_image(d.ctx, blob, size)); err != nil {
+		C.free(blob)
+		return 0, err
+	}
+	if d.image != nil {
+		C.ptype_b200_image_free(d.image)
+	}
+	d.image = blob
+	h := (*C.ptype_image_header)(blob)
+	d.epoch, d.salt = uint64(h.epoch), uint64(h.key_salt)
+	return d.epoch, nil
+}
+
 // UpdateService applies one watch event in place: a node joined (+1) or left (-1) `service`.
 // The table is patched on the GPU (ptype_b200_update_service); nothing is rebuilt or uploaded.
 // The Dispatcher's own node lists must be kept in step by the caller (SetNodes does both).
@@ -328,6 +376,12 @@ type BatchClient struct {
 	errChan   chan error
 	updated   chan struct{}
 	waitGroup sync.WaitGroup
+
+	poolMu sync.Mutex
+	pool   []*Batch
+
+	coalescerOnce sync.Once
+	coalescer     *Coalescer // started by the first Go()
 }
 
 // NewBatchClient mirrors newClient/newConnectionBalancer (rpc.go:45-57,141-170).
@@ -395,6 +449,15 @@ func (c *BatchClient) ConnectionErrs() chan error { return c.errChan }
 func (c *BatchClient) Close() error {
 	c.cancel()
 	c.waitGroup.Wait()
+	if c.coalescer != nil {
+		c.coalescer.Close()
+	}
+	c.poolMu.Lock()
+	for _, b := range c.pool {
+		b.Free()
+	}
+	c.pool = nil
+	c.poolMu.Unlock()
 	close(c.errChan)
 	return nil
 }
@@ -412,10 +475,179 @@ func (c *BatchClient) Call(serviceMethod string, args [3]int64, reply *int64) er
 	return nil
 }
 
-// CallBatch issues len(args) calls of one method.  The sequence range is reserved with ONE
-// atomic add, so routing equals len(args) sequential Call()s.  Failed calls are re-issued with
-// fresh sequence numbers up to cfg.Retries more times (withRetry, rpc.go:107-116, bounded).
+// Batch is one client's set of page-locked buffers, allocated by C once and reused from call to
+// call.  The GPU reads Args/Sel and writes Values across PCIe itself, so what the caller puts in
+// the slices is what travels: 16-25 bytes per call in, 8 out - no 48-byte request records, no
+// staging copy, and no Go pointer ever reaches C (the slices are views of C memory).
+type Batch struct {
+	capacity, argsPerCall int
+	cArgs, cSel, cValues  unsafe.Pointer // ptype_b200_alloc_pinned
+	cReplies              unsafe.Pointer // 16-byte records, only for the array form of CallBatch
+	cFailed               unsafe.Pointer // C.malloc: capacity entries, never truncated
+
+	Args   []int64 // [n*argsPerCall]: calculator.Args{A,B} or prime.Args{Min,Max,Target} per call
+	Sel    []byte  // [n]: index into the method list of the call (batches naming several methods)
+	Values []int64 // [n]: *reply of every call, 0 for a call that failed
+	Failed []FailedCall
+
+	retry *Batch // the failed calls of an attempt are re-issued from here
+}
+
+// FailedCall mirrors ptype_failed: a call whose status is not StatusOK after the last attempt.
+type FailedCall struct {
+	Index  uint32
+	Status uint32
+}
+
+// NewBatch allocates buffers for up to `capacity` calls of argsPerCall (2 or 3) int64 each.
+func NewBatch(capacity, argsPerCall int) (*Batch, error) {
+	if capacity < 1 || (argsPerCall != 2 && argsPerCall != 3) {
+		return nil, errors.New("ptype_b200: bad batch shape")
+	}
+	b := &Batch{capacity: capacity, argsPerCall: argsPerCall}
+	b.cArgs = C.ptype_b200_alloc_pinned(C.size_t(capacity * argsPerCall * 8))
+	b.cSel = C.ptype_b200_alloc_pinned(C.size_t(capacity))
+	b.cValues = C.ptype_b200_alloc_pinned(C.size_t(capacity * 8))
+	b.cFailed = C.malloc(C.size_t(capacity) * C.sizeof_ptype_failed)
+	if b.cArgs == nil || b.cSel == nil || b.cValues == nil || b.cFailed == nil {
+		b.Free()
+		return nil, errors.New("ptype_b200: out of page-locked memory")
+	}
+	b.Args = (*[1 << 30]int64)(b.cArgs)[: capacity*argsPerCall : capacity*argsPerCall]
+	b.Sel = (*[1 << 30]byte)(b.cSel)[:capacity:capacity]
+	b.Values = (*[1 << 30]int64)(b.cValues)[:capacity:capacity]
+	return b, nil
+}
+
+// Free returns the buffers to C.  The slices must not be used afterwards.
+func (b *Batch) Free() {
+	C.ptype_b200_free_pinned(b.cArgs)
+	C.ptype_b200_free_pinned(b.cSel)
+	C.ptype_b200_free_pinned(b.cValues)
+	C.ptype_b200_free_pinned(b.cReplies)
+	C.free(b.cFailed)
+	b.cArgs, b.cSel, b.cValues, b.cReplies, b.cFailed = nil, nil, nil, nil, nil
+	b.Args, b.Sel, b.Values = nil, nil, nil
+	if b.retry != nil {
+		b.retry.Free()
+		b.retry = nil
+	}
+}
+
+func (c *BatchClient) serviceKey() C.uint64_t {
+	c.gpu.mu.Lock()
+	salt := c.gpu.salt
+	c.gpu.mu.Unlock()
+	cservice := C.CString(c.service)
+	defer C.free(unsafe.Pointer(cservice))
+	return C.ptype_b200_service_key(cservice, C.uint64_t(salt))
+}
+
+func methodRefs(serviceMethods []string) ([C.PTYPE_BATCH_METHODS]C.ptype_method_ref, error) {
+	var refs [C.PTYPE_BATCH_METHODS]C.ptype_method_ref
+	if len(serviceMethods) < 1 || len(serviceMethods) > C.PTYPE_BATCH_METHODS {
+		return refs, errors.New("ptype_b200: a batch names 1 to 4 methods")
+	}
+	for i, sm := range serviceMethods {
+		csm := C.CString(sm)
+		C.ptype_b200_method_key(csm, &refs[i].method, &refs[i].recv)
+		C.free(unsafe.Pointer(csm))
+	}
+	return refs, nil
+}
+
+// submitValues is one attempt of a values batch: reserve the sequence range with one atomic add
+// (rpc.go:181 batched: the first call sees base+1), one C call, collect the failed list.
+func (c *BatchClient) submitValues(key C.uint64_t, refs *[C.PTYPE_BATCH_METHODS]C.ptype_method_ref, nm int,
+	b *Batch, n int) ([]FailedCall, error) {
+	m := uint64(n)
+	base := atomic.AddUint64(&c.seq, m) - m
+	var sel *C.uint8_t
+	if nm > 1 {
+		sel = (*C.uint8_t)(b.cSel)
+	}
+	var count C.uint64_t
+	rc := C.ptype_b200_call_batch_values(c.gpu.ctx, 0, key, C.uint64_t(base), &refs[0], C.int(nm), sel,
+		(*C.int64_t)(b.cArgs), C.int(b.argsPerCall), C.size_t(n), (*C.int64_t)(b.cValues),
+		(*C.ptype_failed)(b.cFailed), C.size_t(b.capacity), &count, 0)
+	if err := abiError("ptype_b200_call_batch_values", rc); err != nil {
+		return nil, err
+	}
+	raw := (*[1 << 28]C.ptype_failed)(b.cFailed)[:int(count):int(count)]
+	failed := make([]FailedCall, int(count))
+	for i, f := range raw {
+		failed[i] = FailedCall{Index: uint32(f.index), Status: uint32(f.status)}
+	}
+	return failed, nil
+}
+
+// CallBatchValues issues the first n calls written into b, each naming serviceMethods[b.Sel[j]]
+// (b.Sel is ignored when one method is given).  Routing equals n sequential Call()s.  Results
+// are b.Values and b.Failed.  Calls that failed are re-issued, under fresh sequence numbers, up
+// to cfg.Retries more times (withRetry, rpc.go:107-116, bounded).
+func (c *BatchClient) CallBatchValues(serviceMethods []string, b *Batch, n int) error {
+	return c.callBatchValues(serviceMethods, b, n, c.cfg.Retries)
+}
+
+func (c *BatchClient) callBatchValues(serviceMethods []string, b *Batch, n, retries int) error {
+	b.Failed = b.Failed[:0]
+	if n == 0 {
+		return nil
+	}
+	if n > b.capacity {
+		return errors.New("ptype_b200: batch larger than its buffers")
+	}
+	refs, err := methodRefs(serviceMethods)
+	if err != nil {
+		return err
+	}
+	key := c.serviceKey()
+	failed, err := c.submitValues(key, &refs, len(serviceMethods), b, n)
+	if err != nil {
+		return err
+	}
+	apc := b.argsPerCall
+	for attempt := 0; attempt < retries && len(failed) > 0; attempt++ {
+		sort.Slice(failed, func(x, y int) bool { return failed[x].Index < failed[y].Index })
+		m := len(failed)
+		if b.retry == nil || b.retry.capacity < m {
+			if b.retry != nil {
+				b.retry.Free()
+			}
+			if b.retry, err = NewBatch(m, apc); err != nil {
+				return err
+			}
+		}
+		r := b.retry
+		for t, f := range failed {
+			j := int(f.Index)
+			copy(r.Args[t*apc:(t+1)*apc], b.Args[j*apc:(j+1)*apc])
+			r.Sel[t] = b.Sel[j]
+		}
+		again, err := c.submitValues(key, &refs, len(serviceMethods), r, m)
+		if err != nil {
+			return err
+		}
+		for t, f := range failed {
+			b.Values[f.Index] = r.Values[t]
+		}
+		for i := range again {
+			again[i].Index = failed[again[i].Index].Index
+		}
+		failed = again
+	}
+	b.Failed = failed
+	return nil
+}
+
+// CallBatch is the array form: len(args) calls of one method, with the routing decision of every
+// call in the reply.  Arguments are copied into a pooled Batch, the GPU writes 16-byte reply
+// records, those are unpacked; failed calls go round again like in CallBatchValues.
 func (c *BatchClient) CallBatch(serviceMethod string, args [][3]int64, replies []BatchReply) error {
+	return c.callBatch(serviceMethod, args, replies, c.cfg.Retries)
+}
+
+func (c *BatchClient) callBatch(serviceMethod string, args [][3]int64, replies []BatchReply, retries int) error {
 	n := len(args)
 	if n == 0 {
 		return nil
@@ -423,54 +655,115 @@ func (c *BatchClient) CallBatch(serviceMethod string, args [][3]int64, replies [
 	if len(replies) < n {
 		return errors.New("ptype_b200: replies shorter than args")
 	}
-	csm := C.CString(serviceMethod)
-	var method, recv C.uint32_t
-	C.ptype_b200_method_key(csm, &method, &recv)
-	C.free(unsafe.Pointer(csm))
-	c.gpu.mu.Lock()
-	salt := c.gpu.salt
-	c.gpu.mu.Unlock()
-	cservice := C.CString(c.service)
-	key := C.ptype_b200_service_key(cservice, C.uint64_t(salt))
-	C.free(unsafe.Pointer(cservice))
-
-	// C-owned pinned staging: Go memory is never handed to the asynchronous copy engine.
-	reqs := (*[1 << 30]C.ptype_req)(C.ptype_b200_alloc_pinned(C.size_t(n) * C.sizeof_ptype_req))[:n:n]
-	out := (*[1 << 30]C.ptype_reply)(C.ptype_b200_alloc_pinned(C.size_t(n) * C.sizeof_ptype_reply))[:n:n]
-	failed := (*[1 << 30]C.uint32_t)(C.ptype_b200_alloc_pinned(C.size_t(n) * 4))[:n:n]
-	defer C.ptype_b200_free_pinned(unsafe.Pointer(&reqs[0]))
-	defer C.ptype_b200_free_pinned(unsafe.Pointer(&out[0]))
-	defer C.ptype_b200_free_pinned(unsafe.Pointer(&failed[0]))
-
+	refs, err := methodRefs([]string{serviceMethod})
+	if err != nil {
+		return err
+	}
+	key := c.serviceKey()
+	apc := 2
+	for _, a := range args {
+		if a[2] != 0 {
+			apc = 3
+			break
+		}
+	}
+	b, err := c.acquire(n, apc)
+	if err != nil {
+		return err
+	}
+	defer c.release(b)
+	if b.cReplies == nil {
+		if b.cReplies = C.ptype_b200_alloc_pinned(C.size_t(b.capacity) * C.sizeof_ptype_reply); b.cReplies == nil {
+			return errors.New("ptype_b200: out of page-locked memory")
+		}
+	}
+	out := (*[1 << 28]C.ptype_reply)(b.cReplies)[:b.capacity:b.capacity]
 	todo := make([]int, n)
 	for j := range todo {
 		todo[j] = j
 	}
 	for attempt := 0; ; attempt++ {
 		m := uint64(len(todo))
-		base := atomic.AddUint64(&c.seq, m) - m // rpc.go:181, batched: first call sees base+1
 		for t, j := range todo {
-			reqs[t] = C.ptype_req{svc_key: key, seq: C.uint64_t(base + 1 + uint64(t)), method: method, recv: recv,
-				a0: C.int64_t(args[j][0]), a1: C.int64_t(args[j][1]), a2: C.int64_t(args[j][2])}
+			copy(b.Args[t*apc:(t+1)*apc], args[j][:apc])
 		}
-		var stats C.ptype_batch_stats
-		rc := C.ptype_b200_dispatch_ex(c.gpu.ctx, 0, &reqs[0], C.size_t(m), &out[0], &failed[0], C.size_t(m), &stats, 0)
-		if err := abiError("ptype_b200_dispatch_ex", rc); err != nil {
+		base := atomic.AddUint64(&c.seq, m) - m
+		rc := C.ptype_b200_call_batch(c.gpu.ctx, 0, key, C.uint64_t(base), &refs[0], 1, nil,
+			(*C.int64_t)(b.cArgs), C.int(apc), C.size_t(m), (*C.ptype_reply)(b.cReplies), 0)
+		if err := abiError("ptype_b200_call_batch", rc); err != nil {
 			return err
 		}
+		var next []int
 		for t, j := range todo {
 			replies[j] = BatchReply{Value: int64(out[t].value), Node: uint32(out[t].node), Status: uint32(out[t].status)}
+			if out[t].status != StatusOK {
+				next = append(next, j)
+			}
 		}
-		if stats.failed_count == 0 || attempt >= c.cfg.Retries {
+		if len(next) == 0 || attempt >= retries {
 			return nil
 		}
-		next := make([]int, 0, int(stats.failed_count))
-		for f := 0; f < int(stats.failed_count); f++ {
-			next = append(next, todo[int(failed[f])])
-		}
-		sort.Ints(next)
 		todo = next
 	}
+}
+
+// Batches behind the array form: Call is safe from many goroutines (rpc.go:59), so every call in
+// flight takes its own buffers from a small pool.
+func (c *BatchClient) acquire(n, apc int) (*Batch, error) {
+	c.poolMu.Lock()
+	for i, b := range c.pool {
+		if b.capacity >= n && b.argsPerCall == apc {
+			c.pool = append(c.pool[:i], c.pool[i+1:]...)
+			c.poolMu.Unlock()
+			return b, nil
+		}
+	}
+	c.poolMu.Unlock()
+	capacity := 64
+	for capacity < n {
+		capacity *= 2
+	}
+	return NewBatch(capacity, apc)
+}
+
+func (c *BatchClient) release(b *Batch) {
+	c.poolMu.Lock()
+	if len(c.pool) < 8 {
+		c.pool = append(c.pool, b)
+		b = nil
+	}
+	c.poolMu.Unlock()
+	if b != nil {
+		b.Free()
+	}
+}
+
+// Go is (*Client).Go (rpc.go:69-105): it returns at once with a *rpc.Call whose Done channel
+// receives the call when it has completed.  Like the reference it makes ONE attempt: rpc.go:91
+// tests call.Error of the outer call, still nil at that point, so the retry loop never repeats
+// (SURVEY.md D6).  A failed call is delivered with Error set and *reply untouched
+// (rpc_test.go:262-292).  The call joins the client's Coalescer, so concurrent Go()s and Call()s
+// share GPU batches instead of costing a goroutine and a launch each.
+func (c *BatchClient) Go(serviceMethod string, args [3]int64, reply *int64, done chan *rpc.Call) *rpc.Call {
+	if done == nil {
+		done = make(chan *rpc.Call, 10) // rpc.go:72-74
+	}
+	call := &rpc.Call{ServiceMethod: serviceMethod, Args: args, Reply: reply, Done: done}
+	c.coalescerOnce.Do(func() { c.coalescer = NewCoalescer(c) })
+	p := &pendingCall{method: serviceMethod, args: args, oneAttempt: true, ready: make(chan struct{})}
+	c.coalescer.in <- p
+	go func() {
+		<-p.ready
+		if p.err != nil {
+			call.Error = p.err
+		} else if err := StatusError(p.rep.Status, serviceMethod); err != nil {
+			call.Error = err
+		} else {
+			*reply = p.rep.Value
+		}
+		done <- call
+	}()
+	return call
 }
 
 // Coalescer is the dispatch loop in front of the GPU path: goroutines call Call concurrently,
@@ -485,11 +778,17 @@ type Coalescer struct {
 }
 
 type pendingCall struct {
-	method string
-	args   [3]int64
-	rep    BatchReply
-	err    error
-	ready  chan struct{}
+	method     string
+	args       [3]int64
+	oneAttempt bool // came through Go(): never retried
+	rep        BatchReply
+	err        error
+	ready      chan struct{}
+}
+
+type groupKey struct {
+	method     string
+	oneAttempt bool
 }
 
 func NewCoalescer(c *BatchClient) *Coalescer {
@@ -519,7 +818,7 @@ func (co *Coalescer) Call(serviceMethod string, args [3]int64, reply *int64) err
 func (co *Coalescer) run() {
 	defer close(co.done)
 	for first := range co.in {
-		groups := map[string][]*pendingCall{first.method: {first}}
+		groups := map[groupKey][]*pendingCall{{first.method, first.oneAttempt}: {first}}
 		n := 1
 		timer := time.NewTimer(co.MaxWait)
 	gather:
@@ -529,20 +828,25 @@ func (co *Coalescer) run() {
 				if !ok {
 					break gather
 				}
-				groups[p.method] = append(groups[p.method], p)
+				k := groupKey{p.method, p.oneAttempt}
+				groups[k] = append(groups[k], p)
 				n++
 			case <-timer.C:
 				break gather
 			}
 		}
 		timer.Stop()
-		for method, ps := range groups {
+		for k, ps := range groups {
 			args := make([][3]int64, len(ps))
 			for i, p := range ps {
 				args[i] = p.args
 			}
 			reps := make([]BatchReply, len(ps))
-			err := co.c.CallBatch(method, args, reps)
+			retries := co.c.cfg.Retries
+			if k.oneAttempt {
+				retries = 0
+			}
+			err := co.c.callBatch(k.method, args, reps, retries)
 			for i, p := range ps {
 				p.rep, p.err = reps[i], err
 				close(p.ready)

@@ -27,6 +27,7 @@
 #include <condition_variable>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <functional>
@@ -338,35 +339,28 @@ class MemRegistry : public Registry {
 };
 
 // ----------------------------------------------------------------------------- KVStore
-// cluster/store.go:14-74 over an in-memory ordered map (etcd is not in this image).  Only the
-// options the reference's tests use are mirrored: prefix, limit (sort by key ascending is the
-// map's order).  New use: the place a registry image is published so that
-// every host of a deployment loads the same snapshot epoch.
+// The slice of cluster/store.go:38-62 that snapshot publication needs: Put, and
+// Get with the prefix option, over an in-memory ordered map standing in for etcd (not in this
+// image).  Keys are filepath.Join("store", key) as in the reference.  The rest of KVStore stays in
+// Go: it is not on the dispatch path.
 inline const Error& ErrNoKey() {  // store.go:14-16
     static const Error e("Key could not be found");
     return e;
 }
-struct GetOptions {
-    bool Prefix = false;  // WithPrefix()
-    size_t Limit = 0;     // WithLimit(n), 0 = none
-};
 class KVStore {
    public:
-    // filepath.Join("store", key): joins with '/', drops a trailing '/'
-    static std::string StoreKey(const std::string& key) {
+    static std::string StoreKey(const std::string& key) {  // filepath.Join drops a trailing '/'
         std::string k = "store/" + key;
         while (k.size() > 1 && k.back() == '/') k.pop_back();
         return k;
     }
-    Error Get(const std::string& key, std::vector<std::string>* out, GetOptions opt = {}) {  // store.go:38-54
+    Error Get(const std::string& key, std::vector<std::string>* out, bool withPrefix = false) {  // store.go:38-54
         std::lock_guard<std::mutex> lk(mu_);
         out->clear();
         const std::string k = StoreKey(key);
-        if (opt.Prefix) {
-            for (auto it = kv_.lower_bound(k); it != kv_.end() && it->first.compare(0, k.size(), k) == 0; ++it) {
+        if (withPrefix) {
+            for (auto it = kv_.lower_bound(k); it != kv_.end() && it->first.compare(0, k.size(), k) == 0; ++it)
                 out->push_back(it->second);
-                if (opt.Limit && out->size() == opt.Limit) break;
-            }
         } else {
             auto it = kv_.find(k);
             if (it != kv_.end()) out->push_back(it->second);
@@ -378,15 +372,8 @@ class KVStore {
         kv_[StoreKey(key)] = value;
         return Error();
     }
-    Error Delete(const std::string& key) {  // store.go:64-74
-        std::lock_guard<std::mutex> lk(mu_);
-        return kv_.erase(StoreKey(key)) ? Error() : ErrNoKey();
-    }
-    void PutRaw(const std::string& full_key, const std::string& value) {  // the tests' tmpKV.Put
-        std::lock_guard<std::mutex> lk(mu_);
-        kv_[full_key] = value;
-    }
-    // Publish / load a registry image blob under store/registry_image/<epoch, zero padded>.
+    // A registry image under store/registry_image/<epoch, zero padded>: one host builds and
+    // publishes, every host of the deployment installs the same epoch.
     Error PublishImage(uint64_t epoch, const void* blob, size_t bytes) {
         char name[64];
         std::snprintf(name, sizeof name, "registry_image/%020llu", static_cast<unsigned long long>(epoch));
@@ -394,9 +381,7 @@ class KVStore {
     }
     Error LatestImage(std::string* blob) {
         std::vector<std::string> all;
-        GetOptions o;
-        o.Prefix = true;
-        if (Error e = Get("registry_image/", &all, o)) return e;
+        if (Error e = Get("registry_image/", &all, /*withPrefix=*/true)) return e;
         *blob = all.back();  // keys sort by epoch
         return Error();
     }
@@ -502,6 +487,33 @@ class Dispatcher {
     uint64_t Epoch() {
         std::lock_guard<std::mutex> lk(mu_);
         return epoch_;
+    }
+
+    // Snapshot publication through the KV store.  PublishImage stores the image
+    // this Dispatcher last built; LoadLatestImage, on another host (another Dispatcher), installs
+    // the newest published epoch on its GPU: both then answer from the same bytes.
+    Error PublishImage(KVStore* store) {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (!image_) return Error("ptype_b200: no image built yet");
+        const ptype_image_header* h = static_cast<const ptype_image_header*>(image_);
+        return store->PublishImage(h->epoch, image_, h->total_bytes);
+    }
+    Error LoadLatestImage(KVStore* store) {
+        std::string blob;
+        if (Error e = store->LatestImage(&blob)) return e;
+        std::lock_guard<std::mutex> lk(mu_);
+        int rc = ptype_b200_image_validate(blob.data(), blob.size());
+        if (rc == PTYPE_OK) rc = ptype_b200_publish_image(ctx_, blob.data(), blob.size());
+        if (rc != PTYPE_OK) return Error(std::string("install image: ") + ptype_b200_strerror(rc) + ": " + ptype_b200_last_error());
+        void* copy = std::malloc(blob.size());  // image_free() is free()
+        if (!copy) return Error("out of memory");
+        std::memcpy(copy, blob.data(), blob.size());
+        if (image_) ptype_b200_image_free(image_);
+        image_ = copy;
+        const ptype_image_header* h = static_cast<const ptype_image_header*>(image_);
+        epoch_ = h->epoch;
+        salt_ = h->key_salt;
+        return Error();
     }
 
     // One batch for MANY services: what a process holding one Client per service does when it
@@ -657,48 +669,141 @@ class Client {  // cluster/rpc.go:40-43,126-139
         return Error();
     }
 
-    // N calls routed exactly as N sequential Call()s: the sequence range is reserved with ONE
-    // atomic add (rpc.go:181 batched).  Per-call outcomes are in replies[j].Status; calls that
-    // failed are re-issued with fresh sequence numbers up to cfg.Retries more times (withRetry,
-    // rpc.go:107-116, bounded — see the header comment).
+    // ------------------------------------------------------------------ batches
+    // Page-locked buffers for one Client's batches, allocated once and reused from call to call.
+    // The GPU reads Args()/Sel() and writes Values() (or Replies()) across PCIe itself, so what
+    // the caller puts there is what travels: 16-25 bytes per call in, 8 out, no 48-byte request
+    // records and no staging copy.  (The Go side does the same with slices over C-owned pinned
+    // memory, which is also what the cgo pointer rules want.)
+    class Batch {
+       public:
+        Batch(size_t capacity, int argsPerCall) : cap_(capacity ? capacity : 1), apc_(argsPerCall) {
+            args_ = static_cast<int64_t*>(ptype_b200_alloc_pinned(cap_ * apc_ * sizeof(int64_t)));
+            sel_ = static_cast<uint8_t*>(ptype_b200_alloc_pinned(cap_));
+            values_ = static_cast<int64_t*>(ptype_b200_alloc_pinned(cap_ * sizeof(int64_t)));
+        }
+        ~Batch() {
+            ptype_b200_free_pinned(args_);
+            ptype_b200_free_pinned(sel_);
+            ptype_b200_free_pinned(values_);
+            ptype_b200_free_pinned(replies_);
+        }
+        Batch(const Batch&) = delete;
+        Batch& operator=(const Batch&) = delete;
+        bool Ok() const { return args_ && sel_ && values_; }
+        size_t Capacity() const { return cap_; }
+        int ArgsPerCall() const { return apc_; }
+        int64_t* Args() { return args_; }      // [n][ArgsPerCall]: calculator.Args{A,B} / prime.Args{Min,Max,Target}
+        uint8_t* Sel() { return sel_; }        // [n]: index into the method list of the call (mixed batches)
+        int64_t* Values() { return values_; }  // [n]: *reply of every call, 0 for a failed one
+        // The calls whose status is not OK after the last attempt: (index in the batch, status).
+        const std::vector<ptype_failed>& Failed() const { return failed_; }
+
+       private:
+        friend class Client;
+        ptype_reply* Replies() {  // 16-byte records (value, node, status): only the classic CallBatch wants them
+            if (!replies_) replies_ = static_cast<ptype_reply*>(ptype_b200_alloc_pinned(cap_ * sizeof(ptype_reply)));
+            return replies_;
+        }
+        size_t cap_;
+        int apc_;
+        int64_t* args_ = nullptr;
+        uint8_t* sel_ = nullptr;
+        int64_t* values_ = nullptr;
+        ptype_reply* replies_ = nullptr;
+        std::vector<ptype_failed> failed_, scratch_;
+        std::unique_ptr<ptype_failed[]> rawFailed_;  // where the C ABI writes the failed list (capacity cap_)
+        std::unique_ptr<Batch> retry_;  // the failed calls of an attempt, re-issued from here
+    };
+    std::unique_ptr<Batch> NewBatch(size_t capacity, int argsPerCall = 2) {
+        return std::unique_ptr<Batch>(new Batch(capacity, argsPerCall));
+    }
+
+    // The batch call: n calls whose arguments (and, with more than one method, method selectors)
+    // the caller has written into `b`.  Routed exactly as n sequential Call()s: the sequence range
+    // is reserved with ONE atomic add (rpc.go:181 batched).  Results: b.Values()[j] and b.Failed().
+    // Calls that failed are re-issued with fresh sequence numbers up to cfg.Retries more times
+    // (withRetry, rpc.go:107-116, bounded - see the header comment).
+    Error CallBatch(const std::vector<std::string>& serviceMethods, Batch& b, size_t n) {
+        return CallBatchAttempts(serviceMethods, b, n, cfg_.Retries);
+    }
+    Error CallBatchAttempts(const std::vector<std::string>& serviceMethods, Batch& b, size_t n, int retries) {
+        b.failed_.clear();
+        if (n == 0) return Error();
+        if (n > b.cap_ || !b.Ok()) return Error("ptype_b200: batch larger than its buffers");
+        if (serviceMethods.empty() || serviceMethods.size() > PTYPE_BATCH_METHODS)
+            return Error("ptype_b200: a batch names 1 to 4 methods");
+        ptype_method_ref refs[PTYPE_BATCH_METHODS];
+        for (size_t i = 0; i < serviceMethods.size(); ++i)
+            ptype_b200_method_key(serviceMethods[i].c_str(), &refs[i].method, &refs[i].recv);
+        const int nm = static_cast<int>(serviceMethods.size());
+        const uint64_t key = gpu_->ServiceKey(service_);
+        if (Error e = submitValues(key, refs, nm, b, n, &b.failed_)) return e;
+        // withRetry: only the calls that failed go round again, each with a fresh sequence number
+        for (int attempt = 0; attempt < retries && !b.failed_.empty(); ++attempt) {
+            const size_t m = b.failed_.size();
+            std::sort(b.failed_.begin(), b.failed_.end(),
+                      [](const ptype_failed& x, const ptype_failed& y) { return x.index < y.index; });
+            if (!b.retry_ || b.retry_->cap_ < m) b.retry_.reset(new Batch(m, b.apc_));
+            Batch& r = *b.retry_;
+            if (!r.Ok()) return Error("ptype_b200: out of page-locked memory");
+            for (size_t t = 0; t < m; ++t) {
+                const size_t j = b.failed_[t].index;
+                for (int k = 0; k < b.apc_; ++k) r.args_[t * b.apc_ + k] = b.args_[j * b.apc_ + k];
+                r.sel_[t] = b.sel_[j];
+            }
+            if (Error e = submitValues(key, refs, nm, r, m, &b.scratch_)) return e;
+            for (size_t t = 0; t < m; ++t) b.values_[b.failed_[t].index] = r.values_[t];
+            for (ptype_failed& f : b.scratch_) f.index = b.failed_[f.index].index;
+            b.failed_.swap(b.scratch_);
+        }
+        return Error();
+    }
+
+    // The same through plain arrays, with the routing decision of every call in the reply: args
+    // are copied into a pooled Batch, the GPU writes 16-byte reply records, and those are unpacked.
     Error CallBatch(const std::string& serviceMethod, const int64_t (*args)[3], size_t n, BatchReply* replies) {
         return CallBatchAttempts(serviceMethod, args, n, replies, cfg_.Retries);
     }
     Error CallBatchAttempts(const std::string& serviceMethod, const int64_t (*args)[3], size_t n,
                             BatchReply* replies, int retries) {
         if (n == 0) return Error();
-        uint32_t method = 0, recv = 0;
-        ptype_b200_method_key(serviceMethod.c_str(), &method, &recv);
+        ptype_method_ref ref;
+        ptype_b200_method_key(serviceMethod.c_str(), &ref.method, &ref.recv);
         const uint64_t key = gpu_->ServiceKey(service_);
-        std::vector<ptype_req> reqs(n);
-        std::vector<ptype_reply> out(n);
+        int apc = 2;
+        for (size_t j = 0; j < n && apc == 2; ++j)
+            if (args[j][2] != 0) apc = 3;
+        std::unique_ptr<Batch> b = acquire(n, apc);
+        if (!b->Ok() || !b->Replies()) return Error("ptype_b200: out of page-locked memory");
         std::vector<uint32_t> todo(n);
         for (size_t j = 0; j < n; ++j) todo[j] = static_cast<uint32_t>(j);
+        Error err;
         for (int attempt = 0;; ++attempt) {
-            const uint64_t m = todo.size();
-            const uint64_t base = seq_.fetch_add(m) ;  // value before the add; first call sees base+1
-            for (uint64_t t = 0; t < m; ++t) {
-                const size_t j = todo[t];
-                reqs[t] = ptype_req{key, base + 1 + t, method, recv, args[j][0], args[j][1], args[j][2]};
+            const size_t m = todo.size();
+            for (size_t t = 0; t < m; ++t)
+                for (int k = 0; k < apc; ++k) b->args_[t * apc + k] = args[todo[t]][k];
+            const uint64_t base = seq_.fetch_add(m);  // value before the add; the first call sees base+1
+            int rc = ptype_b200_call_batch(gpu_->ctx(), 0, key, base, &ref, 1, nullptr, b->args_, apc, m,
+                                           b->replies_, 0);
+            if (rc != PTYPE_OK) {
+                err = Error(std::string("ptype_b200_call_batch: ") + ptype_b200_strerror(rc) + ": " + ptype_b200_last_error());
+                break;
             }
-            std::vector<uint32_t> failed(m);
-            ptype_batch_stats stats;
-            int rc = ptype_b200_dispatch_ex(gpu_->ctx(), 0, reqs.data(), m, out.data(), failed.data(), m, &stats, 0);
-            if (rc != PTYPE_OK)
-                return Error(std::string("ptype_b200_dispatch: ") + ptype_b200_strerror(rc) + ": " + ptype_b200_last_error());
-            for (uint64_t t = 0; t < m; ++t) {
-                const size_t j = todo[t];
-                replies[j].Value = out[t].value;
-                replies[j].NodeId = out[t].node;
-                replies[j].Status = out[t].status;
-            }
-            if (stats.failed_count == 0 || attempt >= retries) return Error();
             std::vector<uint32_t> next;
-            next.reserve(stats.failed_count);
-            for (uint64_t f = 0; f < stats.failed_count; ++f) next.push_back(todo[failed[f]]);
-            std::sort(next.begin(), next.end());
+            for (size_t t = 0; t < m; ++t) {
+                const ptype_reply& o = b->replies_[t];
+                BatchReply& out = replies[todo[t]];
+                out.Value = o.value;
+                out.NodeId = o.node;
+                out.Status = o.status;
+                if (o.status != PTYPE_ST_OK) next.push_back(todo[t]);
+            }
+            if (next.empty() || attempt >= retries) break;
             todo.swap(next);
         }
+        release(std::move(b));
+        return err;
     }
 
     // rpc.go:69-105.  The asynchronous twin: the call runs on its own thread and the returned
@@ -723,6 +828,7 @@ class Client {  // cluster/rpc.go:40-43,126-139
 
        private:
         friend class Client;
+        friend class CallCoalescer;
         std::mutex mu;
         std::condition_variable cv;
         bool done = false;
@@ -777,6 +883,43 @@ class Client {  // cluster/rpc.go:40-43,126-139
     Client(Dispatcher* gpu, std::string service, Registry* r, ConnConfig cfg)
         : gpu_(gpu), service_(std::move(service)), registry_(r), cfg_(cfg) {}
 
+    // One attempt of a values batch: reserve the sequence range, one C-ABI call, collect the
+    // (index, status) entries of the calls that failed.
+    Error submitValues(uint64_t key, const ptype_method_ref* refs, int nm, Batch& b, size_t n,
+                       std::vector<ptype_failed>* failed) {
+        const uint64_t base = seq_.fetch_add(n);  // value before the add; the first call sees base+1
+        if (!b.rawFailed_) b.rawFailed_.reset(new ptype_failed[b.cap_]);  // room for every call: never truncated
+        uint64_t count = 0;
+        int rc = ptype_b200_call_batch_values(gpu_->ctx(), 0, key, base, refs, nm, nm > 1 ? b.sel_ : nullptr, b.args_,
+                                              b.apc_, n, b.values_, b.rawFailed_.get(), b.cap_, &count, 0);
+        if (rc != PTYPE_OK)
+            return Error(std::string("ptype_b200_call_batch_values: ") + ptype_b200_strerror(rc) + ": " +
+                         ptype_b200_last_error());
+        failed->assign(b.rawFailed_.get(), b.rawFailed_.get() + count);
+        return Error();
+    }
+    // Batches behind the array-based CallBatch: Call() is safe from many threads (rpc.go:59 is
+    // goroutine-safe), so each call in flight takes its own buffers from a small pool.
+    std::unique_ptr<Batch> acquire(size_t n, int apc) {
+        {
+            std::lock_guard<std::mutex> lk(poolMu_);
+            for (size_t i = 0; i < pool_.size(); ++i) {
+                if (pool_[i]->cap_ >= n && pool_[i]->apc_ == apc) {
+                    std::unique_ptr<Batch> b = std::move(pool_[i]);
+                    pool_.erase(pool_.begin() + static_cast<long>(i));
+                    return b;
+                }
+            }
+        }
+        size_t cap = 64;
+        while (cap < n) cap *= 2;
+        return std::unique_ptr<Batch>(new Batch(cap, apc));
+    }
+    void release(std::unique_ptr<Batch> b) {
+        std::lock_guard<std::mutex> lk(poolMu_);
+        if (pool_.size() < 8) pool_.push_back(std::move(b));
+    }
+
     // rpc.go:226-244: selectNodes happens inside the image; the swap is the publish.
     Error handleNewNodes(const std::vector<Node>& nodes) {
         if (Error e = gpu_->SetNodes(service_, nodes)) return e;
@@ -815,6 +958,8 @@ class Client {  // cluster/rpc.go:40-43,126-139
     std::atomic<uint64_t> connsUpdated_{0};
     std::mutex errMu_;
     std::optional<Error> pendingErr_;
+    std::mutex poolMu_;
+    std::vector<std::unique_ptr<Batch>> pool_;
 };
 
 // -------------------------------------------------------------------------- coalescing
@@ -845,7 +990,7 @@ class CallCoalescer {
         p.args[2] = args[2];
         {
             std::unique_lock<std::mutex> lk(mu_);
-            queue_[serviceMethod].push_back(&p);
+            queue_[{serviceMethod, false}].push_back(&p);
             ++queued_;
             cv_.notify_all();
             done_cv_.wait(lk, [&] { return p.done; });
@@ -855,6 +1000,24 @@ class CallCoalescer {
         *reply = p.rep.Value;
         return Error();
     }
+    // Client.Go without a thread per call: the call joins the next batch and the returned object
+    // is signalled by the dispatch loop.  One attempt, error delivered on the call, *reply
+    // untouched on failure - the semantics of Client::Go above (rpc.go:69-105).
+    std::shared_ptr<Client::AsyncCall> Go(const std::string& serviceMethod, const int64_t (&args)[3], int64_t* reply) {
+        auto call = std::make_shared<Client::AsyncCall>();
+        call->ServiceMethod = serviceMethod;
+        Pending* p = new Pending();
+        p->args[0] = args[0];
+        p->args[1] = args[1];
+        p->args[2] = args[2];
+        p->async = call;
+        p->reply = reply;
+        std::lock_guard<std::mutex> lk(mu_);
+        queue_[{serviceMethod, true}].push_back(p);
+        ++queued_;
+        cv_.notify_all();
+        return call;
+    }
     uint64_t Batches() const { return batches_.load(); }
 
    private:
@@ -863,10 +1026,13 @@ class CallCoalescer {
         BatchReply rep;
         Error err;
         bool done = false;
+        std::shared_ptr<Client::AsyncCall> async;  // set for Go(): completed by the loop, then freed
+        int64_t* reply = nullptr;
     };
+    using GroupKey = std::pair<std::string, bool>;  // method, one attempt only (came through Go)
     void Run() {
         for (;;) {
-            std::map<std::string, std::vector<Pending*>> take;
+            std::map<GroupKey, std::vector<Pending*>> take;
             {
                 std::unique_lock<std::mutex> lk(mu_);
                 cv_.wait(lk, [&] { return stop_ || queued_ > 0; });
@@ -878,17 +1044,32 @@ class CallCoalescer {
             }
             for (auto& group : take) {
                 std::vector<Pending*>& ps = group.second;
+                const std::string& method = group.first.first;
                 std::vector<std::array<int64_t, 3>> args(ps.size());
                 for (size_t i = 0; i < ps.size(); ++i) args[i] = {ps[i]->args[0], ps[i]->args[1], ps[i]->args[2]};
                 std::vector<BatchReply> reps(ps.size());
-                Error e = client_->CallBatch(group.first, reinterpret_cast<const int64_t(*)[3]>(args.data()),
-                                             ps.size(), reps.data());
+                const auto a3 = reinterpret_cast<const int64_t(*)[3]>(args.data());
+                Error e = group.first.second ? client_->CallBatchAttempts(method, a3, ps.size(), reps.data(), 0)
+                                             : client_->CallBatch(method, a3, ps.size(), reps.data());
                 batches_.fetch_add(1);
                 std::lock_guard<std::mutex> lk(mu_);
                 for (size_t i = 0; i < ps.size(); ++i) {
-                    ps[i]->rep = reps[i];
-                    ps[i]->err = e;
-                    ps[i]->done = true;
+                    Pending* p = ps[i];
+                    if (p->async) {
+                        Error ce = e ? e : StatusError(reps[i].Status, method);
+                        if (!ce) *p->reply = reps[i].Value;
+                        {
+                            std::lock_guard<std::mutex> alk(p->async->mu);
+                            p->async->Err = ce;
+                            p->async->done = true;
+                        }
+                        p->async->cv.notify_all();
+                        delete p;
+                        continue;
+                    }
+                    p->rep = reps[i];
+                    p->err = e;
+                    p->done = true;
                 }
             }
             done_cv_.notify_all();
@@ -899,7 +1080,7 @@ class CallCoalescer {
     std::chrono::microseconds max_wait_;
     std::mutex mu_;
     std::condition_variable cv_, done_cv_;
-    std::map<std::string, std::vector<Pending*>> queue_;
+    std::map<GroupKey, std::vector<Pending*>> queue_;
     size_t queued_ = 0;
     bool stop_ = false;
     std::atomic<uint64_t> batches_{0};

@@ -120,29 +120,19 @@ static void TestRegistry_nodes_prefix_case() {
 static void TestKVStore() {
     KVStore kvs;
     std::vector<std::string> vals;
-    kvs.PutRaw("store/raccoon1/", "uwu1");
-    kvs.PutRaw("store/raccoon2/", "uwu2");
-    GetOptions prefix;
-    prefix.Prefix = true;
-    REQUIRE(!kvs.Get("raccoon1", &vals, prefix));
+    // store_test.go: keys live under store/, a prefix Get returns values in key order
+    REQUIRE(!kvs.Put("raccoon1/", "uwu1") && !kvs.Put("raccoon2/", "uwu2"));
+    REQUIRE(!kvs.Get("raccoon1", &vals, true));
     REQUIRE((vals == std::vector<std::string>{"uwu1"}));
     REQUIRE(kvs.Get("raccoon", &vals).Is(ErrNoKey()) && vals.empty());
-    REQUIRE(!kvs.Get("raccoon", &vals, prefix));
+    REQUIRE(!kvs.Get("raccoon", &vals, true));
     REQUIRE((vals == std::vector<std::string>{"uwu1", "uwu2"}));
-    REQUIRE(!kvs.Put("hello1", "world1") && !kvs.Put("hello2", "world2") && !kvs.Put("hello3", "world3"));
-    GetOptions two = prefix;
-    two.Limit = 2;
-    REQUIRE(!kvs.Get("hello", &vals, two));
-    REQUIRE((vals == std::vector<std::string>{"world1", "world2"}));
     REQUIRE(!kvs.Put("hello", "world"));
     REQUIRE(!kvs.Get("hello", &vals) && vals == std::vector<std::string>{"world"});
-    REQUIRE(!kvs.Delete("hello"));
-    REQUIRE(kvs.Get("hello", &vals).Is(ErrNoKey()));
-    REQUIRE(kvs.Delete("hello").Is(ErrNoKey()));
-    // new use: registry images by epoch; the latest epoch wins
-    REQUIRE(kvs.LatestImage(&vals.emplace_back()).Is(ErrNoKey()));
-    REQUIRE(!kvs.PublishImage(9, "nine", 4) && !kvs.PublishImage(10, "ten!", 4) && !kvs.PublishImage(2, "two.", 4));
+    // registry images by epoch; the latest epoch wins
     std::string blob;
+    REQUIRE(kvs.LatestImage(&blob).Is(ErrNoKey()));
+    REQUIRE(!kvs.PublishImage(9, "nine", 4) && !kvs.PublishImage(10, "ten!", 4) && !kvs.PublishImage(2, "two.", 4));
     REQUIRE(!kvs.LatestImage(&blob) && blob == "ten!");
 }
 
@@ -288,6 +278,26 @@ static void TestClient_Go() {
     bad->Wait();
     REQUIRE(call->Done() && !call->Err && reply == 56);
     REQUIRE(bad->Err.msg == "rpc: can't find method Calculator.Nope" && untouched == 0);
+    // the same through the dispatch loop: many asynchronous calls share GPU batches, none retried
+    cfg.Retries = 2;
+    std::unique_ptr<Client> c2;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c2));
+    CallCoalescer loop(c2.get());
+    std::vector<int64_t> replies(500, -1);
+    std::vector<std::shared_ptr<Client::AsyncCall>> calls;
+    for (int i = 0; i < 500; ++i) {
+        const int64_t a[3] = {i, 3, 0};
+        calls.push_back(loop.Go(i % 50 == 49 ? "Calculator.Nope" : "Calculator.Multiply", a, &replies[i]));
+    }
+    for (auto& k : calls) k->Wait();
+    for (int i = 0; i < 500; ++i) {
+        if (i % 50 == 49)
+            REQUIRE(calls[i]->Err.msg == "rpc: can't find method Calculator.Nope" && replies[i] == -1);
+        else
+            REQUIRE(!calls[i]->Err && replies[i] == 3 * i);
+    }
+    REQUIRE(c2->Seq() == 500);          // one attempt per call although Retries is 2 (rpc.go:91)
+    REQUIRE(loop.Batches() < 100);      // gathered, not one launch per call
 }
 
 // The optimus example end to end: one target's splitWork stream through a Prime client, the
@@ -531,6 +541,96 @@ static void TestExample_calculator_with_registry() {
     REQUIRE(sel.size() == 3 && sel[0] != Node({"10.0.0.4", 31234}));
 }
 
+// The batch call on reusable page-locked buffers (what the bench's e2e_mirror times): a mixed
+// Add/Multiply batch routed like consecutive Call()s, values in place, failures listed, and
+// withRetry re-issuing only the calls that failed - each under a fresh sequence number.
+static void TestClient_CallBatch_on_pinned_buffers() {
+    Dispatcher gpu("", 3);
+    gpu.Expose("foo", "Calculator");
+    MockRegistry mock{fakeNodes(5)};
+    ConnConfig cfg = testConnConfig();
+    cfg.Retries = 2;
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&gpu, "foo", &mock, &cfg, &c));
+    const size_t n = 100003;
+    auto b = c->NewBatch(n, 2);
+    REQUIRE(b->Ok() && b->Capacity() == n && b->ArgsPerCall() == 2);
+    for (size_t j = 0; j < n; ++j) {
+        b->Args()[2 * j] = static_cast<int64_t>(j) - 50000;
+        b->Args()[2 * j + 1] = INT64_C(0x7FFFFFFFFFFF) * static_cast<int64_t>(j % 7);
+        b->Sel()[j] = static_cast<uint8_t>(j % 3 == 0);   // 1 = Multiply
+    }
+    REQUIRE(!c->CallBatch({"Calculator.Add", "Calculator.Multiply"}, *b, n));
+    REQUIRE(b->Failed().empty() && c->Seq() == n);
+    for (size_t j = 0; j < n; ++j) {
+        const uint64_t x = static_cast<uint64_t>(b->Args()[2 * j]), y = static_cast<uint64_t>(b->Args()[2 * j + 1]);
+        REQUIRE(b->Values()[j] == static_cast<int64_t>(b->Sel()[j] ? x * y : x + y));
+    }
+    // one method of the three is unknown: those calls fail on every attempt (1 + Retries of them),
+    // the others succeed on the first, and every attempt of every call drew its own number
+    for (size_t j = 0; j < n; ++j) b->Sel()[j] = static_cast<uint8_t>(j % 3);
+    REQUIRE(!c->CallBatch({"Calculator.Add", "Calculator.Multiply", "Calculator.Divide"}, *b, n));
+    const size_t bad = n / 3;  // j % 3 == 2
+    REQUIRE(b->Failed().size() == bad && c->Seq() == n + n + 2 * bad);
+    for (const ptype_failed& f : b->Failed())
+        REQUIRE(f.index % 3 == 2 && f.status == PTYPE_ST_CANT_FIND_METHOD && b->Values()[f.index] == 0);
+    // a batch smaller than the buffers, reused; an empty one; one that does not fit
+    REQUIRE(!c->CallBatch({"Calculator.Add"}, *b, 10));
+    REQUIRE(b->Failed().empty() && b->Values()[9] == b->Args()[18] + b->Args()[19]);
+    REQUIRE(!c->CallBatch({"Calculator.Add"}, *b, 0));
+    REQUIRE(c->CallBatch({"Calculator.Add"}, *b, n + 1));
+    // the array form still reports the routing decision of every call
+    BatchReply rep[3];
+    const int64_t args[3][3] = {{1, 2, 0}, {3, 4, 0}, {5, 6, 0}};
+    const uint64_t before = c->Seq();
+    REQUIRE(!c->CallBatch("Calculator.Multiply", args, 3, rep));
+    auto sel = c->getSelectedNodes();
+    for (uint64_t t = 0; t < 3; ++t)
+        REQUIRE(rep[t].Status == 0 && gpu.NodeOf(rep[t].NodeId) == sel[(before + 1 + t) % 3]);
+    REQUIRE(rep[2].Value == 30);
+}
+
+// one host builds the snapshot and publishes it through the KV store, another
+// host (its own Dispatcher and device context) installs the newest epoch and answers alike.
+static void TestDispatcher_image_through_the_store() {
+    KVStore store;
+    Dispatcher builder("10.0.0.5", 3), follower("10.0.0.5", 3);
+    REQUIRE(follower.LoadLatestImage(&store).Is(ErrNoKey()));
+    builder.Expose("calculator", "Calculator");
+    MemRegistry reg;
+    for (int i = 1; i <= 16; ++i) {
+        char name[32], addr[32];
+        std::snprintf(name, sizeof name, "calculator_node_%02d", i);
+        std::snprintf(addr, sizeof addr, "10.0.0.%d", i);
+        REQUIRE(!reg.Register("calculator", name, addr, 31234));
+    }
+    ConnConfig cfg = testConnConfig();
+    std::unique_ptr<Client> c;
+    REQUIRE(!Client::New(&builder, "calculator", &reg, &cfg, &c));
+    REQUIRE(!builder.PublishImage(&store));
+    REQUIRE(!follower.LoadLatestImage(&store));
+    REQUIRE(follower.Epoch() == builder.Epoch());
+    REQUIRE(follower.SelectedNodes("calculator") == builder.SelectedNodes("calculator"));
+    // the same 48-byte records through either context: the same replies
+    std::vector<ptype_req> reqs(1000);
+    uint32_t m = 0, r = 0;
+    ptype_b200_method_key("Calculator.Multiply", &m, &r);
+    for (size_t j = 0; j < reqs.size(); ++j)
+        reqs[j] = ptype_req{builder.ServiceKey("calculator"), j + 1, m, r, static_cast<int64_t>(j), 3, 0};
+    std::vector<ptype_reply> a(reqs.size()), b(reqs.size());
+    REQUIRE(ptype_b200_dispatch(builder.ctx(), 0, reqs.data(), reqs.size(), a.data(), 0) == PTYPE_OK);
+    REQUIRE(ptype_b200_dispatch(follower.ctx(), 0, reqs.data(), reqs.size(), b.data(), 0) == PTYPE_OK);
+    REQUIRE(std::memcmp(a.data(), b.data(), a.size() * sizeof(ptype_reply)) == 0);
+    REQUIRE(a[7].value == 21 && a[7].status == PTYPE_ST_OK);
+    // a node leaves: new epoch on the builder, published, picked up by the follower
+    REQUIRE(reg.Delete("services/calculator/calculator_node_04/") == 1);
+    REQUIRE(c->WaitConnsUpdated(2, 3s));
+    REQUIRE(!builder.PublishImage(&store));
+    REQUIRE(!follower.LoadLatestImage(&store));
+    REQUIRE(follower.Epoch() == builder.Epoch() && follower.Epoch() == 2);
+    REQUIRE(follower.SelectedNodes("calculator") == builder.SelectedNodes("calculator"));
+}
+
 int main(int argc, char** argv) {
     const bool gpu = argc > 1 && std::string(argv[1]) == "gpu";
     RUN(TestRegistry_Register);
@@ -547,6 +647,7 @@ int main(int argc, char** argv) {
         RUN(TestClient_default_conn_config);
         RUN(TestClient_Call);
         RUN(TestClient_first_call_goes_to_index_1);
+        RUN(TestClient_CallBatch_on_pinned_buffers);
         RUN(TestClient_Call_with_retry_error);
         RUN(TestClient_retry_draws_a_sequence_number_per_attempt);
         RUN(TestBalancer_successful_initial_connect);
@@ -555,6 +656,7 @@ int main(int argc, char** argv) {
         RUN(TestBalancer_roundRobinSelect);
         RUN(TestBalancer_mesh_network);
         RUN(TestExample_calculator_with_registry);
+        RUN(TestDispatcher_image_through_the_store);
     }
     std::printf("%d tests, %d failed\n", g_run, g_fail);
     return g_fail ? 1 : 0;

@@ -25,4 +25,4 @@ def test_client_and_balancer_mirror_gpu():
     exe = _build()
     out = subprocess.run([str(exe), "gpu"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
-    assert "21 tests, 0 failed" in out.stdout
+    assert "23 tests, 0 failed" in out.stdout

@@ -6,6 +6,15 @@
 //
 // Prints calls/s, microseconds per batch and the order-independent checksum of batch 0's
 // replies (tests/test_tools_gpu.py compares it with the oracle's for the same stream).
+//
+//   ./ptype_b200_bench mirror [calls_per_batch=1048576] [steps=200] [device=0] [mesh=0]
+//
+// End to end through the C++ mirror of the reference's client (ptype_b200/host/cluster.hpp):
+// a MemRegistry holding the config-2 registrations, a Dispatcher, one Client created through
+// the registry watch, and `steps` x Client::CallBatch on the client's page-locked Batch - the
+// sequence reservation, the C-ABI call, the PCIe transfers and the failed-list read are all
+// inside the timing.  Then the same batch through the array form of CallBatch (arguments copied
+// in, 16-byte reply records unpacked).  Values are checked against plain C++ arithmetic.
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -16,6 +25,7 @@
 #include <vector>
 
 #include "../include/ptype_b200.h"
+#include "../ptype_b200/host/cluster.hpp"
 
 #define CHECK_ABI(call)                                                                       \
     do {                                                                                      \
@@ -59,7 +69,88 @@ static void calculator_calls(std::vector<ptype_req>& out, size_t n, uint64_t see
     }
 }
 
+static int run_mirror(int argc, char** argv) {
+    using namespace cluster;
+    const size_t n = argc > 2 ? std::strtoull(argv[2], nullptr, 10) : (1u << 20);
+    const int steps = argc > 3 ? std::atoi(argv[3]) : 200;
+    const int device = argc > 4 ? std::atoi(argv[4]) : 0;
+    const int mesh = argc > 5 ? std::atoi(argv[5]) : 0;
+
+    MemRegistry reg;   // what 16 calculator servers wrote through Registry.Register (registry.go:51-86)
+    for (int i = 1; i <= 16; ++i) {
+        char name[64], addr[64];
+        std::snprintf(name, sizeof name, "calculator_node_%02d", i);
+        std::snprintf(addr, sizeof addr, "10.0.0.%d", i);
+        if (reg.Register("calculator", name, addr, 31234)) return 1;
+    }
+    Dispatcher gpu("10.0.0.5", mesh ? 0 : 3, device);
+    if (gpu.Err()) {
+        std::fprintf(stderr, "%s\n", gpu.Err().msg.c_str());
+        return 1;
+    }
+    gpu.Expose("calculator", "Calculator");
+    ConnConfig cfg = DefaultConnConfig();
+    cfg.MaxConnections = mesh ? 0 : 3;
+    std::unique_ptr<Client> client;
+    if (Error e = Client::New(&gpu, "calculator", &reg, &cfg, &client)) {
+        std::fprintf(stderr, "%s\n", e.msg.c_str());
+        return 1;
+    }
+    // the config-2 stream, written straight into the client's page-locked batch
+    std::vector<ptype_req> host;
+    calculator_calls(host, n, 0x5EED0100ull, 0);
+    uint32_t mul_m, mul_r;
+    ptype_b200_method_key("Calculator.Multiply", &mul_m, &mul_r);
+    auto batch = client->NewBatch(n, 2);
+    if (!batch->Ok()) return 1;
+    for (size_t j = 0; j < n; ++j) {
+        batch->Args()[2 * j] = host[j].a0;
+        batch->Args()[2 * j + 1] = host[j].a1;
+        batch->Sel()[j] = host[j].method == mul_m;
+    }
+    const std::vector<std::string> methods = {"Calculator.Add", "Calculator.Multiply"};
+    auto check = [&](const int64_t* values) {
+        for (size_t j = 0; j < n; ++j) {
+            const uint64_t a = static_cast<uint64_t>(host[j].a0), b = static_cast<uint64_t>(host[j].a1);
+            if (values[j] != static_cast<int64_t>(batch->Sel()[j] ? a * b : a + b)) return false;
+        }
+        return true;
+    };
+    for (int i = 0; i < 3; ++i)
+        if (Error e = client->CallBatch(methods, *batch, n)) {
+            std::fprintf(stderr, "%s\n", e.msg.c_str());
+            return 1;
+        }
+    bool ok = batch->Failed().empty() && check(batch->Values());
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < steps; ++i)
+        if (client->CallBatch(methods, *batch, n)) return 1;
+    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    ok = ok && batch->Failed().empty() && check(batch->Values()) && client->Seq() == static_cast<uint64_t>(steps + 3) * n;
+
+    // the array form: one method per call, [n][3] arguments copied in, BatchReply records out
+    std::vector<std::array<int64_t, 3>> plain(n);
+    for (size_t j = 0; j < n; ++j) plain[j] = {host[j].a0, host[j].a1, 0};
+    std::vector<BatchReply> reps(n);
+    const int plain_steps = steps < 20 ? steps : 20;
+    const auto args3 = reinterpret_cast<const int64_t(*)[3]>(plain.data());
+    if (client->CallBatch("Calculator.Multiply", args3, n, reps.data())) return 1;
+    const auto p0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < plain_steps; ++i)
+        if (client->CallBatch("Calculator.Multiply", args3, n, reps.data())) return 1;
+    const double plain_secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - p0).count();
+    for (size_t j = 0; j < n && ok; ++j)
+        ok = reps[j].Status == 0 && reps[j].Value == static_cast<int64_t>(static_cast<uint64_t>(host[j].a0) *
+                                                                         static_cast<uint64_t>(host[j].a1));
+    std::printf("calls %.0f seconds %.6f parity %s h2d_bytes_per_step %zu d2h_bytes_per_step %zu "
+                "array_calls %.0f array_seconds %.6f\n",
+                static_cast<double>(n) * steps, secs, ok ? "ok" : "WRONG", n * 17, n * 8,
+                static_cast<double>(n) * plain_steps, plain_secs);
+    return ok ? 0 : 2;
+}
+
 int main(int argc, char** argv) {
+    if (argc > 1 && std::string(argv[1]) == "mirror") return run_mirror(argc, argv);
     const size_t n = argc > 1 ? std::strtoull(argv[1], nullptr, 10) : (1u << 20);
     const int steps = argc > 2 ? std::atoi(argv[2]) : 2000;
     const int buffers = argc > 3 ? std::atoi(argv[3]) : 8;
