@@ -435,6 +435,15 @@ def measure(ctx, env, workload: str, *, steps: int, warmup: int, nbuf: int, batc
     if live:
         live_update()
     run_steps(plan_steps(steps if not live else min(steps, 2 * every + 1)))
+    # ... and keep the GPU under this load for a while before timing: a B200 that was idle a moment
+    # ago has not settled its clocks and power state after a few hundred microseconds of work, and
+    # a K = 20 timed region is itself only ~0.2 ms long (PTYPE_BENCH_SETTLE_MS, default 50)
+    settle_ms = float(os.environ.get("PTYPE_BENCH_SETTLE_MS", "50"))
+    if settle_ms > 0 and not live:
+        t_end = time.perf_counter() + settle_ms * 1e-3
+        lap = batches_of(0, 4 * nbuf)
+        while time.perf_counter() < t_end:
+            ctx.dispatch_batches(lap, flags=flags, sync=True)
     timed = plan_steps(steps)
     preroll = batches_of(0, min(32, steps))
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -621,40 +621,63 @@ struct BatchList {
     int count;
 };
 
-template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas>
+// How the tiles of a launch are handed out.  counter == nullptr: statically, warp w takes tiles
+// w, w + W, w + 2W, ...  Otherwise dynamically: SMs do not stream from HBM at the same pace (the
+// spread measured on B200 is about a tenth of the launch), so with equal shares the fast ones sit
+// idle at the end - 34 us of a 220 us launch of 20 batches.  Warps therefore draw kGrab consecutive
+// tiles at a time from counter[0] until `fine_start`, and single tiles after it (each draw still
+// advances the counter by kGrab: position fine_start + kGrab * i stands for tile fine_start + i), so
+// that the last tiles go to whoever is free.  The draw for the next group is in flight while the
+// current one is processed.  counter[1] counts finished CTAs; the last one leaves both words at
+// zero for the launch that will use this slot next (context.cu rotates eight slots, and at most
+// two launches of a stream ever overlap).
+constexpr uint32_t kGrab = 4;
+struct TileSchedule {
+    unsigned int* counter;  // nullptr = static round-robin
+    uint32_t fine_start;    // multiple of kGrab
+    uint32_t limit;         // fine_start + kGrab * (total_tiles - fine_start)
+};
+
+template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas, bool kDynamic>
 __global__ void __launch_bounds__(kThreads, kMinCtas)
-    dispatch_multi_kernel(const DeviceImage img, const __grid_constant__ BatchList list) {
+    dispatch_multi_kernel(const DeviceImage img, const __grid_constant__ BatchList list, const TileSchedule sched) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ __align__(16) CtaShared sh;
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warps_per_cta = blockDim.x >> 5;
-    const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
-    griddep_launch_dependents();
-
-    const TransposePlan plan = transpose_plan(lane);
     const uint32_t total_tiles = list.tile_end[list.count - 1];
     const uint32_t total_warps = gridDim.x * warps_per_cta;
     const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
 
+    // first draw before anything else: its latency hides behind the table staging
+    uint32_t drawn = 0;
+    if (kDynamic && lane == 0) drawn = atomicAdd(sched.counter, kGrab);
+
+    const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
+    griddep_launch_dependents();
+
+    const TransposePlan plan = transpose_plan(lane);
     LookupCache cache;
     bool table_ready = !kSmemTable;
-    int cursor[kUnroll];  // batch holding each in-flight tile; tiles only move forward
-#pragma unroll
-    for (int u = 0; u < kUnroll; ++u) cursor[u] = 0;
+    int cursor = 0;  // batch holding the tile being fetched; a warp's tiles only move forward
 
-    for (uint32_t g0 = warp_global; g0 < total_tiles; g0 += total_warps * kUnroll) {
+    // one round: up to kUnroll tiles first, first + stride, ... (count of them)
+    auto round = [&](uint32_t first, uint32_t stride, uint32_t count) {
         uint4 ld[kUnroll][3];
         uint32_t tile[kUnroll];
+        int batch[kUnroll];
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-            const uint32_t g = g0 + u * total_warps;
             tile[u] = 0;
+            batch[u] = 0;
             ld[u][0] = ld[u][1] = ld[u][2] = make_uint4(0, 0, 0, 0);
-            if (g < total_tiles) {
-                int b = cursor[u];
+            if (static_cast<uint32_t>(u) < count) {
+                const uint32_t g = first + u * stride;
+                int b = cursor;
                 while (g >= list.tile_end[b]) ++b;
-                cursor[u] = b;
+                cursor = b;
+                batch[u] = b;
                 tile[u] = g - (b ? list.tile_end[b - 1] : 0u);
                 const size_t n_chunks = static_cast<size_t>(list.n[b]) * 3;
                 const uint4* reqs = list.reqs[b];
@@ -671,17 +694,48 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         }
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-            if (g0 + u * total_warps >= total_tiles) break;  // warp-uniform
+            if (static_cast<uint32_t>(u) >= count) break;  // warp-uniform
             uint4 q[3];
             transpose_tile(plan, lane, ld[u], q);
-            const int b = cursor[u];
+            const int b = batch[u];
             const size_t idx = (static_cast<size_t>(tile[u]) << 5) + lane;
             if (idx < list.n[b])
                 st_stream(list.replies[b] + idx, dispatch_one<kSmemTable>(img, sh, slots, cache, q[0], q[1], q[2]));
         }
+    };
+
+    if (!kDynamic) {
+        for (uint32_t g0 = warp_global; g0 < total_tiles; g0 += total_warps * kUnroll) {
+            const uint32_t left = (total_tiles - g0 + total_warps - 1) / total_warps;
+            round(g0, total_warps, left < static_cast<uint32_t>(kUnroll) ? left : static_cast<uint32_t>(kUnroll));
+        }
+    } else {
+        for (;;) {
+            const uint32_t pos = __shfl_sync(kFull, drawn, 0);
+            if (pos >= sched.limit) break;
+            if (lane == 0) drawn = atomicAdd(sched.counter, kGrab);  // the next group, fetched while this one runs
+            uint32_t first = pos, count = kGrab;
+            if (pos >= sched.fine_start) {
+                first = sched.fine_start + (pos - sched.fine_start) / kGrab;
+                count = 1;
+            }
+            for (uint32_t off = 0; off < count; off += kUnroll)
+                round(first + off, 1u, count - off < static_cast<uint32_t>(kUnroll) ? count - off : static_cast<uint32_t>(kUnroll));
+        }
     }
     if (!table_ready) mbar_wait(&sh.table_bar, 0);
     griddep_wait();
+    if (kDynamic) {
+        __syncthreads();  // every warp of the CTA has had its last draw answered
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(sched.counter + 1, 1u) == gridDim.x - 1) {
+                sched.counter[0] = 0;
+                sched.counter[1] = 0;
+                __threadfence();
+            }
+        }
+    }
 }
 
 // Bulk-staged twin of dispatch_multi_kernel: per-warp TMA ring over the tile stream of many
@@ -1098,7 +1152,8 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
 int max_batches_per_launch() { return kMaxBatchesPerLaunch; }
 
 cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
-                                  const ptype_batch* batches, int count, cudaStream_t stream, bool pdl) {
+                                  const ptype_batch* batches, int count, unsigned int* sched_slot,
+                                  cudaStream_t stream, bool pdl) {
     BatchList list = {};
     uint64_t tiles = 0;
     int m = 0;
@@ -1126,18 +1181,30 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         return launch_kernel(dispatch_bulk_multi_kernel<false, kStagesDefault>, blocks, plan.threads,
                              plan.dyn_smem, stream, pdl, img, list, table_smem);
     }
-    if (plan.threads == kMaxThreads) {
-        if (plan.smem_table)
-            return launch_kernel(dispatch_multi_kernel<true, 2, kMaxThreads, 1>, blocks, plan.threads,
-                                 plan.dyn_smem, stream, pdl, img, list);
-        return launch_kernel(dispatch_multi_kernel<false, 2, kMaxThreads, 1>, blocks, plan.threads,
-                             plan.dyn_smem, stream, pdl, img, list);
+    // Dynamic tile hand-out when the caller gave a counter slot: the last two tiles per warp (of
+    // the grid) are drawn one by one, everything before in groups of kGrab.
+    TileSchedule sched = {};
+    const uint64_t total_warps = static_cast<uint64_t>(blocks) * warps_per_cta;
+    uint64_t fine = total_warps * 2;
+    if (fine > tiles) fine = tiles;
+    const uint64_t fine_start = (tiles - fine) / kGrab * kGrab;
+    const uint64_t limit = fine_start + kGrab * (tiles - fine_start);
+    const bool dynamic = sched_slot != nullptr && limit < 0xFFFFFFF0ull;
+    if (dynamic) {
+        sched.counter = sched_slot;
+        sched.fine_start = static_cast<uint32_t>(fine_start);
+        sched.limit = static_cast<uint32_t>(limit);
     }
-    if (plan.smem_table)
-        return launch_kernel(dispatch_multi_kernel<true, kSmallUnroll, kSmallThreads, kSmallMinCtas>, blocks,
-                             plan.threads, plan.dyn_smem, stream, pdl, img, list);
-    return launch_kernel(dispatch_multi_kernel<false, kSmallUnroll, kSmallThreads, kSmallMinCtas>, blocks,
-                         plan.threads, plan.dyn_smem, stream, pdl, img, list);
+#define PTYPE_MULTI(SM, UNROLL, THREADS, MINCTAS)                                                            \
+    (dynamic ? launch_kernel(dispatch_multi_kernel<SM, UNROLL, THREADS, MINCTAS, true>, blocks, plan.threads, \
+                             plan.dyn_smem, stream, pdl, img, list, sched)                                   \
+             : launch_kernel(dispatch_multi_kernel<SM, UNROLL, THREADS, MINCTAS, false>, blocks, plan.threads, \
+                             plan.dyn_smem, stream, pdl, img, list, sched))
+    if (plan.threads == kMaxThreads)
+        return plan.smem_table ? PTYPE_MULTI(true, 2, kMaxThreads, 1) : PTYPE_MULTI(false, 2, kMaxThreads, 1);
+    return plan.smem_table ? PTYPE_MULTI(true, kSmallUnroll, kSmallThreads, kSmallMinCtas)
+                           : PTYPE_MULTI(false, kSmallUnroll, kSmallThreads, kSmallMinCtas);
+#undef PTYPE_MULTI
 }
 
 namespace {
