@@ -526,7 +526,9 @@ def measure(ctx, env, workload: str, *, steps: int, warmup: int, nbuf: int, batc
            "launches": int(launches), "host_enqueue_s": host_enqueue_s, "calls_all": calls_all,
            "per_launch_calls": per_launch_calls, "achieved_gbs": achieved, "peak": peak, "peak_kind": peak_kind,
            "parity": parity, "parity_ok": bool(ok), "window": (w0, w1), "lone": lone, "hb": hb, "image": image,
-           "spec": spec, "nbuf": nbuf, "batch": batch}
+           "spec": spec if not live else wl.RegistrySpec(sorted(live_nodes.values()), spec.expose, [], spec.local_addr,
+                                                        spec.max_connections),   # the registry as it stands now
+           "nbuf": nbuf, "batch": batch}
     if live:
         out["live_updates"] = {"count": len(update_ms), "every_steps": update_every,
                                "host_ms_avg": float(np.mean(update_ms)) if update_ms else None,

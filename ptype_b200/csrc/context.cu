@@ -38,7 +38,6 @@ int cuda_fail(cudaError_t e, const char* what) {
 
 constexpr int kPipe = 4;                     // host-pointer pipeline depth
 constexpr int kSchedSlots = 8;               // at most two launches of a stream overlap; eight is ample
-constexpr int kSchedStride = 32;             // 32-bit words between slots (one 128-byte line each)
 bool dynamic_tiles_enabled() {               // PTYPE_B200_DYNAMIC=0: static partition (measurement switch)
     static const bool on = [] {
         const char* v = std::getenv("PTYPE_B200_DYNAMIC");
@@ -155,8 +154,7 @@ struct DeviceState {
     uint32_t* d_failed = nullptr;
     size_t failed_cap = 0;
     // Tile counters of the multi-batch launches (dispatch.cu: TileSchedule): kSchedSlots slots of
-    // {next tile, finished CTAs}, a 128-byte line each, used round-robin; every launch leaves its
-    // slot zeroed.  Allocated and cleared once, at the context's first dispatch_batches.
+    // {tiles handed out per SM, finished CTAs}, used round-robin; every launch leaves its slot zeroed.  Allocated and cleared once, at the context's first dispatch_batches.
     unsigned int* d_sched = nullptr;
     uint64_t sched_seq = 0;
     unsigned long long* d_cksum_partials = nullptr;  // scratch of the checksum kernel
@@ -929,8 +927,8 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
         if (batches[b].n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
     }
     if (!(flags & PTYPE_F_ONE_LAUNCH_PER_BATCH) && !d->d_sched && dynamic_tiles_enabled()) {
-        CU(cudaMalloc(&d->d_sched, kSchedSlots * kSchedStride * sizeof(unsigned int)));
-        CU(cudaMemset(d->d_sched, 0, kSchedSlots * kSchedStride * sizeof(unsigned int)));
+        CU(cudaMalloc(&d->d_sched, kSchedSlots * ptype::sched_slot_words() * sizeof(unsigned int)));
+        CU(cudaMemset(d->d_sched, 0, kSchedSlots * ptype::sched_slot_words() * sizeof(unsigned int)));
     }
     if (!(flags & PTYPE_F_ONE_LAUNCH_PER_BATCH)) {
         // One launch per group of batches: the persistent grid walks their tiles as one
@@ -947,9 +945,9 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
             if (e == b) return PTYPE_E_LIMIT;
             if (tiles) {
                 unsigned int* slot =
-                    d->d_sched ? d->d_sched + (d->sched_seq++ % kSchedSlots) * kSchedStride : nullptr;
-                CU(ptype::launch_dispatch_multi(img, plan, d->dispatch_sms, batches + b, static_cast<int>(e - b),
-                                                slot, d->stream, take_pdl(d, flags)));
+                    d->d_sched ? d->d_sched + (d->sched_seq++ % kSchedSlots) * ptype::sched_slot_words() : nullptr;
+                CU(ptype::launch_dispatch_multi(img, plan, d->dispatch_sms, d->sm_count, batches + b,
+                                                static_cast<int>(e - b), slot, d->stream, take_pdl(d, flags)));
                 ctx->launches.fetch_add(1);
             }
             b = e;

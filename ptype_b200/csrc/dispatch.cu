@@ -621,28 +621,45 @@ struct BatchList {
     int count;
 };
 
-// How the tiles of a launch are handed out.  counter == nullptr: statically, warp w takes tiles
-// w, w + W, w + 2W, ...  Otherwise dynamically: SMs do not stream from HBM at the same pace (the
-// spread measured on B200 is about a tenth of the launch), so with equal shares the fast ones sit
-// idle at the end - 34 us of a 220 us launch of 20 batches.  Warps therefore draw kGrab consecutive
-// tiles at a time from counter[0] until `fine_start`, and single tiles after it (each draw still
-// advances the counter by kGrab: position fine_start + kGrab * i stands for tile fine_start + i), so
-// that the last tiles go to whoever is free.  The draw for the next group is in flight while the
-// current one is processed.  counter[1] counts finished CTAs; the last one leaves both words at
-// zero for the launch that will use this slot next (context.cu rotates eight slots, and at most
-// two launches of a stream ever overlap).
-constexpr uint32_t kGrab = 4;
+// How the tiles of a launch are handed out.  next == nullptr: statically, warp w takes tiles
+// w, w + W, w + 2W, ...  Otherwise dynamically.  The SMs of a B200 do not stream from HBM at the
+// same pace: tools/spread_probe.cu shows the same groups of SMs finishing an equal share 20 %
+// later than the fastest ones, launch after launch (profiles/r02_spread_probe.txt), so with equal
+// shares a lone launch ends with most of the chip idle.  Here every SM owns a contiguous range of
+// the launch's tiles and a counter; the warps running on that SM draw kDraw tiles at a time from
+// it (148 counters: no hot address), and when their own range is used up they look at all the
+// counters at once (five loads per lane), pick the SM with the most tiles left and draw from
+// that one.  The draw for the next round is in flight while the current tiles are processed.
+// done[0] counts finished CTAs; the last one zeroes everything for the launch that will use this
+// slot next (context.cu rotates eight slots, and at most two launches of a stream ever overlap).
+constexpr uint32_t kDraw = 2;
+constexpr uint32_t kMaxSms = 256;
 struct TileSchedule {
-    unsigned int* counter;  // nullptr = static round-robin
-    uint32_t fine_start;    // multiple of kGrab
-    uint32_t limit;         // fine_start + kGrab * (total_tiles - fine_start)
+    unsigned int* next;  // [n_sms] tiles handed out of each SM's range; nullptr = static round-robin
+    unsigned int* done;  // [1]
+    uint32_t n_sms;
+    uint32_t per_sm;     // tiles in every SM's range (the last ranges may be cut short or empty)
 };
+
+__device__ __forceinline__ uint32_t sm_id() {
+    uint32_t s;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(s));
+    return s;
+}
+// Tiles in SM s's range [s * per_sm, min((s + 1) * per_sm, total)).
+__device__ __forceinline__ uint32_t range_size(uint32_t total, uint32_t per_sm, uint32_t s) {
+    const uint64_t lo = static_cast<uint64_t>(s) * per_sm;
+    if (lo >= total) return 0u;
+    const uint64_t left = total - lo;
+    return left < per_sm ? static_cast<uint32_t>(left) : per_sm;
+}
 
 template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas, bool kDynamic>
 __global__ void __launch_bounds__(kThreads, kMinCtas)
     dispatch_multi_kernel(const DeviceImage img, const __grid_constant__ BatchList list, const TileSchedule sched) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ __align__(16) CtaShared sh;
+    static_assert(kUnroll == static_cast<int>(kDraw), "a draw is one round of the tile loop");
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warps_per_cta = blockDim.x >> 5;
@@ -651,8 +668,12 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
 
     // first draw before anything else: its latency hides behind the table staging
-    uint32_t drawn = 0;
-    if (kDynamic && lane == 0) drawn = atomicAdd(sched.counter, kGrab);
+    uint32_t from = 0, size = 0, drawn = 0;
+    if (kDynamic) {
+        from = sm_id() % sched.n_sms;
+        size = range_size(total_tiles, sched.per_sm, from);
+        if (lane == 0) drawn = atomicAdd(sched.next + from, kDraw);
+    }
 
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
@@ -660,7 +681,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     const TransposePlan plan = transpose_plan(lane);
     LookupCache cache;
     bool table_ready = !kSmemTable;
-    int cursor = 0;  // batch holding the tile being fetched; a warp's tiles only move forward
+    int cursor = 0;  // batch holding the tile being fetched; tiles only move forward while cursor is kept
 
     // one round: up to kUnroll tiles first, first + stride, ... (count of them)
     auto round = [&](uint32_t first, uint32_t stride, uint32_t count) {
@@ -711,29 +732,53 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         }
     } else {
         for (;;) {
-            const uint32_t pos = __shfl_sync(kFull, drawn, 0);
-            if (pos >= sched.limit) break;
-            if (lane == 0) drawn = atomicAdd(sched.counter, kGrab);  // the next group, fetched while this one runs
-            uint32_t first = pos, count = kGrab;
-            if (pos >= sched.fine_start) {
-                first = sched.fine_start + (pos - sched.fine_start) / kGrab;
-                count = 1;
+            const uint32_t off = __shfl_sync(kFull, drawn, 0);
+            if (off >= size) {
+                // This range is used up: which SM has the most tiles left?  All counters at once.
+                uint32_t best = 0, best_sm = 0;
+                for (uint32_t s = lane; s < sched.n_sms; s += 32) {
+                    const uint32_t sz = range_size(total_tiles, sched.per_sm, s);
+                    const uint32_t used = __ldcg(sched.next + s);
+                    const uint32_t left = used < sz ? sz - used : 0u;
+                    if (left > best) {
+                        best = left;
+                        best_sm = s;
+                    }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const uint32_t ob = __shfl_xor_sync(kFull, best, o), os = __shfl_xor_sync(kFull, best_sm, o);
+                    if (ob > best || (ob == best && os < best_sm)) {
+                        best = ob;
+                        best_sm = os;
+                    }
+                }
+                if (best == 0) break;  // nothing left anywhere
+                from = best_sm;
+                size = range_size(total_tiles, sched.per_sm, from);
+                cursor = 0;
+                if (lane == 0) drawn = atomicAdd(sched.next + from, kDraw);
+                continue;
             }
-            for (uint32_t off = 0; off < count; off += kUnroll)
-                round(first + off, 1u, count - off < static_cast<uint32_t>(kUnroll) ? count - off : static_cast<uint32_t>(kUnroll));
+            if (lane == 0) drawn = atomicAdd(sched.next + from, kDraw);  // the next round, fetched while this one runs
+            const uint32_t left = size - off;
+            round(from * sched.per_sm + off, 1u, left < kDraw ? left : kDraw);
         }
     }
     if (!table_ready) mbar_wait(&sh.table_bar, 0);
     griddep_wait();
     if (kDynamic) {
         __syncthreads();  // every warp of the CTA has had its last draw answered
+        __shared__ unsigned int s_last;
         if (threadIdx.x == 0) {
             __threadfence();
-            if (atomicAdd(sched.counter + 1, 1u) == gridDim.x - 1) {
-                sched.counter[0] = 0;
-                sched.counter[1] = 0;
-                __threadfence();
-            }
+            s_last = atomicAdd(sched.done, 1u) == gridDim.x - 1 ? 1u : 0u;
+        }
+        __syncthreads();
+        if (s_last) {
+            for (uint32_t s = threadIdx.x; s < sched.n_sms; s += blockDim.x) sched.next[s] = 0;
+            if (threadIdx.x == 0) sched.done[0] = 0;
+            __threadfence();
         }
     }
 }
@@ -1150,8 +1195,9 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
 
 // Up to kMaxBatchesPerLaunch device-resident batches in ONE launch.
 int max_batches_per_launch() { return kMaxBatchesPerLaunch; }
+size_t sched_slot_words() { return kMaxSms + 32; }  // per-SM counters, then the finished-CTA count on its own line
 
-cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
+cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count, int device_sms,
                                   const ptype_batch* batches, int count, unsigned int* sched_slot,
                                   cudaStream_t stream, bool pdl) {
     BatchList list = {};
@@ -1181,19 +1227,14 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         return launch_kernel(dispatch_bulk_multi_kernel<false, kStagesDefault>, blocks, plan.threads,
                              plan.dyn_smem, stream, pdl, img, list, table_smem);
     }
-    // Dynamic tile hand-out when the caller gave a counter slot: the last two tiles per warp (of
-    // the grid) are drawn one by one, everything before in groups of kGrab.
+    // Dynamic tile hand-out when the caller gave a counter slot (see TileSchedule).
     TileSchedule sched = {};
-    const uint64_t total_warps = static_cast<uint64_t>(blocks) * warps_per_cta;
-    uint64_t fine = total_warps * 2;
-    if (fine > tiles) fine = tiles;
-    const uint64_t fine_start = (tiles - fine) / kGrab * kGrab;
-    const uint64_t limit = fine_start + kGrab * (tiles - fine_start);
-    const bool dynamic = sched_slot != nullptr && limit < 0xFFFFFFF0ull;
+    const bool dynamic = sched_slot != nullptr && device_sms >= 1 && static_cast<uint32_t>(device_sms) <= kMaxSms;
     if (dynamic) {
-        sched.counter = sched_slot;
-        sched.fine_start = static_cast<uint32_t>(fine_start);
-        sched.limit = static_cast<uint32_t>(limit);
+        sched.next = sched_slot;
+        sched.done = sched_slot + kMaxSms;
+        sched.n_sms = static_cast<uint32_t>(device_sms);
+        sched.per_sm = static_cast<uint32_t>((tiles + device_sms - 1) / device_sms);
     }
 #define PTYPE_MULTI(SM, UNROLL, THREADS, MINCTAS)                                                            \
     (dynamic ? launch_kernel(dispatch_multi_kernel<SM, UNROLL, THREADS, MINCTAS, true>, blocks, plan.threads, \
