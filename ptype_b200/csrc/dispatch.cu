@@ -628,8 +628,8 @@ struct BatchList {
 // shares a lone launch ends with most of the chip idle.  Here every SM owns a contiguous range of
 // the launch's tiles and a counter; the warps running on that SM draw kDraw tiles at a time from
 // it (148 counters: no hot address), and when their own range is used up they look at all the
-// counters at once (five loads per lane), pick the SM with the most tiles left and draw from
-// that one.  The draw for the next round is in flight while the current tiles are processed.
+// counters at once (five loads per lane), pick another SM's range at random in proportion to the
+// tiles it has left, and draw from that one.  The draw for the next round is in flight while the current tiles are processed.
 // done[0] counts finished CTAs; the last one zeroes everything for the launch that will use this
 // slot next (context.cu rotates eight slots, and at most two launches of a stream ever overlap).
 constexpr uint32_t kDraw = 2;
@@ -668,7 +668,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
 
     // first draw before anything else: its latency hides behind the table staging
-    uint32_t from = 0, size = 0, drawn = 0;
+    uint32_t from = 0, size = 0, drawn = 0, steals = 0;
     if (kDynamic) {
         from = sm_id() % sched.n_sms;
         size = range_size(total_tiles, sched.per_sm, from);
@@ -734,24 +734,50 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         for (;;) {
             const uint32_t off = __shfl_sync(kFull, drawn, 0);
             if (off >= size) {
-                // This range is used up: which SM has the most tiles left?  All counters at once.
-                uint32_t best = 0, best_sm = 0;
-                for (uint32_t s = lane; s < sched.n_sms; s += 32) {
-                    const uint32_t sz = range_size(total_tiles, sched.per_sm, s);
-                    const uint32_t used = __ldcg(sched.next + s);
-                    const uint32_t left = used < sz ? sz - used : 0u;
-                    if (left > best) {
-                        best = left;
-                        best_sm = s;
-                    }
-                }
+                // This range is used up.  Read every counter at once and pick another SM's range at
+                // random, in proportion to the tiles it has left: idle warps then spread over the
+                // unfinished ranges instead of all descending on one counter.
+                uint32_t left[kMaxSms / 32];
+                uint32_t lane_sum = 0;
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) {
-                    const uint32_t ob = __shfl_xor_sync(kFull, best, o), os = __shfl_xor_sync(kFull, best_sm, o);
-                    if (ob > best || (ob == best && os < best_sm)) {
-                        best = ob;
-                        best_sm = os;
+                for (uint32_t k = 0; k < kMaxSms / 32; ++k) {
+                    const uint32_t s = lane + 32 * k;
+                    left[k] = 0;
+                    if (s < sched.n_sms) {
+                        const uint32_t sz = range_size(total_tiles, sched.per_sm, s);
+                        const uint32_t used = __ldcg(sched.next + s);
+                        left[k] = used < sz ? sz - used : 0u;
                     }
+                    lane_sum += left[k];
+                }
+                uint32_t incl = lane_sum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t t = __shfl_up_sync(kFull, incl, o);
+                    if (lane >= static_cast<uint32_t>(o)) incl += t;
+                }
+                const uint32_t best = __shfl_sync(kFull, incl, 31);  // tiles left anywhere
+                uint32_t best_sm = 0;
+                if (best != 0) {
+                    uint32_t h = (warp_global + 1u) * 0x9E3779B1u + (++steals) * 0x85EBCA77u;
+                    h ^= h >> 15;
+                    h *= 0x2C1B3C6Du;
+                    h ^= h >> 12;
+                    const uint32_t r = __umulhi(h, best);  // uniform in [0, best)
+                    const bool mine = r >= incl - lane_sum && r < incl;
+                    uint32_t pick = 0;
+                    if (mine) {
+                        uint32_t rr = r - (incl - lane_sum);
+#pragma unroll
+                        for (uint32_t k = 0; k < kMaxSms / 32; ++k) {
+                            if (rr < left[k]) {
+                                pick = lane + 32 * k;
+                                break;
+                            }
+                            rr -= left[k];
+                        }
+                    }
+                    best_sm = __shfl_sync(kFull, pick, __ffs(__ballot_sync(kFull, mine)) - 1);
                 }
                 if (best == 0) break;  // nothing left anywhere
                 from = best_sm;
