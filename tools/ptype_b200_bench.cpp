@@ -203,8 +203,13 @@ int main(int argc, char** argv) {
     const char* reps_env = std::getenv("PTYPE_BENCH_REPS");
     const int reps = reps_env ? std::atoi(reps_env) : 1;
     float ms = 0;
+    // PTYPE_BENCH_PREROLL=p: batches kept in flight right before the timed submission (default: as
+    // many as are timed), so that the timed one meets a GPU that has been busy for a while
+    const char* pre_env = std::getenv("PTYPE_BENCH_PREROLL");
+    std::vector<ptype_batch> preroll(pre_env ? std::atoi(pre_env) : steps);
+    for (size_t i = 0; i < preroll.size(); ++i) preroll[i] = ring[i % buffers];
     for (int rep = 0; rep < (reps > 0 ? reps : 1); ++rep) {
-        CHECK_ABI(ptype_b200_dispatch_batches(ctx, 0, timed.data(), timed.size(), PTYPE_F_DEVICE_PTRS | PTYPE_F_ASYNC));
+        CHECK_ABI(ptype_b200_dispatch_batches(ctx, 0, preroll.data(), preroll.size(), PTYPE_F_DEVICE_PTRS | PTYPE_F_ASYNC));
         cudaEventRecord(e0, stream);
         CHECK_ABI(ptype_b200_dispatch_batches(ctx, 0, timed.data(), timed.size(), PTYPE_F_DEVICE_PTRS | PTYPE_F_ASYNC));
         cudaEventRecord(e1, stream);
