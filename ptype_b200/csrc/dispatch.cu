@@ -625,20 +625,25 @@ struct BatchList {
 // w, w + W, w + 2W, ...  Otherwise dynamically.  The SMs of a B200 do not stream from HBM at the
 // same pace: tools/spread_probe.cu shows the same groups of SMs finishing an equal share 20 %
 // later than the fastest ones, launch after launch (profiles/r02_spread_probe.txt), so with equal
-// shares a lone launch ends with most of the chip idle.  Here every SM owns a contiguous range of
-// the launch's tiles and a counter; the warps running on that SM draw kDraw tiles at a time from
-// it (148 counters: no hot address), and when their own range is used up they look at all the
-// counters at once (five loads per lane), pick another SM's range at random in proportion to the
-// tiles it has left, and draw from that one.  The draw for the next round is in flight while the current tiles are processed.
-// done[0] counts finished CTAs; the last one zeroes everything for the launch that will use this
-// slot next (context.cu rotates eight slots, and at most two launches of a stream ever overlap).
-constexpr uint32_t kDraw = 2;
-constexpr uint32_t kMaxSms = 256;
+// shares a lone launch ends with most of the chip idle.  Two measurements shape the dynamic scheme:
+//  * one counter cannot hand out tiles fast enough (atomics on one address retire at about one
+//    per 2 ns, a tile is done in 0.3 ns), so there are kShards counters, each on its own line;
+//  * the chip must keep sweeping the batches front to back - giving every SM a contiguous range of
+//    its own ran 25 % SLOWER on distinct buffers (148 streams scattered over the DRAM rows instead
+//    of one front), and only looked faster while buffers repeated inside a launch (L2 hits).
+// So tile pair p (tiles 2p, 2p + 1: one round of a warp) belongs to shard p mod kShards, and draw d
+// of shard j is pair d * kShards + j: every shard walks the launch front to back.  A warp draws
+// from the shard its SM maps to; when that one is used up it reads all counters at once, picks
+// another shard at random in proportion to the pairs left, and carries on there.  The draw for the
+// next round is in flight while the current pair is processed.  done[0] counts finished CTAs; the
+// last one zeroes everything for the launch that will use this slot next (context.cu rotates
+// eight slots, and at most two launches of a stream ever overlap).
+constexpr uint32_t kShards = 16;
+constexpr uint32_t kShardStride = 64;  // 32-bit words between counters (256 bytes)
 struct TileSchedule {
-    unsigned int* next;  // [n_sms] tiles handed out of each SM's range; nullptr = static round-robin
+    unsigned int* next;  // kShards counters, kShardStride words apart; nullptr = static round-robin
     unsigned int* done;  // [1]
-    uint32_t n_sms;
-    uint32_t per_sm;     // tiles in every SM's range (the last ranges may be cut short or empty)
+    uint32_t pairs;      // ceil(total tiles / 2)
 };
 
 __device__ __forceinline__ uint32_t sm_id() {
@@ -646,12 +651,9 @@ __device__ __forceinline__ uint32_t sm_id() {
     asm volatile("mov.u32 %0, %%smid;" : "=r"(s));
     return s;
 }
-// Tiles in SM s's range [s * per_sm, min((s + 1) * per_sm, total)).
-__device__ __forceinline__ uint32_t range_size(uint32_t total, uint32_t per_sm, uint32_t s) {
-    const uint64_t lo = static_cast<uint64_t>(s) * per_sm;
-    if (lo >= total) return 0u;
-    const uint64_t left = total - lo;
-    return left < per_sm ? static_cast<uint32_t>(left) : per_sm;
+// Pairs owned by shard j: those p < pairs with p mod kShards == j.
+__device__ __forceinline__ uint32_t shard_size(uint32_t pairs, uint32_t j) {
+    return pairs > j ? (pairs - j + kShards - 1) / kShards : 0u;
 }
 
 template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas, bool kDynamic>
@@ -659,7 +661,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     dispatch_multi_kernel(const DeviceImage img, const __grid_constant__ BatchList list, const TileSchedule sched) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ __align__(16) CtaShared sh;
-    static_assert(kUnroll == static_cast<int>(kDraw), "a draw is one round of the tile loop");
+    static_assert(kUnroll == 2, "a draw is one pair of tiles: one round of the tile loop");
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warps_per_cta = blockDim.x >> 5;
@@ -670,9 +672,9 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     // first draw before anything else: its latency hides behind the table staging
     uint32_t from = 0, size = 0, drawn = 0, steals = 0;
     if (kDynamic) {
-        from = sm_id() % sched.n_sms;
-        size = range_size(total_tiles, sched.per_sm, from);
-        if (lane == 0) drawn = atomicAdd(sched.next + from, kDraw);
+        from = (sm_id() * 11u) % kShards;  // the slow SMs come in runs of ids: neighbours go to different shards
+        size = shard_size(sched.pairs, from);
+        if (lane == 0) drawn = atomicAdd(sched.next + from * kShardStride, 1u);
     }
 
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
@@ -732,63 +734,41 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         }
     } else {
         for (;;) {
-            const uint32_t off = __shfl_sync(kFull, drawn, 0);
-            if (off >= size) {
-                // This range is used up.  Read every counter at once and pick another SM's range at
-                // random, in proportion to the tiles it has left: idle warps then spread over the
-                // unfinished ranges instead of all descending on one counter.
-                uint32_t left[kMaxSms / 32];
-                uint32_t lane_sum = 0;
-#pragma unroll
-                for (uint32_t k = 0; k < kMaxSms / 32; ++k) {
-                    const uint32_t s = lane + 32 * k;
-                    left[k] = 0;
-                    if (s < sched.n_sms) {
-                        const uint32_t sz = range_size(total_tiles, sched.per_sm, s);
-                        const uint32_t used = __ldcg(sched.next + s);
-                        left[k] = used < sz ? sz - used : 0u;
-                    }
-                    lane_sum += left[k];
+            const uint32_t d = __shfl_sync(kFull, drawn, 0);
+            if (d >= size) {
+                // This shard is used up.  Read every counter at once and move to another shard,
+                // picked at random in proportion to the pairs it has left, so that idle warps
+                // spread over the unfinished shards instead of all descending on one counter.
+                uint32_t left = 0;
+                if (lane < kShards) {
+                    const uint32_t sz = shard_size(sched.pairs, lane);
+                    const uint32_t used = __ldcg(sched.next + lane * kShardStride);
+                    left = used < sz ? sz - used : 0u;
                 }
-                uint32_t incl = lane_sum;
+                uint32_t incl = left;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
                     const uint32_t t = __shfl_up_sync(kFull, incl, o);
                     if (lane >= static_cast<uint32_t>(o)) incl += t;
                 }
-                const uint32_t best = __shfl_sync(kFull, incl, 31);  // tiles left anywhere
-                uint32_t best_sm = 0;
-                if (best != 0) {
-                    uint32_t h = (warp_global + 1u) * 0x9E3779B1u + (++steals) * 0x85EBCA77u;
-                    h ^= h >> 15;
-                    h *= 0x2C1B3C6Du;
-                    h ^= h >> 12;
-                    const uint32_t r = __umulhi(h, best);  // uniform in [0, best)
-                    const bool mine = r >= incl - lane_sum && r < incl;
-                    uint32_t pick = 0;
-                    if (mine) {
-                        uint32_t rr = r - (incl - lane_sum);
-#pragma unroll
-                        for (uint32_t k = 0; k < kMaxSms / 32; ++k) {
-                            if (rr < left[k]) {
-                                pick = lane + 32 * k;
-                                break;
-                            }
-                            rr -= left[k];
-                        }
-                    }
-                    best_sm = __shfl_sync(kFull, pick, __ffs(__ballot_sync(kFull, mine)) - 1);
-                }
-                if (best == 0) break;  // nothing left anywhere
-                from = best_sm;
-                size = range_size(total_tiles, sched.per_sm, from);
-                cursor = 0;
-                if (lane == 0) drawn = atomicAdd(sched.next + from, kDraw);
+                const uint32_t total_left = __shfl_sync(kFull, incl, 31);
+                if (total_left == 0) break;  // nothing left anywhere
+                uint32_t h = (warp_global + 1u) * 0x9E3779B1u + (++steals) * 0x85EBCA77u;
+                h ^= h >> 15;
+                h *= 0x2C1B3C6Du;
+                h ^= h >> 12;
+                const uint32_t r = __umulhi(h, total_left);  // uniform in [0, total_left)
+                const bool mine = r >= incl - left && r < incl;
+                from = static_cast<uint32_t>(__ffs(__ballot_sync(kFull, mine)) - 1);
+                size = shard_size(sched.pairs, from);
+                cursor = 0;  // the new shard may be behind this warp's last tile
+                if (lane == 0) drawn = atomicAdd(sched.next + from * kShardStride, 1u);
                 continue;
             }
-            if (lane == 0) drawn = atomicAdd(sched.next + from, kDraw);  // the next round, fetched while this one runs
-            const uint32_t left = size - off;
-            round(from * sched.per_sm + off, 1u, left < kDraw ? left : kDraw);
+            if (lane == 0) drawn = atomicAdd(sched.next + from * kShardStride, 1u);  // next round, fetched while this one runs
+            const uint32_t first = (d * kShards + from) * 2u;
+            const uint32_t remaining = total_tiles - first;
+            round(first, 1u, remaining < 2u ? remaining : 2u);
         }
     }
     if (!table_ready) mbar_wait(&sh.table_bar, 0);
@@ -802,7 +782,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         }
         __syncthreads();
         if (s_last) {
-            for (uint32_t s = threadIdx.x; s < sched.n_sms; s += blockDim.x) sched.next[s] = 0;
+            if (threadIdx.x < kShards) sched.next[threadIdx.x * kShardStride] = 0;
             if (threadIdx.x == 0) sched.done[0] = 0;
             __threadfence();
         }
@@ -1221,7 +1201,15 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
 
 // Up to kMaxBatchesPerLaunch device-resident batches in ONE launch.
 int max_batches_per_launch() { return kMaxBatchesPerLaunch; }
-size_t sched_slot_words() { return kMaxSms + 32; }  // per-SM counters, then the finished-CTA count on its own line
+size_t sched_slot_words() { return kShards * kShardStride + 64; }  // shard counters, then the finished-CTA count
+// Launches shorter than this many tiles keep the static partition (PTYPE_B200_DYNAMIC_MIN_TILES).
+uint64_t dynamic_min_tiles() {
+    static const uint64_t v = [] {
+        const char* e = std::getenv("PTYPE_B200_DYNAMIC_MIN_TILES");
+        return e ? std::strtoull(e, nullptr, 10) : 4ull * 32768ull;
+    }();
+    return v;
+}
 
 cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count, int device_sms,
                                   const ptype_batch* batches, int count, unsigned int* sched_slot,
@@ -1253,15 +1241,16 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         return launch_kernel(dispatch_bulk_multi_kernel<false, kStagesDefault>, blocks, plan.threads,
                              plan.dyn_smem, stream, pdl, img, list, table_smem);
     }
-    // Dynamic tile hand-out when the caller gave a counter slot (see TileSchedule).
+    // Dynamic tile hand-out when the caller gave a counter slot (see TileSchedule) and the launch
+    // is long enough for the balance to outweigh the draws' fixed cost (a few microseconds).
     TileSchedule sched = {};
-    const bool dynamic = sched_slot != nullptr && device_sms >= 1 && static_cast<uint32_t>(device_sms) <= kMaxSms;
+    const bool dynamic = sched_slot != nullptr && tiles >= dynamic_min_tiles() && tiles < 0x7FFFFFF0ull;
     if (dynamic) {
         sched.next = sched_slot;
-        sched.done = sched_slot + kMaxSms;
-        sched.n_sms = static_cast<uint32_t>(device_sms);
-        sched.per_sm = static_cast<uint32_t>((tiles + device_sms - 1) / device_sms);
+        sched.done = sched_slot + kShards * kShardStride;
+        sched.pairs = static_cast<uint32_t>((tiles + 1) / 2);
     }
+    (void)device_sms;
 #define PTYPE_MULTI(SM, UNROLL, THREADS, MINCTAS)                                                            \
     (dynamic ? launch_kernel(dispatch_multi_kernel<SM, UNROLL, THREADS, MINCTAS, true>, blocks, plan.threads, \
                              plan.dyn_smem, stream, pdl, img, list, sched)                                   \
