@@ -643,9 +643,8 @@ constexpr uint32_t kShardStride = 64;  // 32-bit words between counters (256 byt
 struct TileSchedule {
     unsigned int* next;  // kShards counters, kShardStride words apart; nullptr = static round-robin
     unsigned int* done;  // [1]
-    uint32_t pairs;      // ceil(total tiles / 2)
-    uint32_t glog;       // pairs are dealt to the shards in groups of 2^glog consecutive pairs
-    uint32_t by_warp;    // 1: a warp's home shard comes from its index, 0: from its SM
+    uint32_t pairs;      // pairs of tiles handed out dynamically: the launch's last ones
+    uint32_t first_tile; // where they start; the tiles before are shared out statically
 };
 
 __device__ __forceinline__ uint32_t sm_id() {
@@ -653,17 +652,9 @@ __device__ __forceinline__ uint32_t sm_id() {
     asm volatile("mov.u32 %0, %%smid;" : "=r"(s));
     return s;
 }
-// Pairs owned by shard j: the groups g (2^glog consecutive pairs) with g mod kShards == j.
-__device__ __forceinline__ uint32_t shard_size(uint32_t pairs, uint32_t glog, uint32_t j) {
-    const uint32_t groups = (pairs + (1u << glog) - 1) >> glog;
-    if (groups <= j) return 0u;
-    uint32_t mine = ((groups - j + kShards - 1) / kShards) << glog;
-    if ((groups - 1) % kShards == j) mine -= (groups << glog) - pairs;  // the last group may be short
-    return mine;
-}
-// The d-th pair of shard j.
-__device__ __forceinline__ uint32_t shard_pair(uint32_t glog, uint32_t j, uint32_t d) {
-    return ((((d >> glog) * kShards) + j) << glog) | (d & ((1u << glog) - 1u));
+// Pairs owned by shard j: those p < pairs with p mod kShards == j.
+__device__ __forceinline__ uint32_t shard_size(uint32_t pairs, uint32_t j) {
+    return pairs > j ? (pairs - j + kShards - 1) / kShards : 0u;
 }
 
 template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas, bool kDynamic>
@@ -682,9 +673,8 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     // first draw before anything else: its latency hides behind the table staging
     uint32_t from = 0, size = 0, drawn = 0, steals = 0;
     if (kDynamic) {
-        // the slow SMs come in runs of ids: neighbours go to different shards
-        from = ((sched.by_warp ? warp_global : sm_id()) * 11u) % kShards;
-        size = shard_size(sched.pairs, sched.glog, from);
+        from = (sm_id() * 11u) % kShards;  // the slow SMs come in runs of ids: neighbours go to different shards
+        size = shard_size(sched.pairs, from);
         if (lane == 0) drawn = atomicAdd(sched.next + from * kShardStride, 1u);
     }
 
@@ -738,12 +728,13 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         }
     };
 
-    if (!kDynamic) {
-        for (uint32_t g0 = warp_global; g0 < total_tiles; g0 += total_warps * kUnroll) {
-            const uint32_t left = (total_tiles - g0 + total_warps - 1) / total_warps;
-            round(g0, total_warps, left < static_cast<uint32_t>(kUnroll) ? left : static_cast<uint32_t>(kUnroll));
-        }
-    } else {
+    // static share first: tiles [0, static_end), warp w takes w, w + W, w + 2W, ...
+    const uint32_t static_end = kDynamic ? sched.first_tile : total_tiles;
+    for (uint32_t g0 = warp_global; g0 < static_end; g0 += total_warps * kUnroll) {
+        const uint32_t left = (static_end - g0 + total_warps - 1) / total_warps;
+        round(g0, total_warps, left < static_cast<uint32_t>(kUnroll) ? left : static_cast<uint32_t>(kUnroll));
+    }
+    if (kDynamic) {
         for (;;) {
             const uint32_t d = __shfl_sync(kFull, drawn, 0);
             if (d >= size) {
@@ -752,7 +743,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
                 // spread over the unfinished shards instead of all descending on one counter.
                 uint32_t left = 0;
                 if (lane < kShards) {
-                    const uint32_t sz = shard_size(sched.pairs, sched.glog, lane);
+                    const uint32_t sz = shard_size(sched.pairs, lane);
                     const uint32_t used = __ldcg(sched.next + lane * kShardStride);
                     left = used < sz ? sz - used : 0u;
                 }
@@ -771,13 +762,13 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
                 const uint32_t r = __umulhi(h, total_left);  // uniform in [0, total_left)
                 const bool mine = r >= incl - left && r < incl;
                 from = static_cast<uint32_t>(__ffs(__ballot_sync(kFull, mine)) - 1);
-                size = shard_size(sched.pairs, sched.glog, from);
+                size = shard_size(sched.pairs, from);
                 cursor = 0;  // the new shard may be behind this warp's last tile
                 if (lane == 0) drawn = atomicAdd(sched.next + from * kShardStride, 1u);
                 continue;
             }
             if (lane == 0) drawn = atomicAdd(sched.next + from * kShardStride, 1u);  // next round, fetched while this one runs
-            const uint32_t first = shard_pair(sched.glog, from, d) * 2u;
+            const uint32_t first = sched.first_tile + (d * kShards + from) * 2u;
             const uint32_t remaining = total_tiles - first;
             round(first, 1u, remaining < 2u ? remaining : 2u);
         }
@@ -1259,11 +1250,17 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     if (dynamic) {
         sched.next = sched_slot;
         sched.done = sched_slot + kShards * kShardStride;
-        sched.pairs = static_cast<uint32_t>((tiles + 1) / 2);
-        static const uint32_t glog = [] { const char* e = std::getenv("PTYPE_B200_SHARD_GROUP"); return e ? static_cast<uint32_t>(std::atoi(e)) : 0u; }();
-        static const uint32_t by_warp = [] { const char* e = std::getenv("PTYPE_B200_SHARD_BY"); return e ? static_cast<uint32_t>(std::atoi(e)) : 0u; }();
-        sched.glog = glog;
-        sched.by_warp = by_warp;
+        // The last `share` percent of the tiles are drawn; the rest is dealt out in whole rounds of
+        // the grid.  PTYPE_B200_DYNAMIC_SHARE overrides (100 = everything drawn).
+        static const uint64_t share = [] {
+            const char* e = std::getenv("PTYPE_B200_DYNAMIC_SHARE");
+            const long v = e ? std::atol(e) : 15;
+            return static_cast<uint64_t>(v < 0 ? 0 : (v > 100 ? 100 : v));
+        }();
+        const uint64_t round_tiles = static_cast<uint64_t>(blocks) * warps_per_cta * 2;
+        const uint64_t first = (tiles - tiles * share / 100) / round_tiles * round_tiles;
+        sched.first_tile = static_cast<uint32_t>(first);
+        sched.pairs = static_cast<uint32_t>((tiles - first + 1) / 2);
     }
     (void)device_sms;
 #define PTYPE_MULTI(SM, UNROLL, THREADS, MINCTAS)                                                            \
