@@ -37,14 +37,6 @@ int cuda_fail(cudaError_t e, const char* what) {
     } while (0)
 
 constexpr int kPipe = 4;                     // host-pointer pipeline depth
-constexpr int kSchedSlots = 8;               // at most two launches of a stream overlap; eight is ample
-bool dynamic_tiles_enabled() {               // PTYPE_B200_DYNAMIC=0: static partition (measurement switch)
-    static const bool on = [] {
-        const char* v = std::getenv("PTYPE_B200_DYNAMIC");
-        return !(v && v[0] == '0');
-    }();
-    return on;
-}
 constexpr size_t kMaxChunkCalls = 1024 * 1024;  // staging capacity per pipeline slot
 // Calls per pipelined chunk of the host-buffer paths.  PTYPE_B200_CHUNK overrides it
 // (measurement switch; multiples of 32, at most kMaxChunkCalls).
@@ -153,10 +145,6 @@ struct DeviceState {
     unsigned long long* d_stats = nullptr;
     uint32_t* d_failed = nullptr;
     size_t failed_cap = 0;
-    // Tile counters of the multi-batch launches (dispatch.cu: TileSchedule): kSchedSlots slots of
-    // {tiles handed out per SM, finished CTAs}, used round-robin; every launch leaves its slot zeroed.  Allocated and cleared once, at the context's first dispatch_batches.
-    unsigned int* d_sched = nullptr;
-    uint64_t sched_seq = 0;
     unsigned long long* d_cksum_partials = nullptr;  // scratch of the checksum kernel
     unsigned long long* d_cksum_out = nullptr;
     unsigned long long* d_size = nullptr;  // broadcast header scratch
@@ -439,7 +427,6 @@ void ptype_b200_close(ptype_ctx* ctx) {
             if (d->image_buf[b]) cudaFree(d->image_buf[b]);
         if (d->d_stats) cudaFree(d->d_stats);
         if (d->d_failed) cudaFree(d->d_failed);
-        if (d->d_sched) cudaFree(d->d_sched);
         if (d->d_cksum_partials) cudaFree(d->d_cksum_partials);
         if (d->d_cksum_out) cudaFree(d->d_cksum_out);
         if (d->d_size) cudaFree(d->d_size);
@@ -926,10 +913,6 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
         if (misaligned(batches[b].reqs, 16) || misaligned(batches[b].replies, 16)) return PTYPE_E_INVAL;
         if (batches[b].n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
     }
-    if (!(flags & PTYPE_F_ONE_LAUNCH_PER_BATCH) && !d->d_sched && dynamic_tiles_enabled()) {
-        CU(cudaMalloc(&d->d_sched, kSchedSlots * ptype::sched_slot_words() * sizeof(unsigned int)));
-        CU(cudaMemset(d->d_sched, 0, kSchedSlots * ptype::sched_slot_words() * sizeof(unsigned int)));
-    }
     if (!(flags & PTYPE_F_ONE_LAUNCH_PER_BATCH)) {
         // One launch per group of batches: the persistent grid walks their tiles as one
         // stream.  Groups are cut so that a launch stays below 2^32 tiles.
@@ -944,10 +927,8 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
             }
             if (e == b) return PTYPE_E_LIMIT;
             if (tiles) {
-                unsigned int* slot =
-                    d->d_sched ? d->d_sched + (d->sched_seq++ % kSchedSlots) * ptype::sched_slot_words() : nullptr;
-                CU(ptype::launch_dispatch_multi(img, plan, d->dispatch_sms, d->sm_count, batches + b,
-                                                static_cast<int>(e - b), slot, d->stream, take_pdl(d, flags)));
+                CU(ptype::launch_dispatch_multi(img, plan, d->dispatch_sms, batches + b, static_cast<int>(e - b),
+                                                d->stream, take_pdl(d, flags)));
                 ctx->launches.fetch_add(1);
             }
             b = e;

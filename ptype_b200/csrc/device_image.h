@@ -49,13 +49,8 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
                             uint32_t failed_cap, uint32_t idx_base, unsigned long long* stats,
                             cudaStream_t stream, bool pdl);
 int max_batches_per_launch();
-// sched_slot: sched_slot_words() zeroed 32-bit words in device memory for the launch's dynamic
-// tile hand-out (left zeroed again by the kernel), or nullptr for a static partition.  sm_count
-// sizes the grid; device_sms is the device's SM count (the counters are indexed by %smid).
-size_t sched_slot_words();
-cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count, int device_sms,
-                                  const ptype_batch* batches, int count, unsigned int* sched_slot,
-                                  cudaStream_t stream, bool pdl);
+cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
+                                  const ptype_batch* batches, int count, cudaStream_t stream, bool pdl);
 // Values-only output of a client batch: values != nullptr switches the kernel from 16-byte
 // reply records to 8-byte values plus an (index, status) list of the failed calls.
 struct CallBatchOut {

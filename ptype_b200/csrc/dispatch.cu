@@ -621,87 +621,40 @@ struct BatchList {
     int count;
 };
 
-// How the tiles of a launch are handed out.  next == nullptr: statically, warp w takes tiles
-// w, w + W, w + 2W, ...  Otherwise dynamically.  The SMs of a B200 do not stream from HBM at the
-// same pace: tools/spread_probe.cu shows the same groups of SMs finishing an equal share 20 %
-// later than the fastest ones, launch after launch (profiles/r02_spread_probe.txt), so with equal
-// shares a lone launch ends with most of the chip idle.  Two measurements shape the dynamic scheme:
-//  * one counter cannot hand out tiles fast enough (atomics on one address retire at about one
-//    per 2 ns, a tile is done in 0.3 ns), so there are kShards counters, each on its own line;
-//  * the chip must keep sweeping the batches front to back - giving every SM a contiguous range of
-//    its own ran 25 % SLOWER on distinct buffers (148 streams scattered over the DRAM rows instead
-//    of one front), and only looked faster while buffers repeated inside a launch (L2 hits).
-// So tile pair p (tiles 2p, 2p + 1: one round of a warp) belongs to shard p mod kShards, and draw d
-// of shard j is pair d * kShards + j: every shard walks the launch front to back.  A warp draws
-// from the shard its SM maps to; when that one is used up it reads all counters at once, picks
-// another shard at random in proportion to the pairs left, and carries on there.  The draw for the
-// next round is in flight while the current pair is processed.  done[0] counts finished CTAs; the
-// last one zeroes everything for the launch that will use this slot next (context.cu rotates
-// eight slots, and at most two launches of a stream ever overlap).
-constexpr uint32_t kShards = 16;
-constexpr uint32_t kShardStride = 64;  // 32-bit words between counters (256 bytes)
-struct TileSchedule {
-    unsigned int* next;  // kShards counters, kShardStride words apart; nullptr = static round-robin
-    unsigned int* done;  // [1]
-    uint32_t pairs;      // pairs of tiles handed out dynamically: the launch's last ones
-    uint32_t first_tile; // where they start; the tiles before are shared out statically
-};
-
-__device__ __forceinline__ uint32_t sm_id() {
-    uint32_t s;
-    asm volatile("mov.u32 %0, %%smid;" : "=r"(s));
-    return s;
-}
-// Pairs owned by shard j: those p < pairs with p mod kShards == j.
-__device__ __forceinline__ uint32_t shard_size(uint32_t pairs, uint32_t j) {
-    return pairs > j ? (pairs - j + kShards - 1) / kShards : 0u;
-}
-
-template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas, bool kDynamic>
+template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas>
 __global__ void __launch_bounds__(kThreads, kMinCtas)
-    dispatch_multi_kernel(const DeviceImage img, const __grid_constant__ BatchList list, const TileSchedule sched) {
+    dispatch_multi_kernel(const DeviceImage img, const __grid_constant__ BatchList list) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ __align__(16) CtaShared sh;
-    static_assert(kUnroll == 2, "a draw is one pair of tiles: one round of the tile loop");
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warps_per_cta = blockDim.x >> 5;
-    const uint32_t total_tiles = list.tile_end[list.count - 1];
-    const uint32_t total_warps = gridDim.x * warps_per_cta;
-    const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
-
-    // first draw before anything else: its latency hides behind the table staging
-    uint32_t from = 0, size = 0, drawn = 0, steals = 0;
-    if (kDynamic) {
-        from = (sm_id() * 11u) % kShards;  // the slow SMs come in runs of ids: neighbours go to different shards
-        size = shard_size(sched.pairs, from);
-        if (lane == 0) drawn = atomicAdd(sched.next + from * kShardStride, 1u);
-    }
-
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
 
     const TransposePlan plan = transpose_plan(lane);
+    const uint32_t total_tiles = list.tile_end[list.count - 1];
+    const uint32_t total_warps = gridDim.x * warps_per_cta;
+    const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
+
     LookupCache cache;
     bool table_ready = !kSmemTable;
-    int cursor = 0;  // batch holding the tile being fetched; tiles only move forward while cursor is kept
+    int cursor[kUnroll];  // batch holding each in-flight tile; tiles only move forward
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) cursor[u] = 0;
 
-    // one round: up to kUnroll tiles first, first + stride, ... (count of them)
-    auto round = [&](uint32_t first, uint32_t stride, uint32_t count) {
+    for (uint32_t g0 = warp_global; g0 < total_tiles; g0 += total_warps * kUnroll) {
         uint4 ld[kUnroll][3];
         uint32_t tile[kUnroll];
-        int batch[kUnroll];
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
+            const uint32_t g = g0 + u * total_warps;
             tile[u] = 0;
-            batch[u] = 0;
             ld[u][0] = ld[u][1] = ld[u][2] = make_uint4(0, 0, 0, 0);
-            if (static_cast<uint32_t>(u) < count) {
-                const uint32_t g = first + u * stride;
-                int b = cursor;
+            if (g < total_tiles) {
+                int b = cursor[u];
                 while (g >= list.tile_end[b]) ++b;
-                cursor = b;
-                batch[u] = b;
+                cursor[u] = b;
                 tile[u] = g - (b ? list.tile_end[b - 1] : 0u);
                 const size_t n_chunks = static_cast<size_t>(list.n[b]) * 3;
                 const uint4* reqs = list.reqs[b];
@@ -718,77 +671,17 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         }
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-            if (static_cast<uint32_t>(u) >= count) break;  // warp-uniform
+            if (g0 + u * total_warps >= total_tiles) break;  // warp-uniform
             uint4 q[3];
             transpose_tile(plan, lane, ld[u], q);
-            const int b = batch[u];
+            const int b = cursor[u];
             const size_t idx = (static_cast<size_t>(tile[u]) << 5) + lane;
             if (idx < list.n[b])
                 st_stream(list.replies[b] + idx, dispatch_one<kSmemTable>(img, sh, slots, cache, q[0], q[1], q[2]));
         }
-    };
-
-    // static share first: tiles [0, static_end), warp w takes w, w + W, w + 2W, ...
-    const uint32_t static_end = kDynamic ? sched.first_tile : total_tiles;
-    for (uint32_t g0 = warp_global; g0 < static_end; g0 += total_warps * kUnroll) {
-        const uint32_t left = (static_end - g0 + total_warps - 1) / total_warps;
-        round(g0, total_warps, left < static_cast<uint32_t>(kUnroll) ? left : static_cast<uint32_t>(kUnroll));
-    }
-    if (kDynamic) {
-        for (;;) {
-            const uint32_t d = __shfl_sync(kFull, drawn, 0);
-            if (d >= size) {
-                // This shard is used up.  Read every counter at once and move to another shard,
-                // picked at random in proportion to the pairs it has left, so that idle warps
-                // spread over the unfinished shards instead of all descending on one counter.
-                uint32_t left = 0;
-                if (lane < kShards) {
-                    const uint32_t sz = shard_size(sched.pairs, lane);
-                    const uint32_t used = __ldcg(sched.next + lane * kShardStride);
-                    left = used < sz ? sz - used : 0u;
-                }
-                uint32_t incl = left;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const uint32_t t = __shfl_up_sync(kFull, incl, o);
-                    if (lane >= static_cast<uint32_t>(o)) incl += t;
-                }
-                const uint32_t total_left = __shfl_sync(kFull, incl, 31);
-                if (total_left == 0) break;  // nothing left anywhere
-                uint32_t h = (warp_global + 1u) * 0x9E3779B1u + (++steals) * 0x85EBCA77u;
-                h ^= h >> 15;
-                h *= 0x2C1B3C6Du;
-                h ^= h >> 12;
-                const uint32_t r = __umulhi(h, total_left);  // uniform in [0, total_left)
-                const bool mine = r >= incl - left && r < incl;
-                from = static_cast<uint32_t>(__ffs(__ballot_sync(kFull, mine)) - 1);
-                size = shard_size(sched.pairs, from);
-                cursor = 0;  // the new shard may be behind this warp's last tile
-                if (lane == 0) drawn = atomicAdd(sched.next + from * kShardStride, 1u);
-                continue;
-            }
-            if (lane == 0) drawn = atomicAdd(sched.next + from * kShardStride, 1u);  // next round, fetched while this one runs
-            const uint32_t first = sched.first_tile + (d * kShards + from) * 2u;
-            const uint32_t remaining = total_tiles - first;
-            round(first, 1u, remaining < 2u ? remaining : 2u);
-        }
     }
     if (!table_ready) mbar_wait(&sh.table_bar, 0);
     griddep_wait();
-    if (kDynamic) {
-        __syncthreads();  // every warp of the CTA has had its last draw answered
-        __shared__ unsigned int s_last;
-        if (threadIdx.x == 0) {
-            __threadfence();
-            s_last = atomicAdd(sched.done, 1u) == gridDim.x - 1 ? 1u : 0u;
-        }
-        __syncthreads();
-        if (s_last) {
-            if (threadIdx.x < kShards) sched.next[threadIdx.x * kShardStride] = 0;
-            if (threadIdx.x == 0) sched.done[0] = 0;
-            __threadfence();
-        }
-    }
 }
 
 // Bulk-staged twin of dispatch_multi_kernel: per-warp TMA ring over the tile stream of many
@@ -1203,19 +1096,9 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
 
 // Up to kMaxBatchesPerLaunch device-resident batches in ONE launch.
 int max_batches_per_launch() { return kMaxBatchesPerLaunch; }
-size_t sched_slot_words() { return kShards * kShardStride + 64; }  // shard counters, then the finished-CTA count
-// Launches shorter than this many tiles keep the static partition (PTYPE_B200_DYNAMIC_MIN_TILES).
-uint64_t dynamic_min_tiles() {
-    static const uint64_t v = [] {
-        const char* e = std::getenv("PTYPE_B200_DYNAMIC_MIN_TILES");
-        return e ? std::strtoull(e, nullptr, 10) : 4ull * 32768ull;
-    }();
-    return v;
-}
 
-cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count, int device_sms,
-                                  const ptype_batch* batches, int count, unsigned int* sched_slot,
-                                  cudaStream_t stream, bool pdl) {
+cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
+                                  const ptype_batch* batches, int count, cudaStream_t stream, bool pdl) {
     BatchList list = {};
     uint64_t tiles = 0;
     int m = 0;
@@ -1243,36 +1126,18 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         return launch_kernel(dispatch_bulk_multi_kernel<false, kStagesDefault>, blocks, plan.threads,
                              plan.dyn_smem, stream, pdl, img, list, table_smem);
     }
-    // Dynamic tile hand-out when the caller gave a counter slot (see TileSchedule) and the launch
-    // is long enough for the balance to outweigh the draws' fixed cost (a few microseconds).
-    TileSchedule sched = {};
-    const bool dynamic = sched_slot != nullptr && tiles >= dynamic_min_tiles() && tiles < 0x7FFFFFF0ull;
-    if (dynamic) {
-        sched.next = sched_slot;
-        sched.done = sched_slot + kShards * kShardStride;
-        // The last `share` percent of the tiles are drawn; the rest is dealt out in whole rounds of
-        // the grid.  PTYPE_B200_DYNAMIC_SHARE overrides (100 = everything drawn).
-        static const uint64_t share = [] {
-            const char* e = std::getenv("PTYPE_B200_DYNAMIC_SHARE");
-            const long v = e ? std::atol(e) : 15;
-            return static_cast<uint64_t>(v < 0 ? 0 : (v > 100 ? 100 : v));
-        }();
-        const uint64_t round_tiles = static_cast<uint64_t>(blocks) * warps_per_cta * 2;
-        const uint64_t first = (tiles - tiles * share / 100) / round_tiles * round_tiles;
-        sched.first_tile = static_cast<uint32_t>(first);
-        sched.pairs = static_cast<uint32_t>((tiles - first + 1) / 2);
+    if (plan.threads == kMaxThreads) {
+        if (plan.smem_table)
+            return launch_kernel(dispatch_multi_kernel<true, 2, kMaxThreads, 1>, blocks, plan.threads,
+                                 plan.dyn_smem, stream, pdl, img, list);
+        return launch_kernel(dispatch_multi_kernel<false, 2, kMaxThreads, 1>, blocks, plan.threads,
+                             plan.dyn_smem, stream, pdl, img, list);
     }
-    (void)device_sms;
-#define PTYPE_MULTI(SM, UNROLL, THREADS, MINCTAS)                                                            \
-    (dynamic ? launch_kernel(dispatch_multi_kernel<SM, UNROLL, THREADS, MINCTAS, true>, blocks, plan.threads, \
-                             plan.dyn_smem, stream, pdl, img, list, sched)                                   \
-             : launch_kernel(dispatch_multi_kernel<SM, UNROLL, THREADS, MINCTAS, false>, blocks, plan.threads, \
-                             plan.dyn_smem, stream, pdl, img, list, sched))
-    if (plan.threads == kMaxThreads)
-        return plan.smem_table ? PTYPE_MULTI(true, 2, kMaxThreads, 1) : PTYPE_MULTI(false, 2, kMaxThreads, 1);
-    return plan.smem_table ? PTYPE_MULTI(true, kSmallUnroll, kSmallThreads, kSmallMinCtas)
-                           : PTYPE_MULTI(false, kSmallUnroll, kSmallThreads, kSmallMinCtas);
-#undef PTYPE_MULTI
+    if (plan.smem_table)
+        return launch_kernel(dispatch_multi_kernel<true, kSmallUnroll, kSmallThreads, kSmallMinCtas>, blocks,
+                             plan.threads, plan.dyn_smem, stream, pdl, img, list);
+    return launch_kernel(dispatch_multi_kernel<false, kSmallUnroll, kSmallThreads, kSmallMinCtas>, blocks,
+                         plan.threads, plan.dyn_smem, stream, pdl, img, list);
 }
 
 namespace {
