@@ -444,6 +444,52 @@ int ptype_b200_gob_encode_replies(ptype_ctx*, int dev, const ptype_reply* replie
 int ptype_b200_gob_decode_args(ptype_ctx*, int dev, const uint8_t* bytes, const uint64_t* offsets, size_t n,
                                int64_t* args, int args_per_call, uint8_t* status);
 
+/* ---- net/rpc's byte streams on the device -------------------------------------
+ * What travels on a connection dialled by rpc.DialHTTP (cluster/rpc.go:277) after the CONNECT
+ * handshake: encoding/gob messages - per call an rpc.Request{ServiceMethod, Seq} value and an args
+ * value from the client (cluster/rpc.go:65,88), an rpc.Response{ServiceMethod, Seq, Error} value
+ * and a reply value from the server (rpc.Register/HandleHTTP, example/calculator/server/
+ * server.go:16-20), with the type definitions gob sends before a type's first use.
+ *
+ * wire_decode takes the client-to-server bytes of n_streams connections (stream s spans
+ * bytes[stream_off[s] .. stream_off[s+1]), each starting at a message boundary; it may begin with
+ * the connection's type definitions or in mid-conversation) and writes one ptype_req per call:
+ * method/recv hashed from the ServiceMethod string (split at the last '.'), a0..a2 from the args
+ * value, svc_key and seq from the stream's descriptor (call i of stream s gets seq0 + i*seq_step:
+ * the connection IS the client's routing decision, so the sequence number is the caller's to
+ * state).  calls[] keeps what the answer must echo: net/rpc's own Seq and where the method string
+ * lies in `bytes`.  call_off[0..n_streams] receives the index of every stream's first call.
+ * *total_calls is always set; PTYPE_E_LIMIT (nothing decoded) when it exceeds cap.
+ *
+ * wire_encode writes the server-to-client bytes for those calls from their reply records:
+ * Response header + `int` reply, or, for a status other than OK, the Error text net/rpc's server
+ * sends ("rpc: can't find service X", ...) + the empty struct.  state[s] (one byte per stream,
+ * 0 for a fresh connection, updated in place) remembers which definitions the connection has
+ * seen: bit 0 rpc.Response, bit 1 the empty struct.  response_id / empty_id are the gob type ids
+ * the sending process assigned to those two types (Go numbers user types from 65 in order of
+ * first use).  out_off[0..n_streams] receives where every stream's bytes start in `out`;
+ * *total_bytes is always set; PTYPE_E_LIMIT (nothing written, state untouched) beyond out_cap.
+ * All pointers are device pointers on `dev`; both calls wait for completion. */
+#define PTYPE_WIRE_MALFORMED 1u
+typedef struct ptype_wire_stream {
+    uint64_t svc_key;  /* as ptype_req.svc_key: the service this server's node belongs to */
+    uint64_t seq0;     /* ptype_req.seq of the stream's first call ...                      */
+    uint64_t seq_step; /* ... and the step to the next one                                  */
+} ptype_wire_stream;
+typedef struct ptype_wire_call {
+    uint64_t rpc_seq; /* rpc.Request.Seq: net/rpc's per-connection call number, echoed back */
+    uint64_t sm_off;  /* the ServiceMethod string: offset into the request bytes ...         */
+    uint32_t sm_len;  /* ... and length                                                       */
+    uint32_t flags;   /* PTYPE_WIRE_MALFORMED: the call's messages did not parse             */
+} ptype_wire_call;
+int ptype_b200_wire_decode(ptype_ctx*, int dev, const uint8_t* bytes, const uint64_t* stream_off, size_t n_streams,
+                           const ptype_wire_stream* streams, uint64_t* call_off, ptype_req* reqs,
+                           ptype_wire_call* calls, size_t cap, uint64_t* total_calls);
+int ptype_b200_wire_encode(ptype_ctx*, int dev, const uint8_t* request_bytes, const uint64_t* call_off,
+                           size_t n_streams, const ptype_wire_call* calls, const ptype_reply* replies,
+                           uint32_t response_id, uint32_t empty_id, uint8_t* state, uint64_t* out_off, uint8_t* out,
+                           size_t out_cap, uint64_t* total_bytes);
+
 /* ---- the balancer's counters on the device ---------------------------------
  * Every reference Client owns one counter, `seq` (cluster/rpc.go:129); roundRobinSelect takes its
  * next value for each call that finds a non-empty client list - the length check at rpc.go:178-180

@@ -90,6 +90,7 @@ def lib() -> C.CDLL:
             "po_gob_int": (C.c_int, [C.c_int64, C.c_char_p]),
             "po_loopback_run": (C.c_int, [vp, C.c_size_t, vp, C.c_int, C.c_uint32, C.c_uint64,
                                           C.POINTER(LoopbackStats)]),
+            "po_wire_streams": (C.c_int, [vp, C.c_size_t, C.c_uint32, C.c_uint64, vp, C.c_size_t, vp, vp, C.c_size_t, vp]),
             "po_gob_reply_int_message": (C.c_int, [C.c_int64, C.c_char_p]),
             "po_gob_args_body": (C.c_int, [C.POINTER(C.c_int64), C.c_int, C.c_char_p]),
             "po_gob_request_typedef": (C.c_int, [C.c_char_p]),
@@ -243,6 +244,22 @@ class Snapshot:
             self.close()
         except Exception:
             pass
+
+
+def wire_streams(reqs: np.ndarray, receivers: int = 1, check_limit: int = 1 << 16):
+    """The net/rpc byte streams of ONE fresh connection carrying the calls `reqs` (after the CONNECT
+    handshake), from the encoders the loopback run sends over TCP: returns
+    (client_to_server bytes, offsets[n+1], server_to_client bytes, offsets[n+1])."""
+    reqs = np.ascontiguousarray(reqs, dtype=REQ_DTYPE)
+    n = len(reqs)
+    cap = 256 + 160 * n
+    c2s, s2c = np.zeros(cap, dtype=np.uint8), np.zeros(cap + 64 * n, dtype=np.uint8)
+    co, so = np.zeros(n + 1, dtype=np.uint64), np.zeros(n + 1, dtype=np.uint64)
+    rc = lib().po_wire_streams(reqs.ctypes.data, n, receivers, check_limit, c2s.ctypes.data, len(c2s),
+                               co.ctypes.data, s2c.ctypes.data, len(s2c), so.ctypes.data)
+    if rc != 0:
+        raise RuntimeError("po_wire_streams: buffer too small")
+    return c2s[: int(co[n])].copy(), co, s2c[: int(so[n])].copy(), so
 
 
 def reply_checksum(rep: np.ndarray, index_base: int = 0) -> int:

@@ -214,6 +214,87 @@ static void send_all(int fd, const uint8_t* p, size_t n, uint64_t* counter) {
     }
 }
 
+/* What the server does with one decoded request [net/rpc server.readRequestHeader + service.call]:
+ * split at the last '.', find the receiver among those this node registered, find the method,
+ * run it.  Returns NULL and *reply on success, else the error text net/rpc would send. */
+static const char* server_execute(const lb_server* srv, const char* sm, const int64_t* a, int64_t* reply,
+                                  char* errbuf, size_t errcap) {
+    const char* dot = strrchr(sm, '.');
+    *reply = 0;
+    if (!dot) {
+        snprintf(errbuf, errcap, "rpc: service/method request ill-formed: %s", sm);
+        return errbuf;
+    }
+    size_t rl = (size_t)(dot - sm);
+    int is_calc = rl == 10 && !strncmp(sm, "Calculator", 10) && (srv->receivers & 1);
+    int is_prime = rl == 5 && !strncmp(sm, "Prime", 5) && (srv->receivers & 2);
+    if (!is_calc && !is_prime) {
+        snprintf(errbuf, errcap, "rpc: can't find service %s", sm);
+        return errbuf;
+    }
+    if (is_calc && !strcmp(dot + 1, "Multiply")) {
+        *reply = po_multiply(a[0], a[1]);
+    } else if (is_calc && !strcmp(dot + 1, "Add")) {
+        *reply = po_add(a[0], a[1]);
+    } else if (is_prime && !strcmp(dot + 1, "Check")) {
+        if (po_check_width(a[0], a[1], a[2]) > srv->check_limit) {
+            snprintf(errbuf, errcap, "ptype: check range beyond limit");
+            return errbuf;
+        }
+        *reply = po_check(a[0], a[1], a[2]);
+    } else {
+        snprintf(errbuf, errcap, "rpc: can't find method %s", sm);
+        return errbuf;
+    }
+    return NULL;
+}
+
+/* Per-connection encoder state of the server: which type definitions have gone out. */
+typedef struct {
+    int sent_types, sent_empty;
+} lb_server_wire;
+
+/* sendResponse [net/rpc]: gob(Response{ServiceMethod, Seq, Error}) then gob(reply), or on error
+ * gob(invalidRequest = struct{}{}); type definitions precede their first use.  Appends to out. */
+static void server_encode_response(lb_server_wire* st, const char* sm, uint64_t seq, const char* err,
+                                   int64_t reply, wbuf* out) {
+    if (!st->sent_types) {
+        const char* fn[] = {"ServiceMethod", "Seq", "Error"};
+        const int fi[] = {T_STRING, T_UINT, T_STRING};
+        gob_typedef_struct(out, T_RESPONSE, "Response", 3, fn, fi);
+        st->sent_types = 1;
+    }
+    wbuf b = {0};
+    wb_int(&b, T_RESPONSE);
+    wb_byte(&b, 1);
+    wb_string(&b, sm);
+    if (seq) {
+        wb_byte(&b, 1);
+        wb_uint(&b, seq);
+    }
+    if (err) {
+        wb_byte(&b, (uint8_t)(seq ? 1 : 2));
+        wb_string(&b, err);
+    }
+    wb_byte(&b, 0);
+    wb_message(out, &b);
+    b.n = 0;
+    if (err) { /* body is invalidRequest = struct{}{} */
+        if (!st->sent_empty) {
+            gob_typedef_struct(out, T_EMPTY, "", 0, NULL, NULL);
+            st->sent_empty = 1;
+        }
+        wb_int(&b, T_EMPTY);
+        wb_byte(&b, 0);
+    } else {
+        wb_int(&b, T_INT);
+        wb_byte(&b, 0); /* top-level non-struct marker */
+        wb_int(&b, reply);
+    }
+    wb_message(out, &b);
+    free(b.p);
+}
+
 /* ServeConn loop of one accepted connection [net/rpc server.ServeCodec]. */
 static void serve_conn(int fd, const lb_server* srv) {
     rbuf* r = (rbuf*)calloc(1, sizeof *r);
@@ -233,7 +314,7 @@ static void serve_conn(int fd, const lb_server* srv) {
         const char* ok = "HTTP/1.0 200 Connected to Go RPC\n\n";
         send_all(fd, (const uint8_t*)ok, strlen(ok), NULL);
     }
-    int sent_types = 0, sent_empty = 0;
+    lb_server_wire wire = {0, 0};
     wbuf out = {0};
     for (;;) {
         /* ---- readRequestHeader */
@@ -266,74 +347,12 @@ static void serve_conn(int fd, const lb_server* srv) {
             if (rb_int(r, &v)) goto out_loop;
             if (field >= 0 && field < 3) a[field] = v;
         }
-        /* ---- service / method lookup */
-        const char* err = NULL;
+        /* ---- service / method lookup, the call, sendResponse */
         char errbuf[320];
         int64_t reply = 0;
-        const char* dot = strrchr(sm, '.');
-        if (!dot) {
-            snprintf(errbuf, sizeof errbuf, "rpc: service/method request ill-formed: %s", sm);
-            err = errbuf;
-        } else {
-            size_t rl = (size_t)(dot - sm);
-            int is_calc = rl == 10 && !strncmp(sm, "Calculator", 10) && (srv->receivers & 1);
-            int is_prime = rl == 5 && !strncmp(sm, "Prime", 5) && (srv->receivers & 2);
-            if (!is_calc && !is_prime) {
-                snprintf(errbuf, sizeof errbuf, "rpc: can't find service %s", sm);
-                err = errbuf;
-            } else if (is_calc && !strcmp(dot + 1, "Multiply")) {
-                reply = po_multiply(a[0], a[1]);
-            } else if (is_calc && !strcmp(dot + 1, "Add")) {
-                reply = po_add(a[0], a[1]);
-            } else if (is_prime && !strcmp(dot + 1, "Check")) {
-                if (po_check_width(a[0], a[1], a[2]) > srv->check_limit) {
-                    snprintf(errbuf, sizeof errbuf, "ptype: check range beyond limit");
-                    err = errbuf;
-                } else {
-                    reply = po_check(a[0], a[1], a[2]);
-                }
-            } else {
-                snprintf(errbuf, sizeof errbuf, "rpc: can't find method %s", sm);
-                err = errbuf;
-            }
-        }
-        /* ---- sendResponse */
+        const char* err = server_execute(srv, sm, a, &reply, errbuf, sizeof errbuf);
         out.n = 0;
-        if (!sent_types) {
-            const char* fn[] = {"ServiceMethod", "Seq", "Error"};
-            const int fi[] = {T_STRING, T_UINT, T_STRING};
-            gob_typedef_struct(&out, T_RESPONSE, "Response", 3, fn, fi);
-            sent_types = 1;
-        }
-        wbuf b = {0};
-        wb_int(&b, T_RESPONSE);
-        wb_byte(&b, 1);
-        wb_string(&b, sm);
-        if (seq) {
-            wb_byte(&b, 1);
-            wb_uint(&b, seq);
-        }
-        if (err) {
-            wb_byte(&b, (uint8_t)(seq ? 1 : 2));
-            wb_string(&b, err);
-        }
-        wb_byte(&b, 0);
-        wb_message(&out, &b);
-        b.n = 0;
-        if (err) { /* body is invalidRequest = struct{}{} */
-            if (!sent_empty) {
-                gob_typedef_struct(&out, T_EMPTY, "", 0, NULL, NULL);
-                sent_empty = 1;
-            }
-            wb_int(&b, T_EMPTY);
-            wb_byte(&b, 0);
-        } else {
-            wb_int(&b, T_INT);
-            wb_byte(&b, 0); /* top-level non-struct marker */
-            wb_int(&b, reply);
-        }
-        wb_message(&out, &b);
-        free(b.p);
+        server_encode_response(&wire, sm, seq, err, reply, &out);
         send_all(fd, out.p, out.n, NULL);
     }
 out_loop:
@@ -390,11 +409,16 @@ static int server_start(lb_server* s) {
 }
 
 /* ------------------------------------------------------------------ client */
+/* Per-connection encoder state of the client. */
+typedef struct {
+    uint64_t rpc_seq; /* net/rpc's own Seq, starts at 0 per connection */
+    int sent_request_type, sent_args2, sent_args3;
+} lb_client_wire;
+
 typedef struct {
     int fd;
     rbuf* r;
-    uint64_t rpc_seq; /* net/rpc's own Seq, starts at 0 per connection */
-    int sent_request_type, sent_args2, sent_args3;
+    lb_client_wire wire;
     uint64_t bytes_out;
 } lb_conn;
 
@@ -427,36 +451,37 @@ static int conn_dial(lb_conn* c, int port) { /* rpc.DialHTTP (rpc.go:277) */
 }
 
 /* (*rpc.Client).Call: one request in flight, wait for its response. */
-static int conn_call(lb_conn* c, const char* sm, const int64_t* a, int nargs, ptype_reply* rep, wbuf* out) {
-    out->n = 0;
-    if (!c->sent_request_type) {
+/* What (*rpc.Client).send writes for one call [net/rpc + encoding/gob]: gob(Request{ServiceMethod,
+ * Seq}) then gob(args); type definitions precede their first use on the connection.  Appends. */
+static void client_encode_call(lb_client_wire* st, const char* sm, const int64_t* a, int nargs, wbuf* out) {
+    if (!st->sent_request_type) {
         const char* fn[] = {"ServiceMethod", "Seq"};
         const int fi[] = {T_STRING, T_UINT};
         gob_typedef_struct(out, T_REQUEST, "Request", 2, fn, fi);
-        c->sent_request_type = 1;
+        st->sent_request_type = 1;
     }
     wbuf b = {0};
     wb_int(&b, T_REQUEST);
     wb_byte(&b, 1);
     wb_string(&b, sm);
-    if (c->rpc_seq) {
+    if (st->rpc_seq) {
         wb_byte(&b, 1);
-        wb_uint(&b, c->rpc_seq);
+        wb_uint(&b, st->rpc_seq);
     }
     wb_byte(&b, 0);
     wb_message(out, &b);
-    c->rpc_seq++;
+    st->rpc_seq++;
     int tid = nargs == 3 ? T_ARGS3 : T_ARGS2;
-    if (nargs == 3 && !c->sent_args3) {
+    if (nargs == 3 && !st->sent_args3) {
         const char* fn[] = {"Min", "Max", "Target"};
         const int fi[] = {T_INT, T_INT, T_INT};
         gob_typedef_struct(out, T_ARGS3, "Args", 3, fn, fi);
-        c->sent_args3 = 1;
-    } else if (nargs != 3 && !c->sent_args2) {
+        st->sent_args3 = 1;
+    } else if (nargs != 3 && !st->sent_args2) {
         const char* fn[] = {"A", "B"};
         const int fi[] = {T_INT, T_INT};
         gob_typedef_struct(out, T_ARGS2, "Args", 2, fn, fi);
-        c->sent_args2 = 1;
+        st->sent_args2 = 1;
     }
     b.n = 0;
     wb_int(&b, tid);
@@ -470,6 +495,11 @@ static int conn_call(lb_conn* c, const char* sm, const int64_t* a, int nargs, pt
     wb_byte(&b, 0);
     wb_message(out, &b);
     free(b.p);
+}
+
+static int conn_call(lb_conn* c, const char* sm, const int64_t* a, int nargs, ptype_reply* rep, wbuf* out) {
+    out->n = 0;
+    client_encode_call(&c->wire, sm, a, nargs, out);
     send_all(c->fd, out->p, out->n, &c->bytes_out);
 
     /* ---- input(): Response then body */
@@ -591,6 +621,50 @@ int po_loopback_run(const ptype_req* reqs, size_t n, ptype_reply* replies, int k
     free(out.p);
     free(srv);
     free(conns);
+    return rc;
+}
+
+/* The bytes ONE fresh connection carries for the calls reqs[0..n), after the HTTP CONNECT
+ * handshake: what the client writes (c2s) and what the server answers (s2c), produced by the very
+ * encoders po_loopback_run sends over TCP.  Either buffer may be NULL.  off[j] (j = 0..n) is
+ * where call j's first byte lies (type definitions sent with a call count as part of it).
+ * Method strings are chosen from the records like po_loopback_run does.  Returns 0, or -1 when a
+ * buffer is too small (sizes needed are still reported through off[n]). */
+int po_wire_streams(const ptype_req* reqs, size_t n, uint32_t receivers, uint64_t check_limit, uint8_t* c2s,
+                    size_t c2s_cap, uint64_t* c2s_off, uint8_t* s2c, size_t s2c_cap, uint64_t* s2c_off) {
+    lb_client_wire cw;
+    lb_server_wire sw = {0, 0};
+    lb_server srv;
+    memset(&cw, 0, sizeof cw);
+    memset(&srv, 0, sizeof srv);
+    srv.receivers = receivers;
+    srv.check_limit = check_limit;
+    wbuf a = {0}, b = {0};
+    for (size_t j = 0; j < n; j++) {
+        int nargs;
+        const char* sm = method_string(reqs[j].method, &nargs);
+        if (!sm) sm = reqs[j].recv == PTYPE_RECV_ILL_FORMED ? "nodot" : "Unknown.Method";
+        const int64_t args[3] = {reqs[j].a0, reqs[j].a1, nargs == 3 ? reqs[j].a2 : 0};
+        if (c2s_off) c2s_off[j] = a.n;
+        if (s2c_off) s2c_off[j] = b.n;
+        const uint64_t seq = cw.rpc_seq;
+        client_encode_call(&cw, sm, args, nargs, &a);
+        char errbuf[320];
+        int64_t reply = 0;
+        const char* err = server_execute(&srv, sm, args, &reply, errbuf, sizeof errbuf);
+        server_encode_response(&sw, sm, seq, err, reply, &b);
+    }
+    if (c2s_off) c2s_off[n] = a.n;
+    if (s2c_off) s2c_off[n] = b.n;
+    int rc = 0;
+    if (c2s) {
+        if (a.n <= c2s_cap) memcpy(c2s, a.p, a.n); else rc = -1;
+    }
+    if (s2c) {
+        if (b.n <= s2c_cap) memcpy(s2c, b.p, b.n); else rc = -1;
+    }
+    free(a.p);
+    free(b.p);
     return rc;
 }
 

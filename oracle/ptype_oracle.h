@@ -145,6 +145,8 @@ typedef struct po_loopback_stats {
  * registered `receivers` (bit0 Calculator, bit1 Prime).  replies[j].node = connection index. */
 int po_loopback_run(const ptype_req* reqs, size_t n, ptype_reply* replies, int k, uint32_t receivers,
                     uint64_t check_limit, po_loopback_stats* stats);
+int po_wire_streams(const ptype_req* reqs, size_t n, uint32_t receivers, uint64_t check_limit, uint8_t* c2s,
+                    size_t c2s_cap, uint64_t* c2s_off, uint8_t* s2c, size_t s2c_cap, uint64_t* s2c_off);
 int po_gob_reply_int_message(int64_t v, uint8_t* out);
 int po_gob_args_body(const int64_t* a, int nargs, uint8_t* out);
 int po_gob_request_typedef(uint8_t* out);

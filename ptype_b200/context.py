@@ -303,6 +303,74 @@ class Context:
             b.free()
         return args, st
 
+    # ---- net/rpc byte streams (device buffers inside; host arrays in and out) ----
+    WIRE_STREAM_DTYPE = np.dtype([("svc_key", "<u8"), ("seq0", "<u8"), ("seq_step", "<u8")])
+    WIRE_CALL_DTYPE = np.dtype([("rpc_seq", "<u8"), ("sm_off", "<u8"), ("sm_len", "<u4"), ("flags", "<u4")])
+
+    def wire_decode(self, data: np.ndarray, stream_off: np.ndarray, streams: np.ndarray, *, dev: int = 0,
+                    repeat: int = 1):
+        """Client-to-server net/rpc bytes of many connections -> (reqs, calls, call_off, seconds per pass)."""
+        import time
+        n_streams = len(stream_off) - 1
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        d_bytes = self.device_buffer(max(len(data), 1), dev).upload(data)
+        d_soff = self.device_buffer((n_streams + 1) * 8, dev).upload(np.ascontiguousarray(stream_off, dtype=np.uint64))
+        d_streams = self.device_buffer(max(n_streams, 1) * 24, dev).upload(
+            np.ascontiguousarray(streams, dtype=self.WIRE_STREAM_DTYPE))
+        d_coff = self.device_buffer((n_streams + 1) * 8, dev)
+        total = C.c_uint64()
+        rc = lib.ptype_b200_wire_decode(self._h, dev, d_bytes.ptr, d_soff.ptr, n_streams, d_streams.ptr, d_coff.ptr,
+                                        None, None, 0, C.byref(total))
+        if rc not in (_abi.E_OK, _abi.E_LIMIT):
+            check(rc, "wire_decode")
+        n = total.value
+        d_reqs = self.device_buffer(max(n, 1) * 48, dev)
+        d_calls = self.device_buffer(max(n, 1) * 24, dev)
+        t0 = time.perf_counter()
+        for _ in range(repeat):
+            check(lib.ptype_b200_wire_decode(self._h, dev, d_bytes.ptr, d_soff.ptr, n_streams, d_streams.ptr,
+                                             d_coff.ptr, d_reqs.ptr, d_calls.ptr, n, C.byref(total)), "wire_decode")
+        seconds = (time.perf_counter() - t0) / repeat
+        out = (d_reqs.download(REQ_DTYPE, n), d_calls.download(self.WIRE_CALL_DTYPE, n),
+               d_coff.download(np.uint64, n_streams + 1), seconds)
+        for b in (d_bytes, d_soff, d_streams, d_coff, d_reqs, d_calls):
+            b.free()
+        return out
+
+    def wire_encode(self, request_bytes: np.ndarray, call_off: np.ndarray, calls: np.ndarray, replies: np.ndarray,
+                    state: np.ndarray, *, response_id: int = 66, empty_id: int = 69, dev: int = 0, repeat: int = 1):
+        """Reply records -> server-to-client net/rpc bytes: (bytes, out_off, new state, seconds per pass)."""
+        import time
+        n_streams = len(call_off) - 1
+        n = len(calls)
+        d_bytes = self.device_buffer(max(len(request_bytes), 1), dev).upload(
+            np.ascontiguousarray(request_bytes, dtype=np.uint8))
+        d_coff = self.device_buffer((n_streams + 1) * 8, dev).upload(np.ascontiguousarray(call_off, dtype=np.uint64))
+        d_calls = self.device_buffer(max(n, 1) * 24, dev).upload(np.ascontiguousarray(calls, dtype=self.WIRE_CALL_DTYPE))
+        d_rep = self.device_buffer(max(n, 1) * 16, dev).upload(np.ascontiguousarray(replies, dtype=REPLY_DTYPE))
+        state0 = np.ascontiguousarray(state, dtype=np.uint8)
+        d_state = self.device_buffer(max(n_streams, 1), dev).upload(state0)
+        d_ooff = self.device_buffer((n_streams + 1) * 8, dev)
+        total = C.c_uint64()
+        rc = lib.ptype_b200_wire_encode(self._h, dev, d_bytes.ptr, d_coff.ptr, n_streams, d_calls.ptr, d_rep.ptr,
+                                        response_id, empty_id, d_state.ptr, d_ooff.ptr, None, 0, C.byref(total))
+        if rc not in (_abi.E_OK, _abi.E_LIMIT):
+            check(rc, "wire_encode")
+        d_out = self.device_buffer(max(total.value, 1), dev)
+        seconds = 0.0
+        for _ in range(repeat):
+            d_state.upload(state0)
+            t0 = time.perf_counter()
+            check(lib.ptype_b200_wire_encode(self._h, dev, d_bytes.ptr, d_coff.ptr, n_streams, d_calls.ptr, d_rep.ptr,
+                                             response_id, empty_id, d_state.ptr, d_ooff.ptr, d_out.ptr, total.value,
+                                             C.byref(total)), "wire_encode")
+            seconds += (time.perf_counter() - t0) / repeat
+        out = (d_out.download(np.uint8, total.value), d_ooff.download(np.uint64, n_streams + 1),
+               d_state.download(np.uint8, n_streams), seconds)
+        for b in (d_bytes, d_coff, d_calls, d_rep, d_state, d_ooff, d_out):
+            b.free()
+        return out
+
     def sync(self, dev: int = 0) -> None:
         check(lib.ptype_b200_sync(self._h, dev), "sync")
 

@@ -162,6 +162,8 @@ struct DeviceState {
                                             // the kernel leaves both at zero
     unsigned long long* h_tally = nullptr;  // page-locked word the kernel's last CTA writes the count to
     unsigned long long* h_tally_dev = nullptr;
+    uint8_t* d_wire_defs = nullptr;        // gob type definitions of rpc.Response and struct{} (wire_encode)
+    uint32_t wire_ids[2] = {0, 0}, wire_def_len[2] = {0, 0};
     void* d_codec = nullptr;               // scratch of the gob encoder (lengths, block sums)
     size_t codec_cap = 0;
     // retired[b][i]: recorded on dispatch stream i at the moment image buffer b stopped being the
@@ -431,6 +433,7 @@ void ptype_b200_close(ptype_ctx* ctx) {
         if (d->d_cksum_out) cudaFree(d->d_cksum_out);
         if (d->d_size) cudaFree(d->d_size);
         if (d->d_codec) cudaFree(d->d_codec);
+        if (d->d_wire_defs) cudaFree(d->d_wire_defs);
         if (d->d_failed2) cudaFree(d->d_failed2);
         if (d->d_tally) cudaFree(d->d_tally);
         for (int b = 0; b < 2; ++b)
@@ -1225,6 +1228,74 @@ int ptype_b200_gob_decode_args(ptype_ctx* ctx, int dev, const uint8_t* bytes, co
     d->after_dispatch = false;
     CU(ptype::launch_gob_decode_args(bytes, reinterpret_cast<const unsigned long long*>(offsets), n, args,
                                      args_per_call, status, d->stream));
+    ctx->launches.fetch_add(1);
+    CU(cudaStreamSynchronize(d->stream));
+    return PTYPE_OK;
+}
+
+int ptype_b200_wire_decode(ptype_ctx* ctx, int dev, const uint8_t* bytes, const uint64_t* stream_off, size_t n_streams,
+                           const ptype_wire_stream* streams, uint64_t* call_off, ptype_req* reqs,
+                           ptype_wire_call* calls, size_t cap, uint64_t* total_calls) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || !call_off || !total_calls || (n_streams && (!bytes || !stream_off || !streams))) return PTYPE_E_INVAL;
+    if (misaligned(reqs, 16) || misaligned(calls, 8) || misaligned(streams, 8)) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(d->device));
+    d->after_dispatch = false;
+    unsigned long long* off = reinterpret_cast<unsigned long long*>(call_off);
+    CU(ptype::launch_wire_count(bytes, reinterpret_cast<const unsigned long long*>(stream_off), n_streams, off,
+                                d->stream));
+    ctx->launches.fetch_add(2);
+    unsigned long long total = 0;
+    CU(cudaMemcpyAsync(&total, off + n_streams, sizeof total, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    *total_calls = total;
+    if (total > cap || (total && (!reqs || !calls))) return PTYPE_E_LIMIT;
+    CU(ptype::launch_wire_decode(bytes, reinterpret_cast<const unsigned long long*>(stream_off), n_streams, streams,
+                                 off, reqs, calls, d->stream));
+    ctx->launches.fetch_add(1);
+    CU(cudaStreamSynchronize(d->stream));
+    return PTYPE_OK;
+}
+
+int ptype_b200_wire_encode(ptype_ctx* ctx, int dev, const uint8_t* request_bytes, const uint64_t* call_off,
+                           size_t n_streams, const ptype_wire_call* calls, const ptype_reply* replies,
+                           uint32_t response_id, uint32_t empty_id, uint8_t* state, uint64_t* out_off, uint8_t* out,
+                           size_t out_cap, uint64_t* total_bytes) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || !out_off || !total_bytes || (n_streams && (!call_off || !state))) return PTYPE_E_INVAL;
+    if (response_id == 0 || empty_id == 0 || response_id > 0x3FFFFFFFu || empty_id > 0x3FFFFFFFu) return PTYPE_E_INVAL;
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(d->device));
+    // the two type definitions for these ids, kept on the device (rebuilt when the ids change)
+    if (d->wire_ids[0] != response_id || d->wire_ids[1] != empty_id || !d->d_wire_defs) {
+        std::string a, b;
+        ptype::wire_server_typedefs(response_id, empty_id, &a, &b);
+        const std::string both = a + b;
+        CU(cudaStreamSynchronize(d->stream));
+        if (!d->d_wire_defs) CU(cudaMalloc(&d->d_wire_defs, 512));
+        if (both.size() > 512) return PTYPE_E_LIMIT;
+        CU(cudaMemcpy(d->d_wire_defs, both.data(), both.size(), cudaMemcpyHostToDevice));
+        d->wire_ids[0] = response_id;
+        d->wire_ids[1] = empty_id;
+        d->wire_def_len[0] = static_cast<uint32_t>(a.size());
+        d->wire_def_len[1] = static_cast<uint32_t>(b.size());
+    }
+    d->after_dispatch = false;
+    unsigned long long* off = reinterpret_cast<unsigned long long*>(out_off);
+    const unsigned long long* coff = reinterpret_cast<const unsigned long long*>(call_off);
+    CU(ptype::launch_wire_encode(true, request_bytes, coff, n_streams, calls, replies, d->d_wire_defs,
+                                 d->wire_def_len[0], d->wire_def_len[1], response_id, empty_id, state, off, out,
+                                 d->stream));
+    ctx->launches.fetch_add(2);
+    unsigned long long total = 0;
+    CU(cudaMemcpyAsync(&total, off + n_streams, sizeof total, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    *total_bytes = total;
+    if (total > out_cap || (total && !out)) return PTYPE_E_LIMIT;
+    CU(ptype::launch_wire_encode(false, request_bytes, coff, n_streams, calls, replies, d->d_wire_defs,
+                                 d->wire_def_len[0], d->wire_def_len[1], response_id, empty_id, state, off, out,
+                                 d->stream));
     ctx->launches.fetch_add(1);
     CU(cudaStreamSynchronize(d->stream));
     return PTYPE_OK;

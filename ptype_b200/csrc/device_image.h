@@ -83,6 +83,18 @@ cudaError_t launch_gob_encode_replies(const ptype_reply* replies, size_t n, unsi
 cudaError_t launch_gob_decode_args(const uint8_t* bytes, const unsigned long long* offsets, size_t n,
                                    int64_t* args, int args_per_call, uint8_t* status, cudaStream_t stream);
 
+// wire.cu: net/rpc byte streams.  call_off / out_off have n_streams + 1 entries.
+cudaError_t launch_wire_count(const uint8_t* bytes, const unsigned long long* stream_off, size_t n_streams,
+                              unsigned long long* call_off, cudaStream_t stream);
+cudaError_t launch_wire_decode(const uint8_t* bytes, const unsigned long long* stream_off, size_t n_streams,
+                               const ptype_wire_stream* streams, unsigned long long* call_off, ptype_req* reqs,
+                               ptype_wire_call* calls, cudaStream_t stream);
+cudaError_t launch_wire_encode(bool size_only, const uint8_t* req_bytes, const unsigned long long* call_off,
+                               size_t n_streams, const ptype_wire_call* calls, const ptype_reply* replies,
+                               const uint8_t* defs, uint32_t response_def_len, uint32_t empty_def_len,
+                               uint32_t response_id, uint32_t empty_id, uint8_t* state, unsigned long long* out_off,
+                               uint8_t* out, cudaStream_t stream);
+
 cudaError_t launch_patch_service(ptype_slot* slots, const uint32_t* order, uint32_t n_slots, uint32_t seed,
                                  uint64_t key, int delta, uint32_t* result, cudaStream_t stream);
 
@@ -101,6 +113,12 @@ cudaError_t launch_assign_seq(const DeviceImage& img, const RankPlan& plan, ptyp
                               cudaStream_t stream);
 cudaError_t launch_carry_counters(const DeviceImage& from, const unsigned long long* from_counters,
                                   const DeviceImage& to, unsigned long long* to_counters, cudaStream_t stream);
+
+}  // namespace ptype
+#include <string>
+namespace ptype {
+// The gob type-definition messages of rpc.Response and of the empty struct for the given type ids.
+void wire_server_typedefs(uint32_t response_id, uint32_t empty_id, std::string* response_def, std::string* empty_def);
 
 // Records the text ptype_b200_last_error() returns on the calling thread.
 void set_last_error(const char* text);
