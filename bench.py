@@ -538,6 +538,46 @@ def measure(ctx, env, workload: str, *, steps: int, warmup: int, nbuf: int, batc
     return out
 
 
+def measure_wire(ctx, env, n_streams: int = 4096, calls_per_stream: int = 256, repeat: int = 20) -> dict:
+    """SURVEY.md 8f N1 on the device: the net/rpc request streams of `n_streams` connections decoded into
+    records, dispatched, and the replies encoded as Response streams.  Inputs come from the loopback
+    restatement's own encoders (oracle/loopback.c), and the encoded answer must equal its server bytes."""
+    import workloads as wl
+    from oracle import binding as ob
+    p = env.p
+    spec = wl.calculator_registry()
+    ctx.publish(spec.image())
+    c2s, s2c, c_off, s_off, call_off, per = [], [], [0], [0], [0], []
+    for s in range(n_streams):
+        reqs = wl.calculator_calls(calls_per_stream, seed=0x5EED0600 + s)
+        a, _, b, _ = ob.wire_streams(reqs, receivers=1)
+        c2s.append(a)
+        s2c.append(b)
+        c_off.append(c_off[-1] + len(a))
+        s_off.append(s_off[-1] + len(b))
+        call_off.append(call_off[-1] + len(reqs))
+    c2s, s2c = np.concatenate(c2s), np.concatenate(s2c)
+    streams = np.zeros(n_streams, dtype=ctx.WIRE_STREAM_DTYPE)
+    streams["svc_key"], streams["seq0"], streams["seq_step"] = p.service_key("calculator"), 1, 1
+    reqs, calls, got_off, dec_s = ctx.wire_decode(c2s, np.array(c_off, dtype=np.uint64), streams, repeat=repeat)
+    replies = ctx.dispatch(reqs)
+    out, out_off, _, enc_s = ctx.wire_encode(c2s, got_off, calls, replies, np.zeros(n_streams, dtype=np.uint8),
+                                             repeat=repeat)
+    ok = bool(np.array_equal(got_off, np.array(call_off, dtype=np.uint64)) and out.tobytes() == s2c.tobytes())
+    n = len(reqs)
+    peak, _ = measured_peak()
+    dec_bytes = len(c2s) * 2 + n * (48 + 24)            # the stream is walked twice (count, decode)
+    enc_bytes = 2 * n * (24 + 16) + len(out) + int(calls["sm_len"].sum())   # sizes pass + write pass
+    return {"streams": n_streams, "calls": n, "request_bytes": int(len(c2s)), "response_bytes": int(len(out)),
+            "decode_us": dec_s * 1e6, "encode_us": enc_s * 1e6,
+            "decode_calls_per_s": n / dec_s, "encode_calls_per_s": n / enc_s,
+            "decode_gbs": dec_bytes / dec_s / 1e9, "encode_gbs": enc_bytes / enc_s / 1e9,
+            "decode_frac_of_hbm_peak": dec_bytes / dec_s / 1e9 / peak,
+            "encode_frac_of_hbm_peak": enc_bytes / enc_s / 1e9 / peak,
+            "timing": f"wall clock around the C-ABI call (it waits for the GPU), mean of {repeat}",
+            "bytes_equal_loopback_streams": ok, "parity_ok": ok}
+
+
 def extra_summary(m: dict) -> dict:
     """A sub-run as it appears under `extras` in the JSON line."""
     s = {"workload": WORKLOAD_TEXT[m["workload"]], "value": m["value"], "unit": "calls/s", "steps": m["steps"],
@@ -765,15 +805,20 @@ def main():
             windows.append(x["window"])
             extras[name] = x
 
+    wire = None
+    if args.workload == "c2" and not args.no_extras and not args.flags and not multi:
+        wire = measure_wire(ctx, env)
+
     sampler.stop()
     sampler.join(timeout=1.0)
     clocks = sampler.summary(windows)
 
-    parity_ok = m["parity_ok"] and e2e["parity_ok"] and all(x["parity_ok"] for x in extras.values())
+    parity_ok = m["parity_ok"] and e2e["parity_ok"] and all(x["parity_ok"] for x in extras.values()) and \
+        (wire is None or wire["parity_ok"])
     if not parity_ok:
         if rank == 0:
             bad = {"primary": m["parity"], "e2e_ok": e2e["parity_ok"],
-                   "extras": {k: x["parity"] for k, x in extras.items()}}
+                   "extras": {k: x["parity"] for k, x in extras.items()}, "wire": wire and wire["parity_ok"]}
             print(json.dumps({"error": "CUDA replies differ from the oracle - number withheld", "parity": bad}),
                   file=sys.stderr, flush=True)
         ctx.close()
@@ -842,6 +887,7 @@ def main():
             "per_launch": m["lone"],
             "host_enqueue_us_per_step": m["host_enqueue_s"] / args.steps * 1e6,
             "extras": {k: extra_summary(x) for k, x in extras.items()},
+            "wire_codec": wire,
             "clocks": clocks,
         }
         if "live_updates" in m:
