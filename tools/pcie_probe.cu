@@ -12,6 +12,8 @@
 #include <stdint.h>
 
 #include <algorithm>
+#include <chrono>
+#include <string>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -234,7 +236,64 @@ static void report(const char* what, double bytes, double ms) {
     std::fflush(stdout);
 }
 
+// `pcie_probe concurrent <device> <seconds> [wc]`: the box ceiling when several GPUs stream host memory
+// at once.  Start one process per GPU at the same moment; each keeps ONE shape running for `seconds`
+// and prints its sustained rate: the product's mix (16 B in / 8 B out per unit, kernel loads and
+// stores on mapped pinned memory, one CTA per SM), then the two copy engines at once, then the
+// hybrid (copy engine in, kernel stores out).  `wc` allocates the input write-combined.
+static int run_concurrent(int argc, char** argv) {
+    const int device = argc > 2 ? std::atoi(argv[2]) : 0;
+    const double seconds = argc > 3 ? std::atof(argv[3]) : 2.0;
+    const bool wc = argc > 4 && std::string(argv[4]) == "wc";
+    const size_t n = 1u << 20, in_bytes = n * 16, out_bytes = n * 8;
+    CK(cudaSetDevice(device));
+    CK(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
+    cudaStream_t s2;
+    CK(cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking));
+    unsigned char *h_in, *h_out, *d_in, *d_out;
+    CK(cudaHostAlloc(reinterpret_cast<void**>(&h_in), in_bytes,
+                     cudaHostAllocMapped | cudaHostAllocPortable | (wc ? cudaHostAllocWriteCombined : 0)));
+    CK(cudaHostAlloc(reinterpret_cast<void**>(&h_out), in_bytes, cudaHostAllocMapped | cudaHostAllocPortable));
+    CK(cudaMalloc(reinterpret_cast<void**>(&d_in), in_bytes));
+    CK(cudaMalloc(reinterpret_cast<void**>(&d_out), in_bytes));
+    for (size_t i = 0; i < in_bytes; i += 8) *reinterpret_cast<unsigned long long*>(h_in + i) = i * 0x9E3779B97F4A7C15ull;
+    cudaEvent_t fork, join;
+    CK(cudaEventCreateWithFlags(&fork, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&join, cudaEventDisableTiming));
+    auto sustained = [&](const char* what, auto&& one) {
+        const auto t0 = std::chrono::steady_clock::now();
+        size_t reps = 0;
+        double el = 0;
+        do {
+            for (int k = 0; k < 8; ++k) one();
+            CK(cudaStreamSynchronize(g_stream));
+            reps += 8;
+            el = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        } while (el < seconds);
+        std::printf("gpu %d%s %-58s %8.1f us/batch %7.2f GB/s %6.2f G units/s\n", device, wc ? " wc" : "", what,
+                    el / reps * 1e6, (in_bytes + out_bytes) * reps / el * 1e-9, n * reps / el * 1e-9);
+        std::fflush(stdout);
+    };
+    sustained("mix: kernel ld.128 in + st.64 out on host memory, 148 CTAs", [&] {
+        mix_ld<2><<<148, 256, 0, g_stream>>>(reinterpret_cast<const uint4*>(h_in), reinterpret_cast<unsigned long long*>(h_out), n);
+    });
+    sustained("copy engines: H2D in + D2H out at once", [&] {
+        CK(cudaEventRecord(fork, g_stream));
+        CK(cudaStreamWaitEvent(s2, fork, 0));
+        CK(cudaMemcpyAsync(d_in, h_in, in_bytes, cudaMemcpyHostToDevice, g_stream));
+        CK(cudaMemcpyAsync(h_out, d_out, out_bytes, cudaMemcpyDeviceToHost, s2));
+        CK(cudaEventRecord(join, s2));
+        CK(cudaStreamWaitEvent(g_stream, join, 0));
+    });
+    sustained("hybrid: copy engine H2D, kernel HBM in / st.64 host out", [&] {
+        CK(cudaMemcpyAsync(d_in, h_in, in_bytes, cudaMemcpyHostToDevice, g_stream));
+        mix_ld<2><<<148 * 4, 256, 0, g_stream>>>(reinterpret_cast<const uint4*>(d_in), reinterpret_cast<unsigned long long*>(h_out), n);
+    });
+    return 0;
+}
+
 int main(int argc, char** argv) {
+    if (argc > 1 && std::string(argv[1]) == "concurrent") return run_concurrent(argc, argv);
     const size_t n = argc > 1 ? std::strtoull(argv[1], nullptr, 0) : (1u << 20);  // units (calls)
     const size_t in_bytes = n * 16, out_bytes = n * 8;
     CK(cudaSetDevice(0));
