@@ -684,6 +684,68 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     griddep_wait();
 }
 
+// Software-pipelined form of dispatch_multi_kernel: a warp holds ONE tile at a time and has the
+// loads of its next tile in flight while it works on the current one.  With the 32 warps of a
+// 1024-thread CTA (the shape a >100 KiB staged table forces: one CTA per SM, 64 registers per
+// thread) the unrolled kernel above spent 29 % of its warp-time at the first use of a loaded
+// register (profiles/r02_c3_multi_source.csv): a warp's loads were in flight only while it waited
+// for them.  Here they are in flight during the ~260 instructions of the previous tile as well,
+// for the same 24 registers of load targets.
+template <bool kSmemTable, int kThreads, int kMinCtas>
+__global__ void __launch_bounds__(kThreads, kMinCtas)
+    dispatch_multi_prefetch_kernel(const DeviceImage img, const __grid_constant__ BatchList list) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ __align__(16) CtaShared sh;
+
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+    const uint32_t total_tiles = list.tile_end[list.count - 1];
+    const uint32_t total_warps = gridDim.x * warps_per_cta;
+    const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
+
+    int cursor = 0;  // batch of the tile being fetched; a warp's tiles only move forward
+    // where a tile lies: its batch and its index inside the batch; issues its three loads
+    auto fetch = [&](uint32_t g, int& b, uint32_t& tile, uint4 (&ld)[3]) {
+        b = cursor;
+        while (g >= list.tile_end[b]) ++b;
+        cursor = b;
+        tile = g - (b ? list.tile_end[b - 1] : 0u);
+        const size_t n_chunks = static_cast<size_t>(list.n[b]) * 3;
+        const uint4* reqs = list.reqs[b];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            const size_t c = static_cast<size_t>(tile) * 96 + j * 32 + lane;
+            ld[j] = c < n_chunks ? ld_stream(reqs + c) : make_uint4(0, 0, 0, 0);
+        }
+    };
+
+    uint4 nxt[3];
+    int nxt_b = 0;
+    uint32_t nxt_tile = 0;
+    uint32_t g = warp_global;
+    if (g < total_tiles) fetch(g, nxt_b, nxt_tile, nxt);  // before the tables: the longest latency first
+
+    const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
+    griddep_launch_dependents();
+    const TransposePlan plan = transpose_plan(lane);
+    LookupCache cache;
+    if (kSmemTable) mbar_wait(&sh.table_bar, 0);
+
+    while (g < total_tiles) {
+        uint4 cur[3] = {nxt[0], nxt[1], nxt[2]};
+        const int b = nxt_b;
+        const uint32_t tile = nxt_tile;
+        g += total_warps;
+        if (g < total_tiles) fetch(g, nxt_b, nxt_tile, nxt);
+        uint4 q[3];
+        transpose_tile(plan, lane, cur, q);
+        const size_t idx = (static_cast<size_t>(tile) << 5) + lane;
+        if (idx < list.n[b])
+            st_stream(list.replies[b] + idx, dispatch_one<kSmemTable>(img, sh, slots, cache, q[0], q[1], q[2]));
+    }
+    griddep_wait();
+}
+
 // Bulk-staged twin of dispatch_multi_kernel: per-warp TMA ring over the tile stream of many
 // batches.  Fewer registers (more resident warps) than the LDG kernel, which pays off when the
 // method bodies are ALU-heavy (Prime.Check).
@@ -1126,12 +1188,32 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         return launch_kernel(dispatch_bulk_multi_kernel<false, kStagesDefault>, blocks, plan.threads,
                              plan.dyn_smem, stream, pdl, img, list, table_smem);
     }
+    // PTYPE_B200_PREFETCH: 0 = the unrolled kernels everywhere, 1 (default) = the software-pipelined
+    // kernel for the 1024-thread shape, 2 = for the 256-thread shape too (measurement switch)
+    static const int prefetch = [] {
+        const char* e = std::getenv("PTYPE_B200_PREFETCH");
+        return e ? std::atoi(e) : 1;
+    }();
     if (plan.threads == kMaxThreads) {
+        if (prefetch >= 1) {
+            if (plan.smem_table)
+                return launch_kernel(dispatch_multi_prefetch_kernel<true, kMaxThreads, 1>, blocks, plan.threads,
+                                     plan.dyn_smem, stream, pdl, img, list);
+            return launch_kernel(dispatch_multi_prefetch_kernel<false, kMaxThreads, 1>, blocks, plan.threads,
+                                 plan.dyn_smem, stream, pdl, img, list);
+        }
         if (plan.smem_table)
             return launch_kernel(dispatch_multi_kernel<true, 2, kMaxThreads, 1>, blocks, plan.threads,
                                  plan.dyn_smem, stream, pdl, img, list);
         return launch_kernel(dispatch_multi_kernel<false, 2, kMaxThreads, 1>, blocks, plan.threads,
                              plan.dyn_smem, stream, pdl, img, list);
+    }
+    if (prefetch >= 2) {
+        if (plan.smem_table)
+            return launch_kernel(dispatch_multi_prefetch_kernel<true, kSmallThreads, kSmallMinCtas>, blocks,
+                                 plan.threads, plan.dyn_smem, stream, pdl, img, list);
+        return launch_kernel(dispatch_multi_prefetch_kernel<false, kSmallThreads, kSmallMinCtas>, blocks,
+                             plan.threads, plan.dyn_smem, stream, pdl, img, list);
     }
     if (plan.smem_table)
         return launch_kernel(dispatch_multi_kernel<true, kSmallUnroll, kSmallThreads, kSmallMinCtas>, blocks,
