@@ -1188,12 +1188,18 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         return launch_kernel(dispatch_bulk_multi_kernel<false, kStagesDefault>, blocks, plan.threads,
                              plan.dyn_smem, stream, pdl, img, list, table_smem);
     }
-    // PTYPE_B200_PREFETCH: 0 = the unrolled kernels everywhere, 1 (default) = the software-pipelined
-    // kernel for the 1024-thread shape, 2 = for the 256-thread shape too (measurement switch)
-    static const int prefetch = [] {
+    // Which loop: the software-pipelined kernel wins wherever a tile costs more instructions than a
+    // load takes to arrive - the 1024-thread shape (C3: 191 -> 185 us per 2^24 calls) and the
+    // 256-thread shape when nodes are picked through the connection hashes (C2: 10.9 -> 10.5 us per
+    // batch in a lone launch of 20, 9.31 -> 9.23 pipelined); with the identity selection of a mesh
+    // the tile is cheap and the unrolled kernel's two tiles in flight per warp do better (8.70 vs
+    // 9.15 us).  PTYPE_B200_PREFETCH overrides: 0 = never, 1 = the 1024-thread shape only,
+    // 2 = always (measurement switch).
+    static const int forced = [] {
         const char* e = std::getenv("PTYPE_B200_PREFETCH");
-        return e ? std::atoi(e) : 1;
+        return e ? std::atoi(e) : -1;
     }();
+    const int prefetch = forced >= 0 ? forced : (img.max_conn != 0 ? 2 : 1);
     if (plan.threads == kMaxThreads) {
         if (prefetch >= 1) {
             if (plan.smem_table)
