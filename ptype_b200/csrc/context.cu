@@ -351,6 +351,14 @@ void* pinned_alias(const void* host) {
     return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
 }
 
+bool single_via_multi() {  // PTYPE_B200_SINGLE_VIA_MULTI=0: single batches keep dispatch_kernel (measurement switch)
+    static const bool on = [] {
+        const char* v = std::getenv("PTYPE_B200_SINGLE_VIA_MULTI");
+        return !(v && v[0] == '0');
+    }();
+    return on;
+}
+
 bool zero_copy_enabled() {
     static const bool on = [] {
         const char* v = std::getenv("PTYPE_B200_ZERO_COPY");
@@ -819,9 +827,15 @@ int ptype_b200_dispatch_ex(ptype_ctx* ctx, int dev, const ptype_req* reqs, size_
             d->after_dispatch = false;
         }
         if (n) {
-            CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, n, d->dispatch_sms), reqs, n,
-                                      replies, failed_idx, static_cast<uint32_t>(failed_cap), 0u,
-                                      d_stats, d->stream, take_pdl(d, flags)));
+            if (!extras && !plan.bulk && single_via_multi()) {
+                // one batch is a batch list of one: the same (software-pipelined) loop as dispatch_batches
+                const ptype_batch one = {reqs, replies, n};
+                CU(ptype::launch_dispatch_multi(img, plan, d->dispatch_sms, &one, 1, d->stream, take_pdl(d, flags)));
+            } else {
+                CU(ptype::launch_dispatch(img, plan, ptype::grid_for(plan, n, d->dispatch_sms), reqs, n,
+                                          replies, failed_idx, static_cast<uint32_t>(failed_cap), 0u,
+                                          d_stats, d->stream, take_pdl(d, flags)));
+            }
             ctx->launches.fetch_add(1);
         }
         if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
