@@ -156,6 +156,8 @@ struct DeviceState {
     bool seq_in_use = false;                // ptype_b200_assign_seq / seq_set has been called
     uint32_t* rank_rows = nullptr;          // (chunks x n_slots) histogram matrix of assign_seq
     size_t rank_rows_cap = 0;               // entries
+    uint32_t* rank_ids = nullptr;           // the slot each record of the batch is counted under
+    size_t rank_ids_cap = 0;                // entries
     unsigned long long* seq_start = nullptr;
     size_t seq_start_cap = 0;
     unsigned long long* d_tally = nullptr;  // {failed calls, finished CTAs} of a single-launch values batch;
@@ -447,6 +449,7 @@ void ptype_b200_close(ptype_ctx* ctx) {
         for (int b = 0; b < 2; ++b)
             if (d->seq_counters[b]) cudaFree(d->seq_counters[b]);
         if (d->rank_rows) cudaFree(d->rank_rows);
+        if (d->rank_ids) cudaFree(d->rank_ids);
         if (d->seq_start) cudaFree(d->seq_start);
         if (d->h_tally) cudaFreeHost(d->h_tally);
         for (int i = 0; i <= kPipe; ++i)
@@ -1357,6 +1360,14 @@ int ptype_b200_assign_seq(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, 
         CU(cudaMalloc(&d->rank_rows, cells * sizeof(uint32_t)));
         d->rank_rows_cap = cells;
     }
+    if (n > d->rank_ids_cap) {
+        CU(cudaStreamSynchronize(d->stream));
+        if (d->rank_ids) CU(cudaFree(d->rank_ids));
+        d->rank_ids = nullptr;
+        d->rank_ids_cap = 0;
+        CU(cudaMalloc(&d->rank_ids, n * sizeof(uint32_t)));
+        d->rank_ids_cap = n;
+    }
     if (img.n_slots > d->seq_start_cap) {
         CU(cudaStreamSynchronize(d->stream));
         if (d->seq_start) CU(cudaFree(d->seq_start));
@@ -1366,8 +1377,8 @@ int ptype_b200_assign_seq(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, 
         d->seq_start_cap = img.n_slots;
     }
     d->after_dispatch = false;
-    CU(ptype::launch_assign_seq(img, plan, d_reqs, n, d->rank_rows, d->seq_counters[d->active], d->seq_start,
-                                d->stream));
+    CU(ptype::launch_assign_seq(img, plan, d_reqs, n, d->rank_rows, d->rank_ids, d->seq_counters[d->active],
+                                d->seq_start, nullptr, d->stream));
     ctx->launches.fetch_add(3);
     if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
     return PTYPE_OK;

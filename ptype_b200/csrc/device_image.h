@@ -100,17 +100,20 @@ cudaError_t launch_patch_service(ptype_slot* slots, const uint32_t* order, uint3
 
 // rank.cu: balancer counters on the device.
 struct RankPlan {
-    bool staged = false;  // table keys staged in shared memory (else probed in L1/L2)
-    int threads = 0;
-    size_t smem = 0;
-    int n_chunks = 0;     // CTAs = contiguous chunks of the batch = rows of the histogram matrix
+    bool staged = false;  // count pass: table keys staged in shared memory (else probed in L1/L2)
+    int threads = 0;      // count pass: threads per CTA
+    size_t smem = 0;      // count pass: shared memory per CTA
+    int count_ctas = 0;   // count pass: CTAs, each taking `sub` consecutive chunks
+    int sub = 1;
+    int n_chunks = 0;     // contiguous chunks of the batch = rows of the histogram matrix = assign CTAs
     size_t chunk = 0;     // records per chunk
+    size_t assign_smem = 0;
 };
 bool rank_supported(uint32_t n_slots);
 cudaError_t rank_plan(uint32_t n_slots, size_t n, int sm_count, RankPlan* plan);
 cudaError_t launch_assign_seq(const DeviceImage& img, const RankPlan& plan, ptype_req* reqs, size_t n,
-                              uint32_t* rows, unsigned long long* counters, unsigned long long* seq_start,
-                              cudaStream_t stream);
+                              uint32_t* rows, uint32_t* ids, unsigned long long* counters,
+                              unsigned long long* seq_start, unsigned long long* seq_out, cudaStream_t stream);
 cudaError_t launch_carry_counters(const DeviceImage& from, const unsigned long long* from_counters,
                                   const DeviceImage& to, unsigned long long* to_counters, cudaStream_t stream);
 

@@ -7,26 +7,32 @@
 //     seq_j = counter[service_j] + 1 + #{ i < j : service_i == service_j, both counted }
 // and afterwards counter[s] has grown by the number of counted calls to s.  That is a stable
 // per-service rank; it is computed here without sorting:
-//   rank_count_kernel   each CTA owns a contiguous chunk of the batch and histograms it by table
-//                       slot in shared memory; the histogram goes to row `blockIdx.x` of a
-//                       (chunks x n_slots) matrix
+//   rank_count_kernel   the batch is cut into contiguous chunks; a CTA histograms a chunk by table
+//                       slot in shared memory, stores the histogram as row `chunk` of a
+//                       (chunks x n_slots) matrix, and leaves behind the slot id of every record
+//                       (4 bytes per record), so that nobody has to look a key up again
 //   rank_scan_kernel    exclusive scan down every column (eight warps per 32 columns), counter update
-//   rank_assign_kernel  each CTA reloads its row (= calls to each service in earlier chunks) and
-//                       walks its chunk in order, each warp holding 128 consecutive calls per
-//                       trip: __match_any_sync ranks the calls of one service inside a tile of
-//                       32, the warps of the CTA take turns on the running counts (one turn
-//                       settles a warp's four tiles), and the seq field of every record is written
+//   rank_assign_kernel  one 256-thread CTA per chunk reloads its row (= calls to each service in
+//                       earlier chunks) and walks the chunk's slot ids in order, each warp holding
+//                       256 consecutive calls per trip: __match_any_sync ranks the calls of one
+//                       service inside a tile of 32, the warps of the CTA take turns on the running
+//                       counts (one turn settles a warp's eight tiles; only the tile leaders touch
+//                       shared memory inside a turn), and the seq of every record is written
 // Counters are indexed by table slot; carry_counters_kernel moves them to the slots of the next
 // image when the registry flips (services are matched by key).
 //
-// Where they fit (tables up to ~18 500 slots) the table's keys are staged in shared memory beside
-// the histogram, 12 bytes per slot, one 1024-thread CTA per SM: three random 16-byte probes per
-// record against a table in L2 cost more than everything else together (measured on the
-// 12 800-slot registry: 497 + 693 us per 2^24 records for the two passes).  Larger tables, up to
-// 51 200 slots, are probed in L1/L2 by 256-thread CTAs.
+// The count pass stages the table's keys in shared memory where they fit (tables up to ~18 500
+// slots, 12 bytes per slot, one 1024-thread CTA per SM taking several chunks in turn): three random
+// 16-byte probes per record against a table in L2 cost more than everything else together
+// (measured on the 12 800-slot registry: 497 us per 2^24 records).  Larger tables, up to 51 200
+// slots, are probed in L1/L2 by 256-thread CTAs.  The assign pass needs 4 bytes of shared memory
+// per slot, so four of its CTAs share an SM on that registry and their turn chains interleave.
 //
-// HBM traffic: two passes over the keys (a 32-byte sector per 48-byte record each) and one 8-byte
-// store per record; the (chunks x n_slots) matrix stays in L2.
+// HBM traffic: the count pass reads the keys (an 8-byte key drags its 48-byte record along: DRAM
+// moves 64 bytes at a time) and writes 4 bytes per record; the assign pass reads those 4 bytes and
+// stores 8 bytes into every 48-byte record, which the memory system turns into a read and a write
+// of the 32-byte sector (tools/partial_write_probe.cu: 522 MB read + 518 MB written for 2^24
+// records, 184 us on its own) - that store, not the ranking, is the floor of this pass.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -169,42 +175,52 @@ __device__ __forceinline__ void counted_slots(const RankTable& t, const RankShar
     }
 }
 
+// One CTA histograms `sub` consecutive chunks (rows of the matrix), one after the other, and leaves
+// behind the slot every record is counted under (ids[j], kNoSlot for a record that consumes no
+// counter value): the assign pass then needs neither the keys nor the table.
 template <bool kStaged, int kThreads>
 __global__ void __launch_bounds__(kThreads)
     rank_count_kernel(const RankTable t, const ptype_req* __restrict__ reqs, const size_t n, const size_t chunk,
-                      uint32_t* __restrict__ rows) {
+                      const int sub, const int n_chunks, uint32_t* __restrict__ rows, uint32_t* __restrict__ ids) {
     extern __shared__ __align__(16) unsigned char rank_smem[];
     const RankShared<kStaged> sh = rank_shared<kStaged>(t, rank_smem);
-    for (uint32_t s = threadIdx.x; s < t.n_slots; s += kThreads) sh.counts[s] = 0;
-    __syncthreads();
-    const size_t lo = static_cast<size_t>(blockIdx.x) * chunk;
-    const size_t hi = lo + chunk < n ? lo + chunk : n;
     const uint32_t lane = threadIdx.x & 31u;
     constexpr size_t kTrip = static_cast<size_t>(kThreads) * kRankDepth;
-    unsigned long long key[kRankDepth], next[kRankDepth];
-    if (lo < hi) load_keys(reqs, lo, hi, next);
-    for (size_t base = lo; base < hi; base += kTrip) {
+    for (int k = 0; k < sub; ++k) {
+        const int c = static_cast<int>(blockIdx.x) * sub + k;
+        if (c >= n_chunks) break;
+        for (uint32_t s = threadIdx.x; s < t.n_slots; s += kThreads) sh.counts[s] = 0;
+        __syncthreads();
+        const size_t lo = static_cast<size_t>(c) * chunk;
+        const size_t hi = lo + chunk < n ? lo + chunk : n;
+        unsigned long long key[kRankDepth], next[kRankDepth];
+        if (lo < hi) load_keys(reqs, lo, hi, next);
+        for (size_t base = lo; base < hi; base += kTrip) {
 #pragma unroll
-        for (int r = 0; r < kRankDepth; ++r) key[r] = next[r];
-        if (base + kTrip < hi) load_keys(reqs, base + kTrip, hi, next);
-        uint32_t at[kRankDepth];
-        counted_slots<kStaged>(t, sh, key, base, hi, at);
+            for (int r = 0; r < kRankDepth; ++r) key[r] = next[r];
+            if (base + kTrip < hi) load_keys(reqs, base + kTrip, hi, next);
+            uint32_t at[kRankDepth];
+            counted_slots<kStaged>(t, sh, key, base, hi, at);
 #pragma unroll
-        for (int r = 0; r < kRankDepth; ++r) {
-            // A tile that names one service only (a single Client's batch) adds once; otherwise
-            // every counted record adds for itself - __match_any_sync would merge equal slots, but
-            // its latency was ~45 % of this kernel's stall samples on the 10 000-service stream.
-            const uint32_t lead = __shfl_sync(kFull, at[r], 0);
-            if (__all_sync(kFull, at[r] == lead)) {
-                if (lane == 0 && lead != kNoSlot) atomicAdd(&sh.counts[lead], 32u);
-            } else if (at[r] != kNoSlot) {
-                atomicAdd(&sh.counts[at[r]], 1u);
+            for (int r = 0; r < kRankDepth; ++r) {
+                const size_t j = record_index(base, r);
+                if (j < hi) ids[j] = at[r];
+                // A tile that names one service only (a single Client's batch) adds once; otherwise
+                // every counted record adds for itself - __match_any_sync would merge equal slots, but
+                // its latency was ~45 % of this kernel's stall samples on the 10 000-service stream.
+                const uint32_t lead = __shfl_sync(kFull, at[r], 0);
+                if (__all_sync(kFull, at[r] == lead)) {
+                    if (lane == 0 && lead != kNoSlot) atomicAdd(&sh.counts[lead], 32u);
+                } else if (at[r] != kNoSlot) {
+                    atomicAdd(&sh.counts[at[r]], 1u);
+                }
             }
         }
+        __syncthreads();
+        uint32_t* row = rows + static_cast<size_t>(c) * t.n_slots;
+        for (uint32_t s = threadIdx.x; s < t.n_slots; s += kThreads) row[s] = sh.counts[s];
+        __syncthreads();
     }
-    __syncthreads();
-    uint32_t* row = rows + static_cast<size_t>(blockIdx.x) * t.n_slots;
-    for (uint32_t s = threadIdx.x; s < t.n_slots; s += kThreads) row[s] = sh.counts[s];
 }
 
 // Column s of the matrix becomes its exclusive prefix sum; seq_start[s] keeps the counter value
@@ -270,48 +286,49 @@ __global__ void __launch_bounds__(kScanThreads)
     }
 }
 
-template <bool kStaged, int kThreads>
-__global__ void __launch_bounds__(kThreads)
-    rank_assign_kernel(const RankTable t, ptype_req* __restrict__ reqs, const size_t n, const size_t chunk,
+// One 256-thread CTA per chunk (row).  It loads the row (calls to each service in earlier chunks)
+// into shared memory and walks the chunk's slot ids in order: a warp holds kAssignDepth consecutive
+// tiles of 32 records per trip, __match_any_sync ranks the records of one service inside a tile,
+// and the warps take turns on the running counts - a turn settles all of a warp's tiles.  Only the
+// leader lane of each service in a tile touches shared memory inside the turn; everything else
+// (loading ids, matching, fetching the counter base, storing) happens outside it.  Several CTAs
+// share an SM (the counts are all the shared memory a CTA needs), so their turn chains interleave.
+// kScatter: write ptype_req.seq of the records; else a plain array seq_out[j].
+constexpr int kAssignThreads = 256;
+constexpr int kAssignDepth = 8;
+template <bool kScatter>
+__global__ void __launch_bounds__(kAssignThreads)
+    rank_assign_kernel(const uint32_t n_slots, const uint32_t* __restrict__ ids, ptype_req* __restrict__ reqs,
+                       unsigned long long* __restrict__ seq_out, const size_t n, const size_t chunk,
                        const uint32_t* __restrict__ rows, const unsigned long long* __restrict__ seq_start) {
     extern __shared__ __align__(16) unsigned char rank_smem[];
-    const RankShared<kStaged> sh = rank_shared<kStaged>(t, rank_smem);
-    uint32_t* run = sh.counts;  // counted calls to each service before the CTA's cursor
-    const uint32_t* row = rows + static_cast<size_t>(blockIdx.x) * t.n_slots;
-    for (uint32_t s = threadIdx.x; s < t.n_slots; s += kThreads) run[s] = row[s];
+    uint32_t* run = reinterpret_cast<uint32_t*>(rank_smem);  // counted calls to each service before the cursor
+    const uint32_t* row = rows + static_cast<size_t>(blockIdx.x) * n_slots;
+    for (uint32_t s = threadIdx.x; s < n_slots; s += kAssignThreads) run[s] = row[s];
     __syncthreads();
     const size_t lo = static_cast<size_t>(blockIdx.x) * chunk;
     const size_t hi = lo + chunk < n ? lo + chunk : n;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    constexpr size_t kTrip = static_cast<size_t>(kThreads) * kRankDepth;
+    constexpr size_t kTrip = static_cast<size_t>(kAssignThreads) * kAssignDepth;
     for (size_t base = lo; base < hi; base += kTrip) {  // uniform trip count per CTA
-        // Keys are NOT fetched a trip ahead here: this pass writes into the sector it read the
-        // key from, and the longer that sector waits in L2 the likelier it is gone by then
-        // (ncu: 1.2 GB read for 0.8 GB of records with the prefetch in place).
-        unsigned long long key[kRankDepth];
-        load_keys(reqs, base, hi, key);
-        uint32_t at[kRankDepth];
-        counted_slots<kStaged>(t, sh, key, base, hi, at);
-        unsigned long long start[kRankDepth];  // fetched now, needed after the warps' turns
+        const size_t mine = base + static_cast<size_t>(warp) * kAssignDepth * 32 + lane;
+        uint32_t at[kAssignDepth], peers[kAssignDepth], first[kAssignDepth];
 #pragma unroll
-        for (int r = 0; r < kRankDepth; ++r) start[r] = at[r] != kNoSlot ? __ldg(seq_start + at[r]) : 0ull;
-        // calls of one service inside a tile of 32: lanes in `peers`, in batch order
-        uint32_t peers[kRankDepth], before[kRankDepth], first[kRankDepth];
+        for (int r = 0; r < kAssignDepth; ++r) {
+            const size_t j = mine + static_cast<size_t>(r) * 32;
+            at[r] = j < hi ? __ldg(ids + j) : kNoSlot;
+        }
 #pragma unroll
-        for (int r = 0; r < kRankDepth; ++r) {
+        for (int r = 0; r < kAssignDepth; ++r) {
+            // calls of one service inside a tile of 32: lanes in `peers`, in batch order
             peers[r] = __match_any_sync(kFull, at[r] != kNoSlot ? at[r] : 0x80000000u + lane);
-            before[r] = __popc(peers[r] & ((1u << lane) - 1u));
             first[r] = 0;
         }
-        // The warps hold consecutive runs of the batch, so they update the running counts in
-        // warp order; inside its turn a warp settles its tiles in order.  (Passing a ticket from
-        // warp to warp through shared memory instead of CTA-wide barriers was measured too: the
-        // two fences it needs per turn cost what the barrier costs.)
-        for (uint32_t w = 0; w < kThreads / 32; ++w) {
+        for (uint32_t w = 0; w < kAssignThreads / 32; ++w) {
             if (w == warp) {
 #pragma unroll
-                for (int r = 0; r < kRankDepth; ++r) {
-                    if (at[r] != kNoSlot && before[r] == 0) {
+                for (int r = 0; r < kAssignDepth; ++r) {
+                    if (at[r] != kNoSlot && (peers[r] & ((1u << lane) - 1u)) == 0) {
                         first[r] = run[at[r]];
                         run[at[r]] = first[r] + __popc(peers[r]);
                     }
@@ -321,12 +338,17 @@ __global__ void __launch_bounds__(kThreads)
             __syncthreads();
         }
 #pragma unroll
-        for (int r = 0; r < kRankDepth; ++r) {
-            const size_t j = record_index(base, r);
+        for (int r = 0; r < kAssignDepth; ++r) {
+            const size_t j = mine + static_cast<size_t>(r) * 32;
             const uint32_t f = __shfl_sync(kFull, first[r], __ffs(peers[r]) - 1);
             if (j < hi) {
-                const unsigned long long seq = at[r] != kNoSlot ? start[r] + f + before[r] + 1ull : 0ull;
-                reinterpret_cast<unsigned long long*>(reqs + j)[1] = seq;  // ptype_req.seq
+                unsigned long long seq = 0ull;
+                if (at[r] != kNoSlot)
+                    seq = __ldg(seq_start + at[r]) + f + __popc(peers[r] & ((1u << lane) - 1u)) + 1ull;
+                if (kScatter)
+                    reinterpret_cast<unsigned long long*>(reqs + j)[1] = seq;  // ptype_req.seq
+                else
+                    seq_out[j] = seq;
             }
         }
     }
@@ -356,65 +378,80 @@ __global__ void __launch_bounds__(kScanThreads)
 RankTable table_of(const DeviceImage& img) { return RankTable{img.slots, img.n_slots, img.table_seed}; }
 
 template <bool kStaged, int kThreads>
-cudaError_t prepare_variant(size_t smem, int* per_sm) {
-    if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(rank_count_kernel<kStaged, kThreads>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-        if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(rank_assign_kernel<kStaged, kThreads>,
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-        if (e != cudaSuccess) return e;
-    }
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(per_sm, rank_assign_kernel<kStaged, kThreads>, kThreads, smem);
+cudaError_t prepare_count(size_t smem) {
+    if (smem <= 48 * 1024) return cudaSuccess;
+    return cudaFuncSetAttribute(rank_count_kernel<kStaged, kThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(smem));
 }
 
 }  // namespace
 
 bool rank_supported(uint32_t n_slots) { return rank_shared_bytes(false, n_slots) <= 200 * 1024; }
 
-// How a batch of n calls is split: variant, CTAs (= chunks = matrix rows) and records per chunk.
+// How a batch of n calls is split.  Rows of the matrix = chunks = CTAs of the assign pass (256
+// threads, as many per SM as their counts fit); a CTA of the count pass (which may stage the keys
+// and then fits once per SM) takes `sub` consecutive chunks.
 cudaError_t rank_plan(uint32_t n_slots, size_t n, int sm_count, RankPlan* plan) {
     plan->staged = rank_shared_bytes(true, n_slots) <= kRankSmemBudget;
     plan->threads = plan->staged ? kStagedThreads : kProbeThreads;
     plan->smem = rank_shared_bytes(plan->staged, n_slots);
-    int per_sm = 0;
-    cudaError_t e = plan->staged ? prepare_variant<true, kStagedThreads>(plan->smem, &per_sm)
-                                 : prepare_variant<false, kProbeThreads>(plan->smem, &per_sm);
+    plan->assign_smem = static_cast<size_t>(n_slots) * 4;
+    cudaError_t e = plan->staged ? prepare_count<true, kStagedThreads>(plan->smem)
+                                 : prepare_count<false, kProbeThreads>(plan->smem);
     if (e != cudaSuccess) return e;
-    if (per_sm < 1) return cudaErrorInvalidConfiguration;
-    const int cap = plan->staged ? 2 : 4;
-    if (per_sm > cap) per_sm = cap;
-    size_t ctas = static_cast<size_t>(sm_count) * per_sm;
-    const size_t rounds = (n + plan->threads - 1) / plan->threads;
-    if (ctas > rounds) ctas = rounds ? rounds : 1;
-    // a chunk is a whole number of CTA-wide rounds, so chunk boundaries are warp-aligned
-    plan->chunk = (rounds + ctas - 1) / ctas * plan->threads;
+    int assign_per_sm = 0;
+    for (int scatter = 0; scatter < 2; ++scatter) {
+        auto kernel = scatter ? rank_assign_kernel<true> : rank_assign_kernel<false>;
+        if (plan->assign_smem > 48 * 1024) {
+            e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     static_cast<int>(plan->assign_smem));
+            if (e != cudaSuccess) return e;
+        }
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&assign_per_sm, kernel, kAssignThreads, plan->assign_smem);
+        if (e != cudaSuccess) return e;
+    }
+    if (assign_per_sm < 1) return cudaErrorInvalidConfiguration;
+    if (assign_per_sm > 8) assign_per_sm = 8;
+    // a chunk is a whole number of the assign pass's trips, so chunk boundaries are warp-aligned
+    const size_t trip = static_cast<size_t>(kAssignThreads) * kAssignDepth;
+    const size_t trips = (n + trip - 1) / trip;
+    size_t rows = static_cast<size_t>(sm_count) * assign_per_sm;
+    if (rows > trips) rows = trips ? trips : 1;
+    plan->chunk = (trips + rows - 1) / rows * trip;
     plan->n_chunks = static_cast<int>((n + plan->chunk - 1) / plan->chunk);
     if (plan->n_chunks < 1) plan->n_chunks = 1;
+    // count pass: one CTA per SM when it stages the keys (two for small tables), four when it probes
+    int count_ctas = sm_count * (plan->staged ? (plan->smem <= 100 * 1024 ? 2 : 1) : 4);
+    if (count_ctas > plan->n_chunks) count_ctas = plan->n_chunks;
+    plan->sub = (plan->n_chunks + count_ctas - 1) / count_ctas;
+    plan->count_ctas = (plan->n_chunks + plan->sub - 1) / plan->sub;
     return cudaSuccess;
 }
 
-// rows: n_chunks x n_slots uint32 scratch; seq_start: n_slots uint64 scratch.
+// rows: n_chunks x n_slots uint32 scratch; ids: n uint32 scratch; seq_start: n_slots uint64 scratch.
+// seq_out == nullptr: the sequence numbers go into ptype_req.seq of the records; else into seq_out[j].
 cudaError_t launch_assign_seq(const DeviceImage& img, const RankPlan& plan, ptype_req* reqs, size_t n,
-                              uint32_t* rows, unsigned long long* counters, unsigned long long* seq_start,
-                              cudaStream_t stream) {
+                              uint32_t* rows, uint32_t* ids, unsigned long long* counters,
+                              unsigned long long* seq_start, unsigned long long* seq_out, cudaStream_t stream) {
     const RankTable t = table_of(img);
     if (plan.staged)
-        rank_count_kernel<true, kStagedThreads><<<plan.n_chunks, kStagedThreads, plan.smem, stream>>>(t, reqs, n, plan.chunk, rows);
+        rank_count_kernel<true, kStagedThreads><<<plan.count_ctas, kStagedThreads, plan.smem, stream>>>(
+            t, reqs, n, plan.chunk, plan.sub, plan.n_chunks, rows, ids);
     else
-        rank_count_kernel<false, kProbeThreads><<<plan.n_chunks, kProbeThreads, plan.smem, stream>>>(t, reqs, n, plan.chunk, rows);
+        rank_count_kernel<false, kProbeThreads><<<plan.count_ctas, kProbeThreads, plan.smem, stream>>>(
+            t, reqs, n, plan.chunk, plan.sub, plan.n_chunks, rows, ids);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     rank_scan_kernel<<<(img.n_slots + 31) / 32, kScanThreads, 0, stream>>>(rows, plan.n_chunks, img.n_slots, counters,
                                                                           seq_start);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    if (plan.staged)
-        rank_assign_kernel<true, kStagedThreads><<<plan.n_chunks, kStagedThreads, plan.smem, stream>>>(t, reqs, n, plan.chunk, rows,
-                                                                                                   seq_start);
+    if (seq_out == nullptr)
+        rank_assign_kernel<true><<<plan.n_chunks, kAssignThreads, plan.assign_smem, stream>>>(
+            img.n_slots, ids, reqs, nullptr, n, plan.chunk, rows, seq_start);
     else
-        rank_assign_kernel<false, kProbeThreads><<<plan.n_chunks, kProbeThreads, plan.smem, stream>>>(t, reqs, n, plan.chunk, rows,
-                                                                                                  seq_start);
+        rank_assign_kernel<false><<<plan.n_chunks, kAssignThreads, plan.assign_smem, stream>>>(
+            img.n_slots, ids, nullptr, seq_out, n, plan.chunk, rows, seq_start);
     return cudaGetLastError();
 }
 
