@@ -509,6 +509,16 @@ int ptype_b200_wire_encode(ptype_ctx*, int dev, const uint8_t* request_bytes, co
  * Device pointers only; PTYPE_F_ASYNC is honoured.  PTYPE_E_LIMIT: tables beyond 51 200 slots
  * (the per-CTA histogram is one 32-bit count per slot in shared memory). */
 int ptype_b200_assign_seq(ptype_ctx*, int dev, ptype_req* d_reqs, size_t n, uint32_t flags);
+/* The same draw, with the numbers written to a plain array d_seq[0..n) instead of into the records
+ * (which are only read), and the dispatch that takes them from there: call j is routed with
+ * d_seq[j], its record's seq field is ignored.  Same replies as assign_seq + dispatch, for less
+ * memory traffic: storing 8 bytes into every 48-byte record costs the memory system a read and a
+ * write of a 32-byte sector per record, an array of 8-byte numbers is written and read once.
+ * Device pointers only; PTYPE_F_ASYNC is honoured; dispatch_seq accepts PTYPE_F_GLOBAL_TABLE. */
+int ptype_b200_assign_seq_array(ptype_ctx*, int dev, const ptype_req* d_reqs, size_t n, uint64_t* d_seq,
+                                uint32_t flags);
+int ptype_b200_dispatch_seq(ptype_ctx*, int dev, const ptype_req* d_reqs, const uint64_t* d_seq, size_t n,
+                            ptype_reply* d_replies, uint32_t flags);
 /* Read / set one service's counter (the value the next call will exceed by one).
  * PTYPE_E_NOT_FOUND: the installed image has no such service. */
 int ptype_b200_seq_get(ptype_ctx*, int dev, const char* service, uint64_t* value);

@@ -129,6 +129,8 @@ SIGNATURES = [
     ("ptype_b200_wire_encode", C.c_int,
      [_vp, C.c_int, _vp, _vp, C.c_size_t, _vp, _vp, C.c_uint32, C.c_uint32, _vp, _vp, _vp, C.c_size_t, _u64p]),
     ("ptype_b200_assign_seq", C.c_int, [_vp, C.c_int, _vp, C.c_size_t, C.c_uint32]),
+    ("ptype_b200_assign_seq_array", C.c_int, [_vp, C.c_int, _vp, C.c_size_t, _vp, C.c_uint32]),
+    ("ptype_b200_dispatch_seq", C.c_int, [_vp, C.c_int, _vp, _vp, C.c_size_t, _vp, C.c_uint32]),
     ("ptype_b200_seq_get", C.c_int, [_vp, C.c_int, C.c_char_p, _u64p]),
     ("ptype_b200_seq_set", C.c_int, [_vp, C.c_int, C.c_char_p, C.c_uint64]),
     ("ptype_b200_launch_count", C.c_int, [_vp, _u64p]),

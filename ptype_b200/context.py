@@ -101,6 +101,16 @@ class Context:
         """Fill the seq field of n device-resident records as n sequential Client.Call()s would."""
         check(lib.ptype_b200_assign_seq(self._h, dev, _ptr(reqs), n, 0 if sync else F_ASYNC), "assign_seq")
 
+    def assign_seq_array(self, reqs, n: int, seq, *, dev: int = 0, sync: bool = True) -> None:
+        """The same draw with the numbers written to the device array `seq` (n x uint64); records untouched."""
+        check(lib.ptype_b200_assign_seq_array(self._h, dev, _ptr(reqs), n, _ptr(seq), 0 if sync else F_ASYNC),
+              "assign_seq_array")
+
+    def dispatch_seq(self, reqs, seq, n: int, replies, *, dev: int = 0, flags: int = 0, sync: bool = True) -> None:
+        """Dispatch device-resident records whose sequence numbers lie in the device array `seq`."""
+        check(lib.ptype_b200_dispatch_seq(self._h, dev, _ptr(reqs), _ptr(seq), n, _ptr(replies),
+                                          flags | (0 if sync else F_ASYNC)), "dispatch_seq")
+
     def seq_get(self, service: str, dev: int = 0) -> int:
         v = C.c_uint64()
         check(lib.ptype_b200_seq_get(self._h, dev, service.encode(), C.byref(v)), "seq_get")

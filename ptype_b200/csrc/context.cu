@@ -1333,7 +1333,9 @@ uint32_t host_slot_of(const ptype_ctx* ctx, const char* service) {
 }
 }  // namespace
 
-int ptype_b200_assign_seq(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, uint32_t flags) {
+namespace {
+// Shared body of assign_seq (numbers into the records) and assign_seq_array (into d_seq).
+int assign_seq_impl(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, unsigned long long* d_seq, uint32_t flags) {
     DeviceState* d = dev_of(ctx, dev);
     if (!d || (n && !d_reqs) || misaligned(d_reqs, 16)) return PTYPE_E_INVAL;
     if (n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
@@ -1378,8 +1380,47 @@ int ptype_b200_assign_seq(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, 
     }
     d->after_dispatch = false;
     CU(ptype::launch_assign_seq(img, plan, d_reqs, n, d->rank_rows, d->rank_ids, d->seq_counters[d->active],
-                                d->seq_start, nullptr, d->stream));
+                                d->seq_start, d_seq, d->stream));
     ctx->launches.fetch_add(3);
+    if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
+    return PTYPE_OK;
+}
+}  // namespace
+
+int ptype_b200_assign_seq(ptype_ctx* ctx, int dev, ptype_req* d_reqs, size_t n, uint32_t flags) {
+    return assign_seq_impl(ctx, dev, d_reqs, n, nullptr, flags);
+}
+
+int ptype_b200_assign_seq_array(ptype_ctx* ctx, int dev, const ptype_req* d_reqs, size_t n, uint64_t* d_seq,
+                                uint32_t flags) {
+    if ((n && !d_seq) || misaligned(d_seq, 8)) return PTYPE_E_INVAL;
+    if (n == 0) return assign_seq_impl(ctx, dev, nullptr, 0, nullptr, flags);
+    // the records are only read when the numbers go to an array
+    return assign_seq_impl(ctx, dev, const_cast<ptype_req*>(d_reqs), n, reinterpret_cast<unsigned long long*>(d_seq),
+                           flags);
+}
+
+int ptype_b200_dispatch_seq(ptype_ctx* ctx, int dev, const ptype_req* d_reqs, const uint64_t* d_seq, size_t n,
+                            ptype_reply* d_replies, uint32_t flags) {
+    DeviceState* d = dev_of(ctx, dev);
+    if (!d || (n && (!d_reqs || !d_seq || !d_replies))) return PTYPE_E_INVAL;
+    if (misaligned(d_reqs, 16) || misaligned(d_replies, 16) || misaligned(d_seq, 8)) return PTYPE_E_INVAL;
+    if (n > 0xFFFFFFFFull) return PTYPE_E_LIMIT;
+    std::lock_guard<std::mutex> lk(d->mu);
+    if (d->active < 0) return PTYPE_E_NO_IMAGE;
+    CU(cudaSetDevice(d->device));
+    const int buf = d->active;
+    const ptype::DeviceImage img = d->view[buf];
+    // the loop that reads the side array loads requests with LDG: that plan's block shape
+    const ptype::LaunchPlan& plan = d->plan[buf][plan_kind((flags & PTYPE_F_GLOBAL_TABLE) | PTYPE_F_LDG_LOADS)][0];
+    if (n) {
+        const ptype_batch one = {d_reqs, d_replies, n};
+        // d_seq was written by whatever ran before on this stream (assign_seq_array): no overlap with it
+        d->after_dispatch = false;
+        CU(ptype::launch_dispatch_multi(img, plan, d->dispatch_sms, &one, 1, d->stream, take_pdl(d, flags),
+                                        reinterpret_cast<const unsigned long long*>(d_seq)));
+        ctx->launches.fetch_add(1);
+    }
     if (!(flags & PTYPE_F_ASYNC)) CU(cudaStreamSynchronize(d->stream));
     return PTYPE_OK;
 }

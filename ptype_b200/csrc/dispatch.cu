@@ -619,6 +619,9 @@ struct BatchList {
     uint32_t n[kMaxBatchesPerLaunch];
     uint32_t tile_end[kMaxBatchesPerLaunch];  // running total of 32-call tiles (< 2^32 per launch)
     int count;
+    // Sequence numbers kept beside the records (ptype_b200_assign_seq_array): when set, call j of
+    // the launch's ONE batch takes seq[j] instead of its record's seq field.
+    const unsigned long long* seq;
 };
 
 template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas>
@@ -691,7 +694,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
 // register (profiles/r02_c3_multi_source.csv): a warp's loads were in flight only while it waited
 // for them.  Here they are in flight during the ~260 instructions of the previous tile as well,
 // for the same 24 registers of load targets.
-template <bool kSmemTable, int kThreads, int kMinCtas>
+template <bool kSmemTable, int kThreads, int kMinCtas, bool kSideSeq>
 __global__ void __launch_bounds__(kThreads, kMinCtas)
     dispatch_multi_prefetch_kernel(const DeviceImage img, const __grid_constant__ BatchList list) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
@@ -705,7 +708,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
 
     int cursor = 0;  // batch of the tile being fetched; a warp's tiles only move forward
     // where a tile lies: its batch and its index inside the batch; issues its three loads
-    auto fetch = [&](uint32_t g, int& b, uint32_t& tile, uint4 (&ld)[3]) {
+    auto fetch = [&](uint32_t g, int& b, uint32_t& tile, uint4 (&ld)[3], unsigned long long& sq) {
         b = cursor;
         while (g >= list.tile_end[b]) ++b;
         cursor = b;
@@ -717,13 +720,18 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
             const size_t c = static_cast<size_t>(tile) * 96 + j * 32 + lane;
             ld[j] = c < n_chunks ? ld_stream(reqs + c) : make_uint4(0, 0, 0, 0);
         }
+        if (kSideSeq) {  // one batch per launch in this form: call index = tile * 32 + lane
+            const size_t j = (static_cast<size_t>(tile) << 5) + lane;
+            sq = j < list.n[0] ? __ldg(list.seq + j) : 0ull;
+        }
     };
 
     uint4 nxt[3];
     int nxt_b = 0;
     uint32_t nxt_tile = 0;
+    unsigned long long nxt_seq = 0;
     uint32_t g = warp_global;
-    if (g < total_tiles) fetch(g, nxt_b, nxt_tile, nxt);  // before the tables: the longest latency first
+    if (g < total_tiles) fetch(g, nxt_b, nxt_tile, nxt, nxt_seq);  // before the tables: the longest latency first
 
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
@@ -735,10 +743,15 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         uint4 cur[3] = {nxt[0], nxt[1], nxt[2]};
         const int b = nxt_b;
         const uint32_t tile = nxt_tile;
+        const unsigned long long seq = nxt_seq;
         g += total_warps;
-        if (g < total_tiles) fetch(g, nxt_b, nxt_tile, nxt);
+        if (g < total_tiles) fetch(g, nxt_b, nxt_tile, nxt, nxt_seq);
         uint4 q[3];
         transpose_tile(plan, lane, cur, q);
+        if (kSideSeq) {
+            q[0].z = static_cast<uint32_t>(seq);
+            q[0].w = static_cast<uint32_t>(seq >> 32);
+        }
         const size_t idx = (static_cast<size_t>(tile) << 5) + lane;
         if (idx < list.n[b])
             st_stream(list.replies[b] + idx, dispatch_one<kSmemTable>(img, sh, slots, cache, q[0], q[1], q[2]));
@@ -1160,8 +1173,11 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
 int max_batches_per_launch() { return kMaxBatchesPerLaunch; }
 
 cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
-                                  const ptype_batch* batches, int count, cudaStream_t stream, bool pdl) {
+                                  const ptype_batch* batches, int count, cudaStream_t stream, bool pdl,
+                                  const unsigned long long* seq) {
+    if (seq != nullptr && (count != 1 || plan.bulk)) return cudaErrorInvalidValue;
     BatchList list = {};
+    list.seq = seq;
     uint64_t tiles = 0;
     int m = 0;
     for (int b = 0; b < count; ++b) {
@@ -1200,12 +1216,24 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         return e ? std::atoi(e) : -1;
     }();
     const int prefetch = forced >= 0 ? forced : (img.max_conn != 0 ? 2 : 1);
+    if (seq != nullptr) {  // sequence numbers beside the records: the pipelined loop in either shape
+        if (plan.threads == kMaxThreads)
+            return plan.smem_table ? launch_kernel(dispatch_multi_prefetch_kernel<true, kMaxThreads, 1, true>, blocks,
+                                                   plan.threads, plan.dyn_smem, stream, pdl, img, list)
+                                   : launch_kernel(dispatch_multi_prefetch_kernel<false, kMaxThreads, 1, true>, blocks,
+                                                   plan.threads, plan.dyn_smem, stream, pdl, img, list);
+        return plan.smem_table
+                   ? launch_kernel(dispatch_multi_prefetch_kernel<true, kSmallThreads, kSmallMinCtas, true>, blocks,
+                                   plan.threads, plan.dyn_smem, stream, pdl, img, list)
+                   : launch_kernel(dispatch_multi_prefetch_kernel<false, kSmallThreads, kSmallMinCtas, true>, blocks,
+                                   plan.threads, plan.dyn_smem, stream, pdl, img, list);
+    }
     if (plan.threads == kMaxThreads) {
         if (prefetch >= 1) {
             if (plan.smem_table)
-                return launch_kernel(dispatch_multi_prefetch_kernel<true, kMaxThreads, 1>, blocks, plan.threads,
+                return launch_kernel(dispatch_multi_prefetch_kernel<true, kMaxThreads, 1, false>, blocks, plan.threads,
                                      plan.dyn_smem, stream, pdl, img, list);
-            return launch_kernel(dispatch_multi_prefetch_kernel<false, kMaxThreads, 1>, blocks, plan.threads,
+            return launch_kernel(dispatch_multi_prefetch_kernel<false, kMaxThreads, 1, false>, blocks, plan.threads,
                                  plan.dyn_smem, stream, pdl, img, list);
         }
         if (plan.smem_table)
@@ -1216,9 +1244,9 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     }
     if (prefetch >= 2) {
         if (plan.smem_table)
-            return launch_kernel(dispatch_multi_prefetch_kernel<true, kSmallThreads, kSmallMinCtas>, blocks,
+            return launch_kernel(dispatch_multi_prefetch_kernel<true, kSmallThreads, kSmallMinCtas, false>, blocks,
                                  plan.threads, plan.dyn_smem, stream, pdl, img, list);
-        return launch_kernel(dispatch_multi_prefetch_kernel<false, kSmallThreads, kSmallMinCtas>, blocks,
+        return launch_kernel(dispatch_multi_prefetch_kernel<false, kSmallThreads, kSmallMinCtas, false>, blocks,
                              plan.threads, plan.dyn_smem, stream, pdl, img, list);
     }
     if (plan.smem_table)

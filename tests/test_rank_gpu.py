@@ -227,3 +227,38 @@ def test_large_tables_either_side_of_the_staging_limit(oracle, n_slots):
             assert device_assign(ctx, reqs).tobytes() == want.tobytes(), (n_slots, n)
         assert ctx.seq_get("svc0007") == int(counters[snap.client_index("svc0007")]) > 0
         assert ctx.seq_get("idle") == 0
+
+
+@pytest.mark.parametrize("n", [0, 1, 33, 5000, (1 << 20) + 7])
+@pytest.mark.parametrize("mesh", [False, True])
+def test_seq_array_form_equals_the_record_form(stress, oracle, n, mesh):
+    """ptype_b200_assign_seq_array + ptype_b200_dispatch_seq: the numbers go to a plain array and
+    the dispatch takes them from there.  Same numbers, same replies as writing them into the
+    records and dispatching those - and the records are left as they were."""
+    if mesh:   # the 256-thread shape with identity selection (the other loop of the multi-batch kernel)
+        spec = w.calculator_registry(mesh=True)
+        img = spec.image()
+        kv, snap = oracle.snapshot_from_spec(spec, img.salt)
+        reqs = w.calculator_calls(n, seed=3, salt=img.salt)
+    else:
+        spec, img, kv, snap = stress
+        reqs = w.stress_calls(n, seed=31, salt=img.salt)
+    reqs["seq"] = 0xABCD
+    want = reqs.copy()
+    counters = np.zeros(snap.n_clients(), dtype=np.uint64)
+    snap.assign_seq(want, counters)
+    with p.Context([0]) as ctx:
+        ctx.publish(img)
+        d_req = ctx.device_buffer(max(n, 1) * 48).upload(reqs)
+        d_seq = ctx.device_buffer(max(n, 1) * 8)
+        d_rep = ctx.device_buffer(max(n, 1) * 16)
+        for rep in range(2):   # the counters carry on from the first batch to the second
+            if rep:
+                snap.assign_seq(want, counters)
+            ctx.assign_seq_array(d_req, n, d_seq, sync=False)
+            ctx.dispatch_seq(d_req, d_seq, n, d_rep)
+            assert np.array_equal(d_seq.download(np.uint64, n), want["seq"])
+            assert d_req.download(p.REQ_DTYPE, n).tobytes() == reqs.tobytes()
+            assert d_rep.download(p.REPLY_DTYPE, n).tobytes() == snap.dispatch(want, threads=8).tobytes()
+        for b in (d_req, d_seq, d_rep):
+            b.free()

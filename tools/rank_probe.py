@@ -32,6 +32,21 @@ def main() -> None:
             for _ in range(reps):
                 ctx.dispatch_device(d_req, n, d_rep)
             disp_s = (time.perf_counter() - t0) / reps
+            d_seq = ctx.device_buffer(n * 8)
+            for _ in range(3):
+                ctx.assign_seq_array(d_req, n, d_seq)
+                ctx.dispatch_seq(d_req, d_seq, n, d_rep)
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                ctx.assign_seq_array(d_req, n, d_seq)
+            arr_s = (time.perf_counter() - t0) / reps
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                ctx.assign_seq_array(d_req, n, d_seq, sync=False)
+                ctx.dispatch_seq(d_req, d_seq, n, d_rep)
+            both_s = (time.perf_counter() - t0) / reps
+            print(f"{name}: assign_seq_array {arr_s * 1e6:9.1f} us   assign_seq_array + dispatch_seq {both_s * 1e6:9.1f} us",
+                  flush=True)
             print(f"{name}: n={n} slots={image.header.n_slots} assign_seq {rank_s * 1e6:9.1f} us "
                   f"({n / rank_s / 1e9:6.2f} G calls/s)   dispatch (one launch, synchronous) {disp_s * 1e6:9.1f} us",
                   flush=True)
