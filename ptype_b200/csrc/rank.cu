@@ -310,13 +310,21 @@ __global__ void __launch_bounds__(kAssignThreads)
     const size_t hi = lo + chunk < n ? lo + chunk : n;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     constexpr size_t kTrip = static_cast<size_t>(kAssignThreads) * kAssignDepth;
+    const size_t lane_off = static_cast<size_t>(warp) * kAssignDepth * 32 + lane;
+    uint32_t nxt[kAssignDepth];  // the next trip's slot ids, in flight while this trip takes its turns
+#pragma unroll
+    for (int r = 0; r < kAssignDepth; ++r) {
+        const size_t j = lo + lane_off + static_cast<size_t>(r) * 32;
+        nxt[r] = j < hi ? __ldg(ids + j) : kNoSlot;
+    }
     for (size_t base = lo; base < hi; base += kTrip) {  // uniform trip count per CTA
-        const size_t mine = base + static_cast<size_t>(warp) * kAssignDepth * 32 + lane;
+        const size_t mine = base + lane_off;
         uint32_t at[kAssignDepth], peers[kAssignDepth], first[kAssignDepth];
 #pragma unroll
         for (int r = 0; r < kAssignDepth; ++r) {
-            const size_t j = mine + static_cast<size_t>(r) * 32;
-            at[r] = j < hi ? __ldg(ids + j) : kNoSlot;
+            at[r] = nxt[r];
+            const size_t j = mine + kTrip + static_cast<size_t>(r) * 32;
+            nxt[r] = j < hi ? __ldg(ids + j) : kNoSlot;
         }
 #pragma unroll
         for (int r = 0; r < kAssignDepth; ++r) {
@@ -326,13 +334,15 @@ __global__ void __launch_bounds__(kAssignThreads)
         }
         for (uint32_t w = 0; w < kAssignThreads / 32; ++w) {
             if (w == warp) {
+                // One shared-memory atomic per tile, issued by the tile's leaders (distinct slots
+                // within a tile, so no two lanes of an instruction meet); tiles in order, because
+                // the next tile may name the same service from another lane.  The results are
+                // not needed before the turn is over, so the eight atomics go out back to back.
 #pragma unroll
                 for (int r = 0; r < kAssignDepth; ++r) {
-                    if (at[r] != kNoSlot && (peers[r] & ((1u << lane) - 1u)) == 0) {
-                        first[r] = run[at[r]];
-                        run[at[r]] = first[r] + __popc(peers[r]);
-                    }
-                    __syncwarp();  // the next tile may name the same service from another lane
+                    if (at[r] != kNoSlot && (peers[r] & ((1u << lane) - 1u)) == 0)
+                        first[r] = atomicAdd(&run[at[r]], static_cast<uint32_t>(__popc(peers[r])));
+                    __syncwarp();
                 }
             }
             __syncthreads();
