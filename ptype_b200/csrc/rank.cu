@@ -334,14 +334,17 @@ __global__ void __launch_bounds__(kAssignThreads)
         }
         for (uint32_t w = 0; w < kAssignThreads / 32; ++w) {
             if (w == warp) {
-                // One shared-memory atomic per tile, issued by the tile's leaders (distinct slots
-                // within a tile, so no two lanes of an instruction meet); tiles in order, because
-                // the next tile may name the same service from another lane.  The results are
-                // not needed before the turn is over, so the eight atomics go out back to back.
+                // Only a tile's leaders (first lane of each service in the tile: distinct slots,
+                // so no two lanes of an instruction meet) touch the running counts; tiles in order,
+                // because the next tile may name the same service from another lane.  (A shared-
+                // memory atomic per tile instead of the load/store pair measured slower: 286 vs
+                // 220 us per 2^24 records - 32 spread lanes cost an atomic 64 LSU cycles.)
 #pragma unroll
                 for (int r = 0; r < kAssignDepth; ++r) {
-                    if (at[r] != kNoSlot && (peers[r] & ((1u << lane) - 1u)) == 0)
-                        first[r] = atomicAdd(&run[at[r]], static_cast<uint32_t>(__popc(peers[r])));
+                    if (at[r] != kNoSlot && (peers[r] & ((1u << lane) - 1u)) == 0) {
+                        first[r] = run[at[r]];
+                        run[at[r]] = first[r] + __popc(peers[r]);
+                    }
                     __syncwarp();
                 }
             }
