@@ -311,21 +311,18 @@ __global__ void __launch_bounds__(kAssignThreads)
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     constexpr size_t kTrip = static_cast<size_t>(kAssignThreads) * kAssignDepth;
     const size_t lane_off = static_cast<size_t>(warp) * kAssignDepth * 32 + lane;
-    uint32_t nxt[kAssignDepth];  // the next trip's slot ids, in flight while this trip takes its turns
-#pragma unroll
-    for (int r = 0; r < kAssignDepth; ++r) {
-        const size_t j = lo + lane_off + static_cast<size_t>(r) * 32;
-        nxt[r] = j < hi ? __ldg(ids + j) : kNoSlot;
-    }
     for (size_t base = lo; base < hi; base += kTrip) {  // uniform trip count per CTA
         const size_t mine = base + lane_off;
         uint32_t at[kAssignDepth], peers[kAssignDepth], first[kAssignDepth];
+        unsigned long long start[kAssignDepth];  // the counters' values before the batch: fetched now,
+                                                 // needed after the turns, so their latency hides there
 #pragma unroll
         for (int r = 0; r < kAssignDepth; ++r) {
-            at[r] = nxt[r];
-            const size_t j = mine + kTrip + static_cast<size_t>(r) * 32;
-            nxt[r] = j < hi ? __ldg(ids + j) : kNoSlot;
+            const size_t j = mine + static_cast<size_t>(r) * 32;
+            at[r] = j < hi ? __ldg(ids + j) : kNoSlot;
         }
+#pragma unroll
+        for (int r = 0; r < kAssignDepth; ++r) start[r] = at[r] != kNoSlot ? __ldg(seq_start + at[r]) : 0ull;
 #pragma unroll
         for (int r = 0; r < kAssignDepth; ++r) {
             // calls of one service inside a tile of 32: lanes in `peers`, in batch order
@@ -356,8 +353,7 @@ __global__ void __launch_bounds__(kAssignThreads)
             const uint32_t f = __shfl_sync(kFull, first[r], __ffs(peers[r]) - 1);
             if (j < hi) {
                 unsigned long long seq = 0ull;
-                if (at[r] != kNoSlot)
-                    seq = __ldg(seq_start + at[r]) + f + __popc(peers[r] & ((1u << lane) - 1u)) + 1ull;
+                if (at[r] != kNoSlot) seq = start[r] + f + __popc(peers[r] & ((1u << lane) - 1u)) + 1ull;
                 if (kScatter)
                     reinterpret_cast<unsigned long long*>(reqs + j)[1] = seq;  // ptype_req.seq
                 else
