@@ -285,7 +285,7 @@ func (d *Dispatcher) CallMixed(calls []MixedCall, replies []BatchReply) error {
 		return errors.New("ptype_b200: replies shorter than calls")
 	}
 	n := C.size_t(len(calls))
-	var dReq, dRep unsafe.Pointer
+	var dReq, dRep, dSeq unsafe.Pointer
 	if err := abiError("ptype_b200_device_alloc", C.ptype_b200_device_alloc(d.ctx, 0, n*48, &dReq)); err != nil {
 		return err
 	}
@@ -294,23 +294,37 @@ func (d *Dispatcher) CallMixed(calls []MixedCall, replies []BatchReply) error {
 		return err
 	}
 	defer C.ptype_b200_device_free(d.ctx, 0, dRep)
+	if err := abiError("ptype_b200_device_alloc", C.ptype_b200_device_alloc(d.ctx, 0, n*8, &dSeq)); err != nil {
+		return err
+	}
+	defer C.ptype_b200_device_free(d.ctx, 0, dSeq)
 	if err := abiError("ptype_b200_memcpy_h2d",
 		C.ptype_b200_memcpy_h2d(d.ctx, 0, dReq, unsafe.Pointer(&calls[0]), n*48)); err != nil {
 		return err
 	}
-	if err := d.AssignSeq(dReq, len(calls)); err != nil {
+	// The numbers go to an array beside the records and the dispatch reads them there: storing
+	// them into the 48-byte records would cost the GPU a read and a write of a sector per call.
+	if err := abiError("ptype_b200_assign_seq_array", C.ptype_b200_assign_seq_array(d.ctx, 0,
+		(*C.ptype_req)(dReq), n, (*C.uint64_t)(dSeq), C.PTYPE_F_ASYNC)); err != nil {
 		return err
 	}
-	if err := abiError("ptype_b200_dispatch", C.ptype_b200_dispatch(d.ctx, 0, (*C.ptype_req)(dReq), n,
-		(*C.ptype_reply)(dRep), C.PTYPE_F_DEVICE_PTRS)); err != nil {
+	if err := abiError("ptype_b200_dispatch_seq", C.ptype_b200_dispatch_seq(d.ctx, 0, (*C.ptype_req)(dReq),
+		(*C.uint64_t)(dSeq), n, (*C.ptype_reply)(dRep), 0)); err != nil {
 		return err
 	}
 	if err := abiError("ptype_b200_memcpy_d2h",
 		C.ptype_b200_memcpy_d2h(d.ctx, 0, unsafe.Pointer(&replies[0]), dRep, n*16)); err != nil {
 		return err
 	}
-	return abiError("ptype_b200_memcpy_d2h",
-		C.ptype_b200_memcpy_d2h(d.ctx, 0, unsafe.Pointer(&calls[0]), dReq, n*48))
+	seq := make([]uint64, len(calls))
+	if err := abiError("ptype_b200_memcpy_d2h",
+		C.ptype_b200_memcpy_d2h(d.ctx, 0, unsafe.Pointer(&seq[0]), dSeq, n*8)); err != nil {
+		return err
+	}
+	for j := range calls {
+		calls[j].Seq = seq[j]
+	}
+	return nil
 }
 
 // Seq reads a service's counter: the last value drawn.

@@ -525,29 +525,39 @@ class Dispatcher {
     Error CallMixed(std::vector<ptype_req>& reqs, std::vector<ptype_reply>* replies) {
         replies->assign(reqs.size(), ptype_reply{});
         if (reqs.empty()) return Error();
-        void *d_req = nullptr, *d_rep = nullptr;
+        const size_t n = reqs.size();
+        void *d_req = nullptr, *d_rep = nullptr, *d_seq = nullptr;
         auto fail = [&](const char* what, int rc) {
             if (d_req) ptype_b200_device_free(ctx_, 0, d_req);
             if (d_rep) ptype_b200_device_free(ctx_, 0, d_rep);
+            if (d_seq) ptype_b200_device_free(ctx_, 0, d_seq);
             return Error(std::string(what) + ": " + ptype_b200_strerror(rc) + ": " + ptype_b200_last_error());
         };
-        int rc = ptype_b200_device_alloc(ctx_, 0, reqs.size() * sizeof(ptype_req), &d_req);
+        int rc = ptype_b200_device_alloc(ctx_, 0, n * sizeof(ptype_req), &d_req);
         if (rc != PTYPE_OK) return fail("device_alloc", rc);
-        rc = ptype_b200_device_alloc(ctx_, 0, reqs.size() * sizeof(ptype_reply), &d_rep);
+        rc = ptype_b200_device_alloc(ctx_, 0, n * sizeof(ptype_reply), &d_rep);
         if (rc != PTYPE_OK) return fail("device_alloc", rc);
-        rc = ptype_b200_memcpy_h2d(ctx_, 0, d_req, reqs.data(), reqs.size() * sizeof(ptype_req));
+        rc = ptype_b200_device_alloc(ctx_, 0, n * sizeof(uint64_t), &d_seq);
+        if (rc != PTYPE_OK) return fail("device_alloc", rc);
+        rc = ptype_b200_memcpy_h2d(ctx_, 0, d_req, reqs.data(), n * sizeof(ptype_req));
         if (rc != PTYPE_OK) return fail("memcpy_h2d", rc);
-        rc = ptype_b200_assign_seq(ctx_, 0, static_cast<ptype_req*>(d_req), reqs.size(), PTYPE_F_ASYNC);
-        if (rc != PTYPE_OK) return fail("assign_seq", rc);
-        rc = ptype_b200_dispatch(ctx_, 0, static_cast<const ptype_req*>(d_req), reqs.size(),
-                                 static_cast<ptype_reply*>(d_rep), PTYPE_F_DEVICE_PTRS);
-        if (rc != PTYPE_OK) return fail("dispatch", rc);
-        rc = ptype_b200_memcpy_d2h(ctx_, 0, replies->data(), d_rep, reqs.size() * sizeof(ptype_reply));
+        // the numbers go to an array beside the records and the dispatch reads them there: storing
+        // them into the 48-byte records would cost the GPU a read and a write of a sector per call
+        rc = ptype_b200_assign_seq_array(ctx_, 0, static_cast<const ptype_req*>(d_req), n,
+                                         static_cast<uint64_t*>(d_seq), PTYPE_F_ASYNC);
+        if (rc != PTYPE_OK) return fail("assign_seq_array", rc);
+        rc = ptype_b200_dispatch_seq(ctx_, 0, static_cast<const ptype_req*>(d_req), static_cast<const uint64_t*>(d_seq),
+                                     n, static_cast<ptype_reply*>(d_rep), 0);
+        if (rc != PTYPE_OK) return fail("dispatch_seq", rc);
+        rc = ptype_b200_memcpy_d2h(ctx_, 0, replies->data(), d_rep, n * sizeof(ptype_reply));
         if (rc != PTYPE_OK) return fail("memcpy_d2h", rc);
-        rc = ptype_b200_memcpy_d2h(ctx_, 0, reqs.data(), d_req, reqs.size() * sizeof(ptype_req));  // the seq drawn
+        std::vector<uint64_t> seq(n);
+        rc = ptype_b200_memcpy_d2h(ctx_, 0, seq.data(), d_seq, n * sizeof(uint64_t));  // the numbers drawn
         if (rc != PTYPE_OK) return fail("memcpy_d2h", rc);
+        for (size_t j = 0; j < n; ++j) reqs[j].seq = seq[j];
         ptype_b200_device_free(ctx_, 0, d_req);
         ptype_b200_device_free(ctx_, 0, d_rep);
+        ptype_b200_device_free(ctx_, 0, d_seq);
         return Error();
     }
     // The device-side counter of a service's Client (the last value drawn).
