@@ -273,11 +273,15 @@ __device__ __forceinline__ void lookup(const DeviceImage& img, const ptype_slot*
 
 // One call: lookup -> route -> resolve -> execute.  q0 = {svc_key, seq},
 // q1 = {method, recv, a0}, q2 = {a1, a2}.
-template <bool kSmemTable>
+// kCache = false: look the service up every time (registries with thousands of services, where
+// consecutive calls of a lane hardly ever name the same one and the compare is pure overhead).
+template <bool kSmemTable, bool kCache = true>
 __device__ __forceinline__ uint4 dispatch_one(const DeviceImage& img, const CtaShared& sh,
                                               const ptype_slot* slots, LookupCache& cache, uint4 q0,
                                               uint4 q1, uint4 q2) {
-    if (!(cache.valid && cache.key_lo == q0.x && cache.key_hi == q0.y)) {
+    if (!kCache) {
+        lookup<kSmemTable>(img, slots, q0.x, q0.y, cache.node_base, cache.n_and_recv);
+    } else if (!(cache.valid && cache.key_lo == q0.x && cache.key_hi == q0.y)) {
         lookup<kSmemTable>(img, slots, q0.x, q0.y, cache.node_base, cache.n_and_recv);
         cache.key_lo = q0.x;
         cache.key_hi = q0.y;
@@ -753,8 +757,10 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
             q[0].w = static_cast<uint32_t>(seq >> 32);
         }
         const size_t idx = (static_cast<size_t>(tile) << 5) + lane;
+        // the 1024-thread shape means a table beyond 100 KiB: thousands of services, no lookup cache
         if (idx < list.n[b])
-            st_stream(list.replies[b] + idx, dispatch_one<kSmemTable>(img, sh, slots, cache, q[0], q[1], q[2]));
+            st_stream(list.replies[b] + idx,
+                      dispatch_one<kSmemTable, kThreads != kMaxThreads>(img, sh, slots, cache, q[0], q[1], q[2]));
     }
     griddep_wait();
 }
