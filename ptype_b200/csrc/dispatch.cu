@@ -717,12 +717,18 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         while (g >= list.tile_end[b]) ++b;
         cursor = b;
         tile = g - (b ? list.tile_end[b - 1] : 0u);
-        const size_t n_chunks = static_cast<size_t>(list.n[b]) * 3;
-        const uint4* reqs = list.reqs[b];
+        // all tiles of a batch but (perhaps) its last are whole: one 64-bit address, three loads
+        // at constant offsets, nothing to compare or clear
+        const uint32_t calls = list.n[b];
+        const uint4* at = list.reqs[b] + static_cast<size_t>(tile) * 96 + lane;
+        if (tile < (calls >> 5)) {
 #pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            const size_t c = static_cast<size_t>(tile) * 96 + j * 32 + lane;
-            ld[j] = c < n_chunks ? ld_stream(reqs + c) : make_uint4(0, 0, 0, 0);
+            for (int j = 0; j < 3; ++j) ld[j] = ld_stream(at + j * 32);
+        } else {
+            const uint32_t chunks_here = (calls & 31u) * 3u;  // 16-byte chunks of the short last tile
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+                ld[j] = j * 32 + lane < chunks_here ? ld_stream(at + j * 32) : make_uint4(0, 0, 0, 0);
         }
         if (kSideSeq) {  // one batch per launch in this form: call index = tile * 32 + lane
             const size_t j = (static_cast<size_t>(tile) << 5) + lane;
@@ -756,10 +762,10 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
             q[0].z = static_cast<uint32_t>(seq);
             q[0].w = static_cast<uint32_t>(seq >> 32);
         }
-        const size_t idx = (static_cast<size_t>(tile) << 5) + lane;
         // the 1024-thread shape means a table beyond 100 KiB: thousands of services, no lookup cache
-        if (idx < list.n[b])
-            st_stream(list.replies[b] + idx,
+        const uint32_t calls = list.n[b];
+        if (tile < (calls >> 5) || lane < (calls & 31u))
+            st_stream(list.replies[b] + (static_cast<size_t>(tile) << 5) + lane,
                       dispatch_one<kSmemTable, kThreads != kMaxThreads>(img, sh, slots, cache, q[0], q[1], q[2]));
     }
     griddep_wait();
