@@ -578,6 +578,66 @@ def measure_wire(ctx, env, n_streams: int = 4096, calls_per_stream: int = 256, r
             "bytes_equal_loopback_streams": ok, "parity_ok": ok}
 
 
+def measure_assign_seq(ctx, env, n: int = 1 << 24, reps: int = 10) -> dict:
+    """SURVEY.md 8f N4 on the C3 registry: the balancers' counters drawn on the device for a batch that
+    mixes 10 000 services - into the records (assign_seq), and into an array beside them followed by the
+    dispatch that reads it (assign_seq_array + dispatch_seq).  CUDA events on the library's stream;
+    the first draw is compared with the oracle's sequential rule."""
+    import workloads as wl
+    from oracle import binding as ob
+    p, torch = env.p, env.torch
+    spec = wl.stress_registry(10_000, 64)
+    image = spec.image(epoch=1)
+    ctx.publish(image)
+    kv, snap = ob.snapshot_from_spec(spec, image.salt)
+    reqs = wl.stress_calls(n, 10_000, seed=0x5EED0700, salt=image.salt)
+    reqs["seq"] = 0
+    want = reqs.copy()
+    counters = np.zeros(snap.n_clients(), dtype=np.uint64)
+    snap.assign_seq(want, counters)
+    d_req = ctx.device_buffer(n * 48).upload(reqs)
+    d_seq = ctx.device_buffer(n * 8)
+    d_rep = ctx.device_buffer(n * 16)
+    ext = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", env.local_rank))
+    ctx.assign_seq_array(d_req, n, d_seq, sync=False)
+    ctx.dispatch_seq(d_req, d_seq, n, d_rep)
+    ok = bool(np.array_equal(d_seq.download(np.uint64, n), want["seq"]) and
+              d_rep.download(p.REPLY_DTYPE, n).tobytes() ==
+              snap.dispatch(want, check_limit=1 << 16, threads=os.cpu_count() or 1).tobytes())
+
+    def timed(fn):
+        fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ctx.sync()
+        a.record(ext)
+        for _ in range(reps):
+            fn()
+        b.record(ext)
+        ctx.sync()
+        return a.elapsed_time(b) * 1e3 / reps
+
+    in_records = timed(lambda: ctx.assign_seq(d_req, n, sync=False))
+    to_array = timed(lambda: ctx.assign_seq_array(d_req, n, d_seq, sync=False))
+    with_dispatch = timed(lambda: (ctx.assign_seq_array(d_req, n, d_seq, sync=False),
+                                   ctx.dispatch_seq(d_req, d_seq, n, d_rep, sync=False)))
+    for b in (d_req, d_seq, d_rep):
+        b.free()
+    peak, _ = measured_peak()
+    return {"records": n, "services": 10_000,
+            "assign_seq_us": in_records, "assign_seq_array_us": to_array,
+            "assign_seq_array_plus_dispatch_seq_us": with_dispatch,
+            "records_per_s": n / (in_records * 1e-6), "array_records_per_s": n / (to_array * 1e-6),
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_record": 16,
+                         "what": "8-byte key read + 8-byte sequence number written per record",
+                         "achieved_gbs": n * 16 / (in_records * 1e-6) / 1e9, "peak": peak,
+                         "frac": n * 16 / (in_records * 1e-6) / 1e9 / peak,
+                         "frac_array_form": n * 16 / (to_array * 1e-6) / 1e9 / peak,
+                         "note": "the records are 48-byte structures: reading an 8-byte key moves 48 bytes per "
+                                 "record through DRAM, and storing 8 bytes into a record costs a 32-byte sector "
+                                 "read and written (tools/partial_write_probe.cu); the array form avoids the latter"},
+            "parity_ok": ok}
+
+
 def extra_summary(m: dict) -> dict:
     """A sub-run as it appears under `extras` in the JSON line."""
     s = {"workload": WORKLOAD_TEXT[m["workload"]], "value": m["value"], "unit": "calls/s", "steps": m["steps"],
@@ -805,20 +865,22 @@ def main():
             windows.append(x["window"])
             extras[name] = x
 
-    wire = None
+    wire = ranks = None
     if args.workload == "c2" and not args.no_extras and not args.flags and not multi:
         wire = measure_wire(ctx, env)
+        ranks = measure_assign_seq(ctx, env)
 
     sampler.stop()
     sampler.join(timeout=1.0)
     clocks = sampler.summary(windows)
 
     parity_ok = m["parity_ok"] and e2e["parity_ok"] and all(x["parity_ok"] for x in extras.values()) and \
-        (wire is None or wire["parity_ok"])
+        (wire is None or wire["parity_ok"]) and (ranks is None or ranks["parity_ok"])
     if not parity_ok:
         if rank == 0:
             bad = {"primary": m["parity"], "e2e_ok": e2e["parity_ok"],
-                   "extras": {k: x["parity"] for k, x in extras.items()}, "wire": wire and wire["parity_ok"]}
+                   "extras": {k: x["parity"] for k, x in extras.items()}, "wire": wire and wire["parity_ok"],
+                   "assign_seq": ranks and ranks["parity_ok"]}
             print(json.dumps({"error": "CUDA replies differ from the oracle - number withheld", "parity": bad}),
                   file=sys.stderr, flush=True)
         ctx.close()
@@ -888,6 +950,7 @@ def main():
             "host_enqueue_us_per_step": m["host_enqueue_s"] / args.steps * 1e6,
             "extras": {k: extra_summary(x) for k, x in extras.items()},
             "wire_codec": wire,
+            "assign_seq": ranks,
             "clocks": clocks,
         }
         if "live_updates" in m:
