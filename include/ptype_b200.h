@@ -469,7 +469,8 @@ int ptype_b200_gob_decode_args(ptype_ctx*, int dev, const uint8_t* bytes, const 
  * the sending process assigned to those two types (Go numbers user types from 65 in order of
  * first use).  out_off[0..n_streams] receives where every stream's bytes start in `out`;
  * *total_bytes is always set; PTYPE_E_LIMIT (nothing written, state untouched) beyond out_cap.
- * All pointers are device pointers on `dev`; both calls wait for completion. */
+ * All pointers are device pointers on `dev` (`bytes` 16-byte aligned, as cudaMalloc gives it); both
+ * calls wait for completion. */
 #define PTYPE_WIRE_MALFORMED 1u
 typedef struct ptype_wire_stream {
     uint64_t svc_key;  /* as ptype_req.svc_key: the service this server's node belongs to */

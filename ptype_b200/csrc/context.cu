@@ -1255,7 +1255,8 @@ int ptype_b200_wire_decode(ptype_ctx* ctx, int dev, const uint8_t* bytes, const 
                            ptype_wire_call* calls, size_t cap, uint64_t* total_calls) {
     DeviceState* d = dev_of(ctx, dev);
     if (!d || !call_off || !total_calls || (n_streams && (!bytes || !stream_off || !streams))) return PTYPE_E_INVAL;
-    if (misaligned(reqs, 16) || misaligned(calls, 8) || misaligned(streams, 8)) return PTYPE_E_INVAL;
+    if (misaligned(reqs, 16) || misaligned(calls, 8) || misaligned(streams, 8) || misaligned(bytes, 16))
+        return PTYPE_E_INVAL;  // the decoder copies the streams into shared memory 16 bytes at a time
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(d->device));
     d->after_dispatch = false;

@@ -34,17 +34,28 @@ constexpr int kWireThreads = 128;  // four streams per CTA
 constexpr uint32_t kFull = 0xFFFFFFFFu;
 
 // ---------------------------------------------------------------- gob readers
+// A stream is read through a window: the warp copies the next kWindow bytes of its stream into
+// shared memory with coalesced 16-byte loads, and the byte-by-byte readers below (lane 0 walking
+// length prefixes, then every lane parsing its own call) hit shared memory instead of chasing
+// dependent global loads.  Bytes outside the window (a chunk of calls longer than the window) are
+// still read from global memory.
+constexpr uint32_t kWindow = 2048;
 struct Cursor {
     const uint8_t* p;
     uint64_t pos, end;
     bool ok;
+    const uint8_t* win;  // shared-memory copy of p[wbase .. wbase + wlen)
+    uint64_t wbase;
+    uint32_t wlen;
 };
 __device__ __forceinline__ uint32_t rd_byte(Cursor& c) {
     if (c.pos >= c.end) {
         c.ok = false;
         return 0;
     }
-    return __ldg(c.p + c.pos++);
+    const uint64_t off = c.pos - c.wbase;  // wraps to a huge value below the window
+    const uint64_t at = c.pos++;
+    return off < c.wlen ? c.win[off] : __ldg(c.p + at);
 }
 __device__ __forceinline__ uint64_t rd_uint(Cursor& c) {
     const uint32_t b = rd_byte(c);
@@ -78,7 +89,9 @@ __device__ bool next_call(Cursor& c, Framed& f) {
             c.ok = false;
             return false;
         }
-        Cursor m = {c.p, body, body + len, true};
+        Cursor m = c;
+        m.pos = body;
+        m.end = body + len;
         const int64_t id = unzigzag(rd_uint(m));
         c.pos = body + len;
         if (!m.ok) {
@@ -110,27 +123,48 @@ __global__ void __launch_bounds__(kWireThreads)
                        unsigned long long* __restrict__ call_off, ptype_req* __restrict__ reqs,
                        ptype_wire_call* __restrict__ calls) {
     __shared__ Framed s_framed[kWireThreads / 32][32];
+    __shared__ __align__(16) uint8_t s_window[kWireThreads / 32][kWindow];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const size_t s = static_cast<size_t>(blockIdx.x) * (kWireThreads / 32) + warp;
     if (s >= n_streams) return;
-    Cursor c = {bytes, stream_off[s], stream_off[s + 1], true};
+    Cursor c = {bytes, stream_off[s], stream_off[s + 1], true, s_window[warp], 0, 0};
+    unsigned long long next_pos = c.pos;  // where the next chunk of calls starts (lane 0 knows, all lanes need it)
     unsigned long long done = 0;
     const unsigned long long out0 = kCount ? 0ull : call_off[s];
     ptype_wire_stream st = {};
     if (!kCount) st = streams[s];
     for (;;) {
+        // refill the window from the first byte not yet framed (16-byte chunks that lie wholly inside
+        // the stream; `bytes` comes from cudaMalloc, so a 16-aligned offset is a 16-aligned address)
+        {
+            const uint64_t wbase = next_pos & ~15ull;
+            const uint64_t avail = c.end > wbase ? c.end - wbase : 0;
+            const uint32_t wlen = avail >= kWindow ? kWindow : static_cast<uint32_t>(avail & ~15ull);
+            __syncwarp();  // the previous chunk's readers are done with the old window
+            for (uint32_t o = lane * 16; o < wlen; o += 32 * 16)
+                *reinterpret_cast<uint4*>(s_window[warp] + o) = __ldg(reinterpret_cast<const uint4*>(bytes + wbase + o));
+            __syncwarp();
+            c.wbase = wbase;
+            c.wlen = wlen;
+        }
         uint32_t n = 0;
         if (lane == 0) {
+            c.pos = next_pos;
             Framed f;
             while (n < 32 && next_call(c, f)) s_framed[warp][n++] = f;
+            next_pos = c.pos;
         }
         n = __shfl_sync(kFull, n, 0);
+        next_pos = __shfl_sync(kFull, next_pos, 0);
         __syncwarp();
         if (n == 0) break;
         if (!kCount && lane < n) {
             const Framed f = s_framed[warp][lane];
             // ---- rpc.Request{ServiceMethod, Seq}
-            Cursor h = {bytes, f.hdr_pos, f.hdr_end, true};
+            Cursor h = c;
+            h.pos = f.hdr_pos;
+            h.end = f.hdr_end;
+            h.ok = true;
             uint32_t hash = 0x811c9dc5u, hash_at_dot = 0;
             bool dot = false;
             unsigned long long rpc_seq = 0, sm_off = 0;
@@ -164,7 +198,10 @@ __global__ void __launch_bounds__(kWireThreads)
                 }
             }
             // ---- the args value: int fields by position (calculator.Args{A,B} / prime.Args{Min,Max,Target})
-            Cursor a = {bytes, f.arg_pos, f.arg_end, true};
+            Cursor a = c;
+            a.pos = f.arg_pos;
+            a.end = f.arg_end;
+            a.ok = true;
             int64_t v[3] = {0, 0, 0};
             field = -1;
             for (;;) {
