@@ -80,32 +80,64 @@ struct Framed {
 
 // Lane 0: walk messages from `c.pos` until one more call (a Request value and an args value, type
 // definitions skipped) is complete.  False at the end of the stream or on a framing error.
+// The walk is one lane running serial code, so its instruction count is what the whole decoder
+// costs (the first version spent ~250 warp instructions per call here and saturated the SMs'
+// issue slots with 1/32 of the lanes): the usual message - a one-byte length, a type id of at most
+// nine bytes, everything inside the window - takes three shared-memory bytes and a few compares,
+// because framing needs only the length and the SIGN of the type id (the low bit of its last byte).
 __device__ bool next_call(Cursor& c, Framed& f) {
     int have = 0;
     while (c.ok && c.pos < c.end) {
-        const uint64_t len = rd_uint(c);
-        const uint64_t body = c.pos;
-        if (!c.ok || len > c.end - body) {
-            c.ok = false;
-            return false;
+        uint64_t body, len, value_pos;
+        bool definition;
+        const uint64_t off = c.pos - c.wbase;
+        const uint32_t b0 = off + 11 <= c.wlen ? c.win[off] : 255u;
+        if (b0 < 128) {  // fast path: 1-byte length, the id's bytes in the window
+            len = b0;
+            body = c.pos + 1;
+            const uint32_t b1 = c.win[off + 1];
+            uint32_t id_bytes = 1, last = b1;
+            if (b1 >= 128) {
+                const uint32_t nb = 256u - b1;
+                if (nb > 8) {
+                    c.ok = false;
+                    return false;
+                }
+                id_bytes = 1 + nb;
+                last = c.win[off + 1 + nb];
+            }
+            definition = (last & 1u) != 0;  // zig-zag: odd = negative = a type definition
+            value_pos = body + id_bytes;
+            if (len > c.end - body || id_bytes > len) {
+                c.ok = false;
+                return false;
+            }
+        } else {
+            len = rd_uint(c);
+            body = c.pos;
+            if (!c.ok || len > c.end - body) {
+                c.ok = false;
+                return false;
+            }
+            Cursor m = c;
+            m.pos = body;
+            m.end = body + len;
+            definition = unzigzag(rd_uint(m)) < 0;
+            value_pos = m.pos;
+            if (!m.ok) {
+                c.ok = false;
+                return false;
+            }
         }
-        Cursor m = c;
-        m.pos = body;
-        m.end = body + len;
-        const int64_t id = unzigzag(rd_uint(m));
         c.pos = body + len;
-        if (!m.ok) {
-            c.ok = false;
-            return false;
-        }
-        if (id < 0) continue;  // a type definition: nothing to decode, the values are positional
+        if (definition) continue;  // nothing to decode: the values are positional
         if (have == 0) {
-            f.hdr_pos = m.pos;
-            f.hdr_end = m.end;
+            f.hdr_pos = value_pos;
+            f.hdr_end = body + len;
             have = 1;
         } else {
-            f.arg_pos = m.pos;
-            f.arg_end = m.end;
+            f.arg_pos = value_pos;
+            f.arg_end = body + len;
             return true;
         }
     }
