@@ -356,19 +356,16 @@ __device__ __forceinline__ uint4 dispatch_one(const DeviceImage& img, const CtaS
     return out;
 }
 
-// Stage method tables / connection hashes with plain loads and start the bulk copy of the
-// slot table.  Ends with the table copy in flight (wait on sh.table_bar, parity 0).
+// Start the bulk copy of the slot table, then stage method tables / connection hashes with plain
+// loads.  Ends with the table copy in flight (wait on sh.table_bar, parity 0).
 template <bool kSmemTable>
 __device__ __forceinline__ const ptype_slot* stage_tables(const DeviceImage& img, CtaShared& sh,
                                                           unsigned char* table_smem) {
-    if (kSmemTable && threadIdx.x == 0) mbar_init(&sh.table_bar, 1);
-    for (uint32_t i = threadIdx.x; i < PTYPE_MTABLE_SLOTS; i += blockDim.x) sh.mtable[i] = img.mtable[i];
-    for (uint32_t i = threadIdx.x; i < img.n_methods; i += blockDim.x) sh.methods[i] = img.methods[i];
-    if (img.max_conn <= kSmemConn)
-        for (uint32_t i = threadIdx.x; i < img.max_conn; i += blockDim.x) sh.conn[i] = img.conn_hash[i];
-    if (threadIdx.x < PTYPE_ST__COUNT) sh.status[threadIdx.x] = 0;
-    __syncthreads();
+    // The slot table's bulk copy goes out first: only thread 0 touches the barrier before the
+    // __syncthreads below, so nothing has to wait for the small tables' loads (one memory latency
+    // less at the head of every CTA than issuing the copy after them).
     if (kSmemTable && threadIdx.x == 0) {
+        mbar_init(&sh.table_bar, 1);
         const uint32_t bytes = img.n_slots * static_cast<uint32_t>(sizeof(ptype_slot));
         mbar_expect_tx(&sh.table_bar, bytes);
         constexpr uint32_t kChunk = 32768;
@@ -378,6 +375,12 @@ __device__ __forceinline__ const ptype_slot* stage_tables(const DeviceImage& img
                      &sh.table_bar);
         }
     }
+    for (uint32_t i = threadIdx.x; i < PTYPE_MTABLE_SLOTS; i += blockDim.x) sh.mtable[i] = img.mtable[i];
+    for (uint32_t i = threadIdx.x; i < img.n_methods; i += blockDim.x) sh.methods[i] = img.methods[i];
+    if (img.max_conn <= kSmemConn)
+        for (uint32_t i = threadIdx.x; i < img.max_conn; i += blockDim.x) sh.conn[i] = img.conn_hash[i];
+    if (threadIdx.x < PTYPE_ST__COUNT) sh.status[threadIdx.x] = 0;
+    __syncthreads();
     return kSmemTable ? reinterpret_cast<const ptype_slot*>(table_smem) : img.slots;
 }
 
