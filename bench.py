@@ -457,8 +457,9 @@ def measure(ctx, env, workload: str, *, steps: int, warmup: int, nbuf: int, batc
     launches0 = ctx.launch_count()
     w0 = time.perf_counter()
     ev0.record(ext)
+    h0 = time.perf_counter()
     run_steps(timed)
-    host_enqueue_s = time.perf_counter() - w0
+    host_enqueue_s = time.perf_counter() - h0   # the host's cost of submitting the K steps (and C5's updates)
     ev1.record(ext)
     env.barrier(ctx)
     w1 = time.perf_counter()
