@@ -271,46 +271,15 @@ __device__ __forceinline__ void lookup(const DeviceImage& img, const ptype_slot*
     }
 }
 
-// The same lookup on a table staged as two arrays: keys[n_slots] (8 bytes each) then
-// {node_base, n_and_recv}[n_slots].  Three 8-byte probes and one 8-byte payload read put half the
-// wavefronts on the shared-memory pipe that three random 16-byte probes do.
-__device__ __forceinline__ void lookup_split(const DeviceImage& img, const ptype_slot* table, uint32_t key_lo,
-                                             uint32_t key_hi, uint32_t& node_base, uint32_t& n_and_recv) {
-    const uint2* keys = reinterpret_cast<const uint2*>(table);
-    const uint2* vals = keys + img.n_slots;
-    uint32_t at[PTYPE_SLOT_WAYS];
-    uint2 k[PTYPE_SLOT_WAYS];
-#pragma unroll
-    for (int w = 0; w < PTYPE_SLOT_WAYS; ++w) {
-        at[w] = slot_of(key_lo, key_hi, img.table_seed, w, img.n_slots);
-        k[w] = keys[at[w]];
-    }
-    uint32_t hit = PTYPE_SLOT_EMPTY;
-#pragma unroll
-    for (int w = 0; w < PTYPE_SLOT_WAYS; ++w)
-        if (k[w].x == key_lo && k[w].y == key_hi) hit = at[w];
-    node_base = PTYPE_SLOT_EMPTY;
-    n_and_recv = 0;
-    if (hit != PTYPE_SLOT_EMPTY) {
-        const uint2 v = vals[hit];
-        if (v.x != PTYPE_SLOT_EMPTY) {  // a free slot holds key 0: a request naming key 0 must not match it
-            node_base = v.x;
-            n_and_recv = v.y;
-        }
-    }
-}
-
 // One call: lookup -> route -> resolve -> execute.  q0 = {svc_key, seq},
 // q1 = {method, recv, a0}, q2 = {a1, a2}.
 // kCache = false: look the service up every time (registries with thousands of services, where
 // consecutive calls of a lane hardly ever name the same one and the compare is pure overhead).
-template <bool kSmemTable, bool kCache = true, bool kSplitTable = false>
+template <bool kSmemTable, bool kCache = true>
 __device__ __forceinline__ uint4 dispatch_one(const DeviceImage& img, const CtaShared& sh,
                                               const ptype_slot* slots, LookupCache& cache, uint4 q0,
                                               uint4 q1, uint4 q2) {
-    if (kSplitTable) {
-        lookup_split(img, slots, q0.x, q0.y, cache.node_base, cache.n_and_recv);
-    } else if (!kCache) {
+    if (!kCache) {
         lookup<kSmemTable>(img, slots, q0.x, q0.y, cache.node_base, cache.n_and_recv);
     } else if (!(cache.valid && cache.key_lo == q0.x && cache.key_hi == q0.y)) {
         lookup<kSmemTable>(img, slots, q0.x, q0.y, cache.node_base, cache.n_and_recv);
@@ -732,10 +701,9 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
 // register (profiles/r02_c3_multi_source.csv): a warp's loads were in flight only while it waited
 // for them.  Here they are in flight during the ~260 instructions of the previous tile as well,
 // for the same 24 registers of load targets.
-template <bool kSmemTable, int kThreads, int kMinCtas, bool kSideSeq, bool kSplitTable = false>
+template <bool kSmemTable, int kThreads, int kMinCtas, bool kSideSeq>
 __global__ void __launch_bounds__(kThreads, kMinCtas)
     dispatch_multi_prefetch_kernel(const DeviceImage img, const __grid_constant__ BatchList list) {
-    static_assert(!kSplitTable || kSmemTable, "the split layout is a shared-memory layout");
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ __align__(16) CtaShared sh;
 
@@ -778,26 +746,11 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     uint32_t g = warp_global;
     if (g < total_tiles) fetch(g, nxt_b, nxt_tile, nxt, nxt_seq);  // before the tables: the longest latency first
 
-    const ptype_slot* slots;
-    if (kSplitTable) {
-        // keys and payloads into two arrays: copied by the threads (a bulk copy cannot split them)
-        stage_tables<false>(img, sh, dyn_smem);
-        uint2* keys = reinterpret_cast<uint2*>(dyn_smem);
-        uint2* vals = keys + img.n_slots;
-        for (uint32_t i = threadIdx.x; i < img.n_slots; i += blockDim.x) {
-            const uint4 e = __ldg(reinterpret_cast<const uint4*>(img.slots + i));
-            keys[i] = make_uint2(e.x, e.y);
-            vals[i] = make_uint2(e.z, e.w);
-        }
-        __syncthreads();
-        slots = reinterpret_cast<const ptype_slot*>(dyn_smem);
-    } else {
-        slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
-    }
+    const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
     const TransposePlan plan = transpose_plan(lane);
     LookupCache cache;
-    if (kSmemTable && !kSplitTable) mbar_wait(&sh.table_bar, 0);
+    if (kSmemTable) mbar_wait(&sh.table_bar, 0);
 
     while (g < total_tiles) {
         uint4 cur[3] = {nxt[0], nxt[1], nxt[2]};
@@ -816,8 +769,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         const uint32_t calls = list.n[b];
         if (tile < (calls >> 5) || lane < (calls & 31u))
             st_stream(list.replies[b] + (static_cast<size_t>(tile) << 5) + lane,
-                      dispatch_one<kSmemTable, kThreads != kMaxThreads, kSplitTable>(img, sh, slots, cache, q[0], q[1],
-                                                                                     q[2]));
+                      dispatch_one<kSmemTable, kThreads != kMaxThreads>(img, sh, slots, cache, q[0], q[1], q[2]));
     }
     griddep_wait();
 }
@@ -1293,13 +1245,6 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     }
     if (plan.threads == kMaxThreads) {
         if (prefetch >= 1) {
-            static const bool split = [] {  // PTYPE_B200_SPLIT_TABLE=0: one 16-byte entry per slot (measurement switch)
-                const char* e = std::getenv("PTYPE_B200_SPLIT_TABLE");
-                return !(e && e[0] == '0');
-            }();
-            if (plan.smem_table && split)
-                return launch_kernel(dispatch_multi_prefetch_kernel<true, kMaxThreads, 1, false, true>, blocks,
-                                     plan.threads, plan.dyn_smem, stream, pdl, img, list);
             if (plan.smem_table)
                 return launch_kernel(dispatch_multi_prefetch_kernel<true, kMaxThreads, 1, false>, blocks, plan.threads,
                                      plan.dyn_smem, stream, pdl, img, list);
