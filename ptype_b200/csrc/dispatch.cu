@@ -774,6 +774,124 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     griddep_wait();
 }
 
+// The same pipeline with fewer instructions per tile (C3 spent 242 on a tile, a third of them moving
+// data around rather than dispatching).  Three cuts:
+//   * two register sets that swap roles every tile instead of one copied into the other;
+//   * what a warp needs to know about its current batch (tile range, request and reply base with
+//     the lane's offset folded in) lives in registers and changes only when the warp crosses into
+//     another batch, ~7 tiles apart - no constant-bank table walk per tile;
+//   * the sender-side register choice of the transpose as selects, not divergent branches.
+// The reply address is made when the tile is fetched; its bit 0 marks a lane beyond the batch's end.
+__device__ __forceinline__ uint32_t pick3(bool first, bool second, uint32_t a, uint32_t b, uint32_t c) {
+    const uint32_t bc = second ? b : c;
+    return first ? a : bc;
+}
+// Same data movement as transpose_tile.  The register a lane sends in round c depends on the lane
+// modulo 3 only: chunk 32k+s belongs to round (2k+s) mod 3, so round c sends register
+// k = 2(c-s) mod 3, which is 0 when s = c and 1 when s = c+1 (mod 3).
+__device__ __forceinline__ void transpose_tile_sel(uint32_t lane_mod3, uint32_t lane, const uint4 (&ld)[3],
+                                                   uint4 (&q)[3]) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const bool r0 = lane_mod3 == static_cast<uint32_t>(c), r1 = lane_mod3 == static_cast<uint32_t>((c + 1) % 3);
+        const uint32_t src = (3u * lane + c) & 31u;
+        q[c].x = __shfl_sync(kFull, pick3(r0, r1, ld[0].x, ld[1].x, ld[2].x), src);
+        q[c].y = __shfl_sync(kFull, pick3(r0, r1, ld[0].y, ld[1].y, ld[2].y), src);
+        q[c].z = __shfl_sync(kFull, pick3(r0, r1, ld[0].z, ld[1].z, ld[2].z), src);
+        q[c].w = __shfl_sync(kFull, pick3(r0, r1, ld[0].w, ld[1].w, ld[2].w), src);
+    }
+}
+
+struct TileRegs {
+    uint4 ld[3];
+    uint4* out;              // this lane's reply record; bit 0 set: no call behind this lane
+    unsigned long long seq;  // kSideSeq only
+};
+
+template <bool kSmemTable, int kThreads, int kMinCtas, bool kSideSeq>
+__global__ void __launch_bounds__(kThreads, kMinCtas)
+    dispatch_multi_swap_kernel(const DeviceImage img, const __grid_constant__ BatchList list) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ __align__(16) CtaShared sh;
+
+    const uint32_t lane = threadIdx.x & 31u;
+    constexpr uint32_t kWarps = kThreads / 32;  // launched with exactly kThreads threads
+
+    // Where the warp is: batch b, tile `tile` of it.  b_whole = whole tiles in batch b; request and
+    // reply base already point at this lane's 16 bytes of tile 0.
+    int b = 0;
+    uint32_t tile = blockIdx.x * kWarps + (threadIdx.x >> 5);
+    uint32_t b_whole = list.n[0] >> 5;
+    const uint4* b_reqs = list.reqs[0] + lane;
+    uint4* b_out = list.replies[0] + lane;
+
+    // Loads tile (b, tile) after moving (b, tile) forward into the batch that holds it; leaves
+    // b == list.count when the stream has ended.
+    auto fetch = [&](TileRegs& t) {
+        uint32_t calls_here = 32;
+        if (tile >= b_whole) {  // warp-uniform and rare: a short last tile, or on into a later batch
+            for (;;) {
+                const uint32_t nb = list.n[b], tiles_b = (nb + 31u) >> 5;
+                if (tile < tiles_b) {
+                    calls_here = nb & 31u;
+                    break;
+                }
+                tile -= tiles_b;
+                if (++b == list.count) return;
+                b_whole = list.n[b] >> 5;
+                b_reqs = list.reqs[b] + lane;
+                b_out = list.replies[b] + lane;
+                if (tile < b_whole) break;
+            }
+        }
+        const uint4* at = b_reqs + static_cast<size_t>(tile) * 96;
+        t.out = b_out + (static_cast<size_t>(tile) << 5);
+        if (calls_here == 32) {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) t.ld[j] = ld_stream(at + j * 32);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+                t.ld[j] = j * 32 + lane < calls_here * 3u ? ld_stream(at + j * 32) : make_uint4(0, 0, 0, 0);
+            if (lane >= calls_here) t.out = reinterpret_cast<uint4*>(reinterpret_cast<uintptr_t>(t.out) | 1u);
+        }
+        if (kSideSeq)  // one batch per launch in this form: call index = tile * 32 + lane
+            t.seq = lane < calls_here ? __ldg(list.seq + (static_cast<size_t>(tile) << 5) + lane) : 0ull;
+    };
+
+    TileRegs ta, tb;
+    fetch(ta);  // before the tables: the longest latency first
+
+    const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
+    griddep_launch_dependents();
+    const uint32_t lane_mod3 = lane % 3u;
+    LookupCache cache;
+    if (kSmemTable) mbar_wait(&sh.table_bar, 0);
+
+    auto consume = [&](const TileRegs& t) {
+        uint4 q[3];
+        transpose_tile_sel(lane_mod3, lane, t.ld, q);
+        if (kSideSeq) {
+            q[0].z = static_cast<uint32_t>(t.seq);
+            q[0].w = static_cast<uint32_t>(t.seq >> 32);
+        }
+        // the 1024-thread shape means a table beyond 100 KiB: thousands of services, no lookup cache
+        if ((reinterpret_cast<uintptr_t>(t.out) & 1u) == 0)
+            st_stream(t.out, dispatch_one<kSmemTable, kThreads != kMaxThreads>(img, sh, slots, cache, q[0], q[1], q[2]));
+    };
+
+    while (b < list.count) {
+        tile += gridDim.x * kWarps;
+        fetch(tb);
+        consume(ta);
+        if (b == list.count) break;
+        tile += gridDim.x * kWarps;
+        fetch(ta);
+        consume(tb);
+    }
+    griddep_wait();
+}
+
 // Bulk-staged twin of dispatch_multi_kernel: per-warp TMA ring over the tile stream of many
 // batches.  Fewer registers (more resident warps) than the LDG kernel, which pays off when the
 // method bodies are ALU-heavy (Prime.Check).
@@ -1231,6 +1349,22 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         return e ? std::atoi(e) : -1;
     }();
     const int prefetch = forced >= 0 ? forced : (img.max_conn != 0 ? 2 : 1);
+    static const bool swap = [] {
+        const char* e = std::getenv("PTYPE_B200_SWAP");
+        return e ? std::atoi(e) != 0 : false;
+    }();
+    if (swap && seq == nullptr && (plan.threads == kMaxThreads ? prefetch >= 1 : prefetch >= 2)) {
+        if (plan.threads == kMaxThreads)
+            return plan.smem_table ? launch_kernel(dispatch_multi_swap_kernel<true, kMaxThreads, 1, false>, blocks,
+                                                   plan.threads, plan.dyn_smem, stream, pdl, img, list)
+                                   : launch_kernel(dispatch_multi_swap_kernel<false, kMaxThreads, 1, false>, blocks,
+                                                   plan.threads, plan.dyn_smem, stream, pdl, img, list);
+        return plan.smem_table
+                   ? launch_kernel(dispatch_multi_swap_kernel<true, kSmallThreads, kSmallMinCtas, false>, blocks,
+                                   plan.threads, plan.dyn_smem, stream, pdl, img, list)
+                   : launch_kernel(dispatch_multi_swap_kernel<false, kSmallThreads, kSmallMinCtas, false>, blocks,
+                                   plan.threads, plan.dyn_smem, stream, pdl, img, list);
+    }
     if (seq != nullptr) {  // sequence numbers beside the records: the pipelined loop in either shape
         if (plan.threads == kMaxThreads)
             return plan.smem_table ? launch_kernel(dispatch_multi_prefetch_kernel<true, kMaxThreads, 1, true>, blocks,
