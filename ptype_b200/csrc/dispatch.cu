@@ -859,8 +859,8 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
             t.seq = lane < calls_here ? __ldg(list.seq + (static_cast<size_t>(tile) << 5) + lane) : 0ull;
     };
 
-    TileRegs ta, tb;
-    fetch(ta);  // before the tables: the longest latency first
+    TileRegs t;
+    fetch(t);  // before the tables: the longest latency first
 
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
@@ -868,26 +868,21 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     LookupCache cache;
     if (kSmemTable) mbar_wait(&sh.table_bar, 0);
 
-    auto consume = [&](const TileRegs& t) {
+    while (b < list.count) {
+        // The transpose empties the load registers, the next tile's loads go straight back into
+        // them and are in flight while this tile is dispatched.
         uint4 q[3];
         transpose_tile_sel(lane_mod3, lane, t.ld, q);
+        uint4* const out = t.out;
         if (kSideSeq) {
             q[0].z = static_cast<uint32_t>(t.seq);
             q[0].w = static_cast<uint32_t>(t.seq >> 32);
         }
+        tile += gridDim.x * kWarps;
+        fetch(t);
         // the 1024-thread shape means a table beyond 100 KiB: thousands of services, no lookup cache
-        if ((reinterpret_cast<uintptr_t>(t.out) & 1u) == 0)
-            st_stream(t.out, dispatch_one<kSmemTable, kThreads != kMaxThreads>(img, sh, slots, cache, q[0], q[1], q[2]));
-    };
-
-    while (b < list.count) {
-        tile += gridDim.x * kWarps;
-        fetch(tb);
-        consume(ta);
-        if (b == list.count) break;
-        tile += gridDim.x * kWarps;
-        fetch(ta);
-        consume(tb);
+        if ((reinterpret_cast<uintptr_t>(out) & 1u) == 0)
+            st_stream(out, dispatch_one<kSmemTable, kThreads != kMaxThreads>(img, sh, slots, cache, q[0], q[1], q[2]));
     }
     griddep_wait();
 }
