@@ -1256,7 +1256,11 @@ cudaError_t plan_dispatch(const DeviceImage& img, uint32_t flags, bool extras, L
         plan->threads = kBulkThreads;
         plan->dyn_smem = plan->table_smem + kBulkStageBytes;
     } else {
-        plan->threads = plan->table_smem > 100 * 1024 ? kMaxThreads : kSmallThreads;
+        static const size_t big_cta_kb = [] {
+            const char* e = std::getenv("PTYPE_B200_BIG_CTA_KB");
+            return e ? static_cast<size_t>(std::atoi(e)) : size_t(100);
+        }();
+        plan->threads = plan->table_smem > big_cta_kb * 1024 ? kMaxThreads : kSmallThreads;
         plan->dyn_smem = plan->table_smem;
     }
     int ctas = 0;
@@ -1325,6 +1329,14 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     const size_t resident = static_cast<size_t>(sm_count) * plan.ctas_per_sm;
     const int blocks = static_cast<int>(want < resident ? (want ? want : 1) : resident);
     const uint32_t table_smem = static_cast<uint32_t>(plan.table_smem);
+    static const size_t pad = [] {
+        const char* e = std::getenv("PTYPE_B200_PAD_SMEM");
+        return e ? static_cast<size_t>(std::atoi(e)) : size_t(0);
+    }();
+    LaunchPlan padded = plan;
+    padded.dyn_smem += pad;
+    const LaunchPlan& plan_ = padded;
+#define plan plan_
     if (plan.bulk) {
         if (plan.smem_table)
             return launch_kernel(dispatch_bulk_multi_kernel<true, kStagesDefault>, blocks, plan.threads,
@@ -1400,6 +1412,7 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
                          plan.threads, plan.dyn_smem, stream, pdl, img, list);
 }
 
+#undef plan
 namespace {
 template <bool kSmemTable, int kArgs, bool kHasSel>
 cudaError_t launch_call_batch_variant(const DeviceImage& img, const LaunchPlan& plan, int blocks,

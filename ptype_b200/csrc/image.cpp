@@ -53,7 +53,7 @@ const KnownMethod kKnownMethods[] = {
 
 // Largest slot array the dispatch kernel stages in shared memory (200 KiB of the
 // 227 KiB a CTA may use on sm_100a; the rest holds the method table and hashes).
-constexpr uint32_t kSmemSlotBudget = 200 * 1024 / sizeof(ptype_slot);
+constexpr uint32_t kSmemSlotBudget = 192 * 1024 / sizeof(ptype_slot);
 
 bool valid_name(const char* s) {
     if (!s || !*s) return false;
@@ -139,7 +139,7 @@ static int compute_placement(ptype_builder* b) {
         pl.n_slots = b->forced_slots;
     } else {
         size_t want = std::max<size_t>(8, align_up(2 * n_services, 8));
-        if (want > kSmemSlotBudget && n_services * 5 <= static_cast<size_t>(kSmemSlotBudget) * 4)
+        if (want > kSmemSlotBudget && n_services * 20 <= static_cast<size_t>(kSmemSlotBudget) * 17)
             want = kSmemSlotBudget;
         pl.n_slots = static_cast<uint32_t>(want);
     }
