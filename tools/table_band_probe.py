@@ -5,11 +5,13 @@ from which one 1024-thread CTA per SM is launched instead of several 256-thread 
 
     python tools/table_band_probe.py [n_services ...]
 """
+import os
 import sys
 import time
 
-import ptype_b200 as p
-import workloads as w
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import ptype_b200 as p  # noqa: E402
+import workloads as w  # noqa: E402
 
 
 def main():
