@@ -1256,11 +1256,16 @@ cudaError_t plan_dispatch(const DeviceImage& img, uint32_t flags, bool extras, L
         plan->threads = kBulkThreads;
         plan->dyn_smem = plan->table_smem + kBulkStageBytes;
     } else {
-        static const size_t big_cta_kb = [] {
-            const char* e = std::getenv("PTYPE_B200_BIG_CTA_KB");
-            return e ? static_cast<size_t>(std::atoi(e)) : size_t(100);
-        }();
-        plan->threads = plan->table_smem > big_cta_kb * 1024 ? kMaxThreads : kSmallThreads;
+        // Shared memory and L1 are one 256 KiB array per SM, and the streamed request loads wait in
+        // L1 until they arrive.  Once the CTAs of an SM together take more than 196 KiB of shared
+        // memory, 28 KiB of L1 are left, too little for the ~48 KiB the 32 warps keep in flight:
+        // 11.0 instead of 10.1 us per 2^20 calls (tools/table_band_probe.py).  So four 256-thread
+        // CTAs only while four copies of the table stay inside 196 KiB (8.8 us); above that one
+        // 1024-thread CTA (9.5 us for any table up to the budget, where 2 x 256 threads beside a
+        // 97 KiB table took 12.0).
+        constexpr size_t kSmemWithRoomForL1 = 196 * 1024, kPerCtaOverhead = sizeof(CtaShared) + 1024;
+        const bool four_fit = kSmallMinCtas * (plan->table_smem + kPerCtaOverhead) <= kSmemWithRoomForL1;
+        plan->threads = four_fit ? kSmallThreads : kMaxThreads;
         plan->dyn_smem = plan->table_smem;
     }
     int ctas = 0;
@@ -1329,14 +1334,6 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     const size_t resident = static_cast<size_t>(sm_count) * plan.ctas_per_sm;
     const int blocks = static_cast<int>(want < resident ? (want ? want : 1) : resident);
     const uint32_t table_smem = static_cast<uint32_t>(plan.table_smem);
-    static const size_t pad = [] {
-        const char* e = std::getenv("PTYPE_B200_PAD_SMEM");
-        return e ? static_cast<size_t>(std::atoi(e)) : size_t(0);
-    }();
-    LaunchPlan padded = plan;
-    padded.dyn_smem += pad;
-    const LaunchPlan& plan_ = padded;
-#define plan plan_
     if (plan.bulk) {
         if (plan.smem_table)
             return launch_kernel(dispatch_bulk_multi_kernel<true, kStagesDefault>, blocks, plan.threads,
@@ -1412,7 +1409,6 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
                          plan.threads, plan.dyn_smem, stream, pdl, img, list);
 }
 
-#undef plan
 namespace {
 template <bool kSmemTable, int kArgs, bool kHasSel>
 cudaError_t launch_call_batch_variant(const DeviceImage& img, const LaunchPlan& plan, int blocks,
