@@ -431,31 +431,25 @@ __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wa
 // ---- the LDG kernels' transpose.  Lane L loads 16-byte chunks L, 32+L, 64+L of the warp's 96
 // (three fully coalesced 512-byte requests); record r owns chunks 3r..3r+2.  In round c, lane s
 // feeds the lane whose record needs chunk index == s (mod 32): r = 11*(s-c) mod 32
-// (11 = 3^-1 mod 32), out of its register (3r+c)/32.
-struct TransposePlan {
-    uint32_t send_reg[3];
-};
-__device__ __forceinline__ TransposePlan transpose_plan(uint32_t lane) {
-    TransposePlan p;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        const uint32_t r = ((lane - c) * 11u) & 31u;
-        p.send_reg[c] = (3u * r + c) >> 5;
-    }
-    return p;
+// (11 = 3^-1 mod 32).  Which of its three registers a lane sends depends on the lane modulo 3
+// only: chunk 32k+s belongs to round (2k+s) mod 3, so round c sends register k = 2(c-s) mod 3,
+// which is 0 when s = c and 1 when s = c+1 (mod 3).  Written as selects: the compiler turned a
+// choice between whole uint4s into divergent branches, 64 instructions instead of 45.
+__device__ __forceinline__ uint32_t pick3(bool first, bool second, uint32_t a, uint32_t b, uint32_t c) {
+    const uint32_t bc = second ? b : c;
+    return first ? a : bc;
 }
 // ld[0..2]: what this lane loaded; q[0..2]: the 48-byte record of call (tile, lane).  12 shuffles.
-__device__ __forceinline__ void transpose_tile(const TransposePlan& p, uint32_t lane, const uint4 (&ld)[3],
+__device__ __forceinline__ void transpose_tile(uint32_t lane_mod3, uint32_t lane, const uint4 (&ld)[3],
                                                uint4 (&q)[3]) {
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        const uint32_t sr = p.send_reg[c];
-        const uint4 snd = sr == 0 ? ld[0] : (sr == 1 ? ld[1] : ld[2]);
+        const bool r0 = lane_mod3 == static_cast<uint32_t>(c), r1 = lane_mod3 == static_cast<uint32_t>((c + 1) % 3);
         const uint32_t src = (3u * lane + c) & 31u;
-        q[c].x = __shfl_sync(kFull, snd.x, src);
-        q[c].y = __shfl_sync(kFull, snd.y, src);
-        q[c].z = __shfl_sync(kFull, snd.z, src);
-        q[c].w = __shfl_sync(kFull, snd.w, src);
+        q[c].x = __shfl_sync(kFull, pick3(r0, r1, ld[0].x, ld[1].x, ld[2].x), src);
+        q[c].y = __shfl_sync(kFull, pick3(r0, r1, ld[0].y, ld[1].y, ld[2].y), src);
+        q[c].z = __shfl_sync(kFull, pick3(r0, r1, ld[0].z, ld[1].z, ld[2].z), src);
+        q[c].w = __shfl_sync(kFull, pick3(r0, r1, ld[0].w, ld[1].w, ld[2].w), src);
     }
 }
 
@@ -566,7 +560,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
 
-    const TransposePlan plan = transpose_plan(lane);
+    const uint32_t lane_mod3 = lane % 3u;
 
     const size_t n_tiles = (n + 31) >> 5;
     const size_t n_chunks = n * 3;
@@ -597,7 +591,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
             const size_t t = t0 + static_cast<size_t>(u) * total_warps;
             if (t >= n_tiles) break;  // warp-uniform
             uint4 q[3];
-            transpose_tile(plan, lane, ld[u], q);
+            transpose_tile(lane_mod3, lane, ld[u], q);
             const size_t idx = (t << 5) + lane;
             const bool live = idx < n;
             uint4 out = make_uint4(0, 0, 0, 0);
@@ -642,7 +636,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
 
-    const TransposePlan plan = transpose_plan(lane);
+    const uint32_t lane_mod3 = lane % 3u;
     const uint32_t total_tiles = list.tile_end[list.count - 1];
     const uint32_t total_warps = gridDim.x * warps_per_cta;
     const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
@@ -683,7 +677,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         for (int u = 0; u < kUnroll; ++u) {
             if (g0 + u * total_warps >= total_tiles) break;  // warp-uniform
             uint4 q[3];
-            transpose_tile(plan, lane, ld[u], q);
+            transpose_tile(lane_mod3, lane, ld[u], q);
             const int b = cursor[u];
             const size_t idx = (static_cast<size_t>(tile[u]) << 5) + lane;
             if (idx < list.n[b])
@@ -694,114 +688,17 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     griddep_wait();
 }
 
-// Software-pipelined form of dispatch_multi_kernel: a warp holds ONE tile at a time and has the
-// loads of its next tile in flight while it works on the current one.  With the 32 warps of a
-// 1024-thread CTA (the shape a >100 KiB staged table forces: one CTA per SM, 64 registers per
-// thread) the unrolled kernel above spent 29 % of its warp-time at the first use of a loaded
-// register (profiles/r02_c3_multi_source.csv): a warp's loads were in flight only while it waited
-// for them.  Here they are in flight during the ~260 instructions of the previous tile as well,
-// for the same 24 registers of load targets.
-template <bool kSmemTable, int kThreads, int kMinCtas, bool kSideSeq>
-__global__ void __launch_bounds__(kThreads, kMinCtas)
-    dispatch_multi_prefetch_kernel(const DeviceImage img, const __grid_constant__ BatchList list) {
-    extern __shared__ __align__(128) unsigned char dyn_smem[];
-    __shared__ __align__(16) CtaShared sh;
-
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t warps_per_cta = blockDim.x >> 5;
-    const uint32_t total_tiles = list.tile_end[list.count - 1];
-    const uint32_t total_warps = gridDim.x * warps_per_cta;
-    const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
-
-    int cursor = 0;  // batch of the tile being fetched; a warp's tiles only move forward
-    // where a tile lies: its batch and its index inside the batch; issues its three loads
-    auto fetch = [&](uint32_t g, int& b, uint32_t& tile, uint4 (&ld)[3], unsigned long long& sq) {
-        b = cursor;
-        while (g >= list.tile_end[b]) ++b;
-        cursor = b;
-        tile = g - (b ? list.tile_end[b - 1] : 0u);
-        // all tiles of a batch but (perhaps) its last are whole: one 64-bit address, three loads
-        // at constant offsets, nothing to compare or clear
-        const uint32_t calls = list.n[b];
-        const uint4* at = list.reqs[b] + static_cast<size_t>(tile) * 96 + lane;
-        if (tile < (calls >> 5)) {
-#pragma unroll
-            for (int j = 0; j < 3; ++j) ld[j] = ld_stream(at + j * 32);
-        } else {
-            const uint32_t chunks_here = (calls & 31u) * 3u;  // 16-byte chunks of the short last tile
-#pragma unroll
-            for (int j = 0; j < 3; ++j)
-                ld[j] = j * 32 + lane < chunks_here ? ld_stream(at + j * 32) : make_uint4(0, 0, 0, 0);
-        }
-        if (kSideSeq) {  // one batch per launch in this form: call index = tile * 32 + lane
-            const size_t j = (static_cast<size_t>(tile) << 5) + lane;
-            sq = j < list.n[0] ? __ldg(list.seq + j) : 0ull;
-        }
-    };
-
-    uint4 nxt[3];
-    int nxt_b = 0;
-    uint32_t nxt_tile = 0;
-    unsigned long long nxt_seq = 0;
-    uint32_t g = warp_global;
-    if (g < total_tiles) fetch(g, nxt_b, nxt_tile, nxt, nxt_seq);  // before the tables: the longest latency first
-
-    const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
-    griddep_launch_dependents();
-    const TransposePlan plan = transpose_plan(lane);
-    LookupCache cache;
-    if (kSmemTable) mbar_wait(&sh.table_bar, 0);
-
-    while (g < total_tiles) {
-        uint4 cur[3] = {nxt[0], nxt[1], nxt[2]};
-        const int b = nxt_b;
-        const uint32_t tile = nxt_tile;
-        const unsigned long long seq = nxt_seq;
-        g += total_warps;
-        if (g < total_tiles) fetch(g, nxt_b, nxt_tile, nxt, nxt_seq);
-        uint4 q[3];
-        transpose_tile(plan, lane, cur, q);
-        if (kSideSeq) {
-            q[0].z = static_cast<uint32_t>(seq);
-            q[0].w = static_cast<uint32_t>(seq >> 32);
-        }
-        // the 1024-thread shape means a table beyond 100 KiB: thousands of services, no lookup cache
-        const uint32_t calls = list.n[b];
-        if (tile < (calls >> 5) || lane < (calls & 31u))
-            st_stream(list.replies[b] + (static_cast<size_t>(tile) << 5) + lane,
-                      dispatch_one<kSmemTable, kThreads != kMaxThreads>(img, sh, slots, cache, q[0], q[1], q[2]));
-    }
-    griddep_wait();
-}
-
-// The same pipeline with fewer instructions per tile (C3 spent 242 on a tile, a third of them moving
-// data around rather than dispatching).  Three cuts:
-//   * two register sets that swap roles every tile instead of one copied into the other;
-//   * what a warp needs to know about its current batch (tile range, request and reply base with
-//     the lane's offset folded in) lives in registers and changes only when the warp crosses into
-//     another batch, ~7 tiles apart - no constant-bank table walk per tile;
-//   * the sender-side register choice of the transpose as selects, not divergent branches.
-// The reply address is made when the tile is fetched; its bit 0 marks a lane beyond the batch's end.
-__device__ __forceinline__ uint32_t pick3(bool first, bool second, uint32_t a, uint32_t b, uint32_t c) {
-    const uint32_t bc = second ? b : c;
-    return first ? a : bc;
-}
-// Same data movement as transpose_tile.  The register a lane sends in round c depends on the lane
-// modulo 3 only: chunk 32k+s belongs to round (2k+s) mod 3, so round c sends register
-// k = 2(c-s) mod 3, which is 0 when s = c and 1 when s = c+1 (mod 3).
-__device__ __forceinline__ void transpose_tile_sel(uint32_t lane_mod3, uint32_t lane, const uint4 (&ld)[3],
-                                                   uint4 (&q)[3]) {
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        const bool r0 = lane_mod3 == static_cast<uint32_t>(c), r1 = lane_mod3 == static_cast<uint32_t>((c + 1) % 3);
-        const uint32_t src = (3u * lane + c) & 31u;
-        q[c].x = __shfl_sync(kFull, pick3(r0, r1, ld[0].x, ld[1].x, ld[2].x), src);
-        q[c].y = __shfl_sync(kFull, pick3(r0, r1, ld[0].y, ld[1].y, ld[2].y), src);
-        q[c].z = __shfl_sync(kFull, pick3(r0, r1, ld[0].z, ld[1].z, ld[2].z), src);
-        q[c].w = __shfl_sync(kFull, pick3(r0, r1, ld[0].w, ld[1].w, ld[2].w), src);
-    }
-}
-
+// Software-pipelined form of dispatch_multi_kernel: a warp holds ONE tile at a time.  The transpose
+// empties the three load registers into the lane's own record, the next tile's loads go straight
+// back into them and are in flight while this tile is dispatched.  With the 32 warps of a
+// 1024-thread CTA the unrolled kernel above spent 29 % of its warp-time at the first use of a loaded
+// register (profiles/r02_c3_multi_unrolled_sass_top.txt): its loads were in flight only while the
+// warp waited for them.
+// What a warp needs to know about its current batch (whole tiles, request and reply base with the
+// lane's offset folded in) lives in registers and changes only when the warp crosses into another
+// batch, ~7 tiles apart - no constant-bank table walk per tile.  The reply address is made when the
+// tile is fetched; its bit 0 marks a lane beyond the batch's end.  192 instructions per tile on C3
+// (the first pipelined form, which copied one register set into another: 242).
 struct TileRegs {
     uint4 ld[3];
     uint4* out;              // this lane's reply record; bit 0 set: no call behind this lane
@@ -810,7 +707,7 @@ struct TileRegs {
 
 template <bool kSmemTable, int kThreads, int kMinCtas, bool kSideSeq>
 __global__ void __launch_bounds__(kThreads, kMinCtas)
-    dispatch_multi_swap_kernel(const DeviceImage img, const __grid_constant__ BatchList list) {
+    dispatch_multi_prefetch_kernel(const DeviceImage img, const __grid_constant__ BatchList list) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ __align__(16) CtaShared sh;
 
@@ -872,7 +769,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         // The transpose empties the load registers, the next tile's loads go straight back into
         // them and are in flight while this tile is dispatched.
         uint4 q[3];
-        transpose_tile_sel(lane_mod3, lane, t.ld, q);
+        transpose_tile(lane_mod3, lane, t.ld, q);
         uint4* const out = t.out;
         if (kSideSeq) {
             q[0].z = static_cast<uint32_t>(t.seq);
@@ -880,7 +777,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         }
         tile += gridDim.x * kWarps;
         fetch(t);
-        // the 1024-thread shape means a table beyond 100 KiB: thousands of services, no lookup cache
+        // the 1024-thread shape means a table beyond 45 KiB: over a thousand services, no lookup cache
         if ((reinterpret_cast<uintptr_t>(out) & 1u) == 0)
             st_stream(out, dispatch_one<kSmemTable, kThreads != kMaxThreads>(img, sh, slots, cache, q[0], q[1], q[2]));
     }
@@ -1353,22 +1250,6 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         return e ? std::atoi(e) : -1;
     }();
     const int prefetch = forced >= 0 ? forced : (img.max_conn != 0 ? 2 : 1);
-    static const bool swap = [] {
-        const char* e = std::getenv("PTYPE_B200_SWAP");
-        return e ? std::atoi(e) != 0 : false;
-    }();
-    if (swap && seq == nullptr && (plan.threads == kMaxThreads ? prefetch >= 1 : prefetch >= 2)) {
-        if (plan.threads == kMaxThreads)
-            return plan.smem_table ? launch_kernel(dispatch_multi_swap_kernel<true, kMaxThreads, 1, false>, blocks,
-                                                   plan.threads, plan.dyn_smem, stream, pdl, img, list)
-                                   : launch_kernel(dispatch_multi_swap_kernel<false, kMaxThreads, 1, false>, blocks,
-                                                   plan.threads, plan.dyn_smem, stream, pdl, img, list);
-        return plan.smem_table
-                   ? launch_kernel(dispatch_multi_swap_kernel<true, kSmallThreads, kSmallMinCtas, false>, blocks,
-                                   plan.threads, plan.dyn_smem, stream, pdl, img, list)
-                   : launch_kernel(dispatch_multi_swap_kernel<false, kSmallThreads, kSmallMinCtas, false>, blocks,
-                                   plan.threads, plan.dyn_smem, stream, pdl, img, list);
-    }
     if (seq != nullptr) {  // sequence numbers beside the records: the pipelined loop in either shape
         if (plan.threads == kMaxThreads)
             return plan.smem_table ? launch_kernel(dispatch_multi_prefetch_kernel<true, kMaxThreads, 1, true>, blocks,

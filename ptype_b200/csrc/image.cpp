@@ -51,8 +51,10 @@ const KnownMethod kKnownMethods[] = {
     {"Prime", 1, "Check", PTYPE_OP_CHECK},
 };
 
-// Largest slot array the dispatch kernel stages in shared memory (200 KiB of the
-// 227 KiB a CTA may use on sm_100a; the rest holds the method table and hashes).
+// Largest slot array the builder sizes for staging in shared memory: 192 KiB.  With the method
+// table and hashes the CTA then stays inside 196 KiB, the largest carve-out that leaves the SM
+// 60 KiB of L1 for the request loads in flight (a 200 KiB table leaves 28 KiB and cost C3 10 %,
+// see plan_dispatch in dispatch.cu).
 constexpr uint32_t kSmemSlotBudget = 192 * 1024 / sizeof(ptype_slot);
 
 bool valid_name(const char* s) {
@@ -129,7 +131,7 @@ static int compute_placement(ptype_builder* b) {
     }
 
     // Table size: half full when that fits the shared-memory budget, otherwise
-    // fill the budget (up to 80 % load: 3-way cuckoo places that reliably), otherwise
+    // fill the budget (up to 85 % load: 3-way cuckoo places that reliably), otherwise
     // a half-full table probed in L2.
     if (b->forced_slots) {
         // 3-way cuckoo hashing stops placing reliably a little above 90 % load

@@ -133,11 +133,14 @@ def test_table_sizing():
 
 
 def test_stress_image_fits_shared_memory_budget():
-    """C3's 10 000 services get a 12 800-slot (200 KiB) table: the size the kernel stages."""
+    """C3's 10 000 services get a 12 288-slot (192 KiB) table: staged in shared memory, and small
+    enough to leave the SM 60 KiB of L1 beside it.  10 444 services is the most that size takes."""
     spec = w.stress_registry(10_000, 1)
     img = spec.image()
-    assert img.header.n_slots == 12_800 and img.header.n_services == 10_000
-    assert img.header.n_slots * 16 <= 200 * 1024
+    assert img.header.n_slots == 12_288 and img.header.n_services == 10_000
+    assert w.stress_registry(10_444, 1).image().header.n_slots == 12_288
+    assert w.stress_registry(10_445, 1).image().header.n_slots == 2 * 10_448    # probed in L2
+    assert w.stress_registry(6_144, 1).image().header.n_slots == 12_288
 
 
 def slot_candidates(key: np.ndarray, seed: int, n_slots: int) -> np.ndarray:
