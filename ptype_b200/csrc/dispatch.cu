@@ -431,17 +431,46 @@ __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wa
 // ---- the LDG kernels' transpose.  Lane L loads 16-byte chunks L, 32+L, 64+L of the warp's 96
 // (three fully coalesced 512-byte requests); record r owns chunks 3r..3r+2.  In round c, lane s
 // feeds the lane whose record needs chunk index == s (mod 32): r = 11*(s-c) mod 32
-// (11 = 3^-1 mod 32).  Which of its three registers a lane sends depends on the lane modulo 3
-// only: chunk 32k+s belongs to round (2k+s) mod 3, so round c sends register k = 2(c-s) mod 3,
-// which is 0 when s = c and 1 when s = c+1 (mod 3).  Written as selects: the compiler turned a
-// choice between whole uint4s into divergent branches, 64 instructions instead of 45.
+// (11 = 3^-1 mod 32), out of its register (3r+c)/32.
+struct TransposePlan {
+    uint32_t send_reg[3];
+};
+__device__ __forceinline__ TransposePlan transpose_plan(uint32_t lane) {
+    TransposePlan p;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const uint32_t r = ((lane - c) * 11u) & 31u;
+        p.send_reg[c] = (3u * r + c) >> 5;
+    }
+    return p;
+}
+// ld[0..2]: what this lane loaded; q[0..2]: the 48-byte record of call (tile, lane).  12 shuffles.
+__device__ __forceinline__ void transpose_tile(const TransposePlan& p, uint32_t lane, const uint4 (&ld)[3],
+                                               uint4 (&q)[3]) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const uint32_t sr = p.send_reg[c];
+        const uint4 snd = sr == 0 ? ld[0] : (sr == 1 ? ld[1] : ld[2]);
+        const uint32_t src = (3u * lane + c) & 31u;
+        q[c].x = __shfl_sync(kFull, snd.x, src);
+        q[c].y = __shfl_sync(kFull, snd.y, src);
+        q[c].z = __shfl_sync(kFull, snd.z, src);
+        q[c].w = __shfl_sync(kFull, snd.w, src);
+    }
+}
+
+// The same data movement with the sender's choice written as selects.  Which register a lane
+// sends depends on the lane modulo 3 only: chunk 32k+s belongs to round (2k+s) mod 3, so round c
+// sends register k = 2(c-s) mod 3, which is 0 when s = c and 1 when s = c+1 (mod 3).  45
+// instructions where the form above compiles to divergent branches around whole-uint4 moves (64),
+// and one register of state instead of three.  The pipelined loop uses it; in the unrolled loops
+// it measured slower (mesh image, 2000 batches: 9.97 vs 9.06 us per batch), so they keep the other.
 __device__ __forceinline__ uint32_t pick3(bool first, bool second, uint32_t a, uint32_t b, uint32_t c) {
     const uint32_t bc = second ? b : c;
     return first ? a : bc;
 }
-// ld[0..2]: what this lane loaded; q[0..2]: the 48-byte record of call (tile, lane).  12 shuffles.
-__device__ __forceinline__ void transpose_tile(uint32_t lane_mod3, uint32_t lane, const uint4 (&ld)[3],
-                                               uint4 (&q)[3]) {
+__device__ __forceinline__ void transpose_tile_sel(uint32_t lane_mod3, uint32_t lane, const uint4 (&ld)[3],
+                                                   uint4 (&q)[3]) {
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
         const bool r0 = lane_mod3 == static_cast<uint32_t>(c), r1 = lane_mod3 == static_cast<uint32_t>((c + 1) % 3);
@@ -560,7 +589,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
 
-    const uint32_t lane_mod3 = lane % 3u;
+    const TransposePlan plan = transpose_plan(lane);
 
     const size_t n_tiles = (n + 31) >> 5;
     const size_t n_chunks = n * 3;
@@ -591,7 +620,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
             const size_t t = t0 + static_cast<size_t>(u) * total_warps;
             if (t >= n_tiles) break;  // warp-uniform
             uint4 q[3];
-            transpose_tile(lane_mod3, lane, ld[u], q);
+            transpose_tile(plan, lane, ld[u], q);
             const size_t idx = (t << 5) + lane;
             const bool live = idx < n;
             uint4 out = make_uint4(0, 0, 0, 0);
@@ -636,7 +665,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
     const ptype_slot* slots = stage_tables<kSmemTable>(img, sh, dyn_smem);
     griddep_launch_dependents();
 
-    const uint32_t lane_mod3 = lane % 3u;
+    const TransposePlan plan = transpose_plan(lane);
     const uint32_t total_tiles = list.tile_end[list.count - 1];
     const uint32_t total_warps = gridDim.x * warps_per_cta;
     const uint32_t warp_global = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
@@ -677,7 +706,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         for (int u = 0; u < kUnroll; ++u) {
             if (g0 + u * total_warps >= total_tiles) break;  // warp-uniform
             uint4 q[3];
-            transpose_tile(lane_mod3, lane, ld[u], q);
+            transpose_tile(plan, lane, ld[u], q);
             const int b = cursor[u];
             const size_t idx = (static_cast<size_t>(tile[u]) << 5) + lane;
             if (idx < list.n[b])
@@ -769,7 +798,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         // The transpose empties the load registers, the next tile's loads go straight back into
         // them and are in flight while this tile is dispatched.
         uint4 q[3];
-        transpose_tile(lane_mod3, lane, t.ld, q);
+        transpose_tile_sel(lane_mod3, lane, t.ld, q);
         uint4* const out = t.out;
         if (kSideSeq) {
             q[0].z = static_cast<uint32_t>(t.seq);

@@ -128,10 +128,10 @@ def stress(oracle):
 
 @pytest.mark.parametrize("zipf", [False, True])
 def test_c3_registry_stress(ctx, stress, oracle, zipf):
-    """BASELINE config 3: 10k services x 64 nodes (12 800-slot table staged in shared
+    """BASELINE config 3: 10k services x 64 nodes (12 288-slot table staged in shared
     memory), 2^22 routed calls compared in full; 1 % name an unregistered service."""
     spec, img, snap, _ = stress
-    assert img.header.n_slots == 12_800
+    assert img.header.n_slots == 12_288
     ctx.publish(img)
     n = 1 << 22
     req = w.stress_calls(n, 10_000, zipf=zipf)
@@ -535,7 +535,7 @@ def test_call_batch_values_only(ctx, oracle, kind):
 
 
 def test_call_batch_against_the_big_table(ctx, stress, oracle):
-    """The compact form with the 12 800-slot table staged in shared memory (1024-thread CTAs)."""
+    """The compact form with the 12 288-slot table staged in shared memory (1024-thread CTAs)."""
     spec, img, snap, _ = stress
     ctx.publish(img)
     n = 500_000

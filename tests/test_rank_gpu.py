@@ -62,7 +62,7 @@ def test_single_service_batch_counts_from_one(rctx, oracle):
 
 @pytest.mark.parametrize("n", [0, 1, 31, 32, 33, 255, 256, 257, 5000, 1 << 18])
 def test_stress_registry_ragged_sizes(stress, n):
-    """C3 registry (10 000 services, 12 800 slots): uniform services, 1 % unregistered."""
+    """C3 registry (10 000 services, 12 288 slots): uniform services, 1 % unregistered."""
     spec, img, kv, snap = stress
     with p.Context([0]) as ctx:          # counters start at zero, like the oracle's
         ctx.publish(img)
