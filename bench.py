@@ -938,7 +938,9 @@ def main():
                          "frac": m["achieved_gbs"] / m["peak"], "traffic": traffic, "traffic_note": traffic_note,
                          "peak_kind": m["peak_kind"],
                          "kernel": "dispatch_kernel (one launch per batch)" if (args.flags & 32) else
-                                   "dispatch_multi_kernel (one persistent launch per 96 batches)",
+                                   ("dispatch_multi_kernel" if args.workload == "c2mesh" else
+                                    "c4" == args.workload and "dispatch_bulk_multi_kernel" or
+                                    "dispatch_multi_prefetch_kernel") + " (one persistent launch per <= 96 batches)",
                          "algorithmic_bytes_per_call": BYTES_PER_CALL,
                          "frac_of_nominal_8TBs": m["achieved_gbs"] / 8000.0},
             "e2e": e2e["values"] if e2e["values"] is not None else e2e["records"],
