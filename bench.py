@@ -45,6 +45,8 @@ BYTES_PER_CALL = 64  # 48 B request + 16 B reply
 BATCH_OF = {"c2": 1 << 20, "c2mesh": 1 << 20, "c3": 1 << 24, "c4": 1 << 20, "c5": 1 << 20}
 BUFFERS_OF = {"c2": 8, "c2mesh": 8, "c3": 2, "c4": 8, "c5": 8}
 U64 = (1 << 64) - 1
+# the kernel dispatch_batches launches per workload (launch_dispatch_multi in csrc/dispatch.cu picks by image)
+TIMED_KERNEL = {"c2mesh": "dispatch_multi_kernel", "c4": "dispatch_bulk_multi_kernel"}
 
 
 def measured_peak():
@@ -938,9 +940,8 @@ def main():
                          "frac": m["achieved_gbs"] / m["peak"], "traffic": traffic, "traffic_note": traffic_note,
                          "peak_kind": m["peak_kind"],
                          "kernel": "dispatch_kernel (one launch per batch)" if (args.flags & 32) else
-                                   ("dispatch_multi_kernel" if args.workload == "c2mesh" else
-                                    "c4" == args.workload and "dispatch_bulk_multi_kernel" or
-                                    "dispatch_multi_prefetch_kernel") + " (one persistent launch per <= 96 batches)",
+                                   TIMED_KERNEL.get(args.workload, "dispatch_multi_prefetch_kernel") +
+                                   " (one persistent launch per <= 96 batches)",
                          "algorithmic_bytes_per_call": BYTES_PER_CALL,
                          "frac_of_nominal_8TBs": m["achieved_gbs"] / 8000.0},
             "e2e": e2e["values"] if e2e["values"] is not None else e2e["records"],
