@@ -445,6 +445,47 @@ def test_dispatch_batches_equals_one_by_one(ctx, oracle):
         b.free()
 
 
+@pytest.mark.parametrize("shape", ["pipelined_256", "unrolled_mesh", "pipelined_1024"])
+def test_ragged_batch_lists_in_every_multi_batch_loop(ctx, oracle, shape):
+    """130 batches (more than one launch holds) of 0..40, 32k+1 and odd sizes, all carved out of ONE
+    request buffer and ONE reply buffer with 16 guard bytes between neighbours: every loop of the
+    multi-batch kernel has to find each batch's tiles, stop at its last call and leave the bytes
+    between the reply regions alone."""
+    if shape == "pipelined_256":
+        spec, n_services = w.calculator_registry(), None
+    elif shape == "unrolled_mesh":
+        spec, n_services = w.calculator_registry(mesh=True), None
+    else:
+        spec, n_services = w.stress_registry(2000, 5), 2000      # 62 KiB table: one 1024-thread CTA per SM
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    rng = np.random.default_rng(7)
+    sizes = [int(x) for x in rng.integers(0, 41, size=100)] + [32, 64, 31, 33, 1, 0, 4096 + 1, 32 * 1024 + 1,
+                                                              100_003, 65_536] + [int(x) for x in rng.integers(1, 3000, size=20)]
+    assert len(sizes) == 130
+    reqs = [w.stress_calls(n, n_services, seed=40 + i) if n_services else w.calculator_calls(n, seed=40 + i, seq_base=i)
+            for i, n in enumerate(sizes)]
+    total = sum(sizes)
+    d_req = ctx.device_buffer(total * 48 + 48).upload(np.concatenate(reqs))
+    guard = 16
+    rep_off = np.cumsum([0] + [n * 16 + guard for n in sizes])
+    d_rep = ctx.device_buffer(int(rep_off[-1]) + 16)
+    poison = np.full(int(rep_off[-1]) + 16, 0xAB, dtype=np.uint8)
+    req_off = np.cumsum([0] + [n * 48 for n in sizes])
+    triples = [(d_req.ptr + int(req_off[i]), d_rep.ptr + int(rep_off[i]), n) for i, n in enumerate(sizes)]
+    want = [snap.dispatch(r) for r in reqs]
+    for flags in (0, p.F_ONE_LAUNCH_PER_BATCH):
+        d_rep.upload(poison)
+        ctx.dispatch_batches(ctx.make_batches(triples), flags=flags)
+        got = d_rep.download(np.uint8, len(poison))
+        for i, n in enumerate(sizes):
+            lo = int(rep_off[i])
+            assert got[lo:lo + n * 16].tobytes() == want[i].tobytes(), (shape, flags, i, n)
+            assert (got[lo + n * 16:lo + n * 16 + guard] == 0xAB).all(), (shape, flags, i, n)
+    d_req.free()
+    d_rep.free()
+
+
 @pytest.mark.parametrize("n", [1, 33, 4097, 128 * 1024 + 1, 1 << 20])
 @pytest.mark.parametrize("seq_base", [0, (1 << 32) - 7, (1 << 63) - 5])
 def test_call_batch_compact_form(ctx, oracle, n, seq_base):
