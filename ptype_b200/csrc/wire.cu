@@ -181,7 +181,40 @@ __global__ void __launch_bounds__(kWireThreads)
         }
         uint32_t n = 0;
         if (lane == 0) {
-            c.pos = next_pos;
+            // The usual message, walked in 32-bit offsets from the window's base: a one-byte length,
+            // a type id of one byte or of FF + one byte (ids 64..127: every user type of a
+            // connection), all inside the window.  Three independent shared-memory bytes and ~25
+            // instructions per message; anything else - and the stream's end - goes to next_call,
+            // from the start of the call in progress.  This loop is the decoder's cost: it runs on
+            // one lane of 32.
+            const uint64_t span = c.end - c.wbase;
+            const uint32_t lim = span > 0xFFFFFFFFull ? 0xFFFFFFFFu : static_cast<uint32_t>(span);
+            const uint8_t* const win = s_window[warp];
+            uint32_t off = static_cast<uint32_t>(next_pos - c.wbase), call_off = off, hdr_v = 0, hdr_e = 0;
+            bool have = false;
+            while (n < 32 && off + 12 <= c.wlen) {
+                const uint32_t b0 = win[off], b1 = win[off + 1], b2 = win[off + 2];
+                const bool wide = b1 >= 128;
+                const uint32_t id_bytes = wide ? 2u : 1u, last = wide ? b2 : b1;
+                const uint32_t next = off + 1 + b0;
+                if (b0 >= 128 || (wide && b1 != 0xFFu) || id_bytes > b0 || next > lim) break;
+                if (!(last & 1u)) {  // a value, not a type definition
+                    const uint32_t value = off + 1 + id_bytes;
+                    if (!have) {
+                        hdr_v = value;
+                        hdr_e = next;
+                        have = true;
+                    } else {
+                        if (!kCount)
+                            s_framed[warp][n] = Framed{c.wbase + hdr_v, c.wbase + hdr_e, c.wbase + value, c.wbase + next};
+                        ++n;
+                        have = false;
+                        call_off = next;
+                    }
+                }
+                off = next;
+            }
+            c.pos = c.wbase + call_off;
             Framed f;
             while (n < 32 && next_call(c, f)) s_framed[warp][n++] = f;
             next_pos = c.pos;
