@@ -347,12 +347,14 @@ struct WireTypes {
 };
 
 // kSize: only the byte count of every stream (out_off[s]); else the bytes at out_off[s].
+constexpr uint32_t kEncodeStage = 3072;  // bytes of one 32-call chunk assembled in shared memory
 template <bool kSize>
 __global__ void __launch_bounds__(kWireThreads)
     wire_encode_kernel(const uint8_t* __restrict__ req_bytes, const unsigned long long* __restrict__ call_off,
                        const size_t n_streams, const ptype_wire_call* __restrict__ calls,
                        const ptype_reply* __restrict__ replies, const WireTypes types, uint8_t* __restrict__ state,
                        unsigned long long* __restrict__ out_off, uint8_t* __restrict__ out) {
+    __shared__ __align__(16) uint8_t s_stage[kSize ? 1 : kWireThreads / 32][kSize ? 16 : kEncodeStage];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const size_t s = static_cast<size_t>(blockIdx.x) * (kWireThreads / 32) + warp;
     if (s >= n_streams) return;
@@ -391,39 +393,61 @@ __global__ void __launch_bounds__(kWireThreads)
             if (lane >= static_cast<uint32_t>(o)) incl += t;
         }
         const uint32_t chunk_total = __shfl_sync(kFull, incl, 31);
-        if (!kSize && live) {
-            uint8_t* p = out + at + (incl - total);
-            if (def_response)
-                for (uint32_t k = 0; k < types.response_def_len; ++k) *p++ = __ldg(types.defs + k);
-            // Response{ServiceMethod, Seq, Error}
-            put_uint(p, hdr_body);
-            put_uint(p, zigzag(types.response_id));
-            *p++ = 1;
-            put_uint(p, wc.sm_len);
-            for (uint32_t k = 0; k < wc.sm_len; ++k) *p++ = __ldg(req_bytes + wc.sm_off + k);
-            if (wc.rpc_seq) {
+        if (!kSize) {
+            // The chunk's bytes are contiguous in the stream (~36 per call).  They are assembled in
+            // shared memory at the output's own 16-byte phase and leave as 16-byte stores, one run
+            // per warp; written straight to global memory each lane's single-byte stores scattered
+            // over 32 sectors per instruction.  A chunk too long for the stage (long method names
+            // or error texts) still goes the direct way.
+            uint8_t* const dst = out + at;
+            const uint32_t phase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(dst) & 15u);
+            const bool staged = chunk_total + phase <= kEncodeStage;  // warp-uniform
+            if (live) {
+                uint8_t* p = (staged ? s_stage[warp] + phase : dst) + (incl - total);
+                if (def_response)
+                    for (uint32_t k = 0; k < types.response_def_len; ++k) *p++ = __ldg(types.defs + k);
+                // Response{ServiceMethod, Seq, Error}
+                put_uint(p, hdr_body);
+                put_uint(p, zigzag(types.response_id));
                 *p++ = 1;
-                put_uint(p, wc.rpc_seq);
-            }
-            if (failed) {
-                *p++ = wc.rpc_seq ? 1 : 2;
-                put_uint(p, err_len);
-                for (uint32_t k = 0; k < et.len; ++k) *p++ = static_cast<uint8_t>(et.text[k]);
-                if (et.with_method)
-                    for (uint32_t k = 0; k < wc.sm_len; ++k) *p++ = __ldg(req_bytes + wc.sm_off + k);
-            }
-            *p++ = 0;
-            // the reply value, or net/rpc's invalidRequest (struct{}{}) behind an error
-            if (def_empty)
-                for (uint32_t k = 0; k < types.empty_def_len; ++k) *p++ = __ldg(types.defs + types.response_def_len + k);
-            put_uint(p, val_body);
-            if (failed) {
-                put_uint(p, zigzag(types.empty_id));
+                put_uint(p, wc.sm_len);
+                for (uint32_t k = 0; k < wc.sm_len; ++k) *p++ = __ldg(req_bytes + wc.sm_off + k);
+                if (wc.rpc_seq) {
+                    *p++ = 1;
+                    put_uint(p, wc.rpc_seq);
+                }
+                if (failed) {
+                    *p++ = wc.rpc_seq ? 1 : 2;
+                    put_uint(p, err_len);
+                    for (uint32_t k = 0; k < et.len; ++k) *p++ = static_cast<uint8_t>(et.text[k]);
+                    if (et.with_method)
+                        for (uint32_t k = 0; k < wc.sm_len; ++k) *p++ = __ldg(req_bytes + wc.sm_off + k);
+                }
                 *p++ = 0;
-            } else {
-                *p++ = 0x04;  // type id 2 (int)
-                *p++ = 0x00;  // top-level non-struct marker
-                put_uint(p, zz);
+                // the reply value, or net/rpc's invalidRequest (struct{}{}) behind an error
+                if (def_empty)
+                    for (uint32_t k = 0; k < types.empty_def_len; ++k) *p++ = __ldg(types.defs + types.response_def_len + k);
+                put_uint(p, val_body);
+                if (failed) {
+                    put_uint(p, zigzag(types.empty_id));
+                    *p++ = 0;
+                } else {
+                    *p++ = 0x04;  // type id 2 (int)
+                    *p++ = 0x00;  // top-level non-struct marker
+                    put_uint(p, zz);
+                }
+            }
+            if (staged) {
+                __syncwarp();
+                const uint8_t* const src = s_stage[warp] + phase;
+                const uint32_t head = chunk_total < ((16u - phase) & 15u) ? chunk_total : ((16u - phase) & 15u);
+                const uint32_t body = (chunk_total - head) & ~15u;
+                if (lane < head) dst[lane] = src[lane];
+                for (uint32_t o = lane * 16; o < body; o += 32 * 16)
+                    *reinterpret_cast<uint4*>(dst + head + o) = *reinterpret_cast<const uint4*>(src + head + o);
+                const uint32_t tail_at = head + body;
+                if (tail_at + lane < chunk_total) dst[tail_at + lane] = src[tail_at + lane];
+                __syncwarp();  // the stage is free for the next chunk
             }
         }
         at += chunk_total;
