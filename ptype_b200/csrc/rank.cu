@@ -296,6 +296,20 @@ __global__ void __launch_bounds__(kScanThreads)
 // kScatter: write ptype_req.seq of the records; else a plain array seq_out[j].
 constexpr int kAssignThreads = 256;
 constexpr int kAssignDepth = 8;
+#ifndef PTYPE_RANK_MATCH_BALLOT
+#define PTYPE_RANK_MATCH_BALLOT 0
+#endif
+// Lanes of the warp that name the same slot, by one ballot per bit of the slot id.
+__device__ __forceinline__ uint32_t match_slots(uint32_t slot, uint32_t lane, uint32_t bits) {
+    const bool live = slot != kNoSlot;
+    uint32_t peers = __ballot_sync(kFull, live);
+    for (uint32_t b = 0; b < bits; ++b) {
+        const bool one = (slot >> b) & 1u;
+        const uint32_t vote = __ballot_sync(kFull, one);
+        peers &= one ? vote : ~vote;
+    }
+    return live ? peers : 1u << lane;
+}
 template <bool kScatter>
 __global__ void __launch_bounds__(kAssignThreads)
     rank_assign_kernel(const uint32_t n_slots, const uint32_t* __restrict__ ids, ptype_req* __restrict__ reqs,
@@ -309,6 +323,7 @@ __global__ void __launch_bounds__(kAssignThreads)
     const size_t lo = static_cast<size_t>(blockIdx.x) * chunk;
     const size_t hi = lo + chunk < n ? lo + chunk : n;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t slot_bits = 32u - __clz(n_slots - 1u);
     constexpr size_t kTrip = static_cast<size_t>(kAssignThreads) * kAssignDepth;
     const size_t lane_off = static_cast<size_t>(warp) * kAssignDepth * 32 + lane;
     for (size_t base = lo; base < hi; base += kTrip) {  // uniform trip count per CTA
@@ -326,7 +341,11 @@ __global__ void __launch_bounds__(kAssignThreads)
 #pragma unroll
         for (int r = 0; r < kAssignDepth; ++r) {
             // calls of one service inside a tile of 32: lanes in `peers`, in batch order
+#if PTYPE_RANK_MATCH_BALLOT
+            peers[r] = match_slots(at[r], lane, slot_bits);
+#else
             peers[r] = __match_any_sync(kFull, at[r] != kNoSlot ? at[r] : 0x80000000u + lane);
+#endif
             first[r] = 0;
         }
         for (uint32_t w = 0; w < kAssignThreads / 32; ++w) {
