@@ -36,6 +36,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdlib>
+
 #include "../../include/ptype_b200.h"
 #include "device_image.h"
 #include "table_hash.h"
@@ -382,6 +384,133 @@ __global__ void __launch_bounds__(kAssignThreads)
     }
 }
 
+// The same pass without turns.  The running counts of two different slots never meet, so the
+// slots are split into eight classes (slot & 7) and warp k of the CTA owns class k: nobody waits
+// for anybody else's turn.  Per trip of 2048 records:
+//   1. every warp sorts its 256 records into the eight class lists in shared memory, in batch
+//      order (position = class base + records of the class in earlier tiles + rank among the
+//      tile's lanes of that class: four ballots per tile, one exchange of per-warp class totals);
+//   2. warp k walks list k 32 entries at a time: lanes naming the same slot are matched by
+//      ballots over the slot bits above the class, the first of them moves the running count,
+//      every entry's seq is stored where its record lies.
+// The serial chain of a chunk is then its longest class list / 32 steps instead of one step per
+// tile of the whole chunk: 8 x shorter on a registry of thousands of services, and no worse than
+// before when one service has every call (one list, one warp, the same number of steps).
+constexpr int kTripTiles = (kAssignThreads / 32) * kAssignDepth;
+constexpr int kTripRecords = kTripTiles * 32;
+static_assert(kAssignThreads == 256, "eight warps own the eight slot classes");
+__host__ __device__ inline size_t assign_classes_smem(uint32_t n_slots) {
+    return static_cast<size_t>(n_slots) * 4 + kTripRecords * 4 + kTripRecords * 2 + 8 * 8 * 4;
+}
+__device__ __forceinline__ uint32_t pick_class(uint32_t k, uint32_t live, uint32_t v0, uint32_t v1, uint32_t v2) {
+    return live & ((k & 1u) ? v0 : ~v0) & ((k & 2u) ? v1 : ~v1) & ((k & 4u) ? v2 : ~v2);
+}
+template <bool kScatter>
+__global__ void __launch_bounds__(kAssignThreads)
+    rank_assign_classes_kernel(const uint32_t n_slots, const uint32_t* __restrict__ ids, ptype_req* __restrict__ reqs,
+                               unsigned long long* __restrict__ seq_out, const size_t n, const size_t chunk,
+                               const uint32_t* __restrict__ rows, const unsigned long long* __restrict__ seq_start) {
+    extern __shared__ __align__(16) unsigned char rank_smem[];
+    uint32_t* const run = reinterpret_cast<uint32_t*>(rank_smem);  // counted calls to each service before the cursor
+    uint32_t* const list_slot = run + n_slots;                     // the trip's counted records, class by class
+    uint16_t* const list_rec = reinterpret_cast<uint16_t*>(list_slot + kTripRecords);
+    uint32_t* const warp_total = reinterpret_cast<uint32_t*>(list_rec + kTripRecords);  // [warp][class]
+    const uint32_t* row = rows + static_cast<size_t>(blockIdx.x) * n_slots;
+    for (uint32_t s = threadIdx.x; s < n_slots; s += kAssignThreads) run[s] = row[s];
+    const size_t lo = static_cast<size_t>(blockIdx.x) * chunk;
+    const size_t hi = lo + chunk < n ? lo + chunk : n;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t below = (1u << lane) - 1u;
+    const uint32_t slot_bits = 32u - __clz(n_slots - 1u);
+    const uint32_t match_bits = slot_bits > 3u ? slot_bits - 3u : 0u;
+    const uint32_t k = lane & 7u;  // the class this lane keeps the books of in step 1
+
+    auto store_seq = [&](size_t j, unsigned long long seq) {
+        if (kScatter)
+            reinterpret_cast<unsigned long long*>(reqs + j)[1] = seq;  // ptype_req.seq
+        else
+            seq_out[j] = seq;
+    };
+    auto load_ids = [&](size_t base, uint32_t (&at)[kAssignDepth]) {
+#pragma unroll
+        for (int r = 0; r < kAssignDepth; ++r) {
+            const size_t j = base + (static_cast<size_t>(warp) * kAssignDepth + r) * 32 + lane;
+            at[r] = j < hi ? __ldg(ids + j) : kNoSlot;
+        }
+    };
+
+    uint32_t next_at[kAssignDepth];
+    if (lo < hi) load_ids(lo, next_at);
+    for (size_t base = lo; base < hi; base += kTripRecords) {  // uniform trip count per CTA
+        uint32_t at[kAssignDepth], mates[kAssignDepth], cnt[kAssignDepth];
+        uint32_t total = 0;
+#pragma unroll
+        for (int r = 0; r < kAssignDepth; ++r) {
+            at[r] = next_at[r];
+            const bool live = at[r] != kNoSlot;
+            const uint32_t live_mask = __ballot_sync(kFull, live);
+            const uint32_t v0 = __ballot_sync(kFull, at[r] & 1u), v1 = __ballot_sync(kFull, at[r] & 2u),
+                           v2 = __ballot_sync(kFull, at[r] & 4u);
+            mates[r] = pick_class(at[r] & 7u, live_mask, v0, v1, v2);  // the tile's lanes of this lane's class
+            cnt[r] = __popc(pick_class(k, live_mask, v0, v1, v2));     // the tile's records of class k
+            total += cnt[r];
+            const size_t j = base + (static_cast<size_t>(warp) * kAssignDepth + r) * 32 + lane;
+            if (!live && j < hi) store_seq(j, 0ull);  // no Client, or a Client without nodes: no counter value
+        }
+        if (lane < 8) warp_total[warp * 8 + lane] = total;
+        __syncthreads();  // (the lists of the previous trip have been read by now as well)
+        if (base + kTripRecords < hi) load_ids(base + kTripRecords, next_at);  // in flight during step 2
+        // class k: records in earlier warps of this trip, in all warps, and where its list starts
+        uint32_t before = 0, whole = 0;
+#pragma unroll
+        for (uint32_t w = 0; w < 8; ++w) {
+            const uint32_t t = warp_total[w * 8 + k];
+            before += w < warp ? t : 0u;
+            whole += t;
+        }
+        uint32_t list_base = whole;  // exclusive scan over the eight classes (lanes repeat with period 8)
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(kFull, list_base, o, 8);
+            if (k >= static_cast<uint32_t>(o)) list_base += t;
+        }
+        list_base -= whole;
+        uint32_t at_list = list_base + before;
+#pragma unroll
+        for (int r = 0; r < kAssignDepth; ++r) {
+            const uint32_t mine = __shfl_sync(kFull, at_list, at[r] & 7u) + __popc(mates[r] & below);
+            if (at[r] != kNoSlot) {
+                list_slot[mine] = at[r];
+                list_rec[mine] = static_cast<uint16_t>((warp * kAssignDepth + r) * 32 + lane);
+            }
+            at_list += cnt[r];
+        }
+        const uint32_t my_base = __shfl_sync(kFull, list_base, warp), my_count = __shfl_sync(kFull, whole, warp);
+        __syncthreads();
+        // ---- step 2: warp `warp` settles class `warp`
+        for (uint32_t i = 0; i < my_count; i += 32) {
+            const bool valid = i + lane < my_count;
+            const uint32_t slot = valid ? list_slot[my_base + i + lane] : kNoSlot;
+            const uint32_t rec = valid ? list_rec[my_base + i + lane] : 0u;
+            const unsigned long long start = valid ? __ldg(seq_start + slot) : 0ull;
+            uint32_t peers = __ballot_sync(kFull, valid);
+            for (uint32_t b = 0; b < match_bits; ++b) {
+                const bool one = (slot >> (b + 3u)) & 1u;
+                const uint32_t vote = __ballot_sync(kFull, one);
+                peers &= one ? vote : ~vote;
+            }
+            uint32_t first = 0;
+            if (valid && (peers & below) == 0) {  // the first lane of each slot: distinct slots, no two lanes meet
+                first = run[slot];
+                run[slot] = first + __popc(peers);
+            }
+            __syncwarp();
+            first = __shfl_sync(kFull, first, valid ? __ffs(peers) - 1 : lane);
+            if (valid) store_seq(base + rec, start + first + __popc(peers & below) + 1ull);
+        }
+    }
+}
+
 // Counters follow their services from the table of the outgoing image to the table of the
 // incoming one (placement may differ; a service the new image does not know is dropped).
 __global__ void __launch_bounds__(kScanThreads)
@@ -423,13 +552,19 @@ cudaError_t rank_plan(uint32_t n_slots, size_t n, int sm_count, RankPlan* plan) 
     plan->staged = rank_shared_bytes(true, n_slots) <= kRankSmemBudget;
     plan->threads = plan->staged ? kStagedThreads : kProbeThreads;
     plan->smem = rank_shared_bytes(plan->staged, n_slots);
-    plan->assign_smem = static_cast<size_t>(n_slots) * 4;
+    static const bool classes = [] {
+        const char* v = std::getenv("PTYPE_B200_ASSIGN_CLASSES");
+        return v ? std::atoi(v) != 0 : true;
+    }();
+    plan->classes = classes;
+    plan->assign_smem = classes ? assign_classes_smem(n_slots) : static_cast<size_t>(n_slots) * 4;
     cudaError_t e = plan->staged ? prepare_count<true, kStagedThreads>(plan->smem)
                                  : prepare_count<false, kProbeThreads>(plan->smem);
     if (e != cudaSuccess) return e;
     int assign_per_sm = 0;
     for (int scatter = 0; scatter < 2; ++scatter) {
-        auto kernel = scatter ? rank_assign_kernel<true> : rank_assign_kernel<false>;
+        auto kernel = classes ? (scatter ? rank_assign_classes_kernel<true> : rank_assign_classes_kernel<false>)
+                              : (scatter ? rank_assign_kernel<true> : rank_assign_kernel<false>);
         if (plan->assign_smem > 48 * 1024) {
             e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      static_cast<int>(plan->assign_smem));
@@ -474,12 +609,20 @@ cudaError_t launch_assign_seq(const DeviceImage& img, const RankPlan& plan, ptyp
                                                                           seq_start);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    if (seq_out == nullptr)
+    if (plan.classes) {
+        if (seq_out == nullptr)
+            rank_assign_classes_kernel<true><<<plan.n_chunks, kAssignThreads, plan.assign_smem, stream>>>(
+                img.n_slots, ids, reqs, nullptr, n, plan.chunk, rows, seq_start);
+        else
+            rank_assign_classes_kernel<false><<<plan.n_chunks, kAssignThreads, plan.assign_smem, stream>>>(
+                img.n_slots, ids, nullptr, seq_out, n, plan.chunk, rows, seq_start);
+    } else if (seq_out == nullptr) {
         rank_assign_kernel<true><<<plan.n_chunks, kAssignThreads, plan.assign_smem, stream>>>(
             img.n_slots, ids, reqs, nullptr, n, plan.chunk, rows, seq_start);
-    else
+    } else {
         rank_assign_kernel<false><<<plan.n_chunks, kAssignThreads, plan.assign_smem, stream>>>(
             img.n_slots, ids, nullptr, seq_out, n, plan.chunk, rows, seq_start);
+    }
     return cudaGetLastError();
 }
 
