@@ -392,29 +392,33 @@ __global__ void __launch_bounds__(kAssignThreads)
 //      tile's lanes of that class: four ballots per tile, one exchange of per-warp class totals);
 //   2. warp k walks list k 32 entries at a time: lanes naming the same slot are matched by
 //      ballots over the slot bits above the class, the first of them moves the running count,
-//      every entry's seq is stored where its record lies.
+//      and every entry's rank inside the batch goes to a shared-memory array indexed by record;
+//   3. (after the next trip's first barrier) every lane picks up the ranks of its own records,
+//      adds the counter values it gathered while step 2 ran, and stores - consecutive lanes,
+//      consecutive records, as in the load.
 // The serial chain of a chunk is then its longest class list / 32 steps instead of one step per
 // tile of the whole chunk: 8 x shorter on a registry of thousands of services, and no worse than
 // before when one service has every call (one list, one warp, the same number of steps).
 constexpr int kTripTiles = (kAssignThreads / 32) * kAssignDepth;
 constexpr int kTripRecords = kTripTiles * 32;
-constexpr int kClassBatch = 8;  // steps of a class list whose counter values are gathered together
+constexpr int kMatchUnroll = 12;  // slot bits above the class matched without a loop (tables up to 32 768 slots)
 static_assert(kAssignThreads == 256, "eight warps own the eight slot classes");
 __host__ __device__ inline size_t assign_classes_smem(uint32_t n_slots) {
-    return static_cast<size_t>(n_slots) * 4 + kTripRecords * 4 + kTripRecords * 2 + 8 * 8 * 4;
+    return static_cast<size_t>(n_slots) * 4 + kTripRecords * 4 + kTripRecords * 4 + kTripRecords * 2 + 8 * 8 * 4;
 }
 __device__ __forceinline__ uint32_t pick_class(uint32_t k, uint32_t live, uint32_t v0, uint32_t v1, uint32_t v2) {
     return live & ((k & 1u) ? v0 : ~v0) & ((k & 2u) ? v1 : ~v1) & ((k & 4u) ? v2 : ~v2);
 }
 template <bool kScatter>
-__global__ void __launch_bounds__(kAssignThreads)
+__global__ void __launch_bounds__(kAssignThreads, 3)
     rank_assign_classes_kernel(const uint32_t n_slots, const uint32_t* __restrict__ ids, ptype_req* __restrict__ reqs,
                                unsigned long long* __restrict__ seq_out, const size_t n, const size_t chunk,
                                const uint32_t* __restrict__ rows, const unsigned long long* __restrict__ seq_start) {
     extern __shared__ __align__(16) unsigned char rank_smem[];
     uint32_t* const run = reinterpret_cast<uint32_t*>(rank_smem);  // counted calls to each service before the cursor
     uint32_t* const list_slot = run + n_slots;                     // the trip's counted records, class by class
-    uint16_t* const list_rec = reinterpret_cast<uint16_t*>(list_slot + kTripRecords);
+    uint32_t* const rank_of = list_slot + kTripRecords;            // by record of the trip: 1 + counted calls before it
+    uint16_t* const list_rec = reinterpret_cast<uint16_t*>(rank_of + kTripRecords);
     uint32_t* const warp_total = reinterpret_cast<uint32_t*>(list_rec + kTripRecords);  // [warp][class]
     const uint32_t* row = rows + static_cast<size_t>(blockIdx.x) * n_slots;
     for (uint32_t s = threadIdx.x; s < n_slots; s += kAssignThreads) run[s] = row[s];
@@ -424,42 +428,58 @@ __global__ void __launch_bounds__(kAssignThreads)
     const uint32_t below = (1u << lane) - 1u;
     const uint32_t slot_bits = 32u - __clz(n_slots - 1u);
     const uint32_t match_bits = slot_bits > 3u ? slot_bits - 3u : 0u;
-    const uint32_t k = lane & 7u;  // the class this lane keeps the books of in step 1
+    const uint32_t k = lane & 7u;                              // the class this lane keeps the books of in step 1
+    const uint32_t my_rec = warp * kAssignDepth * 32 + lane;   // this lane's first record of a trip
 
-    auto store_seq = [&](size_t j, unsigned long long seq) {
-        if (kScatter)
-            reinterpret_cast<unsigned long long*>(reqs + j)[1] = seq;  // ptype_req.seq
-        else
-            seq_out[j] = seq;
-    };
     auto load_ids = [&](size_t base, uint32_t (&at)[kAssignDepth]) {
 #pragma unroll
         for (int r = 0; r < kAssignDepth; ++r) {
-            const size_t j = base + (static_cast<size_t>(warp) * kAssignDepth + r) * 32 + lane;
+            const size_t j = base + my_rec + r * 32;
             at[r] = j < hi ? __ldg(ids + j) : kNoSlot;
+        }
+    };
+    // step 3 for the trip that started at `base`: start[] = the counters' values before the batch
+    auto store_trip = [&](size_t base, const unsigned long long (&start)[kAssignDepth], uint32_t live_bits) {
+#pragma unroll
+        for (int r = 0; r < kAssignDepth; ++r) {
+            const size_t j = base + my_rec + r * 32;
+            if (j >= hi) continue;
+            // no Client, or a Client without nodes: no counter value, seq 0
+            const unsigned long long seq = (live_bits >> r) & 1u ? start[r] + rank_of[my_rec + r * 32] : 0ull;
+            if (kScatter)
+                reinterpret_cast<unsigned long long*>(reqs + j)[1] = seq;  // ptype_req.seq
+            else
+                seq_out[j] = seq;
         }
     };
 
     uint32_t next_at[kAssignDepth];
+    unsigned long long prev_start[kAssignDepth];
+    uint32_t prev_live = 0;
     if (lo < hi) load_ids(lo, next_at);
     for (size_t base = lo; base < hi; base += kTripRecords) {  // uniform trip count per CTA
         uint32_t at[kAssignDepth], mates[kAssignDepth], cnt[kAssignDepth];
-        uint32_t total = 0;
+        unsigned long long start[kAssignDepth];
+        uint32_t total = 0, live_bits = 0;
 #pragma unroll
         for (int r = 0; r < kAssignDepth; ++r) {
             at[r] = next_at[r];
+            start[r] = at[r] != kNoSlot ? __ldg(seq_start + at[r]) : 0ull;  // needed in step 3, a trip from now
+        }
+#pragma unroll
+        for (int r = 0; r < kAssignDepth; ++r) {
             const bool live = at[r] != kNoSlot;
+            live_bits |= static_cast<uint32_t>(live) << r;
             const uint32_t live_mask = __ballot_sync(kFull, live);
             const uint32_t v0 = __ballot_sync(kFull, at[r] & 1u), v1 = __ballot_sync(kFull, at[r] & 2u),
                            v2 = __ballot_sync(kFull, at[r] & 4u);
             mates[r] = pick_class(at[r] & 7u, live_mask, v0, v1, v2);  // the tile's lanes of this lane's class
             cnt[r] = __popc(pick_class(k, live_mask, v0, v1, v2));     // the tile's records of class k
             total += cnt[r];
-            const size_t j = base + (static_cast<size_t>(warp) * kAssignDepth + r) * 32 + lane;
-            if (!live && j < hi) store_seq(j, 0ull);  // no Client, or a Client without nodes: no counter value
         }
         if (lane < 8) warp_total[warp * 8 + lane] = total;
-        __syncthreads();  // (the lists of the previous trip have been read by now as well)
+        __syncthreads();  // every warp is through step 2 of the previous trip: its ranks are complete, its lists free
+        if (base != lo) store_trip(base - kTripRecords, prev_start, prev_live);
         if (base + kTripRecords < hi) load_ids(base + kTripRecords, next_at);  // in flight during step 2
         // class k: records in earlier warps of this trip, in all warps, and where its list starts
         uint32_t before = 0, whole = 0;
@@ -482,47 +502,45 @@ __global__ void __launch_bounds__(kAssignThreads)
             const uint32_t mine = __shfl_sync(kFull, at_list, at[r] & 7u) + __popc(mates[r] & below);
             if (at[r] != kNoSlot) {
                 list_slot[mine] = at[r];
-                list_rec[mine] = static_cast<uint16_t>((warp * kAssignDepth + r) * 32 + lane);
+                list_rec[mine] = static_cast<uint16_t>(my_rec + r * 32);
             }
             at_list += cnt[r];
+            prev_start[r] = start[r];
         }
+        prev_live = live_bits;
         const uint32_t my_base = __shfl_sync(kFull, list_base, warp), my_count = __shfl_sync(kFull, whole, warp);
         __syncthreads();
-        // ---- step 2: warp `warp` settles class `warp`, kClassBatch steps of 32 entries at a time: the
-        // counters' values before the batch are gathered for all of them first (a gather per step
-        // put its L2 latency into the chain: 48 % of this kernel's stall samples)
-        for (uint32_t i0 = 0; i0 < my_count; i0 += 32 * kClassBatch) {
-            uint32_t slot[kClassBatch];
-            unsigned long long start[kClassBatch];
+        // ---- step 2: warp `warp` settles class `warp`
+        for (uint32_t i = 0; i < my_count; i += 32) {
+            const bool valid = i + lane < my_count;
+            const uint32_t slot = valid ? list_slot[my_base + i + lane] : kNoSlot;
+            const uint32_t key = slot >> 3;
+            uint32_t peers = __ballot_sync(kFull, valid);
 #pragma unroll
-            for (int u = 0; u < kClassBatch; ++u) {
-                const uint32_t e = i0 + u * 32 + lane;
-                slot[u] = e < my_count ? list_slot[my_base + e] : kNoSlot;
+            for (int b = 0; b < kMatchUnroll; ++b) {  // independent ballots, one chain of ANDs
+                const bool one = (key >> b) & 1u;
+                const uint32_t vote = __ballot_sync(kFull, one);
+                if (static_cast<uint32_t>(b) < match_bits) peers &= one ? vote : ~vote;
             }
-#pragma unroll
-            for (int u = 0; u < kClassBatch; ++u) start[u] = slot[u] != kNoSlot ? __ldg(seq_start + slot[u]) : 0ull;
-#pragma unroll
-            for (int u = 0; u < kClassBatch; ++u) {
-                if (i0 + u * 32 >= my_count) break;  // warp-uniform
-                const bool valid = slot[u] != kNoSlot;
-                uint32_t peers = __ballot_sync(kFull, valid);
-                for (uint32_t b = 0; b < match_bits; ++b) {
-                    const bool one = (slot[u] >> (b + 3u)) & 1u;
-                    const uint32_t vote = __ballot_sync(kFull, one);
-                    peers &= one ? vote : ~vote;
-                }
-                uint32_t first = 0;
-                if (valid && (peers & below) == 0) {  // the first lane of each slot: distinct slots, no two lanes meet
-                    first = run[slot[u]];
-                    run[slot[u]] = first + __popc(peers);
-                }
-                __syncwarp();
-                first = __shfl_sync(kFull, first, valid ? __ffs(peers) - 1 : lane);
-                if (valid)
-                    store_seq(base + list_rec[my_base + i0 + u * 32 + lane],
-                              start[u] + first + __popc(peers & below) + 1ull);
+            for (uint32_t b = kMatchUnroll; b < match_bits; ++b) {
+                const bool one = (key >> b) & 1u;
+                const uint32_t vote = __ballot_sync(kFull, one);
+                peers &= one ? vote : ~vote;
             }
+            uint32_t first = 0;
+            if (valid && (peers & below) == 0) {  // the first lane of each slot: distinct slots, no two lanes meet
+                first = run[slot];
+                run[slot] = first + __popc(peers);
+            }
+            __syncwarp();
+            first = __shfl_sync(kFull, first, valid ? __ffs(peers) - 1 : lane);
+            if (valid) rank_of[list_rec[my_base + i + lane]] = first + __popc(peers & below) + 1u;
         }
+    }
+    if (lo < hi) {
+        __syncthreads();
+        const size_t trips = (hi - lo + kTripRecords - 1) / kTripRecords;
+        store_trip(lo + (trips - 1) * kTripRecords, prev_start, prev_live);
     }
 }
 
