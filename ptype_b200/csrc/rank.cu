@@ -515,18 +515,21 @@ __global__ void __launch_bounds__(kAssignThreads, 3)
             const bool valid = i + lane < my_count;
             const uint32_t slot = valid ? list_slot[my_base + i + lane] : kNoSlot;
             const uint32_t key = slot >> 3;
-            uint32_t peers = __ballot_sync(kFull, valid);
+            // lanes whose slot differs from this lane's in some bit above the class: one ballot, one
+            // select and one LOP3 per bit (bits beyond the table's width are zero in every valid lane)
+            uint32_t differ = 0;
+            if (match_bits != 0) {
 #pragma unroll
-            for (int b = 0; b < kMatchUnroll; ++b) {  // independent ballots, one chain of ANDs
-                const bool one = (key >> b) & 1u;
-                const uint32_t vote = __ballot_sync(kFull, one);
-                if (static_cast<uint32_t>(b) < match_bits) peers &= one ? vote : ~vote;
+                for (int b = 0; b < kMatchUnroll; ++b) {
+                    const bool one = (key >> b) & 1u;
+                    differ |= __ballot_sync(kFull, one) ^ (one ? 0xFFFFFFFFu : 0u);
+                }
+                for (uint32_t b = kMatchUnroll; b < match_bits; ++b) {
+                    const bool one = (key >> b) & 1u;
+                    differ |= __ballot_sync(kFull, one) ^ (one ? 0xFFFFFFFFu : 0u);
+                }
             }
-            for (uint32_t b = kMatchUnroll; b < match_bits; ++b) {
-                const bool one = (key >> b) & 1u;
-                const uint32_t vote = __ballot_sync(kFull, one);
-                peers &= one ? vote : ~vote;
-            }
+            const uint32_t peers = __ballot_sync(kFull, valid) & ~differ;
             uint32_t first = 0;
             if (valid && (peers & below) == 0) {  // the first lane of each slot: distinct slots, no two lanes meet
                 first = run[slot];
