@@ -110,7 +110,6 @@ struct RankPlan {
     int n_chunks = 0;     // contiguous chunks of the batch = rows of the histogram matrix = assign CTAs
     size_t chunk = 0;     // records per chunk
     size_t assign_smem = 0;
-    bool classes = true;  // assign pass: warps own slot classes (else: warps take turns)
 };
 bool rank_supported(uint32_t n_slots);
 cudaError_t rank_plan(uint32_t n_slots, size_t n, int sm_count, RankPlan* plan);

@@ -14,7 +14,7 @@
 //   rank_scan_kernel    exclusive scan down every column (eight warps per 32 columns), counter update
 //   rank_assign_kernel  one 256-thread CTA per chunk reloads its row (= calls to each service in
 //                       earlier chunks) and walks the chunk's slot ids in order, each warp holding
-//                       256 consecutive calls per trip: __match_any_sync ranks the calls of one
+//                       256 consecutive calls per trip: ballots over the slot bits rank the calls of one
 //                       service inside a tile of 32, the warps of the CTA take turns on the running
 //                       counts (one turn settles a warp's eight tiles; only the tile leaders touch
 //                       shared memory inside a turn), and the seq of every record is written
@@ -35,8 +35,6 @@
 // records, 184 us on its own) - that store, not the ranking, is the floor of this pass.
 #include <cuda_runtime.h>
 #include <stdint.h>
-
-#include <cstdlib>
 
 #include "../../include/ptype_b200.h"
 #include "device_image.h"
@@ -290,26 +288,30 @@ __global__ void __launch_bounds__(kScanThreads)
 
 // One 256-thread CTA per chunk (row).  It loads the row (calls to each service in earlier chunks)
 // into shared memory and walks the chunk's slot ids in order: a warp holds kAssignDepth consecutive
-// tiles of 32 records per trip, __match_any_sync ranks the records of one service inside a tile,
+// tiles of 32 records per trip, ballots over the slot bits rank the records of one service inside a tile,
 // and the warps take turns on the running counts - a turn settles all of a warp's tiles.  Only the
 // leader lane of each service in a tile touches shared memory inside the turn; everything else
 // (loading ids, matching, fetching the counter base, storing) happens outside it.  Several CTAs
 // share an SM (the counts are all the shared memory a CTA needs), so their turn chains interleave.
 // kScatter: write ptype_req.seq of the records; else a plain array seq_out[j].
+// Tried instead of the turns: the eight warps each own a slot class (slot & 7), every trip's records
+// are sorted into eight class lists in shared memory and each warp settles its own list, nobody
+// waiting for anybody.  Correct, and slower (394 vs 338 us per 2^24 records for the whole
+// assign_seq): the sorting and the per-entry bookkeeping cost five times the instructions
+// (150 M vs 31 M warp instructions) and the pass became issue-bound instead of latency-bound.
 constexpr int kAssignThreads = 256;
 constexpr int kAssignDepth = 8;
-#ifndef PTYPE_RANK_MATCH_BALLOT
-#define PTYPE_RANK_MATCH_BALLOT 0
-#endif
-// Lanes of the warp that name the same slot, by one ballot per bit of the slot id.
+// Lanes of the warp that name the same slot: one ballot per bit of the slot id.  With thousands of
+// services nearly all 32 values of a tile differ, the case in which MATCH.ANY is slowest; the
+// ballots took the whole assign_seq from 368 to 338 us per 2^24 records.
 __device__ __forceinline__ uint32_t match_slots(uint32_t slot, uint32_t lane, uint32_t bits) {
     const bool live = slot != kNoSlot;
-    uint32_t peers = __ballot_sync(kFull, live);
+    uint32_t differ = 0;  // lanes whose slot differs from this lane's in some bit
     for (uint32_t b = 0; b < bits; ++b) {
         const bool one = (slot >> b) & 1u;
-        const uint32_t vote = __ballot_sync(kFull, one);
-        peers &= one ? vote : ~vote;
+        differ |= __ballot_sync(kFull, one) ^ (one ? 0xFFFFFFFFu : 0u);
     }
+    const uint32_t peers = __ballot_sync(kFull, live) & ~differ;
     return live ? peers : 1u << lane;
 }
 template <bool kScatter>
@@ -343,11 +345,7 @@ __global__ void __launch_bounds__(kAssignThreads)
 #pragma unroll
         for (int r = 0; r < kAssignDepth; ++r) {
             // calls of one service inside a tile of 32: lanes in `peers`, in batch order
-#if PTYPE_RANK_MATCH_BALLOT
             peers[r] = match_slots(at[r], lane, slot_bits);
-#else
-            peers[r] = __match_any_sync(kFull, at[r] != kNoSlot ? at[r] : 0x80000000u + lane);
-#endif
             first[r] = 0;
         }
         for (uint32_t w = 0; w < kAssignThreads / 32; ++w) {
@@ -381,169 +379,6 @@ __global__ void __launch_bounds__(kAssignThreads)
                     seq_out[j] = seq;
             }
         }
-    }
-}
-
-// The same pass without turns.  The running counts of two different slots never meet, so the
-// slots are split into eight classes (slot & 7) and warp k of the CTA owns class k: nobody waits
-// for anybody else's turn.  Per trip of 2048 records:
-//   1. every warp sorts its 256 records into the eight class lists in shared memory, in batch
-//      order (position = class base + records of the class in earlier tiles + rank among the
-//      tile's lanes of that class: four ballots per tile, one exchange of per-warp class totals);
-//   2. warp k walks list k 32 entries at a time: lanes naming the same slot are matched by
-//      ballots over the slot bits above the class, the first of them moves the running count,
-//      and every entry's rank inside the batch goes to a shared-memory array indexed by record;
-//   3. (after the next trip's first barrier) every lane picks up the ranks of its own records,
-//      adds the counter values it gathered while step 2 ran, and stores - consecutive lanes,
-//      consecutive records, as in the load.
-// The serial chain of a chunk is then its longest class list / 32 steps instead of one step per
-// tile of the whole chunk: 8 x shorter on a registry of thousands of services, and no worse than
-// before when one service has every call (one list, one warp, the same number of steps).
-constexpr int kTripTiles = (kAssignThreads / 32) * kAssignDepth;
-constexpr int kTripRecords = kTripTiles * 32;
-constexpr int kMatchUnroll = 12;  // slot bits above the class matched without a loop (tables up to 32 768 slots)
-static_assert(kAssignThreads == 256, "eight warps own the eight slot classes");
-__host__ __device__ inline size_t assign_classes_smem(uint32_t n_slots) {
-    return static_cast<size_t>(n_slots) * 4 + kTripRecords * 4 + kTripRecords * 4 + kTripRecords * 2 + 8 * 8 * 4;
-}
-__device__ __forceinline__ uint32_t pick_class(uint32_t k, uint32_t live, uint32_t v0, uint32_t v1, uint32_t v2) {
-    return live & ((k & 1u) ? v0 : ~v0) & ((k & 2u) ? v1 : ~v1) & ((k & 4u) ? v2 : ~v2);
-}
-template <bool kScatter>
-__global__ void __launch_bounds__(kAssignThreads, 3)
-    rank_assign_classes_kernel(const uint32_t n_slots, const uint32_t* __restrict__ ids, ptype_req* __restrict__ reqs,
-                               unsigned long long* __restrict__ seq_out, const size_t n, const size_t chunk,
-                               const uint32_t* __restrict__ rows, const unsigned long long* __restrict__ seq_start) {
-    extern __shared__ __align__(16) unsigned char rank_smem[];
-    uint32_t* const run = reinterpret_cast<uint32_t*>(rank_smem);  // counted calls to each service before the cursor
-    uint32_t* const list_slot = run + n_slots;                     // the trip's counted records, class by class
-    uint32_t* const rank_of = list_slot + kTripRecords;            // by record of the trip: 1 + counted calls before it
-    uint16_t* const list_rec = reinterpret_cast<uint16_t*>(rank_of + kTripRecords);
-    uint32_t* const warp_total = reinterpret_cast<uint32_t*>(list_rec + kTripRecords);  // [warp][class]
-    const uint32_t* row = rows + static_cast<size_t>(blockIdx.x) * n_slots;
-    for (uint32_t s = threadIdx.x; s < n_slots; s += kAssignThreads) run[s] = row[s];
-    const size_t lo = static_cast<size_t>(blockIdx.x) * chunk;
-    const size_t hi = lo + chunk < n ? lo + chunk : n;
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t below = (1u << lane) - 1u;
-    const uint32_t slot_bits = 32u - __clz(n_slots - 1u);
-    const uint32_t match_bits = slot_bits > 3u ? slot_bits - 3u : 0u;
-    const uint32_t k = lane & 7u;                              // the class this lane keeps the books of in step 1
-    const uint32_t my_rec = warp * kAssignDepth * 32 + lane;   // this lane's first record of a trip
-
-    auto load_ids = [&](size_t base, uint32_t (&at)[kAssignDepth]) {
-#pragma unroll
-        for (int r = 0; r < kAssignDepth; ++r) {
-            const size_t j = base + my_rec + r * 32;
-            at[r] = j < hi ? __ldg(ids + j) : kNoSlot;
-        }
-    };
-    // step 3 for the trip that started at `base`: start[] = the counters' values before the batch
-    auto store_trip = [&](size_t base, const unsigned long long (&start)[kAssignDepth], uint32_t live_bits) {
-#pragma unroll
-        for (int r = 0; r < kAssignDepth; ++r) {
-            const size_t j = base + my_rec + r * 32;
-            if (j >= hi) continue;
-            // no Client, or a Client without nodes: no counter value, seq 0
-            const unsigned long long seq = (live_bits >> r) & 1u ? start[r] + rank_of[my_rec + r * 32] : 0ull;
-            if (kScatter)
-                reinterpret_cast<unsigned long long*>(reqs + j)[1] = seq;  // ptype_req.seq
-            else
-                seq_out[j] = seq;
-        }
-    };
-
-    uint32_t next_at[kAssignDepth];
-    unsigned long long prev_start[kAssignDepth];
-    uint32_t prev_live = 0;
-    if (lo < hi) load_ids(lo, next_at);
-    for (size_t base = lo; base < hi; base += kTripRecords) {  // uniform trip count per CTA
-        uint32_t at[kAssignDepth], mates[kAssignDepth], cnt[kAssignDepth];
-        unsigned long long start[kAssignDepth];
-        uint32_t total = 0, live_bits = 0;
-#pragma unroll
-        for (int r = 0; r < kAssignDepth; ++r) {
-            at[r] = next_at[r];
-            start[r] = at[r] != kNoSlot ? __ldg(seq_start + at[r]) : 0ull;  // needed in step 3, a trip from now
-        }
-#pragma unroll
-        for (int r = 0; r < kAssignDepth; ++r) {
-            const bool live = at[r] != kNoSlot;
-            live_bits |= static_cast<uint32_t>(live) << r;
-            const uint32_t live_mask = __ballot_sync(kFull, live);
-            const uint32_t v0 = __ballot_sync(kFull, at[r] & 1u), v1 = __ballot_sync(kFull, at[r] & 2u),
-                           v2 = __ballot_sync(kFull, at[r] & 4u);
-            mates[r] = pick_class(at[r] & 7u, live_mask, v0, v1, v2);  // the tile's lanes of this lane's class
-            cnt[r] = __popc(pick_class(k, live_mask, v0, v1, v2));     // the tile's records of class k
-            total += cnt[r];
-        }
-        if (lane < 8) warp_total[warp * 8 + lane] = total;
-        __syncthreads();  // every warp is through step 2 of the previous trip: its ranks are complete, its lists free
-        if (base != lo) store_trip(base - kTripRecords, prev_start, prev_live);
-        if (base + kTripRecords < hi) load_ids(base + kTripRecords, next_at);  // in flight during step 2
-        // class k: records in earlier warps of this trip, in all warps, and where its list starts
-        uint32_t before = 0, whole = 0;
-#pragma unroll
-        for (uint32_t w = 0; w < 8; ++w) {
-            const uint32_t t = warp_total[w * 8 + k];
-            before += w < warp ? t : 0u;
-            whole += t;
-        }
-        uint32_t list_base = whole;  // exclusive scan over the eight classes (lanes repeat with period 8)
-#pragma unroll
-        for (int o = 1; o < 8; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(kFull, list_base, o, 8);
-            if (k >= static_cast<uint32_t>(o)) list_base += t;
-        }
-        list_base -= whole;
-        uint32_t at_list = list_base + before;
-#pragma unroll
-        for (int r = 0; r < kAssignDepth; ++r) {
-            const uint32_t mine = __shfl_sync(kFull, at_list, at[r] & 7u) + __popc(mates[r] & below);
-            if (at[r] != kNoSlot) {
-                list_slot[mine] = at[r];
-                list_rec[mine] = static_cast<uint16_t>(my_rec + r * 32);
-            }
-            at_list += cnt[r];
-            prev_start[r] = start[r];
-        }
-        prev_live = live_bits;
-        const uint32_t my_base = __shfl_sync(kFull, list_base, warp), my_count = __shfl_sync(kFull, whole, warp);
-        __syncthreads();
-        // ---- step 2: warp `warp` settles class `warp`
-        for (uint32_t i = 0; i < my_count; i += 32) {
-            const bool valid = i + lane < my_count;
-            const uint32_t slot = valid ? list_slot[my_base + i + lane] : kNoSlot;
-            const uint32_t key = slot >> 3;
-            // lanes whose slot differs from this lane's in some bit above the class: one ballot, one
-            // select and one LOP3 per bit (bits beyond the table's width are zero in every valid lane)
-            uint32_t differ = 0;
-            if (match_bits != 0) {
-#pragma unroll
-                for (int b = 0; b < kMatchUnroll; ++b) {
-                    const bool one = (key >> b) & 1u;
-                    differ |= __ballot_sync(kFull, one) ^ (one ? 0xFFFFFFFFu : 0u);
-                }
-                for (uint32_t b = kMatchUnroll; b < match_bits; ++b) {
-                    const bool one = (key >> b) & 1u;
-                    differ |= __ballot_sync(kFull, one) ^ (one ? 0xFFFFFFFFu : 0u);
-                }
-            }
-            const uint32_t peers = __ballot_sync(kFull, valid) & ~differ;
-            uint32_t first = 0;
-            if (valid && (peers & below) == 0) {  // the first lane of each slot: distinct slots, no two lanes meet
-                first = run[slot];
-                run[slot] = first + __popc(peers);
-            }
-            __syncwarp();
-            first = __shfl_sync(kFull, first, valid ? __ffs(peers) - 1 : lane);
-            if (valid) rank_of[list_rec[my_base + i + lane]] = first + __popc(peers & below) + 1u;
-        }
-    }
-    if (lo < hi) {
-        __syncthreads();
-        const size_t trips = (hi - lo + kTripRecords - 1) / kTripRecords;
-        store_trip(lo + (trips - 1) * kTripRecords, prev_start, prev_live);
     }
 }
 
@@ -588,19 +423,13 @@ cudaError_t rank_plan(uint32_t n_slots, size_t n, int sm_count, RankPlan* plan) 
     plan->staged = rank_shared_bytes(true, n_slots) <= kRankSmemBudget;
     plan->threads = plan->staged ? kStagedThreads : kProbeThreads;
     plan->smem = rank_shared_bytes(plan->staged, n_slots);
-    static const bool classes = [] {
-        const char* v = std::getenv("PTYPE_B200_ASSIGN_CLASSES");
-        return v ? std::atoi(v) != 0 : true;
-    }();
-    plan->classes = classes;
-    plan->assign_smem = classes ? assign_classes_smem(n_slots) : static_cast<size_t>(n_slots) * 4;
+    plan->assign_smem = static_cast<size_t>(n_slots) * 4;
     cudaError_t e = plan->staged ? prepare_count<true, kStagedThreads>(plan->smem)
                                  : prepare_count<false, kProbeThreads>(plan->smem);
     if (e != cudaSuccess) return e;
     int assign_per_sm = 0;
     for (int scatter = 0; scatter < 2; ++scatter) {
-        auto kernel = classes ? (scatter ? rank_assign_classes_kernel<true> : rank_assign_classes_kernel<false>)
-                              : (scatter ? rank_assign_kernel<true> : rank_assign_kernel<false>);
+        auto kernel = scatter ? rank_assign_kernel<true> : rank_assign_kernel<false>;
         if (plan->assign_smem > 48 * 1024) {
             e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      static_cast<int>(plan->assign_smem));
@@ -645,20 +474,12 @@ cudaError_t launch_assign_seq(const DeviceImage& img, const RankPlan& plan, ptyp
                                                                           seq_start);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    if (plan.classes) {
-        if (seq_out == nullptr)
-            rank_assign_classes_kernel<true><<<plan.n_chunks, kAssignThreads, plan.assign_smem, stream>>>(
-                img.n_slots, ids, reqs, nullptr, n, plan.chunk, rows, seq_start);
-        else
-            rank_assign_classes_kernel<false><<<plan.n_chunks, kAssignThreads, plan.assign_smem, stream>>>(
-                img.n_slots, ids, nullptr, seq_out, n, plan.chunk, rows, seq_start);
-    } else if (seq_out == nullptr) {
+    if (seq_out == nullptr)
         rank_assign_kernel<true><<<plan.n_chunks, kAssignThreads, plan.assign_smem, stream>>>(
             img.n_slots, ids, reqs, nullptr, n, plan.chunk, rows, seq_start);
-    } else {
+    else
         rank_assign_kernel<false><<<plan.n_chunks, kAssignThreads, plan.assign_smem, stream>>>(
             img.n_slots, ids, nullptr, seq_out, n, plan.chunk, rows, seq_start);
-    }
     return cudaGetLastError();
 }
 
