@@ -1088,10 +1088,14 @@ bool pdl_enabled() {
 // dispatch launch of this library (whose output this kernel does not read) - see after_dispatch in
 // context.cu.  A kernel that asks for more than 48 KiB of dynamic shared memory has to opt in, per
 // function and per device; doing it here covers every variant that is ever launched.
+// The 48 KiB a kernel gets without opting in cover its STATIC shared memory too (the method tables,
+// ~3 KiB), so the opt-in starts well below 48 KiB of dynamic memory: a 46.9 KiB table (1 500
+// services) was refused before this.  Asking for less than the default is harmless.
+constexpr size_t kOptInAbove = 32 * 1024;
 template <typename Kernel, typename... Args>
 cudaError_t launch_kernel(Kernel kernel, int blocks, int threads, size_t smem, cudaStream_t stream, bool pdl,
                           Args... args) {
-    if (smem > 48 * 1024) {
+    if (smem > kOptInAbove) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              static_cast<int>(smem));
         if (e != cudaSuccess) return e;
@@ -1131,7 +1135,7 @@ cudaError_t launch_variant(const DeviceImage& img, const LaunchPlan& plan, int b
 
 template <typename Kernel>
 cudaError_t occupancy_of(Kernel kernel, int threads, size_t dyn_smem, int* ctas_per_sm) {
-    if (dyn_smem > 48 * 1024) {
+    if (dyn_smem > kOptInAbove) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              static_cast<int>(dyn_smem));
         if (e != cudaSuccess) return e;
