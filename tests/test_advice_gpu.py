@@ -143,3 +143,48 @@ def test_dispatch_right_behind_a_producer_on_the_stream(ctx, oracle):
         got_req = d_req.download(p.REQ_DTYPE, n)
         assert_same(d_rep.download(p.REPLY_DTYPE, n), snap.dispatch(got_req, threads=8))
         assert got_req["seq"].max() < 0xDEAD0000   # the counters' values, not the scrambled ones
+
+
+@pytest.mark.parametrize("n_services", [1023, 1025, 1449, 1451, 1535, 1537, 3199, 3201, 6143, 6145, 10444, 10445])
+def test_table_sizes_either_side_of_every_threshold(ctx, oracle, n_services):
+    """Registries one step either side of each size at which something changes: 32 KiB of table
+    (the shared-memory opt-in), 45.3 KiB (four 256-thread CTAs -> one 1024-thread CTA), 48 KiB (the
+    default shared-memory limit), 100 KiB (the old shape switch), 192 KiB (half-full tables end,
+    then the staging budget ends and the table is probed in L2).  Dispatch in one launch and as a
+    batch list, the compact client form, and the balancer's counters drawn on the device."""
+    spec = w.stress_registry(n_services, 3)
+    image = spec.image()
+    ctx.publish(image)
+    kv, snap = oracle.snapshot_from_spec(spec)
+    n = 70_001
+    reqs = w.stress_calls(n, n_services, seed=n_services)
+    want = snap.dispatch(reqs, threads=8)
+    assert_same(ctx.dispatch(reqs), want)
+    d_req = ctx.device_buffer(n * 48).upload(reqs)
+    d_rep = ctx.device_buffer(n * 16)
+    ctx.dispatch_batches(ctx.make_batches([(d_req, d_rep, n), (d_req, d_rep, 0)]))
+    assert_same(d_rep.download(p.REPLY_DTYPE, n), want)
+    one = w.calculator_calls(30_011, seed=3)
+    one["svc_key"] = p.service_key(f"svc_{n_services - 1:05d}")
+    key, base, methods, sel, args = w.as_client_batch(one)
+    assert_same(ctx.call_batch(key, base, methods, args, sel), snap.dispatch(one, threads=8))
+    d_req.free()
+    d_rep.free()
+    # the balancer's counters drawn on the device (a context of its own: counters start at zero),
+    # then the dispatch that uses them
+    assert image.salt == 0
+    blank = reqs.copy()
+    blank["seq"] = 0
+    want_seq = blank.copy()
+    snap.assign_seq(want_seq, np.zeros(snap.n_clients(), dtype=np.uint64))
+    with p.Context([0]) as fresh:
+        fresh.publish(image)
+        d_req = fresh.device_buffer(n * 48).upload(blank)
+        d_rep = fresh.device_buffer(n * 16)
+        fresh.assign_seq(d_req, n)
+        drawn = d_req.download(p.REQ_DTYPE, n)
+        assert np.array_equal(drawn["seq"], want_seq["seq"])
+        fresh.dispatch_device(d_req, n, d_rep)
+        assert_same(d_rep.download(p.REPLY_DTYPE, n), snap.dispatch(want_seq, threads=8))
+        d_req.free()
+        d_rep.free()
