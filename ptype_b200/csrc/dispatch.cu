@@ -1249,6 +1249,7 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     int m = 0;
     for (int b = 0; b < count; ++b) {
         if (batches[b].n == 0) continue;
+        if (batches[b].n > 0xFFFFFFFFull) return cudaErrorInvalidValue;  // the list holds 32-bit counts
         list.reqs[m] = reinterpret_cast<const uint4*>(batches[b].reqs);
         list.replies[m] = reinterpret_cast<uint4*>(batches[b].replies);
         list.n[m] = static_cast<uint32_t>(batches[b].n);
