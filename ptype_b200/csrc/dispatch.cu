@@ -19,11 +19,15 @@
 //            example/optimus/prime.go:15-25)
 //   pack     one 128-bit store per lane: 32 x 16 B contiguous reply records
 //
-// Kernels: dispatch_kernel (one batch, LDG), dispatch_multi_kernel (up to 96 batches per
-// launch, LDG - what ptype_b200_dispatch_batches runs), dispatch_bulk_kernel /
+// Kernels: dispatch_kernel (one batch, LDG), dispatch_multi_kernel and
+// dispatch_multi_prefetch_kernel (up to 96 batches per launch, LDG, two tiles per warp in flight
+// or one tile software-pipelined - what ptype_b200_dispatch_batches runs), dispatch_bulk_kernel /
 // dispatch_bulk_multi_kernel (TMA-staged requests), call_batch_kernel (one Client's batch in
 // compact form), checksum kernels.  All persistent; all carry programmatic-dependent-launch
 // hooks so consecutive launches overlap ramp-up and drain.
+//
+// Shared memory and L1 are one 256 KiB array per SM and the streamed request loads wait in L1:
+// the staged table is sized and the CTA shape chosen (plan_dispatch) so that 60 KiB of L1 remain.
 //
 // HBM-bound integer work: 64 algorithmic bytes per call, no tensor cores.
 #include <cuda_runtime.h>
