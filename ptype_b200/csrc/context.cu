@@ -947,9 +947,10 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
             }
             if (e == b) return PTYPE_E_LIMIT;
             if (tiles) {
+                int kernels = 0;
                 CU(ptype::launch_dispatch_multi(img, plan, d->dispatch_sms, batches + b, static_cast<int>(e - b),
-                                                d->stream, take_pdl(d, flags)));
-                ctx->launches.fetch_add(1);
+                                                d->stream, take_pdl(d, flags), nullptr, &kernels));
+                ctx->launches.fetch_add(static_cast<uint64_t>(kernels));
             }
             b = e;
         }

@@ -656,6 +656,10 @@ struct BatchList {
     // Sequence numbers kept beside the records (ptype_b200_assign_seq_array): when set, call j of
     // the launch's ONE batch takes seq[j] instead of its record's seq field.
     const unsigned long long* seq;
+    // A tail launch (launch_dispatch_multi): its CTAs are short and must not sit on an SM waiting
+    // for the main launch to end, so only CTA 0 does; that is enough to keep completion in
+    // stream order, because a grid is complete when all of its CTAs are.
+    int tail;
 };
 
 template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas>
@@ -718,7 +722,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         }
     }
     if (!table_ready) mbar_wait(&sh.table_bar, 0);
-    griddep_wait();
+    if (!list.tail || blockIdx.x == 0) griddep_wait();
 }
 
 // Software-pipelined form of dispatch_multi_kernel: a warp holds ONE tile at a time.  The transpose
@@ -814,7 +818,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
         if ((reinterpret_cast<uintptr_t>(out) & 1u) == 0)
             st_stream(out, dispatch_one<kSmemTable, kThreads != kMaxThreads>(img, sh, slots, cache, q[0], q[1], q[2]));
     }
-    griddep_wait();
+    if (!list.tail || blockIdx.x == 0) griddep_wait();
 }
 
 // Bulk-staged twin of dispatch_multi_kernel: per-warp TMA ring over the tile stream of many
@@ -1243,31 +1247,95 @@ cudaError_t launch_dispatch(const DeviceImage& img, const LaunchPlan& plan, int 
 // Up to kMaxBatchesPerLaunch device-resident batches in ONE launch.
 int max_batches_per_launch() { return kMaxBatchesPerLaunch; }
 
+namespace {
+// Appends records [first, first + n) of a batch to a list.
+void list_add(BatchList& list, const ptype_batch& bt, uint64_t first, uint64_t n) {
+    const int m = list.count;
+    list.reqs[m] = reinterpret_cast<const uint4*>(bt.reqs + first);
+    list.replies[m] = reinterpret_cast<uint4*>(bt.replies + first);
+    list.n[m] = static_cast<uint32_t>(n);
+    list.tile_end[m] = (m ? list.tile_end[m - 1] : 0u) + static_cast<uint32_t>((n + 31) / 32);
+    list.count = m + 1;
+}
+
+cudaError_t launch_list(const DeviceImage& img, const LaunchPlan& plan, const BatchList& list, int blocks,
+                        cudaStream_t stream, bool pdl);
+}  // namespace
+
+// A lone launch ends with a tail: with equal shares the SMs of a B200 finish up to 20 % apart
+// (tools/spread_probe.cu), and whoever is done early idles until the last one is.  Handing tiles
+// out through counters costs more than it saves once launches follow each other
+// (profiles/r02_tile_scheduling.txt), so the hardware's own block scheduler does it, for the end of
+// the launch only: a list of 2..kTailMaxBatches batches with a small table is cut in two, the first
+// part goes to the persistent grid, the last kTailPercent % to a second launch of short CTAs
+// (kTailTilesPerWarp tiles per warp) behind it.  Those start wherever a persistent CTA has left.
+// Longer lists (a host with that much queued keeps launches coming, and the next launch fills the
+// tail) and single batches (two launches per batch would cost the host more than the tail) stay whole.
+constexpr int kTailMaxBatches = 48;
+constexpr uint32_t kTailTilesPerWarp = 4;
+constexpr uint64_t kTailMinTiles = 16384;  // lists shorter than half a 2^20-call batch are not worth a second launch
+
 cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
                                   const ptype_batch* batches, int count, cudaStream_t stream, bool pdl,
-                                  const unsigned long long* seq) {
+                                  const unsigned long long* seq, int* kernels) {
+    if (kernels) *kernels = 0;
     if (seq != nullptr && (count != 1 || plan.bulk)) return cudaErrorInvalidValue;
-    BatchList list = {};
-    list.seq = seq;
     uint64_t tiles = 0;
-    int m = 0;
+    int live = 0;
     for (int b = 0; b < count; ++b) {
         if (batches[b].n == 0) continue;
         if (batches[b].n > 0xFFFFFFFFull) return cudaErrorInvalidValue;  // the list holds 32-bit counts
-        list.reqs[m] = reinterpret_cast<const uint4*>(batches[b].reqs);
-        list.replies[m] = reinterpret_cast<uint4*>(batches[b].replies);
-        list.n[m] = static_cast<uint32_t>(batches[b].n);
         tiles += (batches[b].n + 31) / 32;
-        list.tile_end[m] = static_cast<uint32_t>(tiles);
-        ++m;
+        ++live;
     }
-    if (m == 0) return cudaSuccess;
+    if (live == 0) return cudaSuccess;
     if (tiles >= 0xFFFFFFFFull) return cudaErrorInvalidValue;
-    list.count = m;
+    static const uint64_t tail_percent = [] {
+        const char* e = std::getenv("PTYPE_B200_TAIL_PERCENT");
+        return e ? static_cast<uint64_t>(std::atoi(e)) : uint64_t(8);
+    }();
+    const bool split = tail_percent > 0 && tail_percent < 100 && seq == nullptr && !plan.bulk &&
+                       plan.threads == kSmallThreads && live >= 2 && live <= kTailMaxBatches && tiles >= kTailMinTiles;
+    const uint64_t tail_tiles = split ? tiles * tail_percent / 100 : 0;
+    const uint64_t main_tiles = tiles - tail_tiles;
+
+    BatchList main_list = {}, tail_list = {};
+    main_list.seq = seq;
+    tail_list.tail = 1;
+    uint64_t seen = 0;  // tiles before the current batch
+    for (int b = 0; b < count; ++b) {
+        const uint64_t n = batches[b].n;
+        if (n == 0) continue;
+        const uint64_t bt = (n + 31) / 32;
+        if (seen + bt <= main_tiles) {
+            list_add(main_list, batches[b], 0, n);
+        } else if (seen >= main_tiles) {
+            list_add(tail_list, batches[b], 0, n);
+        } else {  // the cut falls inside this batch, on a tile boundary
+            const uint64_t head = (main_tiles - seen) * 32;
+            list_add(main_list, batches[b], 0, head);
+            list_add(tail_list, batches[b], head, n - head);
+        }
+        seen += bt;
+    }
     const size_t warps_per_cta = static_cast<size_t>(plan.threads) / 32;
-    size_t want = (tiles + warps_per_cta - 1) / warps_per_cta;
+    const size_t want = (main_tiles + warps_per_cta - 1) / warps_per_cta;
     const size_t resident = static_cast<size_t>(sm_count) * plan.ctas_per_sm;
     const int blocks = static_cast<int>(want < resident ? (want ? want : 1) : resident);
+    cudaError_t e = launch_list(img, plan, main_list, blocks, stream, pdl);
+    if (e != cudaSuccess) return e;
+    if (kernels) *kernels = 1;
+    if (tail_list.count == 0) return cudaSuccess;
+    const uint64_t per_cta = warps_per_cta * kTailTilesPerWarp;
+    e = launch_list(img, plan, tail_list, static_cast<int>((tail_tiles + per_cta - 1) / per_cta), stream, true);
+    if (e == cudaSuccess && kernels) *kernels = 2;
+    return e;
+}
+
+namespace {
+cudaError_t launch_list(const DeviceImage& img, const LaunchPlan& plan, const BatchList& list, int blocks,
+                        cudaStream_t stream, bool pdl) {
+    const unsigned long long* seq = list.seq;
     const uint32_t table_smem = static_cast<uint32_t>(plan.table_smem);
     if (plan.bulk) {
         if (plan.smem_table)
@@ -1327,6 +1395,8 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     return launch_kernel(dispatch_multi_kernel<false, kSmallUnroll, kSmallThreads, kSmallMinCtas>, blocks,
                          plan.threads, plan.dyn_smem, stream, pdl, img, list);
 }
+
+}  // namespace
 
 namespace {
 template <bool kSmemTable, int kArgs, bool kHasSel>
