@@ -486,6 +486,35 @@ def test_ragged_batch_lists_in_every_multi_batch_loop(ctx, oracle, shape):
     d_rep.free()
 
 
+@pytest.mark.parametrize("sizes", [(700_000, 300_017, 50_000), (1 << 20, 1 << 20), (20_000, 1_000_000, 31, 1),
+                                   (524_288, 1) + (40_000,) * 20])
+def test_lists_whose_end_runs_as_a_second_launch(ctx, oracle, sizes):
+    """A list of 2..48 batches is cut in two launches (csrc/dispatch.cu, launch_dispatch_multi): the
+    last 8 % of its tiles go to short CTAs behind the persistent grid.  The cut may fall inside a
+    batch (on a tile boundary), on a batch boundary, or leave tiny batches whole on either side;
+    every reply must be there exactly once and the guard bytes between the regions untouched."""
+    spec = w.calculator_registry()
+    ctx.publish(spec.image())
+    kv, snap = oracle.snapshot_from_spec(spec)
+    reqs = [w.calculator_calls(n, seed=7000 + i, seq_base=i << 21) for i, n in enumerate(sizes)]
+    guard = 32
+    req_off = np.cumsum([0] + [n * 48 for n in sizes])
+    rep_off = np.cumsum([0] + [n * 16 + guard for n in sizes])
+    d_req = ctx.device_buffer(int(req_off[-1]) + 48).upload(np.concatenate(reqs))
+    d_rep = ctx.device_buffer(int(rep_off[-1]))
+    d_rep.upload(np.full(int(rep_off[-1]), 0xCD, dtype=np.uint8))
+    ctx.dispatch_batches(ctx.make_batches(
+        (d_req.ptr + int(req_off[i]), d_rep.ptr + int(rep_off[i]), n) for i, n in enumerate(sizes)), sync=False)
+    ctx.sync()
+    got = d_rep.download(np.uint8, int(rep_off[-1]))
+    for i, n in enumerate(sizes):
+        lo = int(rep_off[i])
+        assert got[lo:lo + n * 16].tobytes() == snap.dispatch(reqs[i], threads=8).tobytes(), (i, n)
+        assert (got[lo + n * 16:lo + n * 16 + guard] == 0xCD).all(), (i, n)
+    d_req.free()
+    d_rep.free()
+
+
 @pytest.mark.parametrize("n", [1, 33, 4097, 128 * 1024 + 1, 1 << 20])
 @pytest.mark.parametrize("seq_base", [0, (1 << 32) - 7, (1 << 63) - 5])
 def test_call_batch_compact_form(ctx, oracle, n, seq_base):
