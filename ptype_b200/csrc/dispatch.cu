@@ -660,6 +660,7 @@ struct BatchList {
     // for the main launch to end, so only CTA 0 does; that is enough to keep completion in
     // stream order, because a grid is complete when all of its CTAs are.
     int tail;
+    uint32_t stagger_ns;  // measurement: every warp sleeps a pseudo-random time below this before it starts
 };
 
 template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas>
@@ -793,6 +794,11 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
             t.seq = lane < calls_here ? __ldg(list.seq + (static_cast<size_t>(tile) << 5) + lane) : 0ull;
     };
 
+    if (list.stagger_ns) {
+        uint32_t h = (blockIdx.x * kWarps + (threadIdx.x >> 5)) * 2654435761u;
+        h ^= h >> 15;
+        __nanosleep(h % list.stagger_ns);
+    }
     TileRegs t;
     fetch(t);  // before the tables: the longest latency first
 
@@ -1300,6 +1306,11 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     const uint64_t main_tiles = tiles - tail_tiles;
 
     BatchList main_list = {}, tail_list = {};
+    static const uint32_t stagger = [] {
+        const char* e = std::getenv("PTYPE_B200_STAGGER_NS");
+        return e ? static_cast<uint32_t>(std::atoi(e)) : 0u;
+    }();
+    main_list.stagger_ns = stagger;
     main_list.seq = seq;
     tail_list.tail = 1;
     uint64_t seen = 0;  // tiles before the current batch
