@@ -1300,8 +1300,16 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         const char* e = std::getenv("PTYPE_B200_TAIL_PERCENT");
         return e ? static_cast<uint64_t>(std::atoi(e)) : uint64_t(8);
     }();
+    static const int tail_max = [] {
+        const char* e = std::getenv("PTYPE_B200_TAIL_MAX");
+        return e ? std::atoi(e) : kTailMaxBatches;
+    }();
+    static const uint32_t tail_tiles_per_warp = [] {
+        const char* e = std::getenv("PTYPE_B200_TAIL_TILES");
+        return e ? static_cast<uint32_t>(std::atoi(e)) : kTailTilesPerWarp;
+    }();
     const bool split = tail_percent > 0 && tail_percent < 100 && seq == nullptr && !plan.bulk &&
-                       plan.threads == kSmallThreads && live >= 2 && live <= kTailMaxBatches && tiles >= kTailMinTiles;
+                       plan.threads == kSmallThreads && live >= 2 && live <= tail_max && tiles >= kTailMinTiles;
     const uint64_t tail_tiles = split ? tiles * tail_percent / 100 : 0;
     const uint64_t main_tiles = tiles - tail_tiles;
 
@@ -1337,7 +1345,7 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     if (e != cudaSuccess) return e;
     if (kernels) *kernels = 1;
     if (tail_list.count == 0) return cudaSuccess;
-    const uint64_t per_cta = warps_per_cta * kTailTilesPerWarp;
+    const uint64_t per_cta = warps_per_cta * tail_tiles_per_warp;
     e = launch_list(img, plan, tail_list, static_cast<int>((tail_tiles + per_cta - 1) / per_cta), stream, true);
     if (e == cudaSuccess && kernels) *kernels = 2;
     return e;
