@@ -447,7 +447,7 @@ def measure(ctx, env, workload: str, *, steps: int, warmup: int, nbuf: int, batc
         while time.perf_counter() < t_end:
             ctx.dispatch_batches(lap, flags=flags, sync=True)
     timed = plan_steps(steps)
-    preroll = batches_of(0, int(os.environ.get("PTYPE_BENCH_PREROLL", min(32, steps))))
+    preroll = batches_of(0, min(32, steps))
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     env.barrier(ctx)
     update_ms.clear()

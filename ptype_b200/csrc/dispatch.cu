@@ -660,7 +660,6 @@ struct BatchList {
     // for the main launch to end, so only CTA 0 does; that is enough to keep completion in
     // stream order, because a grid is complete when all of its CTAs are.
     int tail;
-    uint32_t stagger_ns;  // measurement: every warp sleeps a pseudo-random time below this before it starts
 };
 
 template <bool kSmemTable, int kUnroll, int kThreads, int kMinCtas>
@@ -794,11 +793,6 @@ __global__ void __launch_bounds__(kThreads, kMinCtas)
             t.seq = lane < calls_here ? __ldg(list.seq + (static_cast<size_t>(tile) << 5) + lane) : 0ull;
     };
 
-    if (list.stagger_ns) {
-        uint32_t h = (blockIdx.x * kWarps + (threadIdx.x >> 5)) * 2654435761u;
-        h ^= h >> 15;
-        __nanosleep(h % list.stagger_ns);
-    }
     TileRegs t;
     fetch(t);  // before the tables: the longest latency first
 
@@ -1300,25 +1294,12 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
         const char* e = std::getenv("PTYPE_B200_TAIL_PERCENT");
         return e ? static_cast<uint64_t>(std::atoi(e)) : uint64_t(8);
     }();
-    static const int tail_max = [] {
-        const char* e = std::getenv("PTYPE_B200_TAIL_MAX");
-        return e ? std::atoi(e) : kTailMaxBatches;
-    }();
-    static const uint32_t tail_tiles_per_warp = [] {
-        const char* e = std::getenv("PTYPE_B200_TAIL_TILES");
-        return e ? static_cast<uint32_t>(std::atoi(e)) : kTailTilesPerWarp;
-    }();
     const bool split = tail_percent > 0 && tail_percent < 100 && seq == nullptr && !plan.bulk &&
-                       plan.threads == kSmallThreads && live >= 2 && live <= tail_max && tiles >= kTailMinTiles;
+                       plan.threads == kSmallThreads && live >= 2 && live <= kTailMaxBatches && tiles >= kTailMinTiles;
     const uint64_t tail_tiles = split ? tiles * tail_percent / 100 : 0;
     const uint64_t main_tiles = tiles - tail_tiles;
 
     BatchList main_list = {}, tail_list = {};
-    static const uint32_t stagger = [] {
-        const char* e = std::getenv("PTYPE_B200_STAGGER_NS");
-        return e ? static_cast<uint32_t>(std::atoi(e)) : 0u;
-    }();
-    main_list.stagger_ns = stagger;
     main_list.seq = seq;
     tail_list.tail = 1;
     uint64_t seen = 0;  // tiles before the current batch
@@ -1345,7 +1326,7 @@ cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan
     if (e != cudaSuccess) return e;
     if (kernels) *kernels = 1;
     if (tail_list.count == 0) return cudaSuccess;
-    const uint64_t per_cta = warps_per_cta * tail_tiles_per_warp;
+    const uint64_t per_cta = warps_per_cta * kTailTilesPerWarp;
     e = launch_list(img, plan, tail_list, static_cast<int>((tail_tiles + per_cta - 1) / per_cta), stream, true);
     if (e == cudaSuccess && kernels) *kernels = 2;
     return e;
