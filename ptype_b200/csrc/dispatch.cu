@@ -1167,8 +1167,9 @@ cudaError_t occupancy_variant(const LaunchPlan& plan, int* ctas_per_sm) {
 
 // Which kernel, block shape and residency (measured on B200, profiles/README.md):
 //   slot table <= 200 KiB : table staged in shared memory, requests by LDG + shuffle
-//                           transpose (1024-thread CTA, one per SM, once the table passes
-//                           100 KiB; 256-thread CTAs otherwise)
+//                           transpose (four 256-thread CTAs per SM while four copies of the
+//                           table leave 60 KiB of L1, i.e. up to 45 KiB; one 1024-thread CTA
+//                           above; the image builder sizes staged tables to 192 KiB at most)
 //   larger                : table probed in L2, requests staged by bulk-async copies
 //   table <= 16 KiB and every exposed receiver is Prime (ALU-heavy calls): bulk-async
 //                           request staging with the table in shared memory

@@ -24,7 +24,7 @@
 // The count pass stages the table's keys in shared memory where they fit (tables up to ~18 500
 // slots, 12 bytes per slot, one 1024-thread CTA per SM taking several chunks in turn): three random
 // 16-byte probes per record against a table in L2 cost more than everything else together
-// (measured on the 12 800-slot registry: 497 us per 2^24 records).  Larger tables, up to 51 200
+// (measured on the 10 000-service registry: 497 us per 2^24 records).  Larger tables, up to 51 200
 // slots, are probed in L1/L2 by 256-thread CTAs.  The assign pass needs 4 bytes of shared memory
 // per slot, so four of its CTAs share an SM on that registry and their turn chains interleave.
 //
