@@ -947,9 +947,16 @@ int ptype_b200_dispatch_batches(ptype_ctx* ctx, int dev, const ptype_batch* batc
             }
             if (e == b) return PTYPE_E_LIMIT;
             if (tiles) {
+                // a list that finds the stream idle is on its own: its end may run as a second launch
+                // (cudaStreamQuery reports cudaErrorNotReady for a busy stream; that is not a failure)
+                bool lone = false;
+                if (e - b >= 2) {
+                    lone = cudaStreamQuery(d->stream) == cudaSuccess;
+                    if (!lone) cudaGetLastError();  // leave no "not ready" behind for a later error check
+                }
                 int kernels = 0;
                 CU(ptype::launch_dispatch_multi(img, plan, d->dispatch_sms, batches + b, static_cast<int>(e - b),
-                                                d->stream, take_pdl(d, flags), nullptr, &kernels));
+                                                d->stream, take_pdl(d, flags), nullptr, &kernels, lone));
                 ctx->launches.fetch_add(static_cast<uint64_t>(kernels));
             }
             b = e;

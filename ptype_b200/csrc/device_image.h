@@ -52,7 +52,8 @@ int max_batches_per_launch();
 // seq != nullptr (one batch, not a bulk plan): call j takes seq[j] instead of its record's seq field.
 cudaError_t launch_dispatch_multi(const DeviceImage& img, const LaunchPlan& plan, int sm_count,
                                   const ptype_batch* batches, int count, cudaStream_t stream, bool pdl,
-                                  const unsigned long long* seq = nullptr, int* kernels = nullptr);
+                                  const unsigned long long* seq = nullptr, int* kernels = nullptr,
+                                  bool lone = false);
 // Values-only output of a client batch: values != nullptr switches the kernel from 16-byte
 // reply records to 8-byte values plus an (index, status) list of the failed calls.
 struct CallBatchOut {
