@@ -336,8 +336,8 @@ int ptype_b200_dispatch_ex(ptype_ctx*, int dev, const ptype_req* reqs, size_t n,
                            ptype_batch_stats* stats, uint32_t flags);
 /* Several device-resident batches in one call.  Groups of up to 96 batches run as ONE
  * kernel launch whose persistent grid walks all their tiles as a single stream (no gap or
- * ramp between batches; for a list of 2-48 batches over a small table the last 8 % of the
- * tiles follow as a second launch of short CTAs that evens out the end); with PTYPE_F_ONE_LAUNCH_PER_BATCH, or when the registry table is
+ * ramp between batches; for a list of 2-48 batches over a small table that finds the stream
+ * idle, the last 8 % of the tiles follow as a second launch of short CTAs that evens out the end); with PTYPE_F_ONE_LAUNCH_PER_BATCH, or when the registry table is
  * probed in L2, every batch is its own launch and consecutive kernels overlap through
  * programmatic dependent launch.  Returns without waiting when PTYPE_F_ASYNC is set.  This is what a host pipelining the batches of many Clients
  * (one Client per service, cluster/cluster.go:101-103) submits per scheduling round. */
