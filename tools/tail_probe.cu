@@ -1,0 +1,146 @@
+// tail_probe.cu — what does a second launch of short CTAs behind a persistent grid actually do?
+//
+// Same streaming shape as spread_probe.cu (three coalesced 128-bit loads and one 128-bit store per
+// lane and 32-record tile).  The main grid (4 CTAs of 256 threads per SM) takes the first
+// (100 - tail_percent) % of the tiles in equal shares; a tail grid of short CTAs
+// (tiles_per_warp tiles per warp) takes the rest, launched right behind it with programmatic
+// stream serialization; the main kernel triggers its dependents at once, tail CTAs never wait.
+// Printed: when the main CTAs end, when the tail CTAs start and end, how long a tail CTA lives.
+//
+//   ./tail_probe [batches=20] [tail_percent=8] [tiles_per_warp=4] [repeats=3]
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#define CK(x)                                                                                  \
+    do {                                                                                       \
+        cudaError_t e_ = (x);                                                                  \
+        if (e_ != cudaSuccess) {                                                               \
+            std::fprintf(stderr, "%s: %s\n", #x, cudaGetErrorString(e_));                      \
+            return 1;                                                                          \
+        }                                                                                      \
+    } while (0)
+
+__device__ __forceinline__ uint4 ld_stream(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p));
+    return v;
+}
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ unsigned smid() {
+    unsigned s;
+    asm volatile("mov.u32 %0, %smid;" : "=r"(s));
+    return s;
+}
+
+struct Mark {
+    unsigned long long start, end;
+    unsigned sm, tiles;
+};
+
+__global__ void __launch_bounds__(256, 4)
+    stream_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, size_t first_tile, size_t end_tile,
+                  Mark* marks) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const size_t total_warps = static_cast<size_t>(gridDim.x) * 8, w = static_cast<size_t>(blockIdx.x) * 8 + warp;
+    const unsigned long long t0 = gtime();
+    unsigned done = 0;
+    uint4 a[3];
+    size_t t = first_tile + w;
+    if (t < end_tile)
+        for (int j = 0; j < 3; ++j) a[j] = ld_stream(in + t * 96 + j * 32 + lane);
+    while (t < end_tile) {
+        uint4 r;
+        r.x = a[0].x ^ a[1].y ^ a[2].z;
+        r.y = a[0].y + a[1].z;
+        r.z = a[0].z ^ a[2].w;
+        r.w = a[0].w + a[1].x + a[2].x;
+        const size_t cur = t;
+        t += total_warps;
+        if (t < end_tile)
+            for (int j = 0; j < 3; ++j) a[j] = ld_stream(in + t * 96 + j * 32 + lane);
+        out[cur * 32 + lane] = r;
+        ++done;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) marks[blockIdx.x] = Mark{t0, gtime(), smid(), done};
+}
+
+int main(int argc, char** argv) {
+    const int batches = argc > 1 ? std::atoi(argv[1]) : 20;
+    const int tail_percent = argc > 2 ? std::atoi(argv[2]) : 8;
+    const int tiles_per_warp = argc > 3 ? std::atoi(argv[3]) : 4;
+    const int repeats = argc > 4 ? std::atoi(argv[4]) : 3;
+    const size_t n = static_cast<size_t>(batches) << 20, n_tiles = n / 32;
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    const int grid = sms * 4;
+    const size_t tail_tiles = n_tiles * tail_percent / 100, main_tiles = n_tiles - tail_tiles;
+    const int tail_grid = tail_tiles ? static_cast<int>((tail_tiles + 8 * tiles_per_warp - 1) / (8 * tiles_per_warp)) : 0;
+    uint4 *in = nullptr, *out = nullptr;
+    Mark *d_main = nullptr, *d_tail = nullptr;
+    CK(cudaMalloc(&in, n * 48));
+    CK(cudaMalloc(&out, n * 16));
+    CK(cudaMalloc(&d_main, grid * sizeof(Mark)));
+    CK(cudaMalloc(&d_tail, (tail_grid + 1) * sizeof(Mark)));
+    CK(cudaMemset(in, 1, n * 48));
+    cudaStream_t stream;
+    CK(cudaStreamCreate(&stream));
+    std::vector<Mark> m_main(grid), m_tail(tail_grid);
+    for (int rep = 0; rep < repeats; ++rep) {
+        stream_kernel<<<grid, 256, 0, stream>>>(in, out, 0, main_tiles, d_main);
+        if (tail_grid) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(tail_grid);
+            cfg.blockDim = dim3(256);
+            cfg.stream = stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            CK(cudaLaunchKernelEx(&cfg, stream_kernel, static_cast<const uint4*>(in), out, main_tiles, n_tiles, d_tail));
+        }
+        CK(cudaStreamSynchronize(stream));
+        CK(cudaMemcpy(m_main.data(), d_main, grid * sizeof(Mark), cudaMemcpyDeviceToHost));
+        if (tail_grid) CK(cudaMemcpy(m_tail.data(), d_tail, tail_grid * sizeof(Mark), cudaMemcpyDeviceToHost));
+        unsigned long long first = ~0ull, main_first_end = ~0ull, main_last_end = 0, tail_first_start = ~0ull,
+                           tail_last_end = 0;
+        for (const Mark& m : m_main) {
+            first = std::min(first, m.start);
+            main_first_end = std::min(main_first_end, m.end);
+            main_last_end = std::max(main_last_end, m.end);
+        }
+        double life = 0;
+        std::vector<int> per_sm(sms, 0);
+        for (const Mark& m : m_tail) {
+            tail_first_start = std::min(tail_first_start, m.start);
+            tail_last_end = std::max(tail_last_end, m.end);
+            life += double(m.end - m.start);
+            ++per_sm[m.sm % sms];
+        }
+        const unsigned long long last = std::max(main_last_end, tail_last_end);
+        std::printf("rep %d: all done at %.1f us (%.2f TB/s); main CTAs end %.1f .. %.1f us", rep, double(last - first) / 1e3,
+                    double(n) * 64 / double(last - first) / 1e3, double(main_first_end - first) / 1e3,
+                    double(main_last_end - first) / 1e3);
+        if (tail_grid) {
+            std::sort(per_sm.begin(), per_sm.end());
+            std::printf("; %d tail CTAs: first starts %.1f us, last ends %.1f us, mean life %.2f us, per SM %d .. %d (median %d)",
+                        tail_grid, double(tail_first_start - first) / 1e3, double(tail_last_end - first) / 1e3,
+                        life / tail_grid / 1e3, per_sm.front(), per_sm.back(), per_sm[sms / 2]);
+        }
+        std::printf("\n");
+    }
+    return 0;
+}
