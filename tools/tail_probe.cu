@@ -77,7 +77,12 @@ __global__ void __launch_bounds__(256, 4)
     if (threadIdx.x == 0) marks[blockIdx.x] = Mark{t0, gtime(), smid(), done};
 }
 
+// 55 KiB of dynamic shared memory per CTA: four CTAs fill an SM, as the dispatch kernel's registers do,
+// so a tail CTA can start only where a main CTA has left.
+constexpr int kPadSmem = 55 * 1024;
+
 int main(int argc, char** argv) {
+    CK(cudaFuncSetAttribute(stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPadSmem));
     const int batches = argc > 1 ? std::atoi(argv[1]) : 20;
     const int tail_percent = argc > 2 ? std::atoi(argv[2]) : 8;
     const int tiles_per_warp = argc > 3 ? std::atoi(argv[3]) : 4;
@@ -99,12 +104,13 @@ int main(int argc, char** argv) {
     CK(cudaStreamCreate(&stream));
     std::vector<Mark> m_main(grid), m_tail(tail_grid);
     for (int rep = 0; rep < repeats; ++rep) {
-        stream_kernel<<<grid, 256, 0, stream>>>(in, out, 0, main_tiles, d_main);
+        stream_kernel<<<grid, 256, kPadSmem, stream>>>(in, out, 0, main_tiles, d_main);
         if (tail_grid) {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(tail_grid);
             cfg.blockDim = dim3(256);
             cfg.stream = stream;
+            cfg.dynamicSmemBytes = kPadSmem;
             cudaLaunchAttribute attr[1];
             attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
             attr[0].val.programmaticStreamSerializationAllowed = 1;
