@@ -14,6 +14,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <string>
 #include <vector>
 
 #define CK(x)                                                                                  \
@@ -50,7 +51,7 @@ struct Mark {
 
 __global__ void __launch_bounds__(256, 4)
     stream_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, size_t first_tile, size_t end_tile,
-                  Mark* marks) {
+                  Mark* marks, bool wait_at_end = false) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const size_t total_warps = static_cast<size_t>(gridDim.x) * 8, w = static_cast<size_t>(blockIdx.x) * 8 + warp;
@@ -75,14 +76,70 @@ __global__ void __launch_bounds__(256, 4)
     }
     __syncthreads();
     if (threadIdx.x == 0) marks[blockIdx.x] = Mark{t0, gtime(), smid(), done};
+    if (wait_at_end) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 // 55 KiB of dynamic shared memory per CTA: four CTAs fill an SM, as the dispatch kernel's registers do,
 // so a tail CTA can start only where a main CTA has left.
 constexpr int kPadSmem = 55 * 1024;
 
+// ./tail_probe chain <batches per launch> <launches>: the main grid alone, `launches` times back to back with
+// programmatic stream serialization; prints when each launch's first CTA starts and its last CTA ends.
+int chain(int batches, int launches) {
+    const size_t n = static_cast<size_t>(batches) << 20, n_tiles = n / 32;
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    const int grid = sms * 4;
+    uint4 *in = nullptr, *out = nullptr;
+    Mark* d_marks = nullptr;
+    CK(cudaMalloc(&in, n * 48));
+    CK(cudaMalloc(&out, n * 16));
+    CK(cudaMalloc(&d_marks, static_cast<size_t>(launches) * grid * sizeof(Mark)));
+    CK(cudaMemset(in, 1, n * 48));
+    cudaStream_t stream;
+    CK(cudaStreamCreate(&stream));
+    for (int rep = 0; rep < 2; ++rep) {
+        for (int l = 0; l < launches; ++l) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(grid);
+            cfg.blockDim = dim3(256);
+            cfg.stream = stream;
+            cfg.dynamicSmemBytes = kPadSmem;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = l ? 1 : 0;
+            CK(cudaLaunchKernelEx(&cfg, stream_kernel, static_cast<const uint4*>(in), out, size_t(0), n_tiles,
+                                  d_marks + static_cast<size_t>(l) * grid, true));
+        }
+        CK(cudaStreamSynchronize(stream));
+    }
+    std::vector<Mark> marks(static_cast<size_t>(launches) * grid);
+    CK(cudaMemcpy(marks.data(), d_marks, marks.size() * sizeof(Mark), cudaMemcpyDeviceToHost));
+    unsigned long long t0 = ~0ull, prev_end = 0;
+    for (int i = 0; i < grid; ++i) t0 = std::min(t0, marks[i].start);
+    for (int l = 0; l < launches; ++l) {
+        unsigned long long first = ~0ull, first_end = ~0ull, last_start = 0, last = 0;
+        for (int i = 0; i < grid; ++i) {
+            const Mark& m = marks[static_cast<size_t>(l) * grid + i];
+            first = std::min(first, m.start);
+            last_start = std::max(last_start, m.start);
+            first_end = std::min(first_end, m.end);
+            last = std::max(last, m.end);
+        }
+        std::printf("launch %d: CTAs start %.1f .. %.1f us, end %.1f .. %.1f us; since the previous launch ended: %.1f us "
+                    "= %.2f us per batch\n", l, double(first - t0) / 1e3, double(last_start - t0) / 1e3,
+                    double(first_end - t0) / 1e3, double(last - t0) / 1e3, double(last - (l ? prev_end : t0)) / 1e3,
+                    double(last - (l ? prev_end : t0)) / 1e3 / batches);
+        prev_end = last;
+    }
+    return 0;
+}
+
 int main(int argc, char** argv) {
     CK(cudaFuncSetAttribute(stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPadSmem));
+    if (argc > 3 && std::string(argv[1]) == "chain") return chain(std::atoi(argv[2]), std::atoi(argv[3]));
     const int batches = argc > 1 ? std::atoi(argv[1]) : 20;
     const int tail_percent = argc > 2 ? std::atoi(argv[2]) : 8;
     const int tiles_per_warp = argc > 3 ? std::atoi(argv[3]) : 4;
@@ -104,7 +161,7 @@ int main(int argc, char** argv) {
     CK(cudaStreamCreate(&stream));
     std::vector<Mark> m_main(grid), m_tail(tail_grid);
     for (int rep = 0; rep < repeats; ++rep) {
-        stream_kernel<<<grid, 256, kPadSmem, stream>>>(in, out, 0, main_tiles, d_main);
+        stream_kernel<<<grid, 256, kPadSmem, stream>>>(in, out, 0, main_tiles, d_main, false);
         if (tail_grid) {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(tail_grid);
@@ -116,7 +173,7 @@ int main(int argc, char** argv) {
             attr[0].val.programmaticStreamSerializationAllowed = 1;
             cfg.attrs = attr;
             cfg.numAttrs = 1;
-            CK(cudaLaunchKernelEx(&cfg, stream_kernel, static_cast<const uint4*>(in), out, main_tiles, n_tiles, d_tail));
+            CK(cudaLaunchKernelEx(&cfg, stream_kernel, static_cast<const uint4*>(in), out, main_tiles, n_tiles, d_tail, false));
         }
         CK(cudaStreamSynchronize(stream));
         CK(cudaMemcpy(m_main.data(), d_main, grid * sizeof(Mark), cudaMemcpyDeviceToHost));
