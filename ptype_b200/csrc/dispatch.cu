@@ -1263,8 +1263,9 @@ cudaError_t launch_list(const DeviceImage& img, const LaunchPlan& plan, const Ba
                         cudaStream_t stream, bool pdl);
 }  // namespace
 
-// A lone launch ends with a tail: with equal shares the SMs of a B200 finish up to 20 % apart
-// (tools/spread_probe.cu), and whoever is done early idles until the last one is.  Handing tiles
+// A lone launch ends with a tail: with equal shares the SMs of a B200 finish 4-7 % apart in the
+// pipelined loop and up to 20 % in the unrolled one (tools/tail_probe.cu, tools/spread_probe.cu),
+// and whoever is done early idles until the last one is.  Handing tiles
 // out through counters costs more than it saves once launches follow each other
 // (profiles/r02_tile_scheduling.txt), so the hardware's own block scheduler does it, for the end of
 // the launch only: a list of 2..kTailMaxBatches batches with a small table is cut in two, the first
